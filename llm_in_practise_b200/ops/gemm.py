@@ -1,0 +1,155 @@
+"""K1/K3 — GEMM on the tcgen05 tensor cores (``csrc/gemm_tcgen05.cu``), with a PyTorch oracle.
+
+``gemm`` is the single entry point: ``D = alpha * A @ B^T (+ A2 @ B2^T) (+ bias) + beta * D`` where A is
+logically ``[.., M, K]`` and B logically ``[.., N, K]``; either may be handed over *stored transposed*
+(``a_mn`` / ``b_mn``) so that the three products of a linear layer read their operands in place:
+
+    forward  y  = x  W^T   -> gemm(x,  W)
+    dgrad    dx = dy W     -> gemm(dy, W, b_mn=True)
+    wgrad    dW = dy^T x   -> gemm(dy, x, a_mn=True, b_mn=True)
+
+Replaces the cuBLAS calls behind ``nn.Linear`` / ``torch.matmul`` in every reference script
+(e.g. LLM_Distributed_Trainning/PyTorch/ddp_basics/ddp_gpt_wikitext2.py:86-165) and the three small
+GEMMs of peft's LoRA layer (Fine-Tuning/qwen3-8b-lora-dist.py:118-125).
+"""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional, Tuple
+
+import torch
+
+from . import _native as nv
+
+
+def _as4d(t: torch.Tensor) -> torch.Tensor:
+    while t.dim() < 4:
+        t = t.unsqueeze(0)
+    if t.dim() != 4:
+        raise ValueError("gemm operands must have at most 4 dims")
+    return t
+
+
+def _ref_gemm(a, b, a_mn, b_mn, out, out_dtype, alpha, beta, bias, lora):
+    A = a.transpose(-1, -2) if a_mn else a
+    B = b.transpose(-1, -2) if b_mn else b
+    if A.dim() > 2 and B.dim() > 2 and A.shape[-3] != B.shape[-3]:  # grouped (GQA) batch
+        rep = A.shape[-3] // B.shape[-3]
+        B = B.repeat_interleave(rep, dim=-3)
+    acc = torch.matmul(A.float(), B.float().transpose(-1, -2))
+    if lora is not None:
+        acc = acc + torch.matmul(lora[0].float(), lora[1].float().t())
+    acc = acc * alpha
+    if bias is not None:
+        acc = acc + bias.float()
+    if beta != 0.0:
+        acc = acc + beta * out.float()
+    res = acc.to(out_dtype)
+    if out is not None:
+        out.copy_(res)
+        return out
+    return res
+
+
+def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+         out: Optional[torch.Tensor] = None, out_dtype: Optional[torch.dtype] = None,
+         alpha: float = 1.0, beta: float = 0.0, bias: Optional[torch.Tensor] = None,
+         lora: Optional[Tuple[torch.Tensor, torch.Tensor]] = None) -> torch.Tensor:
+    """See module docstring. ``a``/``b`` are the *stored* tensors (last dim contiguous); leading dims
+    (up to two) are batch dims with arbitrary strides; ``b`` may have fewer batch entries in its
+    inner batch dim (an integer divisor: grouped-query attention)."""
+    if a.dtype != b.dtype:
+        raise TypeError("gemm operands must share a dtype")
+    if out_dtype is None:
+        out_dtype = out.dtype if out is not None else a.dtype
+    if beta != 0.0 and out is None:
+        raise ValueError("beta != 0 needs `out`")
+    if not nv.use_native(a):
+        return _ref_gemm(a, b, a_mn, b_mn, out, out_dtype, alpha, beta, bias, lora)
+
+    if a.dtype == torch.float32 and (a_mn or b_mn):
+        # the tf32 path only takes K-major operands: materialise the transposes (cold path —
+        # fp32 training is the reference's teaching configuration, bf16 is the fast one)
+        if a_mn:
+            a, a_mn = a.transpose(-1, -2).contiguous(), False
+        if b_mn:
+            b, b_mn = b.transpose(-1, -2).contiguous(), False
+    if a.stride(-1) != 1:
+        a = a.contiguous()
+    if b.stride(-1) != 1:
+        b = b.contiguous()
+    a4, b4 = _as4d(a), _as4d(b)
+    if a_mn:
+        K, M = a4.shape[-2], a4.shape[-1]
+    else:
+        M, K = a4.shape[-2], a4.shape[-1]
+    if b_mn:
+        Kb, N = b4.shape[-2], b4.shape[-1]
+    else:
+        N, Kb = b4.shape[-2], b4.shape[-1]
+    if K != Kb:
+        raise ValueError(f"contraction mismatch: {K} vs {Kb}")
+    nb1, nb0 = a4.shape[0], a4.shape[1]
+    if b4.shape[0] not in (nb1, 1) and nb1 != 1:
+        raise ValueError("outer batch dims must match")
+    if nb0 % b4.shape[1] != 0:
+        raise ValueError("inner batch of b must divide inner batch of a")
+    b_div = nb0 // b4.shape[1]
+    if b4.shape[0] == 1 and nb1 > 1:
+        b4 = b4.expand(nb1, *b4.shape[1:])
+    batch = nb0 * nb1
+
+    out_shape = (*a.shape[:-2], M, N)
+    if out is None:
+        out = torch.empty(out_shape, dtype=out_dtype, device=a.device)
+    elif tuple(out.shape) != tuple(out_shape) or out.stride(-1) != 1:
+        raise ValueError(f"`out` must have shape {out_shape} with a contiguous last dim")
+    d4 = _as4d(out)
+
+    args = nv.GemmArgs()
+    args.A, args.B, args.D = a4.data_ptr(), b4.data_ptr(), d4.data_ptr()
+    args.bias = 0 if bias is None else bias.data_ptr()
+    args.bias_dtype = nv.dtype_code(bias.dtype) if bias is not None else 0
+    args.M, args.N, args.K = M, N, K
+    args.batch, args.nb0, args.b_div = batch, nb0, b_div
+    args.a_rs, args.a_bs0, args.a_bs1 = a4.stride(2), a4.stride(1) if nb0 > 1 else 0, a4.stride(0) if nb1 > 1 else 0
+    args.b_rs = b4.stride(2)
+    args.b_bs0 = b4.stride(1) if b4.shape[1] > 1 else 0
+    args.b_bs1 = b4.stride(0) if nb1 > 1 else 0
+    args.d_rs, args.d_bs0, args.d_bs1 = d4.stride(2), d4.stride(1) if nb0 > 1 else 0, d4.stride(0) if nb1 > 1 else 0
+    args.a_mn, args.b_mn = int(a_mn), int(b_mn)
+    args.in_dtype, args.out_dtype = nv.dtype_code(a.dtype), nv.dtype_code(out.dtype)
+    args.alpha, args.beta = alpha, beta
+    keep = None
+    if lora is not None:
+        a2, b2 = lora
+        if a2.dtype != a.dtype or b2.dtype != a.dtype:
+            raise TypeError("lora operands must match the main dtype")
+        a2 = a2 if a2.stride(-1) == 1 else a2.contiguous()
+        b2 = b2 if b2.stride(-1) == 1 else b2.contiguous()
+        keep = (a2, b2)
+        args.A2, args.B2, args.K2 = a2.data_ptr(), b2.data_ptr(), a2.shape[-1]
+        args.a2_rs, args.b2_rs = a2.stride(0), b2.stride(0)
+    else:
+        args.A2 = args.B2 = 0
+        args.K2 = 0
+    rc = nv.lib().b200_gemm(ctypes.byref(args), nv.stream())
+    nv.check(rc, f"gemm M={M} N={N} K={K} batch={batch}")
+    nv.count_launch()
+    del keep
+    return out
+
+
+def linear_fwd(x, w, bias=None, lora=None, out=None, out_dtype=None):
+    """y[M,N] = x[M,K] @ w[N,K]^T (+ bias) (+ lora)."""
+    return gemm(x, w, bias=bias, lora=lora, out=out, out_dtype=out_dtype)
+
+
+def linear_dgrad(dy, w, out=None, beta=0.0, out_dtype=None):
+    """dx[M,K] = dy[M,N] @ w[N,K]."""
+    return gemm(dy, w, b_mn=True, out=out, beta=beta, out_dtype=out_dtype)
+
+
+def linear_wgrad(dy, x, out=None, beta=0.0, out_dtype=None):
+    """dw[N,K] = dy[M,N]^T @ x[M,K]  (beta=1 accumulates into an existing gradient)."""
+    return gemm(dy, x, a_mn=True, b_mn=True, out=out, beta=beta, out_dtype=out_dtype)

@@ -1,0 +1,103 @@
+"""K1/K3 GEMM: tcgen05 kernel vs a plain fp32 PyTorch reference of the same product."""
+import pytest
+import torch
+
+from llm_in_practise_b200.ops import gemm as G
+
+
+def _ref(a, b, a_mn=False, b_mn=False):
+    A = a.transpose(-1, -2) if a_mn else a
+    B = b.transpose(-1, -2) if b_mn else b
+    return A.float() @ B.float().transpose(-1, -2)
+
+
+def test_cpu_fallback_matches_reference():
+    x = torch.randn(37, 48)
+    w = torch.randn(29, 48)
+    y = G.gemm(x, w)
+    assert torch.allclose(y, x @ w.t(), atol=1e-5)
+    dy = torch.randn(37, 29)
+    assert torch.allclose(G.linear_dgrad(dy, w), dy @ w, atol=1e-5)
+    assert torch.allclose(G.linear_wgrad(dy, x), dy.t() @ x, atol=1e-4)
+
+
+def _check(out, ref, tol):
+    err = (out.float() - ref).abs().max().item()
+    scale = ref.abs().max().item() + 1e-6
+    assert err / scale < tol, f"rel err {err / scale:.3e} (abs {err:.3e})"
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K", [(128, 256, 64), (256, 512, 128), (1024, 5120, 5120), (1000, 1000, 520),
+                                   (77, 40, 72), (4096, 30528, 768), (128, 32, 4096)])
+def test_gemm_bf16_kmajor(M, N, K):
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / K ** 0.5
+    y = G.gemm(x, w)
+    _check(y, _ref(x, w), 2e-2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K", [(256, 512, 384), (1024, 5120, 1024), (515, 200, 136)])
+def test_gemm_bf16_dgrad_wgrad(M, N, K):
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / K ** 0.5
+    dy = torch.randn(M, N, device="cuda", dtype=torch.bfloat16)
+    dx = G.linear_dgrad(dy, w)
+    _check(dx, dy.float() @ w.float(), 2e-2)
+    dw = G.linear_wgrad(dy, x, out_dtype=torch.float32)
+    _check(dw, dy.float().t() @ x.float(), 2e-2)
+    # accumulate into an existing gradient (beta = 1)
+    dw2 = dw.clone()
+    G.linear_wgrad(dy, x, out=dw2, beta=1.0)
+    _check(dw2, 2 * (dy.float().t() @ x.float()), 2e-2)
+
+
+@pytest.mark.gpu
+def test_gemm_fp32_tf32():
+    M, N, K = 512, 768, 264
+    x = torch.randn(M, K, device="cuda")
+    w = torch.randn(N, K, device="cuda") / K ** 0.5
+    dy = torch.randn(M, N, device="cuda")
+    _check(G.gemm(x, w), x @ w.t(), 5e-3)
+    _check(G.linear_dgrad(dy, w), dy @ w, 5e-3)
+    _check(G.linear_wgrad(dy, x), dy.t() @ x, 5e-3)
+
+
+@pytest.mark.gpu
+def test_gemm_bias_alpha_fp16():
+    M, N, K = 300, 260, 192
+    x = torch.randn(M, K, device="cuda", dtype=torch.float16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.float16) / K ** 0.5
+    bias = torch.randn(N, device="cuda", dtype=torch.float16)
+    y = G.gemm(x, w, bias=bias, alpha=0.5)
+    _check(y, 0.5 * (x.float() @ w.float().t()) + bias.float(), 1e-2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("r", [8, 16, 64])
+def test_gemm_lora_extra_kblock(r):
+    M, N, K = 1024, 1536, 1024
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    w = torch.randn(N, K, device="cuda", dtype=torch.bfloat16) / K ** 0.5
+    t = torch.randn(M, r, device="cuda", dtype=torch.bfloat16)
+    lb = torch.randn(N, r, device="cuda", dtype=torch.bfloat16)
+    y = G.gemm(x, w, lora=(t, lb))
+    _check(y, x.float() @ w.float().t() + t.float() @ lb.float().t(), 2e-2)
+
+
+@pytest.mark.gpu
+def test_gemm_batched_gqa_strided():
+    # attention-shaped: Q [B,S,H,D] view, K [B,S,Hkv,D] view, scores[b,h] = Q K^T; then P V (b_mn)
+    B, S, H, Hkv, D = 2, 256, 8, 2, 128
+    qkv = torch.randn(B, S, (H + 2 * Hkv) * D, device="cuda", dtype=torch.bfloat16)
+    q = qkv[..., : H * D].view(B, S, H, D).permute(0, 2, 1, 3)
+    k = qkv[..., H * D:(H + Hkv) * D].view(B, S, Hkv, D).permute(0, 2, 1, 3)
+    v = qkv[..., (H + Hkv) * D:].view(B, S, Hkv, D).permute(0, 2, 1, 3)
+    s = G.gemm(q, k, alpha=D ** -0.5, out_dtype=torch.float32)
+    kr = k.repeat_interleave(H // Hkv, dim=1)
+    vr = v.repeat_interleave(H // Hkv, dim=1)
+    _check(s, (q.float() @ kr.float().transpose(-1, -2)) * D ** -0.5, 2e-2)
+    p = torch.softmax(s, dim=-1).to(torch.bfloat16)
+    o = G.gemm(p, v, b_mn=True)
+    _check(o, p.float() @ vr.float(), 2e-2)
