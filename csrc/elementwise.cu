@@ -63,15 +63,19 @@ template <typename T>
 __global__ void __launch_bounds__(256)
 qknorm_rope_fwd_kernel(const T* __restrict__ src, T* __restrict__ dst, const T* __restrict__ qw,
                        const T* __restrict__ kw, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
-                       const int* __restrict__ pos, int tokens, int n_q, int n_k, int D, long long src_rs,
+                       const int* __restrict__ pos, int tokens, int n_q, int n_k, int n_v, int D, long long src_rs,
                        long long dst_rs, int interleaved, float eps, float* __restrict__ rstd_out) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  const int heads = n_q + n_k;
+  const int heads = n_q + n_k + n_v;
   if (warp >= tokens * heads) return;
   const int tok = warp / heads, head = warp - tok * heads;
   const T* s = src + (long long)tok * src_rs + (long long)head * D;
   T* d = dst + (long long)tok * dst_rs + (long long)head * D;
+  if (head >= n_q + n_k) {  // v heads ride along unchanged so the consumer reads one tensor
+    for (int i = lane; i < D; i += 32) d[i] = s[i];
+    return;
+  }
   const T* w = head < n_q ? qw : kw;
   const int half = D >> 1;
   const int p = pos[tok];
@@ -121,16 +125,20 @@ __global__ void __launch_bounds__(256)
 qknorm_rope_bwd_kernel(const T* __restrict__ g_in, const T* __restrict__ raw, T* __restrict__ g_out,
                        const T* __restrict__ qw, const T* __restrict__ kw, const float* __restrict__ cos_t,
                        const float* __restrict__ sin_t, const int* __restrict__ pos, int tokens, int n_q, int n_k,
-                       int D, long long g_rs, long long raw_rs, long long out_rs, int interleaved, float eps,
+                       int n_v, int D, long long g_rs, long long raw_rs, long long out_rs, int interleaved, float eps,
                        float* __restrict__ dwq, float* __restrict__ dwk) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
-  const int heads = n_q + n_k;
+  const int heads = n_q + n_k + n_v;
   if (warp >= tokens * heads) return;
   const int tok = warp / heads, head = warp - tok * heads;
   const T* g = g_in + (long long)tok * g_rs + (long long)head * D;
   const T* x = raw + (long long)tok * raw_rs + (long long)head * D;
   T* o = g_out + (long long)tok * out_rs + (long long)head * D;
+  if (head >= n_q + n_k) {
+    for (int i = lane; i < D; i += 32) o[i] = g[i];
+    return;
+  }
   const T* w = head < n_q ? qw : kw;
   float* dw = head < n_q ? dwq : dwk;
   const int half = D >> 1;
@@ -360,15 +368,15 @@ B200_API int b200_dropout(const void* x, void* y, long long n, unsigned long lon
 }
 
 B200_API int b200_qknorm_rope_fwd(const void* src, void* dst, const void* qw, const void* kw, const float* cos_t,
-                                  const float* sin_t, const int* pos, int tokens, int n_q, int n_k, int D,
+                                  const float* sin_t, const int* pos, int tokens, int n_q, int n_k, int n_v, int D,
                                   long long src_rs, long long dst_rs, int interleaved, float eps, float* rstd_out,
                                   int dtype, void* stream) {
   if (D > 128 || (D & 1) || tokens <= 0) return B200_ERR_BAD_SHAPE;
-  const long long warps = (long long)tokens * (n_q + n_k);
+  const long long warps = (long long)tokens * (n_q + n_k + n_v);
   const int tb = 256;
   const unsigned grid = (unsigned)((warps * 32 + tb - 1) / tb);
   B200_DISPATCH_T(dtype, qknorm_rope_fwd_kernel<T><<<grid, tb, 0, (cudaStream_t)stream>>>(
-      (const T*)src, (T*)dst, (const T*)qw, (const T*)kw, cos_t, sin_t, pos, tokens, n_q, n_k, D, src_rs, dst_rs,
+      (const T*)src, (T*)dst, (const T*)qw, (const T*)kw, cos_t, sin_t, pos, tokens, n_q, n_k, n_v, D, src_rs, dst_rs,
       interleaved, eps, rstd_out));
   B200_LAUNCH_CHECK();
   return 0;
@@ -376,14 +384,14 @@ B200_API int b200_qknorm_rope_fwd(const void* src, void* dst, const void* qw, co
 
 B200_API int b200_qknorm_rope_bwd(const void* g_in, const void* raw, void* g_out, const void* qw, const void* kw,
                                   const float* cos_t, const float* sin_t, const int* pos, int tokens, int n_q, int n_k,
-                                  int D, long long g_rs, long long raw_rs, long long out_rs, int interleaved, float eps,
-                                  float* dwq, float* dwk, int dtype, void* stream) {
+                                  int n_v, int D, long long g_rs, long long raw_rs, long long out_rs, int interleaved,
+                                  float eps, float* dwq, float* dwk, int dtype, void* stream) {
   if (D > 128 || (D & 1) || tokens <= 0) return B200_ERR_BAD_SHAPE;
-  const long long warps = (long long)tokens * (n_q + n_k);
+  const long long warps = (long long)tokens * (n_q + n_k + n_v);
   const int tb = 256;
   const unsigned grid = (unsigned)((warps * 32 + tb - 1) / tb);
   B200_DISPATCH_T(dtype, qknorm_rope_bwd_kernel<T><<<grid, tb, 0, (cudaStream_t)stream>>>(
-      (const T*)g_in, (const T*)raw, (T*)g_out, (const T*)qw, (const T*)kw, cos_t, sin_t, pos, tokens, n_q, n_k, D,
+      (const T*)g_in, (const T*)raw, (T*)g_out, (const T*)qw, (const T*)kw, cos_t, sin_t, pos, tokens, n_q, n_k, n_v, D,
       g_rs, raw_rs, out_rs, interleaved, eps, dwq, dwk));
   B200_LAUNCH_CHECK();
   return 0;

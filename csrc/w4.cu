@@ -1,0 +1,248 @@
+// K2 / K14 — 4-bit weight kernels shared by NF4 (QLoRA) and GPTQ/AWQ (W4A16).
+//
+// One storage convention serves both families: packed[N, K/2] bytes with K contiguous, element 2j
+// in the high nibble and 2j+1 in the low nibble (that IS the bitsandbytes NF4 layout; GPTQ and
+// compressed-tensors checkpoints are repacked into it once at load time), one fp32 scale per
+// `group` consecutive K values, an optional fp32 "zero * scale" term per group, and a 16-entry
+// code book:      w[n, k] = lut[q[n, k]] * scale[n, k / group] - zs[n, k / group]
+//   NF4      : lut = the NormalFloat4 table, group 64, scale = absmax, zs = 0
+//   GPTQ/AWQ : lut = 0..15, group 128, scale = s, zs = zero_point * s  (symmetric: zero_point = 8)
+//
+// Kernels: NF4 quantise (+ nested "double quant" absmax decode), dequantise to bf16/fp16 (feeds the
+// tcgen05 GEMM for large M; reads shards straight from peer GPUs when given several base pointers,
+// which is the ZeRO-3 parameter all-gather fused into the first consumer), and a fused small-M GEMV
+// for decode (memory-bound: 4.25 bits per weight on the wire instead of 16).
+//
+// Replaces bitsandbytes kQuantizeBlockwise / kDequantizeBlockwise / kgemm_4bit_inference_naive
+// (Fine-Tuning/qwen3-14b-qlora-dist-deepspeed.py:101-106) and the Marlin / ExLlama / AWQ kernels that
+// gptqmodel and vLLM dispatch to (Quantization/GPTQModel/inference_qwen3_4b_gptq.py:29,
+// Quantization/LLM-Compressor/AWQ/eval_qwen3_4b_awq.py:11-21).
+#include "common.cuh"
+#include "../include/b200_ops.h"
+
+namespace b200 {
+
+__constant__ float kNF4[16] = {-1.0f, -0.6961928009986877f, -0.5250730514526367f, -0.39491748809814453f,
+                               -0.28444138169288635f, -0.18477343022823334f, -0.09105003625154495f, 0.0f,
+                               0.07958029955625534f, 0.16093020141124725f, 0.24611230194568634f,
+                               0.33791524171829224f, 0.44070982933044434f, 0.5626170039176941f,
+                               0.7229568362236023f, 1.0f};
+
+// nearest NF4 code for x in [-1, 1] (ties resolved like a midpoint decision tree)
+__device__ __forceinline__ uint32_t nf4_encode(float x) {
+  uint32_t best = 0;
+  float bd = fabsf(x - kNF4[0]);
+#pragma unroll
+  for (int i = 1; i < 16; ++i) {
+    const float d = fabsf(x - kNF4[i]);
+    if (d < bd) { bd = d; best = i; }
+  }
+  return best;
+}
+
+// One warp per 64-value block: lane l owns values 2l and 2l+1 -> one packed byte.
+template <typename T>
+__global__ void __launch_bounds__(256)
+nf4_quantize_kernel(const T* __restrict__ w, uint8_t* __restrict__ packed, float* __restrict__ absmax,
+                    long long nblocks) {
+  const long long blk = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (blk >= nblocks) return;
+  const float a = to_f32<T>(w[blk * 64 + 2 * lane]);
+  const float b = to_f32<T>(w[blk * 64 + 2 * lane + 1]);
+  const float am = warp_max(fmaxf(fabsf(a), fabsf(b)));
+  const float inv = am > 0.f ? 1.f / am : 0.f;
+  const uint32_t qa = nf4_encode(a * inv), qb = nf4_encode(b * inv);
+  packed[blk * 32 + lane] = (uint8_t)((qa << 4) | qb);
+  if (lane == 0) absmax[blk] = am;
+}
+
+// nested quantisation of absmax (bitsandbytes "double quant"): absmax = code2[q] * absmax2[i / 256] + offset
+__global__ void nf4_absmax_decode_kernel(const uint8_t* __restrict__ q, const float* __restrict__ code2,
+                                         const float* __restrict__ absmax2, float offset, float* __restrict__ out,
+                                         long long n) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = code2[q[i]] * absmax2[i >> 8] + offset;
+}
+
+struct W4Shards {
+  const uint8_t* packed[8];
+  const float* scale[8];
+  const float* zs[8];
+  long long rows_per_shard;  // shard s holds rows [s * rows_per_shard, (s+1) * rows_per_shard)
+  int nshards;
+};
+
+// Each thread expands 16 packed bytes (32 weights). K % 32 == 0, group % 32 == 0.
+template <typename T>
+__global__ void __launch_bounds__(256)
+w4_dequant_kernel(W4Shards sh, T* __restrict__ out, long long N, int K, int group, const float* __restrict__ lut_g,
+                  long long out_rs) {
+  __shared__ float lut[16];
+  if (threadIdx.x < 16) lut[threadIdx.x] = lut_g ? lut_g[threadIdx.x] : kNF4[threadIdx.x];
+  __syncthreads();
+  const int chunks_per_row = K / 32;
+  const long long cid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (cid >= N * chunks_per_row) return;
+  const long long n = cid / chunks_per_row;
+  const int kc = (int)(cid - n * chunks_per_row);
+  const int s = sh.nshards > 1 ? (int)(n / sh.rows_per_shard) : 0;
+  const long long nl = n - (long long)s * sh.rows_per_shard;
+  const uint4 raw = *reinterpret_cast<const uint4*>(sh.packed[s] + (nl * K / 2) + kc * 16);
+  const int g = (kc * 32) / group;
+  const int groups_per_row = K / group;
+  const float sc = sh.scale[s][nl * groups_per_row + g];
+  const float zs = sh.zs[s] ? sh.zs[s][nl * groups_per_row + g] : 0.f;
+  const uint32_t words[4] = {raw.x, raw.y, raw.z, raw.w};
+  T* o = out + n * out_rs + kc * 32;
+#pragma unroll
+  for (int wi = 0; wi < 4; ++wi) {
+    float v[8];
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const uint32_t byte = (words[wi] >> (8 * b)) & 0xFFu;
+      v[2 * b] = lut[byte >> 4] * sc - zs;
+      v[2 * b + 1] = lut[byte & 15u] * sc - zs;
+    }
+    uint4 ov;
+    T* oe = reinterpret_cast<T*>(&ov);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) oe[j] = from_f32<T>(v[j]);
+    *reinterpret_cast<uint4*>(o + wi * 8) = ov;
+  }
+}
+
+// y[m, n] = sum_k x[m, k] * w[n, k] for m < M <= 8: one warp per output column n.
+template <typename T, int kMaxM>
+__global__ void __launch_bounds__(256)
+w4_gemv_kernel(const T* __restrict__ x, const uint8_t* __restrict__ packed, const float* __restrict__ scale,
+               const float* __restrict__ zsp, const float* __restrict__ lut_g, const T* __restrict__ bias,
+               T* __restrict__ y, int M, long long N, int K, int group, long long x_rs, long long y_rs) {
+  extern __shared__ uint8_t smem_raw[];
+  T* xs = reinterpret_cast<T*>(smem_raw);  // [M, K]
+  __shared__ float lut[16];
+  if (threadIdx.x < 16) lut[threadIdx.x] = lut_g ? lut_g[threadIdx.x] : kNF4[threadIdx.x];
+  for (int i = threadIdx.x * 8; i < M * K; i += blockDim.x * 8) {
+    const int m = i / K, k = i - m * K;
+    *reinterpret_cast<uint4*>(xs + i) = *reinterpret_cast<const uint4*>(x + (long long)m * x_rs + k);
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long n = (long long)blockIdx.x * (blockDim.x >> 5) + warp;
+  if (n >= N) return;
+  const int groups_per_row = K / group;
+  float acc[kMaxM];
+#pragma unroll
+  for (int m = 0; m < kMaxM; ++m) acc[m] = 0.f;
+  const uint8_t* pr = packed + n * (K / 2);
+  for (int kc = lane; kc < K / 32; kc += 32) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(pr + kc * 16);
+    const int g = (kc * 32) / group;
+    const float sc = scale[n * groups_per_row + g];
+    const float zs = zsp ? zsp[n * groups_per_row + g] : 0.f;
+    const uint32_t words[4] = {raw.x, raw.y, raw.z, raw.w};
+    float wv[32];
+#pragma unroll
+    for (int wi = 0; wi < 4; ++wi)
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const uint32_t byte = (words[wi] >> (8 * b)) & 0xFFu;
+        wv[wi * 8 + 2 * b] = lut[byte >> 4] * sc - zs;
+        wv[wi * 8 + 2 * b + 1] = lut[byte & 15u] * sc - zs;
+      }
+#pragma unroll
+    for (int m = 0; m < kMaxM; ++m) {
+      if (m < M) {
+        const T* xr = xs + m * K + kc * 32;
+        float a = 0.f;
+#pragma unroll
+        for (int v8 = 0; v8 < 4; ++v8) {
+          const uint4 xv = *reinterpret_cast<const uint4*>(xr + v8 * 8);
+          const T* xe = reinterpret_cast<const T*>(&xv);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) a += to_f32<T>(xe[j]) * wv[v8 * 8 + j];
+        }
+        acc[m] += a;
+      }
+    }
+  }
+#pragma unroll
+  for (int m = 0; m < kMaxM; ++m) {
+    if (m < M) {
+      const float r = warp_sum(acc[m]);
+      if (lane == 0) y[(long long)m * y_rs + n] = from_f32<T>(r + (bias ? to_f32<T>(bias[n]) : 0.f));
+    }
+  }
+}
+
+}  // namespace b200
+using namespace b200;
+
+B200_API int b200_nf4_quantize(const void* w, uint8_t* packed, float* absmax, long long n, int dtype, void* stream) {
+  if (n <= 0 || n % 64) return B200_ERR_BAD_SHAPE;
+  const long long nblocks = n / 64;
+  const int tb = 256;
+  const unsigned grid = (unsigned)((nblocks * 32 + tb - 1) / tb);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_DT_BF16) nf4_quantize_kernel<__nv_bfloat16><<<grid, tb, 0, st>>>((const __nv_bfloat16*)w, packed, absmax, nblocks);
+  else if (dtype == B200_DT_FP32) nf4_quantize_kernel<float><<<grid, tb, 0, st>>>((const float*)w, packed, absmax, nblocks);
+  else if (dtype == B200_DT_FP16) nf4_quantize_kernel<__half><<<grid, tb, 0, st>>>((const __half*)w, packed, absmax, nblocks);
+  else return B200_ERR_UNSUPPORTED;
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_nf4_absmax_decode(const uint8_t* q, const float* code2, const float* absmax2, float offset,
+                                    float* out, long long n, void* stream) {
+  if (n <= 0) return 0;
+  nf4_absmax_decode_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(q, code2, absmax2, offset, out, n);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// packed/scale/zs: arrays of `nshards` device pointers (peer-mapped pointers allowed); zs entries may be NULL.
+B200_API int b200_w4_dequant(const void* const* packed, const void* const* scale, const void* const* zs, int nshards,
+                             long long rows_per_shard, void* out, long long N, int K, int group, const float* lut,
+                             long long out_rs, int out_dtype, void* stream) {
+  if (nshards < 1 || nshards > 8 || K % 32 || group % 32 || K % group) return B200_ERR_BAD_SHAPE;
+  W4Shards sh;
+  for (int i = 0; i < 8; ++i) {
+    sh.packed[i] = i < nshards ? (const uint8_t*)packed[i] : nullptr;
+    sh.scale[i] = i < nshards ? (const float*)scale[i] : nullptr;
+    sh.zs[i] = (i < nshards && zs) ? (const float*)zs[i] : nullptr;
+  }
+  sh.rows_per_shard = rows_per_shard;
+  sh.nshards = nshards;
+  const long long chunks = N * (K / 32);
+  const unsigned grid = (unsigned)((chunks + 255) / 256);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (out_dtype == B200_DT_BF16) w4_dequant_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(sh, (__nv_bfloat16*)out, N, K, group, lut, out_rs);
+  else if (out_dtype == B200_DT_FP16) w4_dequant_kernel<__half><<<grid, 256, 0, st>>>(sh, (__half*)out, N, K, group, lut, out_rs);
+  else return B200_ERR_UNSUPPORTED;
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_w4_gemv(const void* x, const uint8_t* packed, const float* scale, const float* zs, const float* lut,
+                          const void* bias, void* y, int M, long long N, int K, int group, long long x_rs,
+                          long long y_rs, int dtype, void* stream) {
+  if (M < 1 || M > 8 || K % 32 || group % 32 || K % group || x_rs % 8) return B200_ERR_BAD_SHAPE;
+  const int smem = M * K * 2;
+  if (smem > 200 * 1024) return B200_ERR_TOO_LARGE;
+  const int tb = 256, wpb = tb / 32;
+  const unsigned grid = (unsigned)((N + wpb - 1) / wpb);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_DT_BF16) {
+    static int cfg = 0;
+    if (cfg < smem) { B200_CHECK(cudaFuncSetAttribute(w4_gemv_kernel<__nv_bfloat16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); cfg = 200 * 1024; }
+    w4_gemv_kernel<__nv_bfloat16, 8><<<grid, tb, smem, st>>>((const __nv_bfloat16*)x, packed, scale, zs, lut, (const __nv_bfloat16*)bias, (__nv_bfloat16*)y, M, N, K, group, x_rs, y_rs);
+  } else if (dtype == B200_DT_FP16) {
+    static int cfg = 0;
+    if (cfg < smem) { B200_CHECK(cudaFuncSetAttribute(w4_gemv_kernel<__half, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024)); cfg = 200 * 1024; }
+    w4_gemv_kernel<__half, 8><<<grid, tb, smem, st>>>((const __half*)x, packed, scale, zs, lut, (const __half*)bias, (__half*)y, M, N, K, group, x_rs, y_rs);
+  } else {
+    return B200_ERR_UNSUPPORTED;
+  }
+  B200_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,143 @@
+"""K4 — causal / sliding-window / bidirectional multi-head attention with grouped KV heads.
+
+Two native paths share this front end:
+
+* ``flash`` (``csrc/flash_attn.cu``, when built and the shape qualifies): tcgen05 QK^T and PV with the
+  score tile living in TMEM, online softmax, no L x L tensor in memory.
+* ``tiled`` (always available): batched tcgen05 GEMMs (``csrc/gemm_tcgen05.cu``) around fused
+  masked-softmax kernels (``csrc/loss.cu``); scores exist per (batch, head) as a transient.
+
+Both read q, k and v *in place* from the fused qkv projection ``[tokens, (H + 2 Hkv) * D]`` through
+strided TMA descriptors — no head transposes, no ``repeat_kv`` — and write the context as
+``[tokens, H * D]`` ready for the output projection. The causal mask is implicit; the reference
+builds an L x L boolean mask on every forward (ddp_gpt_wikitext2.py:93-95) and HF Qwen3 relies on
+SDPA / flash-attn behind ``AutoModelForCausalLM`` (Fine-Tuning/*.py).
+"""
+from __future__ import annotations
+
+import ctypes
+import math
+from typing import Optional
+
+import torch
+
+from . import _native as nv
+from .gemm import gemm
+
+vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+
+
+def _softmax_fwd(scores, causal, window, out_dtype):
+    *lead, rows, cols = scores.shape
+    batch = 1
+    for d in lead:
+        batch *= d
+    P = torch.empty(scores.shape, dtype=out_dtype, device=scores.device)
+    fn = nv.proto("b200_softmax_fwd", [vp, vp, i64, i32, i32, i32, i32, f32, i32, i32, vp])
+    nv.check(fn(nv.ptr(scores), nv.ptr(P), batch, rows, cols, int(causal), int(window), 1.0,
+                nv.dtype_code(scores.dtype), nv.dtype_code(out_dtype), nv.stream()), "softmax_fwd")
+    nv.count_launch()
+    return P
+
+
+def _softmax_bwd(P, dP, scale, out_dtype):
+    cols = P.shape[-1]
+    dS = torch.empty(P.shape, dtype=out_dtype, device=P.device)
+    fn = nv.proto("b200_softmax_bwd", [vp, vp, vp, i64, i32, f32, i32, i32, i32, vp])
+    nv.check(fn(nv.ptr(P), nv.ptr(dP), nv.ptr(dS), P.numel() // cols, cols, scale, nv.dtype_code(P.dtype),
+                nv.dtype_code(dP.dtype), nv.dtype_code(out_dtype), nv.stream()), "softmax_bwd")
+    nv.count_launch()
+    return dS
+
+
+def _split_heads(qkv, B, S, H, Hkv, D):
+    """Strided [B, heads, S, D] views of q, k, v inside the fused projection."""
+    t = qkv.view(B, S, H + 2 * Hkv, D)
+    q = t[:, :, :H].permute(0, 2, 1, 3)
+    k = t[:, :, H:H + Hkv].permute(0, 2, 1, 3)
+    v = t[:, :, H + Hkv:].permute(0, 2, 1, 3)
+    return q, k, v
+
+
+class _TiledAttentionFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, qkv, B, S, H, Hkv, D, causal, window, scale, dropout_p):
+        q, k, v = _split_heads(qkv, B, S, H, Hkv, D)
+        scores = gemm(q, k, alpha=scale, out_dtype=torch.float32)            # [B, H, S, S]
+        P = _softmax_fwd(scores, causal, window, qkv.dtype)
+        del scores
+        out = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
+        gemm(P, v, b_mn=True, out=out.permute(0, 2, 1, 3))                   # context, written as [B, S, H, D]
+        ctx.save_for_backward(qkv, P)
+        ctx.cfg = (B, S, H, Hkv, D, scale)
+        return out.view(B * S, H * D)
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, P = ctx.saved_tensors
+        B, S, H, Hkv, D, scale = ctx.cfg
+        g = H // Hkv
+        q, k, v = _split_heads(qkv, B, S, H, Hkv, D)
+        dO = dout.contiguous().view(B, S, H, D).permute(0, 2, 1, 3)         # [B, H, S, D] strided
+        dqkv = torch.empty_like(qkv)
+        dq, dk, dv = _split_heads(dqkv, B, S, H, Hkv, D)
+        dP = gemm(dO, v, out_dtype=torch.float32)                            # [B, H, S, S]
+        dS = _softmax_bwd(P, dP, scale, qkv.dtype)
+        del dP
+        gemm(dS, k, b_mn=True, out=dq)                                       # dQ = dS K
+        if g == 1:
+            gemm(dS, q, a_mn=True, b_mn=True, out=dk)                        # dK = dS^T Q
+            gemm(P, dO, a_mn=True, b_mn=True, out=dv)                        # dV = P^T dO
+        else:
+            dk_h = gemm(dS, q, a_mn=True, b_mn=True, out_dtype=torch.float32)
+            dv_h = gemm(P, dO, a_mn=True, b_mn=True, out_dtype=torch.float32)
+            dk.copy_(dk_h.view(B, Hkv, g, S, D).sum(2))
+            dv.copy_(dv_h.view(B, Hkv, g, S, D).sum(2))
+        return dqkv, None, None, None, None, None, None, None, None, None
+
+
+def _ref_attention(qkv, B, S, H, Hkv, D, causal, window, scale):
+    q, k, v = _split_heads(qkv, B, S, H, Hkv, D)
+    g = H // Hkv
+    kf = k.float().repeat_interleave(g, dim=1)
+    vf = v.float().repeat_interleave(g, dim=1)
+    s = torch.matmul(q.float(), kf.transpose(-1, -2)) * scale
+    if causal:
+        i = torch.arange(S, device=qkv.device)
+        mask = i[None, :] > i[:, None]
+        if window and window > 0:
+            mask = mask | (i[None, :] < i[:, None] - window + 1)
+        s = s.masked_fill(mask, float("-inf"))
+    p = torch.softmax(s, dim=-1)
+    o = torch.matmul(p, vf)
+    return o.permute(0, 2, 1, 3).reshape(B * S, H * D).to(qkv.dtype)
+
+
+_flash_ok = None
+
+
+def _flash_available() -> bool:
+    global _flash_ok
+    if _flash_ok is None:
+        try:
+            _flash_ok = hasattr(nv.lib(), "b200_flash_attn_fwd")
+        except Exception:
+            _flash_ok = False
+    return _flash_ok
+
+
+def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, head_dim: int,
+              causal: bool = True, window: int = 0, scale: Optional[float] = None,
+              impl: str = "auto") -> torch.Tensor:
+    """softmax(Q K^T * scale + mask) V over the fused projection ``qkv`` [B*S, (H + 2 Hkv) * D].
+    Returns the context as [B*S, H * D]."""
+    if scale is None:
+        scale = 1.0 / math.sqrt(head_dim)
+    if not nv.use_native(qkv):
+        return _ref_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale)
+    qkv = qkv.contiguous()
+    if impl in ("auto", "flash") and _flash_available() and qkv.dtype == torch.bfloat16 and head_dim == 128 \
+            and window == 0:
+        from .flash import flash_attention
+        return flash_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, scale)
+    return _TiledAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, 0.0)

@@ -1,0 +1,124 @@
+"""Flat parameter / gradient arenas.
+
+Every trainable tensor of a model lives inside one contiguous buffer per dtype, with its gradient
+at the same offset of a twin buffer (``p.grad`` is pre-assigned as a view, and aliased as
+``p.main_grad`` for the backward kernels that accumulate into it directly). This is what lets the
+optimizer, the gradient-norm scan, the DDP bucket all-reduce and the ZeRO reduce-scatter each be
+ONE kernel launch over a flat range instead of a Python loop over parameters — the role played by
+DeepSpeed's ``contiguous_gradients`` / flat fp32 partitions and by the c10d Reducer's buckets in the
+reference stack (LLM_Distributed_Trainning/DeepSpeed/DeepSpeed-GPTLike-ZeRO-2/ds_config.json:4-12,
+LLM_Distributed_Trainning/PyTorch/ddp_basics/ddp_gpt_wikitext2.py:271-279).
+"""
+from __future__ import annotations
+
+from typing import Dict, Iterable, List, Optional, Tuple
+
+import torch
+from torch import nn
+
+_ALIGN = 64  # elements; 256 B for fp32 — keeps every tensor 16-byte aligned for vector / TMA access
+
+
+def _round_up(n: int, a: int) -> int:
+    return (n + a - 1) // a * a
+
+
+class ParamArena:
+    """Two-phase allocator: ``request`` shapes while building the model, then ``finalize`` once."""
+
+    def __init__(self, dtype: torch.dtype = torch.float32, device=None, pad_to: int = 1):
+        self.dtype = dtype
+        self.device = device
+        self.pad_to = pad_to  # total size is padded to a multiple of this (world size * block for sharding)
+        self._specs: List[Tuple[str, Tuple[int, ...], int]] = []
+        self._size = 0
+        self.data: Optional[torch.Tensor] = None
+        self.grad: Optional[torch.Tensor] = None
+
+    def request(self, name: str, shape) -> int:
+        if self.data is not None:
+            raise RuntimeError("arena already finalised")
+        shape = tuple(int(s) for s in shape)
+        n = 1
+        for s in shape:
+            n *= s
+        off = self._size
+        self._specs.append((name, shape, off))
+        self._size = _round_up(off + n, _ALIGN)
+        return len(self._specs) - 1
+
+    def finalize(self, with_grad: bool = True) -> "ParamArena":
+        total = _round_up(max(self._size, _ALIGN), max(self.pad_to, 1))
+        self.data = torch.zeros(total, dtype=self.dtype, device=self.device)
+        self.grad = torch.zeros(total, dtype=self.dtype, device=self.device) if with_grad else None
+        return self
+
+    @property
+    def numel(self) -> int:
+        return 0 if self.data is None else self.data.numel()
+
+    def view(self, idx: int) -> torch.Tensor:
+        _, shape, off = self._specs[idx]
+        n = 1
+        for s in shape:
+            n *= s
+        return self.data[off:off + n].view(shape)
+
+    def grad_view(self, idx: int) -> torch.Tensor:
+        _, shape, off = self._specs[idx]
+        n = 1
+        for s in shape:
+            n *= s
+        return self.grad[off:off + n].view(shape)
+
+    def parameter(self, idx: int, rows: Optional[Tuple[int, int]] = None, requires_grad: bool = True) -> nn.Parameter:
+        """A Parameter aliasing slot ``idx`` (optionally only rows [lo, hi) of it)."""
+        d = self.view(idx)
+        g = self.grad_view(idx) if self.grad is not None else None
+        if rows is not None:
+            d = d[rows[0]:rows[1]]
+            g = None if g is None else g[rows[0]:rows[1]]
+        p = nn.Parameter(d, requires_grad=requires_grad)
+        if g is not None and requires_grad:
+            p.grad = g
+            p.main_grad = g
+        return p
+
+    def zero_grad(self) -> None:
+        if self.grad is not None:
+            self.grad.zero_()
+
+    def named_slots(self) -> Iterable[Tuple[str, Tuple[int, ...], int]]:
+        return iter(self._specs)
+
+
+def flatten_module(module: nn.Module, dtype: Optional[torch.dtype] = None, device=None,
+                   pad_to: int = 1, only_trainable: bool = True) -> ParamArena:
+    """Re-home the (trainable) parameters of an arbitrary ``nn.Module`` into one arena, in
+    registration order, preserving values; ``p.data`` / ``p.grad`` become views. Tied parameters
+    (the same Parameter object reachable twice) are placed once."""
+    params: List[Tuple[str, nn.Parameter]] = []
+    seen: Dict[int, str] = {}
+    for name, p in module.named_parameters(remove_duplicate=True):
+        if only_trainable and not p.requires_grad:
+            continue
+        if id(p) in seen:
+            continue
+        seen[id(p)] = name
+        params.append((name, p))
+    if not params:
+        raise ValueError("module has no parameters to flatten")
+    dtype = dtype or params[0][1].dtype
+    device = device or params[0][1].device
+    arena = ParamArena(dtype=dtype, device=device, pad_to=pad_to)
+    idxs = [arena.request(n, p.shape) for n, p in params]
+    arena.finalize()
+    with torch.no_grad():
+        for (n, p), i in zip(params, idxs):
+            v = arena.view(i)
+            v.copy_(p.data.to(dtype))
+            p.data = v
+            g = arena.grad_view(i)
+            p.grad = g
+            p.main_grad = g
+    return arena

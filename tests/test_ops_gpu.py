@@ -1,0 +1,225 @@
+"""Numerics of every CUDA kernel vs a plain PyTorch fp32 reference of the same op (SURVEY.md §4:
+"the oracle for every kernel is the plain torch expression the reference script executes")."""
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from llm_in_practise_b200.ops import elementwise as ew
+from llm_in_practise_b200.ops import norm as N
+from llm_in_practise_b200.ops import loss as L
+from llm_in_practise_b200.ops import w4 as W4
+from llm_in_practise_b200.ops import lora as LR
+from llm_in_practise_b200.ops.attention import attention, _ref_attention
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+
+def rel(a, b):
+    return ((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-6)).item()
+
+
+@pytest.mark.parametrize("layer_norm", [False, True])
+@pytest.mark.parametrize("dtype,cols", [(torch.bfloat16, 5120), (torch.bfloat16, 768), (torch.float32, 128)])
+def test_norm_fwd_bwd(layer_norm, dtype, cols):
+    rows = 300
+    x = torch.randn(rows, cols, device=DEV, dtype=dtype, requires_grad=True)
+    r = torch.randn(rows, cols, device=DEV, dtype=dtype, requires_grad=True)
+    w = (1 + 0.1 * torch.randn(cols, device=DEV)).to(dtype).requires_grad_()
+    b = (0.1 * torch.randn(cols, device=DEV)).to(dtype).requires_grad_() if layer_norm else None
+    f = N.layer_norm if layer_norm else N.rms_norm
+    args = (x, w, b, 1e-5, r) if layer_norm else (x, w, 1e-6, r)
+    y, h = f(*args)
+    gy, gh = torch.randn_like(y), torch.randn_like(h)
+    (y * gy).sum().backward(retain_graph=True)
+    (h * gh).sum().backward()
+    got = [y, h, x.grad, r.grad, w.grad] + ([b.grad] if layer_norm else [])
+    # fp32 oracle
+    xf, rf, wf = x.detach().float().requires_grad_(), r.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    bf = b.detach().float().requires_grad_() if layer_norm else None
+    hf = (xf + rf)
+    if layer_norm:
+        yf = F.layer_norm(hf, (cols,), wf, bf, 1e-5)
+    else:
+        yf = hf * torch.rsqrt(hf.pow(2).mean(-1, keepdim=True) + 1e-6) * wf
+    ((yf * gy.float()).sum() + (hf * gh.float()).sum()).backward()
+    want = [yf, hf, xf.grad, rf.grad, wf.grad] + ([bf.grad] if layer_norm else [])
+    tol = 2e-2 if dtype == torch.bfloat16 else 1e-4
+    for g, wnt in zip(got, want):
+        assert rel(g, wnt) < tol
+
+
+@pytest.mark.parametrize("interleaved,D", [(False, 128), (True, 96), (False, 64)])
+def test_qknorm_rope(interleaved, D):
+    T, H, Hkv = 70, 4, 2
+    qkv = torch.randn(T, (H + 2 * Hkv) * D, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    qw = (1 + 0.1 * torch.randn(D, device=DEV)).bfloat16().requires_grad_()
+    kw = (1 + 0.1 * torch.randn(D, device=DEV)).bfloat16().requires_grad_()
+    cos, sin = ew.rope_tables(128, D, 10000.0, DEV)
+    pos = torch.randint(0, 128, (T,), device=DEV, dtype=torch.int32)
+    out = ew.qknorm_rope(qkv, qw, kw, cos, sin, pos, H, Hkv, D, interleaved)
+    g = torch.randn_like(out)
+    (out * g).sum().backward()
+    # oracle in fp32
+    q32 = qkv.detach().float().requires_grad_()
+    qw32, kw32 = qw.detach().float().requires_grad_(), kw.detach().float().requires_grad_()
+    ref_qk = ew._ref_qknorm_rope(q32[:, :(H + Hkv) * D], qw32, kw32, cos, sin, pos, H, Hkv, D, interleaved, 1e-6)
+    ref = torch.cat([ref_qk, q32[:, (H + Hkv) * D:]], dim=1)
+    (ref * g.float()).sum().backward()
+    assert rel(out, ref) < 2e-2
+    assert rel(qkv.grad, q32.grad) < 3e-2
+    assert rel(qw.grad, qw32.grad) < 3e-2
+    assert rel(kw.grad, kw32.grad) < 3e-2
+
+
+def test_swiglu_gelu():
+    gu = torch.randn(257, 2 * 1024, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    h = ew.swiglu(gu)
+    g = torch.randn_like(h)
+    (h * g).sum().backward()
+    g32 = gu.detach().float().requires_grad_()
+    ref = F.silu(g32[:, :1024]) * g32[:, 1024:]
+    (ref * g.float()).sum().backward()
+    assert rel(h, ref) < 2e-2 and rel(gu.grad, g32.grad) < 2e-2
+    x = torch.randn(64, 768, device=DEV, requires_grad=True)
+    y = ew.gelu(x)
+    (y * 2).sum().backward()
+    x2 = x.detach().clone().requires_grad_()
+    (F.gelu(x2) * 2).sum().backward()
+    assert rel(y, F.gelu(x2)) < 1e-5 and rel(x.grad, x2.grad) < 1e-4
+
+
+def test_embedding_and_dropout():
+    table = torch.randn(1000, 256, device=DEV, requires_grad=True)
+    pos = torch.randn(64, 256, device=DEV, requires_grad=True)
+    ids = torch.randint(0, 1000, (4, 64), device=DEV)
+    out = ew.embedding(ids, table, pos)
+    g = torch.randn_like(out)
+    (out * g).sum().backward()
+    t2, p2 = table.detach().clone().requires_grad_(), pos.detach().clone().requires_grad_()
+    ref = F.embedding(ids, t2) + p2
+    (ref * g).sum().backward()
+    assert rel(out, ref) < 1e-6 and rel(table.grad, t2.grad) < 1e-5 and rel(pos.grad, p2.grad) < 1e-5
+    x = torch.randn(1 << 20, device=DEV, requires_grad=True)
+    y = ew.dropout(x, 0.1, True, seed=1234)
+    keep = (y != 0).float().mean().item()
+    assert abs(keep - 0.9) < 5e-3
+    assert torch.allclose(y[y != 0], (x / 0.9)[y != 0])
+    y.sum().backward()
+    assert torch.equal(x.grad != 0, y != 0)
+
+
+@pytest.mark.parametrize("dtype,V", [(torch.bfloat16, 151936), (torch.float32, 30528), (torch.bfloat16, 1000)])
+def test_cross_entropy(dtype, V):
+    M = 96
+    logits = (3 * torch.randn(M, V, device=DEV)).to(dtype).requires_grad_()
+    t = torch.randint(0, V, (M,), device=DEV)
+    t[::7] = -100
+    loss = L.cross_entropy(logits, t)
+    loss.backward()
+    l32 = logits.detach().float().requires_grad_()
+    ref = F.cross_entropy(l32, t, ignore_index=-100)
+    ref.backward()
+    assert abs(loss.item() - ref.item()) < 2e-3 * max(1, abs(ref.item()))
+    assert rel(logits.grad, l32.grad) < (2e-2 if dtype == torch.bfloat16 else 1e-4)
+
+
+def test_linear_cross_entropy():
+    M, K, V = 300, 256, 5003
+    x = torch.randn(M, K, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    w = (torch.randn(V, K, device=DEV) / 16).bfloat16().requires_grad_()
+    t = torch.randint(0, V, (M,), device=DEV)
+    t[:10] = -100
+    loss = L.linear_cross_entropy(x, w, t, chunk_tokens=128)
+    loss.backward()
+    x32, w32 = x.detach().float().requires_grad_(), w.detach().float().requires_grad_()
+    ref = F.cross_entropy(x32 @ w32.t(), t, ignore_index=-100)
+    ref.backward()
+    assert abs(loss.item() - ref.item()) < 5e-3 * abs(ref.item())
+    assert rel(x.grad, x32.grad) < 3e-2 and rel(w.grad, w32.grad) < 3e-2
+
+
+def test_nf4_roundtrip_and_double_quant():
+    w = torch.randn(512, 1024, device=DEV, dtype=torch.bfloat16)
+    packed, absmax = W4.nf4_quantize(w)
+    p_ref, a_ref = W4._nf4_quantize_ref(w)
+    assert torch.equal(absmax, a_ref)
+    assert (packed != p_ref).float().mean().item() < 1e-3   # ties only
+    deq = W4.w4_dequant(packed, absmax, None, 512, 1024, 64)
+    ref = W4._w4_dequant_ref(packed, absmax, None, 512, 1024, 64, None, torch.bfloat16)
+    assert torch.equal(deq, ref)
+    assert rel(deq, w) < 0.2  # 4-bit quantisation error
+    q = W4.NF4Weight.quantize(w, double_quant=True, keep_decoded=False)
+    assert rel(q.scales(), absmax) < 0.02
+    assert rel(q.dequantize(), w) < 0.25
+
+
+def test_w4_gemv_matches_dequant():
+    N_, K, g = 1024, 2048, 128
+    packed = torch.randint(0, 256, (N_ * K // 2,), device=DEV, dtype=torch.uint8)
+    scale = torch.rand(N_ * K // g, device=DEV) * 0.01 + 0.001
+    zs = scale * 8
+    lut = torch.arange(16, device=DEV, dtype=torch.float32)
+    x = torch.randn(3, K, device=DEV, dtype=torch.float16)
+    y = W4.w4_gemv(x, packed, scale, zs, N_, K, g, lut)
+    wd = W4.w4_dequant(packed, scale, zs, N_, K, g, lut, torch.float16)
+    assert rel(y, x.float() @ wd.float().t()) < 5e-3
+
+
+@pytest.mark.parametrize("r,p", [(8, 0.0), (16, 0.1)])
+def test_lora_small_kernels(r, p):
+    M, K = 1000, 1536
+    x = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+    a = (torch.randn(r, K, device=DEV) / 8).bfloat16()
+    seed = 777
+    mask = LR.keep_mask((M, K), seed, p, DEV).float() / (1 - p) if p > 0 else torch.ones(M, K, device=DEV)
+    T = LR.lora_down(x, a, 0.5, seed, p)
+    assert rel(T, 0.5 * (x.float() * mask) @ a.float().t()) < 2e-2
+    pm = torch.randn(M, r, device=DEV, dtype=torch.bfloat16)
+    G = torch.zeros(r, K, device=DEV)
+    LR.lora_wgrad(pm, x, G, 2.0, seed, p)
+    assert rel(G, 2.0 * pm.float().t() @ (x.float() * mask)) < 2e-2
+    dx = torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+    dx0 = dx.clone()
+    LR.lora_dx(pm, a, dx, 1.5, seed, p)
+    assert rel(dx, dx0.float() + 1.5 * mask * (pm.float() @ a.float())) < 2e-2
+
+
+@pytest.mark.parametrize("H,Hkv,D,S", [(8, 2, 128, 256), (12, 12, 64, 255), (4, 4, 64, 100)])
+def test_attention_tiled(H, Hkv, D, S):
+    B = 2
+    Sp = (S + 7) // 8 * 8
+    if Sp != S:
+        pytest.skip("tiled path needs S % 8 == 0 (callers pad)")
+    qkv = torch.randn(B * S, (H + 2 * Hkv) * D, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    out = attention(qkv, B, S, H, Hkv, D, causal=True, impl="tiled")
+    g = torch.randn_like(out)
+    (out * g).sum().backward()
+    q32 = qkv.detach().float().requires_grad_()
+    ref = _ref_attention(q32, B, S, H, Hkv, D, True, 0, D ** -0.5)
+    (ref * g.float()).sum().backward()
+    assert rel(out, ref) < 2e-2
+    assert rel(qkv.grad, q32.grad) < 3e-2
+
+
+def test_adamw_and_8bit():
+    from llm_in_practise_b200.optim import FusedAdamW, PagedAdamW8bit
+    from llm_in_practise_b200.utils.arena import ParamArena
+    n = 10000
+    for cls, tol in [(FusedAdamW, 1e-5), (PagedAdamW8bit, 5e-2)]:
+        arena = ParamArena(device=DEV)
+        i = arena.request("w", (n,))
+        arena.finalize()
+        arena.data.normal_()
+        ref = torch.nn.Parameter(arena.data.clone())
+        opt = cls(arena, lr=1e-2, weight_decay=0.01)
+        ropt = torch.optim.AdamW([ref], lr=1e-2, weight_decay=0.01)
+        for _ in range(10):
+            g = torch.randn(arena.numel, device=DEV)
+            arena.grad.copy_(g)
+            ref.grad = g.clone()
+            opt.step()
+            ropt.step()
+        assert rel(arena.data, ref.data) < tol, cls.__name__
