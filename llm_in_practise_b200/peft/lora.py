@@ -89,7 +89,7 @@ def prepare_model_for_kbit_training(model: nn.Module, use_gradient_checkpointing
     return model
 
 
-def apply_lora(model: nn.Module, config: LoraConfig, pad_to: int = 1) -> ParamArena:
+def apply_lora(model: nn.Module, config: LoraConfig, pad_to: int = 1, alloc=None) -> ParamArena:
     """Attach adapters in place; returns the flat fp32 arena holding every adapter parameter."""
     targets = set(config.targets())
     for p in model.parameters():
@@ -104,7 +104,7 @@ def apply_lora(model: nn.Module, config: LoraConfig, pad_to: int = 1) -> ParamAr
             touched.append(lin)
     if not touched:
         raise ValueError(f"no module matches target_modules={sorted(targets)}")
-    arena.finalize()
+    arena.finalize(alloc=alloc)
     for lin in touched:
         lin.materialize_lora()
     model._lora_arena = arena

@@ -34,6 +34,7 @@ class ParamArena:
         self._size = 0
         self.data: Optional[torch.Tensor] = None
         self.grad: Optional[torch.Tensor] = None
+        self.symmetric = False
 
     def request(self, name: str, shape) -> int:
         if self.data is not None:
@@ -47,10 +48,16 @@ class ParamArena:
         self._size = _round_up(off + n, _ALIGN)
         return len(self._specs) - 1
 
-    def finalize(self, with_grad: bool = True) -> "ParamArena":
+    def finalize(self, with_grad: bool = True, alloc=None) -> "ParamArena":
+        """``alloc(numel, dtype, device) -> zeroed 1-D tensor`` lets the caller place the arena in
+        symmetric (peer-mapped) memory; the data buffer is requested first, then the gradient buffer."""
         total = _round_up(max(self._size, _ALIGN), max(self.pad_to, 1))
-        self.data = torch.zeros(total, dtype=self.dtype, device=self.device)
-        self.grad = torch.zeros(total, dtype=self.dtype, device=self.device) if with_grad else None
+        if alloc is None:
+            alloc = lambda n, dt, dev: torch.zeros(n, dtype=dt, device=dev)  # noqa: E731
+        else:
+            self.symmetric = True
+        self.data = alloc(total, self.dtype, self.device)
+        self.grad = alloc(total, self.dtype, self.device) if with_grad else None
         return self
 
     @property
@@ -93,7 +100,7 @@ class ParamArena:
 
 
 def flatten_module(module: nn.Module, dtype: Optional[torch.dtype] = None, device=None,
-                   pad_to: int = 1, only_trainable: bool = True) -> ParamArena:
+                   pad_to: int = 1, only_trainable: bool = True, alloc=None) -> ParamArena:
     """Re-home the (trainable) parameters of an arbitrary ``nn.Module`` into one arena, in
     registration order, preserving values; ``p.data`` / ``p.grad`` become views. Tied parameters
     (the same Parameter object reachable twice) are placed once."""
@@ -112,7 +119,7 @@ def flatten_module(module: nn.Module, dtype: Optional[torch.dtype] = None, devic
     device = device or params[0][1].device
     arena = ParamArena(dtype=dtype, device=device, pad_to=pad_to)
     idxs = [arena.request(n, p.shape) for n, p in params]
-    arena.finalize()
+    arena.finalize(alloc=alloc)
     with torch.no_grad():
         for (n, p), i in zip(params, idxs):
             v = arena.view(i)
