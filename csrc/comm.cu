@@ -324,23 +324,6 @@ B200_API int b200_allreduce(const void* const* data_ptrs, const void* const* fla
   return 0;
 }
 
-typedef struct {
-  const void* const* grad_ptrs;
-  const void* const* param_ptrs;
-  const void* const* flag_ptrs;
-  const void* const* norm_ptrs;
-  float* gred; float* m; float* v;
-  uint8_t* s1; uint8_t* s2; float* absmax1; float* absmax2;
-  const float* qmap1; const float* qmap2;
-  float* stats_out;
-  long long n;
-  int world, rank, eight_bit, reduce_only;
-  unsigned int epoch;
-  float lr, beta1, beta2, eps, weight_decay, bias_c1, bias_c2, grad_scale, max_norm;
-  unsigned int* grid_ctr;
-  unsigned int grid_target_base;
-  int grid;
-} b200_zero_step_args;
 
 B200_API int b200_zero_step(const b200_zero_step_args* a, void* stream) {
   if (a->world < 1 || a->world > kMaxRanks) return B200_ERR_BAD_SHAPE;

@@ -149,10 +149,6 @@ static inline unsigned flat_grid(long long n, int tb) {
 }  // namespace b200
 using namespace b200;
 
-typedef struct {
-  float lr, beta1, beta2, eps, weight_decay, bias_c1, bias_c2, grad_scale;
-} b200_adam_hyper;
-
 // p: params (p_dtype fp32 or bf16); g: grads (g_dtype); m, v: fp32; p_lowp: optional bf16 copy.
 B200_API int b200_adamw(void* p, const void* g, float* m, float* v, void* p_lowp, long long n,
                         const b200_adam_hyper* hy, const float* dyn_scale, const float* found_inf, int p_dtype,

@@ -3,7 +3,7 @@
  * Every entry point takes raw device pointers plus a cudaStream_t (passed as void*), launches
  * asynchronously on that stream and returns 0 on success, a cudaError_t (< 1000) or a
  * B200_ERR_* code (>= 10001). Nothing here synchronises the device. Entry points that need
- * temporary global memory take it from the caller (`workspace` arguments).
+ * temporary global memory take it from the caller (`scratch` / `workspace` arguments).
  *
  * Each declaration cites the reference call site (path:line under /root/reference) whose
  * library kernel it replaces; the reference itself contains no native code.
@@ -23,13 +23,22 @@ enum {
   B200_DT_FP32 = 2, /* as GEMM input: multiplied on the tensor cores as TF32 */
 };
 
+enum {
+  B200_ERR_BAD_SHAPE_ = 10001,   /* shape / size argument out of the supported domain          */
+  B200_ERR_BAD_ALIGN_ = 10002,   /* pointer or stride not a multiple of 16 bytes               */
+  B200_ERR_NO_DRIVER_ = 10003,   /* cuTensorMapEncodeTiled could not be resolved               */
+  B200_ERR_TENSORMAP_ = 10004,   /* the driver rejected a TMA descriptor                       */
+  B200_ERR_TOO_LARGE_ = 10005,   /* size beyond a kernel's stated maximum                      */
+  B200_ERR_UNSUPPORTED_ = 10006, /* dtype / flag combination not implemented                   */
+};
+
 /* ------------------------------------------------------------------------------------------
  * K1 / K3: tcgen05 GEMM.  D[b] = alpha * A[b] x B[b / b_div]^T (+ A2 x B2^T) (+ bias) + beta * D[b]
  *
  *   A is logically [M, K], B is logically [N, K].  "K-major" means the K index is contiguous
  *   (an nn.Linear weight, an activation matrix); "MN-major" (a_mn / b_mn = 1) means the operand
  *   is stored transposed, [K, M] or [K, N] row-major, so dgrad (dY x W) and wgrad (dY^T x X)
- *   read their operands in place with no transpose copy.
+ *   read their operands in place with no transpose copy (16-bit inputs only).
  *   *_rs is the stride in elements between consecutive rows of the stored matrix;
  *   *_bs0 / *_bs1 are batch strides (batch index b -> (b % nb0, b / nb0)); B uses b / b_div
  *   (grouped-query attention shares one K/V head among b_div query heads).
@@ -56,6 +65,144 @@ typedef struct {
 } b200_gemm_args;
 
 int b200_gemm(const b200_gemm_args* args, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K5: RMSNorm / LayerNorm (layer_norm = 0 / 1) with the residual add fused in.
+ *   fwd: h = x (+ res); y = norm(h) * w (+ b). stats[rows, 2] = (mean, rstd). h_out may be NULL.
+ *   bwd: dx = d norm (+ dres_in); dw / db (optional) are reduced from per-CTA partial rows held in
+ *        `scratch`, which must provide 2 * b200_norm_bwd_parts(rows) * cols floats.
+ *   Replaces nn.LayerNorm (ddp_gpt_wikitext2.py:99-116) and HF Qwen3RMSNorm (Fine-Tuning/*.py).
+ * ------------------------------------------------------------------------------------------ */
+int b200_norm_fwd(int layer_norm, const void* x, const void* res, const void* w, const void* b, void* y,
+                  void* h_out, float* stats, int rows, int cols, float eps, int dtype, int wdtype, void* stream);
+int b200_norm_bwd_parts(int rows);
+int b200_norm_bwd(int layer_norm, const void* dy, const void* h, const void* w, const float* stats,
+                  const void* dres_in, void* dx, void* dw, void* db, float* scratch, int accumulate, int rows,
+                  int cols, int dtype, int wdtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K6 / K7 / K9 / K10: fused element-wise kernels.
+ *   qknorm_rope: per-head RMSNorm of q,k (weights qw/kw, may be NULL) + rotary embedding on the
+ *   fused qkv projection [tokens, (n_q + n_k + n_v) * D]; v heads are copied through.
+ *   interleaved = 0: rotate-half pairs (HF Qwen3); 1: (2i, 2i+1) pairs
+ *   (LLM_Distributed_Trainning/PyTorch/transformer_basics/DeepSeekLike_spare_MoE_wikitext2.py:145-174).
+ *   swiglu: h = silu(gate) * up on [rows, 2F] (HF Qwen3MLP); gelu: exact erf (nn.GELU);
+ *   embedding: gather (+ position table) / scatter-add; dropout: Philox mask from (seed, index).
+ * ------------------------------------------------------------------------------------------ */
+int b200_qknorm_rope_fwd(const void* src, void* dst, const void* qw, const void* kw, const float* cos_t,
+                         const float* sin_t, const int* pos, int tokens, int n_q, int n_k, int n_v, int D,
+                         long long src_rs, long long dst_rs, int interleaved, float eps, float* rstd_out, int dtype,
+                         void* stream);
+int b200_qknorm_rope_bwd(const void* g_in, const void* raw, void* g_out, const void* qw, const void* kw,
+                         const float* cos_t, const float* sin_t, const int* pos, int tokens, int n_q, int n_k, int n_v,
+                         int D, long long g_rs, long long raw_rs, long long out_rs, int interleaved, float eps,
+                         float* dwq, float* dwk, int dtype, void* stream);
+int b200_swiglu_fwd(const void* gu, void* h, long long rows, int F, int dtype, void* stream);
+int b200_swiglu_bwd(const void* dh, const void* gu, void* dgu, long long rows, int F, int dtype, void* stream);
+int b200_gelu_fwd(const void* x, void* y, long long n, int dtype, void* stream);
+int b200_gelu_bwd(const void* dy, const void* x, void* dx, long long n, int dtype, void* stream);
+int b200_embedding_fwd(const long long* ids, const void* table, const void* pos_table, void* out, long long tokens,
+                       int dim, int period, float scale, int dtype, void* stream);
+int b200_embedding_bwd(const long long* ids, const void* dout, float* dtable, long long tokens, int dim, float scale,
+                       int dtype, void* stream);
+int b200_dropout(const void* x, void* y, long long n, unsigned long long seed, float p, int dtype, void* stream);
+int b200_cast(const void* x, void* y, long long n, float scale, int in_dtype, int out_dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K8: cross-entropy with the gradient written in place of the logits, and the masked row softmax
+ *   of the tiled attention path. Replaces nn.CrossEntropyLoss (ddp_gpt_wikitext2.py:282,304), the
+ *   HF ForCausalLM loss, and the L x L boolean-mask softmax of nn.MultiheadAttention (:93-95).
+ * ------------------------------------------------------------------------------------------ */
+int b200_cross_entropy(void* logits, const long long* targets, float* loss_rows, float* lse_rows, long long rows,
+                       int vocab, long long row_stride, long long ignore_index, float grad_scale, int write_grad,
+                       int dtype, void* stream);
+int b200_softmax_fwd(const void* S, void* P, long long batch, int rows, int cols, int causal, int window, float scale,
+                     int in_dtype, int out_dtype, void* stream);
+int b200_softmax_bwd(const void* P, const void* dP, void* dS, long long total_rows, int cols, float scale,
+                     int p_dtype, int g_dtype, int out_dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K11 / K12 / K13 / K15: optimizer kernels over flat ranges. dyn_scale / found_inf are optional
+ *   device scalars (clip coefficient, overflow flag). Replaces torch.optim.AdamW
+ *   (ddp_gpt_wikitext2.py:281), bitsandbytes paged_adamw_8bit
+ *   (Fine-Tuning/qwen3-14b-qlora-dist-deepspeed.py:151), clip_grad_norm_ (llm-demo/minigpt/train.py:44).
+ * ------------------------------------------------------------------------------------------ */
+typedef struct {
+  float lr, beta1, beta2, eps, weight_decay, bias_c1, bias_c2, grad_scale;
+} b200_adam_hyper;
+
+int b200_adamw(void* p, const void* g, float* m, float* v, void* p_lowp, long long n, const b200_adam_hyper* hy,
+               const float* dyn_scale, const float* found_inf, int p_dtype, int g_dtype, void* stream);
+int b200_adamw8bit(void* p, const void* g, uint8_t* s1, uint8_t* s2, float* absmax1, float* absmax2,
+                   const float* qmap1, const float* qmap2, void* p_lowp, long long n, const b200_adam_hyper* hy,
+                   const float* dyn_scale, const float* found_inf, int p_dtype, int g_dtype, void* stream);
+int b200_sumsq(const void* x, long long n, float* out2, float pre_scale, int dtype, void* stream);
+int b200_clip_coef(const float* sumsq, float max_norm, float* coef, float* norm_out, void* stream);
+int b200_scale(void* x, long long n, float scale, const float* dyn_scale, int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K2 / K14: 4-bit weights. packed[N, K/2] (K contiguous, element 2j in the high nibble),
+ *   scale[N, K/group] fp32, optional zs = zero_point * scale, 16-entry code book (NULL = NF4):
+ *   w = lut[q] * scale - zs. `packed/scale/zs` of b200_w4_dequant are arrays of `nshards` base
+ *   pointers (row shards; peer-GPU pointers allowed: the ZeRO-3 gather fused into the dequant).
+ *   Replaces bitsandbytes NF4 kernels (Fine-Tuning/qwen3-14b-qlora-dist-deepspeed.py:101-106) and
+ *   the GPTQ/AWQ kernels of gptqmodel / vLLM (Quantization/GPTQModel/inference_qwen3_4b_gptq.py:29).
+ * ------------------------------------------------------------------------------------------ */
+int b200_nf4_quantize(const void* w, uint8_t* packed, float* absmax, long long n, int dtype, void* stream);
+int b200_nf4_absmax_decode(const uint8_t* q, const float* code2, const float* absmax2, float offset, float* out,
+                           long long n, void* stream);
+int b200_w4_dequant(const void* const* packed, const void* const* scale, const void* const* zs, int nshards,
+                    long long rows_per_shard, void* out, long long N, int K, int group, const float* lut,
+                    long long out_rs, int out_dtype, void* stream);
+int b200_w4_gemv(const void* x, const uint8_t* packed, const float* scale, const float* zs, const float* lut,
+                 const void* bias, void* y, int M, long long N, int K, int group, long long x_rs, long long y_rs,
+                 int dtype, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K3 (small side): skinny LoRA products with dropout fused (bf16).
+ *   Replaces peft lora.Linear's dropout -> lora_A -> lora_B chain (Fine-Tuning/qwen3-8b-lora-dist.py:118-125).
+ * ------------------------------------------------------------------------------------------ */
+int b200_lora_down(const void* X, const void* A, void* T, int M, int K, int r, long long x_rs, long long a_rs,
+                   long long t_rs, float alpha, unsigned long long seed, float p, void* stream);
+int b200_lora_wgrad(const void* P, const void* X, float* G, int M, int K, int r, long long p_rs, long long x_rs,
+                    long long g_rs, float alpha, unsigned long long seed, float p, void* stream);
+int b200_lora_dx(const void* dT, const void* A, void* dX, int M, int K, int r, long long dt_rs, long long a_rs,
+                 long long dx_rs, float alpha, unsigned long long seed, float p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * K-C1 / K-C2 / K-C3: collectives fused with compute over NVLink peer memory. `*_ptrs` are arrays
+ *   of `world` device pointers, index = rank (symmetric memory). Flags: uint32 [channels][8] per
+ *   rank; epochs grow monotonically. grid_ctr is a local uint32 counter; grid_target_base is its
+ *   value before this launch. Replaces ncclAllReduce under DDP (ddp_gpt_wikitext2.py:271-279) and
+ *   DeepSpeed's reduce-scatter / optimizer / all-gather step (Fine-Tuning/ds_zero3_config.json).
+ * ------------------------------------------------------------------------------------------ */
+int b200_allreduce(const void* const* data_ptrs, const void* const* flag_ptrs, const void* const* lowp_ptrs,
+                   long long n, int world, int rank, unsigned int epoch, float scale, unsigned int* grid_ctr,
+                   unsigned int grid_target_base, int grid, void* stream);
+
+typedef struct {
+  const void* const* grad_ptrs;
+  const void* const* param_ptrs;
+  const void* const* flag_ptrs;
+  const void* const* norm_ptrs;
+  float* gred; float* m; float* v;
+  uint8_t* s1; uint8_t* s2; float* absmax1; float* absmax2;
+  const float* qmap1; const float* qmap2;
+  float* stats_out;
+  long long n;
+  int world, rank, eight_bit, reduce_only;
+  unsigned int epoch;
+  float lr, beta1, beta2, eps, weight_decay, bias_c1, bias_c2, grad_scale, max_norm;
+  unsigned int* grid_ctr;
+  unsigned int grid_target_base;
+  int grid;
+} b200_zero_step_args;
+
+int b200_zero_step(const b200_zero_step_args* args, void* stream);
+int b200_peer_gather(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
+                     int world, void* stream);
+int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int rank, unsigned int epoch,
+                      void* stream);
 
 #ifdef __cplusplus
 }
