@@ -301,3 +301,112 @@ B200_API int b200_norm_bwd(int layer_norm, const void* dy, const void* h, const 
   B200_LAUNCH_CHECK();
   return 0;
 }
+
+// =================================================================================================
+// b200_norm_bwd_noalloc — the same backward, for callers that must not allocate.
+//
+// Who that is: anything that reaches this library through the C ABI without an allocator it is
+// allowed to use at call time — an inference/serving process that handed every free byte of HBM to
+// its KV-cache pool at start-up, a plugin host or real-time loop that bans cudaMalloc after
+// initialisation because it serialises the whole device, or a small C/C++ harness that simply has
+// no caching allocator behind it (the Python side of this repository borrows torch's). The regular
+// entry point asks such callers for a `scratch` buffer they have no good way to produce.
+//
+// This variant keeps the per-CTA dw/db partial rows in a fixed array that lives in the library
+// image itself: kNoAllocScratchFloats floats = 8 MiB, present on every GPU that loads
+// libb200ops.so from load until the process exits. To stay inside it the kernel runs with at most
+// kNoAllocParts CTAs, and `cols` may not exceed kNoAllocMaxCols; anything larger is refused with
+// B200_ERR_TOO_LARGE and a message on stderr — nothing is launched and nothing is allocated.
+//
+// Host code cannot hand the array's name to a kernel (on the host it is only a stand-in symbol),
+// so the device address is looked up with cudaGetSymbolAddress, once per device, with that device
+// current, the first time the entry point is called there; the result is cached. That first call
+// therefore does a little extra driver work: make it before starting any stream capture.
+//
+// The array is shared by every call and keeps whatever the last call left in it. Nothing has to
+// be cleared: each call rewrites every partial row its own reduction reads before reading it.
+// The flip side is that two calls whose kernels may overlap on the GPU (different streams, or
+// different host threads on the same device) race on the array — serialise them.
+//
+// No cudaMalloc / cudaFree / allocating library routine is called here, on any path.
+// =================================================================================================
+#include <mutex>
+
+namespace b200 {
+constexpr int kNoAllocMaxCols = 8192;
+constexpr int kNoAllocParts = 128;
+constexpr long long kNoAllocScratchFloats = 2ll * kNoAllocParts * kNoAllocMaxCols;  // dw rows, then db rows
+static __device__ __align__(256) float g_norm_bwd_scratch[kNoAllocScratchFloats];
+
+constexpr int kNoAllocMaxDevices = 64;
+static float* g_norm_bwd_scratch_addr[kNoAllocMaxDevices] = {nullptr};
+static std::mutex g_norm_bwd_scratch_mu;
+
+// device address of the scratch array on the current device (looked up once per device)
+static int norm_bwd_noalloc_scratch(float** out) {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return (int)e;
+  if (dev < 0 || dev >= kNoAllocMaxDevices) return B200_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_norm_bwd_scratch_mu);
+  if (g_norm_bwd_scratch_addr[dev] == nullptr) {
+    float* p = nullptr;
+    e = cudaGetSymbolAddress((void**)&p, g_norm_bwd_scratch);
+    if (e != cudaSuccess) return (int)e;
+    if (p == nullptr) return B200_ERR_UNSUPPORTED;
+    g_norm_bwd_scratch_addr[dev] = p;
+  }
+  *out = g_norm_bwd_scratch_addr[dev];
+  return 0;
+}
+}  // namespace b200
+
+B200_API int b200_norm_bwd_noalloc_max_cols(void) { return b200::kNoAllocMaxCols; }
+
+B200_API int b200_norm_bwd_noalloc(int layer_norm, const void* dy, const void* h, const void* w, const float* stats,
+                                   const void* dres_in, void* dx, void* dw, void* db, int accumulate, int rows,
+                                   int cols, int dtype, int wdtype, void* stream) {
+  cudaStream_t st = (cudaStream_t)stream;
+  const int V = dtype == B200_DT_FP32 ? 4 : 8;
+  if (rows <= 0 || cols <= 0 || cols % V) return B200_ERR_BAD_SHAPE;
+  if (cols > kNoAllocMaxCols) {
+    fprintf(stderr,
+            "b200_norm_bwd_noalloc: cols = %d exceeds the built-in scratch (max %d columns, %lld bytes); "
+            "use b200_norm_bwd with caller-provided scratch instead\n",
+            cols, kNoAllocMaxCols, kNoAllocScratchFloats * 4);
+    return B200_ERR_TOO_LARGE;
+  }
+  const int nvec = cols / V;
+  const int mv = ceil_div(nvec, kNormThreads);
+  if (mv > 4) return B200_ERR_TOO_LARGE;
+  float* scratch = nullptr;
+  int rc = norm_bwd_noalloc_scratch(&scratch);
+  if (rc) return rc;
+  const int grid = rows < kNoAllocParts ? rows : kNoAllocParts;
+  float* dwp = dw ? scratch : nullptr;
+  float* dbp = db ? scratch + (long long)kNoAllocParts * kNoAllocMaxCols : nullptr;
+  rc = B200_ERR_UNSUPPORTED;
+#define B200_NORM_BWD_NA(T, WT)                                                                                      \
+  rc = mv <= 1   ? launch_norm_bwd<T, WT, 1>(layer_norm, dy, h, w, stats, dres_in, dx, dwp, dbp, rows, cols, grid, st) \
+       : mv <= 2 ? launch_norm_bwd<T, WT, 2>(layer_norm, dy, h, w, stats, dres_in, dx, dwp, dbp, rows, cols, grid, st) \
+                 : launch_norm_bwd<T, WT, 4>(layer_norm, dy, h, w, stats, dres_in, dx, dwp, dbp, rows, cols, grid, st)
+  if (dtype == B200_DT_BF16 && wdtype == B200_DT_BF16) { B200_NORM_BWD_NA(__nv_bfloat16, __nv_bfloat16); }
+  else if (dtype == B200_DT_BF16 && wdtype == B200_DT_FP32) { B200_NORM_BWD_NA(__nv_bfloat16, float); }
+  else if (dtype == B200_DT_FP32 && wdtype == B200_DT_FP32) { B200_NORM_BWD_NA(float, float); }
+  else if (dtype == B200_DT_FP16 && wdtype == B200_DT_FP16) { B200_NORM_BWD_NA(__half, __half); }
+#undef B200_NORM_BWD_NA
+  if (rc) return rc;
+  const int tb = 256, gb = ceil_div(cols, tb);
+  if (dw) {
+    if (wdtype == B200_DT_FP32) reduce_partials_kernel<float><<<gb, tb, 0, st>>>(dwp, (float*)dw, grid, cols, accumulate);
+    else if (wdtype == B200_DT_BF16) reduce_partials_kernel<__nv_bfloat16><<<gb, tb, 0, st>>>(dwp, (__nv_bfloat16*)dw, grid, cols, accumulate);
+    else reduce_partials_kernel<__half><<<gb, tb, 0, st>>>(dwp, (__half*)dw, grid, cols, accumulate);
+  }
+  if (db) {
+    if (wdtype == B200_DT_FP32) reduce_partials_kernel<float><<<gb, tb, 0, st>>>(dbp, (float*)db, grid, cols, accumulate);
+    else if (wdtype == B200_DT_BF16) reduce_partials_kernel<__nv_bfloat16><<<gb, tb, 0, st>>>(dbp, (__nv_bfloat16*)db, grid, cols, accumulate);
+    else reduce_partials_kernel<__half><<<gb, tb, 0, st>>>(dbp, (__half*)db, grid, cols, accumulate);
+  }
+  B200_LAUNCH_CHECK();
+  return 0;
+}

@@ -80,6 +80,20 @@ int b200_norm_bwd(int layer_norm, const void* dy, const void* h, const void* w, 
                   const void* dres_in, void* dx, void* dw, void* db, float* scratch, int accumulate, int rows,
                   int cols, int dtype, int wdtype, void* stream);
 
+/* b200_norm_bwd without a scratch argument, for callers that cannot allocate (a serving process
+ * whose HBM is already committed to its KV-cache pool, a host that forbids cudaMalloc after
+ * start-up, a bare C harness with no allocator behind it). This entry point has no counterpart
+ * in the reference. The dw/db partial rows live in an 8 MiB array built into the library (resident on every
+ * GPU that loads it, until exit); limits: cols <= b200_norm_bwd_noalloc_max_cols() (8192), else
+ * B200_ERR_TOO_LARGE_ and nothing runs. It calls no cudaMalloc/cudaFree. The first call on each
+ * device looks the array's address up (cudaGetSymbolAddress) — make that call before any stream
+ * capture. All calls share the array: nothing needs clearing between calls, but calls that may
+ * overlap on the GPU race on it and must be serialised by the caller. */
+int b200_norm_bwd_noalloc_max_cols(void);
+int b200_norm_bwd_noalloc(int layer_norm, const void* dy, const void* h, const void* w, const float* stats,
+                          const void* dres_in, void* dx, void* dw, void* db, int accumulate, int rows, int cols,
+                          int dtype, int wdtype, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * K6 / K7 / K9 / K10: fused element-wise kernels.
  *   qknorm_rope: per-head RMSNorm of q,k (weights qw/kw, may be NULL) + rotary embedding on the
