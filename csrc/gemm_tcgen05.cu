@@ -2,18 +2,23 @@
 //
 //   D[b] = alpha * A[b] x B[b / b_div]^T  (+ A2 x B2^T)  (+ bias)  + beta * D[b]
 //
-// One CTA per SM loops over 128 x BN output tiles. Warp 0 feeds a ring of shared-memory stages
-// with TMA (128-byte swizzle), warp 1 issues tcgen05.mma into one of two TMEM accumulators,
-// warps 2-5 drain the other accumulator with tcgen05.ld and write D, so the epilogue of tile i
-// overlaps the main loop of tile i+1. BN (32..256) and the stage count are run-time values: the
-// host picks the BN that wastes the fewest SM-waves for the problem at hand.
+// Work unit = one CTA (128 x BN tile) or one CTA *pair* (cta_group::2, 256 x BN tile: each CTA
+// stages its own 128 rows of A and half of B, the leader issues one 256-row UMMA for both SMs).
+// The pair halves the B traffic per flop, which matters because at 128 x 256 tiles the kernel is
+// bound by L2->SM bandwidth (~12.5 TB/s), not by the tensor pipe: 85 flop/B caps a single-CTA
+// kernel near 1.0 PFLOP/s, 128 flop/B lifts the cap to ~1.6 (measured; see profiles/).
+// Per unit: warp 0 feeds a ring of shared-memory stages with TMA (128-byte swizzle), warp 1 issues
+// tcgen05.mma into one of two TMEM accumulators, warps 2-5 drain the other accumulator with
+// tcgen05.ld and write D, so the epilogue of tile i overlaps the main loop of tile i+1. BN
+// (16..256), the CTA-group size and the stage count are run-time choices: the host picks the
+// combination with the lowest modelled time (SM-waves x max(tensor-pipe, L2) per k-block).
 //
 // Operands are read in place in either storage order ("K-major" or "MN-major" UMMA descriptors),
 // so forward (X W^T), dgrad (dY W) and wgrad (dY^T X) all run through this one kernel with no
-// transpose copies, for bf16/fp16 (kind::f16) and fp32 (kind::tf32) inputs. The optional A2/B2
-// operands append a rank-K2 update as one extra k-block: that is the LoRA term of peft's
-// lora.Linear (Fine-Tuning/qwen3-8b-lora-dist.py:118-125), computed on the tensor cores inside
-// the same accumulator instead of as three extra cuBLAS calls.
+// transpose copies, for bf16/fp16 (kind::f16) and fp32 (kind::tf32, K-major only) inputs. The
+// optional A2/B2 operands append a rank-K2 update as one extra k-block: that is the LoRA term of
+// peft's lora.Linear (Fine-Tuning/qwen3-8b-lora-dist.py:118-125), computed on the tensor cores
+// inside the same accumulator instead of as three extra cuBLAS calls.
 //
 // Replaces: cuBLAS/cuBLASLt behind every nn.Linear in the reference, e.g.
 // LLM_Distributed_Trainning/PyTorch/ddp_basics/ddp_gpt_wikitext2.py:86-165.
@@ -22,10 +27,11 @@
 #include "../include/b200_ops.h"
 
 #include <stdio.h>
+#include <stdlib.h>
 
 namespace b200 {
 
-constexpr int kBM = 128;             // tile rows = TMEM lanes
+constexpr int kBM = 128;             // rows per CTA = TMEM lanes
 constexpr int kStageABytes = 16384;  // 128 rows x 128 B
 constexpr int kGemmThreads = 192;    // producer, mma, 4 epilogue warps
 constexpr int kAccStride = 256;      // TMEM columns between the two accumulators
@@ -39,21 +45,70 @@ struct GemmKernelParams {
   float alpha, beta;
   int out_dtype, bias_dtype;
   uint32_t idesc_main, idesc_lora;
-  int num_m, num_n, num_k;  // k-blocks of the main operands
+  int num_m, num_n, num_k;  // num_m counts unit tiles (128 * CTAS rows); num_k = k-blocks of the main operands
   int bn, stages, a_mn, b_mn;
   int vec_ok;
+  // stream-K: every unit gets an equal contiguous range of (tile, k-block) work items; a tile that is
+  // split between units is summed through `sk_ws` (one fp32 128 x 256 slot per CTA) by the unit
+  // that owns the tile's first k-block, after the others published their partial (sk_flags = epoch).
+  int stream_k;
+  float* sk_ws;
+  unsigned int* sk_flags;
+  unsigned int sk_epoch;
 };
 
-template <int ES>
+// One accumulator's worth of work: k-blocks [kb0, kb1) of `tile`.
+struct Segment {
+  int tile, kb0, kb1;
+};
+
+// Iterates the segments of one unit, identically in the producer, MMA and epilogue roles.
+struct SegmentIter {
+  long long item, end;  // stream-K: current / last work item of this unit
+  int tile, stride, total_tiles, nkt;
+  bool stream_k;
+  __device__ SegmentIter(const GemmKernelParams& p, int unit, int nunits, int total_tiles_, int nkt_) {
+    stream_k = p.stream_k != 0;
+    total_tiles = total_tiles_;
+    nkt = nkt_;
+    tile = unit;
+    stride = nunits;
+    const long long total = (long long)total_tiles_ * nkt_;
+    item = total * unit / nunits;
+    end = total * (unit + 1) / nunits;
+  }
+  __device__ bool next(Segment& s) {
+    if (!stream_k) {
+      if (tile >= total_tiles) return false;
+      s.tile = tile; s.kb0 = 0; s.kb1 = nkt;
+      tile += stride;
+      return true;
+    }
+    if (item >= end) return false;
+    s.tile = (int)(item / nkt);
+    s.kb0 = (int)(item - (long long)s.tile * nkt);
+    const long long left = end - item;
+    s.kb1 = (long long)(nkt - s.kb0) <= left ? nkt : s.kb0 + (int)left;
+    item += s.kb1 - s.kb0;
+    return true;
+  }
+};
+
+template <int ES, int CTAS>
 __device__ __forceinline__ void umma_issue(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
-  if constexpr (ES == 2) umma_f16(d, a, b, idesc, acc);
-  else umma_tf32(d, a, b, idesc, acc);
+  if constexpr (CTAS == 1) {
+    if constexpr (ES == 2) umma_f16(d, a, b, idesc, acc);
+    else umma_tf32(d, a, b, idesc, acc);
+  } else {
+    if constexpr (ES == 2) umma_f16_2sm(d, a, b, idesc, acc);
+    else umma_tf32_2sm(d, a, b, idesc, acc);
+  }
 }
 
 template <typename OutT>
 __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* __restrict__ drow, int col0,
-                                               const uint32_t (&r)[32], bool row_ok) {
-  // drow points at D[row, 0]; this thread owns columns col0 .. col0+31 of its row.
+                                               int col_limit, const uint32_t (&r)[32], bool row_ok) {
+  // drow points at D[row, 0]; this thread owns columns col0 .. col0+31 (< col_limit) of its row.
   float v[32];
 #pragma unroll
   for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * p.alpha;
@@ -61,7 +116,7 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       int c = col0 + j;
-      if (c < p.N) {
+      if (c < col_limit) {
         float b = p.bias_dtype == B200_DT_FP32 ? reinterpret_cast<const float*>(p.bias)[c]
                   : p.bias_dtype == B200_DT_BF16
                       ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[c])
@@ -71,7 +126,7 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
     }
   }
   if (!row_ok) return;
-  const bool full = (col0 + 32 <= p.N) && p.vec_ok;
+  const bool full = (col0 + 32 <= col_limit) && p.vec_ok;
   if (full) {
     constexpr int kPerVec = 16 / sizeof(OutT);
     constexpr int kVecs = 32 / kPerVec;
@@ -97,7 +152,7 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
       int c = col0 + j;
-      if (c < p.N) {
+      if (c < col_limit) {
         float x = v[j];
         if (p.beta != 0.f) x += p.beta * to_f32<OutT>(drow[c]);
         drow[c] = from_f32<OutT>(x);
@@ -106,7 +161,7 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
   }
 }
 
-template <int ES>
+template <int ES, int CTAS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
@@ -116,7 +171,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   extern __shared__ uint8_t smem_raw[];
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t stage_b_bytes = (uint32_t)p.bn * 128u;
+  const int bn_cta = p.bn / CTAS;  // B rows (output columns) staged by this CTA
+  const uint32_t stage_b_bytes = (uint32_t)bn_cta * 128u;
   const uint32_t sA0 = smem_base;
   const uint32_t sB0 = smem_base + (uint32_t)p.stages * kStageABytes;
   const uint32_t bar0 = sB0 + (uint32_t)p.stages * stage_b_bytes;
@@ -129,6 +185,9 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  const uint32_t rank = CTAS == 2 ? cluster_ctarank() : 0u;
+  const bool leader = rank == 0;
+  const int unit = blockIdx.x / CTAS, nunits = gridDim.x / CTAS;
 
   if (warp == 0 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -138,21 +197,22 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tma_prefetch_desc(&tmB2);
     }
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(full_bar(s), 1);
-      mbar_init(empty_bar(s), 1);
+      mbar_init(full_bar(s), CTAS);   // one arrival per CTA's producer (+ the TMA transaction bytes)
+      mbar_init(empty_bar(s), 1);     // tcgen05.commit (multicast to both CTAs of a pair)
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 4);
+      mbar_init(tempty_bar(a), 4 * CTAS);  // epilogue warps of every CTA in the unit
     }
     fence_mbar_init();
   }
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 512);
-    tmem_relinquish();
+    if constexpr (CTAS == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
+    else { tmem_alloc_2sm(tmem_slot, 512); tmem_relinquish_2sm(); }
   }
   tc_fence_before();
   __syncthreads();
+  if constexpr (CTAS == 2) cluster_sync_all();  // the peer's barriers exist before anyone signals them
   tc_fence_after();
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
@@ -162,83 +222,112 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int num_k_total = p.num_k + (p.K2 > 0 ? 1 : 0);
 
   if (warp == 0) {
-    // ================= TMA producer =================
+    // ================= TMA producer (every CTA loads its own rows of A and its share of B) =========
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t tx_bytes = kStageABytes + stage_b_bytes;
-      const uint32_t a_box_bytes = EPR * 128;  // MN-major A: box of EPR k-rows x 128 B
-      const uint32_t b_box_bytes = EPR * 128;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const uint32_t tx_bytes = (uint32_t)CTAS * (kStageABytes + stage_b_bytes);
+      const uint32_t box_bytes = EPR * 128;  // MN-major operands: one box = EPR k-rows x 128 B
+      SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
+      Segment sg;
+      while (it.next(sg)) {
+        const int tile = sg.tile;
         const int bt = tile / tiles_per_batch;
         const int rem = tile - bt * tiles_per_batch;
         const int n_blk = rem / p.num_m;
         const int m_blk = rem - n_blk * p.num_m;
-        const int m0 = m_blk * kBM, n0 = n_blk * p.bn;
+        const int m0 = m_blk * (kBM * CTAS) + (int)rank * kBM;
+        const int n0 = n_blk * p.bn + (int)rank * bn_cta;
         const int ab0 = bt % p.nb0, ab1 = bt / p.nb0;
         const int btb = bt / p.b_div;
         const int bb0 = btb % p.nb0_b, bb1 = btb / p.nb0_b;
-        for (int kb = 0; kb < num_k_total; ++kb) {
+        for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
-          const uint32_t fb = full_bar(stage);
-          mbar_arrive_expect_tx(fb, tx_bytes);
+          const uint32_t fb_local = full_bar(stage);
+          const uint32_t fb = leader ? fb_local : mapa_shared(fb_local, 0);  // the leader's barrier
+          if (leader) mbar_arrive_expect_tx(fb_local, tx_bytes);
+          else mbar_arrive_cluster(fb);
           const uint32_t sa = sA0 + (uint32_t)stage * kStageABytes;
           const uint32_t sb = sB0 + (uint32_t)stage * stage_b_bytes;
+          auto load = [&](uint32_t dst, const CUtensorMap* tm, int c0, int c1, int c2, int c3) {
+            if constexpr (CTAS == 1) tma_load_4d(dst, tm, fb, c0, c1, c2, c3);
+            else tma_load_4d_2sm(dst, tm, fb, c0, c1, c2, c3);
+          };
           if (kb < p.num_k) {
             const int k0 = kb * EPR;
             if (!p.a_mn) {
-              tma_load_4d(sa, &tmA, fb, k0, m0, ab0, ab1);
+              load(sa, &tmA, k0, m0, ab0, ab1);
             } else {
-              for (int j = 0; j < kBM / EPR; ++j)
-                tma_load_4d(sa + j * a_box_bytes, &tmA, fb, m0 + j * EPR, k0, ab0, ab1);
+              for (int j = 0; j < kBM / EPR; ++j) load(sa + j * box_bytes, &tmA, m0 + j * EPR, k0, ab0, ab1);
             }
             if (!p.b_mn) {
-              tma_load_4d(sb, &tmB, fb, k0, n0, bb0, bb1);
+              load(sb, &tmB, k0, n0, bb0, bb1);
             } else {
-              for (int j = 0; j < p.bn / EPR; ++j)
-                tma_load_4d(sb + j * b_box_bytes, &tmB, fb, n0 + j * EPR, k0, bb0, bb1);
+              for (int j = 0; j < bn_cta / EPR; ++j) load(sb + j * box_bytes, &tmB, n0 + j * EPR, k0, bb0, bb1);
             }
           } else {
-            tma_load_4d(sa, &tmA2, fb, 0, m0, 0, 0);
-            tma_load_4d(sb, &tmB2, fb, 0, n0, 0, 0);
+            load(sa, &tmA2, 0, m0, 0, 0);
+            load(sb, &tmB2, 0, n0, 0, 0);
           }
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
-    // ================= MMA issuer =================
-    if (lane == 0) {
+    // ================= MMA issuer (one thread of the leader CTA) =================
+    if (lane == 0 && leader) {
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      // Shared-memory descriptors, split so that the per-UMMA work is ONE 32-bit add per operand.
+      // (Building each 64-bit descriptor from scratch costs ~45 dependent uniform-datapath ops per
+      // k-block, ~540 cycles, which made this thread — not the tensor pipe — the bottleneck.)
+      //   hi word: stride-byte-offset 1024 (8-row groups) | version 1 | 128-byte swizzle
+      //   lo word: (address >> 4) | (leading-byte-offset >> 4) << 16
+      // K-major: rows of 128 B, k-step = +32 B inside the swizzle row, LBO unused (16).
+      // MN-major: k rows of 128 B, 128-B column chunks one TMA box (EPR rows x 128 B) apart (LBO),
+      //           k-step = UK rows further down.
+      constexpr uint32_t kDescHi = (1024u >> 4) | (1u << 14) | (kSwizzle128B << 29);
+      constexpr uint32_t kLoK = (16u >> 4) << 16, kLoMN = ((uint32_t)(EPR * 128) >> 4) << 16;
+      constexpr uint32_t kStepK = 32u >> 4, kStepMN = (uint32_t)(UK * 128) >> 4;
+      const uint32_t a_lo_main = (sA0 >> 4) | (p.a_mn ? kLoMN : kLoK);
+      const uint32_t b_lo_main = (sB0 >> 4) | (p.b_mn ? kLoMN : kLoK);
+      const uint32_t a_step_main = p.a_mn ? kStepMN : kStepK, b_step_main = p.b_mn ? kStepMN : kStepK;
+      const uint32_t a_lo_lora = (sA0 >> 4) | kLoK, b_lo_lora = (sB0 >> 4) | kLoK;
+      const uint32_t a_stage16 = kStageABytes >> 4, b_stage16 = stage_b_bytes >> 4;
+      const int lora_ksteps = (p.K2 + UK - 1) / UK;
+      auto desc = [](uint32_t lo) { return ((uint64_t)kDescHi << 32) | (uint64_t)lo; };
+      SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
+      Segment sg;
+      while (it.next(sg)) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)acc * kAccStride;
-        for (int kb = 0; kb < num_k_total; ++kb) {
+        for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
-          const uint32_t sa = sA0 + (uint32_t)stage * kStageABytes;
-          const uint32_t sb = sB0 + (uint32_t)stage * stage_b_bytes;
-          const bool lora = kb >= p.num_k;
-          const int ksteps = lora ? (p.K2 + UK - 1) / UK : EPR / UK;
-          const bool amn = p.a_mn && !lora, bmn = p.b_mn && !lora;
-          const uint32_t idesc = lora ? p.idesc_lora : p.idesc_main;
-#pragma unroll 1
-          for (int k = 0; k < ksteps; ++k) {
-            // K-major: rows of 128 B, 8-row groups 1024 B apart, k-step = +32 B inside the swizzle row.
-            // MN-major: k rows of 128 B (8-row groups 1024 B apart), 128-B column chunks one TMA box
-            // (EPR rows x 128 B) apart, k-step = UK rows further down.
-            const uint64_t adesc = amn ? make_smem_desc(sa + k * (UK * 128), EPR * 128, 1024, kSwizzle128B)
-                                       : make_smem_desc(sa + k * 32, 16, 1024, kSwizzle128B);
-            const uint64_t bdesc = bmn ? make_smem_desc(sb + k * (UK * 128), EPR * 128, 1024, kSwizzle128B)
-                                       : make_smem_desc(sb + k * 32, 16, 1024, kSwizzle128B);
-            umma_issue<ES>(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          if (kb < p.num_k) {
+            const uint32_t a_lo = a_lo_main + (uint32_t)stage * a_stage16;
+            const uint32_t b_lo = b_lo_main + (uint32_t)stage * b_stage16;
+            umma_issue<ES, CTAS>(d_tmem, desc(a_lo), desc(b_lo), p.idesc_main, kb != sg.kb0 ? 1u : 0u);
+#pragma unroll
+            for (int k = 1; k < EPR / UK; ++k)
+              umma_issue<ES, CTAS>(d_tmem, desc(a_lo + k * a_step_main), desc(b_lo + k * b_step_main), p.idesc_main, 1u);
+          } else {
+            const uint32_t a_lo = a_lo_lora + (uint32_t)stage * a_stage16;
+            const uint32_t b_lo = b_lo_lora + (uint32_t)stage * b_stage16;
+            for (int k = 0; k < lora_ksteps; ++k)
+              umma_issue<ES, CTAS>(d_tmem, desc(a_lo + k * kStepK), desc(b_lo + k * kStepK), p.idesc_lora,
+                                   (kb != sg.kb0 || k != 0) ? 1u : 0u);
           }
-          umma_commit(empty_bar(stage));
-          if (kb == num_k_total - 1) umma_commit(tfull_bar(acc));
+          if constexpr (CTAS == 1) {
+            umma_commit(empty_bar(stage));
+            if (kb == sg.kb1 - 1) umma_commit(tfull_bar(acc));
+          } else {
+            umma_commit_2sm(empty_bar(stage), 3);
+            if (kb == sg.kb1 - 1) umma_commit_2sm(tfull_bar(acc), 3);
+          }
           if (++stage == p.stages) { stage = 0; phase ^= 1u; }
         }
         acc ^= 1;
@@ -246,16 +335,20 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
     }
   } else {
-    // ================= epilogue (4 warps, one TMEM lane quarter each) =================
+    // ================= epilogue (4 warps per CTA, one TMEM lane quarter each) =================
     const int q = warp & 3;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+    SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
+    Segment sg;
+    const long long sk_total = (long long)total_tiles * num_k_total;
+    while (it.next(sg)) {
+      const int tile = sg.tile;
       const int bt = tile / tiles_per_batch;
       const int rem = tile - bt * tiles_per_batch;
       const int n_blk = rem / p.num_m;
       const int m_blk = rem - n_blk * p.num_m;
-      const int m0 = m_blk * kBM, n0 = n_blk * p.bn;
+      const int m0 = m_blk * (kBM * CTAS) + (int)rank * kBM, n0 = n_blk * p.bn;
       const int ab0 = bt % p.nb0, ab1 = bt / p.nb0;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
@@ -263,23 +356,72 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const bool row_ok = row < p.M;
       const long long doff = (long long)ab0 * p.d_bs0 + (long long)ab1 * p.d_bs1 + (long long)row * p.d_rs;
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * kAccStride;
-      const int nchunks = p.bn / 32;
+      const int col_limit = min(p.N, n0 + p.bn);
+      const int nchunks = (p.bn + 31) / 32;
+      if (sg.kb0 > 0) {
+        // ---- stream-K contributor: publish this CTA's fp32 partial, the tile's owner finishes it ----
+        float* slot = p.sk_ws + ((long long)blockIdx.x * kBM + (q * 32 + lane)) * kAccStride;
+        for (int c = 0; c < nchunks; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(t0 + c * 32, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            reinterpret_cast<uint4*>(slot + c * 32)[j] = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+        }
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 64) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.sk_flags + blockIdx.x), "r"(p.sk_epoch) : "memory");
+      } else {
+        // number of following units that hold later k-blocks of this tile (0 unless stream-K split it)
+        int ncontrib = 0;
+        if (sg.kb1 < num_k_total) {
+          const long long tile_end = (long long)(tile + 1) * num_k_total;
+          for (int v = unit + 1; v < nunits && sk_total * v / nunits < tile_end; ++v) ++ncontrib;
+          for (int v = 1; v <= ncontrib; ++v) {
+            const unsigned int* f = p.sk_flags + (unit + v) * CTAS + rank;
+            unsigned int seen;
+            const long long tw = clock64();
+            do {
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+              if (clock64() - tw > 20000000000ll) {
+                printf("b200 gemm: stream-K wait timed out (block %d waits for block %d)\n", blockIdx.x, (unit + v) * CTAS + (int)rank);
+                __trap();
+              }
+            } while (seen != p.sk_epoch);
+          }
+        }
       for (int c = 0; c < nchunks; ++c) {
         const int col0 = n0 + c * 32;
-        if (col0 >= p.N) break;
+        if (col0 >= col_limit) break;
         uint32_t r[32];
         tmem_ld_32x32(t0 + c * 32, r);
         tmem_ld_wait();
+        for (int v = 1; v <= ncontrib; ++v) {
+          const float* slot = p.sk_ws + ((long long)((unit + v) * CTAS + rank) * kBM + (q * 32 + lane)) * kAccStride + c * 32;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            const float4 w = reinterpret_cast<const float4*>(slot)[j];
+            r[4 * j] = __float_as_uint(__uint_as_float(r[4 * j]) + w.x);
+            r[4 * j + 1] = __float_as_uint(__uint_as_float(r[4 * j + 1]) + w.y);
+            r[4 * j + 2] = __float_as_uint(__uint_as_float(r[4 * j + 2]) + w.z);
+            r[4 * j + 3] = __float_as_uint(__uint_as_float(r[4 * j + 3]) + w.w);
+          }
+        }
         if (p.out_dtype == B200_DT_BF16)
-          epilogue_store<__nv_bfloat16>(p, reinterpret_cast<__nv_bfloat16*>(p.D) + doff, col0, r, row_ok);
+          epilogue_store<__nv_bfloat16>(p, reinterpret_cast<__nv_bfloat16*>(p.D) + doff, col0, col_limit, r, row_ok);
         else if (p.out_dtype == B200_DT_FP32)
-          epilogue_store<float>(p, reinterpret_cast<float*>(p.D) + doff, col0, r, row_ok);
+          epilogue_store<float>(p, reinterpret_cast<float*>(p.D) + doff, col0, col_limit, r, row_ok);
         else
-          epilogue_store<__half>(p, reinterpret_cast<__half*>(p.D) + doff, col0, r, row_ok);
+          epilogue_store<__half>(p, reinterpret_cast<__half*>(p.D) + doff, col0, col_limit, r, row_ok);
+      }
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(tempty_bar(acc));
+      if (lane == 0) {
+        if (leader) mbar_arrive(tempty_bar(acc));
+        else mbar_arrive_cluster(mapa_shared(tempty_bar(acc), 0));
+      }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;
     }
@@ -287,9 +429,11 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 
   tc_fence_before();
   __syncthreads();
+  if constexpr (CTAS == 2) cluster_sync_all();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if constexpr (CTAS == 1) tmem_dealloc(tmem_base, 512);
+    else tmem_dealloc_2sm(tmem_base, 512);
   }
 }
 
@@ -298,6 +442,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 // ------------------------------------------------------------------------------------------------
 static int g_num_sms = 0;
 static int g_max_smem = 0;
+static int g_force_ctas = 0;  // B200_GEMM_CTAS=1|2 pins the CTA-group size (debugging / A-B timing)
 
 static int device_props() {
   if (g_num_sms == 0) {
@@ -306,31 +451,88 @@ static int device_props() {
     if (e != cudaSuccess) return (int)e;
     cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev);
     cudaDeviceGetAttribute(&g_max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
+    const char* f = getenv("B200_GEMM_CTAS");
+    if (f) g_force_ctas = atoi(f);
   }
   return 0;
 }
 
-// Tile-width choice: fewest SM-waves times the per-k-step cost of a 128 x bn tile
-// (tensor pipe: bn/2 cycles; shared-memory operand reads: 32 + bn/4 cycles).
-static int pick_bn(int M, int N, int batch, int step, int num_sms) {
-  if (N <= 32 && step <= 32) return 32;
-  const int num_m = ceil_div(M, kBM);
-  int best_bn = 256;
-  double best = 1e30;
-  for (int bn = 256; bn >= 64; bn -= step) {
-    if (bn % step) continue;
-    const long long tiles = (long long)batch * num_m * ceil_div(N, bn);
-    const long long waves = (tiles + num_sms - 1) / num_sms;
-    const double per = (bn / 2.0 > 32 + bn / 4.0) ? bn / 2.0 : 32 + bn / 4.0;
-    const double cost = (double)waves * (per + 6.0);  // + fixed per-k-block issue/barrier overhead
-    if (cost < best - 1e-9) { best = cost; best_bn = bn; }
+// Modelled cycles per k-block (four k-steps) of one unit tile (128*ctas x bn): the slower of the
+// tensor pipe (2*bn) and this SM's shared-memory port, which carries the TMA fill and the UMMA
+// operand reads of the same bytes ((16 KB + 128 B * bn / ctas) * 2 at 128 B/cycle), plus issue and
+// barrier overhead. A CTA pair halves the B bytes per SM, which is what makes 256-wide tiles
+// tensor-bound.
+static double kblock_cost(int ctas, int bn) {
+  const double t_mma = 2.0 * bn;
+  const double t_smem = 256.0 + 2.0 * bn / ctas;
+  return (t_mma > t_smem ? t_mma : t_smem) + 40.0;
+}
+
+struct GemmConfig {
+  int ctas, bn, stream_k;
+  double cost;
+};
+
+static GemmConfig pick_config(int M, int N, int batch, int nkt, int b_mn, int EPR, int num_sms, bool allow_sk) {
+  GemmConfig best = {1, 256, 0, 1e30};
+  const char* no_sk = getenv("B200_GEMM_NO_STREAMK");
+  for (int ctas = 2; ctas >= 1; --ctas) {
+    if (g_force_ctas && ctas != g_force_ctas) continue;
+    if (ctas == 2 && (M <= kBM || num_sms < 2)) continue;
+    const int step = b_mn ? EPR * ctas : 16 * ctas;  // MN-major B is staged in 128-byte column chunks per CTA
+    const int units = num_sms / ctas;
+    for (int bn = 256; bn >= 16 * ctas; bn -= 16) {
+      if (bn % step) continue;
+      if (bn > 32 && bn > 2 * ((N + 15) / 16 * 16)) continue;  // do not pick tiles far wider than N
+      const long long tiles = (long long)batch * ceil_div(M, kBM * ctas) * ceil_div(N, bn);
+      const long long waves = (tiles + units - 1) / units;
+      const double per = kblock_cost(ctas, bn);
+      const double classic = (double)waves * nkt * per;
+      if (classic < best.cost * 0.999) best = {ctas, bn, 0, classic};
+      if (allow_sk && !no_sk && tiles % units != 0 && tiles * nkt >= 4ll * units) {
+        // equal k-block ranges per unit; ~10 k-blocks' worth of partial-tile write/read/wait per unit
+        const double sk = ((double)tiles * nkt / units + 10.0) * per;
+        // measured: worth it only when classic scheduling wastes a large part of a wave (few tiles);
+        // with many waves the uneven k-ranges cost more L2 locality than the tail they recover
+        if (waves <= 4 && sk < classic * 0.85 && sk < best.cost * 0.97) best = {ctas, bn, 1, sk};
+      }
+    }
   }
-  return best_bn;
+  return best;
+}
+
+template <int ES, int CTAS>
+static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmA2, const CUtensorMap& tmB2,
+                  const GemmKernelParams& p, int grid, int smem, cudaStream_t stream) {
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<ES, CTAS>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_max_smem));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CTAS;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CHECK(cudaLaunchKernelEx(&cfg, gemm_tcgen05_kernel<ES, CTAS>, tmA, tmB, tmA2, tmB2, p));
+  return 0;
 }
 
 }  // namespace b200
 
 using namespace b200;
+
+B200_API long long b200_gemm_workspace_bytes(void) {
+  // one fp32 128 x 256 partial-tile slot per CTA + one flag per CTA, sized for the largest part
+  return 160ll * kBM * kAccStride * 4 + 160ll * 4;
+}
 
 B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   cudaStream_t stream = (cudaStream_t)stream_;
@@ -363,26 +565,36 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   p.alpha = a->alpha; p.beta = a->beta;
   p.out_dtype = a->out_dtype; p.bias_dtype = a->bias_dtype;
   p.a_mn = a->a_mn ? 1 : 0; p.b_mn = a->b_mn ? 1 : 0;
-  const int step = p.b_mn ? EPR : 32;  // MN-major B is loaded in 128-byte column chunks
-  p.bn = pick_bn(a->M, a->N, a->batch, step, g_num_sms);
-  p.num_m = ceil_div(a->M, kBM);
-  p.num_n = ceil_div(a->N, p.bn);
   p.num_k = ceil_div(a->K, EPR);
-  const int stage_bytes = kStageABytes + p.bn * 128;
+  const int nkt = p.num_k + (lora ? 1 : 0);
+  const long long sk_need = (long long)g_num_sms * kBM * kAccStride * 4 + (long long)g_num_sms * 4;
+  const bool allow_sk = a->workspace != nullptr && a->workspace_bytes >= sk_need;
+  const GemmConfig cfg = pick_config(a->M, a->N, a->batch, nkt, p.b_mn, EPR, g_num_sms, allow_sk);
+  const int ctas = cfg.ctas;
+  p.bn = cfg.bn;
+  const int bn_cta = p.bn / ctas;
+  p.num_m = ceil_div(a->M, kBM * ctas);
+  p.num_n = ceil_div(a->N, p.bn);
+  p.stream_k = cfg.stream_k;
+  p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0;
+  if (cfg.stream_k) {
+    static unsigned int epoch = 0;
+    p.sk_ws = reinterpret_cast<float*>(a->workspace);
+    p.sk_flags = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(a->workspace) +
+                                                 (long long)g_num_sms * kBM * kAccStride * 4);
+    p.sk_epoch = ++epoch;
+  }
+  const int stage_bytes = kStageABytes + bn_cta * 128;
   int stages = (g_max_smem - 2048) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 2) return B200_ERR_UNSUPPORTED;
   p.stages = stages;
-  const bool is_bf16 = a->in_dtype == B200_DT_BF16;
-  if (ES == 2) {
-    p.idesc_main = make_idesc_f16(kBM, p.bn, is_bf16, p.a_mn, p.b_mn);
-    p.idesc_lora = make_idesc_f16(kBM, p.bn, is_bf16, false, false);
-  } else {
-    // kind::tf32: a_format = b_format = 2
-    p.idesc_main = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16) |
-                   ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
-    p.idesc_lora = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(p.bn >> 3) << 17) | ((uint32_t)(kBM >> 4) << 24);
-  }
+  const int umma_m = kBM * ctas;
+  const uint32_t fmt = ES == 4 ? 2u : (a->in_dtype == B200_DT_BF16 ? 1u : 0u);  // tf32 / bf16 / f16
+  const uint32_t idesc_base = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(p.bn >> 3) << 17) |
+                              ((uint32_t)(umma_m >> 4) << 24);
+  p.idesc_main = idesc_base | ((uint32_t)p.a_mn << 15) | ((uint32_t)p.b_mn << 16);
+  p.idesc_lora = idesc_base;
   const int out_es = a->out_dtype == B200_DT_FP32 ? 4 : 2;
   const int per_vec = 16 / out_es;
   p.vec_ok = ((reinterpret_cast<uintptr_t>(a->D) & 15) == 0) && (a->d_rs % per_vec == 0) &&
@@ -406,7 +618,7 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   {
     uint64_t dims[4], str[3];
     uint32_t box[4];
-    if (!p.b_mn) { dims[0] = a->K; dims[1] = a->N; box[0] = EPR; box[1] = p.bn; }
+    if (!p.b_mn) { dims[0] = a->K; dims[1] = a->N; box[0] = EPR; box[1] = bn_cta; }
     else         { dims[0] = a->N; dims[1] = a->K; box[0] = EPR; box[1] = EPR; }
     dims[2] = p.nb0_b; dims[3] = nb1_b; box[2] = 1; box[3] = 1;
     str[0] = (uint64_t)a->b_rs * ES; str[1] = (uint64_t)a->b_bs0 * ES; str[2] = (uint64_t)a->b_bs1 * ES;
@@ -419,7 +631,7 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
     rc = make_tensor_map(&tmA2, a->A2, ES, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
     uint64_t dimsb[4] = {(uint64_t)a->K2, (uint64_t)a->N, 1, 1}, strb[3] = {(uint64_t)a->b2_rs * ES, 0, 0};
-    uint32_t boxb[4] = {(uint32_t)EPR, (uint32_t)p.bn, 1, 1};
+    uint32_t boxb[4] = {(uint32_t)EPR, (uint32_t)bn_cta, 1, 1};
     rc = make_tensor_map(&tmB2, a->B2, ES, 4, dimsb, strb, boxb, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
   } else {
@@ -428,23 +640,14 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   }
 
   const long long total_tiles = (long long)p.num_m * p.num_n * p.batch;
-  const int grid = (int)(total_tiles < g_num_sms ? total_tiles : g_num_sms);
+  const int units = g_num_sms / ctas;
+  const int grid = (cfg.stream_k ? units : (int)(total_tiles < units ? total_tiles : units)) * ctas;
   const int smem = stages * stage_bytes + 8 * (2 * stages + 5) + 1024;
-  if (ES == 2) {
-    static int configured = 0;
-    if (configured < smem) {
-      B200_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_max_smem));
-      configured = g_max_smem;
-    }
-    gemm_tcgen05_kernel<2><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmA2, tmB2, p);
-  } else {
-    static int configured = 0;
-    if (configured < smem) {
-      B200_CHECK(cudaFuncSetAttribute(gemm_tcgen05_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, g_max_smem));
-      configured = g_max_smem;
-    }
-    gemm_tcgen05_kernel<4><<<grid, kGemmThreads, smem, stream>>>(tmA, tmB, tmA2, tmB2, p);
-  }
+  if (ES == 2) rc = ctas == 2 ? launch<2, 2>(tmA, tmB, tmA2, tmB2, p, grid, smem, stream)
+                              : launch<2, 1>(tmA, tmB, tmA2, tmB2, p, grid, smem, stream);
+  else rc = ctas == 2 ? launch<4, 2>(tmA, tmB, tmA2, tmB2, p, grid, smem, stream)
+                      : launch<4, 1>(tmA, tmB, tmA2, tmB2, p, grid, smem, stream);
+  if (rc) return rc;
   B200_LAUNCH_CHECK();
   return 0;
 }

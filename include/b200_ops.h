@@ -62,7 +62,15 @@ typedef struct {
   int64_t a2_rs, b2_rs;
   int32_t a_mn, b_mn, in_dtype, out_dtype;
   float alpha, beta;
+  /* Optional stream-K scratch (zero-initialised once by the caller, then owned by one stream):
+   * at least b200_gemm_workspace_bytes() bytes. With it, problems whose tile count does not fill
+   * whole SM waves are split evenly along K across all SMs; without it (NULL) every tile is
+   * computed by one CTA / CTA pair. */
+  void* workspace;
+  int64_t workspace_bytes;
 } b200_gemm_args;
+
+long long b200_gemm_workspace_bytes(void);
 
 int b200_gemm(const b200_gemm_args* args, void* stream);
 

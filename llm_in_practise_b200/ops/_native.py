@@ -120,6 +120,7 @@ class GemmArgs(ctypes.Structure):
         ("a2_rs", ctypes.c_int64), ("b2_rs", ctypes.c_int64),
         ("a_mn", ctypes.c_int32), ("b_mn", ctypes.c_int32), ("in_dtype", ctypes.c_int32), ("out_dtype", ctypes.c_int32),
         ("alpha", ctypes.c_float), ("beta", ctypes.c_float),
+        ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_int64),
     ]
 
 

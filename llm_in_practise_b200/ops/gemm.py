@@ -22,6 +22,21 @@ import torch
 from . import _native as nv
 
 
+_sk_workspaces = {}
+
+
+def _stream_k_workspace(device: torch.device) -> torch.Tensor:
+    """Per (device, stream) scratch for stream-K GEMMs: zeroed once, then owned by that stream."""
+    key = (device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _sk_workspaces.get(key)
+    if ws is None:
+        fn = nv.lib().b200_gemm_workspace_bytes
+        fn.restype = ctypes.c_longlong
+        ws = torch.zeros(int(fn()), dtype=torch.uint8, device=device)
+        _sk_workspaces[key] = ws
+    return ws
+
+
 def _as4d(t: torch.Tensor) -> torch.Tensor:
     while t.dim() < 4:
         t = t.unsqueeze(0)
@@ -133,6 +148,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     else:
         args.A2 = args.B2 = 0
         args.K2 = 0
+    ws = _stream_k_workspace(a.device)
+    args.workspace, args.workspace_bytes = ws.data_ptr(), ws.numel()
     rc = nv.lib().b200_gemm(ctypes.byref(args), nv.stream())
     nv.check(rc, f"gemm M={M} N={N} K={K} batch={batch}")
     nv.count_launch()
