@@ -31,7 +31,8 @@ def symm_available() -> bool:
     if dist.get_backend() != "nccl" or dist.get_world_size() > MAX_RANKS:
         return False
     try:
-        import torch.distributed._symmetric_memory  # noqa: F401
+        import importlib
+        importlib.import_module("torch.distributed._symmetric_memory")
         return True
     except Exception:
         return False
