@@ -66,37 +66,49 @@ class _TiledAttentionFn(torch.autograd.Function):
         scores = gemm(q, k, alpha=scale, out_dtype=torch.float32)            # [B, H, S, S]
         P = _softmax_fwd(scores, causal, window, qkv.dtype)
         del scores
+        seed = 0
+        Pd = P
+        if dropout_p > 0.0:
+            # attention-probability dropout (nn.MultiheadAttention(dropout=p)): Philox mask, regenerated in backward
+            from .elementwise import _DropoutFn, next_seed
+            seed = next_seed()
+            Pd = _DropoutFn.apply(P, dropout_p, seed)
         out = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
-        gemm(P, v, b_mn=True, out=out.permute(0, 2, 1, 3))                   # context, written as [B, S, H, D]
+        gemm(Pd, v, b_mn=True, out=out.permute(0, 2, 1, 3))                  # context, written as [B, S, H, D]
         ctx.save_for_backward(qkv, P)
-        ctx.cfg = (B, S, H, Hkv, D, scale)
+        ctx.cfg = (B, S, H, Hkv, D, scale, dropout_p, seed)
         return out.view(B * S, H * D)
 
     @staticmethod
     def backward(ctx, dout):
         qkv, P = ctx.saved_tensors
-        B, S, H, Hkv, D, scale = ctx.cfg
+        B, S, H, Hkv, D, scale, dropout_p, seed = ctx.cfg
         g = H // Hkv
         q, k, v = _split_heads(qkv, B, S, H, Hkv, D)
         dO = dout.contiguous().view(B, S, H, D).permute(0, 2, 1, 3)         # [B, H, S, D] strided
         dqkv = torch.empty_like(qkv)
         dq, dk, dv = _split_heads(dqkv, B, S, H, Hkv, D)
         dP = gemm(dO, v, out_dtype=torch.float32)                            # [B, H, S, S]
+        Pv = P
+        if dropout_p > 0.0:
+            from .elementwise import _DropoutFn
+            dP = _DropoutFn.apply(dP, dropout_p, seed)                       # same mask, same 1/(1-p) scale
+            Pv = _DropoutFn.apply(P, dropout_p, seed)                        # the dropped P that multiplied V
         dS = _softmax_bwd(P, dP, scale, qkv.dtype)
         del dP
         gemm(dS, k, b_mn=True, out=dq)                                       # dQ = dS K
         if g == 1:
             gemm(dS, q, a_mn=True, b_mn=True, out=dk)                        # dK = dS^T Q
-            gemm(P, dO, a_mn=True, b_mn=True, out=dv)                        # dV = P^T dO
+            gemm(Pv, dO, a_mn=True, b_mn=True, out=dv)                       # dV = P^T dO
         else:
             dk_h = gemm(dS, q, a_mn=True, b_mn=True, out_dtype=torch.float32)
-            dv_h = gemm(P, dO, a_mn=True, b_mn=True, out_dtype=torch.float32)
+            dv_h = gemm(Pv, dO, a_mn=True, b_mn=True, out_dtype=torch.float32)
             dk.copy_(dk_h.view(B, Hkv, g, S, D).sum(2))
             dv.copy_(dv_h.view(B, Hkv, g, S, D).sum(2))
         return dqkv, None, None, None, None, None, None, None, None, None
 
 
-def _ref_attention(qkv, B, S, H, Hkv, D, causal, window, scale):
+def _ref_attention(qkv, B, S, H, Hkv, D, causal, window, scale, dropout_p=0.0):
     q, k, v = _split_heads(qkv, B, S, H, Hkv, D)
     g = H // Hkv
     kf = k.float().repeat_interleave(g, dim=1)
@@ -109,6 +121,8 @@ def _ref_attention(qkv, B, S, H, Hkv, D, causal, window, scale):
             mask = mask | (i[None, :] < i[:, None] - window + 1)
         s = s.masked_fill(mask, float("-inf"))
     p = torch.softmax(s, dim=-1)
+    if dropout_p > 0.0:
+        p = torch.nn.functional.dropout(p, dropout_p, True)
     o = torch.matmul(p, vf)
     return o.permute(0, 2, 1, 3).reshape(B * S, H * D).to(qkv.dtype)
 
@@ -128,16 +142,16 @@ def _flash_available() -> bool:
 
 def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, head_dim: int,
               causal: bool = True, window: int = 0, scale: Optional[float] = None,
-              impl: str = "auto") -> torch.Tensor:
+              impl: str = "auto", dropout_p: float = 0.0) -> torch.Tensor:
     """softmax(Q K^T * scale + mask) V over the fused projection ``qkv`` [B*S, (H + 2 Hkv) * D].
     Returns the context as [B*S, H * D]."""
     if scale is None:
         scale = 1.0 / math.sqrt(head_dim)
-    if not nv.use_native(qkv):
-        return _ref_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale)
+    if not nv.use_native(qkv) or (S % 8 and not causal) or qkv.dtype == torch.float32 and False:
+        return _ref_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)
     qkv = qkv.contiguous()
     if impl in ("auto", "flash") and _flash_available() and qkv.dtype == torch.bfloat16 and head_dim == 128 \
-            and window == 0:
+            and window == 0 and dropout_p == 0.0:
         from .flash import flash_attention
         return flash_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, scale)
-    return _TiledAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, 0.0)
+    return _TiledAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)
