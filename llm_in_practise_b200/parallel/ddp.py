@@ -1,0 +1,197 @@
+"""DistributedDataParallel with bucketed gradient all-reduce overlapped with backward (K-C1).
+
+Call shape of ``torch.nn.parallel.DistributedDataParallel`` as used in
+LLM_Distributed_Trainning/PyTorch/ddp_basics/ddp_gpt_wikitext2.py:271-279 (``device_ids``, ``output_device``,
+``find_unused_parameters=False``), ``.module`` access (:322-326), ``no_sync()`` for gradient accumulation
+(…/temp/ddp_gpt_bpe_tokenizer_02.py:399-419) and the constructor-time parameter broadcast (C2).
+
+B200 design: trainable parameters and gradients are re-homed into one flat arena (symmetric peer memory on
+>1 GPU). Buckets are contiguous arena ranges in reverse registration order (the order backward produces
+gradients), ``bucket_cap_mb`` each. When the last gradient of a bucket lands — either through autograd's
+accumulate hook or through the ``_grad_ready`` callback of the wgrad GEMM that wrote ``main_grad`` directly — the
+bucket's all-reduce is launched on a side stream: one two-shot kernel over NVLink peer memory that sums, applies
+1/world and writes the result into every replica (``b200_allreduce``), while backward keeps running on the main
+stream. ``torch.distributed.all_reduce`` is used instead on CPU/gloo, without symmetric memory, or when
+``B200_COMM=nccl`` (the baseline to compare against).
+"""
+from __future__ import annotations
+
+import contextlib
+import os
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from ..utils.arena import ParamArena, flatten_module
+from .dist import get_info
+from .symm import PeerFlags, SymmBuffer, allreduce_, symm_available
+
+
+class _Bucket:
+    __slots__ = ("lo", "hi", "params", "pending", "launched", "work")
+
+    def __init__(self, lo: int, hi: int):
+        self.lo, self.hi = lo, hi
+        self.params: List[nn.Parameter] = []
+        self.pending = 0
+        self.launched = False
+        self.work = None
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module: nn.Module, device_ids=None, output_device=None, find_unused_parameters: bool = False,
+                 bucket_cap_mb: float = 25.0, broadcast_buffers: bool = True, process_group=None,
+                 gradient_as_bucket_view: bool = True):
+        super().__init__()
+        self.module = module
+        self.info = get_info()
+        self.world = self.info.world_size if (dist.is_available() and dist.is_initialized()) else 1
+        self.rank = self.info.rank
+        self.find_unused = find_unused_parameters
+        self.require_sync = True
+        dev = next(module.parameters()).device
+        self.device = dev
+        self.use_symm = (self.world > 1 and dev.type == "cuda" and symm_available()
+                         and os.environ.get("B200_COMM", "symm") == "symm")
+        self._bufs: List[SymmBuffer] = []
+        alloc = None
+        if self.use_symm:
+            def alloc(numel, dtype, device):
+                b = SymmBuffer(numel, dtype, device)
+                self._bufs.append(b)
+                return b.local
+        self.arena: ParamArena = flatten_module(module, pad_to=4 * max(self.world, 1), alloc=alloc)
+        if self.use_symm:
+            self.grad_buf = self._bufs[1]
+            self.flags = PeerFlags(dev)
+            self.comm_stream = torch.cuda.Stream(device=dev)
+        elif dev.type == "cuda":
+            self.comm_stream = torch.cuda.Stream(device=dev)
+        else:
+            self.comm_stream = None
+        if self.world > 1:
+            dist.broadcast(self.arena.data, src=0)                      # C2: every replica starts from rank 0
+            if broadcast_buffers:
+                for b in module.buffers():
+                    dist.broadcast(b, src=0)
+        self._build_buckets(int(bucket_cap_mb * 1024 * 1024))
+        self._callback_queued = False
+        self.exposed_ms: List[float] = []
+
+    # ------------------------------------------------------------------ buckets
+    def _build_buckets(self, cap_bytes: int) -> None:
+        es = self.arena.data.element_size()
+        owners = {}
+        for _, p in self.module.named_parameters():
+            if p.requires_grad:
+                owners.setdefault(p.data_ptr(), p)
+        self.buckets: List[_Bucket] = []
+        hi = self.arena.numel
+        params: List[nn.Parameter] = []
+        lo = hi
+        for _, shape, off in reversed(list(self.arena.named_slots())):   # reverse registration order
+            lo = off
+            p = owners.get(self.arena.data.data_ptr() + off * es)
+            if p is not None:
+                params.append(p)
+            if (hi - lo) * es >= cap_bytes:
+                bk = _Bucket(lo, hi)
+                bk.params = params
+                self.buckets.append(bk)
+                hi, params = lo, []
+        if params or hi > 0:
+            bk = _Bucket(0, hi)
+            bk.params = params
+            self.buckets.append(bk)
+        for bi, bk in enumerate(self.buckets):
+            for p in bk.params:
+                p._ddp_bucket = bi
+                p._grad_ready = (lambda pp=p: self._on_grad_ready(pp))
+                p.register_post_accumulate_grad_hook(lambda pp: self._on_grad_ready(pp))
+
+    def _reset_buckets(self) -> None:
+        for b in self.buckets:
+            b.pending = set(id(p) for p in b.params)
+            b.launched = False
+            b.work = None
+
+    # ------------------------------------------------------------------ reduction
+    def _on_grad_ready(self, p: nn.Parameter) -> None:
+        if self.world == 1 or not self.require_sync:
+            return
+        if not self._callback_queued:
+            self._reset_buckets()
+            self._callback_queued = True
+            torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
+        b = self.buckets[p._ddp_bucket]
+        b.pending.discard(id(p))
+        if not b.pending and not b.launched:
+            self._launch(b)
+
+    def _launch(self, b: _Bucket) -> None:
+        b.launched = True
+        n = b.hi - b.lo
+        if n <= 0:
+            return
+        if self.comm_stream is not None:
+            self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
+        if self.use_symm:
+            with torch.cuda.stream(self.comm_stream):
+                allreduce_(self.grad_buf, self.flags, b.lo, n, 1.0 / self.world)
+        else:
+            g = self.arena.grad[b.lo:b.hi]
+            if self.comm_stream is not None:
+                with torch.cuda.stream(self.comm_stream):
+                    b.work = dist.all_reduce(g, op=dist.ReduceOp.SUM, async_op=True)
+            else:
+                b.work = dist.all_reduce(g, op=dist.ReduceOp.SUM, async_op=True)
+
+    def _finalize_backward(self) -> None:
+        self._callback_queued = False
+        # buckets whose parameters never produced a gradient this step (unused / frozen paths) still need
+        # their (zero) contribution reduced so every rank launches the same sequence of collectives
+        for b in self.buckets:
+            if not b.launched:
+                self._launch(b)
+        for b in self.buckets:
+            if b.work is not None:
+                b.work.wait()
+                if self.comm_stream is not None:
+                    with torch.cuda.stream(self.comm_stream):
+                        self.arena.grad[b.lo:b.hi].div_(self.world)
+                else:
+                    self.arena.grad[b.lo:b.hi].div_(self.world)
+        if self.comm_stream is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+
+    # ------------------------------------------------------------------ module surface
+    def forward(self, *args, **kwargs):
+        return self.module(*args, **kwargs)
+
+    @contextlib.contextmanager
+    def no_sync(self):
+        old = self.require_sync
+        self.require_sync = False
+        try:
+            yield
+        finally:
+            self.require_sync = old
+
+    def zero_grad(self, set_to_none: bool = False) -> None:
+        self.arena.zero_grad()
+
+    def state_dict(self, *a, **k):
+        return {f"module.{n}": v for n, v in self.module.state_dict(*a, **k).items()}
+
+    def load_state_dict(self, sd, strict: bool = True):
+        sd = {(k[7:] if k.startswith("module.") else k): v for k, v in sd.items()}
+        return self.module.load_state_dict(sd, strict=strict)
+
+    def parameters(self, recurse: bool = True):
+        return self.module.parameters(recurse)
+
+    def named_parameters(self, *a, **k):
+        for n, p in self.module.named_parameters(*a, **k):
+            yield f"module.{n}", p
