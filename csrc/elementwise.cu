@@ -476,3 +476,33 @@ B200_API int b200_cast(const void* x, void* y, long long n, float scale, int in_
   B200_LAUNCH_CHECK();
   return 0;
 }
+
+// y(fp32) += float(x) * scale, then x = 0 when clear_x: folds a low-precision gradient arena into the fp32
+// main-gradient arena in one pass (mixed-precision training; see utils/arena.py MixedArena).
+namespace b200 {
+template <typename T>
+__global__ void fold_grad_kernel(T* __restrict__ x, float* __restrict__ y, long long n, float scale, int clear_x) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    const float v = to_f32<T>(x[i]);
+    if (v != 0.f) {
+      y[i] += v * scale;
+      if (clear_x) x[i] = from_f32<T>(0.f);
+    }
+  }
+}
+}  // namespace b200
+
+B200_API int b200_fold_grad(void* x, float* y, long long n, float scale, int clear_x, int dtype, void* stream) {
+  if (n <= 0) return 0;
+  const int tb = 256;
+  long long g = (n + tb - 1) / tb;
+  const unsigned grid = (unsigned)(g > 148 * 16 ? 148 * 16 : g);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_DT_BF16) b200::fold_grad_kernel<__nv_bfloat16><<<grid, tb, 0, st>>>((__nv_bfloat16*)x, y, n, scale, clear_x);
+  else if (dtype == B200_DT_FP16) b200::fold_grad_kernel<__half><<<grid, tb, 0, st>>>((__half*)x, y, n, scale, clear_x);
+  else return B200_ERR_UNSUPPORTED;
+  B200_LAUNCH_CHECK();
+  return 0;
+}

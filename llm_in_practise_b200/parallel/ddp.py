@@ -43,8 +43,9 @@ class _Bucket:
 class DistributedDataParallel(nn.Module):
     def __init__(self, module: nn.Module, device_ids=None, output_device=None, find_unused_parameters: bool = False,
                  bucket_cap_mb: float = 25.0, broadcast_buffers: bool = True, process_group=None,
-                 gradient_as_bucket_view: bool = True):
+                 gradient_as_bucket_view: bool = True, mixed_precision: Optional[torch.dtype] = None):
         super().__init__()
+        self.mixed = mixed_precision
         self.module = module
         self.info = get_info()
         self.world = self.info.world_size if (dist.is_available() and dist.is_initialized()) else 1
@@ -62,7 +63,12 @@ class DistributedDataParallel(nn.Module):
                 b = SymmBuffer(numel, dtype, device)
                 self._bufs.append(b)
                 return b.local
-        self.arena: ParamArena = flatten_module(module, pad_to=4 * max(self.world, 1), alloc=alloc)
+        if mixed_precision is not None:
+            # bf16/fp16 working weights, fp32 masters + fp32 main grads (the all-reduce runs on the fp32 arena)
+            from ..utils.arena import flatten_module_mixed
+            self.arena = flatten_module_mixed(module, mixed_precision, pad_to=4 * max(self.world, 1), alloc=alloc)
+        else:
+            self.arena: ParamArena = flatten_module(module, pad_to=4 * max(self.world, 1), alloc=alloc)
         if self.use_symm:
             self.grad_buf = self._bufs[1]
             self.flags = PeerFlags(dev)
@@ -73,6 +79,8 @@ class DistributedDataParallel(nn.Module):
             self.comm_stream = None
         if self.world > 1:
             dist.broadcast(self.arena.data, src=0)                      # C2: every replica starts from rank 0
+            if mixed_precision is not None:
+                self.arena.lowp.copy_(self.arena.data)
             if broadcast_buffers:
                 for b in module.buffers():
                     dist.broadcast(b, src=0)
@@ -118,6 +126,19 @@ class DistributedDataParallel(nn.Module):
             b.work = None
 
     # ------------------------------------------------------------------ reduction
+    def make_optimizer(self, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01,
+                       eight_bit: bool = False):
+        """One-launch AdamW over the flat arena (updates fp32 masters and rewrites the low-precision copy)."""
+        from ..optim.adamw import FusedAdamW, PagedAdamW8bit
+        cls = PagedAdamW8bit if eight_bit else FusedAdamW
+        return cls(self.arena, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay,
+                   lowp_copy=getattr(self.arena, "lowp", None))
+
+    def finish_local_grads(self) -> None:
+        """World size 1 / no_sync boundary helper: fold low-precision gradients into the fp32 arena."""
+        if self.mixed is not None:
+            self.arena.fold()
+
     def _on_grad_ready(self, p: nn.Parameter) -> None:
         if self.world == 1 or not self.require_sync:
             return
@@ -135,6 +156,8 @@ class DistributedDataParallel(nn.Module):
         n = b.hi - b.lo
         if n <= 0:
             return
+        if self.mixed is not None:
+            self.arena.fold(b.lo, b.hi)
         if self.comm_stream is not None:
             self.comm_stream.wait_stream(torch.cuda.current_stream(self.device))
         if self.use_symm:

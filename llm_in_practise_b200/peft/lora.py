@@ -209,8 +209,9 @@ class PeftModel(nn.Module):
                 for part in lin._lora_names:
                     lo, hi = lin.part_range(part)
                     w[lo:hi] += lin.lora_delta(part).to(w.device)
+                tgt = torch.bfloat16 if lin.nf4 is not None else lin.weight.dtype
                 lin.nf4 = None
-                lin.weight = nn.Parameter(w.to(torch.bfloat16), requires_grad=False)
+                lin.weight = nn.Parameter(w.to(tgt), requires_grad=False)
                 lin._b_slices = []
                 lin._lora_names = []
                 for attr in ("lora_A", "lora_Bt"):

@@ -129,3 +129,63 @@ def flatten_module(module: nn.Module, dtype: Optional[torch.dtype] = None, devic
             p.grad = g
             p.main_grad = g
     return arena
+
+
+class MixedArena(ParamArena):
+    """fp32 master + fp32 main-gradient arena (``data`` / ``grad``) with a low-precision twin:
+    ``lowp`` holds the working weights the modules compute with (``p.data`` views) and ``lowp_grad`` receives
+    whatever autograd produces in that dtype. Kernels that know about ``p.main_grad`` (wgrad GEMM, fused CE)
+    accumulate straight into the fp32 arena; ``fold()`` adds the rest in one launch. The optimizer updates the
+    master and rewrites ``lowp`` in the same pass (``p_lowp`` of ``b200_adamw``)."""
+
+    lowp: Optional[torch.Tensor] = None
+    lowp_grad: Optional[torch.Tensor] = None
+
+    def fold(self, lo: int = 0, hi: Optional[int] = None) -> None:
+        hi = self.numel if hi is None else hi
+        x, y = self.lowp_grad[lo:hi], self.grad[lo:hi]
+        from ..ops import _native as nv
+        if nv.use_native(x):
+            import ctypes
+            vp, i64, i32, f32 = ctypes.c_void_p, ctypes.c_longlong, ctypes.c_int, ctypes.c_float
+            fn = nv.proto("b200_fold_grad", [vp, vp, i64, f32, i32, i32, vp])
+            nv.check(fn(nv.ptr(x), nv.ptr(y), hi - lo, 1.0, 1, nv.dtype_code(x.dtype), nv.stream()), "fold_grad")
+            nv.count_launch()
+        else:
+            y += x.float()
+            x.zero_()
+
+    def zero_grad(self) -> None:
+        super().zero_grad()
+        if self.lowp_grad is not None:
+            self.lowp_grad.zero_()
+
+
+def flatten_module_mixed(module: nn.Module, lowp_dtype: torch.dtype = torch.bfloat16, pad_to: int = 1,
+                         alloc=None) -> MixedArena:
+    """Mixed-precision re-homing: parameters become ``lowp_dtype`` views, masters and main grads are fp32."""
+    params: List[Tuple[str, nn.Parameter]] = []
+    seen = set()
+    for name, p in module.named_parameters(remove_duplicate=True):
+        if p.requires_grad and id(p) not in seen:
+            seen.add(id(p))
+            params.append((name, p))
+    if not params:
+        raise ValueError("module has no trainable parameters")
+    device = params[0][1].device
+    arena = MixedArena(dtype=torch.float32, device=device, pad_to=pad_to)
+    idxs = [arena.request(n, p.shape) for n, p in params]
+    arena.finalize(alloc=alloc)
+    arena.lowp = torch.zeros(arena.numel, dtype=lowp_dtype, device=device)
+    arena.lowp_grad = torch.zeros(arena.numel, dtype=lowp_dtype, device=device)
+    with torch.no_grad():
+        for (n, p), i in zip(params, idxs):
+            _, shape, off = arena._specs[i]
+            k = p.numel()
+            arena.view(i).copy_(p.data.float())
+            lv = arena.lowp[off:off + k].view(shape)
+            lv.copy_(p.data.to(lowp_dtype))
+            p.data = lv
+            p.grad = arena.lowp_grad[off:off + k].view(shape)
+            p.main_grad = arena.grad_view(i)
+    return arena
