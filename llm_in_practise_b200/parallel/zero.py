@@ -218,6 +218,8 @@ class ZeroEngine(nn.Module):
             arena = apply_lora(model, lora_config, pad_to=self.unit, alloc=alloc)
         elif arena is None:
             arena = getattr(model, "_lora_arena", None)
+            if arena is not None and hasattr(arena, "_symm_bufs") and self.use_symm:
+                self._symm_bufs = list(arena._symm_bufs)
             if arena is None or arena.numel % self.unit or (self.use_symm and not getattr(arena, "symmetric", False)):
                 if arena is not None:
                     raise ValueError("existing adapter arena is not laid out for this world size; pass lora_config "

@@ -89,9 +89,25 @@ def prepare_model_for_kbit_training(model: nn.Module, use_gradient_checkpointing
     return model
 
 
-def apply_lora(model: nn.Module, config: LoraConfig, pad_to: int = 1, alloc=None) -> ParamArena:
-    """Attach adapters in place; returns the flat fp32 arena holding every adapter parameter."""
+def apply_lora(model: nn.Module, config: LoraConfig, pad_to: int = 2048, alloc=None) -> ParamArena:
+    """Attach adapters in place; returns the flat fp32 arena holding every adapter parameter.
+
+    The arena length is a multiple of 2048 (8 ranks x 256-value optimizer blocks) and, when a multi-GPU process
+    group already exists, it is placed in symmetric peer memory right away, so a model prepared with
+    ``get_peft_model`` can later be handed to the ZeRO engine / Trainer(deepspeed=...) as the reference scripts do."""
     targets = set(config.targets())
+    symm_bufs = []
+    if alloc is None:
+        try:
+            from ..parallel.symm import SymmBuffer, symm_available
+            import torch.distributed as dist
+            if symm_available() and dist.get_world_size() > 1 and next(model.parameters()).is_cuda:
+                def alloc(numel, dtype, device):
+                    b = SymmBuffer(numel, dtype, device)
+                    symm_bufs.append(b)
+                    return b.local
+        except Exception:
+            alloc = None
     for p in model.parameters():
         p.requires_grad_(False)
     dev = next(model.parameters()).device
@@ -107,6 +123,8 @@ def apply_lora(model: nn.Module, config: LoraConfig, pad_to: int = 1, alloc=None
     arena.finalize(alloc=alloc)
     for lin in touched:
         lin.materialize_lora()
+    if symm_bufs:
+        arena._symm_bufs = symm_bufs
     model._lora_arena = arena
     model._lora_config = config
     return arena
