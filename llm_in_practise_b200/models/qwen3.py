@@ -42,6 +42,8 @@ class Qwen3Config:
     max_position_embeddings: int = 40960
     tie_word_embeddings: bool = False
     model_type: str = "qwen3"
+    attention_bias: bool = False   # Qwen2-family checkpoints (DeepSeek-R1-Distill-Qwen-1.5B) have q/k/v biases ...
+    qk_norm: bool = True           # ... and no per-head q/k RMSNorm
 
     def to_dict(self):
         return asdict(self)
@@ -77,9 +79,10 @@ class Qwen3DecoderLayer(nn.Module):
         self.idx = idx
         self.input_layernorm = nn.Parameter(torch.ones(h, dtype=dtype, device=device))
         self.post_attention_layernorm = nn.Parameter(torch.ones(h, dtype=dtype, device=device))
-        self.q_norm = nn.Parameter(torch.ones(D, dtype=dtype, device=device))
-        self.k_norm = nn.Parameter(torch.ones(D, dtype=dtype, device=device))
-        self.qkv_proj = FusedLinear(h, [("q_proj", H * D), ("k_proj", Hkv * D), ("v_proj", Hkv * D)], dtype=dtype, device=device)
+        self.q_norm = nn.Parameter(torch.ones(D, dtype=dtype, device=device)) if cfg.qk_norm else None
+        self.k_norm = nn.Parameter(torch.ones(D, dtype=dtype, device=device)) if cfg.qk_norm else None
+        self.qkv_proj = FusedLinear(h, [("q_proj", H * D), ("k_proj", Hkv * D), ("v_proj", Hkv * D)], bias=cfg.attention_bias,
+                                    dtype=dtype, device=device)
         self.o_proj = FusedLinear(H * D, [("o_proj", h)], dtype=dtype, device=device)
         self.gate_up_proj = FusedLinear(h, [("gate_proj", F), ("up_proj", F)], dtype=dtype, device=device)
         self.down_proj = FusedLinear(F, [("down_proj", h)], dtype=dtype, device=device)
