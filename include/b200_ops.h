@@ -226,6 +226,20 @@ int b200_peer_gather(const void* const* src_ptrs, long long src_off_bytes, void*
 int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int rank, unsigned int epoch,
                       void* stream);
 
+/* ---- decode attention (csrc/decode_attn.cu) ----------------------------------------------------
+ * One new token per sequence: appends the rotated K/V of `qkv` [B, (H + 2 Hkv) * D] at position pos[b] of the
+ * caches [B, Hkv, max_len, D] and writes softmax(q K^T * scale) V over positions 0..pos[b] (optionally the last
+ * `window` ones) to out [B, H * D]. The KV-cache step behind HF generate(use_cache=True)
+ * (Fine-Tuning/inferences.py:50-58, Scripts/inference/01-deepseek1.5b-hf-infr.py:8-30). */
+int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, void* out, int B, int H,
+                     int Hkv, int D, int max_len, float scale, int window, int dtype, void* stream);
+
+/* ---- gradient fold (csrc/elementwise.cu) -------------------------------------------------------
+ * y (fp32) += scale * x (bf16/fp16), optionally clearing x: folds the low-precision .grad autograd produced for
+ * non-GEMM parameters into the fp32 main-grad arena (DeepSpeed bf16 "grad_accum_dtype": fp32 behaviour;
+ * LLM-Distributed-Training/04-DeepSpeed/ds_zero2_offload.json). */
+int b200_fold_grad(void* x, float* y, long long n, float scale, int clear_x, int dtype, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,231 @@
+"""Autoregressive generation for the Qwen family: KV cache, sampling, streaming, chat.
+
+Covers the HF ``generate`` usage of the reference: ``do_sample / temperature / top_p / top_k / repetition_penalty /
+max_new_tokens / eos_token_id`` (Fine-Tuning/inferences.py:50-58, Scripts/inference/01-deepseek1.5b-hf-infr.py:8-30,
+Quantization/GPTQModel/inference_qwen3_4b_gptq.py:58-68), token streaming through an iterator while generation runs in
+a background thread (``TextIteratorStreamer`` in Scripts/inference/06-…streaming-infr.py:55-85), and the multi-turn
+``chat(query, history, system_prompt, max_new_tokens)`` helper (Fine-Tuning/inferences.py:28-83).
+
+Prefill runs the training kernels (tcgen05 GEMMs, tiled causal attention) and stores the rotated K/V into the cache;
+each decode step is q|k|v GEMM/GEMV -> qk-norm+RoPE -> ``b200_decode_attn`` (appends to the cache, online softmax) ->
+o_proj -> MLP. 4-bit bases (NF4, GPTQ, AWQ) take the fused GEMV path for M <= 8.
+"""
+from __future__ import annotations
+
+import ctypes
+import queue
+import threading
+from dataclasses import dataclass
+from typing import Callable, Iterator, List, Optional, Sequence
+
+import torch
+
+from ..ops import _native as nv
+from ..ops import elementwise as ew
+from ..ops.attention import attention
+from ..ops.gemm import gemm
+from ..ops.norm import rms_norm
+
+vp, i32, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+
+
+@dataclass
+class GenerationConfig:
+    max_new_tokens: int = 256
+    do_sample: bool = False
+    temperature: float = 1.0
+    top_p: float = 1.0
+    top_k: int = 0
+    repetition_penalty: float = 1.0
+    eos_token_id: Optional[Sequence[int]] = None
+    pad_token_id: int = 0
+
+
+def sample_next(logits: torch.Tensor, cfg: GenerationConfig, prev: Optional[torch.Tensor] = None,
+                generator: Optional[torch.Generator] = None) -> torch.Tensor:
+    """logits [B, V] (any float dtype) -> next ids [B]; HF logits-processor order: repetition penalty,
+    temperature, top-k, top-p, then multinomial (or argmax when not sampling)."""
+    lg = logits.float()
+    if cfg.repetition_penalty != 1.0 and prev is not None:
+        g = lg.gather(1, prev)
+        g = torch.where(g < 0, g * cfg.repetition_penalty, g / cfg.repetition_penalty)
+        lg = lg.scatter(1, prev, g)
+    if not cfg.do_sample or cfg.temperature <= 0:
+        return lg.argmax(-1)
+    lg = lg / cfg.temperature
+    if cfg.top_k and cfg.top_k > 0:
+        kth = lg.topk(min(cfg.top_k, lg.shape[-1])).values[:, -1:]
+        lg = lg.masked_fill(lg < kth, float("-inf"))
+    if cfg.top_p < 1.0:
+        sl, si = lg.sort(descending=True)
+        cp = sl.softmax(-1).cumsum(-1)
+        drop = cp - sl.softmax(-1) > cfg.top_p          # keep the first token that crosses top_p
+        sl = sl.masked_fill(drop, float("-inf"))
+        lg = torch.full_like(lg, float("-inf")).scatter(1, si, sl)
+    return torch.multinomial(lg.softmax(-1), 1, generator=generator).squeeze(1)
+
+
+class KVCache:
+    def __init__(self, n_layers, B, Hkv, max_len, D, dtype, device):
+        self.k = [torch.zeros(B, Hkv, max_len, D, dtype=dtype, device=device) for _ in range(n_layers)]
+        self.v = [torch.zeros(B, Hkv, max_len, D, dtype=dtype, device=device) for _ in range(n_layers)]
+        self.max_len = max_len
+        self.len = 0
+
+
+def _decode_attn(qkv, ck, cv, pos, H, Hkv, D, scale):
+    B = qkv.shape[0]
+    if nv.use_native(qkv):
+        out = torch.empty(B, H * D, dtype=qkv.dtype, device=qkv.device)
+        fn = nv.proto("b200_decode_attn", [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
+        nv.check(fn(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(out), B, H, Hkv, D, ck.shape[2], scale, 0,
+                    nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn")
+        nv.count_launch()
+        return out
+    t = int(pos[0])
+    x = qkv.view(B, H + 2 * Hkv, D)
+    ck[:, :, t] = x[:, H:H + Hkv]
+    cv[:, :, t] = x[:, H + Hkv:]
+    g = H // Hkv
+    k = ck[:, :, :t + 1].float().repeat_interleave(g, 1)
+    v = cv[:, :, :t + 1].float().repeat_interleave(g, 1)
+    s = torch.einsum("bhd,bhtd->bht", x[:, :H].float(), k) * scale
+    return torch.einsum("bht,bhtd->bhd", s.softmax(-1), v).reshape(B, H * D).to(qkv.dtype)
+
+
+class Generator:
+    """Stateful runner around a ``Qwen3ForCausalLM`` (dense, NF4 or W4A16 base; merged or live LoRA)."""
+
+    def __init__(self, model, tokenizer=None, max_len: int = 4096):
+        self.model = getattr(model, "base_model", model)
+        self.tok = tokenizer
+        self.max_len = max_len
+        self.cfg = self.model.config
+
+    @torch.no_grad()
+    def _prefill(self, ids: torch.Tensor, cache: KVCache) -> torch.Tensor:
+        m, c = self.model, self.cfg
+        B, S = ids.shape
+        dev = ids.device
+        H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
+        cos, sin = m.rope(dev, self.max_len)
+        pos = torch.arange(S, device=dev, dtype=torch.int32).repeat(B)
+        Sp = (S + 7) // 8 * 8 if ids.is_cuda else S
+        delta, res = ew.embedding(ids.reshape(-1), m.embed_tokens), None
+        for li, layer in enumerate(m.layers):
+            x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
+            qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
+            t = qkv.view(B, S, H + 2 * Hkv, D)
+            cache.k[li][:, :, :S] = t[:, :, H:H + Hkv].permute(0, 2, 1, 3)
+            cache.v[li][:, :, :S] = t[:, :, H + Hkv:].permute(0, 2, 1, 3)
+            if Sp != S:
+                qkv = torch.nn.functional.pad(qkv.view(B, S, -1), (0, 0, 0, Sp - S)).reshape(B * Sp, -1)
+            ctx = attention(qkv, B, Sp, H, Hkv, D, causal=True)
+            if Sp != S:
+                ctx = ctx.view(B, Sp, -1)[:, :S].reshape(B * S, -1)
+            x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
+            delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
+        h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)
+        cache.len = S
+        last = h.view(B, S, -1)[:, -1]
+        return gemm(last.contiguous(), m.head_weight(), out_dtype=torch.float32)
+
+    @torch.no_grad()
+    def _decode(self, tok: torch.Tensor, cache: KVCache) -> torch.Tensor:
+        m, c = self.model, self.cfg
+        B = tok.shape[0]
+        dev = tok.device
+        H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
+        cos, sin = m.rope(dev, self.max_len)
+        pos = torch.full((B,), cache.len, device=dev, dtype=torch.int32)
+        delta, res = ew.embedding(tok.reshape(-1), m.embed_tokens), None
+        for li, layer in enumerate(m.layers):
+            x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
+            qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
+            ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5)
+            x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
+            delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
+        h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)
+        cache.len += 1
+        return gemm(h, m.head_weight(), out_dtype=torch.float32)
+
+    @torch.no_grad()
+    def generate(self, input_ids: torch.Tensor, config: Optional[GenerationConfig] = None, streamer=None,
+                 seed: Optional[int] = None, return_logprobs: bool = False, **kw):
+        cfg = config or GenerationConfig(**{k: v for k, v in kw.items() if k in GenerationConfig.__dataclass_fields__})
+        eos = cfg.eos_token_id
+        eos = [eos] if isinstance(eos, int) else list(eos or [])
+        was = self.model.training
+        self.model.eval()
+        B, S = input_ids.shape
+        dev = input_ids.device
+        total = min(self.max_len, S + cfg.max_new_tokens)
+        cache = KVCache(self.cfg.num_hidden_layers, B, self.cfg.num_key_value_heads, total, self.cfg.head_dim,
+                        self.model.embed_tokens.dtype, dev)
+        gen = torch.Generator(device=dev).manual_seed(seed) if seed is not None else None
+        logits = self._prefill(input_ids, cache)
+        out = input_ids
+        done = torch.zeros(B, dtype=torch.bool, device=dev)
+        logprobs: List[torch.Tensor] = []
+        for _ in range(total - S):
+            nxt = sample_next(logits, cfg, out, gen)
+            if return_logprobs:
+                logprobs.append(logits.float().log_softmax(-1).gather(1, nxt[:, None]).squeeze(1))
+            nxt = torch.where(done, torch.full_like(nxt, cfg.pad_token_id), nxt)
+            out = torch.cat([out, nxt[:, None]], 1)
+            if streamer is not None:
+                streamer.put(nxt)
+            for e in eos:
+                done |= nxt == e
+            if bool(done.all()):
+                break
+            logits = self._decode(nxt, cache)
+        if streamer is not None:
+            streamer.end()
+        self.model.train(was)
+        return (out, torch.stack(logprobs, 1)) if return_logprobs else out
+
+
+class TextIteratorStreamer:
+    """Iterator over decoded text pieces, fed by ``generate`` from another thread."""
+
+    def __init__(self, tokenizer, skip_prompt: bool = True, timeout: Optional[float] = None, **decode_kw):
+        self.tok, self.q, self.timeout, self.kw = tokenizer, queue.Queue(), timeout, decode_kw
+        self._end = object()
+
+    def put(self, ids: torch.Tensor) -> None:
+        self.q.put(self.tok.decode(ids.reshape(-1).tolist(), **self.kw))
+
+    def end(self) -> None:
+        self.q.put(self._end)
+
+    def __iter__(self) -> Iterator[str]:
+        return self
+
+    def __next__(self) -> str:
+        v = self.q.get(timeout=self.timeout)
+        if v is self._end:
+            raise StopIteration
+        return v
+
+
+def stream_generate(gen: Generator, input_ids: torch.Tensor, tokenizer, **kw) -> Iterator[str]:
+    st = TextIteratorStreamer(tokenizer)
+    th = threading.Thread(target=lambda: gen.generate(input_ids, streamer=st, **kw), daemon=True)
+    th.start()
+    return st
+
+
+def chat(gen: Generator, tokenizer, query: str, history=None, system_prompt: str = "You are a helpful assistant.",
+         max_new_tokens: int = 256, do_sample: bool = True, temperature: float = 0.7, top_p: float = 0.9, **kw):
+    """One chat turn with hand-rendered ChatML; returns (response, new_history)."""
+    from ..data.chat import build_messages, render_chatml
+    history = list(history or [])
+    text = render_chatml(build_messages(query, None, system_prompt, history), add_generation_prompt=True, space_before_end=False)
+    ids = torch.tensor([tokenizer.encode(text)], device=gen.model.embed_tokens.device)
+    eos = [t for t in (getattr(tokenizer, "eos_token_id", None),) if t is not None]
+    out = gen.generate(ids, max_new_tokens=max_new_tokens, do_sample=do_sample, temperature=temperature, top_p=top_p,
+                       eos_token_id=eos, **kw)
+    resp = tokenizer.decode(out[0, ids.shape[1]:].tolist())
+    history.append((query, resp))
+    return resp, history

@@ -101,6 +101,8 @@ def save_file(tensors: Dict[str, torch.Tensor], path: str, metadata: Optional[Di
         if t.device.type != "cpu":
             t = t.cpu()
         t = t.contiguous()
+        if t.dim() and t.stride(-1) != 1:          # size-1 dims keep odd strides through contiguous()
+            t = torch.empty(t.shape, dtype=t.dtype).copy_(t)
         if t.dtype not in _NAMES:
             raise TypeError(f"cannot store dtype {t.dtype}")
         n = t.numel() * t.element_size()

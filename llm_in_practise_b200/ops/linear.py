@@ -93,13 +93,13 @@ class _FrozenLinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, layer):
         ctx.layer = layer
-        return gemm(x, layer._materialize_weight(), bias=layer.bias)
+        return gemm(x, layer._materialize_weight(x.dtype), bias=layer.bias)
 
     @staticmethod
     def backward(ctx, dy):
         if not ctx.needs_input_grad[0]:
             return None, None
-        return gemm(dy.contiguous(), ctx.layer._materialize_weight(), b_mn=True), None
+        return gemm(dy.contiguous(), ctx.layer._materialize_weight(dy.dtype), b_mn=True), None
 
 
 class _LoraLinearFn(torch.autograd.Function):
@@ -110,7 +110,7 @@ class _LoraLinearFn(torch.autograd.Function):
     def forward(ctx, x, layer, seed, *adapter_params):
         layer._refresh_adapter_buffers()
         p = layer.lora_dropout if layer.training else 0.0
-        W = layer._materialize_weight()
+        W = layer._materialize_weight(x.dtype)
         T = lora_down(x, layer._A_stack, 1.0, seed, p)                       # [M, r_total]
         y = gemm(x, W, lora=(T, layer._B_block), bias=layer.bias)
         ctx.save_for_backward(x, T)
@@ -130,7 +130,7 @@ class _LoraLinearFn(torch.autograd.Function):
             lora_wgrad(T[:, c0:c1], dy[:, lo:hi], gBt, scale, 0, 0.0)        # d(B_i^T) [r, N_i]
         dx = None
         if ctx.needs_input_grad[0]:
-            W = layer._materialize_weight()
+            W = layer._materialize_weight(dy.dtype)
             if p > 0.0:
                 dx = gemm(dy, W, b_mn=True)
                 lora_dx(dT, layer._A_stack, dx, 1.0, seed, p)
@@ -189,10 +189,11 @@ class FusedLinear(nn.Module):
         self.nf4 = q
         self.weight = None
 
-    def _materialize_weight(self) -> torch.Tensor:
+    def _materialize_weight(self, dtype=None) -> torch.Tensor:
         if self.nf4 is not None:
-            ws = weight_workspace(self.nf4.packed.device, torch.bfloat16, self.out_features * self.in_features)
-            return self.nf4.dequantize(torch.bfloat16, out=ws.view(self.out_features, self.in_features))
+            dtype = dtype or torch.bfloat16
+            ws = weight_workspace(self.nf4.packed.device, dtype, self.out_features * self.in_features)
+            return self.nf4.dequantize(dtype, out=ws.view(self.out_features, self.in_features))
         return self.weight
 
     def dense_weight(self) -> torch.Tensor:
@@ -293,6 +294,15 @@ class FusedLinear(nn.Module):
         if self.has_lora:
             seed = ew.layer_seed(self.layer_uid) if (self.training and self.lora_dropout > 0) else 0
             y = _LoraLinearFn.apply(x2, self, seed, *self._adapter_params())
+        elif (self.nf4 is not None and x2.shape[0] <= 8 and not torch.is_grad_enabled() and x2.is_cuda
+              and hasattr(self.nf4, "group") and not hasattr(self.nf4, "shards")
+              and x2.dtype in (torch.bfloat16, torch.float16)):
+            # decode: fused 4-bit GEMV straight from the packed weights (memory-bound, 4.25 bits/weight read)
+            from .w4 import w4_gemv
+            q = self.nf4
+            sc = q.scales() if hasattr(q, "scales") else q.scale
+            lut = q._lut() if hasattr(q, "_lut") else None
+            y = w4_gemv(x2, q.packed, sc, getattr(q, "zs", None), q.N, q.K, q.group, lut, self.bias)
         elif self.nf4 is not None or not (self.weight.requires_grad or
                                           (self.bias is not None and self.bias.requires_grad)):
             y = _FrozenLinearFn.apply(x2, self)

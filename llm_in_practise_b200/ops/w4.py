@@ -118,7 +118,8 @@ def w4_dequant(packed, scale, zs, N: int, K: int, group: int, lut: Optional[torc
                shards: Optional[Sequence[Sequence[int]]] = None, rows_per_shard: int = 0) -> torch.Tensor:
     """Expand 4-bit weights to ``dtype`` [N, K]. With ``shards`` = [(packed_ptr, scale_ptr, zs_ptr), ...]
     the rows are read from several (possibly peer-GPU) buffers of ``rows_per_shard`` rows each."""
-    if not (packed.is_cuda and nv.use_native(packed)):
+    want = out.dtype if out is not None else dtype
+    if not (packed.is_cuda and nv.use_native(packed)) or want == torch.float32:   # fp32 only in calibration searches
         res = _w4_dequant_ref(packed, scale, zs, N, K, group, lut, dtype)
         if out is not None:
             out.copy_(res)
