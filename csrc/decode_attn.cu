@@ -14,19 +14,22 @@
 namespace b200 {
 
 // qkv: [B, (H + 2 Hkv) * D] (post-RoPE) for the new token; cache_k / cache_v: [B, Hkv, max_len, D];
-// pos[b] = index the new token is written at (= number of tokens already cached); out: [B, H * D]
+// pos[b] = index the new token is written at (= number of tokens already cached); slots[b] (optional) = cache row
+// of batch row b; out: [B, H * D]
 template <typename T, int D>
 __global__ void __launch_bounds__(128)
 decode_attn_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __restrict__ cache_v,
-                   const int* __restrict__ pos, T* __restrict__ out, int H, int Hkv, int max_len, float scale, int window) {
+                   const int* __restrict__ pos, const int* __restrict__ slots, T* __restrict__ out, int H, int Hkv, int max_len,
+                   float scale, int window) {
   constexpr int PER = D / 32;  // elements per lane
   const int b = blockIdx.x / H, h = blockIdx.x % H;
   const int kvh = h / (H / Hkv);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t_new = pos[b];
   const long long row = (long long)b * (H + 2 * Hkv) * D;
-  T* kc = cache_k + ((long long)b * Hkv + kvh) * max_len * D;
-  T* vc = cache_v + ((long long)b * Hkv + kvh) * max_len * D;
+  const long long slot = slots ? slots[b] : b;  // continuous batching: batch row -> cache slot
+  T* kc = cache_k + (slot * Hkv + kvh) * max_len * D;
+  T* vc = cache_v + (slot * Hkv + kvh) * max_len * D;
   // append the new K / V row once per kv head (the first query head of the group does it)
   if (h % (H / Hkv) == 0 && warp == 0) {
     for (int i = lane; i < D; i += 32) {
@@ -95,12 +98,12 @@ decode_attn_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __rest
 }  // namespace b200
 using namespace b200;
 
-B200_API int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, void* out, int B, int H,
+B200_API int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B, int H,
                               int Hkv, int D, int max_len, float scale, int window, int dtype, void* stream) {
   if (B <= 0 || H % Hkv) return B200_ERR_BAD_SHAPE;
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned grid = (unsigned)(B * H);
-#define B200_DA(T, DD) decode_attn_kernel<T, DD><<<grid, 128, 0, st>>>((const T*)qkv, (T*)cache_k, (T*)cache_v, pos, (T*)out, H, Hkv, max_len, scale, window)
+#define B200_DA(T, DD) decode_attn_kernel<T, DD><<<grid, 128, 0, st>>>((const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, (T*)out, H, Hkv, max_len, scale, window)
   if (dtype == B200_DT_BF16) {
     if (D == 128) B200_DA(__nv_bfloat16, 128); else if (D == 64) B200_DA(__nv_bfloat16, 64);
     else if (D == 32) B200_DA(__nv_bfloat16, 32); else if (D == 96) B200_DA(__nv_bfloat16, 96); else return B200_ERR_UNSUPPORTED;

@@ -228,10 +228,10 @@ int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int 
 
 /* ---- decode attention (csrc/decode_attn.cu) ----------------------------------------------------
  * One new token per sequence: appends the rotated K/V of `qkv` [B, (H + 2 Hkv) * D] at position pos[b] of the
- * caches [B, Hkv, max_len, D] and writes softmax(q K^T * scale) V over positions 0..pos[b] (optionally the last
+ * caches [n_slots, Hkv, max_len, D] (row slots[b], or b when slots is NULL) and writes softmax(q K^T * scale) V over positions 0..pos[b] (optionally the last
  * `window` ones) to out [B, H * D]. The KV-cache step behind HF generate(use_cache=True)
  * (Fine-Tuning/inferences.py:50-58, Scripts/inference/01-deepseek1.5b-hf-infr.py:8-30). */
-int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, void* out, int B, int H,
+int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B, int H,
                      int Hkv, int D, int max_len, float scale, int window, int dtype, void* stream);
 
 /* ---- gradient fold (csrc/elementwise.cu) -------------------------------------------------------

@@ -73,23 +73,26 @@ class KVCache:
         self.len = 0
 
 
-def _decode_attn(qkv, ck, cv, pos, H, Hkv, D, scale):
+def _decode_attn(qkv, ck, cv, pos, H, Hkv, D, scale, slots=None):
     B = qkv.shape[0]
     if nv.use_native(qkv):
         out = torch.empty(B, H * D, dtype=qkv.dtype, device=qkv.device)
-        fn = nv.proto("b200_decode_attn", [vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
-        nv.check(fn(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(out), B, H, Hkv, D, ck.shape[2], scale, 0,
+        fn = nv.proto("b200_decode_attn", [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
+        nv.check(fn(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), B, H, Hkv, D, ck.shape[2], scale, 0,
                     nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn")
         nv.count_launch()
         return out
-    t = int(pos[0])
     x = qkv.view(B, H + 2 * Hkv, D)
-    ck[:, :, t] = x[:, H:H + Hkv]
-    cv[:, :, t] = x[:, H + Hkv:]
     g = H // Hkv
-    k = ck[:, :, :t + 1].float().repeat_interleave(g, 1)
-    v = cv[:, :, :t + 1].float().repeat_interleave(g, 1)
+    rows = (slots if slots is not None else torch.arange(B, device=qkv.device)).long()
+    p = pos.long()
+    ck[rows, :, p] = x[:, H:H + Hkv]
+    cv[rows, :, p] = x[:, H + Hkv:]
+    tmax = int(p.max()) + 1
+    k = ck[rows, :, :tmax].float().repeat_interleave(g, 1)
+    v = cv[rows, :, :tmax].float().repeat_interleave(g, 1)
     s = torch.einsum("bhd,bhtd->bht", x[:, :H].float(), k) * scale
+    s = s.masked_fill(torch.arange(tmax, device=qkv.device)[None, None, :] > p[:, None, None], float("-inf"))
     return torch.einsum("bht,bhtd->bhd", s.softmax(-1), v).reshape(B, H * D).to(qkv.dtype)
 
 
@@ -103,10 +106,12 @@ class Generator:
         self.cfg = self.model.config
 
     @torch.no_grad()
-    def _prefill(self, ids: torch.Tensor, cache: KVCache) -> torch.Tensor:
+    def _prefill(self, ids: torch.Tensor, cache: KVCache, slots: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """Run the prompt(s) [B, S], store K/V in cache rows ``slots`` (default 0..B-1), return last-token logits."""
         m, c = self.model, self.cfg
         B, S = ids.shape
         dev = ids.device
+        rows = slots.long() if slots is not None else slice(None)
         H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
         cos, sin = m.rope(dev, self.max_len)
         pos = torch.arange(S, device=dev, dtype=torch.int32).repeat(B)
@@ -116,8 +121,8 @@ class Generator:
             x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
             qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
             t = qkv.view(B, S, H + 2 * Hkv, D)
-            cache.k[li][:, :, :S] = t[:, :, H:H + Hkv].permute(0, 2, 1, 3)
-            cache.v[li][:, :, :S] = t[:, :, H + Hkv:].permute(0, 2, 1, 3)
+            cache.k[li][rows, :, :S] = t[:, :, H:H + Hkv].permute(0, 2, 1, 3)
+            cache.v[li][rows, :, :S] = t[:, :, H + Hkv:].permute(0, 2, 1, 3)
             if Sp != S:
                 qkv = torch.nn.functional.pad(qkv.view(B, S, -1), (0, 0, 0, Sp - S)).reshape(B * Sp, -1)
             ctx = attention(qkv, B, Sp, H, Hkv, D, causal=True)
@@ -131,18 +136,22 @@ class Generator:
         return gemm(last.contiguous(), m.head_weight(), out_dtype=torch.float32)
 
     @torch.no_grad()
-    def _decode(self, tok: torch.Tensor, cache: KVCache) -> torch.Tensor:
+    def _decode(self, tok: torch.Tensor, cache: KVCache, pos: Optional[torch.Tensor] = None,
+                slots: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """One token per sequence. ``pos`` [B] int32 = tokens already cached per sequence (default: cache.len for
+        all); ``slots`` [B] int32 = cache row of each batch row (continuous batching)."""
         m, c = self.model, self.cfg
         B = tok.shape[0]
         dev = tok.device
         H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
         cos, sin = m.rope(dev, self.max_len)
-        pos = torch.full((B,), cache.len, device=dev, dtype=torch.int32)
+        if pos is None:
+            pos = torch.full((B,), cache.len, device=dev, dtype=torch.int32)
         delta, res = ew.embedding(tok.reshape(-1), m.embed_tokens), None
         for li, layer in enumerate(m.layers):
             x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
             qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
-            ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5)
+            ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5, slots)
             x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
             delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
         h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)

@@ -1,0 +1,267 @@
+"""Continuous-batching inference engine — the in-process replacement for the vLLM server every serving recipe of the
+reference points at (``vllm serve … --max-model-len … --max-num-seqs … --gpu-memory-utilization …``;
+Deployment/Ray/serve_run_examples/deepseek.py:5-41, Deployment/Basics-02/docker-compose.yml:56-65,
+Quantization/README.md:172-176).
+
+One scheduler thread owns the GPU. The KV cache is a fixed pool of ``max_num_seqs`` rows per layer
+([slots, Hkv, max_model_len, D], sized once — 180 GB of HBM3e hold e.g. 64 x 32k-token rows of Qwen3-14B in bf16
+next to the NF4 weights); each iteration admits waiting requests into free rows (one prefill each: tcgen05 GEMMs +
+causal attention, K/V stored straight into the row) and then advances *all* running sequences by one token in a
+single batched decode step (``b200_decode_attn`` takes per-row positions and slot indices, so sequences of different
+lengths share the launch). Finished rows are recycled immediately, so the batch never drains.
+
+Counters follow the vLLM metric names the reference's autoscaling rules read
+(``vllm:num_requests_waiting``, ``vllm:time_to_first_token_seconds``;
+LLM_on_Kubernetes/Inference_Platfrom/05-KEDA-AutoScale/keda-scaledobject.yaml:12-53).
+"""
+from __future__ import annotations
+
+import itertools
+import queue
+import threading
+import time
+from collections import deque
+from dataclasses import dataclass, field
+from typing import Deque, Dict, Iterator, List, Optional, Sequence
+
+import torch
+
+from ..inference.generate import GenerationConfig, Generator, KVCache, sample_next
+
+
+@dataclass
+class EngineArgs:
+    max_num_seqs: int = 16
+    max_model_len: int = 4096
+    max_prefill_per_step: int = 4        # bound on admissions per iteration so decode latency stays flat
+    seed: Optional[int] = None
+
+
+@dataclass
+class Request:
+    rid: int
+    prompt_ids: List[int]
+    cfg: GenerationConfig
+    arrival: float = field(default_factory=time.perf_counter)
+    first_token_time: Optional[float] = None
+    finish_time: Optional[float] = None
+    output_ids: List[int] = field(default_factory=list)
+    finish_reason: Optional[str] = None
+    slot: int = -1
+    done: threading.Event = field(default_factory=threading.Event)
+    stream: "queue.Queue" = field(default_factory=queue.Queue)
+    error: Optional[str] = None
+
+    @property
+    def ttft(self) -> Optional[float]:
+        return None if self.first_token_time is None else self.first_token_time - self.arrival
+
+    def tokens(self) -> Iterator[int]:
+        """Blocking iterator over generated ids (used by the SSE endpoint)."""
+        while True:
+            t = self.stream.get()
+            if t is None:
+                return
+            yield t
+
+
+class EngineMetrics:
+    TTFT_BUCKETS = (0.001, 0.005, 0.01, 0.02, 0.04, 0.06, 0.08, 0.1, 0.25, 0.5, 0.75, 1.0, 2.5, 5.0, 7.5, 10.0)
+
+    def __init__(self):
+        self.lock = threading.Lock()
+        self.prompt_tokens = 0
+        self.generation_tokens = 0
+        self.requests_finished: Dict[str, int] = {}
+        self.ttft_counts = [0] * (len(self.TTFT_BUCKETS) + 1)
+        self.ttft_sum = 0.0
+        self.e2e_sum = 0.0
+        self.steps = 0
+
+    def observe_ttft(self, v: float) -> None:
+        with self.lock:
+            self.ttft_sum += v
+            for i, b in enumerate(self.TTFT_BUCKETS):
+                if v <= b:
+                    self.ttft_counts[i] += 1
+                    return
+            self.ttft_counts[-1] += 1
+
+
+class LLMEngine:
+    def __init__(self, model, tokenizer=None, args: Optional[EngineArgs] = None, model_name: str = "b200-model"):
+        self.args = args or EngineArgs()
+        self.gen = Generator(model, tokenizer, self.args.max_model_len)
+        self.model, self.tokenizer, self.model_name = self.gen.model, tokenizer, model_name
+        c = self.model.config
+        self.device = self.model.embed_tokens.device
+        self.cache = KVCache(c.num_hidden_layers, self.args.max_num_seqs, c.num_key_value_heads, self.args.max_model_len,
+                             c.head_dim, self.model.embed_tokens.dtype, self.device)
+        self.free: List[int] = list(range(self.args.max_num_seqs))[::-1]
+        self.waiting: Deque[Request] = deque()
+        self.running: List[Request] = []
+        self.metrics = EngineMetrics()
+        self._ids = itertools.count()
+        self._cv = threading.Condition()
+        self._stop = False
+        self._thread: Optional[threading.Thread] = None
+        self._rng = None
+        if self.args.seed is not None:
+            self._rng = torch.Generator(device=self.device).manual_seed(self.args.seed)
+        self.model.eval()
+
+    # ------------------------------------------------------------------ client side
+    def submit(self, prompt_ids: Sequence[int], cfg: Optional[GenerationConfig] = None) -> Request:
+        cfg = cfg or GenerationConfig()
+        ids = list(prompt_ids)
+        if len(ids) == 0:
+            raise ValueError("empty prompt")
+        if len(ids) >= self.args.max_model_len:
+            raise ValueError(f"prompt of {len(ids)} tokens does not fit max_model_len={self.args.max_model_len}")
+        r = Request(next(self._ids), ids, cfg)
+        with self._cv:
+            self.waiting.append(r)
+            self._cv.notify()
+        return r
+
+    def generate(self, prompts: Sequence[Sequence[int]], cfg: Optional[GenerationConfig] = None) -> List[Request]:
+        """Synchronous helper: submit everything, drive the scheduler in this thread (or wait for the background
+        thread) until all requests finished."""
+        reqs = [self.submit(p, cfg) for p in prompts]
+        if self._thread is None:
+            while not all(r.done.is_set() for r in reqs):
+                self.step()
+        else:
+            for r in reqs:
+                r.done.wait()
+        return reqs
+
+    def start(self) -> "LLMEngine":
+        if self._thread is None:
+            self._stop = False
+            self._thread = threading.Thread(target=self._loop, name="b200-engine", daemon=True)
+            self._thread.start()
+        return self
+
+    def shutdown(self) -> None:
+        with self._cv:
+            self._stop = True
+            self._cv.notify_all()
+        if self._thread is not None:
+            self._thread.join(timeout=30)
+            self._thread = None
+
+    @property
+    def num_waiting(self) -> int:
+        return len(self.waiting)
+
+    @property
+    def num_running(self) -> int:
+        return len(self.running)
+
+    def kv_cache_usage(self) -> float:
+        used = sum(len(r.prompt_ids) + len(r.output_ids) for r in self.running)
+        return used / float(self.args.max_num_seqs * self.args.max_model_len)
+
+    # ------------------------------------------------------------------ scheduler
+    def _loop(self) -> None:
+        if self.device.type == "cuda":
+            torch.cuda.set_device(self.device)
+        while True:
+            with self._cv:
+                while not self._stop and not self.waiting and not self.running:
+                    self._cv.wait(timeout=0.5)
+                if self._stop:
+                    break
+            try:
+                self.step()
+            except Exception as e:  # fail the in-flight requests, keep serving
+                for r in self.running + list(self.waiting):
+                    r.error = f"{type(e).__name__}: {e}"
+                    self._finish(r, "error")
+                self.running.clear()
+                self.waiting.clear()
+                self.free = list(range(self.args.max_num_seqs))[::-1]
+
+    def _eos(self, cfg: GenerationConfig) -> List[int]:
+        e = cfg.eos_token_id
+        if e is None:
+            t = getattr(self.tokenizer, "eos_token_id", None)
+            return [] if t is None else [t]
+        return [e] if isinstance(e, int) else list(e)
+
+    def _finish(self, r: Request, reason: str) -> None:
+        r.finish_reason = reason
+        r.finish_time = time.perf_counter()
+        if r.slot >= 0:
+            self.free.append(r.slot)
+            r.slot = -1
+        with self.metrics.lock:
+            self.metrics.requests_finished[reason] = self.metrics.requests_finished.get(reason, 0) + 1
+            self.metrics.e2e_sum += r.finish_time - r.arrival
+        r.stream.put(None)
+        r.done.set()
+
+    def _emit(self, r: Request, tok: int) -> bool:
+        """Record one sampled token; returns True when the request is finished."""
+        now = time.perf_counter()
+        if r.first_token_time is None:
+            r.first_token_time = now
+            self.metrics.observe_ttft(now - r.arrival)
+        if tok in self._eos(r.cfg):
+            self._finish(r, "stop")
+            return True
+        r.output_ids.append(tok)
+        r.stream.put(tok)
+        with self.metrics.lock:
+            self.metrics.generation_tokens += 1
+        if len(r.output_ids) >= r.cfg.max_new_tokens or len(r.prompt_ids) + len(r.output_ids) >= self.args.max_model_len:
+            self._finish(r, "length")
+            return True
+        return False
+
+    def _sample(self, logits: torch.Tensor, reqs: List[Request]) -> List[int]:
+        """Per-request sampling parameters: requests sharing a config are sampled together."""
+        out = [0] * len(reqs)
+        groups: Dict[tuple, List[int]] = {}
+        for i, r in enumerate(reqs):
+            c = r.cfg
+            groups.setdefault((c.do_sample, c.temperature, c.top_p, c.top_k, c.repetition_penalty), []).append(i)
+        for key, idx in groups.items():
+            cfg = reqs[idx[0]].cfg
+            prev = None
+            if cfg.repetition_penalty != 1.0:
+                seqs = [reqs[i].prompt_ids + reqs[i].output_ids for i in idx]
+                L = max(len(s) for s in seqs)
+                prev = torch.tensor([s + [s[-1]] * (L - len(s)) for s in seqs], device=logits.device)
+            ids = sample_next(logits[idx], cfg, prev, self._rng)
+            for i, t in zip(idx, ids.tolist()):
+                out[i] = t
+        return out
+
+    @torch.no_grad()
+    def step(self) -> None:
+        """One scheduler iteration: admit + prefill, then one batched decode step."""
+        admitted = 0
+        while self.waiting and self.free and admitted < self.args.max_prefill_per_step:
+            with self._cv:
+                r = self.waiting.popleft()
+            r.slot = self.free.pop()
+            ids = torch.tensor([r.prompt_ids], device=self.device)
+            logits = self.gen._prefill(ids, self.cache, torch.tensor([r.slot], device=self.device))
+            with self.metrics.lock:
+                self.metrics.prompt_tokens += len(r.prompt_ids)
+            tok = self._sample(logits, [r])[0]
+            if not self._emit(r, tok):
+                self.running.append(r)
+            admitted += 1
+        if not self.running:
+            return
+        reqs = self.running
+        last = torch.tensor([r.output_ids[-1] for r in reqs], device=self.device)
+        pos = torch.tensor([len(r.prompt_ids) + len(r.output_ids) - 1 for r in reqs], device=self.device, dtype=torch.int32)
+        slots = torch.tensor([r.slot for r in reqs], device=self.device, dtype=torch.int32)
+        logits = self.gen._decode(last, self.cache, pos, slots)
+        toks = self._sample(logits, reqs)
+        self.running = [r for r, t in zip(reqs, toks) if not self._emit(r, t)]
+        self.metrics.steps += 1

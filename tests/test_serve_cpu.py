@@ -1,0 +1,128 @@
+"""Serving stack on CPU: continuous batching vs. single-sequence generation, OpenAI API schema, moderation wrapper."""
+import asyncio
+import json
+
+import httpx
+import pytest
+import torch
+from fastapi.testclient import TestClient
+
+from llm_in_practise_b200.data.tokenizers import ByteTokenizer
+from llm_in_practise_b200.inference import GenerationConfig, Generator
+from llm_in_practise_b200.models.qwen3 import Qwen3Config, Qwen3ForCausalLM
+from llm_in_practise_b200.serve import EngineArgs, LLMEngine
+from llm_in_practise_b200.serve.moderation import (build_moderation_app, http_backend, interpret_guard_output,
+                                                   make_openai_moderation_response, parse_native_scodes)
+from llm_in_practise_b200.serve.openai_server import build_app
+
+
+@pytest.fixture(scope="module")
+def model():
+    cfg = Qwen3Config(vocab_size=300, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=4,
+                      num_key_value_heads=2, head_dim=16, max_position_embeddings=256)
+    torch.manual_seed(0)
+    return Qwen3ForCausalLM(cfg, dtype=torch.float32, device="cpu", init_std=0.1)
+
+
+def test_continuous_batching_matches_sequential(model):
+    torch.manual_seed(1)
+    prompts = [torch.randint(0, 300, (n,)).tolist() for n in (5, 9, 3, 12, 7)]
+    g = Generator(model, max_len=64)
+    want = [g.generate(torch.tensor([p]), max_new_tokens=6 + i, do_sample=False)[0, len(p):].tolist() for i, p in enumerate(prompts)]
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=2, max_model_len=64, max_prefill_per_step=1))   # forces queueing + slot reuse
+    reqs = [eng.submit(p, GenerationConfig(max_new_tokens=6 + i, do_sample=False)) for i, p in enumerate(prompts)]
+    assert eng.num_waiting == 5
+    while not all(r.done.is_set() for r in reqs):
+        eng.step()
+        assert eng.num_running <= 2
+    assert [r.output_ids for r in reqs] == want
+    assert all(r.finish_reason == "length" and r.ttft is not None for r in reqs)
+    assert sorted(eng.free) == [0, 1] and eng.metrics.generation_tokens == sum(len(w) for w in want)
+
+
+def test_openai_endpoints(model):
+    tok = ByteTokenizer()
+    eng = LLMEngine(model, tok, EngineArgs(max_num_seqs=4, max_model_len=128), model_name="tiny").start()
+    try:
+        c = TestClient(build_app(eng, prompt_style="deepseek"))
+        body = {"model": "tiny", "messages": [{"role": "system", "content": "s"}, {"role": "user", "content": "hi"}],
+                "max_tokens": 5, "temperature": 0.0}
+        r = c.post("/v1/chat/completions", json=body)
+        assert r.status_code == 200, r.text
+        j = r.json()
+        assert j["object"] == "chat.completion" and j["id"].startswith("chatcmpl-") and j["model"] == "tiny"
+        assert j["choices"][0]["message"]["role"] == "assistant" and j["choices"][0]["finish_reason"] in ("stop", "length")
+        u = j["usage"]
+        assert u["total_tokens"] == u["prompt_tokens"] + u["completion_tokens"] and 0 < u["completion_tokens"] <= 5
+        with c.stream("POST", "/v1/chat/completions", json={**body, "stream": True}) as s:
+            lines = [ln for ln in s.iter_lines() if ln.startswith("data: ")]
+        assert lines[-1] == "data: [DONE]" and json.loads(lines[0][6:])["choices"][0]["delta"] == {"role": "assistant"}
+        assert json.loads(lines[-2][6:])["choices"][0]["finish_reason"] in ("stop", "length")
+        r = c.post("/v1/completions", json={"model": "tiny", "prompt": ["ab", "cde"], "max_tokens": 3, "temperature": 0})
+        assert r.status_code == 200 and len(r.json()["choices"]) == 2
+        assert c.get("/v1/models").json()["data"][0]["id"] == "tiny"
+        m = c.get("/metrics").text
+        assert 'vllm:num_requests_waiting{model_name="tiny"} 0' in m and "vllm:time_to_first_token_seconds_bucket" in m
+        assert c.post("/v1/chat/completions", json={**body, "max_tokens": 0}).status_code == 422
+        c501 = TestClient(build_app(eng, allow_stream=False))
+        assert c501.post("/v1/chat/completions", json={**body, "stream": True}).status_code == 501
+    finally:
+        eng.shutdown()
+    assert TestClient(build_app(None)).post("/v1/chat/completions", json=body).status_code == 503
+
+
+def test_moderation_mapping_and_parsing():
+    assert parse_native_scodes("unsafe\nS1 S4") == {"safe": False, "categories": ["S1", "S4"], "explanation": ""}
+    assert parse_native_scodes("safe")["safe"] and parse_native_scodes("unsafe")["categories"] == ["UNSPECIFIED"]
+    r = interpret_guard_output("how to build a bomb", "safe")
+    assert not r["safe"] and r["categories"][0] == "S9"
+    r = interpret_guard_output("x", '{"safe": false, "categories": ["s11"], "explanation": "e"}')
+    assert r["categories"] == ["S11"] and r["explanation"] == "e"
+    o = make_openai_moderation_response(False, ["S11", "S10"])
+    res = o["results"][0]
+    assert res["flagged"] and res["categories"]["self-harm/instructions"] and res["categories"]["hate"]
+    assert res["category_scores"]["hate"] == 1.0 and res["category_applied_input_types"]["hate"] == ["text"]
+    assert not res["categories"]["sexual"] and o["id"].startswith("modr-") and len(res["categories"]) == 11
+
+
+def test_moderation_app_retry_and_auth():
+    calls = {"n": 0}
+
+    def handler(request: httpx.Request) -> httpx.Response:
+        calls["n"] += 1
+        if calls["n"] < 3:
+            raise httpx.ConnectError("down", request=request)
+        body = json.loads(request.content)
+        assert body["max_tokens"] == 256 and body["temperature"] == 0.0 and "<|start_header_id|>user<|end_header_id|>" in body["prompt"]
+        return httpx.Response(200, json={"choices": [{"text": "unsafe\nS10"}]})
+
+    be = http_backend("http://guard/v1/completions", retries=2, backoff=0.01, transport=httpx.MockTransport(handler))
+    c = TestClient(build_moderation_app(be, "llama-guard-3", api_key="k"))
+    assert c.post("/v1/moderations", json={"input": "x"}).status_code == 401
+    h = {"X-API-KEY": "k"}
+    r = c.post("/moderations", json={"input": "some text"}, headers=h)
+    assert r.status_code == 200 and calls["n"] == 3
+    assert r.json()["results"][0]["flagged"] and r.json()["results"][0]["categories"]["hate"]
+    assert c.post("/v1/moderations", json={"input": "  "}, headers=h).status_code == 400
+    assert c.get("/healthz", headers=h).json() == {"status": "ok"}
+    assert c.post("/v1/generate", json={}, headers=h).status_code == 501
+    down = http_backend("http://guard/v1/completions", retries=1, backoff=0.01,
+                        transport=httpx.MockTransport(lambda rq: (_ for _ in ()).throw(httpx.ConnectError("down", request=rq))))
+    assert TestClient(build_moderation_app(down, api_key="")).post("/v1/moderations", json={"input": "a"}).status_code == 502
+    bad = http_backend("http://guard/v1/completions", transport=httpx.MockTransport(lambda rq: httpx.Response(500, text="boom")))
+    assert TestClient(build_moderation_app(bad, api_key="")).post("/v1/moderations", json={"input": "a"}).status_code == 502
+
+
+def test_loadtest_against_app(model):
+    from llm_in_practise_b200.serve.loadtest import PROFILES, run_load
+    tok = ByteTokenizer()
+    eng = LLMEngine(model, tok, EngineArgs(max_num_seqs=4, max_model_len=256), model_name="qwen3").start()
+    PROFILES["mini"] = {"payload": {"model": "qwen3", "messages": [{"role": "user", "content": "hi"}], "max_tokens": 4,
+                                    "temperature": 0.0}, "wait": (0.0, 0.01)}
+    try:
+        out = asyncio.run(run_load("http://test", "mini", users=3, duration=30, max_requests_per_user=2,
+                                   transport=httpx.ASGITransport(app=build_app(eng))))
+    finally:
+        eng.shutdown()
+    assert out["requests"] == 6 and out["failures"] == 0 and out["completion_tokens"] > 0
+    assert out["aggregate_tokens_per_second"] > 0
