@@ -153,6 +153,56 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// Long waits (an epilogue warp waiting ~20 us for its accumulator): back off with nanosleep so the spinning warp
+// does not eat half of its scheduler's issue slots (measured: ~2900 polls, ~23k instructions per tile and warp).
+__device__ __forceinline__ void mbar_wait_sleep(uint32_t bar, uint32_t parity, uint32_t ns) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(ns);
+    if (clock64() - t0 > B200_MBAR_TIMEOUT_CYCLES) {
+      printf("b200: mbarrier wait timed out (block %d,%d thread %d bar 0x%x parity %u)\n",
+             blockIdx.x, blockIdx.y, threadIdx.x, bar, parity);
+      __trap();
+    }
+  }
+}
+
+// Spin on the non-blocking test_wait (try_wait may park the thread for a system-dependent time).
+__device__ __forceinline__ void mbar_wait_spin(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  const long long t0 = clock64();
+  do {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (!ok && clock64() - t0 > B200_MBAR_TIMEOUT_CYCLES) {
+      printf("b200: mbarrier wait timed out (block %d thread %d bar 0x%x parity %u)\n", blockIdx.x, threadIdx.x, bar, parity);
+      __trap();
+    }
+  } while (!ok);
+}
+
+// Whole-warp wait with one polling lane: 32 lanes spinning on try_wait steal issue slots and shared-memory
+// bandwidth from the warps that share their scheduler (the UMMA-issuing thread among them).
+__device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
+  if ((threadIdx.x & 31) == 0) {
+    if (!mbar_try_wait(bar, parity)) {
+      const long long t0 = clock64();
+      while (!mbar_try_wait(bar, parity)) {
+        if (clock64() - t0 > B200_MBAR_TIMEOUT_CYCLES) {
+          printf("b200: mbarrier wait timed out (block %d,%d thread %d bar 0x%x parity %u)\n",
+                 blockIdx.x, blockIdx.y, threadIdx.x, bar, parity);
+          __trap();
+        }
+      }
+    }
+  }
+  __syncwarp();
+}
+
 // --------------------------------------------------------------------------------------------
 // proxy fences
 // --------------------------------------------------------------------------------------------

@@ -28,6 +28,7 @@
 
 #include <stdio.h>
 #include <stdlib.h>
+#include <string.h>
 
 namespace b200 {
 
@@ -56,6 +57,33 @@ struct GemmKernelParams {
   unsigned int* sk_flags;
   unsigned int sk_epoch;
 };
+
+// Fused 4-bit B operand (W4 = true instantiation): the weight matrix W [rows, kw] is stored packed (two codes per
+// byte, kw contiguous, even element in the high nibble) with one fp32 scale (and optional zero*scale) per `group`
+// elements, possibly split by rows over up to 8 buffers (ZeRO-3 shards in peer memory, read through NVLink by TMA).
+// w = lut[code] * scale - zs. b_mn = 0: B = W (forward, GEMM N = rows, K = kw); b_mn = 1: B = W^T read in place
+// (dgrad, GEMM N = kw, K = rows).
+struct W4Params {
+  CUtensorMap tmW[8];
+  const float* scale[8];
+  const float* zs[8];
+  const float* lut;  // 16 entries, nullptr = NF4
+  int nshards, rows_per_shard, group, kw;
+  int raw_stages, is_bf16;
+  int lut_bytes;
+  int debug;  // B200_W4_DEBUG bit mask (timing experiments only): 1 no table look-ups, 2 no proxy fence, 4 release.cluster arrive
+};
+
+constexpr int kW4Threads = 480;      // + 8 dequant warps + 1 packed-tile TMA warp
+constexpr int kW4DqWarps = 8;
+constexpr int kRawStageBytes = 4096; // 128 rows x 32 B (K-major) or 64 rows x 64 B (MN-major) of packed codes
+constexpr int kLutBytes = 256 * 32 * 4;
+
+__constant__ float kNF4Table[16] = {-1.0f, -0.6961928009986877f, -0.5250730514526367f, -0.39491748809814453f,
+                                    -0.28444138169288635f, -0.18477343022823334f, -0.09105003625154495f, 0.0f,
+                                    0.07958029955625534f, 0.16093020141124725f, 0.24611230194568634f,
+                                    0.33791524171829224f, 0.44070982933044434f, 0.5626170039176941f,
+                                    0.7229568362236023f, 1.0f};
 
 // One accumulator's worth of work: k-blocks [kb0, kb1) of `tile`.
 struct Segment {
@@ -161,11 +189,9 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
   }
 }
 
-template <int ES, int CTAS>
-__global__ void __launch_bounds__(kGemmThreads, 1)
-gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                    const GemmKernelParams p) {
+template <int ES, int CTAS, bool W4>
+__device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensorMap& tmA2,
+                                          const CUtensorMap& tmB2, const GemmKernelParams& p, const W4Params* w4) {
   constexpr int EPR = 128 / ES;  // elements per 128-byte swizzle row = k-block depth
   constexpr int UK = 32 / ES;    // elements per UMMA k-step
 
@@ -175,13 +201,18 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const uint32_t stage_b_bytes = (uint32_t)bn_cta * 128u;
   const uint32_t sA0 = smem_base;
   const uint32_t sB0 = smem_base + (uint32_t)p.stages * kStageABytes;
-  const uint32_t bar0 = sB0 + (uint32_t)p.stages * stage_b_bytes;
-  // barrier block: full[stages] | empty[stages] | tmem_full[2] | tmem_empty[2] | tmem_ptr
+  const int raw_stages = W4 ? w4->raw_stages : 0;
+  const uint32_t raw0 = sB0 + (uint32_t)p.stages * stage_b_bytes;          // packed-code ring (W4 only)
+  const uint32_t lut0 = raw0 + (uint32_t)raw_stages * kRawStageBytes;      // byte -> 2 x 16-bit table, one copy per lane
+  const uint32_t bar0 = lut0 + (W4 ? (uint32_t)w4->lut_bytes : 0u);
+  // barrier block: full[stages] | empty[stages] | tmem_full[2] | tmem_empty[2] | tmem_ptr | raw_full[] | raw_empty[]
   auto full_bar = [&](int s) { return bar0 + 8u * s; };
   auto empty_bar = [&](int s) { return bar0 + 8u * (p.stages + s); };
   auto tfull_bar = [&](int a) { return bar0 + 8u * (2 * p.stages + a); };
   auto tempty_bar = [&](int a) { return bar0 + 8u * (2 * p.stages + 2 + a); };
   const uint32_t tmem_slot = bar0 + 8u * (2 * p.stages + 4);
+  auto rfull_bar = [&](int s) { return bar0 + 8u * (2 * p.stages + 5 + s); };
+  auto rempty_bar = [&](int s) { return bar0 + 8u * (2 * p.stages + 5 + raw_stages + s); };
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -197,8 +228,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       tma_prefetch_desc(&tmB2);
     }
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(full_bar(s), CTAS);   // one arrival per CTA's producer (+ the TMA transaction bytes)
+      // one arrival per CTA's producer (+ the TMA transaction bytes) (+ W4: the dequant warps of every CTA)
+      mbar_init(full_bar(s), (W4 && !(w4->debug & 128)) ? CTAS * 2 : CTAS);   // W4: + one arrival per CTA from its dequant warps
       mbar_init(empty_bar(s), 1);     // tcgen05.commit (multicast to both CTAs of a pair)
+    }
+    for (int s = 0; s < raw_stages; ++s) {
+      mbar_init(rfull_bar(s), 1);
+      mbar_init(rempty_bar(s), (w4->debug & 256) ? 1 : kW4DqWarps);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
@@ -209,6 +245,19 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 1) {
     if constexpr (CTAS == 1) { tmem_alloc(tmem_slot, 512); tmem_relinquish(); }
     else { tmem_alloc_2sm(tmem_slot, 512); tmem_relinquish_2sm(); }
+  }
+  if (W4 && w4->lut_bytes) {
+    // entry (byte, lane) = {16-bit lut[byte >> 4] (even element, low half), 16-bit lut[byte & 15]}: lane l only ever
+    // reads column l, so the 32 lanes of a warp hit 32 different banks whatever their bytes are
+    for (int i = threadIdx.x; i < 256 * 32; i += blockDim.x) {
+      const int byte = i >> 5;
+      const float lo = w4->lut ? w4->lut[byte >> 4] : kNF4Table[byte >> 4];
+      const float hi = w4->lut ? w4->lut[byte & 15] : kNF4Table[byte & 15];
+      uint32_t v;
+      if (w4->is_bf16) v = pack_bf16x2(lo, hi);
+      else { const __half2 h = __floats2half2_rn(lo, hi); v = *reinterpret_cast<const uint32_t*>(&h); }
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(lut0 + 4u * i), "r"(v) : "memory");
+    }
   }
   tc_fence_before();
   __syncthreads();
@@ -226,7 +275,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t tx_bytes = (uint32_t)CTAS * (kStageABytes + stage_b_bytes);
+      const uint32_t tx_full = (uint32_t)CTAS * (kStageABytes + stage_b_bytes);
+      const uint32_t tx_a_only = (uint32_t)CTAS * kStageABytes;
       const uint32_t box_bytes = EPR * 128;  // MN-major operands: one box = EPR k-rows x 128 B
       SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
       Segment sg;
@@ -245,7 +295,8 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t fb_local = full_bar(stage);
           const uint32_t fb = leader ? fb_local : mapa_shared(fb_local, 0);  // the leader's barrier
-          if (leader) mbar_arrive_expect_tx(fb_local, tx_bytes);
+          const bool dbg_b = W4 && (w4->debug & 64);   // timing experiment: also stream a (dummy) B tile through TMA
+          if (leader) mbar_arrive_expect_tx(fb_local, (W4 && kb < p.num_k && !dbg_b) ? tx_a_only : tx_full);
           else mbar_arrive_cluster(fb);
           const uint32_t sa = sA0 + (uint32_t)stage * kStageABytes;
           const uint32_t sb = sB0 + (uint32_t)stage * stage_b_bytes;
@@ -260,10 +311,13 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             } else {
               for (int j = 0; j < kBM / EPR; ++j) load(sa + j * box_bytes, &tmA, m0 + j * EPR, k0, ab0, ab1);
             }
-            if (!p.b_mn) {
-              load(sb, &tmB, k0, n0, bb0, bb1);
-            } else {
-              for (int j = 0; j < bn_cta / EPR; ++j) load(sb + j * box_bytes, &tmB, n0 + j * EPR, k0, bb0, bb1);
+            if constexpr (W4) { if (dbg_b) load(sb, &tmB, k0, (n0 % 512), bb0, bb1); }
+            if constexpr (!W4) {
+              if (!p.b_mn) {
+                load(sb, &tmB, k0, n0, bb0, bb1);
+              } else {
+                for (int j = 0; j < bn_cta / EPR; ++j) load(sb + j * box_bytes, &tmB, n0 + j * EPR, k0, bb0, bb1);
+              }
             }
           } else {
             load(sa, &tmA2, 0, m0, 0, 0);
@@ -334,7 +388,155 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (acc == 0) acc_phase ^= 1u;
       }
     }
-  } else {
+  } else if (W4 && warp >= 6 && ((w4->debug & 128) || ((w4->debug & 256) && warp > 6 && warp < 6 + kW4DqWarps))) {
+    // timing experiment: the extra warps stay out of the way
+  } else if (W4 && warp == 6 + kW4DqWarps) {
+    // ================= packed-weight TMA producer: runs `raw_stages` k-blocks ahead of the dequant warps ========
+    if constexpr (W4) if (lane == 0) {
+      int rs = 0;
+      uint32_t rphase = 0;
+      SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
+      Segment sg;
+      while (it.next(sg)) {
+        const int rem = sg.tile % tiles_per_batch;
+        const int n_blk = rem / p.num_m;
+        const int n0 = n_blk * p.bn + (int)rank * bn_cta;
+        for (int kb = sg.kb0; kb < sg.kb1 && kb < p.num_k; ++kb) {
+          mbar_wait(rempty_bar(rs), rphase ^ 1u);
+          if (w4->debug & 32) {   // timing experiment: no packed-tile traffic
+            mbar_arrive(rfull_bar(rs));
+            if (++rs == raw_stages) { rs = 0; rphase ^= 1u; }
+            continue;
+          }
+          mbar_arrive_expect_tx(rfull_bar(rs), kRawStageBytes);
+          const uint32_t dst = raw0 + (uint32_t)rs * kRawStageBytes;
+          if (!p.b_mn) {   // rows n0.. of W, bytes k0/2..
+            const int sh = n0 / w4->rows_per_shard;
+            tma_load_2d(dst, &w4->tmW[sh], rfull_bar(rs), kb * (EPR / 2), n0 - sh * w4->rows_per_shard);
+          } else {         // rows k0.. of W, bytes n0/2..
+            const int k0 = kb * EPR;
+            const int sh = k0 / w4->rows_per_shard;
+            tma_load_2d(dst, &w4->tmW[sh], rfull_bar(rs), n0 / 2, k0 - sh * w4->rows_per_shard);
+          }
+          if (++rs == raw_stages) { rs = 0; rphase ^= 1u; }
+        }
+      }
+    }
+  } else if (W4 && warp >= 6) {
+    // ================= dequant warps: packed codes -> swizzled 16-bit B stage =================
+    if constexpr (W4) {
+      const int t = threadIdx.x - 192;   // 0..255: two threads per 128-byte row of the B stage
+      int stage = 0, rs = 0;
+      uint32_t phase = 0, rphase = 0;
+      const int gpr = w4->kw / w4->group;     // scale groups per stored row of W
+      const uint32_t lut_lane = lut0 + 4u * lane;
+      const bool bf = w4->is_bf16 != 0;
+      SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
+      Segment sg;
+      while (it.next(sg)) {
+        const int rem = sg.tile % tiles_per_batch;
+        const int n_blk = rem / p.num_m;
+        const int n0 = n_blk * p.bn + (int)rank * bn_cta;
+        // K-major: B row n0 + t/2, k half t&1 of the block. MN-major: k row t/4, column half (t>>1)&1, 32-column part t&1.
+        const int r_loc = p.b_mn ? (t >> 2) : (t >> 1);
+        const int half = p.b_mn ? ((t >> 1) & 1) : 0;
+        const int sub = t & 1;                 // which 16 packed bytes (4 of the row's 8 sixteen-byte chunks)
+        const uint32_t raw_off = p.b_mn ? (uint32_t)(r_loc * 64 + half * 32 + sub * 16) : (uint32_t)(r_loc * 32 + sub * 16);
+        const uint32_t dst_off = p.b_mn ? (uint32_t)(half * EPR * 128 + r_loc * 128) : (uint32_t)(r_loc * 128);
+        const uint32_t key = (uint32_t)(r_loc & 7);
+        auto scale_at = [&](int kb, float& sc, float& zs) {
+          long long idx;
+          int sh;
+          if (!p.b_mn) {
+            const int n = n0 + r_loc;
+            sh = n / w4->rows_per_shard;
+            idx = (long long)(n - sh * w4->rows_per_shard) * gpr + (kb * EPR) / w4->group;
+          } else {
+            const int o = kb * EPR + r_loc;
+            sh = o / w4->rows_per_shard;
+            idx = (long long)(o - sh * w4->rows_per_shard) * gpr + (n0 + half * 64) / w4->group;
+          }
+          sc = __ldg(w4->scale[sh] + idx);
+          zs = w4->zs[sh] ? __ldg(w4->zs[sh] + idx) : 0.f;
+        };
+        // scales are fetched 3 k-blocks ahead (L2 latency is longer than one k-block of tensor work)
+        float scq[3] = {0.f, 0.f, 0.f}, zsq[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < 3; ++j)
+          if (sg.kb0 + j < sg.kb1 && sg.kb0 + j < p.num_k) scale_at(sg.kb0 + j, scq[j], zsq[j]);
+        for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
+          const uint32_t fb_local = full_bar(stage);
+          if (kb < p.num_k) {
+            const float sc = scq[0], zs = zsq[0];
+            scq[0] = scq[1]; scq[1] = scq[2]; zsq[0] = zsq[1]; zsq[1] = zsq[2];
+            if (kb + 3 < sg.kb1 && kb + 3 < p.num_k) scale_at(kb + 3, scq[2], zsq[2]);
+            uint32_t sc2, nz2;
+            if (w4->is_bf16) { sc2 = pack_bf16x2(sc, sc); nz2 = pack_bf16x2(-zs, -zs); }
+            else {
+              const __half2 a = __floats2half2_rn(sc, sc), b = __floats2half2_rn(-zs, -zs);
+              sc2 = *reinterpret_cast<const uint32_t*>(&a); nz2 = *reinterpret_cast<const uint32_t*>(&b);
+            }
+            if (w4->debug & 8) {   // timing experiment: no expansion at all, only the barrier traffic
+              mbar_wait(rfull_bar(rs), rphase);
+              __syncwarp();
+              if (lane == 0) mbar_arrive(rempty_bar(rs));
+              if (++rs == raw_stages) { rs = 0; rphase ^= 1u; }
+              mbar_wait(empty_bar(stage), phase ^ 1u);
+              goto signal;
+            }
+            mbar_wait(rfull_bar(rs), rphase);
+            uint32_t w[4];
+            const uint32_t src = raw0 + (uint32_t)rs * kRawStageBytes + raw_off;
+            asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]) : "r"(src) : "memory");
+            // table look-ups first (16 independent loads in flight), arithmetic and stores after
+            uint32_t v[16];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+#pragma unroll
+              for (int b = 0; b < 4; ++b) {
+                const uint32_t off = b == 0 ? (w[c] << 7) & 0x7F80u : (w[c] >> (8 * b - 7)) & 0x7F80u;
+                if (w4->debug & 1) v[c * 4 + b] = off;
+                else asm("ld.shared.u32 %0, [%1];" : "=r"(v[c * 4 + b]) : "r"(lut_lane + off));
+              }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(rempty_bar(rs));
+            if (++rs == raw_stages) { rs = 0; rphase ^= 1u; }
+            mbar_wait(empty_bar(stage), phase ^ 1u);
+            const uint32_t dst = sB0 + (uint32_t)stage * stage_b_bytes + dst_off;
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              uint32_t o[4];
+              if (bf) {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(o[b]) : "r"(v[c * 4 + b]), "r"(sc2), "r"(nz2));
+              } else {
+#pragma unroll
+                for (int b = 0; b < 4; ++b) asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(o[b]) : "r"(v[c * 4 + b]), "r"(sc2), "r"(nz2));
+              }
+              if (!(w4->debug & 16))
+              asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (((uint32_t)(sub * 4 + c) ^ key) << 4)), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+              else asm volatile("" ::"r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]));
+            }
+            if (!(w4->debug & 2)) fence_proxy_async_smem();   // generic-proxy stores to this CTA's smem -> visible to tcgen05.mma
+          } else {
+            mbar_wait(empty_bar(stage), phase ^ 1u);             // LoRA k-block: B2 comes from TMA, nothing to expand
+          }
+        signal:
+          if (!(w4->debug & 256)) asm volatile("bar.sync 2, 256;" ::: "memory");   // all dequant warps of this CTA wrote (and fenced) their part
+          if (t == 0 && !(w4->debug & 4)) {
+            // same signalling as a TMA-less CUTLASS producer: proxy fence by every writer, then a plain arrive
+            if (leader) mbar_arrive(fb_local);
+            else mbar_arrive_cluster(mapa_shared(fb_local, 0));
+          } else if (t == 0) {
+            if (leader) asm volatile("mbarrier.arrive.release.cluster.shared::cta.b64 _, [%0];" ::"r"(fb_local) : "memory");
+            else asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(mapa_shared(fb_local, 0)) : "memory");
+          }
+          if (++stage == p.stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp >= 2 && warp < 6) {
     // ================= epilogue (4 warps per CTA, one TMEM lane quarter each) =================
     const int q = warp & 3;
     int acc = 0;
@@ -350,7 +552,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int m_blk = rem - n_blk * p.num_m;
       const int m0 = m_blk * (kBM * CTAS) + (int)rank * kBM, n0 = n_blk * p.bn;
       const int ab0 = bt % p.nb0, ab1 = bt / p.nb0;
-      mbar_wait(tfull_bar(acc), acc_phase);
+      mbar_wait_sleep(tfull_bar(acc), acc_phase, 128);
       tc_fence_after();
       const int row = m0 + q * 32 + lane;
       const bool row_ok = row < p.M;
@@ -435,6 +637,23 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     if constexpr (CTAS == 1) tmem_dealloc(tmem_base, 512);
     else tmem_dealloc_2sm(tmem_base, 512);
   }
+}
+
+template <int ES, int CTAS>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
+                    const GemmKernelParams p) {
+  gemm_body<ES, CTAS, false>(tmA, tmB, tmA2, tmB2, p, nullptr);
+}
+
+// Same pipeline with the B operand expanded from 4-bit codes inside the kernel (NF4 / GPTQ / AWQ weights, optionally
+// sharded over peer GPUs): no 16-bit copy of the weight ever exists in global memory.
+__global__ void __launch_bounds__(kW4Threads, 1)
+gemm_w4_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
+                       const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ W4Params w4,
+                       const GemmKernelParams p) {
+  gemm_body<2, 2, true>(tmA, tmA, tmA2, tmB2, p, &w4);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -587,6 +806,7 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   const int stage_bytes = kStageABytes + bn_cta * 128;
   int stages = (g_max_smem - 2048) / stage_bytes;
   if (stages > 8) stages = 8;
+  { const char* e = getenv("B200_GEMM_STAGES"); if (e && atoi(e) >= 2 && atoi(e) < stages) stages = atoi(e); }
   if (stages < 2) return B200_ERR_UNSUPPORTED;
   p.stages = stages;
   const int umma_m = kBM * ctas;
@@ -648,6 +868,138 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   else rc = ctas == 2 ? launch<4, 2>(tmA, tmB, tmA2, tmB2, p, grid, smem, stream)
                       : launch<4, 1>(tmA, tmB, tmA2, tmB2, p, grid, smem, stream);
   if (rc) return rc;
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_gemm_w4(const b200_gemm_args* a, const b200_w4_desc* w, void* stream_) {
+  cudaStream_t stream = (cudaStream_t)stream_;
+  constexpr int ES = 2, EPR = 64, ctas = 2, bn = 256, bn_cta = 128;
+  if (a->M <= 0 || a->N <= 0 || a->K <= 0) return B200_ERR_BAD_SHAPE;
+  if (a->in_dtype != B200_DT_BF16 && a->in_dtype != B200_DT_FP16) return B200_ERR_UNSUPPORTED;
+  if (a->batch > 1 || a->a_mn || a->M <= kBM || a->N % bn || a->K % EPR) return B200_ERR_UNSUPPORTED;
+  if (w->nshards < 1 || w->nshards > 8 || w->group % 64 || w->kw % 64 || w->kw % w->group) return B200_ERR_UNSUPPORTED;
+  const long long rps = w->nshards > 1 ? w->rows_per_shard : w->rows;
+  if (rps * w->nshards < w->rows || rps % (a->b_mn ? 64 : 128)) return B200_ERR_UNSUPPORTED;
+  if (!a->b_mn ? (a->N != w->rows || a->K != w->kw) : (a->N != w->kw || a->K != w->rows)) return B200_ERR_BAD_SHAPE;
+  const bool lora = a->K2 > 0 && a->A2 && a->B2;
+  if (lora && a->K2 > EPR) return B200_ERR_UNSUPPORTED;
+  auto al16 = [&](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; };
+  if (!al16(a->A) || (a->a_rs * ES) % 16) return B200_ERR_BAD_ALIGN;
+  if (lora && (!al16(a->A2) || !al16(a->B2) || (a->a2_rs * ES) % 16 || (a->b2_rs * ES) % 16)) return B200_ERR_BAD_ALIGN;
+  for (int i = 0; i < w->nshards; ++i)
+    if (!al16(w->packed[i])) return B200_ERR_BAD_ALIGN;
+  int rc = device_props();
+  if (rc) return rc;
+
+  GemmKernelParams p;
+  p.D = a->D;
+  p.bias = a->bias;
+  p.M = a->M; p.N = a->N; p.K = a->K; p.K2 = lora ? a->K2 : 0;
+  p.batch = 1; p.nb0 = 1; p.b_div = 1; p.nb0_b = 1;
+  p.d_rs = a->d_rs; p.d_bs0 = 0; p.d_bs1 = 0;
+  p.alpha = a->alpha; p.beta = a->beta;
+  p.out_dtype = a->out_dtype; p.bias_dtype = a->bias_dtype;
+  p.a_mn = 0; p.b_mn = a->b_mn ? 1 : 0;
+  p.num_k = a->K / EPR;
+  const int nkt = p.num_k + (lora ? 1 : 0);
+  p.bn = bn;
+  p.num_m = ceil_div(a->M, kBM * ctas);
+  p.num_n = a->N / bn;
+  const int units = g_num_sms / ctas;
+  const long long tiles = (long long)p.num_m * p.num_n;
+  const long long sk_need = (long long)g_num_sms * kBM * kAccStride * 4 + (long long)g_num_sms * 4;
+  const bool allow_sk = a->workspace != nullptr && a->workspace_bytes >= sk_need && !getenv("B200_GEMM_NO_STREAMK");
+  const long long waves = (tiles + units - 1) / units;
+  const double classic = (double)waves * nkt, sk = (double)tiles * nkt / units + 10.0;
+  p.stream_k = (allow_sk && tiles % units != 0 && tiles * nkt >= 4ll * units && waves <= 4 && sk < classic * 0.85) ? 1 : 0;
+  p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0;
+  if (p.stream_k) {
+    static unsigned int epoch = 0x40000000u;   // own epoch space: flags are shared with b200_gemm's workspace
+    p.sk_ws = reinterpret_cast<float*>(a->workspace);
+    p.sk_flags = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(a->workspace) +
+                                                 (long long)g_num_sms * kBM * kAccStride * 4);
+    p.sk_epoch = ++epoch;
+  }
+  const int stage_bytes = kStageABytes + bn_cta * 128;
+  int raw_stages = 8, lut_bytes = kLutBytes;
+  { const char* e = getenv("B200_W4_RAW"); if (e) raw_stages = atoi(e); }
+  { const char* e = getenv("B200_W4_NOLUT"); if (e) lut_bytes = 0; }
+  int stages = (g_max_smem - 1024 - lut_bytes - raw_stages * kRawStageBytes - 8 * (2 * 8 + 5 + 2 * raw_stages)) / stage_bytes;
+  if (stages > 8) stages = 8;
+  if (stages < 3) return B200_ERR_UNSUPPORTED;
+  p.stages = stages;
+  const uint32_t fmt = a->in_dtype == B200_DT_BF16 ? 1u : 0u;
+  const uint32_t idesc_base = (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(bn >> 3) << 17) |
+                              ((uint32_t)((kBM * ctas) >> 4) << 24);
+  p.idesc_main = idesc_base | ((uint32_t)p.b_mn << 16);
+  p.idesc_lora = idesc_base;
+  const int out_es = a->out_dtype == B200_DT_FP32 ? 4 : 2;
+  const int per_vec = 16 / out_es;
+  p.vec_ok = ((reinterpret_cast<uintptr_t>(a->D) & 15) == 0) && (a->d_rs % per_vec == 0);
+
+  CUtensorMap tmA, tmA2, tmB2;
+  {
+    uint64_t dims[4] = {(uint64_t)a->K, (uint64_t)a->M, 1, 1}, str[3] = {(uint64_t)a->a_rs * ES, 0, 0};
+    uint32_t box[4] = {(uint32_t)EPR, (uint32_t)kBM, 1, 1};
+    rc = make_tensor_map(&tmA, a->A, ES, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  }
+  if (lora) {
+    uint64_t dims[4] = {(uint64_t)a->K2, (uint64_t)a->M, 1, 1}, str[3] = {(uint64_t)a->a2_rs * ES, 0, 0};
+    uint32_t box[4] = {(uint32_t)EPR, (uint32_t)kBM, 1, 1};
+    rc = make_tensor_map(&tmA2, a->A2, ES, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    uint64_t dimsb[4] = {(uint64_t)a->K2, (uint64_t)a->N, 1, 1}, strb[3] = {(uint64_t)a->b2_rs * ES, 0, 0};
+    uint32_t boxb[4] = {(uint32_t)EPR, (uint32_t)bn_cta, 1, 1};
+    rc = make_tensor_map(&tmB2, a->B2, ES, 4, dimsb, strb, boxb, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+  } else {
+    tmA2 = tmA;
+    tmB2 = tmA;
+  }
+  W4Params wp;
+  memset(&wp, 0, sizeof(wp));
+  for (int i = 0; i < 8; ++i) {
+    const int j = i < w->nshards ? i : 0;
+    const long long rows_here = w->nshards > 1 ? rps : w->rows;
+    uint64_t dims[2] = {(uint64_t)w->kw / 2, (uint64_t)rows_here}, str[1] = {(uint64_t)w->kw / 2};
+    uint32_t box[2] = {a->b_mn ? 64u : 32u, a->b_mn ? 64u : 128u};
+    rc = make_tensor_map(&wp.tmW[i], w->packed[j], 1, 2, dims, str, box, CU_TENSOR_MAP_SWIZZLE_NONE);
+    if (rc) return rc;
+    wp.scale[i] = w->scale[j];
+    wp.zs[i] = w->zs[j];
+  }
+  wp.lut = w->lut;
+  wp.nshards = w->nshards;
+  wp.rows_per_shard = (int)rps;
+  wp.group = w->group;
+  wp.kw = w->kw;
+  wp.raw_stages = raw_stages;
+  wp.lut_bytes = lut_bytes;
+  wp.is_bf16 = a->in_dtype == B200_DT_BF16;
+  { const char* d = getenv("B200_W4_DEBUG"); wp.debug = d ? atoi(d) : 0; }
+
+  const int grid = (p.stream_k ? units : (int)(tiles < units ? tiles : units)) * ctas;
+  const int smem = stages * stage_bytes + raw_stages * kRawStageBytes + lut_bytes + 8 * (2 * stages + 5 + 2 * raw_stages) + 1024;
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK(cudaFuncSetAttribute(gemm_w4_tcgen05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, g_max_smem));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kW4Threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = ctas;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  B200_CHECK(cudaLaunchKernelEx(&cfg, gemm_w4_tcgen05_kernel, tmA, tmA2, tmB2, wp, p));
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -38,98 +38,154 @@ __device__ __forceinline__ void keep8(unsigned long long seed, unsigned long lon
   k[4] = b.x >= thresh; k[5] = b.y >= thresh; k[6] = b.z >= thresh; k[7] = b.w >= thresh;
 }
 
-// ---- down: one warp per row of X, A staged through shared memory in 256-column chunks ----------
-template <int R>
+// ---- down: a CTA owns ROWS rows; its 8 warps split K in 256-column chunks (lane = 8 columns), every lane keeps
+// ROWS x R partial sums, A is read straight from L2 (it is r x K, shared by every CTA) and reused for the ROWS rows.
+// No shared-memory staging and no block barriers in the main loop: all loads of a chunk are independent.
+template <int R, int ROWS>
 __global__ void __launch_bounds__(256)
 lora_down_kernel(const __nv_bfloat16* __restrict__ X, const __nv_bfloat16* __restrict__ A,
                  __nv_bfloat16* __restrict__ T, int M, int K, int r, long long x_rs, long long a_rs, long long t_rs,
                  float alpha, unsigned long long seed, uint32_t thresh, float inv_keep) {
-  __shared__ __align__(16) __nv_bfloat16 As[R * 256];
+  __shared__ float red[8][ROWS * R];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m = blockIdx.x * 8 + warp;
-  float acc[R];
+  const int m0 = blockIdx.x * ROWS;
+  float acc[ROWS][R];
 #pragma unroll
-  for (int j = 0; j < R; ++j) acc[j] = 0.f;
-  for (int k0 = 0; k0 < K; k0 += 256) {
-    __syncthreads();
-    // stage A[:, k0 : k0+256] (zero-padded)
-    for (int i = threadIdx.x; i < R * 32; i += 256) {
-      const int j = i >> 5, c = (i & 31) * 8;
-      uint4 v = make_uint4(0, 0, 0, 0);
-      if (j < r && k0 + c < K) v = *reinterpret_cast<const uint4*>(A + (long long)j * a_rs + k0 + c);
-      *reinterpret_cast<uint4*>(As + j * 256 + c) = v;
-    }
-    __syncthreads();
-    const int k = k0 + lane * 8;
-    if (m < M && k < K) {
-      const uint4 xr = *reinterpret_cast<const uint4*>(X + (long long)m * x_rs + k);
+  for (int i = 0; i < ROWS; ++i)
+#pragma unroll
+    for (int j = 0; j < R; ++j) acc[i][j] = 0.f;
+  for (int k = warp * 256 + lane * 8; k < K; k += 2048) {
+    float xv[ROWS][8];
+#pragma unroll
+    for (int i = 0; i < ROWS; ++i) {
+      uint4 xr = make_uint4(0, 0, 0, 0);
+      if (m0 + i < M) xr = *reinterpret_cast<const uint4*>(X + (long long)(m0 + i) * x_rs + k);
       const __nv_bfloat16* xe = reinterpret_cast<const __nv_bfloat16*>(&xr);
-      float xv[8];
 #pragma unroll
-      for (int e = 0; e < 8; ++e) xv[e] = __bfloat162float(xe[e]);
+      for (int e = 0; e < 8; ++e) xv[i][e] = __bfloat162float(xe[e]);
       if (thresh) {
         bool kp[8];
-        keep8(seed, (unsigned long long)m * K + k, thresh, kp);
+        keep8(seed, (unsigned long long)(m0 + i) * K + k, thresh, kp);
 #pragma unroll
-        for (int e = 0; e < 8; ++e) xv[e] = kp[e] ? xv[e] * inv_keep : 0.f;
+        for (int e = 0; e < 8; ++e) xv[i][e] = kp[e] ? xv[i][e] * inv_keep : 0.f;
       }
+    }
 #pragma unroll
-      for (int j = 0; j < R; ++j) {
-        const uint4 ar = *reinterpret_cast<const uint4*>(As + j * 256 + lane * 8);
+    for (int j = 0; j < R; ++j) {
+      if (j < r) {
+        const uint4 ar = __ldg(reinterpret_cast<const uint4*>(A + (long long)j * a_rs + k));
         const __nv_bfloat16* ae = reinterpret_cast<const __nv_bfloat16*>(&ar);
-        float s = 0.f;
+        float av[8];
 #pragma unroll
-        for (int e = 0; e < 8; ++e) s += xv[e] * __bfloat162float(ae[e]);
-        acc[j] += s;
+        for (int e = 0; e < 8; ++e) av[e] = __bfloat162float(ae[e]);
+#pragma unroll
+        for (int i = 0; i < ROWS; ++i) {
+          float sacc = 0.f;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) sacc += xv[i][e] * av[e];
+          acc[i][j] += sacc;
+        }
       }
     }
   }
 #pragma unroll
-  for (int j = 0; j < R; ++j) {
-    const float s = warp_sum(acc[j]);
-    if (lane == 0 && m < M && j < r) T[(long long)m * t_rs + j] = __float2bfloat16_rn(s * alpha);
+  for (int i = 0; i < ROWS; ++i)
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      const float v = warp_sum(acc[i][j]);
+      if (lane == 0) red[warp][i * R + j] = v;
+    }
+  __syncthreads();
+  for (int o = threadIdx.x; o < ROWS * R; o += 256) {
+    const int i = o / R, j = o - i * R;
+    if (m0 + i < M && j < r) {
+      float v = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) v += red[w][o];
+      T[(long long)(m0 + i) * t_rs + j] = __float2bfloat16_rn(v * alpha);
+    }
   }
 }
 
-// ---- wgrad: grid (K / 256, row slices); thread owns one column, r accumulators; fp32 atomics ----
-template <int R>
+// ---- wgrad: grid (column blocks, row slices); a thread owns COLS consecutive columns and R x COLS accumulators,
+// walks the rows of its slice with independent vector loads of X, takes P from shared memory (broadcast) and ends
+// with (vector) fp32 atomics into the gradient arena. One Philox call covers the thread's 4 columns of a row.
+template <int R, int COLS>
 __global__ void __launch_bounds__(256)
 lora_wgrad_kernel(const __nv_bfloat16* __restrict__ P, const __nv_bfloat16* __restrict__ X, float* __restrict__ G,
                   int M, int K, int r, long long p_rs, long long x_rs, long long g_rs, float alpha,
-                  unsigned long long seed, uint32_t thresh, float inv_keep, int rows_per_slice) {
-  __shared__ float Ps[64 * R];
-  const int k = blockIdx.x * 256 + threadIdx.x;
+                  unsigned long long seed, uint32_t thresh, float inv_keep, int rows_per_slice, int vec_atomics) {
+  __shared__ float Ps[32 * R];
+  const int k = (blockIdx.x * 256 + threadIdx.x) * COLS;
   const int m_begin = blockIdx.y * rows_per_slice;
   const int m_end = min(M, m_begin + rows_per_slice);
-  float acc[R];
+  float acc[R][COLS];
 #pragma unroll
-  for (int j = 0; j < R; ++j) acc[j] = 0.f;
-  for (int m0 = m_begin; m0 < m_end; m0 += 64) {
+  for (int j = 0; j < R; ++j)
+#pragma unroll
+    for (int c = 0; c < COLS; ++c) acc[j][c] = 0.f;
+  for (int m0 = m_begin; m0 < m_end; m0 += 32) {
     __syncthreads();
-    for (int i = threadIdx.x; i < 64 * R; i += 256) {
+    for (int i = threadIdx.x; i < 32 * R; i += 256) {
       const int mm = i / R, j = i - mm * R;
       Ps[i] = (m0 + mm < m_end && j < r) ? __bfloat162float(P[(long long)(m0 + mm) * p_rs + j]) : 0.f;
     }
     __syncthreads();
     if (k < K) {
-      const int lim = min(64, m_end - m0);
+      const int lim = min(32, m_end - m0);
+#pragma unroll 4
       for (int mm = 0; mm < lim; ++mm) {
-        float xv = __bfloat162float(X[(long long)(m0 + mm) * x_rs + k]);
+        const __nv_bfloat16* xp = X + (long long)(m0 + mm) * x_rs + k;
+        float xv[COLS];
+        if constexpr (COLS == 4) {
+          const uint2 raw = *reinterpret_cast<const uint2*>(xp);
+          const __nv_bfloat16* xe = reinterpret_cast<const __nv_bfloat16*>(&raw);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) xv[c] = __bfloat162float(xe[c]);
+        } else {
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) xv[c] = __bfloat162float(xp[c]);
+        }
         if (thresh) {
           const unsigned long long e = (unsigned long long)(m0 + mm) * K + k;
           const uint4 b = lora_philox(seed, e >> 2);
-          const uint32_t w = (e & 3) == 0 ? b.x : (e & 3) == 1 ? b.y : (e & 3) == 2 ? b.z : b.w;
-          xv = w >= thresh ? xv * inv_keep : 0.f;
+          const uint32_t w[4] = {b.x, b.y, b.z, b.w};
+          if constexpr (COLS == 4) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) xv[c] = w[c] >= thresh ? xv[c] * inv_keep : 0.f;
+          } else {
+#pragma unroll
+            for (int c = 0; c < COLS; ++c) {
+              const uint32_t ww = w[(e + c) & 3];   // COLS in {1, 2} never crosses a 4-element Philox block when k % COLS == 0
+              xv[c] = ww >= thresh ? xv[c] * inv_keep : 0.f;
+            }
+          }
         }
 #pragma unroll
-        for (int j = 0; j < R; ++j) acc[j] += Ps[mm * R + j] * xv;
+        for (int j = 0; j < R; ++j) {
+          const float pv = Ps[mm * R + j];
+#pragma unroll
+          for (int c = 0; c < COLS; ++c) acc[j][c] += pv * xv[c];
+        }
       }
     }
   }
   if (k < K) {
 #pragma unroll
-    for (int j = 0; j < R; ++j)
-      if (j < r) atomicAdd(G + (long long)j * g_rs + k, acc[j] * alpha);
+    for (int j = 0; j < R; ++j) {
+      if (j < r) {
+        float* g = G + (long long)j * g_rs + k;
+        if constexpr (COLS == 4) {
+          if (vec_atomics) {
+            atomicAdd(reinterpret_cast<float4*>(g),
+                      make_float4(acc[j][0] * alpha, acc[j][1] * alpha, acc[j][2] * alpha, acc[j][3] * alpha));
+            continue;
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < COLS; ++c) atomicAdd(g + c, acc[j][c] * alpha);
+      }
+    }
   }
 }
 
@@ -187,9 +243,15 @@ B200_API int b200_lora_down(const void* X, const void* A, void* T, int M, int K,
   if (M <= 0 || K % 8 || x_rs % 8 || a_rs % 8 || r < 1) return B200_ERR_BAD_SHAPE;
   uint32_t thresh; float inv_keep;
   drop_params(p, &thresh, &inv_keep);
-  const unsigned grid = (unsigned)((M + 7) / 8);
-  B200_R_DISPATCH(r, lora_down_kernel<R><<<grid, 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)X, (const __nv_bfloat16*)A, (__nv_bfloat16*)T, M, K, r, x_rs, a_rs, t_rs, alpha, seed, thresh, inv_keep));
+  cudaStream_t st = (cudaStream_t)stream;
+#define B200_DOWN(R, ROWS) lora_down_kernel<R, ROWS><<<(unsigned)((M + ROWS - 1) / ROWS), 256, 0, st>>>( \
+      (const __nv_bfloat16*)X, (const __nv_bfloat16*)A, (__nv_bfloat16*)T, M, K, r, x_rs, a_rs, t_rs, alpha, seed, thresh, inv_keep)
+  if (r <= 8) B200_DOWN(8, 4);
+  else if (r <= 16) B200_DOWN(16, 4);
+  else if (r <= 32) B200_DOWN(32, 2);
+  else if (r <= 64) B200_DOWN(64, 1);
+  else return B200_ERR_TOO_LARGE;
+#undef B200_DOWN
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -200,13 +262,24 @@ B200_API int b200_lora_wgrad(const void* P, const void* X, float* G, int M, int 
   if (M <= 0 || r < 1) return B200_ERR_BAD_SHAPE;
   uint32_t thresh; float inv_keep;
   drop_params(p, &thresh, &inv_keep);
-  const int kblocks = (K + 255) / 256;
-  int slices = (2 * kNumSMs + kblocks - 1) / kblocks;
-  int rows_per_slice = ((M + slices - 1) / slices + 63) / 64 * 64;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool vec4 = K % 4 == 0 && x_rs % 4 == 0 && ((uintptr_t)X % 8) == 0 && r <= 16;
+  const bool vec2 = K % 2 == 0;
+  const int cols = vec4 ? 4 : (r <= 32 && vec2 ? 2 : 1);
+  const int vec_atomics = vec4 && g_rs % 4 == 0 && ((uintptr_t)G % 16) == 0;
+  const int kblocks = (K / cols + 255) / 256;
+  int slices = (3 * kNumSMs + kblocks - 1) / kblocks;
+  int rows_per_slice = ((M + slices - 1) / slices + 31) / 32 * 32;
   slices = (M + rows_per_slice - 1) / rows_per_slice;
   dim3 grid(kblocks, slices);
-  B200_R_DISPATCH(r, lora_wgrad_kernel<R><<<grid, 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)P, (const __nv_bfloat16*)X, G, M, K, r, p_rs, x_rs, g_rs, alpha, seed, thresh, inv_keep, rows_per_slice));
+#define B200_WG(R, C) lora_wgrad_kernel<R, C><<<grid, 256, 0, st>>>((const __nv_bfloat16*)P, (const __nv_bfloat16*)X, G, M, K, r, \
+      p_rs, x_rs, g_rs, alpha, seed, thresh, inv_keep, rows_per_slice, vec_atomics)
+  if (r <= 8) { if (cols == 4) B200_WG(8, 4); else if (cols == 2) B200_WG(8, 2); else B200_WG(8, 1); }
+  else if (r <= 16) { if (cols == 4) B200_WG(16, 4); else if (cols == 2) B200_WG(16, 2); else B200_WG(16, 1); }
+  else if (r <= 32) { if (cols == 2) B200_WG(32, 2); else B200_WG(32, 1); }
+  else if (r <= 64) B200_WG(64, 1);
+  else return B200_ERR_TOO_LARGE;
+#undef B200_WG
   B200_LAUNCH_CHECK();
   return 0;
 }

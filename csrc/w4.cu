@@ -112,6 +112,55 @@ w4_dequant_kernel(W4Shards sh, T* __restrict__ out, long long N, int K, int grou
   }
 }
 
+// Transposed expansion: out_t[k, n] = w[n, k] (out_t row stride out_rs elements). Used by the backward pass so that
+// dgrad (dY x W) reads W^T as a K-major tcgen05 operand instead of the slower MN-major path. One CTA (128 threads)
+// owns a 64(n) x 64(k) tile: each thread expands one 16-byte chunk (32 weights of one row) into a padded shared
+// tile t[k][n], then the tile is written out as 64 rows of 128 contiguous bytes. N % 64 == 0, K % 64 == 0.
+template <typename T>
+__global__ void __launch_bounds__(128)
+w4_dequant_t_kernel(W4Shards sh, T* __restrict__ out, long long N, int K, int group, const float* __restrict__ lut_g,
+                    long long out_rs) {
+  constexpr int TS = 72;  // padded row stride (elements): 144 B keeps 16-byte alignment and staggers banks
+  __shared__ float lut[16];
+  __shared__ __align__(16) T tile[64 * TS];
+  if (threadIdx.x < 16) lut[threadIdx.x] = lut_g ? lut_g[threadIdx.x] : kNF4[threadIdx.x];
+  __syncthreads();
+  const int k_tiles = K / 64;
+  const long long n0 = (long long)(blockIdx.x / k_tiles) * 64;
+  const int k0 = (int)(blockIdx.x % k_tiles) * 64;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  {
+    const int nl_t = (warp & 1) * 32 + lane, c = warp >> 1;
+    const long long n = n0 + nl_t;
+    const int s = sh.nshards > 1 ? (int)(n / sh.rows_per_shard) : 0;
+    const long long nl = n - (long long)s * sh.rows_per_shard;
+    const int kc = k0 / 32 + c;
+    const uint4 raw = *reinterpret_cast<const uint4*>(sh.packed[s] + (nl * K / 2) + kc * 16);
+    const int g = (kc * 32) / group;
+    const int groups_per_row = K / group;
+    const float sc = sh.scale[s][nl * groups_per_row + g];
+    const float zs = sh.zs[s] ? sh.zs[s][nl * groups_per_row + g] : 0.f;
+    const uint32_t words[4] = {raw.x, raw.y, raw.z, raw.w};
+    T* col = tile + (c * 32) * TS + nl_t;
+#pragma unroll
+    for (int wi = 0; wi < 4; ++wi) {
+#pragma unroll
+      for (int b = 0; b < 4; ++b) {
+        const uint32_t byte = (words[wi] >> (8 * b)) & 0xFFu;
+        col[(wi * 8 + 2 * b) * TS] = from_f32<T>(lut[byte >> 4] * sc - zs);
+        col[(wi * 8 + 2 * b + 1) * TS] = from_f32<T>(lut[byte & 15u] * sc - zs);
+      }
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int it = 0; it < 4; ++it) {
+    const int k = it * 16 + warp * 4 + (lane >> 3), seg = lane & 7;
+    const uint4 v = *reinterpret_cast<const uint4*>(tile + k * TS + seg * 8);
+    *reinterpret_cast<uint4*>(out + (long long)(k0 + k) * out_rs + n0 + seg * 8) = v;
+  }
+}
+
 // y[m, n] = sum_k x[m, k] * w[n, k] for m < M <= 8: one warp per output column n.
 template <typename T, int kMaxM>
 __global__ void __launch_bounds__(256)
@@ -218,6 +267,29 @@ B200_API int b200_w4_dequant(const void* const* packed, const void* const* scale
   cudaStream_t st = (cudaStream_t)stream;
   if (out_dtype == B200_DT_BF16) w4_dequant_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(sh, (__nv_bfloat16*)out, N, K, group, lut, out_rs);
   else if (out_dtype == B200_DT_FP16) w4_dequant_kernel<__half><<<grid, 256, 0, st>>>(sh, (__half*)out, N, K, group, lut, out_rs);
+  else return B200_ERR_UNSUPPORTED;
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// Same as b200_w4_dequant but writes the transpose: out_t [K, N] (row stride out_rs). N % 64 == 0, K % 64 == 0.
+B200_API int b200_w4_dequant_t(const void* const* packed, const void* const* scale, const void* const* zs, int nshards,
+                               long long rows_per_shard, void* out, long long N, int K, int group, const float* lut,
+                               long long out_rs, int out_dtype, void* stream) {
+  if (nshards < 1 || nshards > 8 || K % 64 || N % 64 || group % 32 || K % group) return B200_ERR_BAD_SHAPE;
+  if (nshards > 1 && rows_per_shard % 64) return B200_ERR_BAD_SHAPE;
+  W4Shards sh;
+  for (int i = 0; i < 8; ++i) {
+    sh.packed[i] = i < nshards ? (const uint8_t*)packed[i] : nullptr;
+    sh.scale[i] = i < nshards ? (const float*)scale[i] : nullptr;
+    sh.zs[i] = (i < nshards && zs) ? (const float*)zs[i] : nullptr;
+  }
+  sh.rows_per_shard = rows_per_shard;
+  sh.nshards = nshards;
+  const unsigned grid = (unsigned)((N / 64) * (K / 64));
+  cudaStream_t st = (cudaStream_t)stream;
+  if (out_dtype == B200_DT_BF16) w4_dequant_t_kernel<__nv_bfloat16><<<grid, 128, 0, st>>>(sh, (__nv_bfloat16*)out, N, K, group, lut, out_rs);
+  else if (out_dtype == B200_DT_FP16) w4_dequant_t_kernel<__half><<<grid, 128, 0, st>>>(sh, (__half*)out, N, K, group, lut, out_rs);
   else return B200_ERR_UNSUPPORTED;
   B200_LAUNCH_CHECK();
   return 0;

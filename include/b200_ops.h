@@ -74,6 +74,28 @@ long long b200_gemm_workspace_bytes(void);
 
 int b200_gemm(const b200_gemm_args* args, void* stream);
 
+/* The same GEMM with the B operand expanded from 4-bit codes inside the kernel: NF4 (QLoRA base,
+ * Fine-Tuning/qwen3-14b-qlora-dist-deepspeed.py:101-106) or GPTQ/AWQ W4A16 weights
+ * (Quantization/GPTQModel/quantize_qwen3_4b_gptq.py:16-21), optionally row-sharded over up to 8 buffers that may be
+ * peer-GPU memory (ZeRO-3 / FSDP parameter shards; the all-gather happens as TMA reads inside the GEMM). W is
+ * [rows, kw], packed [rows, kw / 2] uint8 (even element in the high nibble), scale / zs fp32 [rows, kw / group];
+ * w = lut[code] * scale - zs (lut NULL = NF4). args->B is ignored. args->b_mn = 0: D = A x W^T (forward, N = rows,
+ * K = kw); b_mn = 1: D = A x W (dgrad, N = kw, K = rows). LoRA operands (A2/B2), bias, alpha/beta and the stream-K
+ * workspace work as in b200_gemm. Returns B200_ERR_UNSUPPORTED_ for shapes outside its domain (M <= 128,
+ * N % 256, K % 64, group % 64, shard rows % 128 (forward) / % 64 (dgrad), fp32 inputs): callers fall back to
+ * b200_w4_dequant + b200_gemm. */
+typedef struct {
+  const void* packed[8];
+  const float* scale[8];
+  const float* zs[8];   /* entries may be NULL */
+  const float* lut;     /* 16 floats, or NULL for the NF4 code book */
+  int32_t nshards;
+  int32_t rows, kw, group;
+  int64_t rows_per_shard;
+} b200_w4_desc;
+
+int b200_gemm_w4(const b200_gemm_args* args, const b200_w4_desc* w, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * K5: RMSNorm / LayerNorm (layer_norm = 0 / 1) with the residual add fused in.
  *   fwd: h = x (+ res); y = norm(h) * w (+ b). stats[rows, 2] = (mean, rstd). h_out may be NULL.
@@ -176,6 +198,11 @@ int b200_nf4_absmax_decode(const uint8_t* q, const float* code2, const float* ab
 int b200_w4_dequant(const void* const* packed, const void* const* scale, const void* const* zs, int nshards,
                     long long rows_per_shard, void* out, long long N, int K, int group, const float* lut,
                     long long out_rs, int out_dtype, void* stream);
+/* Transposed variant: out_t [K, N] = W^T, so the backward dgrad GEMM (dY x W) reads a K-major operand
+ * (N % 64 == 0, K % 64 == 0, rows_per_shard % 64 == 0). */
+int b200_w4_dequant_t(const void* const* packed, const void* const* scale, const void* const* zs, int nshards,
+                      long long rows_per_shard, void* out, long long N, int K, int group, const float* lut,
+                      long long out_rs, int out_dtype, void* stream);
 int b200_w4_gemv(const void* x, const uint8_t* packed, const float* scale, const float* zs, const float* lut,
                  const void* bias, void* y, int M, long long N, int K, int group, long long x_rs, long long y_rs,
                  int dtype, void* stream);

@@ -115,7 +115,6 @@ class Generator:
         H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
         cos, sin = m.rope(dev, self.max_len)
         pos = torch.arange(S, device=dev, dtype=torch.int32).repeat(B)
-        Sp = (S + 7) // 8 * 8 if ids.is_cuda else S
         delta, res = ew.embedding(ids.reshape(-1), m.embed_tokens), None
         for li, layer in enumerate(m.layers):
             x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
@@ -123,11 +122,7 @@ class Generator:
             t = qkv.view(B, S, H + 2 * Hkv, D)
             cache.k[li][rows, :, :S] = t[:, :, H:H + Hkv].permute(0, 2, 1, 3)
             cache.v[li][rows, :, :S] = t[:, :, H + Hkv:].permute(0, 2, 1, 3)
-            if Sp != S:
-                qkv = torch.nn.functional.pad(qkv.view(B, S, -1), (0, 0, 0, Sp - S)).reshape(B * Sp, -1)
-            ctx = attention(qkv, B, Sp, H, Hkv, D, causal=True)
-            if Sp != S:
-                ctx = ctx.view(B, Sp, -1)[:, :S].reshape(B * S, -1)
+            ctx = attention(qkv, B, S, H, Hkv, D, causal=True)
             x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
             delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
         h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)

@@ -149,6 +149,14 @@ def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, 
         scale = 1.0 / math.sqrt(head_dim)
     if not nv.use_native(qkv) or (S % 8 and not causal) or qkv.dtype == torch.float32 and False:
         return _ref_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)
+    if S % 8:
+        # the score / probability matrices need 16-byte row strides: pad the sequence to a multiple of 8; under the
+        # causal mask the real rows never see the padded keys, so the result is exact
+        Sp = (S + 7) // 8 * 8
+        W = qkv.shape[1]
+        qp = torch.nn.functional.pad(qkv.view(B, S, W), (0, 0, 0, Sp - S)).reshape(B * Sp, W)
+        out = attention(qp, B, Sp, n_heads, n_kv_heads, head_dim, causal, window, scale, impl, dropout_p)
+        return out.view(B, Sp, -1)[:, :S].reshape(B * S, -1)
     qkv = qkv.contiguous()
     if impl in ("auto", "flash") and _flash_available() and qkv.dtype == torch.bfloat16 and head_dim == 128 \
             and window == 0 and dropout_p == 0.0:

@@ -15,6 +15,7 @@ GEMMs of peft's LoRA layer (Fine-Tuning/qwen3-8b-lora-dist.py:118-125).
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -170,3 +171,93 @@ def linear_dgrad(dy, w, out=None, beta=0.0, out_dtype=None):
 def linear_wgrad(dy, x, out=None, beta=0.0, out_dtype=None):
     """dw[N,K] = dy[M,N]^T @ x[M,K]  (beta=1 accumulates into an existing gradient)."""
     return gemm(dy, x, a_mn=True, b_mn=True, out=out, beta=beta, out_dtype=out_dtype)
+
+
+# ------------------------------------------------------------------------------------------------
+# 4-bit B operand expanded inside the GEMM (csrc/gemm_tcgen05.cu: gemm_w4_tcgen05_kernel)
+# ------------------------------------------------------------------------------------------------
+class W4Desc(ctypes.Structure):
+    _fields_ = [("packed", ctypes.c_void_p * 8), ("scale", ctypes.c_void_p * 8), ("zs", ctypes.c_void_p * 8),
+                ("lut", ctypes.c_void_p), ("nshards", ctypes.c_int32), ("rows", ctypes.c_int32), ("kw", ctypes.c_int32),
+                ("group", ctypes.c_int32), ("rows_per_shard", ctypes.c_int64)]
+
+
+# Off by default: on B200 the dense kernel is already bound by the shared-memory port (TMA fill + UMMA operand reads),
+# so the extra smem traffic and barrier hand-offs of in-kernel expansion cost more than the separate bandwidth-bound
+# dequant pass saves at M = 1024 (gate_up fwd: 0.61 ms fused vs 0.27 + 0.10 ms; profiles/w4_fused_gemm.md).
+# B200_W4_FUSED=1 turns it on (it wins when the 16-bit copy would not fit or M is large enough to amortise nothing).
+W4_FUSED = os.environ.get("B200_W4_FUSED", "0") == "1"
+
+
+def w4_desc(q) -> Optional[W4Desc]:
+    """Build (and cache on ``q``) the C descriptor of a 4-bit weight: NF4Weight, ShardedNF4 (peer shards) or W4Weight."""
+    d = getattr(q, "_w4desc", None)
+    if d is not None:
+        return d
+    d = W4Desc()
+    shards = getattr(q, "shards", None)
+    if shards is not None:
+        if len(shards) > 8:
+            return None
+        for i, (pp, sp, zp) in enumerate(shards):
+            d.packed[i], d.scale[i], d.zs[i] = pp, sp, zp or None
+        d.nshards, d.rows_per_shard = len(shards), q.rows
+        keep = None
+    else:
+        sc = q.scales() if hasattr(q, "scales") else q.scale
+        zs = getattr(q, "zs", None)
+        d.packed[0], d.scale[0], d.zs[0] = q.packed.data_ptr(), sc.data_ptr(), None if zs is None else zs.data_ptr()
+        d.nshards, d.rows_per_shard = 1, q.N
+        keep = (sc, zs)
+    lut = q._lut() if hasattr(q, "_lut") else None
+    d.lut = None if lut is None else lut.data_ptr()
+    d.rows, d.kw, d.group = q.N, q.K, q.group
+    q._w4desc, q._w4keep = d, (keep, lut)
+    return d
+
+
+def gemm_w4(a: torch.Tensor, q, *, b_mn: bool = False, out: Optional[torch.Tensor] = None, bias=None, lora=None,
+            alpha: float = 1.0, beta: float = 0.0, force: bool = False) -> Optional[torch.Tensor]:
+    """``a @ W^T`` (b_mn False) or ``a @ W`` (b_mn True) with W read as 4-bit codes. Returns None when the fused
+    kernel does not cover the shape, so the caller can take the dequantise-then-GEMM path."""
+    if not ((W4_FUSED or force) and nv.use_native(a)) or a.dtype not in (torch.bfloat16, torch.float16) or a.dim() != 2:
+        return None
+    M, K = a.shape
+    N = q.K if b_mn else q.N
+    if M <= 128 or N % 256 or K % 64 or q.group % 64 or K != (q.N if b_mn else q.K):
+        return None
+    d = w4_desc(q)
+    if d is None or (d.nshards > 1 and d.rows_per_shard % (64 if b_mn else 128)):
+        return None
+    if a.stride(-1) != 1:
+        a = a.contiguous()
+    if out is None:
+        out = torch.empty(M, N, dtype=a.dtype, device=a.device)
+    args = nv.GemmArgs()
+    args.A, args.B, args.D = a.data_ptr(), 0, out.data_ptr()
+    args.bias = 0 if bias is None else bias.data_ptr()
+    args.bias_dtype = nv.dtype_code(bias.dtype) if bias is not None else 0
+    args.M, args.N, args.K = M, N, K
+    args.batch, args.nb0, args.b_div = 1, 1, 1
+    args.a_rs, args.d_rs = a.stride(0), out.stride(0)
+    args.a_mn, args.b_mn = 0, int(b_mn)
+    args.in_dtype, args.out_dtype = nv.dtype_code(a.dtype), nv.dtype_code(out.dtype)
+    args.alpha, args.beta = alpha, beta
+    keep = None
+    if lora is not None:
+        a2, b2 = lora
+        a2 = a2 if a2.stride(-1) == 1 else a2.contiguous()
+        b2 = b2 if b2.stride(-1) == 1 else b2.contiguous()
+        keep = (a2, b2)
+        args.A2, args.B2, args.K2 = a2.data_ptr(), b2.data_ptr(), a2.shape[-1]
+        args.a2_rs, args.b2_rs = a2.stride(0), b2.stride(0)
+    ws = _stream_k_workspace(a.device)
+    args.workspace, args.workspace_bytes = ws.data_ptr(), ws.numel()
+    fn = nv.proto("b200_gemm_w4", [ctypes.POINTER(nv.GemmArgs), ctypes.POINTER(W4Desc), ctypes.c_void_p])
+    rc = fn(ctypes.byref(args), ctypes.byref(d), nv.stream())
+    if rc == 10006:      # B200_ERR_UNSUPPORTED_: shape outside the fused kernel's domain
+        return None
+    nv.check(rc, f"gemm_w4 M={M} N={N} K={K}")
+    nv.count_launch()
+    del keep
+    return out

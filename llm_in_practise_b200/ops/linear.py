@@ -26,7 +26,7 @@ from torch import nn
 
 from . import _native as nv
 from . import elementwise as ew
-from .gemm import gemm
+from .gemm import gemm, gemm_w4
 from .lora import lora_down, lora_dx, lora_wgrad
 from .w4 import NF4Weight
 
@@ -93,13 +93,13 @@ class _FrozenLinearFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, layer):
         ctx.layer = layer
-        return gemm(x, layer._materialize_weight(x.dtype), bias=layer.bias)
+        return layer._fwd(x)
 
     @staticmethod
     def backward(ctx, dy):
         if not ctx.needs_input_grad[0]:
             return None, None
-        return gemm(dy.contiguous(), ctx.layer._materialize_weight(dy.dtype), b_mn=True), None
+        return ctx.layer._dgrad(dy.contiguous()), None
 
 
 class _LoraLinearFn(torch.autograd.Function):
@@ -110,9 +110,8 @@ class _LoraLinearFn(torch.autograd.Function):
     def forward(ctx, x, layer, seed, *adapter_params):
         layer._refresh_adapter_buffers()
         p = layer.lora_dropout if layer.training else 0.0
-        W = layer._materialize_weight(x.dtype)
         T = lora_down(x, layer._A_stack, 1.0, seed, p)                       # [M, r_total]
-        y = gemm(x, W, lora=(T, layer._B_block), bias=layer.bias)
+        y = layer._fwd(x, lora=(T, layer._B_block))
         ctx.save_for_backward(x, T)
         ctx.layer, ctx.seed, ctx.p = layer, seed, p
         return y
@@ -130,12 +129,11 @@ class _LoraLinearFn(torch.autograd.Function):
             lora_wgrad(T[:, c0:c1], dy[:, lo:hi], gBt, scale, 0, 0.0)        # d(B_i^T) [r, N_i]
         dx = None
         if ctx.needs_input_grad[0]:
-            W = layer._materialize_weight(dy.dtype)
             if p > 0.0:
-                dx = gemm(dy, W, b_mn=True)
+                dx = layer._dgrad(dy)
                 lora_dx(dT, layer._A_stack, dx, 1.0, seed, p)
             else:
-                dx = gemm(dy, W, b_mn=True, lora=(dT, layer._At))
+                dx = layer._dgrad(dy, lora=(dT, layer._At))
         return (dx, None, None) + (None,) * (len(ctx.needs_input_grad) - 3)
 
 
@@ -195,6 +193,28 @@ class FusedLinear(nn.Module):
             ws = weight_workspace(self.nf4.packed.device, dtype, self.out_features * self.in_features)
             return self.nf4.dequantize(dtype, out=ws.view(self.out_features, self.in_features))
         return self.weight
+
+    def _fwd(self, x: torch.Tensor, lora=None) -> torch.Tensor:
+        """y = x W^T (+ low-rank term) (+ bias); a 4-bit base goes through the dequant-fused tcgen05 GEMM."""
+        if self.nf4 is not None:
+            y = gemm_w4(x, self.nf4, lora=lora, bias=self.bias)
+            if y is not None:
+                return y
+        return gemm(x, self._materialize_weight(x.dtype), lora=lora, bias=self.bias)
+
+    def _dgrad(self, dy: torch.Tensor, lora=None) -> torch.Tensor:
+        """dX = dY x W (+ low-rank term). A 4-bit base is expanded straight into W^T so the GEMM reads two K-major
+        operands (the MN-major B path of the tcgen05 kernel is ~25 % slower)."""
+        q = self.nf4
+        if q is not None:
+            dx = gemm_w4(dy, q, b_mn=True, lora=lora)          # codes expanded inside the GEMM (peer shards included)
+            if dx is not None:
+                return dx
+        if q is not None and dy.is_cuda and getattr(q, "can_transpose", lambda: False)() and dy.dtype != torch.float32:
+            ws = weight_workspace(q.packed.device, dy.dtype, self.out_features * self.in_features)
+            wt = q.dequantize(dy.dtype, out=ws.view(self.in_features, self.out_features), transpose=True)
+            return gemm(dy, wt, lora=lora)
+        return gemm(dy, self._materialize_weight(dy.dtype), b_mn=True, lora=lora)
 
     def dense_weight(self) -> torch.Tensor:
         """A fresh dense copy of the base weight (for merging / export)."""

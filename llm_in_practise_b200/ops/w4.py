@@ -115,18 +115,22 @@ def nf4_quantize(w: torch.Tensor):
 
 def w4_dequant(packed, scale, zs, N: int, K: int, group: int, lut: Optional[torch.Tensor] = None,
                dtype=torch.bfloat16, out: Optional[torch.Tensor] = None,
-               shards: Optional[Sequence[Sequence[int]]] = None, rows_per_shard: int = 0) -> torch.Tensor:
-    """Expand 4-bit weights to ``dtype`` [N, K]. With ``shards`` = [(packed_ptr, scale_ptr, zs_ptr), ...]
-    the rows are read from several (possibly peer-GPU) buffers of ``rows_per_shard`` rows each."""
+               shards: Optional[Sequence[Sequence[int]]] = None, rows_per_shard: int = 0,
+               transpose: bool = False) -> torch.Tensor:
+    """Expand 4-bit weights to ``dtype`` [N, K] (``transpose``: [K, N], the layout the dgrad GEMM wants). With
+    ``shards`` = [(packed_ptr, scale_ptr, zs_ptr), ...] the rows are read from several (possibly peer-GPU) buffers
+    of ``rows_per_shard`` rows each."""
     want = out.dtype if out is not None else dtype
     if not (packed.is_cuda and nv.use_native(packed)) or want == torch.float32:   # fp32 only in calibration searches
         res = _w4_dequant_ref(packed, scale, zs, N, K, group, lut, dtype)
+        if transpose:
+            res = res.t().contiguous()
         if out is not None:
             out.copy_(res)
             return out
         return res
     if out is None:
-        out = torch.empty(N, K, dtype=dtype, device=packed.device)
+        out = torch.empty((K, N) if transpose else (N, K), dtype=dtype, device=packed.device)
     if shards is None:
         shards = [(packed.data_ptr(), scale.data_ptr(), 0 if zs is None else zs.data_ptr())]
         rows_per_shard = N
@@ -134,7 +138,8 @@ def w4_dequant(packed, scale, zs, N: int, K: int, group: int, lut: Optional[torc
     PA = (ctypes.c_void_p * n)(*[s[0] for s in shards])
     SA = (ctypes.c_void_p * n)(*[s[1] for s in shards])
     ZA = (ctypes.c_void_p * n)(*[s[2] or None for s in shards])
-    fn = nv.proto("b200_w4_dequant", [vp, vp, vp, i32, i64, vp, i64, i32, i32, vp, i64, i32, vp])
+    fn = nv.proto("b200_w4_dequant_t" if transpose else "b200_w4_dequant",
+                  [vp, vp, vp, i32, i64, vp, i64, i32, i32, vp, i64, i32, vp])
     nv.check(fn(ctypes.cast(PA, vp), ctypes.cast(SA, vp), ctypes.cast(ZA, vp), n, rows_per_shard, nv.ptr(out), N, K,
                 group, nv.ptr(lut), out.stride(0), nv.dtype_code(out.dtype), nv.stream()), "w4_dequant")
     nv.count_launch()
@@ -202,8 +207,12 @@ class NF4Weight:
             return out
         return dequantize_blockwise_8bit(self.absmax_q, self.absmax2, self.code2, 256) + self.offset
 
-    def dequantize(self, dtype=torch.bfloat16, out=None) -> torch.Tensor:
-        return w4_dequant(self.packed, self.scales(), None, self.N, self.K, self.group, None, dtype, out)
+    def dequantize(self, dtype=torch.bfloat16, out=None, transpose: bool = False) -> torch.Tensor:
+        return w4_dequant(self.packed, self.scales(), None, self.N, self.K, self.group, None, dtype, out,
+                          transpose=transpose)
+
+    def can_transpose(self) -> bool:
+        return self.N % 64 == 0 and self.K % 64 == 0
 
     def nbytes(self) -> int:
         n = self.packed.numel()

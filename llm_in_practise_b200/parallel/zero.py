@@ -81,9 +81,12 @@ class ShardedNF4:
         self.packed = packed_buf.local  # for .device
         self.shards = [(packed_buf.ptrs[r] + p_off, scale_buf.ptrs[r] + s_off * 4, 0) for r in range(world)]
 
-    def dequantize(self, dtype=torch.bfloat16, out=None) -> torch.Tensor:
+    def dequantize(self, dtype=torch.bfloat16, out=None, transpose: bool = False) -> torch.Tensor:
         return w4_dequant(self._pbuf.local, self._sbuf.local, None, self.N, self.K, self.group, None, dtype, out,
-                          shards=self.shards, rows_per_shard=self.rows)
+                          shards=self.shards, rows_per_shard=self.rows, transpose=transpose)
+
+    def can_transpose(self) -> bool:
+        return self.N % 64 == 0 and self.K % 64 == 0 and self.rows % 64 == 0
 
     def local_shard(self) -> Tuple[torch.Tensor, torch.Tensor]:
         nb = self.rows * self.K // 2

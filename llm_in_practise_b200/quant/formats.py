@@ -43,8 +43,12 @@ class W4Weight:
             self.lut = self.lut.to(self.packed.device)
         return self.lut
 
-    def dequantize(self, dtype=torch.bfloat16, out=None) -> torch.Tensor:
-        return w4_dequant(self.packed, self.scale, self.zs, self.N, self.K, self.group, self._lut(), dtype, out)
+    def dequantize(self, dtype=torch.bfloat16, out=None, transpose: bool = False) -> torch.Tensor:
+        return w4_dequant(self.packed, self.scale, self.zs, self.N, self.K, self.group, self._lut(), dtype, out,
+                          transpose=transpose)
+
+    def can_transpose(self) -> bool:
+        return self.N % 64 == 0 and self.K % 64 == 0
 
     def gemv(self, x: torch.Tensor, bias=None) -> torch.Tensor:
         return w4_gemv(x, self.packed, self.scale, self.zs, self.N, self.K, self.group, self._lut(), bias)

@@ -101,3 +101,68 @@ def test_gemm_batched_gqa_strided():
     p = torch.softmax(s, dim=-1).to(torch.bfloat16)
     o = G.gemm(p, v, b_mn=True)
     _check(o, p.float() @ vr.float(), 2e-2)
+
+
+# ------------------------------------------------------------------------------------------------
+# 4-bit B operand expanded inside the GEMM
+# ------------------------------------------------------------------------------------------------
+class _FakeSharded:
+    """Two row shards in separate buffers on one GPU: same descriptor layout as ZeRO-3's ShardedNF4."""
+
+    def __init__(self, q, world=2):
+        self.N, self.K, self.group = q.N, q.K, q.group
+        self.rows = q.N // world
+        sc = q.scales()
+        self._bufs = []
+        self.shards = []
+        for r in range(world):
+            p = q.packed.view(q.N, q.K // 2)[r * self.rows:(r + 1) * self.rows].contiguous().clone()
+            s = sc.view(q.N, -1)[r * self.rows:(r + 1) * self.rows].contiguous().clone()
+            self._bufs.append((p, s))
+            self.shards.append((p.data_ptr(), s.data_ptr(), 0))
+        self.packed = self._bufs[0][0]
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("M,N,K,b_mn", [(1024, 1024, 512, False), (300, 256, 64, False), (1024, 5120, 17408, False),
+                                        (512, 7168, 5120, False), (1024, 512, 1024, True), (1024, 5120, 7168, True),
+                                        (260, 256, 128, True)])
+def test_gemm_w4_nf4_fused(M, N, K, b_mn):
+    from llm_in_practise_b200.ops.w4 import NF4Weight
+    torch.manual_seed(0)
+    rows, kw = (K, N) if b_mn else (N, K)            # stored weight W [rows, kw]
+    w = torch.randn(rows, kw, device="cuda", dtype=torch.bfloat16) / kw ** 0.5
+    q = NF4Weight.quantize(w, double_quant=True)
+    wd = q.dequantize(torch.bfloat16).float()
+    x = torch.randn(M, K, device="cuda", dtype=torch.bfloat16)
+    ref = x.float() @ (wd if b_mn else wd.t())
+    y = G.gemm_w4(x, q, b_mn=b_mn, force=True)
+    assert y is not None, "fused kernel refused a supported shape"
+    _check(y, ref, 2e-2)
+    # low-rank term + bias ride along as in the dense kernel
+    a2 = torch.randn(M, 16, device="cuda", dtype=torch.bfloat16)
+    b2 = torch.randn(N, 16, device="cuda", dtype=torch.bfloat16) / 4
+    bias = torch.randn(N, device="cuda", dtype=torch.bfloat16)
+    y2 = G.gemm_w4(x, q, b_mn=b_mn, lora=(a2, b2), bias=bias, force=True)
+    _check(y2, ref + a2.float() @ b2.float().t() + bias.float(), 2e-2)
+    # row shards in separate buffers (the ZeRO-3 layout): identical result
+    if rows % 256 == 0:
+        y3 = G.gemm_w4(x, _FakeSharded(q), b_mn=b_mn, force=True)
+        assert y3 is not None and torch.equal(y3, y)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("sym", [True, False])
+def test_gemm_w4_int4_fp16(sym):
+    from llm_in_practise_b200.quant.formats import quantize_rtn
+    torch.manual_seed(1)
+    w = torch.randn(1024, 2048, device="cuda") / 45
+    q = quantize_rtn(w, 128, sym)
+    x = torch.randn(512, 2048, device="cuda", dtype=torch.float16)
+    wd = q.dequantize(torch.float16).float()
+    y = G.gemm_w4(x, q, force=True)
+    assert y is not None
+    _check(y, x.float() @ wd.t(), 2e-2)
+    dy = torch.randn(512, 1024, device="cuda", dtype=torch.float16)
+    dx = G.gemm_w4(dy, q, b_mn=True, force=True)
+    _check(dx, dy.float() @ wd, 2e-2)

@@ -156,6 +156,41 @@ def test_nf4_roundtrip_and_double_quant():
     assert rel(q.dequantize(), w) < 0.25
 
 
+def test_w4_dequant_transposed_and_dgrad():
+    from llm_in_practise_b200.ops.linear import FusedLinear
+    w = torch.randn(512, 1024, device=DEV, dtype=torch.bfloat16)
+    q = W4.NF4Weight.quantize(w, double_quant=True)
+    assert torch.equal(q.dequantize(transpose=True), q.dequantize().t().contiguous())
+    # asymmetric W4A16 (zs, integer LUT, group 128) through the same kernel
+    packed = torch.randint(0, 256, (256 * 384 // 2,), device=DEV, dtype=torch.uint8)
+    scale = torch.rand(256 * 384 // 128, device=DEV) * 0.01 + 0.001
+    lut = torch.arange(16, device=DEV, dtype=torch.float32)
+    a = W4.w4_dequant(packed, scale, scale * 7, 256, 384, 128, lut, torch.float16)
+    b = W4.w4_dequant(packed, scale, scale * 7, 256, 384, 128, lut, torch.float16, transpose=True)
+    assert torch.equal(b, a.t().contiguous())
+    # the frozen-base backward uses it: dX must match dY @ W
+    lin = FusedLinear(1024, [("p", 512)], dtype=torch.bfloat16, device=DEV)
+    lin.weight.data.copy_(w)
+    lin.quantize_nf4(True)
+    x = torch.randn(256, 1024, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    dy = torch.randn(256, 512, device=DEV, dtype=torch.bfloat16)
+    lin(x).backward(dy)
+    assert rel(x.grad, dy.float() @ lin.nf4.dequantize().float()) < 1e-2
+
+
+@pytest.mark.parametrize("r,K", [(32, 1024), (64, 512), (8, 1030)])
+def test_lora_small_kernels_wide_ranks(r, K):
+    M = 300
+    x = torch.randn(M, K + 8, device=DEV, dtype=torch.bfloat16)[:, 2:K + 2] if K % 8 else torch.randn(M, K, device=DEV, dtype=torch.bfloat16)
+    pm = torch.randn(M, r, device=DEV, dtype=torch.bfloat16)
+    G = torch.zeros(r, K, device=DEV)
+    LR.lora_wgrad(pm, x, G, 1.0, 5, 0.0)
+    assert rel(G, pm.float().t() @ x.float()) < 2e-2
+    if K % 8 == 0:
+        a = (torch.randn(r, K, device=DEV) / 8).bfloat16()
+        assert rel(LR.lora_down(x, a, 1.0, 5, 0.0), x.float() @ a.float().t()) < 2e-2
+
+
 def test_w4_gemv_matches_dequant():
     N_, K, g = 1024, 2048, 128
     packed = torch.randint(0, 256, (N_ * K // 2,), device=DEV, dtype=torch.uint8)
