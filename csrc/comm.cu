@@ -287,13 +287,39 @@ zero_step_kernel(ZeroStepParams p) {
 // ---------------------------------------------------------------------------------------------
 // K-C3 (dense): out[s * shard_bytes ...] = shard of rank s, for every s (16-byte vectors).
 // ---------------------------------------------------------------------------------------------
+// Every thread keeps 8 independent 16-byte loads in flight: a peer read over NVLink has ~3x the latency of a local
+// HBM read, so bytes in flight — not SM count — set the bandwidth; a small grid (64 CTAs x 256 threads x 128 B = 2 MiB
+// in flight) sustains the link and leaves the SMs to the GEMMs this copy overlaps with.
 __global__ void __launch_bounds__(kCommThreads)
-peer_gather_kernel(PeerPtrs src, long long src_off_bytes, uint4* __restrict__ out, long long shard_vecs, int world) {
-  const long long total = shard_vecs * world;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int s = (int)(i / shard_vecs);
-    const long long j = i - (long long)s * shard_vecs;
-    out[i] = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(src.p[s]) + src_off_bytes)[j];
+peer_gather_kernel(PeerPtrs src, long long src_off_bytes, uint4* __restrict__ out, long long shard_vecs, int world, int skip) {
+  // skip >= 0: that rank's slot is left untouched (the caller reads its own shard in place); the copy then covers
+  // world - 1 shards, addressed through a compacted index
+  const int nsrc = skip >= 0 ? world - 1 : world;
+  const long long total = shard_vecs * nsrc;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  for (; i + 7 * stride < total; i += 8 * stride) {
+    uint4 v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const long long k = i + u * stride;
+      const int c = (int)(k / shard_vecs);
+      const int s = (skip >= 0 && c >= skip) ? c + 1 : c;
+      v[u] = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(src.p[s]) + src_off_bytes)[k - (long long)c * shard_vecs];
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const long long k = i + u * stride;
+      const int c = (int)(k / shard_vecs);
+      const int s = (skip >= 0 && c >= skip) ? c + 1 : c;
+      out[(long long)s * shard_vecs + (k - (long long)c * shard_vecs)] = v[u];
+    }
+  }
+  for (; i < total; i += stride) {
+    const int c = (int)(i / shard_vecs);
+    const int s = (skip >= 0 && c >= skip) ? c + 1 : c;
+    const long long j = i - (long long)c * shard_vecs;
+    out[(long long)s * shard_vecs + j] = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(src.p[s]) + src_off_bytes)[j];
   }
 }
 
@@ -349,16 +375,29 @@ B200_API int b200_zero_step(const b200_zero_step_args* a, void* stream) {
   return 0;
 }
 
-B200_API int b200_peer_gather(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
-                              int world, void* stream) {
-  if (world < 1 || world > kMaxRanks || shard_bytes % 16 || src_off_bytes % 16) return B200_ERR_BAD_SHAPE;
+static int peer_gather_launch(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
+                              int world, int skip, void* stream) {
+  if (world < 1 || world > kMaxRanks || shard_bytes % 16 || src_off_bytes % 16 || skip >= world) return B200_ERR_BAD_SHAPE;
   const long long vecs = shard_bytes / 16;
-  long long g = (vecs * world + kCommThreads - 1) / kCommThreads;
-  const int grid = (int)(g > kNumSMs * 4 ? kNumSMs * 4 : (g < 1 ? 1 : g));
+  const int nsrc = skip >= 0 ? world - 1 : world;
+  if (nsrc == 0) return 0;
+  long long g = (vecs * nsrc + kCommThreads - 1) / kCommThreads;
+  const int grid = (int)(g > 64 ? 64 : (g < 1 ? 1 : g));
   peer_gather_kernel<<<grid, kCommThreads, 0, (cudaStream_t)stream>>>(to_peers(src_ptrs, world), src_off_bytes,
-                                                                       (uint4*)out, vecs, world);
+                                                                       (uint4*)out, vecs, world, skip);
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+B200_API int b200_peer_gather(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
+                              int world, void* stream) {
+  return peer_gather_launch(src_ptrs, src_off_bytes, out, shard_bytes, world, -1, stream);
+}
+
+// Same, but rank `skip`'s slot of `out` is not written (the caller uses its own shard in place).
+B200_API int b200_peer_gather_skip(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
+                                   int world, int skip, void* stream) {
+  return peer_gather_launch(src_ptrs, src_off_bytes, out, shard_bytes, world, skip, stream);
 }
 
 B200_API int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int rank, unsigned int epoch,

@@ -250,6 +250,10 @@ typedef struct {
 int b200_zero_step(const b200_zero_step_args* args, void* stream);
 int b200_peer_gather(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
                      int world, void* stream);
+/* b200_peer_gather that leaves rank `skip`'s slot of `out` untouched (ZeRO-3 layer prefetch: the local shard is read
+ * in place, only the world - 1 remote shards cross NVLink). */
+int b200_peer_gather_skip(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
+                          int world, int skip, void* stream);
 int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int rank, unsigned int epoch,
                       void* stream);
 

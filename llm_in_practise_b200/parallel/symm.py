@@ -118,11 +118,12 @@ def peer_barrier(flags: PeerFlags, channel: int = 7) -> None:
     nv.count_launch()
 
 
-def peer_gather(src: SymmBuffer, out: torch.Tensor, src_off_bytes: int, shard_bytes: int) -> torch.Tensor:
-    """out = concat over ranks of src[r][off : off + shard_bytes]  (pull-based all-gather)."""
+def peer_gather(src: SymmBuffer, out: torch.Tensor, src_off_bytes: int, shard_bytes: int, skip: int = -1) -> torch.Tensor:
+    """out = concat over ranks of src[r][off : off + shard_bytes]  (pull-based all-gather); ``skip`` >= 0 leaves that
+    rank's slot of ``out`` untouched."""
     vp, i32, i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong
-    fn = nv.proto("b200_peer_gather", [vp, i64, vp, i64, i32, vp])
-    nv.check(fn(ctypes.cast(src.c_ptrs(), vp), src_off_bytes, nv.ptr(out), shard_bytes, src.world, nv.stream()), "peer_gather")
+    fn = nv.proto("b200_peer_gather_skip", [vp, i64, vp, i64, i32, i32, vp])
+    nv.check(fn(ctypes.cast(src.c_ptrs(), vp), src_off_bytes, nv.ptr(out), shard_bytes, src.world, skip, nv.stream()), "peer_gather")
     nv.count_launch()
     return out
 
