@@ -249,7 +249,13 @@ def load_or_train_bpe(path: str, texts_fn, vocab_size: int = 3000, rank: int = 0
 def load_pretrained_tokenizer(name_or_path: str, add_pad_token: bool = True):
     """``AutoTokenizer.from_pretrained`` for local files only (no network here); adds ``[PAD]`` if absent."""
     from transformers import AutoTokenizer
+    if os.path.isdir(name_or_path) and not any(os.path.exists(os.path.join(name_or_path, f)) for f in
+                                               ("tokenizer.json", "vocab.json", "vocab.txt", "tokenizer.model", "spiece.model")):
+        # transformers would build an EMPTY tokenizer of the config's model_type here (encode() -> [])
+        raise FileNotFoundError(f"no tokenizer files in {name_or_path}")
     tok = AutoTokenizer.from_pretrained(name_or_path, local_files_only=True, trust_remote_code=False)
+    if len(tok.encode("hello world")) == 0:
+        raise ValueError(f"tokenizer loaded from {name_or_path} has an empty vocabulary")
     if add_pad_token and tok.pad_token is None:
         if tok.eos_token is not None:
             tok.pad_token = tok.eos_token

@@ -38,6 +38,8 @@ def quantize_model(model: Qwen3ForCausalLM, batches: Sequence[torch.Tensor], qc:
         states.append([ew.embedding(ids.reshape(-1), model.embed_tokens), None, pos, B, S])
     smax = max((s[4] for s in states), default=1)
     cos, sin = model.rope(dev, smax)
+    if qc.method != "rtn" and not states:
+        raise ValueError(f"{qc.method} needs calibration data: every row was empty or shorter than 2 tokens")
     need_h = qc.method == "gptq"
     for li, layer in enumerate(model.layers):
         lins = layer.fused_linears()

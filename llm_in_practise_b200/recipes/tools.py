@@ -1,0 +1,147 @@
+"""Small command-line tools of the reference, one sub-command each:
+
+``python -m llm_in_practise_b200.recipes.tools <cmd> [...]``
+
+* ``merge``      merge a LoRA adapter into its base and save a plain HF checkpoint; auto-detects ``adapter_model.safetensors`` /
+                 ``peft_model.safetensors`` vs a full fine-tune (Scripts/fine-tuning/02-merge-lora-adapter-and-model.py:27-38,
+                 04-…-02.py:35-48; ``llamafactory-cli export`` in Fine-Tuning/LLaMA-Factory/README.md:240-246)
+* ``quantize``   GPTQ / AWQ / RTN W4A16 quantisation with the calibration recipe of the lesson: first 128 rows,
+                 ``instruction\\ninput\\noutput`` (Quantization/GPTQModel/quantize_qwen3_4b_gptq.py:16-48,
+                 Quantization/LLM-Compressor/{GPTQ,AWQ}/quantize_qwen3_4b_*.py, Quantization/LoRA-AWQ/quantize-…-awq.py)
+* ``eval-ppl``   the "self perplexity" check: greedy 256 tokens per prompt, mean chosen-token log-prob, pass bar 9.0 vs 8.19
+                 (Quantization/LLM-Compressor/*/eval_qwen3_4b_*.py:30-81)
+* ``convert-self-cognition``   JSONL -> Alpaca JSON with the per-language placeholder substitution
+                 (Fine-Tuning/LLaMA-Factory/convert_self_cognition_to_alpaca.py:4-48)
+* ``env``        device name, compute capability, CUDA / torch versions (HF_Basics/env_test.py)
+* ``loadtest``   the Locust profiles against an OpenAI-compatible endpoint (Deployment/Ray/scripts/locustfile*.py)
+* ``moderation`` the Llama-Guard moderation wrapper service (Deployment/litellm-proxy/llama-guard-wrapper/app.py)
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+
+def _calibration_rows(path, n):
+    """JSON / JSONL rows with instruction / input / output (alpaca-gpt4-data-zh layout); synthetic text if no file."""
+    rows = []
+    if path and os.path.exists(path):
+        with open(path, encoding="utf-8") as f:
+            txt = f.read().strip()
+        data = json.loads(txt) if txt.startswith("[") else [json.loads(ln) for ln in txt.splitlines() if ln.strip()]
+        for r in data:
+            instr = r.get("instruction") or r.get("prompt") or r.get("query") or ""
+            outp = r.get("output") or r.get("completion") or r.get("response") or r.get("text") or ""
+            t = (instr + "\n" + (r.get("input") or "") + "\n" + outp).strip() or " ".join(str(v) for v in r.values())
+            rows.append(t)
+    else:
+        from ..data.datasets import synthetic_corpus
+        rows = synthetic_corpus(max(8 * n, 1024), seed=1)
+    return [r for r in rows if len(r.strip()) >= 16]
+
+
+def main(argv=None):
+    ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
+    sub = ap.add_subparsers(dest="cmd", required=True)
+    m = sub.add_parser("merge")
+    m.add_argument("--base", required=True)
+    m.add_argument("--adapter", required=True)
+    m.add_argument("--out", required=True)
+    q = sub.add_parser("quantize")
+    q.add_argument("--model", required=True)
+    q.add_argument("--method", choices=["gptq", "awq", "rtn"], default="gptq")
+    q.add_argument("--frontend", choices=["gptqmodel", "llmcompressor"], default="llmcompressor")
+    q.add_argument("--scheme", default="W4A16")
+    q.add_argument("--out", required=True)
+    q.add_argument("--calib", default=None)
+    q.add_argument("--num_calibration_samples", type=int, default=128)
+    q.add_argument("--max_seq_length", type=int, default=2048)
+    e = sub.add_parser("eval-ppl")
+    e.add_argument("--model", required=True)
+    e.add_argument("--calib", default=None)
+    e.add_argument("--num_samples", type=int, default=128)
+    e.add_argument("--max_tokens", type=int, default=256)
+    c = sub.add_parser("convert-self-cognition")
+    c.add_argument("--input", default=None)
+    c.add_argument("--output", required=True)
+    sub.add_parser("env")
+    l = sub.add_parser("loadtest")
+    l.add_argument("rest", nargs=argparse.REMAINDER)
+    mod = sub.add_parser("moderation")
+    mod.add_argument("--port", type=int, default=int(os.getenv("WRAPPER_PORT", "8099")))
+    a = ap.parse_args(argv)
+
+    if a.cmd == "env":
+        print("torch", torch.__version__, "cuda", torch.version.cuda, "available", torch.cuda.is_available())
+        if torch.cuda.is_available():
+            for i in range(torch.cuda.device_count()):
+                p = torch.cuda.get_device_properties(i)
+                print(f"GPU {i}: {p.name}, sm_{p.major}{p.minor}, {p.total_memory / 2 ** 30:.0f} GiB, {p.multi_processor_count} SMs")
+        from ..ops import _native as nv
+        print("libb200ops:", nv.lib_path(), "present" if nv.available() else "NOT BUILT")
+        return
+    if a.cmd == "loadtest":
+        from ..serve.loadtest import main as lt
+        return lt(a.rest)
+    if a.cmd == "moderation":
+        import uvicorn
+        from ..serve.moderation import build_moderation_app
+        return uvicorn.run(build_moderation_app(), host="0.0.0.0", port=a.port, log_level="info")
+    if a.cmd == "convert-self-cognition":
+        from ..data.chat import convert_self_cognition_to_alpaca, load_self_cognition
+        rows = load_self_cognition(a.input, "{{NAME}}", "{{AUTHOR}}")
+        with open(a.output, "w", encoding="utf-8") as f:
+            json.dump(convert_self_cognition_to_alpaca(rows), f, ensure_ascii=False, indent=2)
+        print(f"{len(rows)} rows -> {a.output}")
+        return
+
+    from ..io.hf import from_pretrained, save_pretrained
+    from .infer import _load
+    if a.cmd == "merge":
+        has_adapter = any(os.path.exists(os.path.join(a.adapter, n)) for n in ("adapter_model.safetensors", "peft_model.safetensors", "adapter_model.bin"))
+        if not has_adapter:                       # a full fine-tune: nothing to merge, just re-save
+            model, tok = _load(a.adapter)
+        else:
+            model, tok = _load(a.base, a.adapter)
+            model = model.merge_and_unload()
+        save_pretrained(model, a.out, tokenizer=tok)
+        print("merged checkpoint written to", a.out)
+        return
+    if a.cmd == "quantize":
+        from ..quant import AWQModifier, GPTQModel, GPTQModifier, QuantizationModifier, QuantizeConfig, oneshot
+        model, tok = _load(a.model)
+        rows = _calibration_rows(a.calib, a.num_calibration_samples)[: a.num_calibration_samples]
+        if a.frontend == "gptqmodel":
+            gm = GPTQModel(model, QuantizeConfig(bits=4, group_size=128, desc_act=False, method=a.method), tok)
+            gm.quantize(rows, batch_size=1, max_seq_length=a.max_seq_length, progress=True)
+            gm.save(a.out)
+        else:
+            Mod = {"gptq": GPTQModifier, "awq": AWQModifier, "rtn": QuantizationModifier}[a.method]
+            oneshot(model=model, recipe=[Mod(targets="Linear", scheme=a.scheme, ignore=["lm_head"])], tokenizer=tok,
+                    dataset=[{"text": t} for t in rows], output_dir=a.out, max_seq_length=a.max_seq_length,
+                    num_calibration_samples=len(rows), progress=True)
+        if hasattr(tok, "save_pretrained"):
+            tok.save_pretrained(a.out)
+        print("quantised checkpoint written to", a.out)
+        return
+    if a.cmd == "eval-ppl":
+        from ..data.chat import build_messages, render_chatml
+        from ..inference import Generator
+        from ..quant import self_perplexity
+        model, tok = _load(a.model)
+        rows = _calibration_rows(a.calib, 2 * a.num_samples)[a.num_samples: 2 * a.num_samples]      # held-out rows [128:256]
+        dev = model.embed_tokens.device
+        prompts = [torch.tensor([tok.encode(render_chatml(build_messages(r.split("\n")[0]), add_generation_prompt=True, space_before_end=False))],
+                                device=dev) for r in rows]
+        eos = getattr(tok, "eos_token_id", None)
+        mean, std = self_perplexity(Generator(model, tok, 4096), prompts, a.max_tokens, [eos] if eos is not None else None)
+        print(f"self perplexity: {mean:.3f} ± {std:.3f}   (reference bar: unquantised ≈ 8.19, pass < 9.0)")
+        return mean
+
+
+if __name__ == "__main__":
+    main()

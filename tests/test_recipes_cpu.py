@@ -1,0 +1,63 @@
+"""Recipes: the pretraining runner under every strategy (2 gloo processes) and the tool sub-commands, on CPU."""
+import json
+import os
+
+import pytest
+import torch
+from dist_utils import run_distributed
+
+
+def _run(rank, world, strategy, tmp):
+    from llm_in_practise_b200.recipes.pretrain import PRESETS
+    from llm_in_practise_b200.train import PretrainConfig, run_pretraining
+    ds = None
+    if strategy.startswith("zero"):
+        ds = {"train_micro_batch_size_per_gpu": 4, "gradient_accumulation_steps": 1, "zero_optimization": {"stage": int(strategy[-1])},
+              "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "weight_decay": 0.0}}}
+        strategy = "zero"
+    cfg = PretrainConfig(strategy=strategy, ds_config=ds, tokenizer="byte", block_size=32, n_layer=2, n_head=2, d_model=32, dropout=0.0,
+                         epochs=2, batch_size=4, lr=1e-3, max_lines=120, log_every=0, save_dir=os.path.join(tmp, "ck"), val_fraction=0.1,
+                         clip_grad_norm=1.0, no_decay_groups=True)
+    out = run_pretraining(cfg)
+    h = out["history"]
+    assert len(h) == 2 and h[1]["train_loss"] < h[0]["train_loss"], h
+    if rank == 0:
+        json.dump([r["train_loss"] for r in h], open(os.path.join(tmp, "loss.json"), "w"))
+
+
+@pytest.mark.parametrize("strategy", ["ddp", "fsdp", "fsdp2", "zero2", "zero3"])
+def test_pretrain_strategies(strategy, tmp_path):
+    run_distributed(_run, 2, (strategy, str(tmp_path)))
+    assert os.path.exists(tmp_path / "loss.json")
+    assert os.listdir(tmp_path / "ck")
+
+
+def test_preset_table_is_consistent():
+    from dataclasses import fields
+    from llm_in_practise_b200.recipes.pretrain import PRESETS, build_parser
+    from llm_in_practise_b200.train import PretrainConfig
+    names = {f.name for f in fields(PretrainConfig)}
+    for k, v in PRESETS.items():
+        assert set(v) <= names, (k, set(v) - names)
+        PretrainConfig(**v)
+        if isinstance(v.get("ds_config"), str):
+            assert os.path.exists(v["ds_config"]), v["ds_config"]
+    a = build_parser().parse_args(["--recipe", "ddp_gpt_wikitext2", "--epochs", "1", "--n_head", "4", "--resume", "true"])
+    assert a.epochs == 1 and a.n_head == 4 and a.resume is True
+
+
+def test_tools_roundtrip(tmp_path):
+    from llm_in_practise_b200.io.hf import from_pretrained, save_pretrained
+    from llm_in_practise_b200.quant import detect_quant_format
+    from llm_in_practise_b200.recipes import finetune, infer, tools
+    d = str(tmp_path)
+    save_pretrained(from_pretrained("qwen3-tiny", dtype=torch.float32, device="cpu"), d + "/base")
+    finetune.main(["--recipe", "qwen3-8b-qlora", "--model", d + "/base", "--max_steps", "2", "--max_length", "48", "--output_dir", d + "/ft"])
+    assert os.path.exists(d + "/ft/adapter_model.safetensors")
+    tools.main(["merge", "--base", d + "/base", "--adapter", d + "/ft", "--out", d + "/merged"])
+    tools.main(["quantize", "--model", d + "/merged", "--method", "awq", "--out", d + "/awq", "--num_calibration_samples", "3",
+                "--max_seq_length", "48"])
+    assert detect_quant_format(d + "/awq") == "compressed-tensors"
+    ppl = tools.main(["eval-ppl", "--model", d + "/awq", "--num_samples", "2", "--max_tokens", "6"])
+    assert ppl == ppl and ppl > 1.0
+    infer.main(["once", "--model", d + "/awq", "--max_new_tokens", "4"])
