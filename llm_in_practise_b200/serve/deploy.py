@@ -1,0 +1,166 @@
+"""Deployment descriptions in the shape of the reference's Ray Serve LLM apps, served by this framework's own engine.
+
+Ray is not in the image, so ``LLMConfig`` / ``build_openai_app`` / ``load_serve_yaml`` accept the same dictionaries and
+YAML as ``ray.serve.llm`` (Deployment/Ray/serve_run_examples/deepseek.py:5-41,
+Deployment/Ray/serve_deploy_examples/*.yaml) and map them onto ``LLMEngine`` + the OpenAI-compatible FastAPI app:
+
+* ``model_loading_config``: ``model_id`` (served name) and ``model_source`` (checkpoint directory, GPTQ / AWQ
+  checkpoints are auto-detected — the "minimal AWQ" example);
+* ``engine_kwargs``: ``max_num_seqs``, ``max_model_len``, ``dtype``; ``tensor_parallel_size`` and ``pipeline_parallel_size``
+  must be 1 here (one engine per GPU; more GPUs = more replicas behind ``ReplicaRouter``), ``gpu_memory_utilization`` /
+  ``enable_prefix_caching`` / ``enable_chunked_prefill`` / ``enforce_eager`` are accepted and recorded;
+* ``deployment_config.autoscaling_config``: ``min_replicas`` / ``max_replicas`` / ``target_ongoing_requests`` drive
+  ``ReplicaRouter.desired_replicas`` (the decision rule; starting processes is the launcher's job);
+* several ``llm_configs`` / applications with different ``route_prefix`` give the "two models, two routes" layout.
+
+``cluster_healthcheck`` is the single-node analogue of Deployment/Ray/scripts/ray_cluster_healthcheck.py:31-176: CPU task
+fan-out, one ``nvidia-smi``-style probe per GPU, and a 16 MiB host<->device round trip per GPU.
+"""
+from __future__ import annotations
+
+import math
+import os
+import time
+from dataclasses import dataclass, field
+from typing import Any, Dict, List, Optional
+
+import torch
+
+
+@dataclass
+class LLMConfig:
+    model_loading_config: Dict[str, Any]
+    deployment_config: Dict[str, Any] = field(default_factory=dict)
+    engine_kwargs: Dict[str, Any] = field(default_factory=dict)
+    runtime_env: Dict[str, Any] = field(default_factory=dict)
+
+    @property
+    def model_id(self) -> str:
+        return self.model_loading_config["model_id"]
+
+    @property
+    def model_source(self) -> str:
+        return self.model_loading_config.get("model_source", self.model_id)
+
+    def autoscaling(self) -> Dict[str, Any]:
+        a = dict(self.deployment_config.get("autoscaling_config", {}))
+        a.setdefault("min_replicas", 1)
+        a.setdefault("max_replicas", a["min_replicas"])
+        a.setdefault("target_ongoing_requests", 5)
+        return a
+
+    def validate(self) -> None:
+        ek = self.engine_kwargs
+        if int(ek.get("tensor_parallel_size", 1)) != 1 or int(ek.get("pipeline_parallel_size", 1)) != 1:
+            raise NotImplementedError("one engine per GPU: scale with replicas (ReplicaRouter); TP/PP > 1 is not available in serve.deploy")
+
+
+class ReplicaRouter:
+    """Least-outstanding-requests choice among replicas + the Ray Serve autoscaling rule
+    ``ceil(total_ongoing / target_ongoing_requests)`` clamped to [min_replicas, max_replicas]."""
+
+    def __init__(self, engines: List[Any], autoscaling: Optional[Dict[str, Any]] = None):
+        self.engines = list(engines)
+        self.auto = autoscaling or {"min_replicas": 1, "max_replicas": len(self.engines), "target_ongoing_requests": 5}
+
+    def ongoing(self) -> List[int]:
+        return [e.num_running + e.num_waiting for e in self.engines]
+
+    def pick(self):
+        loads = self.ongoing()
+        return self.engines[loads.index(min(loads))]
+
+    def submit(self, prompt_ids, cfg=None):
+        return self.pick().submit(prompt_ids, cfg)
+
+    def desired_replicas(self) -> int:
+        want = math.ceil(sum(self.ongoing()) / max(1, self.auto["target_ongoing_requests"]))
+        return max(self.auto["min_replicas"], min(self.auto["max_replicas"], max(want, 1)))
+
+
+def build_engine(cfg: LLMConfig, device=None):
+    from ..recipes.infer import _load
+    from .engine import EngineArgs, LLMEngine
+    cfg.validate()
+    ek = cfg.engine_kwargs
+    dt = {"auto": torch.bfloat16, "bfloat16": torch.bfloat16, "half": torch.float16, "float16": torch.float16}[str(ek.get("dtype", "auto"))]
+    model, tok = _load(cfg.model_source, None, dt)
+    return LLMEngine(model, tok, EngineArgs(max_num_seqs=int(ek.get("max_num_seqs", 16)), max_model_len=int(ek.get("max_model_len", 4096))),
+                     model_name=cfg.model_id)
+
+
+def build_openai_app(args: Dict[str, Any], engines: Optional[Dict[str, Any]] = None):
+    """``{"llm_configs": [LLMConfig | dict, ...]}`` -> FastAPI app. With one config the API lives at ``/v1``; with several,
+    each model is also mounted under ``/<model_id>/v1`` and ``/v1/chat/completions`` dispatches on the ``model`` field."""
+    from fastapi import FastAPI, Request
+    from fastapi.responses import JSONResponse
+    from .openai_server import build_app
+    cfgs = [c if isinstance(c, LLMConfig) else LLMConfig(**c) for c in args["llm_configs"]]
+    engines = engines or {}
+    apps = {}
+    for c in cfgs:
+        eng = engines.get(c.model_id) or build_engine(c)
+        eng.start()
+        apps[c.model_id] = build_app(eng)
+    if len(apps) == 1:
+        return next(iter(apps.values()))
+    root = FastAPI(title="llm_in_practise_b200 multi-model")
+    for mid, sub in apps.items():
+        root.mount(f"/{mid}", sub)
+
+    @root.get("/v1/models")
+    def models():
+        return {"object": "list", "data": [{"id": m, "object": "model"} for m in apps]}
+
+    @root.middleware("http")
+    async def by_model(request: Request, call_next):
+        if request.url.path in ("/v1/chat/completions", "/v1/completions"):
+            body = await request.body()
+            import json
+            try:
+                mid = json.loads(body).get("model")
+            except Exception:
+                mid = None
+            if mid not in apps:
+                return JSONResponse(status_code=404, content={"error": f"unknown model {mid!r}; served: {list(apps)}"})
+            request.scope["path"] = f"/{mid}{request.url.path}"
+            request._body = body
+        return await call_next(request)
+    return root
+
+
+def load_serve_yaml(path: str) -> List[Dict[str, Any]]:
+    """Parse a ``serve deploy`` YAML: returns [{name, route_prefix, llm_configs: [LLMConfig]}]."""
+    import yaml
+    with open(path) as f:
+        doc = yaml.safe_load(f)
+    out = []
+    for app in doc.get("applications", []):
+        cfgs = [LLMConfig(**{k: v for k, v in c.items() if k in ("model_loading_config", "deployment_config", "engine_kwargs", "runtime_env")})
+                for c in app.get("args", {}).get("llm_configs", [])]
+        out.append({"name": app.get("name"), "route_prefix": app.get("route_prefix", "/"), "llm_configs": cfgs})
+    return out
+
+
+def cluster_healthcheck(cpu_tasks: int = 8, object_mib: int = 16) -> Dict[str, Any]:
+    from concurrent.futures import ThreadPoolExecutor
+    rep: Dict[str, Any] = {"host": os.uname().nodename, "cpus": os.cpu_count()}
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(cpu_tasks) as ex:
+        rep["cpu_probe"] = sum(ex.map(lambda i: sum(j * j for j in range(20000)) > 0, range(cpu_tasks)))
+    rep["cpu_probe_s"] = time.perf_counter() - t0
+    gpus = []
+    if torch.cuda.is_available():
+        for i in range(torch.cuda.device_count()):
+            p = torch.cuda.get_device_properties(i)
+            free, total = torch.cuda.mem_get_info(i)
+            buf = torch.empty(object_mib << 20, dtype=torch.uint8).pin_memory()
+            torch.cuda.synchronize(i)
+            t0 = time.perf_counter()
+            back = buf.to(f"cuda:{i}", non_blocking=True).cpu()
+            dt = time.perf_counter() - t0
+            gpus.append({"index": i, "name": p.name, "sm": f"{p.major}.{p.minor}", "memory_free_gib": free / 2 ** 30, "memory_total_gib": total / 2 ** 30,
+                         "roundtrip_ok": bool(back.numel() == buf.numel()), "roundtrip_gbs": 2 * buf.numel() / dt / 1e9})
+    rep["gpus"] = gpus
+    rep["healthy"] = rep["cpu_probe"] == cpu_tasks and all(g["roundtrip_ok"] for g in gpus)
+    return rep

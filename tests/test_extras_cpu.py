@@ -1,0 +1,93 @@
+"""Classic-ML projects and the Ray-Serve-shaped deployment layer, on CPU."""
+import textwrap
+
+import numpy as np
+import torch
+from fastapi.testclient import TestClient
+
+
+def test_fault_prediction_pipeline_and_service():
+    from llm_in_practise_b200.extras import classic_ml as M
+    df = M.generate_system_metrics(1500)
+    assert abs(df["label"].mean() - 0.05) < 0.01 and set(df["device_id"]) == {"server_001", "server_002"}
+    d, feats = M.extract_features(df)
+    assert feats == M.FAULT_FEATURES and d["cpu_usage_mean"].notna().all()
+    Xb, yb = M.smote(np.random.rand(100, 3), np.array([0] * 90 + [1] * 10))
+    assert (yb == 0).sum() == (yb == 1).sum() == 90
+    out = M.train_fault_model(df, n_iter=2, cv=2)
+    assert out["auc"] > 0.95
+    c = TestClient(M.build_fault_app(out["model"], out["scaler"]))
+    assert c.get("/health").json() == {"status": "healthy"}
+    bad = {"cpu_usage": 97, "ram_usage": 92, "disk_io": 20, "temperature": 48, "error_count": 15, "timestamp": "2025-07-12 08:00:00", "device_id": "server_001"}
+    r = c.post("/predict_fault", json=bad).json()
+    assert r["is_fault_predicted"] and r["fault_probability"] > 0.5 and set(r["feature_importance"]) == set(feats)
+    ok = dict(bad, cpu_usage=50, ram_usage=60, temperature=40, error_count=2)
+    assert not c.post("/predict_fault", json=ok).json()["is_fault_predicted"]
+
+
+def test_rca_pipeline_and_service(tmp_path):
+    from llm_in_practise_b200.extras import classic_ml as M
+    cfgp = tmp_path / "config.yaml"
+    cfgp.write_text(textwrap.dedent("""
+        data: {features: [cpu_usage, memory_usage, disk_io, network_latency], target: failure_cause}
+        model: {type: random_forest, params: {n_estimators: 30, random_state: 42}}
+        anomaly_detection: {contamination: 0.1}
+    """))
+    out = M.run_rca_pipeline(str(cfgp))
+    assert out["accuracy"] > 0.9 and 0.05 < out["data"]["anomaly"].mean() < 0.15 and len(out["importance"]) == 4
+    c = TestClient(M.build_rca_app(out["model"], out["scaler"], out["features"]))
+    r = c.post("/predict", json={"cpu_usage": 90, "memory_usage": 50, "disk_io": 30, "network_latency": 20}).json()
+    assert r["failure_cause"] == "cpu_overload"
+    b = c.post("/batch_predict", json={"metrics": [{"cpu_usage": 40, "memory_usage": 95, "disk_io": 30, "network_latency": 20}] * 2}).json()
+    assert [p["failure_cause"] for p in b["predictions"]] == ["memory_leak"] * 2
+    assert c.get("/health").json()["status"] == "healthy"
+
+
+def test_deploy_layer(tmp_path):
+    from llm_in_practise_b200.data.tokenizers import ByteTokenizer
+    from llm_in_practise_b200.models.qwen3 import QWEN3_PRESETS, Qwen3ForCausalLM
+    from llm_in_practise_b200.serve import EngineArgs, LLMEngine
+    from llm_in_practise_b200.serve.deploy import LLMConfig, ReplicaRouter, build_openai_app, cluster_healthcheck, load_serve_yaml
+    y = tmp_path / "app.yaml"
+    y.write_text(textwrap.dedent("""
+        applications:
+          - name: qwen3_app
+            route_prefix: /
+            import_path: ray.serve.llm:build_openai_app
+            args:
+              llm_configs:
+                - model_loading_config: {model_id: qwen3, model_source: /models/q}
+                  deployment_config: {autoscaling_config: {min_replicas: 1, max_replicas: 4, target_ongoing_requests: 5}}
+                  engine_kwargs: {tensor_parallel_size: 1, pipeline_parallel_size: 2, max_model_len: 4096}
+    """))
+    apps = load_serve_yaml(str(y))
+    cfg = apps[0]["llm_configs"][0]
+    assert cfg.model_id == "qwen3" and cfg.autoscaling()["max_replicas"] == 4
+    try:
+        cfg.validate()
+        raise AssertionError("pipeline_parallel_size 2 must be rejected")
+    except NotImplementedError:
+        pass
+    torch.manual_seed(0)
+    m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32, device="cpu")
+    e1, e2 = (LLMEngine(m, ByteTokenizer(), EngineArgs(max_num_seqs=2, max_model_len=64), model_name=n) for n in ("a", "b"))
+    router = ReplicaRouter([e1, e2], {"min_replicas": 1, "max_replicas": 4, "target_ongoing_requests": 5})
+    for _ in range(12):
+        router.submit([1, 2, 3])
+    assert router.ongoing() == [6, 6] and router.desired_replicas() == 3
+    for e in (e1, e2):
+        e.waiting.clear()
+    app = build_openai_app({"llm_configs": [LLMConfig({"model_id": "a"}), LLMConfig({"model_id": "b"})]}, engines={"a": e1, "b": e2})
+    c = TestClient(app)
+    try:
+        body = {"model": "b", "messages": [{"role": "user", "content": "hi"}], "max_tokens": 3, "temperature": 0}
+        r = c.post("/v1/chat/completions", json=body)
+        assert r.status_code == 200 and r.json()["model"] == "b"
+        assert c.post("/a/v1/chat/completions", json=dict(body, model="a")).status_code == 200
+        assert c.post("/v1/chat/completions", json=dict(body, model="zzz")).status_code == 404
+        assert {d["id"] for d in c.get("/v1/models").json()["data"]} == {"a", "b"}
+    finally:
+        e1.shutdown()
+        e2.shutdown()
+    h = cluster_healthcheck(4, 1)
+    assert h["healthy"] and h["cpu_probe"] == 4
