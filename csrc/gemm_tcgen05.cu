@@ -52,7 +52,7 @@ struct GemmKernelParams {
   // stream-K: every unit gets an equal contiguous range of (tile, k-block) work items; a tile that is
   // split between units is summed through `sk_ws` (one fp32 128 x 256 slot per CTA) by the unit
   // that owns the tile's first k-block, after the others published their partial (sk_flags = epoch).
-  int stream_k;
+  int stream_k, sk_group;
   float* sk_ws;
   unsigned int* sk_flags;
   unsigned int sk_epoch;
@@ -93,7 +93,7 @@ struct Segment {
 // Iterates the segments of one unit, identically in the producer, MMA and epilogue roles.
 struct SegmentIter {
   long long item, end;  // stream-K: current / last work item of this unit
-  int tile, stride, total_tiles, nkt;
+  int tile, stride, total_tiles, nkt, grp_size, member;
   bool stream_k;
   __device__ SegmentIter(const GemmKernelParams& p, int unit, int nunits, int total_tiles_, int nkt_) {
     stream_k = p.stream_k != 0;
@@ -101,9 +101,20 @@ struct SegmentIter {
     nkt = nkt_;
     tile = unit;
     stride = nunits;
-    const long long total = (long long)total_tiles_ * nkt_;
-    item = total * unit / nunits;
-    end = total * (unit + 1) / nunits;
+    // stream-K work space = (panel, k-block), a panel being the sk_group M-tiles that share one B panel. The units
+    // form groups of sk_group members: a group walks one contiguous (panel, k) range and member j computes M-tile j
+    // of it, so the members read the same B tiles at the same time (one DRAM fetch, sk_group - 1 L2 hits). With
+    // sk_group = 1 this is plain per-tile stream-K.
+    grp_size = p.stream_k ? p.sk_group : 1;
+    member = unit % grp_size;
+    const int ngroups = nunits / grp_size, grp = unit / grp_size;
+    const long long total = (long long)(total_tiles_ / grp_size) * nkt_;
+    if (grp < ngroups) {
+      item = total * grp / ngroups;
+      end = total * (grp + 1) / ngroups;
+    } else {
+      item = end = 0;   // spare units beyond the last whole group
+    }
   }
   __device__ bool next(Segment& s) {
     if (!stream_k) {
@@ -113,8 +124,9 @@ struct SegmentIter {
       return true;
     }
     if (item >= end) return false;
-    s.tile = (int)(item / nkt);
-    s.kb0 = (int)(item - (long long)s.tile * nkt);
+    const int panel = (int)(item / nkt);
+    s.tile = panel * grp_size + member;
+    s.kb0 = (int)(item - (long long)panel * nkt);
     const long long left = end - item;
     s.kb1 = (long long)(nkt - s.kb0) <= left ? nkt : s.kb0 + (int)left;
     item += s.kb1 - s.kb0;
@@ -543,7 +555,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     uint32_t acc_phase = 0;
     SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
     Segment sg;
-    const long long sk_total = (long long)total_tiles * num_k_total;
+    const int sk_g = p.stream_k ? p.sk_group : 1;
+    const int sk_groups = nunits / sk_g, sk_grp = unit / sk_g;
+    const long long sk_total = (long long)(total_tiles / sk_g) * num_k_total;
     while (it.next(sg)) {
       const int tile = sg.tile;
       const int bt = tile / tiles_per_batch;
@@ -578,16 +592,16 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         // number of following units that hold later k-blocks of this tile (0 unless stream-K split it)
         int ncontrib = 0;
         if (sg.kb1 < num_k_total) {
-          const long long tile_end = (long long)(tile + 1) * num_k_total;
-          for (int v = unit + 1; v < nunits && sk_total * v / nunits < tile_end; ++v) ++ncontrib;
+          const long long tile_end = (long long)(tile / sk_g + 1) * num_k_total;
+          for (int v = sk_grp + 1; v < sk_groups && sk_total * v / sk_groups < tile_end; ++v) ++ncontrib;
           for (int v = 1; v <= ncontrib; ++v) {
-            const unsigned int* f = p.sk_flags + (unit + v) * CTAS + rank;
+            const unsigned int* f = p.sk_flags + (unit + v * sk_g) * CTAS + rank;   // same member of the next group
             unsigned int seen;
             const long long tw = clock64();
             do {
               asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
               if (clock64() - tw > 20000000000ll) {
-                printf("b200 gemm: stream-K wait timed out (block %d waits for block %d)\n", blockIdx.x, (unit + v) * CTAS + (int)rank);
+                printf("b200 gemm: stream-K wait timed out (block %d waits for block %d)\n", blockIdx.x, (unit + v * sk_g) * CTAS + (int)rank);
                 __trap();
               }
             } while (seen != p.sk_epoch);
@@ -600,7 +614,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         tmem_ld_32x32(t0 + c * 32, r);
         tmem_ld_wait();
         for (int v = 1; v <= ncontrib; ++v) {
-          const float* slot = p.sk_ws + ((long long)((unit + v) * CTAS + rank) * kBM + (q * 32 + lane)) * kAccStride + c * 32;
+          const float* slot = p.sk_ws + ((long long)((unit + v * sk_g) * CTAS + rank) * kBM + (q * 32 + lane)) * kAccStride + c * 32;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
             const float4 w = reinterpret_cast<const float4*>(slot)[j];
@@ -795,8 +809,13 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   p.num_m = ceil_div(a->M, kBM * ctas);
   p.num_n = ceil_div(a->N, p.bn);
   p.stream_k = cfg.stream_k;
+  p.sk_group = 1;
   p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0;
   if (cfg.stream_k) {
+    // lock-step groups when the M-tiles of a panel fit a group and at most ~5 % of the units are left without one
+    const int units_sk = g_num_sms / ctas;
+    if (p.num_m > 1 && p.num_m <= units_sk && (units_sk % p.num_m) * 20 <= units_sk && !getenv("B200_GEMM_SK_FLAT"))
+      p.sk_group = p.num_m;
     static unsigned int epoch = 0;
     p.sk_ws = reinterpret_cast<float*>(a->workspace);
     p.sk_flags = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(a->workspace) +
@@ -913,6 +932,7 @@ B200_API int b200_gemm_w4(const b200_gemm_args* a, const b200_w4_desc* w, void* 
   const long long waves = (tiles + units - 1) / units;
   const double classic = (double)waves * nkt, sk = (double)tiles * nkt / units + 10.0;
   p.stream_k = (allow_sk && tiles % units != 0 && tiles * nkt >= 4ll * units && waves <= 4 && sk < classic * 0.85) ? 1 : 0;
+  p.sk_group = 1;
   p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0;
   if (p.stream_k) {
     static unsigned int epoch = 0x40000000u;   // own epoch space: flags are shared with b200_gemm's workspace
