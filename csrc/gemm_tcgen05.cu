@@ -824,7 +824,9 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   }
   const int stage_bytes = kStageABytes + bn_cta * 128;
   int stages = (g_max_smem - 2048) / stage_bytes;
-  if (stages > 8) stages = 8;
+  // 6 stages sustain the pipe (5..7 measure the same); the 32 KB left free let bandwidth-bound kernels of other streams
+  // (the next weight's dequant, the ZeRO-3 shard pull) co-reside with the persistent GEMM CTAs
+  if (stages > 6) stages = 6;
   { const char* e = getenv("B200_GEMM_STAGES"); if (e && atoi(e) >= 2 && atoi(e) < stages) stages = atoi(e); }
   if (stages < 2) return B200_ERR_UNSUPPORTED;
   p.stages = stages;
