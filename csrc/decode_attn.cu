@@ -13,6 +13,23 @@
 
 namespace b200 {
 
+// PER consecutive elements -> fp32, as one vector load when PER * sizeof(T) is 4, 8 or 16 bytes
+template <typename T, int PER>
+__device__ __forceinline__ void load_row(const T* __restrict__ p, float (&out)[PER]) {
+  constexpr int BYTES = PER * (int)sizeof(T);
+  if constexpr (BYTES == 16 || BYTES == 8 || BYTES == 4) {
+    union { uint4 v16; uint2 v8; uint32_t v4; T e[16 / sizeof(T)]; } u;
+    if constexpr (BYTES == 16) u.v16 = *reinterpret_cast<const uint4*>(p);
+    else if constexpr (BYTES == 8) u.v8 = *reinterpret_cast<const uint2*>(p);
+    else u.v4 = *reinterpret_cast<const uint32_t*>(p);
+#pragma unroll
+    for (int i = 0; i < PER; ++i) out[i] = to_f32<T>(u.e[i]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < PER; ++i) out[i] = to_f32<T>(p[i]);
+  }
+}
+
 // qkv: [B, (H + 2 Hkv) * D] (post-RoPE) for the new token; cache_k / cache_v: [B, Hkv, max_len, D];
 // pos[b] = index the new token is written at (= number of tokens already cached); slots[b] (optional) = cache row
 // of batch row b; out: [B, H * D]
@@ -48,30 +65,46 @@ decode_attn_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __rest
   for (int i = 0; i < PER; ++i) acc[i] = 0.f;
   int t0 = 0;
   if (window > 0 && t_new + 1 > window) t0 = t_new + 1 - window;
-  for (int t = t0 + warp; t <= t_new; t += 4) {
-    float kx[PER], vx[PER];
-    if (t == t_new) {
+  // Each warp takes blocks of 8 consecutive positions: 16 independent vector loads in flight per lane (the loop is
+  // latency-bound otherwise: one 8-byte load and a 5-step shuffle reduction per position), one softmax rescale per block.
+  constexpr int UN = 8;
+  const T* knew = qkv + row + (long long)(H + kvh) * D + lane * PER;
+  const T* vnew = qkv + row + (long long)(H + Hkv + kvh) * D + lane * PER;
+  for (int tb = t0 + warp * UN; tb <= t_new; tb += 4 * UN) {
+    float kx[UN][PER], vx[UN][PER], sc[UN];
 #pragma unroll
-      for (int i = 0; i < PER; ++i) {
-        kx[i] = to_f32<T>(qkv[row + (long long)(H + kvh) * D + lane * PER + i]);
-        vx[i] = to_f32<T>(qkv[row + (long long)(H + Hkv + kvh) * D + lane * PER + i]);
-      }
-    } else {
+    for (int u = 0; u < UN; ++u) {
+      const int t = tb + u;
+      if (t <= t_new) {
+        load_row<T, PER>(t == t_new ? knew : kc + (long long)t * D + lane * PER, kx[u]);
+        load_row<T, PER>(t == t_new ? vnew : vc + (long long)t * D + lane * PER, vx[u]);
+      } else {
 #pragma unroll
-      for (int i = 0; i < PER; ++i) {
-        kx[i] = to_f32<T>(kc[(long long)t * D + lane * PER + i]);
-        vx[i] = to_f32<T>(vc[(long long)t * D + lane * PER + i]);
+        for (int i = 0; i < PER; ++i) { kx[u][i] = 0.f; vx[u][i] = 0.f; }
       }
     }
-    float s = 0.f;
+    float bm = -INFINITY;
 #pragma unroll
-    for (int i = 0; i < PER; ++i) s += q[i] * kx[i];
-    s = warp_sum(s);
-    const float mn = fmaxf(m, s);
-    const float c = __expf(m - mn), p = __expf(s - mn);
-    l = l * c + p;
+    for (int u = 0; u < UN; ++u) {
+      float d = 0.f;
 #pragma unroll
-    for (int i = 0; i < PER; ++i) acc[i] = acc[i] * c + p * vx[i];
+      for (int i = 0; i < PER; ++i) d += q[i] * kx[u][i];
+      d = warp_sum(d);
+      sc[u] = (tb + u <= t_new) ? d : -INFINITY;
+      bm = fmaxf(bm, sc[u]);
+    }
+    const float mn = fmaxf(m, bm);
+    const float c = __expf(m - mn);
+    l *= c;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) acc[i] *= c;
+#pragma unroll
+    for (int u = 0; u < UN; ++u) {
+      const float pr = __expf(sc[u] - mn);      // exp(-inf) = 0 for the padded tail
+      l += pr;
+#pragma unroll
+      for (int i = 0; i < PER; ++i) acc[i] += pr * vx[u][i];
+    }
     m = mn;
   }
   __shared__ float sm[4], sl[4], sacc[4][D];

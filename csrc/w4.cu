@@ -161,6 +161,133 @@ w4_dequant_t_kernel(W4Shards sh, T* __restrict__ out, long long N, int K, int gr
   }
 }
 
+// Decode GEMV on the tensor cores: y[m, n] = sum_k x[m, k] * w[n, k] for M <= 8 tokens, reading the weights once at
+// 4 bits. A CTA owns 16 output rows; its 8 warps take interleaved 128-wide k chunks and each issues
+// mma.sync.m16n8k16 with the 16 weight rows as the A operand and the (<= 8) tokens as the 8-wide B operand, so the
+// per-token cost is hidden inside the MMA instead of multiplying the ALU and shared-memory work by M. The k index
+// of a tensor-core dot product may be permuted freely as long as A and B agree, which lets every lane fetch its
+// operands as whole 16-byte vectors: lane (g, t) loads the 32 consecutive weights [k + 32t, k + 32t + 32) of rows g and
+// g + 8 (16 packed bytes each) and the same 32 activations of token g, and MMA j of the chunk consumes elements
+// 4j .. 4j+3 of those. Codes become 16-bit pairs through a byte -> (lut[hi], lut[lo]) table kept once per lane in shared
+// memory (bank = lane: conflict-free for any byte values), scaled by one packed FMA. Memory-bound by construction:
+// 0.5 B per weight from HBM, x from L1.
+template <bool BF16>
+__global__ void __launch_bounds__(256)
+w4_gemv_mma_kernel(const uint16_t* __restrict__ x, const uint8_t* __restrict__ packed, const float* __restrict__ scale,
+                   const float* __restrict__ zsp, const float* __restrict__ lut_g, const uint16_t* __restrict__ bias,
+                   uint16_t* __restrict__ y, int M, long long N, int K, int group, long long x_rs, long long y_rs) {
+  __shared__ uint32_t table[256 * 32];
+  __shared__ float red[8][128];
+  for (int i = threadIdx.x; i < 256 * 32; i += 256) {
+    const int byte = i >> 5;
+    const float lo = lut_g ? lut_g[byte >> 4] : kNF4[byte >> 4];
+    const float hi = lut_g ? lut_g[byte & 15] : kNF4[byte & 15];
+    uint32_t v;
+    if (BF16) v = pack_bf16x2(lo, hi);
+    else { const __half2 h = __floats2half2_rn(lo, hi); v = *reinterpret_cast<const uint32_t*>(&h); }
+    table[i] = v;
+  }
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int gpr = K / group;
+  const uint32_t* tl = table + lane;
+  const int nchunks = K / 128;
+  const long long ntiles = (N + 15) / 16;
+  // persistent over 16-row tiles (the table is built once per CTA); the next chunk's codes and scales are fetched while
+  // the current chunk goes through the table and the tensor core
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long row0 = tile * 16;
+    const long long rA = min(row0 + g, N - 1), rB = min(row0 + g + 8, N - 1);
+    float c[4] = {0.f, 0.f, 0.f, 0.f};
+    uint4 wa, wb;
+    float sa, sb, za, zb;
+    auto fetch = [&](int ch, uint4& a_, uint4& b_, float& sa_, float& sb_, float& za_, float& zb_) {
+      const int k = ch * 128 + t * 32;
+      a_ = __ldg(reinterpret_cast<const uint4*>(packed + rA * (K / 2) + k / 2));
+      b_ = __ldg(reinterpret_cast<const uint4*>(packed + rB * (K / 2) + k / 2));
+      sa_ = __ldg(scale + rA * gpr + k / group);
+      sb_ = __ldg(scale + rB * gpr + k / group);
+      za_ = zsp ? __ldg(zsp + rA * gpr + k / group) : 0.f;
+      zb_ = zsp ? __ldg(zsp + rB * gpr + k / group) : 0.f;
+    };
+    if (warp < nchunks) fetch(warp, wa, wb, sa, sb, za, zb);
+    for (int ch = warp; ch < nchunks; ch += 8) {
+      const int k = ch * 128 + t * 32;
+      const uint4 cwa = wa, cwb = wb;
+      const float csa = sa, csb = sb, cza = za, czb = zb;
+      if (ch + 8 < nchunks) fetch(ch + 8, wa, wb, sa, sb, za, zb);
+      uint32_t xw[16];
+      if (g < M) {
+        const uint4* xp = reinterpret_cast<const uint4*>(x + (long long)g * x_rs + k);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 v = __ldg(xp + i);
+          xw[4 * i] = v.x; xw[4 * i + 1] = v.y; xw[4 * i + 2] = v.z; xw[4 * i + 3] = v.w;
+        }
+      } else {
+#pragma unroll
+        for (int i = 0; i < 16; ++i) xw[i] = 0u;
+      }
+      uint32_t sa2, sb2, za2, zb2;
+      if (BF16) { sa2 = pack_bf16x2(csa, csa); sb2 = pack_bf16x2(csb, csb); za2 = pack_bf16x2(-cza, -cza); zb2 = pack_bf16x2(-czb, -czb); }
+      else {
+        __half2 h;
+        h = __floats2half2_rn(csa, csa); sa2 = *reinterpret_cast<uint32_t*>(&h);
+        h = __floats2half2_rn(csb, csb); sb2 = *reinterpret_cast<uint32_t*>(&h);
+        h = __floats2half2_rn(-cza, -cza); za2 = *reinterpret_cast<uint32_t*>(&h);
+        h = __floats2half2_rn(-czb, -czb); zb2 = *reinterpret_cast<uint32_t*>(&h);
+      }
+      const uint32_t wA[4] = {cwa.x, cwa.y, cwa.z, cwa.w}, wB[4] = {cwb.x, cwb.y, cwb.z, cwb.w};
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        // bytes 2j and 2j+1 of the lane's 16 packed bytes = elements 4j .. 4j+3
+        const uint32_t ba0 = (wA[j >> 1] >> ((j & 1) * 16)) & 0xFFu, ba1 = (wA[j >> 1] >> ((j & 1) * 16 + 8)) & 0xFFu;
+        const uint32_t bb0 = (wB[j >> 1] >> ((j & 1) * 16)) & 0xFFu, bb1 = (wB[j >> 1] >> ((j & 1) * 16 + 8)) & 0xFFu;
+        uint32_t a0 = tl[ba0 << 5], a2 = tl[ba1 << 5], a1 = tl[bb0 << 5], a3 = tl[bb1 << 5];
+        if (BF16) {
+          asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(a0) : "r"(a0), "r"(sa2), "r"(za2));
+          asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(a2) : "r"(a2), "r"(sa2), "r"(za2));
+          asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(a1) : "r"(a1), "r"(sb2), "r"(zb2));
+          asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(a3) : "r"(a3), "r"(sb2), "r"(zb2));
+          asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(xw[2 * j]), "r"(xw[2 * j + 1]));
+        } else {
+          asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(a0) : "r"(a0), "r"(sa2), "r"(za2));
+          asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(a2) : "r"(a2), "r"(sa2), "r"(za2));
+          asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(a1) : "r"(a1), "r"(sb2), "r"(zb2));
+          asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(a3) : "r"(a3), "r"(sb2), "r"(zb2));
+          asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                       : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                       : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(xw[2 * j]), "r"(xw[2 * j + 1]));
+        }
+      }
+    }
+    // c0: (row g, token 2t), c1: (row g, token 2t+1), c2: (row g+8, token 2t), c3: (row g+8, token 2t+1)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) red[warp][lane * 4 + i] = c[i];
+    __syncthreads();
+    if (threadIdx.x < 128) {
+      float s = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x];
+      const int ln = threadIdx.x >> 2, i = threadIdx.x & 3;
+      const long long row = row0 + (ln >> 2) + ((i & 2) ? 8 : 0);
+      const int tok = 2 * (ln & 3) + (i & 1);
+      if (row < N && tok < M) {
+        if (bias) s += BF16 ? __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(bias + row))
+                            : __half2float(*reinterpret_cast<const __half*>(bias + row));
+        uint16_t o;
+        if (BF16) { const __nv_bfloat16 b = __float2bfloat16_rn(s); o = *reinterpret_cast<const uint16_t*>(&b); }
+        else { const __half h = __float2half_rn(s); o = *reinterpret_cast<const uint16_t*>(&h); }
+        y[(long long)tok * y_rs + row] = o;
+      }
+    }
+    __syncthreads();   // `red` is reused by the next tile
+  }
+}
+
 // y[m, n] = sum_k x[m, k] * w[n, k] for m < M <= 8: one warp per output column n.
 template <typename T, int kMaxM>
 __global__ void __launch_bounds__(256)
@@ -299,6 +426,17 @@ B200_API int b200_w4_gemv(const void* x, const uint8_t* packed, const float* sca
                           const void* bias, void* y, int M, long long N, int K, int group, long long x_rs,
                           long long y_rs, int dtype, void* stream) {
   if (M < 1 || M > 8 || K % 32 || group % 32 || K % group || x_rs % 8) return B200_ERR_BAD_SHAPE;
+  if (K % 128 == 0 && (dtype == B200_DT_BF16 || dtype == B200_DT_FP16) && !getenv("B200_W4_GEMV_SIMT")) {
+    const long long tiles16 = (N + 15) / 16;
+    const unsigned g16 = (unsigned)(tiles16 < kNumSMs * 4 ? tiles16 : kNumSMs * 4);
+    cudaStream_t s2 = (cudaStream_t)stream;
+    if (dtype == B200_DT_BF16)
+      w4_gemv_mma_kernel<true><<<g16, 256, 0, s2>>>((const uint16_t*)x, packed, scale, zs, lut, (const uint16_t*)bias, (uint16_t*)y, M, N, K, group, x_rs, y_rs);
+    else
+      w4_gemv_mma_kernel<false><<<g16, 256, 0, s2>>>((const uint16_t*)x, packed, scale, zs, lut, (const uint16_t*)bias, (uint16_t*)y, M, N, K, group, x_rs, y_rs);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
   const int smem = M * K * 2;
   if (smem > 200 * 1024) return B200_ERR_TOO_LARGE;
   const int tb = 256, wpb = tb / 32;

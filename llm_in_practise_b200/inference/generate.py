@@ -104,6 +104,8 @@ class Generator:
         self.tok = tokenizer
         self.max_len = max_len
         self.cfg = self.model.config
+        self._graphs = {}
+        self._caches = {}
 
     @torch.no_grad()
     def _prefill(self, ids: torch.Tensor, cache: KVCache, slots: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -154,6 +156,37 @@ class Generator:
         return gemm(h, m.head_weight(), out_dtype=torch.float32)
 
     @torch.no_grad()
+    def decode_graphed(self, tok: torch.Tensor, cache: KVCache, pos: torch.Tensor, slots: torch.Tensor) -> torch.Tensor:
+        """``_decode`` replayed from a CUDA graph (one per batch size and cache): a decode step is ~14 launches per
+        layer of a few microseconds each, so eager execution is bound by the Python launch rate, not by the GPU. The
+        kernels read token ids, positions and cache slots from device tensors, so one graph serves any set of
+        sequences. Falls back to the eager path on CPU, under tensor parallelism (the peer all-reduce takes a host
+        epoch) and for batches above 8 rows (those go through the multi-stream dequant pipeline)."""
+        B = tok.shape[0]
+        L = cache.len                                   # ``cache.len`` is the caller's to advance, never this method's
+        if not tok.is_cuda or B > 8 or getattr(self.model, "tp", None) is not None and self.model.tp.world > 1:
+            out = self._decode(tok, cache, pos, slots)
+            cache.len = L
+            return out
+        key = (B, id(cache))
+        g = self._graphs.get(key)
+        if g is None:
+            st = {"tok": tok.clone(), "pos": pos.clone(), "slots": slots.clone()}
+            self._decode(st["tok"], cache, st["pos"], st["slots"])          # warm-up: allocates every lazily built buffer
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph):
+                st["logits"] = self._decode(st["tok"], cache, st["pos"], st["slots"])
+            g = self._graphs[key] = (graph, st)
+            cache.len = L
+        graph, st = g
+        st["tok"].copy_(tok)
+        st["pos"].copy_(pos)
+        st["slots"].copy_(slots)
+        graph.replay()
+        return st["logits"]
+
+    @torch.no_grad()
     def generate(self, input_ids: torch.Tensor, config: Optional[GenerationConfig] = None, streamer=None,
                  seed: Optional[int] = None, return_logprobs: bool = False, **kw):
         cfg = config or GenerationConfig(**{k: v for k, v in kw.items() if k in GenerationConfig.__dataclass_fields__})
@@ -164,10 +197,21 @@ class Generator:
         B, S = input_ids.shape
         dev = input_ids.device
         total = min(self.max_len, S + cfg.max_new_tokens)
-        cache = KVCache(self.cfg.num_hidden_layers, B, self.cfg.num_key_value_heads, total, self.cfg.head_dim,
-                        self.model.embed_tokens.dtype, dev)
+        if input_ids.is_cuda and B <= 8:
+            # one persistent full-length cache per batch size: its CUDA graph (which bakes the addresses in) is reused
+            cache = self._caches.get(B)
+            if cache is None:
+                cache = self._caches[B] = KVCache(self.cfg.num_hidden_layers, B, self.cfg.num_key_value_heads, self.max_len,
+                                                  self.cfg.head_dim, self.model.embed_tokens.dtype, dev)
+        else:
+            cache = KVCache(self.cfg.num_hidden_layers, B, self.cfg.num_key_value_heads, total, self.cfg.head_dim,
+                            self.model.embed_tokens.dtype, dev)
         gen = torch.Generator(device=dev).manual_seed(seed) if seed is not None else None
         logits = self._prefill(input_ids, cache)
+        use_graph = input_ids.is_cuda and B <= 8 and kw.get("cuda_graph", True)
+        if use_graph:
+            pos_t = torch.zeros(B, dtype=torch.int32, device=dev)
+            slots_t = torch.arange(B, dtype=torch.int32, device=dev)
         out = input_ids
         done = torch.zeros(B, dtype=torch.bool, device=dev)
         logprobs: List[torch.Tensor] = []
@@ -183,7 +227,12 @@ class Generator:
                 done |= nxt == e
             if bool(done.all()):
                 break
-            logits = self._decode(nxt, cache)
+            if use_graph:
+                pos_t.fill_(cache.len)
+                logits = self.decode_graphed(nxt, cache, pos_t, slots_t)
+                cache.len += 1
+            else:
+                logits = self._decode(nxt, cache)
         if streamer is not None:
             streamer.end()
         self.model.train(was)

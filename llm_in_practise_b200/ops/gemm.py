@@ -149,8 +149,12 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     else:
         args.A2 = args.B2 = 0
         args.K2 = 0
-    ws = _stream_k_workspace(a.device)
-    args.workspace, args.workspace_bytes = ws.data_ptr(), ws.numel()
+    if torch.cuda.is_current_stream_capturing():
+        # stream-K epochs are host-side counters baked into the launch: a replayed graph must not use them
+        args.workspace, args.workspace_bytes = 0, 0
+    else:
+        ws = _stream_k_workspace(a.device)
+        args.workspace, args.workspace_bytes = ws.data_ptr(), ws.numel()
     rc = nv.lib().b200_gemm(ctypes.byref(args), nv.stream())
     nv.check(rc, f"gemm M={M} N={N} K={K} batch={batch}")
     nv.count_launch()

@@ -191,7 +191,7 @@ class FusedLinear(nn.Module):
     def _materialize_weight(self, dtype=None) -> torch.Tensor:
         if self.nf4 is not None:
             dtype = dtype or torch.bfloat16
-            if dq.ENABLED and self.nf4.packed.is_cuda and nv.available():
+            if dq.ENABLED and self.nf4.packed.is_cuda and nv.available() and not torch.cuda.is_current_stream_capturing():
                 return dq.pipeline(self.nf4.packed.device).get(self.nf4, dtype, False)   # expanded one GEMM ahead
             ws = weight_workspace(self.nf4.packed.device, dtype, self.out_features * self.in_features)
             return self.nf4.dequantize(dtype, out=ws.view(self.out_features, self.in_features))
@@ -214,7 +214,7 @@ class FusedLinear(nn.Module):
             if dx is not None:
                 return dx
         if q is not None and dy.is_cuda and getattr(q, "can_transpose", lambda: False)() and dy.dtype != torch.float32:
-            if dq.ENABLED and nv.available():
+            if dq.ENABLED and nv.available() and not torch.cuda.is_current_stream_capturing():
                 return gemm(dy, dq.pipeline(q.packed.device).get(q, dy.dtype, True), lora=lora)
             ws = weight_workspace(q.packed.device, dy.dtype, self.out_features * self.in_features)
             wt = q.dequantize(dy.dtype, out=ws.view(self.in_features, self.out_features), transpose=True)

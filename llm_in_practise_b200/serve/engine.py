@@ -261,7 +261,7 @@ class LLMEngine:
         last = torch.tensor([r.output_ids[-1] for r in reqs], device=self.device)
         pos = torch.tensor([len(r.prompt_ids) + len(r.output_ids) - 1 for r in reqs], device=self.device, dtype=torch.int32)
         slots = torch.tensor([r.slot for r in reqs], device=self.device, dtype=torch.int32)
-        logits = self.gen._decode(last, self.cache, pos, slots)
+        logits = self.gen.decode_graphed(last, self.cache, pos, slots)
         toks = self._sample(logits, reqs)
         self.running = [r for r, t in zip(reqs, toks) if not self._emit(r, t)]
         self.metrics.steps += 1

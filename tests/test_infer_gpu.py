@@ -71,3 +71,25 @@ def test_w4_decode_path_and_quantize_on_device():
     for t in range(16, 22):
         row = full[:, t - 1]
         assert (row.max(-1).values - row.gather(1, out[:, t:t + 1]).squeeze(1) < 0.2).all(), t
+
+
+def test_cuda_graph_decode_matches_eager():
+    from llm_in_practise_b200.inference import Generator
+    from llm_in_practise_b200.quant.formats import quantize_rtn
+    m = _tiny()
+    for layer in m.layers:
+        for lin in layer.fused_linears().values():
+            lin.set_nf4(quantize_rtn(lin.weight.data, 128, True))
+    ids = torch.randint(0, 512, (3, 9), device="cuda")
+    g = Generator(m, max_len=64)
+    a = g.generate(ids, max_new_tokens=12, do_sample=False, cuda_graph=True)
+    assert len(g._graphs) == 1
+    b = g.generate(ids, max_new_tokens=12, do_sample=False, cuda_graph=False)
+    assert torch.equal(a, b)
+    # a second generation reuses... a new cache means a new graph; the engine keeps one cache and one graph per batch size
+    from llm_in_practise_b200.serve import EngineArgs, LLMEngine
+    eng = LLMEngine(m, None, EngineArgs(max_num_seqs=4, max_model_len=64))
+    from llm_in_practise_b200.inference import GenerationConfig
+    reqs = eng.generate([ids[i].tolist() for i in range(3)], GenerationConfig(max_new_tokens=12, do_sample=False))
+    assert [r.output_ids for r in reqs] == [a[i, 9:].tolist() for i in range(3)]
+    assert 1 <= len(eng.gen._graphs) <= 3

@@ -1,0 +1,50 @@
+"""Tensor-parallel sharding on CPU/gloo (2 processes): dense and 4-bit models give the single-process logits and tokens."""
+import pytest
+import torch
+from dist_utils import run_distributed
+
+
+def _model(quant):
+    from llm_in_practise_b200.models.qwen3 import Qwen3Config, Qwen3ForCausalLM
+    from llm_in_practise_b200.quant.formats import quantize_rtn
+    cfg = Qwen3Config(vocab_size=256, hidden_size=256, intermediate_size=512, num_hidden_layers=2, num_attention_heads=4,
+                      num_key_value_heads=2, head_dim=64, max_position_embeddings=128)
+    torch.manual_seed(0)
+    m = Qwen3ForCausalLM(cfg, dtype=torch.float32, device="cpu", init_std=0.05)
+    if quant == "nf4":
+        m.quantize_nf4(True)
+    elif quant == "w4":
+        for layer in m.layers:
+            for lin in layer.fused_linears().values():
+                lin.set_nf4(quantize_rtn(lin.weight.data, 128, False))
+    return m
+
+
+def _worker(rank, world, quant, tmp):
+    from llm_in_practise_b200.inference import Generator
+    from llm_in_practise_b200.parallel.dist import setup_distributed
+    from llm_in_practise_b200.parallel.tp import shard_qwen3
+    setup_distributed()
+    m = _model(quant)
+    tp = shard_qwen3(m)
+    assert tp.world == 2 and m.config.num_attention_heads == 2 and m.layers[0].qkv_proj.out_features == (4 + 2 + 2) * 64 // 2
+    ids = torch.arange(12).view(1, 12) % 256
+    with torch.no_grad():
+        logits = m(ids)["logits"]
+    out = Generator(m, max_len=64).generate(ids, max_new_tokens=5, do_sample=False)
+    if rank == 0:
+        torch.save({"logits": logits, "out": out, "calls": tp.calls}, f"{tmp}/tp.pt")
+
+
+@pytest.mark.parametrize("quant", ["dense", "nf4", "w4"])
+def test_tp2_matches_single(quant, tmp_path):
+    from llm_in_practise_b200.inference import Generator
+    run_distributed(_worker, 2, (quant, str(tmp_path)))
+    got = torch.load(tmp_path / "tp.pt")
+    m = _model(quant)
+    ids = torch.arange(12).view(1, 12) % 256
+    with torch.no_grad():
+        ref = m(ids)["logits"]
+    assert torch.allclose(got["logits"], ref, atol=2e-4, rtol=1e-3), (got["logits"] - ref).abs().max()
+    assert torch.equal(got["out"], Generator(m, max_len=64).generate(ids, max_new_tokens=5, do_sample=False))
+    assert got["calls"] > 0
