@@ -128,8 +128,176 @@ decode_attn_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __rest
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Split ("flash-decoding") variant for serving batches: one CTA per (sequence, kv head, split) serves all G query heads
+// of the group, so K and V are read once per group instead of once per query head, and the cached positions are spread
+// over `nsplit` CTAs. Per 32-position block a warp works in two layouts:
+//   scores : lane = position. The lane streams its own K row in 16-byte vectors and accumulates the G dot products
+//            against q held in shared memory (broadcast reads) - no shuffle per position, 16 independent loads in flight;
+//   values : lane = D/32 output channels. The block's probabilities go through shared memory, V rows are read coalesced.
+// Each CTA leaves (max, sum, unnormalised output) per head in `part`; decode_attn_combine_kernel merges the splits.
+// 16-bit types, D = 128 or 64, window-less.
+template <typename T, int D, int G>
+__global__ void __launch_bounds__(128)
+decode_attn_split_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __restrict__ cache_v,
+                         const int* __restrict__ pos, const int* __restrict__ slots, float* __restrict__ part, int H, int Hkv,
+                         int max_len, float scale, int nsplit) {
+  constexpr int PER = D / 32, CH = D / 8;   // output channels per lane; 16-byte chunks per row
+  __shared__ __align__(16) float qs[G][D];
+  __shared__ float ps[4][G][32];
+  __shared__ float sm_m[4][G], sm_l[4][G];
+  __shared__ float sacc[4][G][D];
+  const int sp = blockIdx.x % nsplit, kvh = (blockIdx.x / nsplit) % Hkv, b = blockIdx.x / (nsplit * Hkv);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t_new = pos[b];
+  const long long row = (long long)b * (H + 2 * Hkv) * D;
+  const long long slot = slots ? slots[b] : b;
+  T* kc = cache_k + (slot * Hkv + kvh) * max_len * D;
+  T* vc = cache_v + (slot * Hkv + kvh) * max_len * D;
+  const T* knew = qkv + row + (long long)(H + kvh) * D;
+  const T* vnew = qkv + row + (long long)(H + Hkv + kvh) * D;
+  if (sp == 0 && warp == 0) {   // append the new token's K / V (read back from qkv below, never from the cache)
+    for (int i = lane; i < D; i += 32) {
+      kc[(long long)t_new * D + i] = knew[i];
+      vc[(long long)t_new * D + i] = vnew[i];
+    }
+  }
+  for (int i = threadIdx.x; i < G * D; i += 128)
+    qs[i / D][i % D] = to_f32<T>(qkv[row + (long long)(kvh * G + i / D) * D + i % D]) * scale;
+  __syncthreads();
+  float m[G], l[G], acc[G][PER];
+#pragma unroll
+  for (int h = 0; h < G; ++h) {
+    m[h] = -INFINITY; l[h] = 0.f;
+#pragma unroll
+    for (int i = 0; i < PER; ++i) acc[h][i] = 0.f;
+  }
+  for (int base = (sp * 4 + warp) * 32; base <= t_new; base += nsplit * 4 * 32) {
+    // ---- scores: lane = position ----
+    const int t = base + lane;
+    const bool valid = t <= t_new;
+    const T* kr = !valid ? knew : (t == t_new ? knew : kc + (long long)t * D);
+    float s[G];
+#pragma unroll
+    for (int h = 0; h < G; ++h) s[h] = 0.f;
+#pragma unroll 4
+    for (int c = 0; c < CH; ++c) {
+      const uint4 raw = *reinterpret_cast<const uint4*>(kr + c * 8);
+      const T* ke = reinterpret_cast<const T*>(&raw);
+      float kf[8];
+#pragma unroll
+      for (int e = 0; e < 8; ++e) kf[e] = to_f32<T>(ke[e]);
+#pragma unroll
+      for (int h = 0; h < G; ++h) {
+        const float4 q0 = *reinterpret_cast<const float4*>(&qs[h][c * 8]);
+        const float4 q1 = *reinterpret_cast<const float4*>(&qs[h][c * 8 + 4]);
+        s[h] += q0.x * kf[0] + q0.y * kf[1] + q0.z * kf[2] + q0.w * kf[3] + q1.x * kf[4] + q1.y * kf[5] + q1.z * kf[6] + q1.w * kf[7];
+      }
+    }
+#pragma unroll
+    for (int h = 0; h < G; ++h) {
+      const float sv = valid ? s[h] : -INFINITY;
+      const float mn = fmaxf(m[h], warp_max(sv));
+      const float c = __expf(m[h] - mn);
+      const float p = valid ? __expf(sv - mn) : 0.f;
+      ps[warp][h][lane] = p;
+      l[h] = l[h] * c + warp_sum(p);
+      m[h] = mn;
+#pragma unroll
+      for (int i = 0; i < PER; ++i) acc[h][i] *= c;
+    }
+    __syncwarp();
+    // ---- values: lane = output channels ----
+    const int nv_ = min(32, t_new - base + 1);
+#pragma unroll 4
+    for (int tt = 0; tt < nv_; ++tt) {
+      const int tv = base + tt;
+      float vf[PER];
+      load_row<T, PER>((tv == t_new ? vnew : vc + (long long)tv * D) + lane * PER, vf);
+#pragma unroll
+      for (int h = 0; h < G; ++h) {
+        const float p = ps[warp][h][tt];
+#pragma unroll
+        for (int i = 0; i < PER; ++i) acc[h][i] += p * vf[i];
+      }
+    }
+    __syncwarp();
+  }
+  // ---- merge the 4 warps, publish this split's partial ----
+#pragma unroll
+  for (int h = 0; h < G; ++h) {
+    if (lane == 0) { sm_m[warp][h] = m[h]; sm_l[warp][h] = l[h]; }
+#pragma unroll
+    for (int i = 0; i < PER; ++i) sacc[warp][h][lane * PER + i] = acc[h][i];
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < G * D; o += 128) {
+    const int h = o / D, d = o % D;
+    const float gm = fmaxf(fmaxf(sm_m[0][h], sm_m[1][h]), fmaxf(sm_m[2][h], sm_m[3][h]));
+    float gl = 0.f, go = 0.f;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float wgt = sm_m[w][h] == -INFINITY ? 0.f : __expf(sm_m[w][h] - gm);
+      gl += sm_l[w][h] * wgt;
+      go += sacc[w][h][d] * wgt;
+    }
+    float* dst = part + (((long long)b * H + kvh * G + h) * nsplit + sp) * (D + 2);
+    dst[2 + d] = go;
+    if (d == 0) { dst[0] = gm; dst[1] = gl; }
+  }
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(D)
+decode_attn_combine_kernel(const float* __restrict__ part, T* __restrict__ out, int nsplit) {
+  const long long bh = blockIdx.x;   // b * H + h
+  const int d = threadIdx.x;
+  const float* p = part + bh * nsplit * (D + 2);
+  float gm = -INFINITY;
+  for (int s = 0; s < nsplit; ++s) gm = fmaxf(gm, p[s * (D + 2)]);
+  float gl = 0.f, go = 0.f;
+  for (int s = 0; s < nsplit; ++s) {
+    const float ms = p[s * (D + 2)];
+    const float w = ms == -INFINITY ? 0.f : __expf(ms - gm);
+    gl += p[s * (D + 2) + 1] * w;
+    go += p[s * (D + 2) + 2 + d] * w;
+  }
+  out[bh * D + d] = from_f32<T>(gl > 0.f ? go / gl : 0.f);
+}
+
 }  // namespace b200
 using namespace b200;
+
+// scratch: B * H * nsplit * (D + 2) floats. Returns B200_ERR_UNSUPPORTED for shapes the split kernel does not cover
+// (callers use b200_decode_attn then).
+B200_API int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out,
+                                    float* scratch, int B, int H, int Hkv, int D, int max_len, float scale, int nsplit,
+                                    int dtype, void* stream) {
+  if (B <= 0 || H % Hkv || nsplit < 1 || nsplit > 64) return B200_ERR_BAD_SHAPE;
+  if (dtype != B200_DT_BF16 && dtype != B200_DT_FP16) return B200_ERR_UNSUPPORTED;
+  const int G = H / Hkv;
+  cudaStream_t st = (cudaStream_t)stream;
+  const unsigned grid = (unsigned)(B * Hkv * nsplit), grid2 = (unsigned)(B * H);
+#define B200_DS(T, DD, GG)                                                                                              \
+  do {                                                                                                                  \
+    decode_attn_split_kernel<T, DD, GG><<<grid, 128, 0, st>>>((const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, scratch, \
+                                                              H, Hkv, max_len, scale, nsplit);                         \
+    decode_attn_combine_kernel<T, DD><<<grid2, DD, 0, st>>>(scratch, (T*)out, nsplit);                                  \
+  } while (0)
+#define B200_DS_G(T, DD)                                                         \
+  if (G == 1) B200_DS(T, DD, 1); else if (G == 2) B200_DS(T, DD, 2);              \
+  else if (G == 4) B200_DS(T, DD, 4); else if (G == 5) B200_DS(T, DD, 5);         \
+  else if (G == 8) B200_DS(T, DD, 8); else return B200_ERR_UNSUPPORTED
+  if (dtype == B200_DT_BF16) {
+    if (D == 128) { B200_DS_G(__nv_bfloat16, 128); } else if (D == 64) { B200_DS_G(__nv_bfloat16, 64); } else return B200_ERR_UNSUPPORTED;
+  } else {
+    if (D == 128) { B200_DS_G(__half, 128); } else if (D == 64) { B200_DS_G(__half, 64); } else return B200_ERR_UNSUPPORTED;
+  }
+#undef B200_DS_G
+#undef B200_DS
+  B200_LAUNCH_CHECK();
+  return 0;
+}
 
 B200_API int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B, int H,
                               int Hkv, int D, int max_len, float scale, int window, int dtype, void* stream) {

@@ -1,0 +1,203 @@
+// Small-M products for decode / serving steps: y[m, n] = sum_k x[m, k] * w[n, k] (+ bias) for M <= 64 tokens, with the
+// weight matrix read exactly once — 16-bit dense weights (`b200_gemv16`) or 4-bit codes (`b200_w4_gemv_batched`).
+//
+// Same scheme as w4_gemv_mma_kernel (w4.cu): a CTA owns 16 output rows, its 8 warps take interleaved 128-wide k chunks,
+// the weights are the A operand of mma.sync.m16n8k16 and the tokens the 8-wide B operand; the k index is permuted so
+// that every lane fetches whole 16-byte vectors (lane (g, t) owns k in [128 c + 32 t, +32) of rows g and g + 8, MMA j of
+// the chunk consumes elements 4j .. 4j+3). New here: TG token groups of 8 share one pass over the weights — the A
+// fragments (expanded once for 4-bit codes) are reused by TG MMAs, so up to 64 concurrent sequences cost one read of
+// the model per step. That is the regime of the reference's serving table (concurrency 8..64,
+// LLM_on_Kubernetes/Inference_Platfrom/README.md:1504-1509), where a 128-row tensor-core tile would be >87 % padding.
+#include "common.cuh"
+#include "../include/b200_ops.h"
+
+#include <stdlib.h>
+
+namespace b200 {
+
+__constant__ float kNF4g[16] = {-1.0f, -0.6961928009986877f, -0.5250730514526367f, -0.39491748809814453f,
+                                -0.28444138169288635f, -0.18477343022823334f, -0.09105003625154495f, 0.0f,
+                                0.07958029955625534f, 0.16093020141124725f, 0.24611230194568634f,
+                                0.33791524171829224f, 0.44070982933044434f, 0.5626170039176941f,
+                                0.7229568362236023f, 1.0f};
+
+template <bool BF16>
+__device__ __forceinline__ void mma16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  if (BF16)
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+  else
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+template <bool BF16>
+__device__ __forceinline__ uint32_t pack2(float a, float b) {
+  if (BF16) return pack_bf16x2(a, b);
+  const __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&h);
+}
+
+template <bool BF16>
+__device__ __forceinline__ uint32_t fma2(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  if (BF16) asm("fma.rn.bf16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  else asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
+struct GemvParams {
+  const uint16_t* x;      // [M, K] 16-bit activations
+  const void* w;          // dense: uint16 [N, w_rs]; 4-bit: packed uint8 [N, K / 2]
+  const float* scale;     // 4-bit only: [N, K / group]
+  const float* zs;        // 4-bit only, may be null
+  const float* lut;       // 4-bit only, null = NF4
+  const void* bias;       // 16-bit, may be null
+  void* y;                // [M, y_rs] 16-bit or fp32
+  int M, K, group, out_f32;
+  long long N, x_rs, w_rs, y_rs;
+};
+
+template <bool BF16, bool W4, int TG>
+__global__ void __launch_bounds__(256)
+gemv_mma_kernel(const GemvParams p) {
+  extern __shared__ uint32_t table[];   // 4-bit only: byte -> two 16-bit values, one column per lane (conflict-free)
+  __shared__ float red[8][128];
+  if (W4) {
+    for (int i = threadIdx.x; i < 256 * 32; i += 256) {
+      const int byte = i >> 5;
+      const float lo = p.lut ? p.lut[byte >> 4] : kNF4g[byte >> 4];
+      const float hi = p.lut ? p.lut[byte & 15] : kNF4g[byte & 15];
+      table[i] = pack2<BF16>(lo, hi);
+    }
+    __syncthreads();
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, t = lane & 3;
+  const int K = p.K, M = p.M;
+  const long long N = p.N;
+  const int gpr = W4 ? K / p.group : 0;
+  const uint32_t* tl = table + lane;
+  const int nchunks = K / 128;
+  const long long ntiles = (N + 15) / 16;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long row0 = tile * 16;
+    const long long rA = min(row0 + g, N - 1), rB = min(row0 + g + 8, N - 1);
+    float c[TG][4];
+#pragma unroll
+    for (int tg = 0; tg < TG; ++tg)
+#pragma unroll
+      for (int i = 0; i < 4; ++i) c[tg][i] = 0.f;
+    for (int ch = warp; ch < nchunks; ch += 8) {
+      const int k = ch * 128 + t * 32;
+      uint32_t aA[16], aB[16];   // rows g / g+8: 32 weights each as 16-bit pairs
+      if (W4) {
+        const uint8_t* pk = reinterpret_cast<const uint8_t*>(p.w);
+        const uint4 wa = __ldg(reinterpret_cast<const uint4*>(pk + rA * (K / 2) + k / 2));
+        const uint4 wb = __ldg(reinterpret_cast<const uint4*>(pk + rB * (K / 2) + k / 2));
+        const float sa = __ldg(p.scale + rA * gpr + k / p.group), sb = __ldg(p.scale + rB * gpr + k / p.group);
+        const float za = p.zs ? __ldg(p.zs + rA * gpr + k / p.group) : 0.f, zb = p.zs ? __ldg(p.zs + rB * gpr + k / p.group) : 0.f;
+        const uint32_t sa2 = pack2<BF16>(sa, sa), sb2 = pack2<BF16>(sb, sb), za2 = pack2<BF16>(-za, -za), zb2 = pack2<BF16>(-zb, -zb);
+        const uint32_t wA[4] = {wa.x, wa.y, wa.z, wa.w}, wB[4] = {wb.x, wb.y, wb.z, wb.w};
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {   // byte i of the 16 packed bytes = elements 2i, 2i+1
+          const uint32_t ba = (wA[i >> 2] >> ((i & 3) * 8)) & 0xFFu, bb = (wB[i >> 2] >> ((i & 3) * 8)) & 0xFFu;
+          aA[i] = fma2<BF16>(tl[ba << 5], sa2, za2);
+          aB[i] = fma2<BF16>(tl[bb << 5], sb2, zb2);
+        }
+      } else {
+        const uint16_t* wd = reinterpret_cast<const uint16_t*>(p.w);
+        const uint4* pa = reinterpret_cast<const uint4*>(wd + rA * p.w_rs + k);
+        const uint4* pb = reinterpret_cast<const uint4*>(wd + rB * p.w_rs + k);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const uint4 va = __ldg(pa + i), vb = __ldg(pb + i);
+          aA[4 * i] = va.x; aA[4 * i + 1] = va.y; aA[4 * i + 2] = va.z; aA[4 * i + 3] = va.w;
+          aB[4 * i] = vb.x; aB[4 * i + 1] = vb.y; aB[4 * i + 2] = vb.z; aB[4 * i + 3] = vb.w;
+        }
+      }
+#pragma unroll
+      for (int tg = 0; tg < TG; ++tg) {
+        const int tok = tg * 8 + g;
+        uint32_t xw[16];
+        if (tok < M) {
+          const uint4* xp = reinterpret_cast<const uint4*>(p.x + (long long)tok * p.x_rs + k);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const uint4 v = __ldg(xp + i);
+            xw[4 * i] = v.x; xw[4 * i + 1] = v.y; xw[4 * i + 2] = v.z; xw[4 * i + 3] = v.w;
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) xw[i] = 0u;
+        }
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          mma16816<BF16>(c[tg], aA[2 * j], aB[2 * j], aA[2 * j + 1], aB[2 * j + 1], xw[2 * j], xw[2 * j + 1]);
+      }
+    }
+    // c0: (row g, token 2t), c1: (row g, token 2t+1), c2: (row g+8, token 2t), c3: (row g+8, token 2t+1) of the group
+#pragma unroll
+    for (int tg = 0; tg < TG; ++tg) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) red[warp][lane * 4 + i] = c[tg][i];
+      __syncthreads();
+      if (threadIdx.x < 128) {
+        float s = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) s += red[w][threadIdx.x];
+        const int ln = threadIdx.x >> 2, i = threadIdx.x & 3;
+        const long long row = row0 + (ln >> 2) + ((i & 2) ? 8 : 0);
+        const int tok = tg * 8 + 2 * (ln & 3) + (i & 1);
+        if (row < N && tok < M) {
+          if (p.bias) s += BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[row])
+                                : __half2float(reinterpret_cast<const __half*>(p.bias)[row]);
+          if (p.out_f32) reinterpret_cast<float*>(p.y)[(long long)tok * p.y_rs + row] = s;
+          else if (BF16) reinterpret_cast<__nv_bfloat16*>(p.y)[(long long)tok * p.y_rs + row] = __float2bfloat16_rn(s);
+          else reinterpret_cast<__half*>(p.y)[(long long)tok * p.y_rs + row] = __float2half_rn(s);
+        }
+      }
+      __syncthreads();   // `red` is reused by the next token group / tile
+    }
+  }
+}
+
+template <bool BF16, bool W4>
+static int launch_gemv(const GemvParams& p, cudaStream_t st) {
+  const long long tiles = (p.N + 15) / 16;
+  const unsigned grid = (unsigned)(tiles < kNumSMs * 4 ? tiles : kNumSMs * 4);
+  const int smem = W4 ? 256 * 32 * 4 : 0;
+  if (p.M <= 8) gemv_mma_kernel<BF16, W4, 1><<<grid, 256, smem, st>>>(p);
+  else if (p.M <= 16) gemv_mma_kernel<BF16, W4, 2><<<grid, 256, smem, st>>>(p);
+  else if (p.M <= 32) gemv_mma_kernel<BF16, W4, 4><<<grid, 256, smem, st>>>(p);
+  else gemv_mma_kernel<BF16, W4, 8><<<grid, 256, smem, st>>>(p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace b200
+using namespace b200;
+
+B200_API int b200_gemv16(const void* x, const void* w, const void* bias, void* y, int M, long long N, int K, long long x_rs,
+                         long long w_rs, long long y_rs, int dtype, int out_f32, void* stream) {
+  if (M < 1 || M > 64 || K % 128 || x_rs % 8 || w_rs % 8) return B200_ERR_BAD_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(w)) & 15) return B200_ERR_BAD_ALIGN;
+  GemvParams p = {};
+  p.x = (const uint16_t*)x; p.w = w; p.bias = bias; p.y = y;
+  p.M = M; p.K = K; p.N = N; p.x_rs = x_rs; p.w_rs = w_rs; p.y_rs = y_rs; p.out_f32 = out_f32; p.group = 128;
+  if (dtype == B200_DT_BF16) return launch_gemv<true, false>(p, (cudaStream_t)stream);
+  if (dtype == B200_DT_FP16) return launch_gemv<false, false>(p, (cudaStream_t)stream);
+  return B200_ERR_UNSUPPORTED;
+}
+
+B200_API int b200_w4_gemv_batched(const void* x, const uint8_t* packed, const float* scale, const float* zs, const float* lut,
+                                  const void* bias, void* y, int M, long long N, int K, int group, long long x_rs,
+                                  long long y_rs, int dtype, void* stream) {
+  if (M < 1 || M > 64 || K % 128 || group % 32 || K % group || x_rs % 8) return B200_ERR_BAD_SHAPE;
+  GemvParams p = {};
+  p.x = (const uint16_t*)x; p.w = packed; p.scale = scale; p.zs = zs; p.lut = lut; p.bias = bias; p.y = y;
+  p.M = M; p.K = K; p.N = N; p.x_rs = x_rs; p.w_rs = 0; p.y_rs = y_rs; p.out_f32 = 0; p.group = group;
+  if (dtype == B200_DT_BF16) return launch_gemv<true, true>(p, (cudaStream_t)stream);
+  if (dtype == B200_DT_FP16) return launch_gemv<false, true>(p, (cudaStream_t)stream);
+  return B200_ERR_UNSUPPORTED;
+}

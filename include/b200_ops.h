@@ -265,6 +265,27 @@ int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int 
 int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B, int H,
                      int Hkv, int D, int max_len, float scale, int window, int dtype, void* stream);
 
+/* Split ("flash-decoding") variant for serving batches: one CTA per (sequence, kv head, split) serves every query head
+ * of the group (K/V read once per group), `nsplit` CTAs share the cached positions and a combine kernel merges them.
+ * scratch: B * H * nsplit * (D + 2) floats. 16-bit dtypes, D in {64, 128}, H / Hkv in {1, 2, 4, 5, 8}; otherwise
+ * B200_ERR_UNSUPPORTED_ (use b200_decode_attn). */
+int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out,
+                           float* scratch, int B, int H, int Hkv, int D, int max_len, float scale, int nsplit,
+                           int dtype, void* stream);
+
+/* ---- small-M products for decode / serving steps (csrc/gemv.cu) ---------------------------------
+ * y[m, n] = sum_k x[m, k] w[n, k] (+ bias[n]) for 1 <= M <= 64 tokens with the weights read exactly once (mma.sync with
+ * the weight rows as the A operand, token groups of 8 as B). K % 128 == 0; x / w 16-byte aligned, row strides
+ * multiples of 8 elements. b200_gemv16: 16-bit dense weights [N, w_rs], output 16-bit or fp32 (out_f32 = 1: the
+ * lm_head logits). b200_w4_gemv_batched: 4-bit weights in the b200_w4_dequant layout. What HF generate / vLLM decode
+ * spend their time in (Scripts/inference/07-deepseek1.5b-api-infr.py:118-131; serving table in
+ * LLM_on_Kubernetes/Inference_Platfrom/README.md:1504-1511). */
+int b200_gemv16(const void* x, const void* w, const void* bias, void* y, int M, long long N, int K, long long x_rs,
+                long long w_rs, long long y_rs, int dtype, int out_f32, void* stream);
+int b200_w4_gemv_batched(const void* x, const uint8_t* packed, const float* scale, const float* zs, const float* lut,
+                         const void* bias, void* y, int M, long long N, int K, int group, long long x_rs, long long y_rs,
+                         int dtype, void* stream);
+
 /* ---- gradient fold (csrc/elementwise.cu) -------------------------------------------------------
  * y (fp32) += scale * x (bf16/fp16), optionally clearing x: folds the low-precision .grad autograd produced for
  * non-GEMM parameters into the fp32 main-grad arena (DeepSpeed bf16 "grad_accum_dtype": fp32 behaviour;

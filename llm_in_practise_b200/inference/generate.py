@@ -23,10 +23,11 @@ import torch
 from ..ops import _native as nv
 from ..ops import elementwise as ew
 from ..ops.attention import attention
-from ..ops.gemm import gemm
+from ..ops.gemm import gemm, gemv16
 from ..ops.norm import rms_norm
 
 vp, i32, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+_SPLIT_DECODE = __import__("os").environ.get("B200_DECODE_SPLIT", "1") != "0"
 
 
 @dataclass
@@ -77,6 +78,15 @@ def _decode_attn(qkv, ck, cv, pos, H, Hkv, D, scale, slots=None):
     B = qkv.shape[0]
     if nv.use_native(qkv):
         out = torch.empty(B, H * D, dtype=qkv.dtype, device=qkv.device)
+        if _SPLIT_DECODE and qkv.dtype in (torch.bfloat16, torch.float16) and D in (64, 128) and H // Hkv in (1, 2, 4, 5, 8):
+            # K/V read once per GQA group; enough (sequence, kv head, split) CTAs to fill the 148 SMs about twice
+            nsplit = max(1, min(16, -(-296 // (B * Hkv))))
+            scratch = torch.empty(B * H * nsplit * (D + 2), dtype=torch.float32, device=qkv.device)
+            fs = nv.proto("b200_decode_attn_split", [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
+            nv.check(fs(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), nv.ptr(scratch), B, H, Hkv, D,
+                        ck.shape[2], scale, nsplit, nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn_split")
+            nv.count_launch(2)
+            return out
         fn = nv.proto("b200_decode_attn", [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
         nv.check(fn(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), B, H, Hkv, D, ck.shape[2], scale, 0,
                     nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn")
@@ -153,18 +163,19 @@ class Generator:
             delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
         h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)
         cache.len += 1
-        return gemm(h, m.head_weight(), out_dtype=torch.float32)
+        logits = gemv16(h, m.head_weight(), out_dtype=torch.float32)
+        return logits if logits is not None else gemm(h, m.head_weight(), out_dtype=torch.float32)
 
     @torch.no_grad()
     def decode_graphed(self, tok: torch.Tensor, cache: KVCache, pos: torch.Tensor, slots: torch.Tensor) -> torch.Tensor:
         """``_decode`` replayed from a CUDA graph (one per batch size and cache): a decode step is ~14 launches per
         layer of a few microseconds each, so eager execution is bound by the Python launch rate, not by the GPU. The
         kernels read token ids, positions and cache slots from device tensors, so one graph serves any set of
-        sequences. Falls back to the eager path on CPU, under tensor parallelism (the peer all-reduce takes a host
-        epoch) and for batches above 8 rows (those go through the multi-stream dequant pipeline)."""
+        sequences. Falls back to the eager path on CPU and under tensor parallelism (the peer all-reduce takes a host
+        epoch). Inside a capture the GEMMs run without stream-K and 4-bit weights are expanded in line."""
         B = tok.shape[0]
         L = cache.len                                   # ``cache.len`` is the caller's to advance, never this method's
-        if not tok.is_cuda or B > 8 or getattr(self.model, "tp", None) is not None and self.model.tp.world > 1:
+        if not tok.is_cuda or B > 512 or getattr(self.model, "tp", None) is not None and self.model.tp.world > 1:
             out = self._decode(tok, cache, pos, slots)
             cache.len = L
             return out

@@ -177,6 +177,29 @@ def linear_wgrad(dy, x, out=None, beta=0.0, out_dtype=None):
     return gemm(dy, x, a_mn=True, b_mn=True, out=out, beta=beta, out_dtype=out_dtype)
 
 
+def gemv16(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
+           out_dtype: Optional[torch.dtype] = None) -> Optional[torch.Tensor]:
+    """``x @ w^T`` for 1..64 rows of 16-bit ``x`` [M, K] and a dense 16-bit ``w`` [N, K], reading ``w`` once
+    (csrc/gemv.cu). Returns None when the shape is outside the kernel's domain (the caller then uses ``gemm``)."""
+    if not nv.use_native(x) or x.dim() != 2 or x.dtype not in (torch.bfloat16, torch.float16) or w.dtype != x.dtype:
+        return None
+    M, K = x.shape
+    N = w.shape[0]
+    out_dtype = out_dtype or x.dtype
+    if M > 64 or K % 128 or w.stride(-1) != 1 or w.stride(0) % 8 or out_dtype not in (x.dtype, torch.float32) \
+            or (bias is not None and bias.dtype != x.dtype) or w.data_ptr() % 16:
+        return None
+    if x.stride(-1) != 1 or x.stride(0) % 8 or x.data_ptr() % 16:
+        x = x.contiguous()
+    y = torch.empty(M, N, dtype=out_dtype, device=x.device)
+    vp, i32, i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong
+    fn = nv.proto("b200_gemv16", [vp, vp, vp, vp, i32, i64, i32, i64, i64, i64, i32, i32, vp])
+    nv.check(fn(nv.ptr(x), nv.ptr(w), nv.ptr(bias), nv.ptr(y), M, N, K, x.stride(0), w.stride(0), y.stride(0),
+                nv.dtype_code(x.dtype), int(out_dtype == torch.float32), nv.stream()), f"gemv16 M={M} N={N} K={K}")
+    nv.count_launch()
+    return y
+
+
 # ------------------------------------------------------------------------------------------------
 # 4-bit B operand expanded inside the GEMM (csrc/gemm_tcgen05.cu: gemm_w4_tcgen05_kernel)
 # ------------------------------------------------------------------------------------------------

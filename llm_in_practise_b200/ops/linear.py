@@ -27,7 +27,7 @@ from torch import nn
 from . import _native as nv
 from . import dequant_pipeline as dq
 from . import elementwise as ew
-from .gemm import gemm, gemm_w4
+from .gemm import gemm, gemm_w4, gemv16
 from .lora import lora_down, lora_dx, lora_wgrad
 from .w4 import NF4Weight
 
@@ -319,7 +319,8 @@ class FusedLinear(nn.Module):
         if self.has_lora:
             seed = ew.layer_seed(self.layer_uid) if (self.training and self.lora_dropout > 0) else 0
             y = _LoraLinearFn.apply(x2, self, seed, *self._adapter_params())
-        elif (self.nf4 is not None and x2.shape[0] <= 8 and not torch.is_grad_enabled() and x2.is_cuda
+        elif (self.nf4 is not None and not torch.is_grad_enabled() and x2.is_cuda
+              and (x2.shape[0] <= 8 or (x2.shape[0] <= 32 and self.in_features % 128 == 0))
               and hasattr(self.nf4, "group") and not hasattr(self.nf4, "shards")
               and x2.dtype in (torch.bfloat16, torch.float16)):
             # decode: fused 4-bit GEMV straight from the packed weights (memory-bound, 4.25 bits/weight read)
@@ -330,7 +331,12 @@ class FusedLinear(nn.Module):
             y = w4_gemv(x2, q.packed, sc, getattr(q, "zs", None), q.N, q.K, q.group, lut, self.bias)
         elif self.nf4 is not None or not (self.weight.requires_grad or
                                           (self.bias is not None and self.bias.requires_grad)):
-            y = _FrozenLinearFn.apply(x2, self)
+            y = None
+            # measured on Qwen3-8B bf16: 6.1 vs 8.5 ms per step at 8 rows, but 20.6 vs 15.1 ms at 64 (mma.sync-bound): <= 16 only
+            if self.nf4 is None and x2.shape[0] <= 16 and not torch.is_grad_enabled():
+                y = gemv16(x2, self.weight, self.bias)       # decode / serving step: weights read once, no 128-row tile padding
+            if y is None:
+                y = _FrozenLinearFn.apply(x2, self)
         else:
             if x2.dtype != self.compute_dtype:
                 x2 = x2.to(self.compute_dtype)

@@ -157,6 +157,12 @@ def w4_gemv(x, packed, scale, zs, N: int, K: int, group: int, lut=None, bias=Non
         return y.to(x.dtype)
     x = x.contiguous()
     y = torch.empty(M, N, dtype=x.dtype, device=x.device)
+    if M > 8:     # 9..64 tokens: token groups of 8 share one pass over the codes (csrc/gemv.cu)
+        fb = nv.proto("b200_w4_gemv_batched", [vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, i64, i64, i32, vp])
+        nv.check(fb(nv.ptr(x), nv.ptr(packed), nv.ptr(scale), nv.ptr(zs), nv.ptr(lut), nv.ptr(bias), nv.ptr(y), M, N, K,
+                    group, x.stride(0), y.stride(0), nv.dtype_code(x.dtype), nv.stream()), "w4_gemv_batched")
+        nv.count_launch()
+        return y
     fn = nv.proto("b200_w4_gemv", [vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, i64, i64, i32, vp])
     nv.check(fn(nv.ptr(x), nv.ptr(packed), nv.ptr(scale), nv.ptr(zs), nv.ptr(lut), nv.ptr(bias), nv.ptr(y), M, N, K,
                 group, x.stride(0), y.stride(0), nv.dtype_code(x.dtype), nv.stream()), "w4_gemv")

@@ -51,6 +51,7 @@ class Request:
     done: threading.Event = field(default_factory=threading.Event)
     stream: "queue.Queue" = field(default_factory=queue.Queue)
     error: Optional[str] = None
+    token_times: List[float] = field(default_factory=list)   # perf_counter at every emitted token (TTFT / ITL statistics)
 
     @property
     def ttft(self) -> Optional[float]:
@@ -95,7 +96,8 @@ class LLMEngine:
         self.model, self.tokenizer, self.model_name = self.gen.model, tokenizer, model_name
         c = self.model.config
         self.device = self.model.embed_tokens.device
-        self.cache = KVCache(c.num_hidden_layers, self.args.max_num_seqs, c.num_key_value_heads, self.args.max_model_len,
+        # one extra row: the scratch slot that padded rows of a bucketed (CUDA-graph) decode batch write into
+        self.cache = KVCache(c.num_hidden_layers, self.args.max_num_seqs + 1, c.num_key_value_heads, self.args.max_model_len,
                              c.head_dim, self.model.embed_tokens.dtype, self.device)
         self.free: List[int] = list(range(self.args.max_num_seqs))[::-1]
         self.waiting: Deque[Request] = deque()
@@ -212,6 +214,7 @@ class LLMEngine:
             self._finish(r, "stop")
             return True
         r.output_ids.append(tok)
+        r.token_times.append(now)
         r.stream.put(tok)
         with self.metrics.lock:
             self.metrics.generation_tokens += 1
@@ -258,10 +261,18 @@ class LLMEngine:
         if not self.running:
             return
         reqs = self.running
-        last = torch.tensor([r.output_ids[-1] for r in reqs], device=self.device)
-        pos = torch.tensor([len(r.prompt_ids) + len(r.output_ids) - 1 for r in reqs], device=self.device, dtype=torch.int32)
-        slots = torch.tensor([r.slot for r in reqs], device=self.device, dtype=torch.int32)
-        logits = self.gen.decode_graphed(last, self.cache, pos, slots)
+        n = len(reqs)
+        nb = n
+        if self.device.type == "cuda":          # pad to a power-of-two bucket: one captured graph per bucket, not per batch size
+            nb = 1
+            while nb < n:
+                nb *= 2
+        pad = nb - n
+        scratch = self.args.max_num_seqs
+        last = torch.tensor([r.output_ids[-1] for r in reqs] + [0] * pad, device=self.device)
+        pos = torch.tensor([len(r.prompt_ids) + len(r.output_ids) - 1 for r in reqs] + [0] * pad, device=self.device, dtype=torch.int32)
+        slots = torch.tensor([r.slot for r in reqs] + [scratch] * pad, device=self.device, dtype=torch.int32)
+        logits = self.gen.decode_graphed(last, self.cache, pos, slots)[:n]
         toks = self._sample(logits, reqs)
         self.running = [r for r, t in zip(reqs, toks) if not self._emit(r, t)]
         self.metrics.steps += 1

@@ -258,3 +258,23 @@ def test_adamw_and_8bit():
             opt.step()
             ropt.step()
         assert rel(arena.data, ref.data) < tol, cls.__name__
+
+
+@pytest.mark.parametrize("M", [1, 8, 13, 40, 64])
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_small_m_gemv_kernels(M, dtype):
+    from llm_in_practise_b200.ops.gemm import gemv16
+    torch.manual_seed(M)
+    N_, K = 1000, 1024                      # N not a multiple of 16: the last row tile is partial
+    x = torch.randn(M, K, device=DEV, dtype=dtype)
+    w = (torch.randn(N_, K, device=DEV) / 32).to(dtype)
+    b = torch.randn(N_, device=DEV, dtype=dtype)
+    ref = x.float() @ w.float().t() + b.float()
+    assert rel(gemv16(x, w, b), ref) < 1e-2
+    assert rel(gemv16(x, w, None, out_dtype=torch.float32), x.float() @ w.float().t()) < 5e-3
+    packed = torch.randint(0, 256, (N_ * K // 2,), device=DEV, dtype=torch.uint8)
+    scale = torch.rand(N_ * K // 128, device=DEV) * 0.01 + 0.001
+    lut = torch.arange(16, device=DEV, dtype=torch.float32)
+    y = W4.w4_gemv(x, packed, scale, scale * 8, N_, K, 128, lut, b)
+    wd = W4.w4_dequant(packed, scale, scale * 8, N_, K, 128, lut, dtype)
+    assert rel(y, x.float() @ wd.float().t() + b.float()) < 1e-2
