@@ -27,6 +27,9 @@ from .gemm import gemm
 vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
 
 
+_BLOCK_Q = 512   # query rows per block of the blocked causal path
+
+
 def _softmax_fwd(scores, causal, window, out_dtype):
     *lead, rows, cols = scores.shape
     batch = 1
@@ -57,6 +60,59 @@ def _split_heads(qkv, B, S, H, Hkv, D):
     k = t[:, :, H:H + Hkv].permute(0, 2, 1, 3)
     v = t[:, :, H + Hkv:].permute(0, 2, 1, 3)
     return q, k, v
+
+
+class _BlockedCausalAttentionFn(torch.autograd.Function):
+    """Causal attention in query blocks of ``bs`` rows: block i only multiplies against keys [0, end of block i), so the
+    score / probability matrices hold ~S^2/2 entries instead of S^2 and the work above the diagonal (half of it at long
+    sequence length) is never done. Same kernels as the one-shot path: strided tcgen05 GEMMs straight out of the fused
+    qkv projection, the row softmax with its implicit causal offset (last query row <-> last key column), accumulation
+    of dK / dV across blocks in the GEMM epilogue (beta = 1). Used for S > 512 (the 4k-token LoRA configuration)."""
+
+    @staticmethod
+    def forward(ctx, qkv, B, S, H, Hkv, D, scale, bs):
+        q, k, v = _split_heads(qkv, B, S, H, Hkv, D)
+        out = torch.empty(B, S, H, D, dtype=qkv.dtype, device=qkv.device)
+        o4 = out.permute(0, 2, 1, 3)
+        Ps = []
+        for q0 in range(0, S, bs):
+            q1 = min(S, q0 + bs)
+            sc = gemm(q[:, :, q0:q1], k[:, :, :q1], alpha=scale, out_dtype=torch.float32)      # [B, H, bs, q1]
+            P = _softmax_fwd(sc, True, 0, qkv.dtype)
+            del sc
+            gemm(P, v[:, :, :q1], b_mn=True, out=o4[:, :, q0:q1])
+            Ps.append(P)
+        ctx.save_for_backward(qkv, *Ps)
+        ctx.cfg = (B, S, H, Hkv, D, scale, bs)
+        return out.view(B * S, H * D)
+
+    @staticmethod
+    def backward(ctx, dout):
+        qkv, *Ps = ctx.saved_tensors
+        B, S, H, Hkv, D, scale, bs = ctx.cfg
+        g = H // Hkv
+        q, k, v = _split_heads(qkv, B, S, H, Hkv, D)
+        dO = dout.contiguous().view(B, S, H, D).permute(0, 2, 1, 3)
+        dqkv = torch.empty_like(qkv)
+        dq, dk, dv = _split_heads(dqkv, B, S, H, Hkv, D)
+        dk_h = torch.zeros(B, H, S, D, dtype=torch.float32, device=qkv.device)
+        dv_h = torch.zeros(B, H, S, D, dtype=torch.float32, device=qkv.device)
+        for i, q0 in enumerate(range(0, S, bs)):
+            q1 = min(S, q0 + bs)
+            P = Ps[i]
+            dP = gemm(dO[:, :, q0:q1], v[:, :, :q1], out_dtype=torch.float32)
+            dS = _softmax_bwd(P, dP, scale, qkv.dtype)
+            del dP
+            gemm(dS, k[:, :, :q1], b_mn=True, out=dq[:, :, q0:q1])
+            gemm(dS, q[:, :, q0:q1], a_mn=True, b_mn=True, out=dk_h[:, :, :q1], beta=1.0)
+            gemm(P, dO[:, :, q0:q1], a_mn=True, b_mn=True, out=dv_h[:, :, :q1], beta=1.0)
+        if g == 1:
+            dk.copy_(dk_h)
+            dv.copy_(dv_h)
+        else:
+            dk.copy_(dk_h.view(B, Hkv, g, S, D).sum(2))
+            dv.copy_(dv_h.view(B, Hkv, g, S, D).sum(2))
+        return dqkv, None, None, None, None, None, None, None
 
 
 class _TiledAttentionFn(torch.autograd.Function):
@@ -162,4 +218,6 @@ def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, 
             and window == 0 and dropout_p == 0.0:
         from .flash import flash_attention
         return flash_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, scale)
+    if causal and window == 0 and dropout_p == 0.0 and S > _BLOCK_Q and S % 8 == 0:
+        return _BlockedCausalAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, scale, _BLOCK_Q)
     return _TiledAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)

@@ -86,7 +86,7 @@ class DistributedDataParallel(nn.Module):
                     dist.broadcast(b, src=0)
         self._build_buckets(int(bucket_cap_mb * 1024 * 1024))
         self._callback_queued = False
-        self.exposed_ms: List[float] = []
+        self._exposed_events: List[tuple] = []
 
     # ------------------------------------------------------------------ buckets
     def _build_buckets(self, cap_bytes: int) -> None:
@@ -187,7 +187,24 @@ class DistributedDataParallel(nn.Module):
                 else:
                     self.arena.grad[b.lo:b.hi].div_(self.world)
         if self.comm_stream is not None:
-            torch.cuda.current_stream(self.device).wait_stream(self.comm_stream)
+            cur = torch.cuda.current_stream(self.device)
+            # exposed communication = how long the compute stream sits in this wait (events are read lazily)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(cur)
+            cur.wait_stream(self.comm_stream)
+            e1.record(cur)
+            self._exposed_events.append((e0, e1))
+            if len(self._exposed_events) > 64:
+                self._exposed_events.pop(0)
+
+    @property
+    def exposed_ms(self) -> List[float]:
+        """Per-step time (ms) the compute stream waited for the gradient all-reduce after backward had finished."""
+        out = []
+        for e0, e1 in self._exposed_events:
+            if e1.query():
+                out.append(e0.elapsed_time(e1))
+        return out
 
     # ------------------------------------------------------------------ module surface
     def forward(self, *args, **kwargs):

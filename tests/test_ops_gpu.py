@@ -222,7 +222,7 @@ def test_lora_small_kernels(r, p):
     assert rel(dx, dx0.float() + 1.5 * mask * (pm.float() @ a.float())) < 2e-2
 
 
-@pytest.mark.parametrize("H,Hkv,D,S", [(8, 2, 128, 256), (12, 12, 64, 255), (4, 4, 64, 100)])
+@pytest.mark.parametrize("H,Hkv,D,S", [(8, 2, 128, 256), (12, 12, 64, 255), (4, 4, 64, 100), (4, 2, 128, 1536), (2, 2, 64, 1032)])
 def test_attention_tiled(H, Hkv, D, S):
     B = 2
     Sp = (S + 7) // 8 * 8
