@@ -27,7 +27,7 @@ from .gemm import gemm
 vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
 
 
-_BLOCK_Q = 512   # query rows per block of the blocked causal path
+_BLOCK_Q = int(__import__("os").environ.get("B200_ATTN_BLOCK_Q", "512"))   # query rows per block of the blocked causal path
 
 
 def _softmax_fwd(scores, causal, window, out_dtype):

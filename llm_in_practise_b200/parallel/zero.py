@@ -31,6 +31,7 @@ collectives — that path is the CPU test vehicle and the "NCCL baseline" of the
 """
 from __future__ import annotations
 
+import contextlib
 import ctypes
 import json
 import logging
@@ -340,6 +341,7 @@ class ZeroEngine(nn.Module):
         self._stats = torch.zeros(4, dtype=torch.float32, device=dev)
         self._gred = torch.zeros(self.shard_len, dtype=torch.float32, device=dev) if self.use_symm else None
         self._timers: Dict[str, List] = {}
+        self._breakdown = bool(self.config.wall_clock_breakdown) and self.device.type == "cuda"
         self._last_norm = None
 
     # ------------------------------------------------------------------ construction helpers
@@ -385,16 +387,51 @@ class ZeroEngine(nn.Module):
         raise ValueError(f"unsupported scheduler type {sc.get('type')}")
 
     # ------------------------------------------------------------------ training surface
+    @contextlib.contextmanager
+    def _phase(self, name: str):
+        """``wall_clock_breakdown``: a device timer (CUDA event pair, read lazily by ``comm_stats`` /
+        ``wall_clock_report``) and an NVTX range around one phase; free when the option is off."""
+        if not self._breakdown:
+            yield
+            return
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.nvtx.range_push(f"b200.{name}")
+        e0.record()
+        try:
+            yield
+        finally:
+            e1.record()
+            torch.cuda.nvtx.range_pop()
+            lst = self._timers.setdefault(name, [])
+            lst.append((e0, e1))
+            if len(lst) > 256:
+                del lst[:128]
+
+    def wall_clock_report(self) -> Dict[str, float]:
+        """Mean milliseconds per phase (forward / backward / step [/ zero_step]) over the recorded steps, max over ranks."""
+        torch.cuda.synchronize()
+        out = {}
+        for k, evs in self._timers.items():
+            ms = [a.elapsed_time(b) for a, b in evs]
+            if ms:
+                t = torch.tensor([sum(ms) / len(ms)], device=self.device)
+                if self.world > 1:
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                out[k + "_ms"] = float(t)
+        return out
+
     def forward(self, *args, **kwargs):
         ew.set_step(self.global_steps, self.micro_steps % self.ga)
-        return self.module(*args, **kwargs)
+        with self._phase("forward"):
+            return self.module(*args, **kwargs)
 
     def backward(self, loss: torch.Tensor) -> None:
         """Scales by 1/accumulation (and the fp16 loss scale) like DeepSpeed, then backpropagates into the arena."""
         s = 1.0 / self.ga
         if self.scaler is not None:
             s *= self.scaler.scale
-        (loss * s).backward()
+        with self._phase("backward"):
+            (loss * s).backward()
         self.micro_steps += 1
 
     def train_micro_batch(self, input_ids, labels=None, **kw) -> torch.Tensor:
@@ -410,12 +447,13 @@ class ZeroEngine(nn.Module):
         if not self.is_gradient_accumulation_boundary():
             return  # non-boundary micro-steps issue no collective at all
         inv_scale = 1.0 / self.scaler.scale if self.scaler is not None else 1.0
-        if self.world == 1:
-            self._step_single(inv_scale)
-        elif self.use_symm and not self.offload:
-            self._step_fused(inv_scale)
-        else:
-            self._step_collectives(inv_scale)
+        with self._phase("step"):
+            if self.world == 1:
+                self._step_single(inv_scale)
+            elif self.use_symm and not self.offload:
+                self._step_fused(inv_scale)
+            else:
+                self._step_collectives(inv_scale)
         self.arena.zero_grad()
         if self.lr_scheduler is not None:
             self.lr_scheduler.step()

@@ -82,6 +82,13 @@ def build_parser() -> argparse.ArgumentParser:
             caster = {"int": int, "float": float, "str": str, "Optional[int]": int, "Optional[str]": str, "Optional[float]": float}.get(str(f.type), str)
             ap.add_argument(f"--{f.name}", type=caster, default=None)
     ap.add_argument("--per_device_batch_size", type=int, default=None, help="alias of --batch_size (temp/ddp_gpt_wikitext2.py)")
+    # spellings of temp/ddp_gpt_bpe_tokenizer_02.py:55-78 and the DeepSpeed drafts
+    ap.add_argument("--deepspeed_config", type=str, default=None, help="alias of --ds_config")
+    ap.add_argument("--val_split_ratio", type=float, default=None, help="alias of --val_fraction")
+    ap.add_argument("--gradient_accumulation_steps", type=int, default=None, help="alias of --grad_accum")
+    ap.add_argument("--eval_interval", type=int, default=None, help="accepted; validation runs once per epoch")
+    ap.add_argument("--train_tokenizer", action="store_true", help="train a byte-level BPE on the corpus (tokenizer=bytelevel-bpe)")
+    ap.add_argument("--use_pretrained_tokenizer", type=str, default=None, help="name or path of a pretrained tokenizer (tokenizer=<value>)")
     ap.add_argument("--local_rank", type=int, default=None, help="accepted for launcher compatibility")
     return ap
 
@@ -99,6 +106,16 @@ def main(argv=None) -> dict:
             kw[f.name] = v
     if a.per_device_batch_size is not None:
         kw["batch_size"] = a.per_device_batch_size
+    if a.deepspeed_config:
+        kw["ds_config"] = a.deepspeed_config
+    if a.val_split_ratio is not None:
+        kw["val_fraction"] = a.val_split_ratio
+    if a.gradient_accumulation_steps is not None:
+        kw["grad_accum"] = a.gradient_accumulation_steps
+    if a.train_tokenizer:
+        kw["tokenizer"] = "bytelevel-bpe"
+    if a.use_pretrained_tokenizer:
+        kw["tokenizer"] = a.use_pretrained_tokenizer
     try:
         out = run_pretraining(PretrainConfig(**kw))
     finally:

@@ -95,6 +95,7 @@ class PretrainConfig:
     seed_per_rank: bool = False
     save_dir: Optional[str] = None
     save_interval: int = 1
+    keep_last: int = 5
     final_model_path: Optional[str] = None
     resume: bool = False
     early_stop_patience: int = 0
@@ -318,6 +319,8 @@ def run_pretraining(cfg: PretrainConfig) -> Dict[str, Any]:
                 start_epoch = int((client or {}).get("epoch", -1)) + 1
         else:
             cks = sorted(glob.glob(os.path.join(cfg.save_dir, "checkpoint_epoch_*.pt")), key=lambda p: int(p.rsplit("_", 1)[1][:-3]))
+            if os.path.exists(os.path.join(cfg.save_dir, "latest_checkpoint.pt")):
+                cks.append(os.path.join(cfg.save_dir, "latest_checkpoint.pt"))
             if cks and cfg.strategy in ("single", "ddp"):
                 ck = torch.load(cks[-1], map_location=device, weights_only=False)
                 _bare(wrapped).load_state_dict(ck["model_state_dict"])
@@ -327,6 +330,12 @@ def run_pretraining(cfg: PretrainConfig) -> Dict[str, Any]:
                 if scaler is not None and ck.get("scaler_state_dict"):
                     scaler.load_state_dict(ck["scaler_state_dict"])
                 start_epoch, best_val = ck["epoch"] + 1, ck.get("best_val", best_val)
+                global_step = ck.get("global_step", 0)
+                if ck.get("torch_random_state") is not None:
+                    __import__("random").setstate(ck["random_state"])
+                    torch.set_rng_state(ck["torch_random_state"].cpu())
+                    if ck.get("cuda_random_state") is not None and torch.cuda.is_available():
+                        torch.cuda.set_rng_state_all([t.cpu() for t in ck["cuda_random_state"]])
                 log.info("resumed from %s (epoch %d)", cks[-1], ck["epoch"])
 
     log.info("model %s: %.2f M parameters, vocab %d, %d training blocks, world %d, strategy %s", cfg.model, n_params / 1e6, vocab,
@@ -409,8 +418,18 @@ def run_pretraining(cfg: PretrainConfig) -> Dict[str, Any]:
                 ck = {"epoch": epoch, "model_state_dict": _bare(wrapped).state_dict(), "optimizer_state_dict": optimizer.state_dict(),
                       "scheduler_state_dict": scheduler.state_dict() if scheduler is not None else None,
                       "scaler_state_dict": scaler.state_dict() if scaler is not None else None,
-                      "loss": train_loss, "best_val": best_val, "config": asdict(cfg)}
-                torch.save(ck, os.path.join(cfg.save_dir, f"checkpoint_epoch_{epoch + 1}.pt"))
+                      "loss": train_loss, "best_val": best_val, "config": asdict(cfg), "global_step": global_step,
+                      "vocab_size": vocab, "block_size": cfg.block_size,
+                      # RNG streams, so a resumed run draws the same dropout masks / shuffles (temp/ddp_gpt_bpe_tokenizer_02.py:347-383)
+                      "random_state": __import__("random").getstate(), "torch_random_state": torch.get_rng_state(),
+                      "cuda_random_state": torch.cuda.get_rng_state_all() if torch.cuda.is_available() else None}
+                path = os.path.join(cfg.save_dir, f"checkpoint_epoch_{epoch + 1}.pt")
+                torch.save(ck, path)
+                torch.save(ck, os.path.join(cfg.save_dir, "latest_checkpoint.pt"))
+                if cfg.keep_last > 0:                        # keep-last-N rotation (GPTLike_wikitext2_fixed_pe.py:382-401 keeps 5)
+                    old_cks = sorted(glob.glob(os.path.join(cfg.save_dir, "checkpoint_epoch_*.pt")), key=lambda q: int(q.rsplit("_", 1)[1][:-3]))
+                    for q in old_cks[:-cfg.keep_last]:
+                        os.remove(q)
                 if improved:
                     torch.save(_bare(wrapped).state_dict(), os.path.join(cfg.save_dir, "best_model.pt"))
         if distributed:
