@@ -143,6 +143,40 @@ class Generator:
         return gemm(last.contiguous(), m.head_weight(), out_dtype=torch.float32)
 
     @torch.no_grad()
+    def _prefill_packed(self, prompts, cache: KVCache, slots) -> torch.Tensor:
+        """Prefill several prompts of different lengths in ONE pass: the tokens are packed back to back ([T, hidden]
+        through every linear, so the GEMMs see T rows instead of one short problem per prompt), attention runs per
+        sequence through the packed flash kernel, K/V rows are scattered to cache row ``slots[i]``. Returns the
+        last-token logits [n, vocab]."""
+        m, c = self.model, self.cfg
+        dev = m.embed_tokens.device
+        lens = [len(p) for p in prompts]
+        H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
+        cos, sin = m.rope(dev, self.max_len)
+        ids = torch.tensor([t for p in prompts for t in p], device=dev)
+        cu_l = [0]
+        for n in lens:
+            cu_l.append(cu_l[-1] + n)
+        cu = torch.tensor(cu_l, device=dev, dtype=torch.int32)
+        pos = torch.cat([torch.arange(n, dtype=torch.int32) for n in lens]).to(dev)
+        row = torch.repeat_interleave(torch.as_tensor(list(slots), dtype=torch.long), torch.tensor(lens)).to(dev)
+        pl = pos.long()
+        from ..ops.flash import flash_attention_varlen
+        delta, res = ew.embedding(ids, m.embed_tokens), None
+        for li, layer in enumerate(m.layers):
+            x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
+            qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
+            t = qkv.view(-1, H + 2 * Hkv, D)
+            cache.k[li][row, :, pl] = t[:, H:H + Hkv]
+            cache.v[li][row, :, pl] = t[:, H + Hkv:]
+            ctx = flash_attention_varlen(qkv, cu, max(lens), H, Hkv, D, D ** -0.5)
+            x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
+            delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
+        h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)
+        last = h[(cu[1:] - 1).long()].contiguous()
+        return gemm(last, m.head_weight(), out_dtype=torch.float32)
+
+    @torch.no_grad()
     def _decode(self, tok: torch.Tensor, cache: KVCache, pos: Optional[torch.Tensor] = None,
                 slots: Optional[torch.Tensor] = None) -> torch.Tensor:
         """One token per sequence. ``pos`` [B] int32 = tokens already cached per sequence (default: cache.len for

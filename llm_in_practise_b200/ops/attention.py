@@ -2,8 +2,8 @@
 
 Two native paths share this front end:
 
-* ``flash`` (``csrc/flash_attn.cu``, when built and the shape qualifies): tcgen05 QK^T and PV with the
-  score tile living in TMEM, online softmax, no L x L tensor in memory.
+* ``flash`` (``csrc/flash_attn.cu``; 16-bit dtypes, head_dim 64 / 128, no window, no probability dropout): 64 x 64
+  tiles, online softmax forward, recomputing backward, no L x L tensor in memory in either direction.
 * ``tiled`` (always available): batched tcgen05 GEMMs (``csrc/gemm_tcgen05.cu``) around fused
   masked-softmax kernels (``csrc/loss.cu``); scores exist per (batch, head) as a transient.
 
@@ -190,7 +190,7 @@ def _flash_available() -> bool:
     global _flash_ok
     if _flash_ok is None:
         try:
-            _flash_ok = hasattr(nv.lib(), "b200_flash_attn_fwd")
+            _flash_ok = hasattr(nv.lib(), "b200_flash_attn_fwd") and __import__("os").environ.get("B200_FLASH", "1") != "0"
         except Exception:
             _flash_ok = False
     return _flash_ok
@@ -205,6 +205,10 @@ def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, 
         scale = 1.0 / math.sqrt(head_dim)
     if not nv.use_native(qkv) or (S % 8 and not causal) or qkv.dtype == torch.float32 and False:
         return _ref_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)
+    if impl in ("auto", "flash") and _flash_available() and qkv.dtype in (torch.bfloat16, torch.float16) \
+            and head_dim in (64, 128) and window == 0 and dropout_p == 0.0:
+        from .flash import flash_attention
+        return flash_attention(qkv.contiguous(), B, S, n_heads, n_kv_heads, head_dim, causal, scale)
     if S % 8:
         # the score / probability matrices need 16-byte row strides: pad the sequence to a multiple of 8; under the
         # causal mask the real rows never see the padded keys, so the result is exact
@@ -214,10 +218,6 @@ def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, 
         out = attention(qp, B, Sp, n_heads, n_kv_heads, head_dim, causal, window, scale, impl, dropout_p)
         return out.view(B, Sp, -1)[:, :S].reshape(B * S, -1)
     qkv = qkv.contiguous()
-    if impl in ("auto", "flash") and _flash_available() and qkv.dtype == torch.bfloat16 and head_dim == 128 \
-            and window == 0 and dropout_p == 0.0:
-        from .flash import flash_attention
-        return flash_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, scale)
     if causal and window == 0 and dropout_p == 0.0 and S > _BLOCK_Q and S % 8 == 0:
         return _BlockedCausalAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, scale, _BLOCK_Q)
     return _TiledAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)

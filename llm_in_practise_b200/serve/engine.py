@@ -33,7 +33,8 @@ from ..inference.generate import GenerationConfig, Generator, KVCache, sample_ne
 class EngineArgs:
     max_num_seqs: int = 16
     max_model_len: int = 4096
-    max_prefill_per_step: int = 4        # bound on admissions per iteration so decode latency stays flat
+    max_prefill_per_step: int = 8        # bound on admissions per iteration so decode latency stays flat
+    max_prefill_tokens: int = 2048       # ... and on their total prompt tokens (one packed prefill pass per iteration)
     seed: Optional[int] = None
 
 
@@ -245,19 +246,29 @@ class LLMEngine:
     @torch.no_grad()
     def step(self) -> None:
         """One scheduler iteration: admit + prefill, then one batched decode step."""
-        admitted = 0
-        while self.waiting and self.free and admitted < self.args.max_prefill_per_step:
+        batch: List[Request] = []
+        budget = self.args.max_prefill_tokens
+        while self.waiting and self.free and len(batch) < self.args.max_prefill_per_step:
             with self._cv:
+                if batch and len(self.waiting[0].prompt_ids) > budget:
+                    break
                 r = self.waiting.popleft()
             r.slot = self.free.pop()
-            ids = torch.tensor([r.prompt_ids], device=self.device)
-            logits = self.gen._prefill(ids, self.cache, torch.tensor([r.slot], device=self.device))
+            budget -= len(r.prompt_ids)
+            batch.append(r)
+        if batch:
+            # the admitted prompts run as ONE packed pass (token-level batching): GEMMs see the sum of the prompt lengths
+            if len(batch) == 1:
+                r = batch[0]
+                logits = self.gen._prefill(torch.tensor([r.prompt_ids], device=self.device), self.cache,
+                                           torch.tensor([r.slot], device=self.device))
+            else:
+                logits = self.gen._prefill_packed([r.prompt_ids for r in batch], self.cache, [r.slot for r in batch])
             with self.metrics.lock:
-                self.metrics.prompt_tokens += len(r.prompt_ids)
-            tok = self._sample(logits, [r])[0]
-            if not self._emit(r, tok):
-                self.running.append(r)
-            admitted += 1
+                self.metrics.prompt_tokens += sum(len(r.prompt_ids) for r in batch)
+            for r, tok in zip(batch, self._sample(logits, batch)):
+                if not self._emit(r, tok):
+                    self.running.append(r)
         if not self.running:
             return
         reqs = self.running

@@ -93,3 +93,24 @@ def test_cuda_graph_decode_matches_eager():
     reqs = eng.generate([ids[i].tolist() for i in range(3)], GenerationConfig(max_new_tokens=12, do_sample=False))
     assert [r.output_ids for r in reqs] == [a[i, 9:].tolist() for i in range(3)]
     assert 1 <= len(eng.gen._graphs) <= 3
+
+
+def test_packed_prefill_matches_per_prompt_prefill_gpu():
+    """Varlen flash kernel + scattered cache writes: one packed pass over prompts of different lengths (including ones
+    that cross 64-row tile boundaries) equals a prefill per prompt."""
+    from llm_in_practise_b200.inference import Generator
+    from llm_in_practise_b200.inference.generate import KVCache
+    m = _tiny()
+    g = Generator(m, max_len=256)
+    c = m.config
+    gen = torch.Generator().manual_seed(1)
+    prompts = [torch.randint(0, 512, (n,), generator=gen).tolist() for n in (5, 130, 64, 77)]
+    mk = lambda: KVCache(c.num_hidden_layers, 5, c.num_key_value_heads, 256, c.head_dim, torch.bfloat16, "cuda")
+    ca, cb = mk(), mk()
+    slots = [4, 0, 2, 1]
+    packed = g._prefill_packed(prompts, ca, slots)
+    for i, (p, s) in enumerate(zip(prompts, slots)):
+        one = g._prefill(torch.tensor([p], device="cuda"), cb, torch.tensor([s], device="cuda"))
+        assert (packed[i] - one[0]).abs().max() < 0.05 * one.abs().max()
+        assert packed[i].argmax() == one[0].argmax()
+        assert torch.equal(ca.k[0][s, :, :len(p)], cb.k[0][s, :, :len(p)])

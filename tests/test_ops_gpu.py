@@ -239,6 +239,30 @@ def test_attention_tiled(H, Hkv, D, S):
     assert rel(qkv.grad, q32.grad) < 3e-2
 
 
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("H,Hkv,D,S,dtype", [(8, 2, 128, 256, torch.bfloat16), (12, 12, 64, 255, torch.bfloat16),
+                                             (5, 1, 128, 77, torch.float16), (4, 2, 128, 1100, torch.bfloat16),
+                                             (40, 8, 128, 512, torch.bfloat16), (2, 2, 64, 64, torch.float16)])
+def test_flash_attention(H, Hkv, D, S, dtype, causal):
+    """csrc/flash_attn.cu forward + backward against the fp32 reference of the same op (any S, GQA, both mask modes)."""
+    B = 2
+    torch.manual_seed(S + H)
+    qkv = torch.randn(B * S, (H + 2 * Hkv) * D, device=DEV, dtype=dtype, requires_grad=True)
+    out = attention(qkv, B, S, H, Hkv, D, causal=causal, impl="flash")
+    g = torch.randn_like(out)
+    (out * g).sum().backward()
+    q32 = qkv.detach().float().requires_grad_()
+    ref = _ref_attention(q32, B, S, H, Hkv, D, causal, 0, D ** -0.5)
+    (ref * g.float()).sum().backward()
+    assert rel(out, ref) < 2e-2
+    W = (H + 2 * Hkv) * D
+    for name, lo, hi in (("dq", 0, H * D), ("dk", H * D, (H + Hkv) * D), ("dv", (H + Hkv) * D, W)):
+        assert rel(qkv.grad[:, lo:hi], q32.grad[:, lo:hi]) < 3e-2, name
+    with torch.no_grad():
+        out2 = attention(qkv, B, S, H, Hkv, D, causal=causal)
+    assert torch.equal(out2, out)
+
+
 def test_adamw_and_8bit():
     from llm_in_practise_b200.optim import FusedAdamW, PagedAdamW8bit
     from llm_in_practise_b200.utils.arena import ParamArena

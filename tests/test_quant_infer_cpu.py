@@ -136,3 +136,22 @@ def test_eos_stops_and_streamer():
     st = TextIteratorStreamer(Tok())
     g.generate(ids, max_new_tokens=5, do_sample=False, streamer=st)
     assert len("".join(st)) == 5
+
+
+def test_packed_prefill_matches_per_prompt_prefill():
+    """Several prompts of different lengths in one packed pass == one prefill each (logits and cached K/V)."""
+    from llm_in_practise_b200.inference.generate import KVCache
+    m = tiny()
+    g = Generator(m, max_len=64)
+    c = m.config
+    prompts = [[5, 9, 200, 3, 17], [11, 12], [7] * 13]
+    mk = lambda: KVCache(c.num_hidden_layers, 4, c.num_key_value_heads, 64, c.head_dim, torch.float32, "cpu")
+    ca, cb = mk(), mk()
+    slots = [2, 0, 3]
+    packed = g._prefill_packed(prompts, ca, slots)
+    for i, (p, s) in enumerate(zip(prompts, slots)):
+        one = g._prefill(torch.tensor([p]), cb, torch.tensor([s]))
+        torch.testing.assert_close(packed[i:i + 1], one, rtol=1e-4, atol=1e-4)
+        for li in range(c.num_hidden_layers):
+            torch.testing.assert_close(ca.k[li][s, :, :len(p)], cb.k[li][s, :, :len(p)], rtol=1e-5, atol=1e-5)
+            torch.testing.assert_close(ca.v[li][s, :, :len(p)], cb.v[li][s, :, :len(p)], rtol=1e-5, atol=1e-5)
