@@ -20,6 +20,8 @@
 #include "common.cuh"
 #include "../include/b200_ops.h"
 
+#include <stdlib.h>
+
 namespace b200 {
 
 struct FlashParams {
@@ -453,6 +455,209 @@ flash_bwd_kernel(const FlashParams p) {
   }
 }
 
+// Backward with 128-query blocks: same math as flash_bwd_kernel, warp tiles of 32 x 32 (S, dP, dK, dV) and 32 x 64 (dQ) so
+// every ldmatrix feeds twice as many MMAs (the 64-query kernel is bound by shared-memory bandwidth, not by the tensor pipe).
+template <bool BF16, int D, bool CAUSAL>
+__global__ void __launch_bounds__(256, 1)
+flash_bwd128_kernel(const FlashParams p) {
+  constexpr int CH = D / 8, KS = D / 16, NT = 256;
+  constexpr uint32_t kTile = 64 * D * 2, kPT = 128 * 64 * 2;
+  extern __shared__ __align__(128) uint8_t fsm[];
+  // K | V | Q[2][128] | dO[2][128] | P[128][64] | dS[128][64] | lse[2][128] | delta[2][128]
+  const uint32_t sK = smem_u32(fsm), sV = sK + kTile, sQ = sV + kTile, sdO = sQ + 4 * kTile, sP = sdO + 4 * kTile, sdS = sP + kPT;
+  uint8_t* pP = fsm + 10 * kTile;
+  uint8_t* pS = pP + kPT;
+  float* sL = reinterpret_cast<float*>(fsm + 10 * kTile + 2 * kPT);
+  float* sDl = sL + 256;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31, g = lane >> 2, t = lane & 3;
+  const int kb = blockIdx.x, h = blockIdx.y, b = blockIdx.z, hk = h / (p.H / p.Hkv);
+  const int S = p.S, k0 = kb * 64, nqb = (S + 127) / 128;
+  const uint16_t* base = reinterpret_cast<const uint16_t*>(p.qkv) + (long long)b * S * p.W;
+  const uint16_t* gq = base + (long long)h * D;
+  const uint16_t* gk = base + (long long)(p.H + hk) * D;
+  const uint16_t* gv = base + (long long)(p.H + p.Hkv + hk) * D;
+  const uint16_t* gdo = reinterpret_cast<const uint16_t*>(p.dout) + (long long)b * S * p.H * D + (long long)h * D;
+  const float* glse = p.lse + ((long long)b * p.H + h) * S;
+  const float* gdl = p.delta + ((long long)b * p.H + h) * S;
+  const int qb0 = CAUSAL ? (k0 >> 7) : 0;
+
+  auto load_q = [&](int qb, int buf) {
+    load_tile64<D, NT>(sQ + buf * 2 * kTile, gq, p.W, qb * 128, S, tid);
+    load_tile64<D, NT>(sQ + buf * 2 * kTile + kTile, gq, p.W, qb * 128 + 64, S, tid);
+    load_tile64<D, NT>(sdO + buf * 2 * kTile, gdo, (long long)p.H * D, qb * 128, S, tid);
+    load_tile64<D, NT>(sdO + buf * 2 * kTile + kTile, gdo, (long long)p.H * D, qb * 128 + 64, S, tid);
+    if (tid < 128) {
+      const int r = qb * 128 + tid;
+      sL[buf * 128 + tid] = r < S ? glse[r] * kLog2e : 0.f;
+      sDl[buf * 128 + tid] = r < S ? gdl[r] : 0.f;
+    }
+  };
+  load_tile64<D, NT>(sK, gk, p.W, k0, S, tid);
+  load_tile64<D, NT>(sV, gv, p.W, k0, S, tid);
+  load_q(qb0, 0);
+  cp_async_commit();
+
+  // dK / dV: warp tile = keys 32 kg .. x d columns 32 dq ..
+  const int kg = warp & 1, dq4 = warp >> 1;
+  float dk[2][4][4], dv[2][4][4];
+#pragma unroll
+  for (int m = 0; m < 2; ++m)
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) { dk[m][i][c] = 0.f; dv[m][i][c] = 0.f; }
+  const int rq = warp & 3, ck = warp >> 2;   // S / dP: queries 32 rq .., keys 32 ck ..;  dQ: queries 32 rq .., d 64 ck ..
+
+  for (int qb = qb0; qb < nqb; ++qb) {
+    const int buf = (qb - qb0) & 1;
+    const uint32_t cQ = sQ + buf * 2 * kTile, cdO = sdO + buf * 2 * kTile;   // 128 rows: row r lives in tile r / 64
+    if (qb + 1 < nqb) {
+      load_q(qb + 1, buf ^ 1);
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    {
+      float s[2][4][4], dp[2][4][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) { s[m][i][c] = 0.f; dp[m][i][c] = 0.f; }
+      const uint32_t tq = cQ + (rq >> 1) * kTile, tdo = cdO + (rq >> 1) * kTile;
+      const int r0 = (rq & 1) * 32;
+#pragma unroll
+      for (int ks = 0; ks < KS; ++ks) {
+        uint32_t aq[2][4], ad[2][4];
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          load_a<CH>(tq, r0 + m * 16, ks, lane, aq[m]);
+          load_a<CH>(tdo, r0 + m * 16, ks, lane, ad[m]);
+        }
+#pragma unroll
+        for (int np = 0; np < 2; ++np) {
+          uint32_t bk[4], bv[4];
+          load_b_nk<CH>(sK, ck * 32 + np * 16, ks, lane, bk);
+          load_b_nk<CH>(sV, ck * 32 + np * 16, ks, lane, bv);
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            mma_16816<BF16>(s[m][2 * np], aq[m][0], aq[m][1], aq[m][2], aq[m][3], bk[0], bk[1]);
+            mma_16816<BF16>(s[m][2 * np + 1], aq[m][0], aq[m][1], aq[m][2], aq[m][3], bk[2], bk[3]);
+            mma_16816<BF16>(dp[m][2 * np], ad[m][0], ad[m][1], ad[m][2], ad[m][3], bv[0], bv[1]);
+            mma_16816<BF16>(dp[m][2 * np + 1], ad[m][0], ad[m][1], ad[m][2], ad[m][3], bv[2], bv[3]);
+          }
+        }
+      }
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        const int lrA = rq * 32 + m * 16 + g, lrB = lrA + 8;
+        const float lA = sL[buf * 128 + lrA], lB = sL[buf * 128 + lrB], dA = sDl[buf * 128 + lrA], dB = sDl[buf * 128 + lrB];
+        const int qA = qb * 128 + lrA, qB = qA + 8;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float pv[4], dsv[4];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int key = k0 + ck * 32 + i * 8 + 2 * t + (c & 1), q = (c & 2) ? qB : qA;
+            const bool ok = key < S && q < S && (!CAUSAL || key <= q);
+            const float pr = ok ? exp2f(s[m][i][c] * p.scale_log2 - ((c & 2) ? lB : lA)) : 0.f;
+            pv[c] = pr;
+            dsv[c] = pr * (dp[m][i][c] - ((c & 2) ? dB : dA)) * p.scale;
+          }
+          const int chunk = ck * 4 + i;
+          *reinterpret_cast<uint32_t*>(pP + tile_off<8>(lrA, chunk) + t * 4) = pack16<BF16>(pv[0], pv[1]);
+          *reinterpret_cast<uint32_t*>(pP + tile_off<8>(lrB, chunk) + t * 4) = pack16<BF16>(pv[2], pv[3]);
+          *reinterpret_cast<uint32_t*>(pS + tile_off<8>(lrA, chunk) + t * 4) = pack16<BF16>(dsv[0], dsv[1]);
+          *reinterpret_cast<uint32_t*>(pS + tile_off<8>(lrB, chunk) + t * 4) = pack16<BF16>(dsv[2], dsv[3]);
+        }
+      }
+    }
+    __syncthreads();
+    // dV += P^T dO, dK += dS^T Q over the 128 queries of this block
+#pragma unroll
+    for (int kk = 0; kk < 8; ++kk) {
+      uint32_t ap[2][4], as[2][4];
+      const uint32_t tq = cQ + (kk >> 2) * kTile, tdo = cdO + (kk >> 2) * kTile;
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        load_a_t<8>(sP, kk * 16, kg * 4 + m * 2, lane, ap[m]);
+        load_a_t<8>(sdS, kk * 16, kg * 4 + m * 2, lane, as[m]);
+      }
+#pragma unroll
+      for (int np = 0; np < 2; ++np) {
+        uint32_t bo[4], bq[4];
+        load_b_kn<CH>(tdo, (kk & 3) * 16, dq4 * 4 + np * 2, lane, bo);
+        load_b_kn<CH>(tq, (kk & 3) * 16, dq4 * 4 + np * 2, lane, bq);
+#pragma unroll
+        for (int m = 0; m < 2; ++m) {
+          mma_16816<BF16>(dv[m][2 * np], ap[m][0], ap[m][1], ap[m][2], ap[m][3], bo[0], bo[1]);
+          mma_16816<BF16>(dv[m][2 * np + 1], ap[m][0], ap[m][1], ap[m][2], ap[m][3], bo[2], bo[3]);
+          mma_16816<BF16>(dk[m][2 * np], as[m][0], as[m][1], as[m][2], as[m][3], bq[0], bq[1]);
+          mma_16816<BF16>(dk[m][2 * np + 1], as[m][0], as[m][1], as[m][2], as[m][3], bq[2], bq[3]);
+        }
+      }
+    }
+    // dQ[32 rq .., d half ck] = dS K
+    {
+      constexpr int NP = D / 32;   // n-tile pairs in this warp's half of the head dimension
+      float dq[2][2 * NP][4];
+#pragma unroll
+      for (int m = 0; m < 2; ++m)
+#pragma unroll
+        for (int i = 0; i < 2 * NP; ++i)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) dq[m][i][c] = 0.f;
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        uint32_t as[2][4];
+        load_a<8>(sdS, rq * 32, kk, lane, as[0]);
+        load_a<8>(sdS, rq * 32 + 16, kk, lane, as[1]);
+#pragma unroll
+        for (int np = 0; np < NP; ++np) {
+          uint32_t bk[4];
+          load_b_kn<CH>(sK, kk * 16, ck * (CH / 2) + 2 * np, lane, bk);
+#pragma unroll
+          for (int m = 0; m < 2; ++m) {
+            mma_16816<BF16>(dq[m][2 * np], as[m][0], as[m][1], as[m][2], as[m][3], bk[0], bk[1]);
+            mma_16816<BF16>(dq[m][2 * np + 1], as[m][0], as[m][1], as[m][2], as[m][3], bk[2], bk[3]);
+          }
+        }
+      }
+      float* gdq = p.dqkv32 + (long long)b * S * p.W + (long long)h * D + ck * (D / 2) + 2 * t;
+#pragma unroll
+      for (int m = 0; m < 2; ++m) {
+        const int qA = qb * 128 + rq * 32 + m * 16 + g, qB = qA + 8;
+#pragma unroll
+        for (int i = 0; i < 2 * NP; ++i) {
+          if (qA < S) red_add_v2(gdq + (long long)qA * p.W + i * 8, dq[m][i][0], dq[m][i][1]);
+          if (qB < S) red_add_v2(gdq + (long long)qB * p.W + i * 8, dq[m][i][2], dq[m][i][3]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  float* gdk = p.dqkv32 + (long long)b * S * p.W + (long long)(p.H + hk) * D + dq4 * 32 + 2 * t;
+  float* gdv = p.dqkv32 + (long long)b * S * p.W + (long long)(p.H + p.Hkv + hk) * D + dq4 * 32 + 2 * t;
+#pragma unroll
+  for (int m = 0; m < 2; ++m) {
+    const int keyA = k0 + kg * 32 + m * 16 + g, keyB = keyA + 8;
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      if (keyA < S) {
+        red_add_v2(gdk + (long long)keyA * p.W + i * 8, dk[m][i][0], dk[m][i][1]);
+        red_add_v2(gdv + (long long)keyA * p.W + i * 8, dv[m][i][0], dv[m][i][1]);
+      }
+      if (keyB < S) {
+        red_add_v2(gdk + (long long)keyB * p.W + i * 8, dk[m][i][2], dk[m][i][3]);
+        red_add_v2(gdv + (long long)keyB * p.W + i * 8, dv[m][i][2], dv[m][i][3]);
+      }
+    }
+  }
+}
+
 // dqkv (16-bit) = dqkv32
 template <bool BF16>
 __global__ void __launch_bounds__(256)
@@ -478,14 +683,38 @@ static int launch_fwd(const FlashParams& p, int causal, cudaStream_t st) {
   return 0;
 }
 
+template <bool BF16>
+static int finish_bwd(const FlashParams& p, void* dqkv, cudaStream_t st) {
+  const long long n4 = (long long)p.B * p.S * p.W / 4;
+  const unsigned cg = (unsigned)((n4 + 255) / 256 < kNumSMs * 8 ? (n4 + 255) / 256 : kNumSMs * 8);
+  flash_cast_kernel<BF16><<<cg, 256, 0, st>>>(reinterpret_cast<const float4*>(p.dqkv32), reinterpret_cast<uint2*>(dqkv), n4);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
 template <bool BF16, int D>
 static int launch_bwd(const FlashParams& p, const void* out, void* dqkv, int causal, cudaStream_t st) {
   const long long rows = (long long)p.B * p.S * p.H;
   flash_delta_kernel<BF16, D><<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(
       reinterpret_cast<const uint16_t*>(out), reinterpret_cast<const uint16_t*>(p.dout), const_cast<float*>(p.delta), p.B, p.S, p.H);
   B200_LAUNCH_CHECK();
-  const int smem = 6 * 64 * D * 2 + 2 * 64 * 64 * 2 + 4 * 64 * 4;
   const dim3 grid((p.S + 63) / 64, p.H, p.B);
+  static const bool force64 = getenv("B200_FLASH_BWD64") != nullptr;
+  if constexpr (D == 128) {
+    if (!force64 && p.S > 64) {
+      const int smem128 = 10 * 64 * D * 2 + 2 * 128 * 64 * 2 + 4 * 128 * 4;
+      if (causal) {
+        B200_CHECK(cudaFuncSetAttribute(flash_bwd128_kernel<BF16, D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem128));
+        flash_bwd128_kernel<BF16, D, true><<<grid, 256, smem128, st>>>(p);
+      } else {
+        B200_CHECK(cudaFuncSetAttribute(flash_bwd128_kernel<BF16, D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem128));
+        flash_bwd128_kernel<BF16, D, false><<<grid, 256, smem128, st>>>(p);
+      }
+      B200_LAUNCH_CHECK();
+      return finish_bwd<BF16>(p, dqkv, st);
+    }
+  }
+  const int smem = 6 * 64 * D * 2 + 2 * 64 * 64 * 2 + 4 * 64 * 4;
   if (causal) {
     B200_CHECK(cudaFuncSetAttribute(flash_bwd_kernel<BF16, D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     flash_bwd_kernel<BF16, D, true><<<grid, 256, smem, st>>>(p);
@@ -494,11 +723,7 @@ static int launch_bwd(const FlashParams& p, const void* out, void* dqkv, int cau
     flash_bwd_kernel<BF16, D, false><<<grid, 256, smem, st>>>(p);
   }
   B200_LAUNCH_CHECK();
-  const long long n4 = (long long)p.B * p.S * p.W / 4;
-  const unsigned cg = (unsigned)((n4 + 255) / 256 < kNumSMs * 8 ? (n4 + 255) / 256 : kNumSMs * 8);
-  flash_cast_kernel<BF16><<<cg, 256, 0, st>>>(reinterpret_cast<const float4*>(p.dqkv32), reinterpret_cast<uint2*>(dqkv), n4);
-  B200_LAUNCH_CHECK();
-  return 0;
+  return finish_bwd<BF16>(p, dqkv, st);
 }
 
 static int flash_check(int B, int S, int H, int Hkv, int D, int dtype) {
