@@ -36,6 +36,7 @@ class EngineArgs:
     max_prefill_per_step: int = 8        # bound on admissions per iteration so decode latency stays flat
     max_prefill_tokens: int = 2048       # ... and on their total prompt tokens (one packed prefill pass per iteration)
     seed: Optional[int] = None
+    warmup: bool = True                  # capture the prefill / decode CUDA graphs in start() instead of in the first requests
 
 
 @dataclass
@@ -114,6 +115,26 @@ class LLMEngine:
         self.model.eval()
 
     # ------------------------------------------------------------------ client side
+    @torch.no_grad()
+    def warmup(self) -> None:
+        """Capture the CUDA graphs of every prefill bucket and decode bucket up front (dummy tokens in the scratch cache
+        row), so no request pays a capture (~0.1 s each) in its time to first token."""
+        if self.device.type != "cuda":
+            return
+        scratch = self.args.max_num_seqs
+        for tb in self.gen._PREFILL_BUCKETS:
+            if tb < self.args.max_model_len:
+                self.gen._prefill_packed([[0] * tb], self.cache, [scratch], scratch_slot=scratch)
+        nb = 1
+        while True:
+            z = torch.zeros(nb, dtype=torch.int32, device=self.device)
+            self.gen.decode_graphed(torch.zeros(nb, dtype=torch.long, device=self.device), self.cache, z,
+                                    torch.full((nb,), scratch, dtype=torch.int32, device=self.device))
+            if nb >= self.args.max_num_seqs:
+                break
+            nb *= 2
+        torch.cuda.synchronize()
+
     def submit(self, prompt_ids: Sequence[int], cfg: Optional[GenerationConfig] = None) -> Request:
         cfg = cfg or GenerationConfig()
         ids = list(prompt_ids)
@@ -141,6 +162,8 @@ class LLMEngine:
 
     def start(self) -> "LLMEngine":
         if self._thread is None:
+            if self.args.warmup:
+                self.warmup()
             self._stop = False
             self._thread = threading.Thread(target=self._loop, name="b200-engine", daemon=True)
             self._thread.start()
@@ -258,7 +281,11 @@ class LLMEngine:
             batch.append(r)
         if batch:
             # the admitted prompts run as ONE packed pass (token-level batching): GEMMs see the sum of the prompt lengths
-            if len(batch) == 1:
+            if self.device.type == "cuda":
+                # ... replayed from a CUDA graph per token-count bucket; padding tokens land in the scratch cache row
+                logits = self.gen._prefill_packed([r.prompt_ids for r in batch], self.cache, [r.slot for r in batch],
+                                                  scratch_slot=self.args.max_num_seqs)
+            elif len(batch) == 1:
                 r = batch[0]
                 logits = self.gen._prefill(torch.tensor([r.prompt_ids], device=self.device), self.cache,
                                            torch.tensor([r.slot], device=self.device))

@@ -50,6 +50,7 @@ gcfg = GenerationConfig(max_new_tokens=a.output_len, do_sample=False, eos_token_
 rows = []
 for C in a.concurrency:
     eng = LLMEngine(model, None, EngineArgs(max_num_seqs=C, max_model_len=a.max_model_len, max_prefill_per_step=8), model_name=a.model)
+    eng.warmup()
     # warm-up: a few requests through prefill and decode (graph capture, lazily built buffers)
     for r in eng.generate(prompts[:min(C, 8)], GenerationConfig(max_new_tokens=8, do_sample=False, eos_token_id=[])):
         assert r.error is None, r.error

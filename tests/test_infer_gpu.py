@@ -114,3 +114,13 @@ def test_packed_prefill_matches_per_prompt_prefill_gpu():
         assert (packed[i] - one[0]).abs().max() < 0.05 * one.abs().max()
         assert packed[i].argmax() == one[0].argmax()
         assert torch.equal(ca.k[0][s, :, :len(p)], cb.k[0][s, :, :len(p)])
+    # CUDA-graph path: bucketed token count, padded sequence count, padding tokens land in the scratch cache row
+    cc = mk()
+    for _ in range(2):                       # capture, then replay
+        graphed = g._prefill_packed(prompts, cc, slots, scratch_slot=3)
+        assert (graphed - packed).abs().max() < 0.02 * packed.abs().max()
+    other = [torch.randint(0, 512, (n,), generator=gen).tolist() for n in (31, 200)]   # another bucket, other lengths
+    g2 = g._prefill_packed(other, cc, [0, 1], scratch_slot=3)
+    e2 = g._prefill_packed(other, cb, [0, 1])
+    assert (g2 - e2).abs().max() < 0.02 * e2.abs().max()
+    assert torch.equal(cc.k[1][1, :, :200], cb.k[1][1, :, :200])
