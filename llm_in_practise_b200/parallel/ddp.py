@@ -91,6 +91,9 @@ class DistributedDataParallel(nn.Module):
     # ------------------------------------------------------------------ buckets
     def _build_buckets(self, cap_bytes: int) -> None:
         es = self.arena.data.element_size()
+        # module parameters are views of the working-weight buffer: the fp32 arena itself, or its low-precision twin
+        lowp = getattr(self.arena, "lowp", None)
+        pbase, pes = (lowp.data_ptr(), lowp.element_size()) if lowp is not None else (self.arena.data.data_ptr(), es)
         owners = {}
         for _, p in self.module.named_parameters():
             if p.requires_grad:
@@ -101,7 +104,7 @@ class DistributedDataParallel(nn.Module):
         lo = hi
         for _, shape, off in reversed(list(self.arena.named_slots())):   # reverse registration order
             lo = off
-            p = owners.get(self.arena.data.data_ptr() + off * es)
+            p = owners.get(pbase + off * pes)
             if p is not None:
                 params.append(p)
             if (hi - lo) * es >= cap_bytes:
