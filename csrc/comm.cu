@@ -124,6 +124,80 @@ allreduce_kernel(PeerPtrs data, PeerPtrs flags, PeerPtrs lowp, long long n, int 
 }
 
 // ---------------------------------------------------------------------------------------------
+// K-C5 (decode): one-shot all-reduce (sum) of a small 16-bit activation [tokens, hidden] for tensor-parallel decode.
+// Everything the kernel needs between launches lives on the device (state[0] = epoch, state[1] = grid-barrier ticket,
+// state[2] = exit ticket), so the same launch can be replayed from a CUDA graph on every rank — the two-shot kernel
+// above takes its epoch from the host and cannot be.
+//   A: copy y into this rank's half (epoch parity) of the symmetric 16-bit staging buffer; grid barrier
+//   B: publish epoch e to every peer, wait for every peer's e
+//   C: every rank sums all staged copies in rank order (bitwise identical results everywhere) into its own `out`
+// A staging half is rewritten two epochs later; by then every peer has signalled epoch e + 1, which it only does after
+// it has finished reading epoch e. The grid is fixed (kOneShotGrid CTAs, all co-resident).
+// ---------------------------------------------------------------------------------------------
+constexpr int kOneShotGrid = 32;
+
+template <bool BF16>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_oneshot_kernel(const uint4* __restrict__ y, PeerPtrs stage, PeerPtrs flags, uint4* __restrict__ out,
+                         long long nvec, long long half_vec, int world, int rank, int channel, unsigned int* state) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const uint32_t e = *((volatile unsigned int*)state) + 1u;
+  const long long base = (long long)(e & 1u) * half_vec;
+  uint4* mine = reinterpret_cast<uint4*>(stage.p[rank]) + base;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) mine[i] = y[i];
+  __threadfence_system();
+  // ticket barrier: the counter only ever serves this kernel with this grid size
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int old = atomicAdd(state + 1, 1u);
+    const unsigned int target = (old / gridDim.x + 1u) * gridDim.x;
+    const long long t0 = clock64();
+    while ((int)(*((volatile unsigned int*)(state + 1)) - target) < 0) {
+      if (clock64() - t0 > 20000000000ll) { printf("b200 comm: one-shot grid barrier timed out (block %d)\n", blockIdx.x); __trap(); }
+    }
+    __threadfence_system();
+  }
+  __syncthreads();
+  if (blockIdx.x == 0) signal_all(flags, channel, world, rank, e);
+  wait_all(flags, channel, world, rank, e);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r) {
+      if (r < world) {
+        const uint4 v = (reinterpret_cast<const uint4*>(stage.p[r]) + base)[i];
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float2 f;
+          if (BF16) f = unpack_bf16x2(w[j]);
+          else f = __half22float2(*reinterpret_cast<const __half2*>(&w[j]));
+          acc[2 * j] += f.x; acc[2 * j + 1] += f.y;
+        }
+      }
+    }
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (BF16) o[j] = pack_bf16x2(acc[2 * j], acc[2 * j + 1]);
+      else { const __half2 hh = __floats2half2_rn(acc[2 * j], acc[2 * j + 1]); o[j] = *reinterpret_cast<const uint32_t*>(&hh); }
+    }
+    out[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tkt = atomicAdd(state + 2, 1u);
+    if (tkt == gridDim.x - 1) {
+      state[2] = 0u;
+      __threadfence();
+      *((volatile unsigned int*)state) = e;   // the next launch (stream order) sees the new epoch
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // K-C2: ZeRO step.
 // ---------------------------------------------------------------------------------------------
 struct ZeroStepParams {
@@ -398,6 +472,23 @@ B200_API int b200_peer_gather(const void* const* src_ptrs, long long src_off_byt
 B200_API int b200_peer_gather_skip(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
                                    int world, int skip, void* stream) {
   return peer_gather_launch(src_ptrs, src_off_bytes, out, shard_bytes, world, skip, stream);
+}
+
+B200_API int b200_allreduce_oneshot(const void* y, const void* const* stage_ptrs, const void* const* flag_ptrs, void* out,
+                                    long long n, long long half_elems, int world, int rank, int channel,
+                                    unsigned int* state, int dtype, void* stream) {
+  if (world < 1 || world > kMaxRanks || n < 8 || n % 8 || half_elems % 8 || n > half_elems) return B200_ERR_BAD_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(out)) & 15) return B200_ERR_BAD_ALIGN;
+  cudaStream_t st = (cudaStream_t)stream;
+  cudaError_t e;
+  if (dtype == B200_DT_BF16)
+    e = launch_pdl(allreduce_oneshot_kernel<true>, kOneShotGrid, kCommThreads, 0, st, (const uint4*)y, to_peers(stage_ptrs, world),
+                   to_peers(flag_ptrs, world), (uint4*)out, n / 8, half_elems / 8, world, rank, channel, state);
+  else if (dtype == B200_DT_FP16)
+    e = launch_pdl(allreduce_oneshot_kernel<false>, kOneShotGrid, kCommThreads, 0, st, (const uint4*)y, to_peers(stage_ptrs, world),
+                   to_peers(flag_ptrs, world), (uint4*)out, n / 8, half_elems / 8, world, rank, channel, state);
+  else return B200_ERR_UNSUPPORTED;
+  return (int)e;
 }
 
 B200_API int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int rank, unsigned int epoch,

@@ -39,6 +39,8 @@ decode_attn_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __rest
                    const int* __restrict__ pos, const int* __restrict__ slots, T* __restrict__ out, int H, int Hkv, int max_len,
                    float scale, int window) {
   constexpr int PER = D / 32;  // elements per lane
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.x / H, h = blockIdx.x % H;
   const int kvh = h / (H / Hkv);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -143,6 +145,8 @@ decode_attn_split_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* 
                          const int* __restrict__ pos, const int* __restrict__ slots, float* __restrict__ part, int H, int Hkv,
                          int max_len, float scale, int nsplit) {
   constexpr int PER = D / 32, CH = D / 8;   // output channels per lane; 16-byte chunks per row
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ __align__(16) float qs[G][D];
   __shared__ float ps[4][G][32];
   __shared__ float sm_m[4][G], sm_l[4][G];
@@ -250,6 +254,8 @@ decode_attn_split_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* 
 template <typename T, int D>
 __global__ void __launch_bounds__(D)
 decode_attn_combine_kernel(const float* __restrict__ part, T* __restrict__ out, int nsplit) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long bh = blockIdx.x;   // b * H + h
   const int d = threadIdx.x;
   const float* p = part + bh * nsplit * (D + 2);
@@ -280,9 +286,9 @@ B200_API int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_
   const unsigned grid = (unsigned)(B * Hkv * nsplit), grid2 = (unsigned)(B * H);
 #define B200_DS(T, DD, GG)                                                                                              \
   do {                                                                                                                  \
-    decode_attn_split_kernel<T, DD, GG><<<grid, 128, 0, st>>>((const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, scratch, \
-                                                              H, Hkv, max_len, scale, nsplit);                         \
-    decode_attn_combine_kernel<T, DD><<<grid2, DD, 0, st>>>(scratch, (T*)out, nsplit);                                  \
+    launch_pdl(decode_attn_split_kernel<T, DD, GG>, grid, 128, 0, st, (const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, \
+               scratch, H, Hkv, max_len, scale, nsplit);                                                               \
+    launch_pdl(decode_attn_combine_kernel<T, DD>, grid2, DD, 0, st, (const float*)scratch, (T*)out, nsplit);            \
   } while (0)
 #define B200_DS_G(T, DD)                                                         \
   if (G == 1) B200_DS(T, DD, 1); else if (G == 2) B200_DS(T, DD, 2);              \
@@ -304,7 +310,7 @@ B200_API int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, con
   if (B <= 0 || H % Hkv) return B200_ERR_BAD_SHAPE;
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned grid = (unsigned)(B * H);
-#define B200_DA(T, DD) decode_attn_kernel<T, DD><<<grid, 128, 0, st>>>((const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, (T*)out, H, Hkv, max_len, scale, window)
+#define B200_DA(T, DD) launch_pdl(decode_attn_kernel<T, DD>, grid, 128, 0, st, (const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, (T*)out, H, Hkv, max_len, scale, window)
   if (dtype == B200_DT_BF16) {
     if (D == 128) B200_DA(__nv_bfloat16, 128); else if (D == 64) B200_DA(__nv_bfloat16, 64);
     else if (D == 32) B200_DA(__nv_bfloat16, 32); else if (D == 96) B200_DA(__nv_bfloat16, 96); else return B200_ERR_UNSUPPORTED;

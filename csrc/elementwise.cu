@@ -65,6 +65,8 @@ qknorm_rope_fwd_kernel(const T* __restrict__ src, T* __restrict__ dst, const T* 
                        const T* __restrict__ kw, const float* __restrict__ cos_t, const float* __restrict__ sin_t,
                        const int* __restrict__ pos, int tokens, int n_q, int n_k, int n_v, int D, long long src_rs,
                        long long dst_rs, int interleaved, float eps, float* __restrict__ rstd_out) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int lane = threadIdx.x & 31;
   const int heads = n_q + n_k + n_v;
@@ -207,6 +209,8 @@ qknorm_rope_bwd_kernel(const T* __restrict__ g_in, const T* __restrict__ raw, T*
 // ---------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void swiglu_fwd_kernel(const T* __restrict__ gu, T* __restrict__ h, long long rows, int F) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int V = 16 / sizeof(T);
   const long long idx = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * V;
   if (idx >= rows * F) return;
@@ -302,6 +306,8 @@ template <typename T>
 __global__ void embedding_fwd_kernel(const long long* __restrict__ ids, const T* __restrict__ table,
                                      const T* __restrict__ pos_table, T* __restrict__ out, long long tokens, int dim,
                                      int period, float scale) {
+  pdl_launch_dependents();
+  pdl_wait();
   constexpr int V = 16 / sizeof(T);
   const long long t = blockIdx.x;
   const long long id = ids[t];
@@ -375,7 +381,7 @@ B200_API int b200_qknorm_rope_fwd(const void* src, void* dst, const void* qw, co
   const long long warps = (long long)tokens * (n_q + n_k + n_v);
   const int tb = 256;
   const unsigned grid = (unsigned)((warps * 32 + tb - 1) / tb);
-  B200_DISPATCH_T(dtype, qknorm_rope_fwd_kernel<T><<<grid, tb, 0, (cudaStream_t)stream>>>(
+  B200_DISPATCH_T(dtype, launch_pdl(qknorm_rope_fwd_kernel<T>, grid, tb, 0, (cudaStream_t)stream, 
       (const T*)src, (T*)dst, (const T*)qw, (const T*)kw, cos_t, sin_t, pos, tokens, n_q, n_k, n_v, D, src_rs, dst_rs,
       interleaved, eps, rstd_out));
   B200_LAUNCH_CHECK();
@@ -403,7 +409,7 @@ B200_API int b200_swiglu_fwd(const void* gu, void* h, long long rows, int F, int
   const long long nvec = rows * F / V;
   const int tb = 256;
   const unsigned grid = (unsigned)((nvec + tb - 1) / tb);
-  B200_DISPATCH_T(dtype, swiglu_fwd_kernel<T><<<grid, tb, 0, (cudaStream_t)stream>>>((const T*)gu, (T*)h, rows, F));
+  B200_DISPATCH_T(dtype, launch_pdl(swiglu_fwd_kernel<T>, grid, tb, 0, (cudaStream_t)stream, (const T*)gu, (T*)h, rows, F));
   B200_LAUNCH_CHECK();
   return 0;
 }
@@ -444,7 +450,7 @@ B200_API int b200_embedding_fwd(const long long* ids, const void* table, const v
   if (dim % V || tokens <= 0) return B200_ERR_BAD_SHAPE;
   int tb = dim / V;
   tb = tb > 256 ? 256 : (tb < 32 ? 32 : (tb + 31) / 32 * 32);
-  B200_DISPATCH_T(dtype, embedding_fwd_kernel<T><<<(unsigned)tokens, tb, 0, (cudaStream_t)stream>>>(
+  B200_DISPATCH_T(dtype, launch_pdl(embedding_fwd_kernel<T>, (unsigned)tokens, tb, 0, (cudaStream_t)stream, 
       ids, (const T*)table, (const T*)pos_table, (T*)out, tokens, dim, period > 0 ? period : 1, scale));
   B200_LAUNCH_CHECK();
   return 0;

@@ -63,7 +63,8 @@ __global__ void __launch_bounds__(256)
 gemv_mma_kernel(const GemvParams p) {
   extern __shared__ uint32_t table[];   // 4-bit only: byte -> two 16-bit values, one column per lane (conflict-free)
   __shared__ float red[8][128];
-  if (W4) {
+  pdl_launch_dependents();
+  if (W4) {   // the table depends on no earlier kernel: it is built while the previous kernel drains
     for (int i = threadIdx.x; i < 256 * 32; i += 256) {
       const int byte = i >> 5;
       const float lo = p.lut ? p.lut[byte >> 4] : kNF4g[byte >> 4];
@@ -72,6 +73,7 @@ gemv_mma_kernel(const GemvParams p) {
     }
     __syncthreads();
   }
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t = lane & 3;
   const int K = p.K, M = p.M;
@@ -167,12 +169,12 @@ static int launch_gemv(const GemvParams& p, cudaStream_t st) {
   const long long tiles = (p.N + 15) / 16;
   const unsigned grid = (unsigned)(tiles < kNumSMs * 4 ? tiles : kNumSMs * 4);
   const int smem = W4 ? 256 * 32 * 4 : 0;
-  if (p.M <= 8) gemv_mma_kernel<BF16, W4, 1><<<grid, 256, smem, st>>>(p);
-  else if (p.M <= 16) gemv_mma_kernel<BF16, W4, 2><<<grid, 256, smem, st>>>(p);
-  else if (p.M <= 32) gemv_mma_kernel<BF16, W4, 4><<<grid, 256, smem, st>>>(p);
-  else gemv_mma_kernel<BF16, W4, 8><<<grid, 256, smem, st>>>(p);
-  B200_LAUNCH_CHECK();
-  return 0;
+  cudaError_t e;
+  if (p.M <= 8) e = launch_pdl(gemv_mma_kernel<BF16, W4, 1>, grid, 256, smem, st, p);
+  else if (p.M <= 16) e = launch_pdl(gemv_mma_kernel<BF16, W4, 2>, grid, 256, smem, st, p);
+  else if (p.M <= 32) e = launch_pdl(gemv_mma_kernel<BF16, W4, 4>, grid, 256, smem, st, p);
+  else e = launch_pdl(gemv_mma_kernel<BF16, W4, 8>, grid, 256, smem, st, p);
+  return (int)e;
 }
 
 }  // namespace b200

@@ -45,6 +45,8 @@ norm_fwd_kernel(const T* __restrict__ x, const T* __restrict__ res, const WT* __
                 float* __restrict__ stats, int cols, float eps) {
   constexpr int V = 16 / sizeof(T);
   __shared__ float red[32];
+  pdl_launch_dependents();
+  pdl_wait();
   const long long row = blockIdx.x;
   const T* xr = x + row * cols;
   const T* rr = res ? res + row * cols : nullptr;
@@ -211,13 +213,10 @@ template <typename T, typename WT>
 static int launch_norm_fwd(int layer_norm, const void* x, const void* res, const void* w, const void* b, void* y,
                            void* h_out, float* stats, int rows, int cols, float eps, cudaStream_t st) {
   if (layer_norm)
-    norm_fwd_kernel<T, WT, true><<<rows, kNormThreads, 0, st>>>((const T*)x, (const T*)res, (const WT*)w,
-                                                               (const WT*)b, (T*)y, (T*)h_out, stats, cols, eps);
-  else
-    norm_fwd_kernel<T, WT, false><<<rows, kNormThreads, 0, st>>>((const T*)x, (const T*)res, (const WT*)w,
-                                                                (const WT*)b, (T*)y, (T*)h_out, stats, cols, eps);
-  B200_LAUNCH_CHECK();
-  return 0;
+    return (int)launch_pdl(norm_fwd_kernel<T, WT, true>, rows, kNormThreads, 0, st, (const T*)x, (const T*)res, (const WT*)w,
+                           (const WT*)b, (T*)y, (T*)h_out, stats, cols, eps);
+  return (int)launch_pdl(norm_fwd_kernel<T, WT, false>, rows, kNormThreads, 0, st, (const T*)x, (const T*)res, (const WT*)w,
+                         (const WT*)b, (T*)y, (T*)h_out, stats, cols, eps);
 }
 
 template <typename T, typename WT, int MV>

@@ -178,6 +178,7 @@ w4_gemv_mma_kernel(const uint16_t* __restrict__ x, const uint8_t* __restrict__ p
                    uint16_t* __restrict__ y, int M, long long N, int K, int group, long long x_rs, long long y_rs) {
   __shared__ uint32_t table[256 * 32];
   __shared__ float red[8][128];
+  pdl_launch_dependents();   // the table below depends on no earlier kernel: built while the previous kernel drains
   for (int i = threadIdx.x; i < 256 * 32; i += 256) {
     const int byte = i >> 5;
     const float lo = lut_g ? lut_g[byte >> 4] : kNF4[byte >> 4];
@@ -188,6 +189,7 @@ w4_gemv_mma_kernel(const uint16_t* __restrict__ x, const uint8_t* __restrict__ p
     table[i] = v;
   }
   __syncthreads();
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, t = lane & 3;
   const int gpr = K / group;
@@ -431,11 +433,8 @@ B200_API int b200_w4_gemv(const void* x, const uint8_t* packed, const float* sca
     const unsigned g16 = (unsigned)(tiles16 < kNumSMs * 4 ? tiles16 : kNumSMs * 4);
     cudaStream_t s2 = (cudaStream_t)stream;
     if (dtype == B200_DT_BF16)
-      w4_gemv_mma_kernel<true><<<g16, 256, 0, s2>>>((const uint16_t*)x, packed, scale, zs, lut, (const uint16_t*)bias, (uint16_t*)y, M, N, K, group, x_rs, y_rs);
-    else
-      w4_gemv_mma_kernel<false><<<g16, 256, 0, s2>>>((const uint16_t*)x, packed, scale, zs, lut, (const uint16_t*)bias, (uint16_t*)y, M, N, K, group, x_rs, y_rs);
-    B200_LAUNCH_CHECK();
-    return 0;
+      return (int)launch_pdl(w4_gemv_mma_kernel<true>, g16, 256, 0, s2, (const uint16_t*)x, packed, scale, zs, lut, (const uint16_t*)bias, (uint16_t*)y, M, N, K, group, x_rs, y_rs);
+    return (int)launch_pdl(w4_gemv_mma_kernel<false>, g16, 256, 0, s2, (const uint16_t*)x, packed, scale, zs, lut, (const uint16_t*)bias, (uint16_t*)y, M, N, K, group, x_rs, y_rs);
   }
   const int smem = M * K * 2;
   if (smem > 200 * 1024) return B200_ERR_TOO_LARGE;

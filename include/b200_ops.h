@@ -250,6 +250,15 @@ typedef struct {
 int b200_zero_step(const b200_zero_step_args* args, void* stream);
 int b200_peer_gather(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
                      int world, void* stream);
+/* One-shot all-reduce (sum) of a small 16-bit tensor for tensor-parallel decode: y [n] local, stage_ptrs = every rank's
+ * symmetric 16-bit staging buffer of 2 * half_elems elements, out [n] local. Epoch and barrier tickets live in `state`
+ * (3 zero-initialised uint32 on the device), so the launch can be captured in a CUDA graph and replayed on every rank
+ * (b200_allreduce takes its epoch from the host). `channel` must not be shared with any other collective. n % 8 == 0.
+ * vLLM's custom all-reduce behind --tensor-parallel-size (Fine-Tuning/README.md:345-348) is the counterpart. */
+int b200_allreduce_oneshot(const void* y, const void* const* stage_ptrs, const void* const* flag_ptrs, void* out,
+                           long long n, long long half_elems, int world, int rank, int channel, unsigned int* state,
+                           int dtype, void* stream);
+
 /* b200_peer_gather that leaves rank `skip`'s slot of `out` untouched (ZeRO-3 layer prefetch: the local shard is read
  * in place, only the world - 1 remote shards cross NVLink). */
 int b200_peer_gather_skip(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,

@@ -256,7 +256,11 @@ class Generator:
         epoch). Inside a capture the GEMMs run without stream-K and 4-bit weights are expanded in line."""
         B = tok.shape[0]
         L = cache.len                                   # ``cache.len`` is the caller's to advance, never this method's
-        if not tok.is_cuda or B > 512 or getattr(self.model, "tp", None) is not None and self.model.tp.world > 1:
+        tp = getattr(self.model, "tp", None)
+        # under tensor parallelism the step is replayable only when its all-reduce keeps its epoch on the device
+        tp_eager = tp is not None and tp.world > 1 and not (getattr(tp, "fused", False) and getattr(tp, "oneshot", False)
+                                                            and B * self.cfg.hidden_size <= getattr(tp, "half16", 0))
+        if not tok.is_cuda or B > 512 or tp_eager:
             out = self._decode(tok, cache, pos, slots)
             cache.len = L
             return out

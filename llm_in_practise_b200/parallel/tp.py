@@ -17,12 +17,15 @@ because they read the head counts from ``model.config``.
 from __future__ import annotations
 
 import copy
+import ctypes
+import os
 from typing import List, Optional
 
 import torch
 import torch.distributed as dist
 from torch import nn
 
+from ..ops import _native as nv
 from ..ops.linear import FusedLinear
 from ..ops.w4 import NF4Weight
 from .dist import get_info
@@ -42,6 +45,11 @@ class TensorParallel:
             self.buf = SymmBuffer(self.n_max, torch.float32, self.device, group)
             self.lowp = SymmBuffer(self.n_max, torch.bfloat16, self.device, group)
             self.flags = PeerFlags(self.device)
+            # decode-sized messages: one-shot kernel whose epoch lives on the device (CUDA-graph replayable)
+            self.half16 = min(self.n_max, 64 * hidden) // 8 * 8
+            self.stage16 = SymmBuffer(2 * self.half16, torch.bfloat16, self.device, group)
+            self.state16 = torch.zeros(4, dtype=torch.int32, device=self.device)
+            self.oneshot = os.environ.get("B200_TP_ONESHOT", "1") != "0"
         self.calls = 0
 
     def all_reduce(self, y: torch.Tensor) -> torch.Tensor:
@@ -54,6 +62,16 @@ class TensorParallel:
             out = y.float()
             dist.all_reduce(out, group=self.group)
             return out.to(y.dtype)
+        if self.oneshot and y.dtype in (torch.bfloat16, torch.float16) and n <= self.half16 and n % 8 == 0:
+            y = y.contiguous()
+            out = torch.empty_like(y)
+            vp, i32, i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong
+            fn = nv.proto("b200_allreduce_oneshot", [vp, vp, vp, vp, i64, i64, i32, i32, i32, vp, i32, vp])
+            nv.check(fn(nv.ptr(y), ctypes.cast(self.stage16.c_ptrs(), vp), ctypes.cast(self.flags.flags.c_ptrs(), vp), nv.ptr(out),
+                        n, self.half16, self.world, self.rank, 6, nv.ptr(self.state16), nv.dtype_code(y.dtype), nv.stream()),
+                     "allreduce_oneshot")
+            nv.count_launch()
+            return out
         self.buf.local[:n].view(y.shape).copy_(y)                       # fp32 partial into the symmetric buffer
         allreduce_(self.buf, self.flags, 0, n, 1.0, lowp=self.lowp if y.dtype == torch.bfloat16 else None)
         src = self.lowp.local if y.dtype == torch.bfloat16 else self.buf.local

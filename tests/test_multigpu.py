@@ -34,3 +34,18 @@ def test_zero3_prefetch_matches_direct_peer_reads():
     assert a["losses"] == pytest.approx(b["losses"], rel=1e-2), (a, b)
     assert a["lora_abs_sum"] == pytest.approx(b["lora_abs_sum"], rel=5e-3), (a, b)
     assert all(x == x and x < 20 for x in a["losses"])
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_tp_oneshot_allreduce_eager_and_graph():
+    """The decode-sized all-reduce keeps its epoch on the device: same numbers as NCCL, replayable from a CUDA graph,
+    bitwise identical on every rank."""
+    import os, subprocess, sys, json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                          "127.0.0.1", "--master-port", "29631", os.path.join(root, "scripts", "check_tp_oneshot.py")],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    r = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1])
+    assert r["eager_rel_err"] < 2e-2 and r["graph_rel_err"] < 3e-2 and r["ranks_identical"], r
