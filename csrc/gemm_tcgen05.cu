@@ -55,7 +55,8 @@ struct GemmKernelParams {
   int stream_k, sk_group;
   float* sk_ws;
   unsigned int* sk_flags;
-  unsigned int sk_epoch;
+  unsigned int sk_epoch;      // host-provided epoch (used when sk_state is null)
+  unsigned int* sk_state;     // device epoch: [0] = epoch of the last stream-K launch, [1] = ticket counter (graph-replayable)
 };
 
 // Fused 4-bit B operand (W4 = true instantiation): the weight matrix W [rows, kw] is stored packed (two codes per
@@ -232,7 +233,24 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
   const bool leader = rank == 0;
   const int unit = blockIdx.x / CTAS, nunits = gridDim.x / CTAS;
 
+  const uint32_t sk_epoch_slot = tmem_slot + 4u;   // second half of the 8-byte TMEM-pointer slot (no static shared memory: the
+                                                   // dynamic allocation already takes the whole 227 KB)
   if (warp == 0 && lane == 0) {
+    if (p.stream_k) {
+      unsigned int e = p.sk_epoch;
+      if (p.sk_state) {
+        // every CTA of the launch reads the old epoch, then takes a ticket; the last ticket publishes the new epoch for the
+        // next launch on this stream. Nothing here comes from the host, so a captured launch can be replayed.
+        e = *((volatile unsigned int*)p.sk_state) + 1u;
+        __threadfence();
+        if (atomicAdd(p.sk_state + 1, 1u) == gridDim.x - 1) {
+          p.sk_state[1] = 0u;
+          __threadfence();
+          *((volatile unsigned int*)p.sk_state) = e;
+        }
+      }
+      asm volatile("st.shared.u32 [%0], %1;" ::"r"(sk_epoch_slot), "r"(e) : "memory");
+    }
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
     if (p.K2 > 0) {
@@ -556,6 +574,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
     Segment sg;
     const int sk_g = p.stream_k ? p.sk_group : 1;
+    unsigned int sk_epoch_v = 0;
+    if (p.stream_k) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sk_epoch_v) : "r"(sk_epoch_slot) : "memory");
     const int sk_groups = nunits / sk_g, sk_grp = unit / sk_g;
     const long long sk_total = (long long)(total_tiles / sk_g) * num_k_total;
     while (it.next(sg)) {
@@ -587,7 +607,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         }
         __threadfence();
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (threadIdx.x == 64) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.sk_flags + blockIdx.x), "r"(p.sk_epoch) : "memory");
+        if (threadIdx.x == 64) asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p.sk_flags + blockIdx.x), "r"(sk_epoch_v) : "memory");
       } else {
         // number of following units that hold later k-blocks of this tile (0 unless stream-K split it)
         int ncontrib = 0;
@@ -604,7 +624,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
                 printf("b200 gemm: stream-K wait timed out (block %d waits for block %d)\n", blockIdx.x, (unit + v * sk_g) * CTAS + (int)rank);
                 __trap();
               }
-            } while (seen != p.sk_epoch);
+            } while (seen != sk_epoch_v);
           }
         }
       for (int c = 0; c < nchunks; ++c) {
@@ -762,9 +782,18 @@ static int launch(const CUtensorMap& tmA, const CUtensorMap& tmB, const CUtensor
 
 using namespace b200;
 
+// A full-size workspace (b200_gemm_workspace_bytes()) carries the stream-K epoch on the device, in its last 16 bytes:
+// every stream-K launch on that workspace (b200_gemm and b200_gemm_w4 alike) then takes its epoch from there and the launch
+// can be captured in a CUDA graph. A smaller workspace falls back to the host-side counters.
+static unsigned int* sk_state_of(const b200_gemm_args* a) {
+  const long long full = 160ll * kBM * kAccStride * 4 + 160ll * 4 + 16;
+  if (a->workspace_bytes < full) return nullptr;
+  return reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(a->workspace) + full - 16);
+}
+
 B200_API long long b200_gemm_workspace_bytes(void) {
   // one fp32 128 x 256 partial-tile slot per CTA + one flag per CTA, sized for the largest part
-  return 160ll * kBM * kAccStride * 4 + 160ll * 4;
+  return 160ll * kBM * kAccStride * 4 + 160ll * 4 + 16;   // + the device epoch state of stream-K
 }
 
 B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
@@ -810,7 +839,7 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   p.num_n = ceil_div(a->N, p.bn);
   p.stream_k = cfg.stream_k;
   p.sk_group = 1;
-  p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0;
+  p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0; p.sk_state = nullptr;
   if (cfg.stream_k) {
     // lock-step groups when the M-tiles of a panel fit a group and at most ~5 % of the units are left without one
     const int units_sk = g_num_sms / ctas;
@@ -821,6 +850,7 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
     p.sk_flags = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(a->workspace) +
                                                  (long long)g_num_sms * kBM * kAccStride * 4);
     p.sk_epoch = ++epoch;
+    p.sk_state = sk_state_of(a);
   }
   const int stage_bytes = kStageABytes + bn_cta * 128;
   int stages = (g_max_smem - 2048) / stage_bytes;
@@ -935,13 +965,14 @@ B200_API int b200_gemm_w4(const b200_gemm_args* a, const b200_w4_desc* w, void* 
   const double classic = (double)waves * nkt, sk = (double)tiles * nkt / units + 10.0;
   p.stream_k = (allow_sk && tiles % units != 0 && tiles * nkt >= 4ll * units && waves <= 4 && sk < classic * 0.85) ? 1 : 0;
   p.sk_group = 1;
-  p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0;
+  p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0; p.sk_state = nullptr;
   if (p.stream_k) {
     static unsigned int epoch = 0x40000000u;   // own epoch space: flags are shared with b200_gemm's workspace
     p.sk_ws = reinterpret_cast<float*>(a->workspace);
     p.sk_flags = reinterpret_cast<unsigned int*>(reinterpret_cast<char*>(a->workspace) +
                                                  (long long)g_num_sms * kBM * kAccStride * 4);
     p.sk_epoch = ++epoch;
+    p.sk_state = sk_state_of(a);
   }
   const int stage_bytes = kStageABytes + bn_cta * 128;
   int raw_stages = 8, lut_bytes = kLutBytes;

@@ -25,7 +25,7 @@ import torch
 from ..ops import _native as nv
 from ..ops import elementwise as ew
 from ..ops.attention import attention
-from ..ops.gemm import gemm, gemv16
+from ..ops.gemm import ensure_graph_workspace, gemm, gemv16
 from ..ops.norm import rms_norm
 
 vp, i32, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
@@ -208,6 +208,7 @@ class Generator:
         g = self._graphs.get(key)
         if g is None:
             st = {"ids": ids_h.to(dev), "pos": pos_h.to(dev), "row": row_h.to(dev), "cu": cu_h.to(dev), "last": last_h.to(dev)}
+            ensure_graph_workspace(dev)
             self._prefill_packed_core(st["ids"], st["pos"], st["row"], st["cu"], st["last"], Tb, cache)   # warm-up
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
@@ -268,6 +269,7 @@ class Generator:
         g = self._graphs.get(key)
         if g is None:
             st = {"tok": tok.clone(), "pos": pos.clone(), "slots": slots.clone()}
+            ensure_graph_workspace(tok.device)                              # stream-K scratch of captured GEMMs
             self._decode(st["tok"], cache, st["pos"], st["slots"])          # warm-up: allocates every lazily built buffer
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()

@@ -26,8 +26,26 @@ from . import _native as nv
 _sk_workspaces = {}
 
 
-def _stream_k_workspace(device: torch.device) -> torch.Tensor:
+def ensure_graph_workspace(device: torch.device) -> None:
+    """Allocate (outside any capture) the stream-K scratch that GEMMs captured into CUDA graphs use. The stream-K epoch
+    lives in the workspace itself, so captured launches are replayable; all graphs of a device share this one scratch and
+    must therefore be replayed on one stream at a time (the serving engine and ``Generator`` do)."""
+    if os.environ.get("B200_GRAPH_STREAMK", "0") != "1":
+        # measured on the serving sweep (Qwen3-8B bf16, decode GEMMs at M = 32..128 are weight-bandwidth-bound): stream-K
+        # inside the decode graph costs 10-14 % of the throughput (fp32 partial tiles + fix-up traffic), so captured
+        # launches run one CTA pair per tile unless asked otherwise
+        return
+    key = (device.index, "graph")
+    if key not in _sk_workspaces and not torch.cuda.is_current_stream_capturing():
+        fn = nv.lib().b200_gemm_workspace_bytes
+        fn.restype = ctypes.c_longlong
+        _sk_workspaces[key] = torch.zeros(int(fn()), dtype=torch.uint8, device=device)
+
+
+def _stream_k_workspace(device: torch.device) -> Optional[torch.Tensor]:
     """Per (device, stream) scratch for stream-K GEMMs: zeroed once, then owned by that stream."""
+    if torch.cuda.is_current_stream_capturing():
+        return _sk_workspaces.get((device.index, "graph"))       # None: captured without stream-K
     key = (device.index, torch.cuda.current_stream(device).cuda_stream)
     ws = _sk_workspaces.get(key)
     if ws is None:
@@ -149,11 +167,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     else:
         args.A2 = args.B2 = 0
         args.K2 = 0
-    if torch.cuda.is_current_stream_capturing():
-        # stream-K epochs are host-side counters baked into the launch: a replayed graph must not use them
+    ws = _stream_k_workspace(a.device)
+    if ws is None:
         args.workspace, args.workspace_bytes = 0, 0
     else:
-        ws = _stream_k_workspace(a.device)
         args.workspace, args.workspace_bytes = ws.data_ptr(), ws.numel()
     rc = nv.lib().b200_gemm(ctypes.byref(args), nv.stream())
     nv.check(rc, f"gemm M={M} N={N} K={K} batch={batch}")
