@@ -35,10 +35,40 @@ struct FlashParams {
   int B, S, H, Hkv, D;
   long long W;
   float scale, scale_log2;
+  unsigned long long seed;   // attention-probability dropout (nn.MultiheadAttention(dropout=p)): Philox, regenerated in backward
+  uint32_t drop_thresh;      // 0 = no dropout; P(drop) = thresh / 2^32
+  float inv_keep;
 };
 
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
+
+// Philox4x32-10. One call covers the 2 x 2 patch a thread holds of a score tile: rows (r, r + 8), keys (2 kp, 2 kp + 1), so the
+// mask of an element depends only on (seed, batch*head, row, key) and forward / backward regenerate it identically.
+__device__ __forceinline__ uint4 flash_philox(unsigned long long seed, unsigned long long q) {
+  constexpr uint32_t kA = 0xD2511F53u, kB = 0xCD9E8D57u, kW0 = 0x9E3779B9u, kW1 = 0xBB67AE85u;
+  uint2 key = make_uint2((uint32_t)seed, (uint32_t)(seed >> 32));
+  uint4 ctr = make_uint4((uint32_t)q, (uint32_t)(q >> 32), 0x6a09e667u, 0u);
+#pragma unroll
+  for (int i = 0; i < 10; ++i) {
+    const uint32_t hi0 = __umulhi(kA, ctr.x), lo0 = kA * ctr.x;
+    const uint32_t hi1 = __umulhi(kB, ctr.z), lo1 = kB * ctr.z;
+    ctr = make_uint4(hi1 ^ ctr.y ^ key.x, lo1, hi0 ^ ctr.w ^ key.y, lo0);
+    key.x += kW0;
+    key.y += kW1;
+  }
+  return ctr;
+}
+// keep/scale factors of the patch (row_lo, row_lo + 8) x (key0, key0 + 1), key0 even: m[c] for fragment element c
+__device__ __forceinline__ void flash_drop4(const FlashParams& p, long long bh, int row_lo, int key0, float (&m)[4]) {
+  const unsigned long long q = ((unsigned long long)bh * (unsigned long long)p.S + (unsigned long long)row_lo) *
+                               (unsigned long long)((p.S + 1) / 2) + (unsigned long long)(key0 >> 1);
+  const uint4 r = flash_philox(p.seed, q);
+  m[0] = r.x >= p.drop_thresh ? p.inv_keep : 0.f;
+  m[1] = r.y >= p.drop_thresh ? p.inv_keep : 0.f;
+  m[2] = r.z >= p.drop_thresh ? p.inv_keep : 0.f;
+  m[3] = r.w >= p.drop_thresh ? p.inv_keep : 0.f;
+}
 
 // byte offset of 16-byte chunk `c` of row `r` in a tile with CH chunks per row (CH = 8 or 16)
 template <int CH>
@@ -220,6 +250,15 @@ flash_fwd_kernel(const FlashParams p) {
     }
 #pragma unroll
     for (int r = 0; r < 2; ++r) lrow[r] = lrow[r] * alpha[r] + rs[r];
+    if (p.drop_thresh) {   // the normaliser above is of the undropped probabilities; only the P that multiplies V is dropped
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float dm[4];
+        flash_drop4(p, (long long)b * p.H + h, rowA, k0 + i * 8 + 2 * t, dm);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) s[i][c] *= dm[c];
+      }
+    }
 #pragma unroll
     for (int i = 0; i < D / 8; ++i) {
       o[i][0] *= alpha[0]; o[i][1] *= alpha[0]; o[i][2] *= alpha[1]; o[i][3] *= alpha[1];
@@ -385,7 +424,19 @@ flash_bwd_kernel(const FlashParams p) {
         const bool ok = key < S && q < S && (!CAUSAL || key <= q);
         const float pr = ok ? exp2f(s[i][c] * p.scale_log2 - ((c & 2) ? lB : lA)) : 0.f;
         pv[c] = pr;
-        dsv[c] = pr * (dp[i][c] - ((c & 2) ? dB : dA)) * p.scale;
+        dsv[c] = dp[i][c];
+      }
+      if (p.drop_thresh) {   // dV takes the dropped P, dS the undropped P times the masked dP
+        float dm[4];
+        flash_drop4(p, (long long)b * p.H + h, qA, k0 + cw * 32 + i * 8 + 2 * t, dm);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          dsv[c] = pv[c] * (dsv[c] * dm[c] - ((c & 2) ? dB : dA)) * p.scale;
+          pv[c] *= dm[c];
+        }
+      } else {
+#pragma unroll
+        for (int c = 0; c < 4; ++c) dsv[c] = pv[c] * (dsv[c] - ((c & 2) ? dB : dA)) * p.scale;
       }
       const int chunk = cw * 4 + i;
       uint8_t* pP = fsm + 6 * kTile;
@@ -565,7 +616,19 @@ flash_bwd128_kernel(const FlashParams p) {
             const bool ok = key < S && q < S && (!CAUSAL || key <= q);
             const float pr = ok ? exp2f(s[m][i][c] * p.scale_log2 - ((c & 2) ? lB : lA)) : 0.f;
             pv[c] = pr;
-            dsv[c] = pr * (dp[m][i][c] - ((c & 2) ? dB : dA)) * p.scale;
+            dsv[c] = dp[m][i][c];
+          }
+          if (p.drop_thresh) {
+            float dm[4];
+            flash_drop4(p, (long long)b * p.H + h, qA, k0 + ck * 32 + i * 8 + 2 * t, dm);
+#pragma unroll
+            for (int c = 0; c < 4; ++c) {
+              dsv[c] = pv[c] * (dsv[c] * dm[c] - ((c & 2) ? dB : dA)) * p.scale;
+              pv[c] *= dm[c];
+            }
+          } else {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) dsv[c] = pv[c] * (dsv[c] - ((c & 2) ? dB : dA)) * p.scale;
           }
           const int chunk = ck * 4 + i;
           *reinterpret_cast<uint32_t*>(pP + tile_off<8>(lrA, chunk) + t * 4) = pack16<BF16>(pv[0], pv[1]);
@@ -739,13 +802,21 @@ static int flash_check(int B, int S, int H, int Hkv, int D, int dtype) {
 }  // namespace b200
 using namespace b200;
 
+static void set_dropout(FlashParams& p, float dropout_p, unsigned long long seed) {
+  p.seed = seed;
+  if (dropout_p <= 0.f) { p.drop_thresh = 0; p.inv_keep = 1.f; return; }
+  p.drop_thresh = dropout_p >= 1.f ? 0xFFFFFFFFu : (uint32_t)((double)dropout_p * 4294967296.0);
+  p.inv_keep = dropout_p >= 1.f ? 0.f : 1.f / (1.f - dropout_p);
+}
+
 B200_API int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int H, int Hkv, int D, int causal,
-                                 float scale, int dtype, void* stream) {
+                                 float scale, float dropout_p, unsigned long long seed, int dtype, void* stream) {
   if (int rc = flash_check(B, S, H, Hkv, D, dtype)) return rc;
   if ((reinterpret_cast<uintptr_t>(qkv) | reinterpret_cast<uintptr_t>(out)) & 15) return B200_ERR_BAD_ALIGN;
   FlashParams p = {};
   p.qkv = qkv; p.out = out; p.lse = lse; p.B = B; p.S = S; p.H = H; p.Hkv = Hkv; p.D = D;
   p.W = (long long)(H + 2 * Hkv) * D; p.scale = scale; p.scale_log2 = scale * kLog2e;
+  set_dropout(p, dropout_p, seed);
   cudaStream_t st = (cudaStream_t)stream;
   const bool bf = dtype == B200_DT_BF16;
   if (D == 128) return bf ? launch_fwd<true, 128>(p, causal, st) : launch_fwd<false, 128>(p, causal, st);
@@ -768,7 +839,7 @@ B200_API int b200_flash_attn_varlen_fwd(const void* qkv, void* out, const int* c
 
 B200_API int b200_flash_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                                  float* dqkv32, void* dqkv, int B, int S, int H, int Hkv, int D, int causal, float scale,
-                                 int dtype, void* stream) {
+                                 float dropout_p, unsigned long long seed, int dtype, void* stream) {
   if (int rc = flash_check(B, S, H, Hkv, D, dtype)) return rc;
   if ((reinterpret_cast<uintptr_t>(qkv) | reinterpret_cast<uintptr_t>(dout) | reinterpret_cast<uintptr_t>(dqkv32) |
        reinterpret_cast<uintptr_t>(dqkv)) & 15) return B200_ERR_BAD_ALIGN;
@@ -776,6 +847,7 @@ B200_API int b200_flash_attn_bwd(const void* qkv, const void* out, const void* d
   p.qkv = qkv; p.dout = dout; p.lse = const_cast<float*>(lse); p.delta = delta; p.dqkv32 = dqkv32;
   p.B = B; p.S = S; p.H = H; p.Hkv = Hkv; p.D = D;
   p.W = (long long)(H + 2 * Hkv) * D; p.scale = scale; p.scale_log2 = scale * kLog2e;
+  set_dropout(p, dropout_p, seed);
   cudaStream_t st = (cudaStream_t)stream;
   B200_CHECK(cudaMemsetAsync(dqkv32, 0, (size_t)B * S * p.W * sizeof(float), st));
   const bool bf = dtype == B200_DT_BF16;

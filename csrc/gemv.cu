@@ -58,8 +58,8 @@ struct GemvParams {
   long long N, x_rs, w_rs, y_rs;
 };
 
-template <bool BF16, bool W4, int TG>
-__global__ void __launch_bounds__(256)
+template <bool BF16, bool W4, int TG, int MINB>
+__global__ void __launch_bounds__(256, MINB)
 gemv_mma_kernel(const GemvParams p) {
   extern __shared__ uint32_t table[];   // 4-bit only: byte -> two 16-bit values, one column per lane (conflict-free)
   __shared__ float red[8][128];
@@ -164,16 +164,34 @@ gemv_mma_kernel(const GemvParams p) {
   }
 }
 
+template <bool BF16, bool W4, int TG, int MINB>
+static cudaError_t launch_gemv_one(const GemvParams& p, cudaStream_t st) {
+  // persistent over 16-row tiles: one resident wave (occupancy x SMs), never more CTAs than tiles
+  static int occ = 0;
+  const int smem = W4 ? 256 * 32 * 4 : 0;
+  if (!occ) {
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gemv_mma_kernel<BF16, W4, TG, MINB>, 256, smem) != cudaSuccess || occ < 1) occ = 1;
+  }
+  const long long tiles = (p.N + 15) / 16;
+  const unsigned grid = (unsigned)(tiles < (long long)kNumSMs * occ ? tiles : (long long)kNumSMs * occ);
+  return launch_pdl(gemv_mma_kernel<BF16, W4, TG, MINB>, grid, 256, smem, st, p);
+}
+
 template <bool BF16, bool W4>
 static int launch_gemv(const GemvParams& p, cudaStream_t st) {
-  const long long tiles = (p.N + 15) / 16;
-  const unsigned grid = (unsigned)(tiles < kNumSMs * 4 ? tiles : kNumSMs * 4);
-  const int smem = W4 ? 256 * 32 * 4 : 0;
+  // dense weights: registers cap the occupancy (96 -> 2 CTAs per SM); forcing 3 trades a few spills for 50 % more loads in
+  // flight, which is what a weight-streaming kernel is short of (B200_GEMV_MINB=2|3|4 to compare)
+  static const int minb = [] { const char* e = getenv("B200_GEMV_MINB"); return e ? atoi(e) : 0; }();
   cudaError_t e;
-  if (p.M <= 8) e = launch_pdl(gemv_mma_kernel<BF16, W4, 1>, grid, 256, smem, st, p);
-  else if (p.M <= 16) e = launch_pdl(gemv_mma_kernel<BF16, W4, 2>, grid, 256, smem, st, p);
-  else if (p.M <= 32) e = launch_pdl(gemv_mma_kernel<BF16, W4, 4>, grid, 256, smem, st, p);
-  else e = launch_pdl(gemv_mma_kernel<BF16, W4, 8>, grid, 256, smem, st, p);
+#define B200_GV(TGv)                                                                     \
+  (W4 || minb == 0 || minb == 2 ? launch_gemv_one<BF16, W4, TGv, W4 ? 1 : 2>(p, st)        \
+   : minb == 3                  ? launch_gemv_one<BF16, W4, TGv, W4 ? 1 : 3>(p, st)        \
+                                : launch_gemv_one<BF16, W4, TGv, W4 ? 1 : 4>(p, st))
+  if (p.M <= 8) e = B200_GV(1);
+  else if (p.M <= 16) e = B200_GV(2);
+  else if (p.M <= 32) e = B200_GV(4);
+  else e = B200_GV(8);
+#undef B200_GV
   return (int)e;
 }
 

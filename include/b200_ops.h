@@ -286,17 +286,19 @@ int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_v, const 
  * softmax(Q K^T * scale [+ causal mask]) V read in place from the fused projection qkv [B*S, (H + 2 Hkv) * D]; context to
  * out [B*S, H*D], row log-sum-exp (natural log) to lse [B, H, S]. No S x S tensor, no mask tensor (the reference builds
  * an L x L boolean mask per forward, ddp_gpt_wikitext2.py:93-95; HF Qwen3 uses SDPA, Fine-Tuning/qwen3-8b-lora-dist.py:118).
+ * dropout_p > 0 drops attention probabilities (nn.MultiheadAttention(dropout=0.1), ddp_gpt_wikitext2.py:92) with a Philox
+ * mask that depends only on (seed, batch, head, row, key): pass the same p and seed to the backward.
  * 16-bit dtypes, D in {64, 128}, any S. The backward recomputes P from lse: delta [B, H, S] and dqkv32 [B*S, W] (fp32)
  * are caller-provided work buffers (dqkv32 is zeroed inside), dqkv [B*S, W] receives the 16-bit gradient. */
 int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int H, int Hkv, int D, int causal,
-                        float scale, int dtype, void* stream);
+                        float scale, float dropout_p, unsigned long long seed, int dtype, void* stream);
 /* Packed ("varlen") forward for serving prefill: qkv [T, W] holds n_seqs sequences back to back, sequence b = rows
  * [cu_seqlens[b], cu_seqlens[b+1]) (device int32 [n_seqs + 1]); max_seqlen bounds the grid. No lse. */
 int b200_flash_attn_varlen_fwd(const void* qkv, void* out, const int* cu_seqlens, int n_seqs, int max_seqlen, int H,
                                int Hkv, int D, int causal, float scale, int dtype, void* stream);
 int b200_flash_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                         float* dqkv32, void* dqkv, int B, int S, int H, int Hkv, int D, int causal, float scale,
-                        int dtype, void* stream);
+                        float dropout_p, unsigned long long seed, int dtype, void* stream);
 
 /* ---- small-M products for decode / serving steps (csrc/gemv.cu) ---------------------------------
  * y[m, n] = sum_k x[m, k] w[n, k] (+ bias[n]) for 1 <= M <= 64 tokens with the weights read exactly once (mma.sync with

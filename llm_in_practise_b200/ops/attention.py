@@ -2,7 +2,7 @@
 
 Two native paths share this front end:
 
-* ``flash`` (``csrc/flash_attn.cu``; 16-bit dtypes, head_dim 64 / 128, no window, no probability dropout): 64 x 64
+* ``flash`` (``csrc/flash_attn.cu``; 16-bit dtypes, head_dim 64 / 128, no window; probability dropout in-kernel): 64 x 64
   tiles, online softmax forward, recomputing backward, no L x L tensor in memory in either direction.
 * ``tiled`` (always available): batched tcgen05 GEMMs (``csrc/gemm_tcgen05.cu``) around fused
   masked-softmax kernels (``csrc/loss.cu``); scores exist per (batch, head) as a transient.
@@ -206,9 +206,13 @@ def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, 
     if not nv.use_native(qkv) or (S % 8 and not causal) or qkv.dtype == torch.float32 and False:
         return _ref_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)
     if impl in ("auto", "flash") and _flash_available() and qkv.dtype in (torch.bfloat16, torch.float16) \
-            and head_dim in (64, 128) and window == 0 and dropout_p == 0.0:
+            and head_dim in (64, 128) and window == 0:
         from .flash import flash_attention
-        return flash_attention(qkv.contiguous(), B, S, n_heads, n_kv_heads, head_dim, causal, scale)
+        seed = 0
+        if dropout_p > 0.0:
+            from .elementwise import next_seed
+            seed = next_seed()
+        return flash_attention(qkv.contiguous(), B, S, n_heads, n_kv_heads, head_dim, causal, scale, dropout_p, seed)
     if S % 8:
         # the score / probability matrices need 16-byte row strides: pad the sequence to a multiple of 8; under the
         # causal mask the real rows never see the padded keys, so the result is exact

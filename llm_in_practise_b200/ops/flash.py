@@ -11,18 +11,18 @@ import torch
 
 from . import _native as nv
 
-vp, i32, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float
+vp, i32, f32, u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_ulonglong
 
 
 def flash_supported(qkv: torch.Tensor, head_dim: int) -> bool:
     return qkv.dtype in (torch.bfloat16, torch.float16) and head_dim in (64, 128)
 
 
-def _fwd(qkv, B, S, H, Hkv, D, causal, scale, want_lse=True):
+def _fwd(qkv, B, S, H, Hkv, D, causal, scale, want_lse=True, dropout_p=0.0, seed=0):
     out = torch.empty(B * S, H * D, dtype=qkv.dtype, device=qkv.device)
     lse = torch.empty(B, H, S, dtype=torch.float32, device=qkv.device) if want_lse else None
-    fn = nv.proto("b200_flash_attn_fwd", [vp, vp, vp, i32, i32, i32, i32, i32, i32, f32, i32, vp])
-    nv.check(fn(nv.ptr(qkv), nv.ptr(out), nv.ptr(lse), B, S, H, Hkv, D, int(causal), float(scale),
+    fn = nv.proto("b200_flash_attn_fwd", [vp, vp, vp, i32, i32, i32, i32, i32, i32, f32, f32, u64, i32, vp])
+    nv.check(fn(nv.ptr(qkv), nv.ptr(out), nv.ptr(lse), B, S, H, Hkv, D, int(causal), float(scale), float(dropout_p), int(seed),
                 nv.dtype_code(qkv.dtype), nv.stream()), "flash_attn_fwd")
     nv.count_launch()
     return out, lse
@@ -30,32 +30,35 @@ def _fwd(qkv, B, S, H, Hkv, D, causal, scale, want_lse=True):
 
 class _FlashAttentionFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, qkv, B, S, H, Hkv, D, causal, scale):
-        out, lse = _fwd(qkv, B, S, H, Hkv, D, causal, scale)
+    def forward(ctx, qkv, B, S, H, Hkv, D, causal, scale, dropout_p, seed):
+        out, lse = _fwd(qkv, B, S, H, Hkv, D, causal, scale, True, dropout_p, seed)
         ctx.save_for_backward(qkv, out, lse)
-        ctx.cfg = (B, S, H, Hkv, D, causal, scale)
+        ctx.cfg = (B, S, H, Hkv, D, causal, scale, dropout_p, seed)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         qkv, out, lse = ctx.saved_tensors
-        B, S, H, Hkv, D, causal, scale = ctx.cfg
+        B, S, H, Hkv, D, causal, scale, dropout_p, seed = ctx.cfg
         dout = dout.contiguous()
         dqkv = torch.empty_like(qkv)
         dqkv32 = torch.empty(qkv.shape, dtype=torch.float32, device=qkv.device)
         delta = torch.empty(B, H, S, dtype=torch.float32, device=qkv.device)
-        fn = nv.proto("b200_flash_attn_bwd", [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, f32, i32, vp])
+        fn = nv.proto("b200_flash_attn_bwd", [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, f32, f32, u64, i32, vp])
         nv.check(fn(nv.ptr(qkv), nv.ptr(out), nv.ptr(dout), nv.ptr(lse), nv.ptr(delta), nv.ptr(dqkv32), nv.ptr(dqkv),
-                    B, S, H, Hkv, D, int(causal), float(scale), nv.dtype_code(qkv.dtype), nv.stream()), "flash_attn_bwd")
+                    B, S, H, Hkv, D, int(causal), float(scale), float(dropout_p), int(seed), nv.dtype_code(qkv.dtype),
+                    nv.stream()), "flash_attn_bwd")
         nv.count_launch(4)   # memset, delta, backward, cast
-        return dqkv, None, None, None, None, None, None, None
+        return dqkv, None, None, None, None, None, None, None, None, None
 
 
-def flash_attention(qkv: torch.Tensor, B: int, S: int, H: int, Hkv: int, D: int, causal: bool, scale: float) -> torch.Tensor:
-    """Context [B*S, H*D] of softmax(Q K^T * scale + mask) V over the fused projection ``qkv`` [B*S, (H + 2 Hkv) * D]."""
+def flash_attention(qkv: torch.Tensor, B: int, S: int, H: int, Hkv: int, D: int, causal: bool, scale: float,
+                    dropout_p: float = 0.0, seed: int = 0) -> torch.Tensor:
+    """Context [B*S, H*D] of dropout(softmax(Q K^T * scale + mask)) V over the fused projection ``qkv``
+    [B*S, (H + 2 Hkv) * D]. The dropout mask is a pure function of (seed, batch, head, row, key)."""
     if not (qkv.requires_grad and torch.is_grad_enabled()):
-        return _fwd(qkv, B, S, H, Hkv, D, causal, scale, want_lse=False)[0]
-    return _FlashAttentionFn.apply(qkv, B, S, H, Hkv, D, causal, scale)
+        return _fwd(qkv, B, S, H, Hkv, D, causal, scale, False, dropout_p, seed)[0]
+    return _FlashAttentionFn.apply(qkv, B, S, H, Hkv, D, causal, scale, dropout_p, seed)
 
 
 def flash_attention_varlen(qkv: torch.Tensor, cu_seqlens: torch.Tensor, max_seqlen: int, H: int, Hkv: int, D: int,

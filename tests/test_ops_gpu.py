@@ -240,6 +240,42 @@ def test_attention_tiled(H, Hkv, D, S):
 
 
 @pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("D,dtype", [(64, torch.bfloat16), (128, torch.float16)])
+def test_flash_attention_dropout(D, dtype, causal):
+    """In-kernel attention-probability dropout: the mask is read back through one-hot values (q = k = 0 makes P uniform),
+    then forward and backward with random inputs and the same seed must match the fp32 reference that uses that mask."""
+    from llm_in_practise_b200.ops.flash import flash_attention
+    B, H, Hkv, S, p, seed = 2, 4, 2, D, 0.25, 0x1234ABCD5678
+    g = H // Hkv
+    W = (H + 2 * Hkv) * D
+    probe = torch.zeros(B, S, H + 2 * Hkv, D, device=DEV, dtype=dtype)
+    probe[:, :, H + Hkv:] = torch.eye(S, device=DEV, dtype=dtype)[None, :, None, :]          # v[key] = one-hot(key)
+    with torch.no_grad():
+        o = flash_attention(probe.view(B * S, W), B, S, H, Hkv, D, False, D ** -0.5, p, seed)
+    pm = o.view(B, S, H, D).permute(0, 2, 1, 3).float() * S                                  # [B, H, row, key] = mask / keep
+    keep = (pm > 0)
+    assert abs(keep.float().mean().item() - (1 - p)) < 0.02
+    assert torch.allclose(pm[keep], torch.full_like(pm[keep], 1 / (1 - p)), rtol=2e-2)
+    torch.manual_seed(5)
+    qkv = torch.randn(B * S, W, device=DEV, dtype=dtype, requires_grad=True)
+    out = flash_attention(qkv, B, S, H, Hkv, D, causal, D ** -0.5, p, seed)
+    go = torch.randn_like(out)
+    (out * go).sum().backward()
+    q32 = qkv.detach().float().requires_grad_()
+    t = q32.view(B, S, H + 2 * Hkv, D)
+    q, k, v = t[:, :, :H].permute(0, 2, 1, 3), t[:, :, H:H + Hkv].permute(0, 2, 1, 3), t[:, :, H + Hkv:].permute(0, 2, 1, 3)
+    sc = torch.matmul(q, k.repeat_interleave(g, 1).transpose(-1, -2)) * D ** -0.5
+    if causal:
+        i = torch.arange(S, device=DEV)
+        sc = sc.masked_fill(i[None, :] > i[:, None], float("-inf"))
+    ref = torch.matmul(torch.softmax(sc, -1) * keep.float() / (1 - p), v.repeat_interleave(g, 1))
+    ref = ref.permute(0, 2, 1, 3).reshape(B * S, H * D)
+    (ref * go.float()).sum().backward()
+    assert rel(out, ref) < 2e-2
+    assert rel(qkv.grad, q32.grad) < 3e-2
+
+
+@pytest.mark.parametrize("causal", [True, False])
 @pytest.mark.parametrize("H,Hkv,D,S,dtype", [(8, 2, 128, 256, torch.bfloat16), (12, 12, 64, 255, torch.bfloat16),
                                              (5, 1, 128, 77, torch.float16), (4, 2, 128, 1100, torch.bfloat16),
                                              (40, 8, 128, 512, torch.bfloat16), (2, 2, 64, 64, torch.float16)])
