@@ -55,16 +55,23 @@ struct GemvParams {
   const void* bias;       // 16-bit, may be null
   void* y;                // [M, y_rs] 16-bit or fp32
   int M, K, group, out_f32;
+  float lin_a, lin_off;   // LIN: lut[code] = lin_a * (code - lin_off), lin_off an integer
   long long N, x_rs, w_rs, y_rs;
 };
 
-template <bool BF16, bool W4, int TG, int MINB>
+// LIN (4-bit codes that are a linear function of the code, i.e. RTN / GPTQ / AWQ integers): no lookup table. A nibble is
+// OR-ed into the mantissa of 128.0 (bf16) / 1024.0 (fp16), one exact add removes that bias and the code offset, one FMA
+// applies scale and zero: two FP instructions per pair of weights instead of a shared-memory lookup — the table variant is
+// bound by the LSU pipe (profiles/decode_kernels_ncu.md). Nibbles are taken four pairs at a time from each 32-bit word
+// ((w >> 4 i) & 0x000F000F), which pairs elements (e, e + 4); the activations get the same pairing with two PRMTs per
+// word, so the k order inside an MMA is permuted consistently on both operands.
+template <bool BF16, bool W4, int TG, int MINB, bool LIN = false>
 __global__ void __launch_bounds__(256, MINB)
 gemv_mma_kernel(const GemvParams p) {
-  extern __shared__ uint32_t table[];   // 4-bit only: byte -> two 16-bit values, one column per lane (conflict-free)
+  extern __shared__ uint32_t table[];   // 4-bit table variant only: byte -> two 16-bit values, one column per lane (conflict-free)
   __shared__ float red[8][128];
   pdl_launch_dependents();
-  if (W4) {   // the table depends on no earlier kernel: it is built while the previous kernel drains
+  if (W4 && !LIN) {   // the table depends on no earlier kernel: it is built while the previous kernel drains
     for (int i = threadIdx.x; i < 256 * 32; i += 256) {
       const int byte = i >> 5;
       const float lo = p.lut ? p.lut[byte >> 4] : kNF4g[byte >> 4];
@@ -101,11 +108,33 @@ gemv_mma_kernel(const GemvParams p) {
         const float za = p.zs ? __ldg(p.zs + rA * gpr + k / p.group) : 0.f, zb = p.zs ? __ldg(p.zs + rB * gpr + k / p.group) : 0.f;
         const uint32_t sa2 = pack2<BF16>(sa, sa), sb2 = pack2<BF16>(sb, sb), za2 = pack2<BF16>(-za, -za), zb2 = pack2<BF16>(-zb, -zb);
         const uint32_t wA[4] = {wa.x, wa.y, wa.z, wa.w}, wB[4] = {wb.x, wb.y, wb.z, wb.w};
+        if (LIN) {
+          constexpr uint32_t kMagic = BF16 ? 0x43004300u : 0x64006400u, kMask = 0x000F000Fu;
+          const float bias0 = (BF16 ? 128.f : 1024.f) + p.lin_off;
+          const uint32_t one2 = pack2<BF16>(1.f, 1.f), neg2 = pack2<BF16>(-bias0, -bias0);
+          const uint32_t la2 = pack2<BF16>(sa * p.lin_a, sa * p.lin_a), lb2 = pack2<BF16>(sb * p.lin_a, sb * p.lin_a);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {   // byte i of the 16 packed bytes = elements 2i, 2i+1
-          const uint32_t ba = (wA[i >> 2] >> ((i & 3) * 8)) & 0xFFu, bb = (wB[i >> 2] >> ((i & 3) * 8)) & 0xFFu;
-          aA[i] = fma2<BF16>(tl[ba << 5], sa2, za2);
-          aB[i] = fma2<BF16>(tl[bb << 5], sb2, zb2);
+          for (int q = 0; q < 4; ++q) {   // word q = elements 8q .. 8q+7; register order (e0,e4) (e1,e5) (e2,e6) (e3,e7)
+            const uint32_t a0 = (wA[q] & kMask) | kMagic, a1 = ((wA[q] >> 4) & kMask) | kMagic;
+            const uint32_t a2 = ((wA[q] >> 8) & kMask) | kMagic, a3 = ((wA[q] >> 12) & kMask) | kMagic;
+            const uint32_t b0 = (wB[q] & kMask) | kMagic, b1 = ((wB[q] >> 4) & kMask) | kMagic;
+            const uint32_t b2 = ((wB[q] >> 8) & kMask) | kMagic, b3 = ((wB[q] >> 12) & kMask) | kMagic;
+            aA[4 * q + 0] = fma2<BF16>(fma2<BF16>(a1, one2, neg2), la2, za2);
+            aA[4 * q + 1] = fma2<BF16>(fma2<BF16>(a0, one2, neg2), la2, za2);
+            aA[4 * q + 2] = fma2<BF16>(fma2<BF16>(a3, one2, neg2), la2, za2);
+            aA[4 * q + 3] = fma2<BF16>(fma2<BF16>(a2, one2, neg2), la2, za2);
+            aB[4 * q + 0] = fma2<BF16>(fma2<BF16>(b1, one2, neg2), lb2, zb2);
+            aB[4 * q + 1] = fma2<BF16>(fma2<BF16>(b0, one2, neg2), lb2, zb2);
+            aB[4 * q + 2] = fma2<BF16>(fma2<BF16>(b3, one2, neg2), lb2, zb2);
+            aB[4 * q + 3] = fma2<BF16>(fma2<BF16>(b2, one2, neg2), lb2, zb2);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) {   // byte i of the 16 packed bytes = elements 2i, 2i+1
+            const uint32_t ba = (wA[i >> 2] >> ((i & 3) * 8)) & 0xFFu, bb = (wB[i >> 2] >> ((i & 3) * 8)) & 0xFFu;
+            aA[i] = fma2<BF16>(tl[ba << 5], sa2, za2);
+            aB[i] = fma2<BF16>(tl[bb << 5], sb2, zb2);
+          }
         }
       } else {
         const uint16_t* wd = reinterpret_cast<const uint16_t*>(p.w);
@@ -132,6 +161,16 @@ gemv_mma_kernel(const GemvParams p) {
         } else {
 #pragma unroll
           for (int i = 0; i < 16; ++i) xw[i] = 0u;
+        }
+        if (LIN) {   // same (e, e + 4) pairing as the weights
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const uint32_t x0 = xw[4 * q], x1 = xw[4 * q + 1], x2 = xw[4 * q + 2], x3 = xw[4 * q + 3];
+            xw[4 * q + 0] = __byte_perm(x0, x2, 0x5410);
+            xw[4 * q + 1] = __byte_perm(x0, x2, 0x7632);
+            xw[4 * q + 2] = __byte_perm(x1, x3, 0x5410);
+            xw[4 * q + 3] = __byte_perm(x1, x3, 0x7632);
+          }
         }
 #pragma unroll
         for (int j = 0; j < 8; ++j)
@@ -164,17 +203,27 @@ gemv_mma_kernel(const GemvParams p) {
   }
 }
 
-template <bool BF16, bool W4, int TG, int MINB>
+template <bool BF16, bool W4, int TG, int MINB, bool LIN = false>
 static cudaError_t launch_gemv_one(const GemvParams& p, cudaStream_t st) {
   // persistent over 16-row tiles: one resident wave (occupancy x SMs), never more CTAs than tiles
   static int occ = 0;
-  const int smem = W4 ? 256 * 32 * 4 : 0;
+  const int smem = (W4 && !LIN) ? 256 * 32 * 4 : 0;
   if (!occ) {
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gemv_mma_kernel<BF16, W4, TG, MINB>, 256, smem) != cudaSuccess || occ < 1) occ = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gemv_mma_kernel<BF16, W4, TG, MINB, LIN>, 256, smem) != cudaSuccess || occ < 1) occ = 1;
   }
   const long long tiles = (p.N + 15) / 16;
   const unsigned grid = (unsigned)(tiles < (long long)kNumSMs * occ ? tiles : (long long)kNumSMs * occ);
-  return launch_pdl(gemv_mma_kernel<BF16, W4, TG, MINB>, grid, 256, smem, st, p);
+  return launch_pdl(gemv_mma_kernel<BF16, W4, TG, MINB, LIN>, grid, 256, smem, st, p);
+}
+
+template <bool BF16>
+static int launch_gemv_lin(const GemvParams& p, cudaStream_t st) {
+  cudaError_t e;
+  if (p.M <= 8) e = launch_gemv_one<BF16, true, 1, 2, true>(p, st);
+  else if (p.M <= 16) e = launch_gemv_one<BF16, true, 2, 2, true>(p, st);
+  else if (p.M <= 32) e = launch_gemv_one<BF16, true, 4, 2, true>(p, st);
+  else e = launch_gemv_one<BF16, true, 8, 1, true>(p, st);
+  return (int)e;
 }
 
 template <bool BF16, bool W4>
@@ -219,5 +268,19 @@ B200_API int b200_w4_gemv_batched(const void* x, const uint8_t* packed, const fl
   p.M = M; p.K = K; p.N = N; p.x_rs = x_rs; p.w_rs = 0; p.y_rs = y_rs; p.out_f32 = 0; p.group = group;
   if (dtype == B200_DT_BF16) return launch_gemv<true, true>(p, (cudaStream_t)stream);
   if (dtype == B200_DT_FP16) return launch_gemv<false, true>(p, (cudaStream_t)stream);
+  return B200_ERR_UNSUPPORTED;
+}
+
+B200_API int b200_w4_gemv_linear(const void* x, const uint8_t* packed, const float* scale, const float* zs, const void* bias,
+                                 void* y, int M, long long N, int K, int group, long long x_rs, long long y_rs, float lin_a,
+                                 float lin_off, int dtype, void* stream) {
+  if (M < 1 || M > 64 || K % 128 || group % 32 || K % group || x_rs % 8) return B200_ERR_BAD_SHAPE;
+  if (lin_off != (float)(int)lin_off || lin_off < -64.f || lin_off > 64.f) return B200_ERR_UNSUPPORTED;
+  GemvParams p = {};
+  p.x = (const uint16_t*)x; p.w = packed; p.scale = scale; p.zs = zs; p.lut = nullptr; p.bias = bias; p.y = y;
+  p.M = M; p.K = K; p.N = N; p.x_rs = x_rs; p.w_rs = 0; p.y_rs = y_rs; p.out_f32 = 0; p.group = group;
+  p.lin_a = lin_a; p.lin_off = lin_off;
+  if (dtype == B200_DT_BF16) return launch_gemv_lin<true>(p, (cudaStream_t)stream);
+  if (dtype == B200_DT_FP16) return launch_gemv_lin<false>(p, (cudaStream_t)stream);
   return B200_ERR_UNSUPPORTED;
 }

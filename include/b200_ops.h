@@ -312,6 +312,12 @@ int b200_gemv16(const void* x, const void* w, const void* bias, void* y, int M, 
 int b200_w4_gemv_batched(const void* x, const uint8_t* packed, const float* scale, const float* zs, const float* lut,
                          const void* bias, void* y, int M, long long N, int K, int group, long long x_rs, long long y_rs,
                          int dtype, void* stream);
+/* The same for 4-bit codes whose table is linear, lut[c] = lin_a * (c - lin_off) with an integer lin_off (RTN / GPTQ / AWQ
+ * integers: lin_a 1, lin_off 8 or 0): table-free conversion (nibble OR-ed into the mantissa of 128.0 / 1024.0, one exact
+ * add, one FMA), 1 <= M <= 64. NF4 (non-linear code book) keeps the table kernels. */
+int b200_w4_gemv_linear(const void* x, const uint8_t* packed, const float* scale, const float* zs, const void* bias, void* y,
+                        int M, long long N, int K, int group, long long x_rs, long long y_rs, float lin_a, float lin_off,
+                        int dtype, void* stream);
 
 /* ---- gradient fold (csrc/elementwise.cu) -------------------------------------------------------
  * y (fp32) += scale * x (bf16/fp16), optionally clearing x: folds the low-precision .grad autograd produced for

@@ -146,8 +146,34 @@ def w4_dequant(packed, scale, zs, N: int, K: int, group: int, lut: Optional[torc
     return out
 
 
+_LIN_CACHE = {}
+_LIN_ON = __import__("os").environ.get("B200_W4_LINEAR", "1") != "0"
+
+
+def linear_lut(lut) -> Optional[tuple]:
+    """(a, off) when ``lut[c] == a * (c - off)`` with an integer ``off`` (RTN / GPTQ / AWQ integer codes), else None.
+    Decided once per table (one device read, cached by storage), never inside a graph capture."""
+    if lut is None or not _LIN_ON:
+        return None
+    key = (lut.data_ptr(), lut.device)
+    hit = _LIN_CACHE.get(key, 0)
+    if hit != 0:
+        return hit
+    if lut.is_cuda and torch.cuda.is_current_stream_capturing():
+        return None
+    v = lut.detach().float().cpu().tolist()
+    a = v[1] - v[0]
+    res = None
+    if len(v) == 16 and a != 0.0:
+        off = -v[0] / a
+        if abs(off - round(off)) < 1e-6 and abs(off) <= 64 and all(abs(v[c] - a * (c - round(off))) <= 1e-6 * max(1.0, abs(v[c])) for c in range(16)):
+            res = (float(a), float(round(off)))
+    _LIN_CACHE[key] = res
+    return res
+
+
 def w4_gemv(x, packed, scale, zs, N: int, K: int, group: int, lut=None, bias=None) -> torch.Tensor:
-    """y[m, :] = x[m, :] @ dequant(W)^T for 1 <= m <= 8 rows (decode)."""
+    """y[m, :] = x[m, :] @ dequant(W)^T for 1 <= m <= 64 rows (decode / serving steps)."""
     M = x.shape[0]
     if not nv.use_native(x):
         w = _w4_dequant_ref(packed, scale, zs, N, K, group, lut, torch.float32)
@@ -157,6 +183,14 @@ def w4_gemv(x, packed, scale, zs, N: int, K: int, group: int, lut=None, bias=Non
         return y.to(x.dtype)
     x = x.contiguous()
     y = torch.empty(M, N, dtype=x.dtype, device=x.device)
+    lin = linear_lut(lut) if K % 128 == 0 else None
+    if lin is not None:   # integer codes: table-free conversion (csrc/gemv.cu, LIN)
+        f32 = ctypes.c_float
+        fl = nv.proto("b200_w4_gemv_linear", [vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, i64, i64, f32, f32, i32, vp])
+        nv.check(fl(nv.ptr(x), nv.ptr(packed), nv.ptr(scale), nv.ptr(zs), nv.ptr(bias), nv.ptr(y), M, N, K, group,
+                    x.stride(0), y.stride(0), lin[0], lin[1], nv.dtype_code(x.dtype), nv.stream()), "w4_gemv_linear")
+        nv.count_launch()
+        return y
     if M > 8:     # 9..64 tokens: token groups of 8 share one pass over the codes (csrc/gemv.cu)
         fb = nv.proto("b200_w4_gemv_batched", [vp, vp, vp, vp, vp, vp, vp, i32, i64, i32, i32, i64, i64, i32, vp])
         nv.check(fb(nv.ptr(x), nv.ptr(packed), nv.ptr(scale), nv.ptr(zs), nv.ptr(lut), nv.ptr(bias), nv.ptr(y), M, N, K,

@@ -338,3 +338,11 @@ def test_small_m_gemv_kernels(M, dtype):
     y = W4.w4_gemv(x, packed, scale, scale * 8, N_, K, 128, lut, b)
     wd = W4.w4_dequant(packed, scale, scale * 8, N_, K, 128, lut, dtype)
     assert rel(y, x.float() @ wd.float().t() + b.float()) < 1e-2
+    # integer codes take the table-free kernel; a non-linear table (NF4, or this shuffled one) and symmetric int4 with the
+    # offset inside the table (lut[c] = c - 8, no zero term) must agree with the dequantised product too
+    assert W4.linear_lut(lut) == (1.0, 0.0)
+    for tbl, zs in ((lut - 8, None), (lut.flip(0).contiguous() * 0.5, None), (torch.tensor([0.1 * (c % 5) - c * c / 100 for c in range(16)], device=DEV), scale * 0.3)):
+        y2 = W4.w4_gemv(x, packed, scale, zs, N_, K, 128, tbl, None)
+        wd2 = W4.w4_dequant(packed, scale, zs, N_, K, 128, tbl, dtype)
+        assert rel(y2, x.float() @ wd2.float().t()) < 1e-2
+    assert W4.linear_lut(lut - 8) == (1.0, 8.0) and W4.linear_lut(lut.flip(0).contiguous() * 0.5) == (-0.5, 15.0)
