@@ -94,23 +94,36 @@ allreduce_kernel(PeerPtrs data, PeerPtrs flags, PeerPtrs lowp, long long n, int 
   const long long nvec = n / 4;
   const long long per = (nvec + world - 1) / world;
   const long long lo = per * rank, hi = min(nvec, lo + per);
-  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  // U vectors per thread per step: U x world 16-byte loads in flight per thread hide the ~2-3 us NVLink round trip
+  constexpr int U = 4;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += step * U) {
+    float4 v[U][kMaxRanks];
 #pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r) {
-      if (r < world) {
-        const float4 v = reinterpret_cast<const float4*>(data.p[r])[i];
-        acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
-      }
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * step;
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r)
+        if (r < world && i < hi) v[u][r] = reinterpret_cast<const float4*>(data.p[r])[i];
     }
-    acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
 #pragma unroll
-    for (int r = 0; r < kMaxRanks; ++r) {
-      if (r < world) {
-        reinterpret_cast<float4*>(data.p[r])[i] = acc;
-        if (lowp.p[r]) {
-          uint2 pk = make_uint2(pack_bf16x2(acc.x, acc.y), pack_bf16x2(acc.z, acc.w));
-          reinterpret_cast<uint2*>(lowp.p[r])[i] = pk;
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * step;
+      if (i >= hi) break;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < world) { acc.x += v[u][r].x; acc.y += v[u][r].y; acc.z += v[u][r].z; acc.w += v[u][r].w; }
+      }
+      acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r) {
+        if (r < world) {
+          reinterpret_cast<float4*>(data.p[r])[i] = acc;
+          if (lowp.p[r]) {
+            uint2 pk = make_uint2(pack_bf16x2(acc.x, acc.y), pack_bf16x2(acc.z, acc.w));
+            reinterpret_cast<uint2*>(lowp.p[r])[i] = pk;
+          }
         }
       }
     }

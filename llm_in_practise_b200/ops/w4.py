@@ -146,17 +146,15 @@ def w4_dequant(packed, scale, zs, N: int, K: int, group: int, lut: Optional[torc
     return out
 
 
-_LIN_CACHE = {}
 _LIN_ON = __import__("os").environ.get("B200_W4_LINEAR", "1") != "0"
 
 
 def linear_lut(lut) -> Optional[tuple]:
     """(a, off) when ``lut[c] == a * (c - off)`` with an integer ``off`` (RTN / GPTQ / AWQ integer codes), else None.
-    Decided once per table (one device read, cached by storage), never inside a graph capture."""
+    Decided once per table tensor (one device read), never inside a graph capture."""
     if lut is None or not _LIN_ON:
         return None
-    key = (lut.data_ptr(), lut.device)
-    hit = _LIN_CACHE.get(key, 0)
+    hit = getattr(lut, "_b200_lin", 0)      # cached on the tensor object (an address can be reused by another table)
     if hit != 0:
         return hit
     if lut.is_cuda and torch.cuda.is_current_stream_capturing():
@@ -168,7 +166,7 @@ def linear_lut(lut) -> Optional[tuple]:
         off = -v[0] / a
         if abs(off - round(off)) < 1e-6 and abs(off) <= 64 and all(abs(v[c] - a * (c - round(off))) <= 1e-6 * max(1.0, abs(v[c])) for c in range(16)):
             res = (float(a), float(round(off)))
-    _LIN_CACHE[key] = res
+    lut._b200_lin = res
     return res
 
 

@@ -159,11 +159,11 @@ def test_packed_prefill_matches_per_prompt_prefill():
 
 def test_linear_code_table_detection():
     """Integer code books (RTN / GPTQ / AWQ) are recognised as a * (code - off); NF4 and arbitrary tables are not."""
-    from llm_in_practise_b200.ops.w4 import NF4_TABLE, linear_lut
+    from llm_in_practise_b200.ops.w4 import NF4_CODE, linear_lut
     lut = torch.arange(16, dtype=torch.float32)
     assert linear_lut(lut) == (1.0, 0.0)
     assert linear_lut(lut - 8) == (1.0, 8.0)
     assert linear_lut((lut - 8) * 0.25) == (0.25, 8.0)
-    assert linear_lut(NF4_TABLE.clone()) is None
+    assert linear_lut(NF4_CODE.clone().float()) is None
     assert linear_lut(lut * lut) is None
     assert linear_lut(lut - 7.5) is None          # offset must be an integer
