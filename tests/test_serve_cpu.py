@@ -40,6 +40,26 @@ def test_continuous_batching_matches_sequential(model):
     assert sorted(eng.free) == [0, 1] and eng.metrics.generation_tokens == sum(len(w) for w in want)
 
 
+def test_packed_admission_respects_token_budget(model):
+    """Several prompts admitted in one iteration run as one packed prefill; the token budget splits a burst over
+    iterations (a single over-long prompt is still admitted alone); results equal one-by-one generation."""
+    torch.manual_seed(2)
+    prompts = [torch.randint(0, 300, (n,)).tolist() for n in (6, 6, 6, 20, 4)]
+    g = Generator(model, max_len=64)
+    want = [g.generate(torch.tensor([p]), max_new_tokens=5, do_sample=False)[0, len(p):].tolist() for p in prompts]
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=8, max_model_len=64, max_prefill_per_step=8, max_prefill_tokens=13))
+    reqs = [eng.submit(p, GenerationConfig(max_new_tokens=5, do_sample=False)) for p in prompts]
+    eng.step()
+    assert eng.num_running == 2 and eng.num_waiting == 3          # 6 + 6 fit the budget of 13, the third prompt does not
+    eng.step()
+    assert eng.num_waiting == 2                                    # third admitted alone (20 does not fit behind it)
+    eng.step()
+    assert eng.num_waiting == 1                                    # the 20-token prompt exceeds the budget but goes alone
+    while not all(r.done.is_set() for r in reqs):
+        eng.step()
+    assert [r.output_ids for r in reqs] == want
+
+
 def test_openai_endpoints(model):
     tok = ByteTokenizer()
     eng = LLMEngine(model, tok, EngineArgs(max_num_seqs=4, max_model_len=128), model_name="tiny").start()
