@@ -146,3 +146,40 @@ def test_loadtest_against_app(model):
         eng.shutdown()
     assert out["requests"] == 6 and out["failures"] == 0 and out["completion_tokens"] > 0
     assert out["aggregate_tokens_per_second"] > 0
+
+
+def test_cache_gateway_levels_and_metrics():
+    """Exact (L2) and semantic (L3) response caches in front of a chat endpoint: miss -> upstream, identical request -> L2,
+    re-worded request -> L3 (then promoted to L2), sampled / streaming requests bypass, upstream failures become 502."""
+    from fastapi.testclient import TestClient
+    from llm_in_practise_b200.serve.cache_gateway import build_cache_gateway, hashed_ngram_embedding
+    calls = []
+
+    async def upstream(payload):
+        if payload["messages"][-1]["content"] == "boom":
+            raise RuntimeError("backend down")
+        calls.append(payload)
+        return {"id": f"cmpl-{len(calls)}", "choices": [{"message": {"role": "assistant", "content": f"answer {len(calls)}"}}],
+                "usage": {"completion_tokens": 2}}
+
+    c = TestClient(build_cache_gateway(upstream, ttl=60, semantic_threshold=0.9))
+    q1 = {"model": "m", "messages": [{"role": "user", "content": "How do I restart the nginx service on the server?"}]}
+    r = c.post("/v1/chat/completions", json=q1)
+    assert r.status_code == 200 and r.headers["X-Cache"] == "MISS" and len(calls) == 1
+    r2 = c.post("/v1/chat/completions", json=q1)
+    assert r2.headers["X-Cache"] == "HIT-L2" and r2.json() == r.json() and len(calls) == 1
+    q2 = {"model": "m", "messages": [{"role": "user", "content": "how do I restart the nginx service on the server ?"}]}
+    r3 = c.post("/v1/chat/completions", json=q2)
+    assert r3.headers["X-Cache"] == "HIT-L3" and r3.json() == r.json() and len(calls) == 1
+    assert c.post("/v1/chat/completions", json=q2).headers["X-Cache"] == "HIT-L2"          # promoted
+    q3 = {"model": "m", "messages": [{"role": "user", "content": "Write a haiku about tensor cores."}]}
+    assert c.post("/v1/chat/completions", json=q3).headers["X-Cache"] == "MISS" and len(calls) == 2
+    assert c.post("/v1/chat/completions", json=dict(q1, temperature=0.8)).headers["X-Cache"] == "BYPASS" and len(calls) == 3
+    assert c.post("/v1/chat/completions", json={"model": "m", "messages": []}).status_code == 400
+    assert c.post("/v1/chat/completions", json={"model": "m", "messages": [{"role": "user", "content": "boom"}]}).status_code == 502
+    m = c.get("/metrics").text
+    assert 'cache_gateway_requests_total{result="l2_hit"} 2' in m and 'result="l3_hit"} 1' in m and 'result="miss"} 3' in m
+    assert 'result="bypass"} 1' in m and 'result="upstream_error"} 1' in m and "cache_gateway_latency_seconds_bucket" in m
+    assert c.get("/healthz").json() == {"status": "ok"}
+    a, b = hashed_ngram_embedding("restart nginx now"), hashed_ngram_embedding("completely different text about GPUs")
+    assert abs(float(a.norm()) - 1) < 1e-5 and float(a @ b) < 0.5
