@@ -14,6 +14,8 @@
 #include "common.cuh"
 #include "../include/b200_ops.h"
 
+#include <stdlib.h>
+
 namespace b200 {
 
 __device__ __forceinline__ uint4 lora_philox(unsigned long long seed, unsigned long long q) {
@@ -237,6 +239,62 @@ using namespace b200;
   else if (r <= 64) { constexpr int R = 64; __VA_ARGS__; } \
   else return B200_ERR_TOO_LARGE;
 
+namespace b200 {
+// ---- down on the tensor cores (r <= 16, K % 32 == 0): the adapter rows are the 16-row A operand of mma.sync.m16n8k16, eight
+// tokens the B operand; a CTA owns 8 tokens, its 8 warps split K. Lane (g, t) fetches one 16-byte vector of token g and
+// of adapter rows g, g + 8 at k = 32 c + 8 t: both operands use the same lane -> k mapping, so the k order inside an
+// MMA is permuted consistently. Dropped elements are zeroed in place (exact) and 1 / keep is folded into the output scale.
+// Same Philox stream as the SIMT kernel above and as the backward kernels.
+__device__ __forceinline__ void mma_bf16_16816(float (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0, %1, %2, %3}, {%4, %5, %6, %7}, {%8, %9}, {%0, %1, %2, %3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1));
+}
+
+__global__ void __launch_bounds__(256)
+lora_down_mma_kernel(const uint16_t* __restrict__ X, const uint16_t* __restrict__ A, __nv_bfloat16* __restrict__ T, int M, int K,
+                     int r, long long x_rs, long long a_rs, long long t_rs, float alpha_eff, unsigned long long seed,
+                     uint32_t thresh) {
+  __shared__ float red[8][128];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+  const int m0 = blockIdx.x * 8, tok = m0 + g;
+  const bool tok_ok = tok < M, ra_ok = g < r, rb_ok = g + 8 < r;
+  const uint16_t* xp = X + (long long)(tok_ok ? tok : 0) * x_rs;
+  const uint16_t* pa = A + (long long)(ra_ok ? g : 0) * a_rs;
+  const uint16_t* pb = A + (long long)(rb_ok ? g + 8 : 0) * a_rs;
+  float c[4] = {0.f, 0.f, 0.f, 0.f};
+  const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+  for (int ch = warp; ch < K / 32; ch += 8) {
+    const int k = ch * 32 + t * 8;
+    uint4 xa = tok_ok ? *reinterpret_cast<const uint4*>(xp + k) : zero;
+    const uint4 wa = ra_ok ? __ldg(reinterpret_cast<const uint4*>(pa + k)) : zero;
+    const uint4 wb = rb_ok ? __ldg(reinterpret_cast<const uint4*>(pb + k)) : zero;
+    if (thresh && tok_ok) {
+      bool kp[8];
+      keep8(seed, (unsigned long long)tok * K + k, thresh, kp);
+      xa.x &= (kp[0] ? 0x0000FFFFu : 0u) | (kp[1] ? 0xFFFF0000u : 0u);
+      xa.y &= (kp[2] ? 0x0000FFFFu : 0u) | (kp[3] ? 0xFFFF0000u : 0u);
+      xa.z &= (kp[4] ? 0x0000FFFFu : 0u) | (kp[5] ? 0xFFFF0000u : 0u);
+      xa.w &= (kp[6] ? 0x0000FFFFu : 0u) | (kp[7] ? 0xFFFF0000u : 0u);
+    }
+    mma_bf16_16816(c, wa.x, wb.x, wa.y, wb.y, xa.x, xa.y);
+    mma_bf16_16816(c, wa.z, wb.z, wa.w, wb.w, xa.z, xa.w);
+  }
+  // c0: (row g, token 2t), c1: (row g, token 2t+1), c2: (row g+8, token 2t), c3: (row g+8, token 2t+1)
+#pragma unroll
+  for (int i = 0; i < 4; ++i) red[warp][lane * 4 + i] = c[i];
+  __syncthreads();
+  if (threadIdx.x < 128) {
+    float sum = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) sum += red[w][threadIdx.x];
+    const int ln = threadIdx.x >> 2, i = threadIdx.x & 3;
+    const int row = (ln >> 2) + ((i & 2) ? 8 : 0), tk = m0 + 2 * (ln & 3) + (i & 1);
+    if (row < r && tk < M) T[(long long)tk * t_rs + row] = __float2bfloat16_rn(sum * alpha_eff);
+  }
+}
+
+}  // namespace b200
+
 B200_API int b200_lora_down(const void* X, const void* A, void* T, int M, int K, int r, long long x_rs,
                             long long a_rs, long long t_rs, float alpha, unsigned long long seed, float p,
                             void* stream) {
@@ -244,6 +302,13 @@ B200_API int b200_lora_down(const void* X, const void* A, void* T, int M, int K,
   uint32_t thresh; float inv_keep;
   drop_params(p, &thresh, &inv_keep);
   cudaStream_t st = (cudaStream_t)stream;
+  static const bool simt = getenv("B200_LORA_DOWN_SIMT") != nullptr;
+  if (!simt && r <= 16 && K % 32 == 0 && ((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(A)) & 15) == 0) {
+    lora_down_mma_kernel<<<(unsigned)((M + 7) / 8), 256, 0, st>>>((const uint16_t*)X, (const uint16_t*)A, (__nv_bfloat16*)T, M, K, r,
+                                                                x_rs, a_rs, t_rs, alpha * inv_keep, seed, thresh);
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
 #define B200_DOWN(R, ROWS) lora_down_kernel<R, ROWS><<<(unsigned)((M + ROWS - 1) / ROWS), 256, 0, st>>>( \
       (const __nv_bfloat16*)X, (const __nv_bfloat16*)A, (__nv_bfloat16*)T, M, K, r, x_rs, a_rs, t_rs, alpha, seed, thresh, inv_keep)
   if (r <= 8) B200_DOWN(8, 4);

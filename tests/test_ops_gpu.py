@@ -222,6 +222,17 @@ def test_lora_small_kernels(r, p):
     assert rel(dx, dx0.float() + 1.5 * mask * (pm.float() @ a.float())) < 2e-2
 
 
+def test_lora_down_tensor_core_edges():
+    """mma.sync lora_down: token count not a multiple of 8, rank not a multiple of 8, strided activations, dropout."""
+    M, K, r, p, seed = 1003, 2048, 12, 0.2, 4242
+    x = torch.randn(M, K + 64, device=DEV, dtype=torch.bfloat16)[:, 32:K + 32]          # row stride K + 64, 16-byte aligned
+    a = (torch.randn(r, K, device=DEV) / 8).bfloat16()
+    mask = LR.keep_mask((M, K), seed, p, DEV).float() / (1 - p)
+    T = LR.lora_down(x, a, 2.0, seed, p)
+    assert T.shape == (M, r)
+    assert rel(T, 2.0 * (x.float() * mask) @ a.float().t()) < 2e-2
+
+
 @pytest.mark.parametrize("H,Hkv,D,S", [(8, 2, 128, 256), (12, 12, 64, 255), (4, 4, 64, 100), (4, 2, 128, 1536), (2, 2, 64, 1032)])
 def test_attention_tiled(H, Hkv, D, S):
     B = 2
