@@ -112,6 +112,54 @@ w4_dequant_kernel(W4Shards sh, T* __restrict__ out, long long N, int K, int grou
   }
 }
 
+// Same expansion with fully coalesced traffic: lane l of a warp takes the 32-bit word l of a 128-byte run of codes (8 weights)
+// and writes one 16-byte vector, so a warp reads 128 contiguous bytes and writes 512 contiguous bytes per step (the kernel
+// above gives every thread a 64-byte output run, i.e. 16-byte pieces at a 64-byte stride per store instruction). Four
+// independent steps per thread keep loads in flight. K % 8 == 0.
+template <typename T>
+__global__ void __launch_bounds__(256)
+w4_dequant_coalesced_kernel(W4Shards sh, T* __restrict__ out, long long N, int K, int group, const float* __restrict__ lut_g,
+                            long long out_rs) {
+  __shared__ float lut[16];
+  if (threadIdx.x < 16) lut[threadIdx.x] = lut_g ? lut_g[threadIdx.x] : kNF4[threadIdx.x];
+  __syncthreads();
+  constexpr int U = 4;
+  const long long nwords = N * (long long)K / 8;
+  const long long w0 = ((long long)blockIdx.x * blockDim.x + (threadIdx.x & ~31)) * U + (threadIdx.x & 31);
+  const int groups_per_row = K / group;
+  uint32_t code[U];
+  float sc[U], zs[U];
+  long long oidx[U];
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    const long long w = w0 + u * 32;
+    oidx[u] = -1;
+    if (w < nwords) {
+      const long long e = w * 8, n = e / K;
+      const int k = (int)(e - n * K);
+      const int s = sh.nshards > 1 ? (int)(n / sh.rows_per_shard) : 0;
+      const long long nl = n - (long long)s * sh.rows_per_shard;
+      code[u] = *reinterpret_cast<const uint32_t*>(sh.packed[s] + (nl * K + k) / 2);
+      sc[u] = sh.scale[s][nl * groups_per_row + k / group];
+      zs[u] = sh.zs[s] ? sh.zs[s][nl * groups_per_row + k / group] : 0.f;
+      oidx[u] = n * out_rs + k;
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < U; ++u) {
+    if (oidx[u] < 0) continue;
+    uint4 ov;
+    T* oe = reinterpret_cast<T*>(&ov);
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const uint32_t byte = (code[u] >> (8 * b)) & 0xFFu;
+      oe[2 * b] = from_f32<T>(lut[byte >> 4] * sc[u] - zs[u]);
+      oe[2 * b + 1] = from_f32<T>(lut[byte & 15u] * sc[u] - zs[u]);
+    }
+    *reinterpret_cast<uint4*>(out + oidx[u]) = ov;
+  }
+}
+
 // Transposed expansion: out_t[k, n] = w[n, k] (out_t row stride out_rs elements). Used by the backward pass so that
 // dgrad (dY x W) reads W^T as a K-major tcgen05 operand instead of the slower MN-major path. One CTA (128 threads)
 // owns a 64(n) x 64(k) tile: each thread expands one 16-byte chunk (32 weights of one row) into a padded shared
@@ -394,6 +442,16 @@ B200_API int b200_w4_dequant(const void* const* packed, const void* const* scale
   const long long chunks = N * (K / 32);
   const unsigned grid = (unsigned)((chunks + 255) / 256);
   cudaStream_t st = (cudaStream_t)stream;
+  static const bool v1 = getenv("B200_W4_DEQUANT_V1") != nullptr;
+  if (!v1 && out_rs % 8 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+    const long long nwords = N * (long long)K / 8;
+    const unsigned g2 = (unsigned)((nwords + 256 * 4 - 1) / (256 * 4));
+    if (out_dtype == B200_DT_BF16) w4_dequant_coalesced_kernel<__nv_bfloat16><<<g2, 256, 0, st>>>(sh, (__nv_bfloat16*)out, N, K, group, lut, out_rs);
+    else if (out_dtype == B200_DT_FP16) w4_dequant_coalesced_kernel<__half><<<g2, 256, 0, st>>>(sh, (__half*)out, N, K, group, lut, out_rs);
+    else return B200_ERR_UNSUPPORTED;
+    B200_LAUNCH_CHECK();
+    return 0;
+  }
   if (out_dtype == B200_DT_BF16) w4_dequant_kernel<__nv_bfloat16><<<grid, 256, 0, st>>>(sh, (__nv_bfloat16*)out, N, K, group, lut, out_rs);
   else if (out_dtype == B200_DT_FP16) w4_dequant_kernel<__half><<<grid, 256, 0, st>>>(sh, (__half*)out, N, K, group, lut, out_rs);
   else return B200_ERR_UNSUPPORTED;
