@@ -115,7 +115,7 @@ w4_dequant_kernel(W4Shards sh, T* __restrict__ out, long long N, int K, int grou
 // Same expansion with fully coalesced traffic: lane l of a warp takes the 32-bit word l of a 128-byte run of codes (8 weights)
 // and writes one 16-byte vector, so a warp reads 128 contiguous bytes and writes 512 contiguous bytes per step (the kernel
 // above gives every thread a 64-byte output run, i.e. 16-byte pieces at a 64-byte stride per store instruction). Four
-// independent steps per thread keep loads in flight. K % 8 == 0.
+// independent steps per thread keep loads in flight. K % 8 == 0. Measured slower than the kernel above (see b200_w4_dequant): opt-in.
 template <typename T>
 __global__ void __launch_bounds__(256)
 w4_dequant_coalesced_kernel(W4Shards sh, T* __restrict__ out, long long N, int K, int group, const float* __restrict__ lut_g,
@@ -442,8 +442,10 @@ B200_API int b200_w4_dequant(const void* const* packed, const void* const* scale
   const long long chunks = N * (K / 32);
   const unsigned grid = (unsigned)((chunks + 255) / 256);
   cudaStream_t st = (cudaStream_t)stream;
-  static const bool v1 = getenv("B200_W4_DEQUANT_V1") != nullptr;
-  if (!v1 && out_rs % 8 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+  // measured inside a training step (8-layer slice, ncu launch list): 63.5 us per call for the coalesced kernel vs 47.7 us for
+  // the one-chunk-per-thread kernel below (4x the load instructions, scale fetched per word) — kept as an option only
+  static const bool coalesced = getenv("B200_W4_DEQUANT_COALESCED") != nullptr;
+  if (coalesced && out_rs % 8 == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
     const long long nwords = N * (long long)K / 8;
     const unsigned g2 = (unsigned)((nwords + 256 * 4 - 1) / (256 * 4));
     if (out_dtype == B200_DT_BF16) w4_dequant_coalesced_kernel<__nv_bfloat16><<<g2, 256, 0, st>>>(sh, (__nv_bfloat16*)out, N, K, group, lut, out_rs);
