@@ -70,9 +70,15 @@ __device__ __forceinline__ void flash_drop4(const FlashParams& p, long long bh, 
   m[3] = r.w >= p.drop_thresh ? p.inv_keep : 0.f;
 }
 
-// byte offset of 16-byte chunk `c` of row `r` in a tile with CH chunks per row (CH = 8 or 16)
+// byte offset of 16-byte chunk `c` of row `r` in a tile with CH chunks per row. Rows of 128 / 256 bytes (CH = 8, 16) XOR the
+// chunk with the row's low 3 bits; rows of 64 / 192 bytes (CH = 4, 12: head_dim 32, 96) alternate between the two halves of
+// a 128-byte line by themselves, so XOR-ing the low 2 bits with (r >> 1) & 3 is what spreads 8 consecutive rows over the 8
+// 16-byte slots. Either way every ldmatrix (8 rows x 16 bytes) is conflict-free.
 template <int CH>
-__device__ __forceinline__ uint32_t tile_off(int r, int c) { return (uint32_t)((r * CH + (c ^ (r & 7))) << 4); }
+__device__ __forceinline__ uint32_t tile_off(int r, int c) {
+  if constexpr (CH % 8 == 0) return (uint32_t)((r * CH + (c ^ (r & 7))) << 4);
+  else return (uint32_t)((r * CH + (c ^ ((r >> 1) & 3))) << 4);
+}
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
   const int n = valid ? 16 : 0;
@@ -320,7 +326,8 @@ flash_delta_kernel(const uint16_t* __restrict__ o, const uint16_t* __restrict__ 
   const uint16_t* pd = dout + w * D;
   float acc = 0.f;
 #pragma unroll
-  for (int i = 0; i < D / 64; ++i) {
+  for (int i = 0; i < (D + 63) / 64; ++i) {
+    if ((i * 32 + lane) * 2 >= D) break;
     const uint32_t a = *reinterpret_cast<const uint32_t*>(po + (i * 32 + lane) * 2);
     const uint32_t c = *reinterpret_cast<const uint32_t*>(pd + (i * 32 + lane) * 2);
     float2 fa, fc;
@@ -793,7 +800,7 @@ static int launch_bwd(const FlashParams& p, const void* out, void* dqkv, int cau
 
 static int flash_check(int B, int S, int H, int Hkv, int D, int dtype) {
   if (B < 1 || S < 1 || H < 1 || Hkv < 1 || H % Hkv) return B200_ERR_BAD_SHAPE;
-  if (D != 64 && D != 128) return B200_ERR_UNSUPPORTED;
+  if (D != 32 && D != 64 && D != 96 && D != 128) return B200_ERR_UNSUPPORTED;
   if (dtype != B200_DT_BF16 && dtype != B200_DT_FP16) return B200_ERR_UNSUPPORTED;
   if (B > 65535 || H > 65535) return B200_ERR_BAD_SHAPE;
   return 0;
@@ -820,6 +827,8 @@ B200_API int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, 
   cudaStream_t st = (cudaStream_t)stream;
   const bool bf = dtype == B200_DT_BF16;
   if (D == 128) return bf ? launch_fwd<true, 128>(p, causal, st) : launch_fwd<false, 128>(p, causal, st);
+  if (D == 96) return bf ? launch_fwd<true, 96>(p, causal, st) : launch_fwd<false, 96>(p, causal, st);
+  if (D == 32) return bf ? launch_fwd<true, 32>(p, causal, st) : launch_fwd<false, 32>(p, causal, st);
   return bf ? launch_fwd<true, 64>(p, causal, st) : launch_fwd<false, 64>(p, causal, st);
 }
 
@@ -834,6 +843,8 @@ B200_API int b200_flash_attn_varlen_fwd(const void* qkv, void* out, const int* c
   cudaStream_t st = (cudaStream_t)stream;
   const bool bf = dtype == B200_DT_BF16;
   if (D == 128) return bf ? launch_fwd<true, 128>(p, causal, st) : launch_fwd<false, 128>(p, causal, st);
+  if (D == 96) return bf ? launch_fwd<true, 96>(p, causal, st) : launch_fwd<false, 96>(p, causal, st);
+  if (D == 32) return bf ? launch_fwd<true, 32>(p, causal, st) : launch_fwd<false, 32>(p, causal, st);
   return bf ? launch_fwd<true, 64>(p, causal, st) : launch_fwd<false, 64>(p, causal, st);
 }
 
@@ -852,5 +863,7 @@ B200_API int b200_flash_attn_bwd(const void* qkv, const void* out, const void* d
   B200_CHECK(cudaMemsetAsync(dqkv32, 0, (size_t)B * S * p.W * sizeof(float), st));
   const bool bf = dtype == B200_DT_BF16;
   if (D == 128) return bf ? launch_bwd<true, 128>(p, out, dqkv, causal, st) : launch_bwd<false, 128>(p, out, dqkv, causal, st);
+  if (D == 96) return bf ? launch_bwd<true, 96>(p, out, dqkv, causal, st) : launch_bwd<false, 96>(p, out, dqkv, causal, st);
+  if (D == 32) return bf ? launch_bwd<true, 32>(p, out, dqkv, causal, st) : launch_bwd<false, 32>(p, out, dqkv, causal, st);
   return bf ? launch_bwd<true, 64>(p, out, dqkv, causal, st) : launch_bwd<false, 64>(p, out, dqkv, causal, st);
 }

@@ -288,7 +288,7 @@ int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_v, const 
  * an L x L boolean mask per forward, ddp_gpt_wikitext2.py:93-95; HF Qwen3 uses SDPA, Fine-Tuning/qwen3-8b-lora-dist.py:118).
  * dropout_p > 0 drops attention probabilities (nn.MultiheadAttention(dropout=0.1), ddp_gpt_wikitext2.py:92) with a Philox
  * mask that depends only on (seed, batch, head, row, key): pass the same p and seed to the backward.
- * 16-bit dtypes, D in {64, 128}, any S. The backward recomputes P from lse: delta [B, H, S] and dqkv32 [B*S, W] (fp32)
+ * 16-bit dtypes, D in {32, 64, 96, 128}, any S. The backward recomputes P from lse: delta [B, H, S] and dqkv32 [B*S, W] (fp32)
  * are caller-provided work buffers (dqkv32 is zeroed inside), dqkv [B*S, W] receives the 16-bit gradient. */
 int b200_flash_attn_fwd(const void* qkv, void* out, float* lse, int B, int S, int H, int Hkv, int D, int causal,
                         float scale, float dropout_p, unsigned long long seed, int dtype, void* stream);

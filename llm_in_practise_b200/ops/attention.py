@@ -2,7 +2,7 @@
 
 Two native paths share this front end:
 
-* ``flash`` (``csrc/flash_attn.cu``; 16-bit dtypes, head_dim 64 / 128, no window; probability dropout in-kernel): 64 x 64
+* ``flash`` (``csrc/flash_attn.cu``; 16-bit dtypes, head_dim 32 / 64 / 96 / 128, no window; probability dropout in-kernel): 64 x 64
   tiles, online softmax forward, recomputing backward, no L x L tensor in memory in either direction.
 * ``tiled`` (always available): batched tcgen05 GEMMs (``csrc/gemm_tcgen05.cu``) around fused
   masked-softmax kernels (``csrc/loss.cu``); scores exist per (batch, head) as a transient.
@@ -206,7 +206,7 @@ def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, 
     if not nv.use_native(qkv) or (S % 8 and not causal) or qkv.dtype == torch.float32 and False:
         return _ref_attention(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)
     if impl in ("auto", "flash") and _flash_available() and qkv.dtype in (torch.bfloat16, torch.float16) \
-            and head_dim in (64, 128) and window == 0:
+            and head_dim in (32, 64, 96, 128) and window == 0:
         from .flash import flash_attention
         seed = 0
         if dropout_p > 0.0:

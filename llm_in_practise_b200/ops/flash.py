@@ -15,7 +15,7 @@ vp, i32, f32, u64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_ulon
 
 
 def flash_supported(qkv: torch.Tensor, head_dim: int) -> bool:
-    return qkv.dtype in (torch.bfloat16, torch.float16) and head_dim in (64, 128)
+    return qkv.dtype in (torch.bfloat16, torch.float16) and head_dim in (32, 64, 96, 128)
 
 
 def _fwd(qkv, B, S, H, Hkv, D, causal, scale, want_lse=True, dropout_p=0.0, seed=0):

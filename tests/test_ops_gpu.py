@@ -251,7 +251,7 @@ def test_attention_tiled(H, Hkv, D, S):
 
 
 @pytest.mark.parametrize("causal", [True, False])
-@pytest.mark.parametrize("D,dtype", [(64, torch.bfloat16), (128, torch.float16)])
+@pytest.mark.parametrize("D,dtype", [(64, torch.bfloat16), (128, torch.float16), (32, torch.bfloat16), (96, torch.float16)])
 def test_flash_attention_dropout(D, dtype, causal):
     """In-kernel attention-probability dropout: the mask is read back through one-hot values (q = k = 0 makes P uniform),
     then forward and backward with random inputs and the same seed must match the fp32 reference that uses that mask."""
@@ -289,7 +289,9 @@ def test_flash_attention_dropout(D, dtype, causal):
 @pytest.mark.parametrize("causal", [True, False])
 @pytest.mark.parametrize("H,Hkv,D,S,dtype", [(8, 2, 128, 256, torch.bfloat16), (12, 12, 64, 255, torch.bfloat16),
                                              (5, 1, 128, 77, torch.float16), (4, 2, 128, 1100, torch.bfloat16),
-                                             (40, 8, 128, 512, torch.bfloat16), (2, 2, 64, 64, torch.float16)])
+                                             (40, 8, 128, 512, torch.bfloat16), (2, 2, 64, 64, torch.float16),
+                                             (4, 4, 32, 256, torch.bfloat16), (8, 2, 96, 200, torch.bfloat16),
+                                             (6, 3, 96, 130, torch.float16), (4, 1, 32, 77, torch.float16)])
 def test_flash_attention(H, Hkv, D, S, dtype, causal):
     """csrc/flash_attn.cu forward + backward against the fp32 reference of the same op (any S, GQA, both mask modes)."""
     B = 2
