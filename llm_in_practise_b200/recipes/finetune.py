@@ -76,9 +76,52 @@ PRESETS: Dict[str, Dict[str, Any]] = {
 }
 
 
+_ALL_LINEAR = ["q_proj", "k_proj", "v_proj", "o_proj", "gate_proj", "up_proj", "down_proj"]
+
+
+def preset_from_llamafactory_yaml(path: str) -> Dict[str, Any]:
+    """A LLaMA-Factory ``*_lora_sft.yaml`` (Fine-Tuning/LLaMA-Factory/deepseek-r1-0528-qwen3_lora_sft.yaml:1-32:
+    ``stage: sft, finetuning_type: lora, lora_target: all, cutoff_len, per_device_train_batch_size,
+    gradient_accumulation_steps, learning_rate, num_train_epochs, lr_scheduler_type, warmup_ratio, bf16, output_dir,
+    logging_steps, save_steps``) as a preset of this pipeline. LLaMA-Factory's defaults fill what the file leaves out
+    (lora_rank 8, lora_alpha 2 x rank, lora_dropout 0); ``quantization_bit: 4`` selects the NF4 base."""
+    import yaml
+    with open(path, encoding="utf-8") as f:
+        text = f.read()
+    try:
+        y = yaml.safe_load(text) or {}
+    except yaml.YAMLError:
+        # the shipped recipe is not strict YAML (a scalar `dataset:` followed by list items): read top-level `key: value`
+        # lines only, which is all this front end uses
+        y = {}
+        for ln in text.splitlines():
+            ln = ln.split("#", 1)[0].rstrip()
+            if not ln or ln[0] in " \t-" or ":" not in ln:
+                continue
+            k, v = ln.split(":", 1)
+            y[k.strip()] = yaml.safe_load(v.strip()) if v.strip() else None
+    if y.get("stage", "sft") != "sft" or y.get("finetuning_type", "lora") != "lora":
+        raise ValueError(f"{path}: only `stage: sft` with `finetuning_type: lora` is supported")
+    tgt = y.get("lora_target", "all")
+    targets = _ALL_LINEAR if tgt == "all" else [t.strip() for t in str(tgt).split(",") if t.strip()]
+    r = int(y.get("lora_rank", 8))
+    args = dict(output_dir=y.get("output_dir", "./finetuned/llamafactory-sft"),
+                per_device_train_batch_size=int(y.get("per_device_train_batch_size", 1)),
+                gradient_accumulation_steps=int(y.get("gradient_accumulation_steps", 8)),
+                learning_rate=float(y.get("learning_rate", 1e-4)), num_train_epochs=float(y.get("num_train_epochs", 3.0)),
+                lr_scheduler_type=str(y.get("lr_scheduler_type", "cosine")), warmup_ratio=float(y.get("warmup_ratio", 0.0)),
+                bf16=bool(y.get("bf16", False)), fp16=bool(y.get("fp16", False)), logging_steps=int(y.get("logging_steps", 10)),
+                save_steps=int(y.get("save_steps", 500)))
+    return dict(model=y.get("model_name_or_path", "qwen3-8b"), nf4=int(y.get("quantization_bit", 0) or 0) == 4,
+                lora=dict(r=r, lora_alpha=int(y.get("lora_alpha", 2 * r)), lora_dropout=float(y.get("lora_dropout", 0.0)),
+                          target_modules=targets),
+                args=args, max_length=int(y.get("cutoff_len", 2048)), dynamic_padding=True)
+
+
 def main(argv=None):
     ap = argparse.ArgumentParser(description=__doc__.split("\n")[0], formatter_class=argparse.RawDescriptionHelpFormatter)
     ap.add_argument("--recipe", choices=sorted(PRESETS), default="qwen3-14b-qlora-dist-deepspeed")
+    ap.add_argument("--llamafactory_yaml", default=None, help="a LLaMA-Factory *_lora_sft.yaml: replaces --recipe")
     ap.add_argument("--model", default=None, help="HF checkpoint directory or preset name")
     ap.add_argument("--tokenizer", default=None, help="tokenizer directory (defaults to --model; byte tokenizer if none is found)")
     ap.add_argument("--data", default=None, help="self_cognition.jsonl (default: the copy shipped with the reference tree)")
@@ -89,9 +132,15 @@ def main(argv=None):
     ap.add_argument("--output_dir", default=None)
     ap.add_argument("--local_rank", type=int, default=-1)
     a = ap.parse_args(argv)
-    pre = PRESETS[a.recipe]
+    pre = preset_from_llamafactory_yaml(a.llamafactory_yaml) if a.llamafactory_yaml else PRESETS[a.recipe]
+    if a.llamafactory_yaml and "--max_length" not in (argv if argv is not None else __import__("sys").argv):
+        a.max_length = pre["max_length"]
     info = setup_distributed(a.local_rank)
     model_path = a.model or pre["model"]
+    if a.llamafactory_yaml and a.model is None and not os.path.isdir(str(model_path)):
+        from ..models.qwen3 import QWEN3_PRESETS
+        if str(model_path) not in QWEN3_PRESETS:
+            model_path = "qwen3-8b"                          # the YAML names a checkpoint directory that is not on this box
 
     # ---- tokenizer ----
     tok = None

@@ -61,3 +61,25 @@ def test_tools_roundtrip(tmp_path):
     ppl = tools.main(["eval-ppl", "--model", d + "/awq", "--num_samples", "2", "--max_tokens", "6"])
     assert ppl == ppl and ppl > 1.0
     infer.main(["once", "--model", d + "/awq", "--max_new_tokens", "4"])
+
+
+def test_finetune_from_llamafactory_yaml(tmp_path):
+    """A LLaMA-Factory `*_lora_sft.yaml` drives the same fine-tuning pipeline: lora_target all -> the seven Qwen3 linears,
+    cutoff_len, cosine schedule; the (not strictly valid) recipe shipped with the reference parses too."""
+    import json
+    from llm_in_practise_b200.recipes import finetune
+    ref = "/root/reference/Fine-Tuning/LLaMA-Factory/deepseek-r1-0528-qwen3_lora_sft.yaml"
+    if os.path.exists(ref):
+        q = finetune.preset_from_llamafactory_yaml(ref)
+        assert q["args"]["gradient_accumulation_steps"] == 8 and q["args"]["lr_scheduler_type"] == "cosine" and q["max_length"] == 2048
+        assert len(q["lora"]["target_modules"]) == 7 and q["lora"]["r"] == 8 and q["lora"]["lora_alpha"] == 16
+    d = str(tmp_path)
+    y = d + "/sft.yaml"
+    with open(y, "w") as f:
+        f.write("model_name_or_path: qwen3-tiny\nstage: sft\nfinetuning_type: lora\nlora_target: q_proj,v_proj\nlora_rank: 4\n"
+                "cutoff_len: 40\noutput_dir: %s/out\nper_device_train_batch_size: 2\ngradient_accumulation_steps: 1\n"
+                "learning_rate: 1.0e-3\nnum_train_epochs: 1.0\nlr_scheduler_type: cosine\nwarmup_ratio: 0.1\nbf16: true\n" % d)
+    finetune.main(["--llamafactory_yaml", y, "--max_steps", "2"])
+    assert os.path.exists(d + "/out/adapter_model.safetensors")
+    cfg = json.load(open(d + "/out/adapter_config.json"))
+    assert cfg["r"] == 4 and cfg["lora_alpha"] == 8 and sorted(cfg["target_modules"]) == ["q_proj", "v_proj"]
