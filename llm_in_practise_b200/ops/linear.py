@@ -44,6 +44,10 @@ def weight_workspace(device, dtype, numel: int, slot: int = 0) -> torch.Tensor:
     return buf[:numel]
 
 
+# largest token count served by the 4-bit GEMV instead of dequant + GEMM (measured, profiles/inference.md: at batch 48 the
+# table-free GEMV gives 12.4 ms per token vs 14.3 ms for dequant + GEMM, at batch 64 14.1 vs 14.7 ms)
+_W4_GEMV_MAX_M = int(__import__("os").environ.get("B200_W4_GEMV_MAX_M", "64"))   # integer-code weights (table-free kernel); NF4: 32
+
 class _LinearFn(torch.autograd.Function):
     """Dense linear. If ``w`` has ``main_grad`` (flat-arena fp32 gradient) the weight gradient is
     accumulated there by the wgrad GEMM (beta = 1) and autograd receives None for it."""
@@ -320,7 +324,8 @@ class FusedLinear(nn.Module):
             seed = ew.layer_seed(self.layer_uid) if (self.training and self.lora_dropout > 0) else 0
             y = _LoraLinearFn.apply(x2, self, seed, *self._adapter_params())
         elif (self.nf4 is not None and not torch.is_grad_enabled() and x2.is_cuda
-              and (x2.shape[0] <= 8 or (x2.shape[0] <= 32 and self.in_features % 128 == 0))
+              and (x2.shape[0] <= 8 or (x2.shape[0] <= (_W4_GEMV_MAX_M if hasattr(self.nf4, "_lut") else 32)
+                                        and self.in_features % 128 == 0))
               and hasattr(self.nf4, "group") and not hasattr(self.nf4, "shards")
               and x2.dtype in (torch.bfloat16, torch.float16)):
             # decode: fused 4-bit GEMV straight from the packed weights (memory-bound, 4.25 bits/weight read)
