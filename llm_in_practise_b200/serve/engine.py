@@ -54,6 +54,7 @@ class Request:
     stream: "queue.Queue" = field(default_factory=queue.Queue)
     error: Optional[str] = None
     token_times: List[float] = field(default_factory=list)   # perf_counter at every emitted token (TTFT / ITL statistics)
+    aborted: bool = False                                    # set by LLMEngine.abort(): dropped at the next scheduler iteration
 
     @property
     def ttft(self) -> Optional[float]:
@@ -134,6 +135,19 @@ class LLMEngine:
                 break
             nb *= 2
         torch.cuda.synchronize()
+
+    def abort(self, r: Request) -> None:
+        """Stop generating for ``r`` (client went away, or a stop string matched in the server layer): a waiting request
+        finishes immediately, a running one leaves the batch and frees its KV slot at the next iteration
+        (``finish_reason = "abort"``)."""
+        with self._cv:
+            if r.done.is_set():
+                return
+            r.aborted = True
+            if r in self.waiting:
+                self.waiting.remove(r)
+                self._finish(r, "abort")
+            self._cv.notify_all()
 
     def submit(self, prompt_ids: Sequence[int], cfg: Optional[GenerationConfig] = None) -> Request:
         cfg = cfg or GenerationConfig()
@@ -296,6 +310,10 @@ class LLMEngine:
             for r, tok in zip(batch, self._sample(logits, batch)):
                 if not self._emit(r, tok):
                     self.running.append(r)
+        if any(r.aborted for r in self.running):
+            for r in [r for r in self.running if r.aborted]:
+                self._finish(r, "abort")
+            self.running = [r for r in self.running if not r.aborted]
         if not self.running:
             return
         reqs = self.running

@@ -43,6 +43,7 @@ class ChatCompletionRequest(BaseModel):
     stream: Optional[bool] = False
     top_k: Optional[int] = 0
     repetition_penalty: Optional[float] = 1.0
+    stop: Optional[Union[str, List[str]]] = None    # vLLM / OpenAI stop strings (not in the reference's FastAPI schema)
 
 
 class CompletionRequest(BaseModel):
@@ -52,6 +53,7 @@ class CompletionRequest(BaseModel):
     top_p: Optional[float] = 1.0
     max_tokens: Optional[int] = 16
     stream: Optional[bool] = False
+    stop: Optional[Union[str, List[str]]] = None
 
 
 def deepseek_prompt_from_messages(messages: List[ChatMessage]) -> str:
@@ -72,6 +74,16 @@ def chatml_prompt_from_messages(messages: List[ChatMessage]) -> str:
 
 
 PROMPT_STYLES = {"deepseek": deepseek_prompt_from_messages, "chatml": chatml_prompt_from_messages}
+
+
+def _stops(stop) -> List[str]:
+    return [] if not stop else ([stop] if isinstance(stop, str) else [x for x in stop if x])
+
+
+def cut_at_stop(text: str, stops: List[str]):
+    """(text truncated at the earliest stop string, True if one matched)."""
+    cut = min((i for i in (text.find(x) for x in stops) if i >= 0), default=-1)
+    return (text, False) if cut < 0 else (text[:cut], True)
 
 
 def render_metrics(engine: LLMEngine) -> str:
@@ -163,25 +175,36 @@ def build_app(engine: Optional[LLMEngine], prompt_style: str = "chatml", allow_s
             def events():
                 head = {"id": cid, "object": "chat.completion.chunk", "created": created, "model": req.model}
                 yield "data: " + json.dumps({**head, "choices": [{"index": 0, "delta": {"role": "assistant"}, "finish_reason": None}]}) + "\n\n"
-                sent, acc = "", []
+                sent, acc, stops, hit = "", [], _stops(req.stop), False
+                hold = max((len(x) for x in stops), default=1) - 1     # characters that could still become a stop string
                 for tok in r.tokens():
                     acc.append(tok)
                     text = decode(eng, acc)
                     if text.endswith("�"):          # incomplete UTF-8 sequence: wait for the next token
                         continue
-                    delta, sent = text[len(sent):], text
+                    text, hit = cut_at_stop(text, stops)
+                    safe = text if hit else text[:max(len(text) - hold, len(sent))]
+                    delta, sent = safe[len(sent):], safe
                     if delta:
                         yield "data: " + json.dumps({**head, "choices": [{"index": 0, "delta": {"content": delta}, "finish_reason": None}]}, ensure_ascii=False) + "\n\n"
-                yield "data: " + json.dumps({**head, "choices": [{"index": 0, "delta": {}, "finish_reason": r.finish_reason}]}) + "\n\n"
+                    if hit:
+                        eng.abort(r)
+                        break
+                if not hit:
+                    tail = cut_at_stop(decode(eng, acc), stops)[0][len(sent):]
+                    if tail:
+                        yield "data: " + json.dumps({**head, "choices": [{"index": 0, "delta": {"content": tail}, "finish_reason": None}]}, ensure_ascii=False) + "\n\n"
+                yield "data: " + json.dumps({**head, "choices": [{"index": 0, "delta": {}, "finish_reason": "stop" if hit else r.finish_reason}]}) + "\n\n"
                 yield "data: [DONE]\n\n"
             return StreamingResponse(events(), media_type="text/event-stream")
         r.done.wait()
         if r.error:
             raise HTTPException(status_code=500, detail=r.error)
         text = decode(eng, r.output_ids).replace("<|user|>", "").replace("<|assistant|>", "").strip()
+        text, hit = cut_at_stop(text, _stops(req.stop))
         n_p, n_c = len(ids), len(r.output_ids)
         return {"id": cid, "object": "chat.completion", "created": created, "model": req.model,
-                "choices": [{"index": 0, "message": {"role": "assistant", "content": text}, "finish_reason": r.finish_reason}],
+                "choices": [{"index": 0, "message": {"role": "assistant", "content": text}, "finish_reason": "stop" if hit else r.finish_reason}],
                 "usage": {"prompt_tokens": n_p, "completion_tokens": n_c, "total_tokens": n_p + n_c}}
 
     @app.post("/v1/completions")
@@ -200,7 +223,8 @@ def build_app(engine: Optional[LLMEngine], prompt_style: str = "chatml", allow_s
             r.done.wait()
             if r.error:
                 raise HTTPException(status_code=500, detail=r.error)
-            choices.append({"index": i, "text": decode(eng, r.output_ids), "finish_reason": r.finish_reason, "logprobs": None})
+            text, hit = cut_at_stop(decode(eng, r.output_ids), _stops(req.stop))
+            choices.append({"index": i, "text": text, "finish_reason": "stop" if hit else r.finish_reason, "logprobs": None})
             n_p += len(r.prompt_ids)
             n_c += len(r.output_ids)
         return {"id": f"cmpl-{uuid.uuid4().hex}", "object": "text_completion", "created": int(time.time()), "model": req.model,

@@ -183,3 +183,47 @@ def test_cache_gateway_levels_and_metrics():
     assert c.get("/healthz").json() == {"status": "ok"}
     a, b = hashed_ngram_embedding("restart nginx now"), hashed_ngram_embedding("completely different text about GPUs")
     assert abs(float(a.norm()) - 1) < 1e-5 and float(a @ b) < 0.5
+
+
+def test_stop_strings_and_abort(model):
+    """`stop` truncates the completion at the first match (finish_reason "stop"), also while streaming, where the rest of the
+    generation is aborted; LLMEngine.abort frees the KV slot of a running request and drops a waiting one."""
+    import json
+    tok = ByteTokenizer()
+    eng = LLMEngine(model, tok, EngineArgs(max_num_seqs=2, max_model_len=128), model_name="tiny").start()
+    try:
+        c = TestClient(build_app(eng, prompt_style="deepseek"))
+        body = {"model": "tiny", "messages": [{"role": "user", "content": "hello there"}], "max_tokens": 24, "temperature": 0.0}
+        full = c.post("/v1/chat/completions", json=body).json()["choices"][0]["message"]["content"]
+        assert len(full) >= 6
+        stop = full[3:5]
+        want = full[:full.find(stop)]
+        j = c.post("/v1/chat/completions", json=dict(body, stop=[stop, "\x00never"])).json()
+        assert j["choices"][0]["message"]["content"] == want.strip() or j["choices"][0]["message"]["content"] == want
+        assert j["choices"][0]["finish_reason"] == "stop"
+        with c.stream("POST", "/v1/chat/completions", json=dict(body, stream=True, stop=stop)) as r:
+            chunks = [json.loads(ln[6:]) for ln in r.iter_lines() if ln.startswith("data: {")]
+        text = "".join(ch["choices"][0]["delta"].get("content", "") for ch in chunks)
+        assert stop not in text and want.startswith(text.rstrip()) or text == want
+        assert chunks[-1]["choices"][0]["finish_reason"] == "stop"
+        cj = c.post("/v1/completions", json={"model": "tiny", "prompt": "abc", "max_tokens": 12, "temperature": 0.0, "stop": "\x00never"}).json()
+        assert cj["choices"][0]["finish_reason"] == "length"
+    finally:
+        eng.shutdown()
+    eng2 = LLMEngine(model, None, EngineArgs(max_num_seqs=1, max_model_len=64))
+    a = eng2.submit([1, 2, 3], GenerationConfig(max_new_tokens=40, do_sample=False))
+    b = eng2.submit([4, 5], GenerationConfig(max_new_tokens=3, do_sample=False))
+    eng2.step(); eng2.step()
+    assert eng2.num_running == 1 and eng2.num_waiting == 1
+    eng2.abort(a)
+    while not b.done.is_set():
+        eng2.step()
+    assert a.finish_reason == "abort" and a.done.is_set() and 0 < len(a.output_ids) < 40
+    assert b.finish_reason == "length" and len(b.output_ids) == 3 and sorted(eng2.free) == [0]
+    w = eng2.submit([7], GenerationConfig(max_new_tokens=2, do_sample=False))
+    w2 = eng2.submit([8], GenerationConfig(max_new_tokens=2, do_sample=False))
+    eng2.abort(w2)
+    assert w2.finish_reason == "abort" and eng2.num_waiting == 1
+    while not w.done.is_set():
+        eng2.step()
+    assert len(w.output_ids) == 2
