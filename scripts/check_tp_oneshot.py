@@ -1,6 +1,7 @@
-"""One-shot tensor-parallel all-reduce (b200_allreduce_oneshot) against NCCL, eagerly and replayed from a CUDA graph.
+"""One-shot tensor-parallel all-reduce (b200_allreduce_oneshot) against NCCL, eagerly and replayed from a CUDA graph, with
+injected rank skew (device-side sleeps before eager calls, host-side sleeps before replays).
   torchrun --nproc-per-node 2 --master-addr 127.0.0.1 scripts/check_tp_oneshot.py"""
-import json, os, sys
+import json, os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 import torch.distributed as dist
@@ -17,6 +18,8 @@ for it, (rows, dt) in enumerate([(1, torch.bfloat16), (8, torch.bfloat16), (64, 
     y = torch.randn(rows, 1024, device=dev, generator=g).to(dt)
     want = y.float().clone()
     dist.all_reduce(want)
+    if it % world == rank:
+        torch.cuda._sleep(20_000_000)                     # injected rank skew (~10 ms on the device): peers must wait on the flags
     got = tp.all_reduce(y)
     worst = max(worst, float((got.float() - want).abs().max() / want.abs().max()))
 # graph: three dependent all-reduces per replay, new inputs every replay
@@ -37,6 +40,8 @@ with torch.cuda.graph(graph):
 gworst = 0.0
 for it in range(6):
     x.copy_(torch.randn(8, 1024, device=dev, generator=g).to(torch.bfloat16))
+    if it % world == rank:
+        time.sleep(0.02)                                  # host-side skew between the ranks' replays
     graph.replay()
     xs = x.float().clone()
     dist.all_reduce(xs)                                   # a = sum x
