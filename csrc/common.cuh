@@ -62,15 +62,18 @@ inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, s
 }
 
 // Error codes returned by the C ABI on top of cudaError_t (which is < 1000).
-enum B200Status : int {
+#ifndef B200_STATUS_CODES
+#define B200_STATUS_CODES
+enum B200Status {
   B200_OK = 0,
   B200_ERR_BAD_SHAPE = 10001,
   B200_ERR_BAD_ALIGN = 10002,
   B200_ERR_NO_DRIVER = 10003,
   B200_ERR_TENSORMAP = 10004,
   B200_ERR_TOO_LARGE = 10005,
-  B200_ERR_UNSUPPORTED = 10006,
+  B200_ERR_UNSUPPORTED = 10006
 };
+#endif
 
 namespace b200 {
 

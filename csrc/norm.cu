@@ -377,7 +377,14 @@ B200_API int b200_norm_bwd_noalloc(int layer_norm, const void* dy, const void* h
   }
   const int nvec = cols / V;
   const int mv = ceil_div(nvec, kNormThreads);
-  if (mv > 4) return B200_ERR_TOO_LARGE;
+  if (mv > 4) {
+    // fp32 activations: a thread holds 4 columns per vector instead of 8, so the row limit of the kernel is half
+    fprintf(stderr,
+            "b200_norm_bwd_noalloc: cols = %d exceeds the limit for this activation type (%d columns for fp32, %d for "
+            "bf16 / fp16); use b200_norm_bwd with caller-provided scratch instead\n",
+            cols, kNoAllocMaxCols / 2, kNoAllocMaxCols);
+    return B200_ERR_TOO_LARGE;
+  }
   float* scratch = nullptr;
   int rc = norm_bwd_noalloc_scratch(&scratch);
   if (rc) return rc;

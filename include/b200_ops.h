@@ -23,14 +23,18 @@ enum {
   B200_DT_FP32 = 2, /* as GEMM input: multiplied on the tensor cores as TF32 */
 };
 
-enum {
-  B200_ERR_BAD_SHAPE_ = 10001,   /* shape / size argument out of the supported domain          */
-  B200_ERR_BAD_ALIGN_ = 10002,   /* pointer or stride not a multiple of 16 bytes               */
-  B200_ERR_NO_DRIVER_ = 10003,   /* cuTensorMapEncodeTiled could not be resolved               */
-  B200_ERR_TENSORMAP_ = 10004,   /* the driver rejected a TMA descriptor                       */
-  B200_ERR_TOO_LARGE_ = 10005,   /* size beyond a kernel's stated maximum                      */
-  B200_ERR_UNSUPPORTED_ = 10006, /* dtype / flag combination not implemented                   */
+#ifndef B200_STATUS_CODES
+#define B200_STATUS_CODES
+enum B200Status {
+  B200_OK = 0,
+  B200_ERR_BAD_SHAPE = 10001,   /* shape / size argument out of the supported domain          */
+  B200_ERR_BAD_ALIGN = 10002,   /* pointer or stride not a multiple of 16 bytes               */
+  B200_ERR_NO_DRIVER = 10003,   /* cuTensorMapEncodeTiled could not be resolved               */
+  B200_ERR_TENSORMAP = 10004,   /* the driver rejected a TMA descriptor                       */
+  B200_ERR_TOO_LARGE = 10005,   /* size beyond a kernel's stated maximum                      */
+  B200_ERR_UNSUPPORTED = 10006  /* dtype / flag combination not implemented                   */
 };
+#endif
 
 /* ------------------------------------------------------------------------------------------
  * K1 / K3: tcgen05 GEMM.  D[b] = alpha * A[b] x B[b / b_div]^T (+ A2 x B2^T) (+ bias) + beta * D[b]
@@ -114,8 +118,9 @@ int b200_norm_bwd(int layer_norm, const void* dy, const void* h, const void* w, 
  * whose HBM is already committed to its KV-cache pool, a host that forbids cudaMalloc after
  * start-up, a bare C harness with no allocator behind it). This entry point has no counterpart
  * in the reference. The dw/db partial rows live in an 8 MiB array built into the library (resident on every
- * GPU that loads it, until exit); limits: cols <= b200_norm_bwd_noalloc_max_cols() (8192), else
- * B200_ERR_TOO_LARGE_ and nothing runs. It calls no cudaMalloc/cudaFree. The first call on each
+ * GPU that loads it, until exit); limits: cols <= b200_norm_bwd_noalloc_max_cols() (8192) for bf16 / fp16
+ * activations and half of that (4096) for fp32 activations, else B200_ERR_TOO_LARGE with a message on
+ * stderr and nothing runs. It calls no cudaMalloc/cudaFree. The first call on each
  * device looks the array's address up (cudaGetSymbolAddress) — make that call before any stream
  * capture. All calls share the array: nothing needs clearing between calls, but calls that may
  * overlap on the GPU race on it and must be serialised by the caller. */

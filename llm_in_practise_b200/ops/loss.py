@@ -70,22 +70,48 @@ def cross_entropy(logits: torch.Tensor, targets: torch.Tensor, ignore_index: int
     return F.cross_entropy(logits.reshape(-1, vocab).float(), targets.reshape(-1), ignore_index=ignore_index)
 
 
+# Upstream gradient the training loop will send into the loss (1 / grad_accum, times the fp16 loss scale), declared
+# BEFORE the forward pass. With it declared, a head weight that lives in a flat arena gets its gradient accumulated
+# straight into ``main_grad`` during the forward launch sequence, already scaled; without it (None) the weight gradient
+# is kept in a temporary and added to ``main_grad`` in backward, multiplied by whatever gradient autograd delivers.
+_DECLARED_GRAD_SCALE: Optional[float] = None
+
+
+class grad_scale_context:
+    """``with grad_scale_context(1 / grad_accum * loss_scale): loss = model(x, y)`` — the engines and training loops
+    of this package wrap their forward in it; ``loss.backward(gradient=that scale)`` (or ``(loss * scale).backward()``)
+    must follow."""
+
+    def __init__(self, scale: Optional[float]):
+        self.scale, self.prev = scale, None
+
+    def __enter__(self):
+        global _DECLARED_GRAD_SCALE
+        self.prev, _DECLARED_GRAD_SCALE = _DECLARED_GRAD_SCALE, self.scale
+        return self
+
+    def __exit__(self, *exc):
+        global _DECLARED_GRAD_SCALE
+        _DECLARED_GRAD_SCALE = self.prev
+        return False
+
+
 class _LinearCEFn(torch.autograd.Function):
-    """loss = mean CE(x @ w^T). Gradients are formed in forward (scaled by 1/n_valid) and multiplied
-    by the upstream scalar in backward."""
+    """loss = mean CE(x @ w^T). Gradients are formed in forward (scaled by 1/n_valid, and by the declared upstream
+    scale when there is one) and multiplied by the (remaining) upstream factor in backward."""
 
     @staticmethod
-    def forward(ctx, x, w, targets, ignore_index, n_valid, chunk_tokens, w_main_grad):
+    def forward(ctx, x, w, targets, ignore_index, n_valid, chunk_tokens, w_main_grad, need_dx, need_dw, declared):
         M, K = x.shape
         V = w.shape[0]
         ld = (V + 7) // 8 * 8  # padded leading dimension keeps every logits row 16-byte aligned
-        need_dx = x.requires_grad
-        need_dw = w.requires_grad
+        pre = 1.0 if declared is None else float(declared)     # folded into the gradients formed here
         inv = 1.0 / max(n_valid, 1)
         dx = torch.empty_like(x) if need_dx else None
         dw = None
+        in_place = need_dw and w_main_grad is not None and declared is not None
         if need_dw:
-            dw = w_main_grad if w_main_grad is not None else torch.zeros(V, K, dtype=torch.float32, device=x.device)
+            dw = w_main_grad if in_place else torch.zeros(V, K, dtype=torch.float32, device=x.device)
         loss_sum = torch.zeros((), dtype=torch.float32, device=x.device)
         t = targets.reshape(-1).contiguous()
         chunk = min(chunk_tokens, M)
@@ -94,37 +120,49 @@ class _LinearCEFn(torch.autograd.Function):
             e = min(M, s + chunk)
             lg = buf[: e - s, :V]
             gemm(x[s:e], w, out=lg)
-            rows = _ce_native(lg, t[s:e], inv, need_dx or need_dw, ignore_index)
+            rows = _ce_native(lg, t[s:e], inv * pre, need_dx or need_dw, ignore_index)
             loss_sum += rows.sum()
             if need_dx:
                 gemm(lg, w, b_mn=True, out=dx[s:e])
             if need_dw:
                 gemm(lg, x[s:e], a_mn=True, b_mn=True, out=dw, beta=1.0)
-        ctx.save_for_backward(dx, dw if (need_dw and w_main_grad is None) else None)
-        ctx.dw_in_place = need_dw and w_main_grad is not None
+        ctx.save_for_backward(dx, None if (in_place or not need_dw) else dw)
+        ctx.pre = pre
+        ctx.main_grad = w_main_grad if (need_dw and not in_place) else None
         ctx.w_dtype = w.dtype
         return loss_sum * inv
 
     @staticmethod
     def backward(ctx, g):
         dx, dw = ctx.saved_tensors
-        gdx = None if dx is None else dx * g.to(dx.dtype)
-        gdw = None if dw is None else (dw * g).to(ctx.w_dtype)
-        return gdx, gdw, None, None, None, None, None
+        f = g if ctx.pre == 1.0 else g / ctx.pre            # what is left of the upstream gradient (1 when it was declared right)
+        gdx = None if dx is None else dx * f.to(dx.dtype)
+        gdw = None
+        if dw is not None:
+            if ctx.main_grad is not None:
+                ctx.main_grad.add_(dw * f)
+            else:
+                gdw = (dw * f).to(ctx.w_dtype)
+        # no ``_grad_ready`` call here: a tied head still receives the embedding's contribution at the very end of
+        # backward, and DDP reduces buckets whose hooks never fired when backward finishes
+        return (gdx, gdw) + (None,) * 8
 
 
 def linear_cross_entropy(x: torch.Tensor, w: torch.Tensor, targets: torch.Tensor, ignore_index: int = -100,
                          n_valid: Optional[int] = None, chunk_tokens: int = 4096) -> torch.Tensor:
     """Fused lm_head + cross-entropy. x: [tokens, K], w: [vocab, K], targets: [tokens].
 
-    If ``w`` carries a ``main_grad`` fp32 buffer (flat-arena parameters) the weight gradient is
-    accumulated there directly and autograd sees no gradient for ``w``; this assumes the upstream
-    gradient of the loss is 1 (the usual ``loss.backward()``), which the training engines guarantee
-    by folding loss scaling into ``n_valid``."""
+    Under ``torch.no_grad()`` (evaluation) no gradient of any kind is formed. If ``w`` carries a ``main_grad`` fp32
+    buffer (flat-arena parameters) the weight gradient ends up there and autograd sees none for ``w``: accumulated
+    during forward when the upstream gradient was declared with ``grad_scale_context`` (the engines do), otherwise
+    held in a temporary and added in backward times the gradient autograd delivers — correct for any
+    ``(loss * c).backward()``."""
     if nv.use_native(x) and x.dtype in (torch.bfloat16, torch.float16):
         if n_valid is None:
             n_valid = int((targets != ignore_index).sum().item())
+        ge = torch.is_grad_enabled()
         return _LinearCEFn.apply(x.contiguous(), w, targets, ignore_index, n_valid, chunk_tokens,
-                                 getattr(w, "main_grad", None))
+                                 getattr(w, "main_grad", None), ge and x.requires_grad, ge and w.requires_grad,
+                                 _DECLARED_GRAD_SCALE if ge else None)
     logits = x.float() @ w.float().t()
     return F.cross_entropy(logits, targets.reshape(-1), ignore_index=ignore_index)

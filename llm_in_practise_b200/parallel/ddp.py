@@ -30,13 +30,14 @@ from .symm import PeerFlags, SymmBuffer, allreduce_, symm_available
 
 
 class _Bucket:
-    __slots__ = ("lo", "hi", "params", "pending", "launched", "work")
+    __slots__ = ("lo", "hi", "params", "pending", "launched", "ready", "work")
 
     def __init__(self, lo: int, hi: int):
         self.lo, self.hi = lo, hi
         self.params: List[nn.Parameter] = []
         self.pending = 0
         self.launched = False
+        self.ready = False
         self.work = None
 
 
@@ -85,6 +86,7 @@ class DistributedDataParallel(nn.Module):
                 for b in module.buffers():
                     dist.broadcast(b, src=0)
         self._build_buckets(int(bucket_cap_mb * 1024 * 1024))
+        self._next_bucket = 0
         self._callback_queued = False
         self._exposed_events: List[tuple] = []
 
@@ -126,7 +128,9 @@ class DistributedDataParallel(nn.Module):
         for b in self.buckets:
             b.pending = set(id(p) for p in b.params)
             b.launched = False
+            b.ready = False
             b.work = None
+        self._next_bucket = 0
 
     # ------------------------------------------------------------------ reduction
     def make_optimizer(self, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8, weight_decay: float = 0.01,
@@ -151,8 +155,17 @@ class DistributedDataParallel(nn.Module):
             torch.autograd.Variable._execution_engine.queue_callback(self._finalize_backward)
         b = self.buckets[p._ddp_bucket]
         b.pending.discard(id(p))
-        if not b.pending and not b.launched:
-            self._launch(b)
+        if not b.pending:
+            b.ready = True
+        # Buckets are reduced strictly in index order, like torch's Reducer: the collectives of one step share the
+        # epoch-flag channels, so every rank has to issue the same sequence even when gradients become ready in a
+        # different order on different ranks (data-dependent MoE routing, unused parameters). A ready bucket waits
+        # for its predecessors; whatever is left is flushed, in order, when backward ends.
+        while self._next_bucket < len(self.buckets) and self.buckets[self._next_bucket].ready:
+            nb = self.buckets[self._next_bucket]
+            self._next_bucket += 1
+            if not nb.launched:
+                self._launch(nb)
 
     def _launch(self, b: _Bucket) -> None:
         b.launched = True

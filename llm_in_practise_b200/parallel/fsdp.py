@@ -287,7 +287,7 @@ class FullyShardedDataParallel(nn.Module):
 
     # ------------------------------------------------------------------ scheduling
     def _post_forward(self, u: _Unit) -> None:
-        if self.strategy == ShardingStrategy.FULL_SHARD and torch.is_grad_enabled() is not None:
+        if self.strategy == ShardingStrategy.FULL_SHARD:
             u.reshard()
 
     def _on_grad(self, p: nn.Parameter) -> None:

@@ -420,16 +420,23 @@ class ZeroEngine(nn.Module):
                 out[k + "_ms"] = float(t)
         return out
 
+    def _loss_factor(self) -> float:
+        s = 1.0 / self.ga
+        if self.scaler is not None:
+            s *= self.scaler.scale
+        return s
+
     def forward(self, *args, **kwargs):
         ew.set_step(self.global_steps, self.micro_steps % self.ga)
-        with self._phase("forward"):
+        from ..ops.loss import grad_scale_context
+        # the factor ``backward`` will apply is declared up front so a fused lm_head + loss can scale the gradients
+        # it forms during the forward launches (tied / trainable heads write their weight gradient there)
+        with self._phase("forward"), grad_scale_context(self._loss_factor() if torch.is_grad_enabled() else None):
             return self.module(*args, **kwargs)
 
     def backward(self, loss: torch.Tensor) -> None:
         """Scales by 1/accumulation (and the fp16 loss scale) like DeepSpeed, then backpropagates into the arena."""
-        s = 1.0 / self.ga
-        if self.scaler is not None:
-            s *= self.scaler.scale
+        s = self._loss_factor()
         with self._phase("backward"):
             (loss * s).backward()
         self.micro_steps += 1
@@ -522,10 +529,15 @@ class ZeroEngine(nn.Module):
         nv.check(fn(ctypes.byref(a), nv.stream()), "zero_step")
         nv.count_launch()
         ev1.record()
-        self._timers.setdefault("zero_step", []).append((ev0, ev1))
+        lst = self._timers.setdefault("zero_step", [])
+        lst.append((ev0, ev1))
+        if len(lst) > 256:
+            del lst[:128]
         torch.autograd.graph.increment_version(self.arena.data)
         if self.scaler is not None:
             overflow = bool(self._stats[2].item() != 0)
+            if overflow:
+                opt._step -= 1          # a skipped step does not advance the bias-correction counter (DeepSpeed semantics)
             self.skipped_steps += int(overflow)
             self.scaler.update(overflow)
 
@@ -631,6 +643,9 @@ class ZeroEngine(nn.Module):
                 self.optimizer.load_state_dict(st["optimizer_state_dict"])
                 if self.scaler is not None and st.get("loss_scale"):
                     self.scaler.scale = st["loss_scale"]
+            else:
+                log.warning("checkpoint %s was written by %d ranks, this job has %d: optimizer state NOT restored "
+                            "(parameters are); the moments restart from zero", d, st["world_size"], self.world)
         torch.autograd.graph.increment_version(self.arena.data)
         return d, ms.get("client_state", {})
 

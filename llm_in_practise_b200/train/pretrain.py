@@ -44,6 +44,7 @@ from ..data.datasets import DistributedSampler, TokenizedDataset, default_collat
 from ..data.tokenizers import BPETokenizer, ByteTokenizer, load_or_train_bpe, load_pretrained_tokenizer
 from ..models.deepseeklike import DeepSeekLike
 from ..models.gpt import GPTLike, SimpleTransformer
+from ..ops.loss import grad_scale_context
 from ..parallel.dist import all_reduce_mean_scalar, cleanup_distributed, get_info, setup_distributed
 
 
@@ -359,10 +360,10 @@ def run_pretraining(cfg: PretrainConfig) -> Dict[str, Any]:
                 sync_ctx = wrapped.no_sync() if (not boundary and hasattr(wrapped, "no_sync")) else None
                 if sync_ctx is not None:
                     sync_ctx.__enter__()
-                with _autocast(cfg, device):
+                up = (scaler.scale if scaler is not None else 1.0) / cfg.grad_accum
+                with _autocast(cfg, device), grad_scale_context(up):
                     loss = _loss_of(wrapped(x, y))
-                l = loss / cfg.grad_accum
-                (l * scaler.scale if scaler is not None else l).backward()
+                (loss * up).backward()
                 if sync_ctx is not None:
                     sync_ctx.__exit__(None, None, None)
                 if boundary:

@@ -221,9 +221,12 @@ class Trainer:
             loss = _get_loss(out)
             self.engine.backward(loss)
             return loss.detach()
-        out = self.fsdp(**batch)
+        from ..ops.loss import grad_scale_context
+        up = 1.0 / self.args.gradient_accumulation_steps
+        with grad_scale_context(up):
+            out = self.fsdp(**batch)
         loss = _get_loss(out)
-        (loss / self.args.gradient_accumulation_steps).backward()
+        (loss * up).backward()
         return loss.detach()
 
     def _optimizer_step(self) -> None:
@@ -426,8 +429,17 @@ class Trainer:
     def _save_checkpoint(self) -> None:
         d = os.path.join(self.args.output_dir, f"checkpoint-{self.state.global_step}")
         self.save_model(d)
+        W, R = self.info.world_size, self.info.rank
+        if W > 1:
+            dist.barrier()          # rank 0 has created the directory
+            # ZeRO (stage >= 1) and FSDP keep optimizer state only for this rank's shard: one file per rank, like
+            # DeepSpeed's zero_pp_rank_<r>_* files (HF writes the same through engine.save_checkpoint)
+            os.makedirs(d, exist_ok=True)
+            torch.save({"world_size": W, "rank": R, "state": self.optimizer.state_dict()},
+                       os.path.join(d, f"optimizer_rank{R}.pt"))
         if self.is_world_process_zero():
-            torch.save(self.optimizer.state_dict(), os.path.join(d, "optimizer.pt"))
+            if W == 1:
+                torch.save(self.optimizer.state_dict(), os.path.join(d, "optimizer.pt"))
             torch.save(self.lr_scheduler.state_dict(), os.path.join(d, "scheduler.pt"))
             torch.save({"python": random.getstate(), "numpy": np.random.get_state(), "cpu": torch.get_rng_state(),
                         "cuda": torch.cuda.get_rng_state_all() if torch.cuda.is_available() else None},
@@ -465,7 +477,21 @@ class Trainer:
 
     def _load_checkpoint(self, d: str) -> None:
         self._load_model_weights(d)
-        if os.path.exists(os.path.join(d, "optimizer.pt")):
+        W, R = self.info.world_size, self.info.rank
+        mine = os.path.join(d, f"optimizer_rank{R}.pt")
+        if W > 1 and os.path.exists(mine):
+            ck = torch.load(mine, map_location="cpu", weights_only=False)
+            if ck["world_size"] != W:
+                raise RuntimeError(f"{d} holds optimizer shards of a {ck['world_size']}-rank job; this job has {W} ranks "
+                                   "(sharded optimizer state cannot be re-partitioned on load)")
+            self.optimizer.load_state_dict(ck["state"])
+        elif W > 1 and any(f.startswith("optimizer_rank") for f in os.listdir(d)):
+            raise RuntimeError(f"{d} has per-rank optimizer files but none for rank {R}: written by a smaller job")
+        elif W > 1 and os.path.exists(os.path.join(d, "optimizer.pt")):
+            import logging
+            logging.getLogger("llm_in_practise_b200.trainer").warning(
+                "%s holds a single-process optimizer.pt; with %d ranks the state is sharded, so it is NOT loaded", d, W)
+        elif os.path.exists(os.path.join(d, "optimizer.pt")):
             self.optimizer.load_state_dict(torch.load(os.path.join(d, "optimizer.pt"), map_location="cpu", weights_only=False))
         if os.path.exists(os.path.join(d, "scheduler.pt")):
             self.lr_scheduler.load_state_dict(torch.load(os.path.join(d, "scheduler.pt"), weights_only=False))

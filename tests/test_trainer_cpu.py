@@ -81,3 +81,41 @@ def test_classifier_trainer_eval_and_best_model(tmp_path):
     assert "eval_accuracy" in m and "eval_loss" in m
     assert m["eval_accuracy"] >= 0.8 and abs(m["eval_accuracy"] - tr.state.best_metric) < 1e-9   # best checkpoint was reloaded
     assert tr.state.best_model_checkpoint is not None
+
+
+def _two_rank_resume(rank, world, out):
+    """2 ranks (gloo), ZeRO stage 2: optimizer state is sharded, so resume must load THIS rank's moments."""
+    from llm_in_practise_b200.parallel.dist import setup_distributed
+    setup_distributed()
+
+    def make():
+        torch.manual_seed(0)
+        model = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32)
+        return get_peft_model(model, LoraConfig(r=4, lora_alpha=8, target_modules=["q_proj", "v_proj"]))
+
+    ds = _Rows(32, 16, 1024)
+
+    def args(epochs, d):
+        return TrainingArguments(output_dir=os.path.join(out, d), per_device_train_batch_size=2, gradient_accumulation_steps=1,
+                                 num_train_epochs=epochs, learning_rate=5e-3, logging_steps=100, save_steps=4, save_total_limit=4,
+                                 lr_scheduler_type="constant",
+                                 report_to="none", deepspeed={"zero_optimization": {"stage": 2}, "gradient_clipping": 1.0,
+                                                              "gradient_accumulation_steps": "auto",
+                                                              "train_micro_batch_size_per_gpu": "auto", "train_batch_size": "auto"})
+    coll = DataCollatorForLanguageModeling(pad_token_id=0)
+    # uninterrupted: 2 epochs = 16 steps
+    pm = make()
+    Trainer(model=pm, args=args(2, "a"), train_dataset=ds, data_collator=coll).train()
+    # interrupted after 1 epoch (8 steps, checkpoint-8), resumed by a fresh trainer for the second epoch
+    pm1 = make()
+    Trainer(model=pm1, args=args(1, "b"), train_dataset=ds, data_collator=coll).train()
+    assert os.path.exists(os.path.join(out, "b", "checkpoint-8", f"optimizer_rank{rank}.pt"))
+    pm2 = make()
+    r = Trainer(model=pm2, args=args(2, "b"), train_dataset=ds, data_collator=coll).train(resume_from_checkpoint=True)
+    assert r.global_step == 16
+    assert torch.allclose(pm2.arena.data, pm.arena.data, rtol=1e-5, atol=1e-6), float((pm2.arena.data - pm.arena.data).abs().max())
+
+
+def test_two_rank_resume_restores_each_ranks_optimizer_shard(tmp_path):
+    from dist_utils import run_distributed
+    run_distributed(_two_rank_resume, 2, (str(tmp_path),))

@@ -100,3 +100,20 @@ def test_noalloc_refuses_sizes_beyond_its_scratch():
     rc = f_na(0, _ptr(t), _ptr(t), _ptr(w), _ptr(stats), None, _ptr(t.clone()), _ptr(w.clone()), None, 0, 2, cols,
               nv.DT_BF16, nv.DT_BF16, ctypes.c_void_p(torch.cuda.current_stream().cuda_stream))
     assert rc == 10005  # B200_ERR_TOO_LARGE: refused, nothing launched
+
+
+def test_noalloc_fp32_limit_is_half_the_16bit_one():
+    """fp32 activations are held 4 columns per vector, so the limit is 4096 columns; 4104 is refused (with a message on
+    stderr), 4096 runs."""
+    lib = nv.lib()
+    f_na = lib.b200_norm_bwd_noalloc
+    f_na.argtypes, f_na.restype = _ARGS_NOALLOC, ctypes.c_int
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    for cols, want in ((4104, 10005), (4096, 0)):
+        t = torch.randn(4, cols, device="cuda", dtype=torch.float32)
+        w = torch.ones(cols, device="cuda", dtype=torch.float32)
+        stats = torch.ones(4, 2, device="cuda")
+        rc = f_na(0, _ptr(t), _ptr(t), _ptr(w), _ptr(stats), None, _ptr(torch.empty_like(t)), _ptr(torch.zeros_like(w)), None,
+                  0, 4, cols, nv.DT_FP32, nv.DT_FP32, stream)
+        assert rc == want, (cols, rc)
+    torch.cuda.synchronize()
