@@ -487,6 +487,23 @@ B200_API int b200_peer_gather_skip(const void* const* src_ptrs, long long src_of
   return peer_gather_launch(src_ptrs, src_off_bytes, out, shard_bytes, world, skip, stream);
 }
 
+// Pull-based all-gather on the COPY ENGINES: one cudaMemcpyAsync per owner (peer pointers are ordinary UVA addresses
+// for the runtime), so prefetching the next layer's shards takes no SM and no shared memory away from the GEMMs that
+// run meanwhile. out = concat_r src_ptrs[r][off : off + shard_bytes]; rank `skip` (>= 0) is left out.
+B200_API int b200_peer_gather_ce(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
+                                 int world, int skip, void* stream) {
+  if (world < 1 || world > kMaxRanks || shard_bytes <= 0) return B200_ERR_BAD_SHAPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  for (int r = 0; r < world; ++r) {
+    if (r == skip) continue;
+    cudaError_t e = cudaMemcpyAsync(static_cast<char*>(out) + (long long)r * shard_bytes,
+                                    static_cast<const char*>(src_ptrs[r]) + src_off_bytes, (size_t)shard_bytes,
+                                    cudaMemcpyDeviceToDevice, st);
+    if (e != cudaSuccess) return (int)e;
+  }
+  return 0;
+}
+
 B200_API int b200_allreduce_oneshot(const void* y, const void* const* stage_ptrs, const void* const* flag_ptrs, void* out,
                                     long long n, long long half_elems, int world, int rank, int channel,
                                     unsigned int* state, int dtype, void* stream) {

@@ -22,7 +22,7 @@ template <typename T>
 __global__ void __launch_bounds__(kCEThreads)
 cross_entropy_kernel(T* __restrict__ logits, const long long* __restrict__ targets, float* __restrict__ loss_rows,
                      float* __restrict__ lse_rows, int vocab, long long row_stride, long long ignore_index,
-                     float grad_scale, int write_grad) {
+                     float grad_scale, int write_grad, const float* __restrict__ row_scale) {
   constexpr int V = 16 / sizeof(T);
   __shared__ float red[32];
   const long long row = blockIdx.x;
@@ -60,7 +60,9 @@ cross_entropy_kernel(T* __restrict__ logits, const long long* __restrict__ targe
   }
   if (!write_grad) return;
   __syncthreads();  // the target logit has been read before anyone overwrites the row
-  const float gsc = ignored ? 0.f : grad_scale;
+  // row_scale: per-row factor computed on the device (1 / (n_valid of the row's micro-batch * accumulation steps)),
+  // so the host never has to read the count of non-ignored targets back
+  const float gsc = ignored ? 0.f : grad_scale * (row_scale ? row_scale[row] : 1.f);
   for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
     uint4 raw = *reinterpret_cast<const uint4*>(lr + (long long)i * V);
     const T* e = reinterpret_cast<const T*>(&raw);
@@ -137,26 +139,34 @@ softmax_bwd_kernel(const TP* __restrict__ P, const TG* __restrict__ dP, TO* __re
 }  // namespace b200
 using namespace b200;
 
-B200_API int b200_cross_entropy(void* logits, const long long* targets, float* loss_rows, float* lse_rows,
-                                long long rows, int vocab, long long row_stride, long long ignore_index,
-                                float grad_scale, int write_grad, int dtype, void* stream) {
+// row_scale (may be NULL): float[rows], multiplied into grad_scale per row (device-computed normalisation).
+B200_API int b200_cross_entropy_rows(void* logits, const long long* targets, float* loss_rows, float* lse_rows,
+                                     long long rows, int vocab, long long row_stride, long long ignore_index,
+                                     float grad_scale, int write_grad, const float* row_scale, int dtype, void* stream) {
   if (rows <= 0 || vocab <= 0) return B200_ERR_BAD_SHAPE;
   const int es = dtype == B200_DT_FP32 ? 4 : 2;
   if ((row_stride * es) % 16 || (reinterpret_cast<uintptr_t>(logits) & 15)) return B200_ERR_BAD_ALIGN;
   cudaStream_t st = (cudaStream_t)stream;
   if (dtype == B200_DT_BF16)
     cross_entropy_kernel<__nv_bfloat16><<<(unsigned)rows, kCEThreads, 0, st>>>(
-        (__nv_bfloat16*)logits, targets, loss_rows, lse_rows, vocab, row_stride, ignore_index, grad_scale, write_grad);
+        (__nv_bfloat16*)logits, targets, loss_rows, lse_rows, vocab, row_stride, ignore_index, grad_scale, write_grad, row_scale);
   else if (dtype == B200_DT_FP32)
     cross_entropy_kernel<float><<<(unsigned)rows, kCEThreads, 0, st>>>(
-        (float*)logits, targets, loss_rows, lse_rows, vocab, row_stride, ignore_index, grad_scale, write_grad);
+        (float*)logits, targets, loss_rows, lse_rows, vocab, row_stride, ignore_index, grad_scale, write_grad, row_scale);
   else if (dtype == B200_DT_FP16)
     cross_entropy_kernel<__half><<<(unsigned)rows, kCEThreads, 0, st>>>(
-        (__half*)logits, targets, loss_rows, lse_rows, vocab, row_stride, ignore_index, grad_scale, write_grad);
+        (__half*)logits, targets, loss_rows, lse_rows, vocab, row_stride, ignore_index, grad_scale, write_grad, row_scale);
   else
     return B200_ERR_UNSUPPORTED;
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+B200_API int b200_cross_entropy(void* logits, const long long* targets, float* loss_rows, float* lse_rows,
+                                long long rows, int vocab, long long row_stride, long long ignore_index,
+                                float grad_scale, int write_grad, int dtype, void* stream) {
+  return b200_cross_entropy_rows(logits, targets, loss_rows, lse_rows, rows, vocab, row_stride, ignore_index, grad_scale,
+                                 write_grad, nullptr, dtype, stream);
 }
 
 B200_API int b200_softmax_fwd(const void* S, void* P, long long batch, int rows, int cols, int causal, int window,

@@ -165,6 +165,10 @@ int b200_cast(const void* x, void* y, long long n, float scale, int in_dtype, in
 int b200_cross_entropy(void* logits, const long long* targets, float* loss_rows, float* lse_rows, long long rows,
                        int vocab, long long row_stride, long long ignore_index, float grad_scale, int write_grad,
                        int dtype, void* stream);
+/* same, with a per-row factor read from the device (row_scale: float[rows] or NULL) multiplied into grad_scale */
+int b200_cross_entropy_rows(void* logits, const long long* targets, float* loss_rows, float* lse_rows, long long rows,
+                            int vocab, long long row_stride, long long ignore_index, float grad_scale, int write_grad,
+                            const float* row_scale, int dtype, void* stream);
 int b200_softmax_fwd(const void* S, void* P, long long batch, int rows, int cols, int causal, int window, float scale,
                      int in_dtype, int out_dtype, void* stream);
 int b200_softmax_bwd(const void* P, const void* dP, void* dS, long long total_rows, int cols, float scale,
@@ -268,6 +272,9 @@ int b200_allreduce_oneshot(const void* y, const void* const* stage_ptrs, const v
  * in place, only the world - 1 remote shards cross NVLink). */
 int b200_peer_gather_skip(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
                           int world, int skip, void* stream);
+/* the same gather issued as one cudaMemcpyAsync per owner (copy engines instead of SMs): the ZeRO-3 shard prefetch */
+int b200_peer_gather_ce(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
+                        int world, int skip, void* stream);
 int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int rank, unsigned int epoch,
                       void* stream);
 

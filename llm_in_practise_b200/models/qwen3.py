@@ -23,7 +23,7 @@ from torch.utils.checkpoint import checkpoint
 from ..ops import elementwise as ew
 from ..ops.attention import attention
 from ..ops.linear import FusedLinear
-from ..ops.loss import linear_cross_entropy
+from ..ops.loss import linear_cross_entropy, micro_batch_row_scale
 from ..ops.norm import rms_norm
 from ..ops.gemm import gemm
 
@@ -172,7 +172,10 @@ class Qwen3ForCausalLM(nn.Module):
 
     def forward(self, input_ids: torch.Tensor, labels: Optional[torch.Tensor] = None,
                 position_ids: Optional[torch.Tensor] = None, attention_mask=None, n_valid: Optional[int] = None,
-                **_) -> dict:
+                micro_batches: int = 0, **_) -> dict:
+        """``micro_batches`` = G > 0: the batch is G gradient-accumulation micro-batches stacked along dim 0; the loss
+        is the mean over micro-batches of each one's mean token loss (identical to G separate passes with loss / G)
+        and the normalisation is computed on the device (no host read-back)."""
         B, S = input_ids.shape
         hidden = self.hidden_states(input_ids, position_ids)
         if labels is None:
@@ -181,8 +184,9 @@ class Qwen3ForCausalLM(nn.Module):
         # HF causal-LM loss: predict token t+1 from position t; ignore_index = -100
         targets = torch.full_like(labels, -100)
         targets[:, :-1] = labels[:, 1:]
+        rs = micro_batch_row_scale(targets, micro_batches) if micro_batches > 0 else None
         loss = linear_cross_entropy(hidden, self.head_weight(), targets.reshape(-1), -100, n_valid,
-                                    self.ce_chunk_tokens)
+                                    self.ce_chunk_tokens, row_scale=rs)
         return {"loss": loss}
 
     # -------------------------------------------------------------------------------------

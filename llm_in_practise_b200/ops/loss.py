@@ -24,12 +24,13 @@ from .gemm import gemm
 vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
 
 
-def _ce_native(logits2, targets, grad_scale, write_grad, ignore_index):
+def _ce_native(logits2, targets, grad_scale, write_grad, ignore_index, row_scale=None):
     rows, vocab = logits2.shape
     loss_rows = torch.empty(rows, dtype=torch.float32, device=logits2.device)
-    fn = nv.proto("b200_cross_entropy", [vp, vp, vp, vp, i64, i32, i64, i64, f32, i32, i32, vp])
+    fn = nv.proto("b200_cross_entropy_rows", [vp, vp, vp, vp, i64, i32, i64, i64, f32, i32, vp, i32, vp])
     nv.check(fn(nv.ptr(logits2), nv.ptr(targets), nv.ptr(loss_rows), None, rows, vocab, logits2.stride(0),
-                ignore_index, grad_scale, int(write_grad), nv.dtype_code(logits2.dtype), nv.stream()), "cross_entropy")
+                ignore_index, grad_scale, int(write_grad), None if row_scale is None else nv.ptr(row_scale),
+                nv.dtype_code(logits2.dtype), nv.stream()), "cross_entropy")
     nv.count_launch()
     return loss_rows
 
@@ -101,12 +102,13 @@ class _LinearCEFn(torch.autograd.Function):
     scale when there is one) and multiplied by the (remaining) upstream factor in backward."""
 
     @staticmethod
-    def forward(ctx, x, w, targets, ignore_index, n_valid, chunk_tokens, w_main_grad, need_dx, need_dw, declared):
+    def forward(ctx, x, w, targets, ignore_index, n_valid, chunk_tokens, w_main_grad, need_dx, need_dw, declared,
+                row_scale=None):
         M, K = x.shape
         V = w.shape[0]
         ld = (V + 7) // 8 * 8  # padded leading dimension keeps every logits row 16-byte aligned
         pre = 1.0 if declared is None else float(declared)     # folded into the gradients formed here
-        inv = 1.0 / max(n_valid, 1)
+        inv = 1.0 if row_scale is not None else 1.0 / max(n_valid, 1)   # row_scale already holds the normalisation
         dx = torch.empty_like(x) if need_dx else None
         dw = None
         in_place = need_dw and w_main_grad is not None and declared is not None
@@ -120,8 +122,9 @@ class _LinearCEFn(torch.autograd.Function):
             e = min(M, s + chunk)
             lg = buf[: e - s, :V]
             gemm(x[s:e], w, out=lg)
-            rows = _ce_native(lg, t[s:e], inv * pre, need_dx or need_dw, ignore_index)
-            loss_sum += rows.sum()
+            rs = None if row_scale is None else row_scale[s:e]
+            rows = _ce_native(lg, t[s:e], inv * pre, need_dx or need_dw, ignore_index, rs)
+            loss_sum += rows.sum() if rs is None else torch.dot(rows, rs)
             if need_dx:
                 gemm(lg, w, b_mn=True, out=dx[s:e])
             if need_dw:
@@ -145,12 +148,24 @@ class _LinearCEFn(torch.autograd.Function):
                 gdw = (dw * f).to(ctx.w_dtype)
         # no ``_grad_ready`` call here: a tied head still receives the embedding's contribution at the very end of
         # backward, and DDP reduces buckets whose hooks never fired when backward finishes
-        return (gdx, gdw) + (None,) * 8
+        return (gdx, gdw) + (None,) * 9
+
+
+def micro_batch_row_scale(targets: torch.Tensor, micro_batches: int, ignore_index: int = -100) -> torch.Tensor:
+    """float[tokens]: 1 / (micro_batches * n_valid(m)) for the rows of micro-batch m, 0 for ignored rows — the weights
+    with which ``sum(loss_rows * scale)`` equals the mean over micro-batches of each micro-batch's mean loss (what
+    ``gradient_accumulation_steps`` separate passes with ``loss / steps`` produce). Computed on the device."""
+    valid = (targets.reshape(micro_batches, -1) != ignore_index).to(torch.float32)
+    n = valid.sum(1, keepdim=True).clamp_min_(1.0)
+    return (valid / (n * micro_batches)).reshape(-1)
 
 
 def linear_cross_entropy(x: torch.Tensor, w: torch.Tensor, targets: torch.Tensor, ignore_index: int = -100,
-                         n_valid: Optional[int] = None, chunk_tokens: int = 4096) -> torch.Tensor:
+                         n_valid: Optional[int] = None, chunk_tokens: int = 4096,
+                         row_scale: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Fused lm_head + cross-entropy. x: [tokens, K], w: [vocab, K], targets: [tokens].
+    ``row_scale`` (float[tokens], device) replaces the 1 / n_valid normalisation by per-row weights
+    (``micro_batch_row_scale``); with it no host read-back of the valid-token count happens.
 
     Under ``torch.no_grad()`` (evaluation) no gradient of any kind is formed. If ``w`` carries a ``main_grad`` fp32
     buffer (flat-arena parameters) the weight gradient ends up there and autograd sees none for ``w``: accumulated
@@ -158,11 +173,14 @@ def linear_cross_entropy(x: torch.Tensor, w: torch.Tensor, targets: torch.Tensor
     held in a temporary and added in backward times the gradient autograd delivers — correct for any
     ``(loss * c).backward()``."""
     if nv.use_native(x) and x.dtype in (torch.bfloat16, torch.float16):
-        if n_valid is None:
+        if n_valid is None and row_scale is None:
             n_valid = int((targets != ignore_index).sum().item())
         ge = torch.is_grad_enabled()
-        return _LinearCEFn.apply(x.contiguous(), w, targets, ignore_index, n_valid, chunk_tokens,
+        return _LinearCEFn.apply(x.contiguous(), w, targets, ignore_index, n_valid or 1, chunk_tokens,
                                  getattr(w, "main_grad", None), ge and x.requires_grad, ge and w.requires_grad,
-                                 _DECLARED_GRAD_SCALE if ge else None)
+                                 _DECLARED_GRAD_SCALE if ge else None, row_scale)
     logits = x.float() @ w.float().t()
+    if row_scale is not None:
+        rows = F.cross_entropy(logits, targets.reshape(-1), ignore_index=ignore_index, reduction="none")
+        return torch.dot(rows, row_scale.to(rows.dtype))
     return F.cross_entropy(logits, targets.reshape(-1), ignore_index=ignore_index)

@@ -128,6 +128,14 @@ def peer_gather(src: SymmBuffer, out: torch.Tensor, src_off_bytes: int, shard_by
     return out
 
 
+def peer_gather_ce(src: SymmBuffer, out: torch.Tensor, src_off_bytes: int, shard_bytes: int, skip: int = -1) -> torch.Tensor:
+    """``peer_gather`` on the copy engines: one ``cudaMemcpyAsync`` per owner on the current stream (no kernel)."""
+    vp, i32, i64 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong
+    fn = nv.proto("b200_peer_gather_ce", [vp, i64, vp, i64, i32, i32, vp])
+    nv.check(fn(ctypes.cast(src.c_ptrs(), vp), src_off_bytes, nv.ptr(out), shard_bytes, src.world, skip, nv.stream()), "peer_gather_ce")
+    return out
+
+
 def allreduce_(buf: SymmBuffer, flags: PeerFlags, offset: int, n: int, scale: float,
                lowp: Optional[SymmBuffer] = None, grid: int = 64) -> None:
     """In-place average (``scale`` = 1/world) of fp32 ``buf[offset : offset+n]`` across ranks — K-C1."""

@@ -71,16 +71,17 @@ class _ZeroStepArgs(ctypes.Structure):
 # stage-3 sharding of the frozen NF4 base
 # --------------------------------------------------------------------------------------------------
 class ShardedNF4:
-    """An NF4 matrix whose rows are partitioned across ranks; duck-types ``NF4Weight.dequantize``."""
+    """An NF4 matrix whose rows are partitioned across ranks; duck-types ``NF4Weight.dequantize``.
+    Codes and block scales of a shard live in ONE symmetric byte buffer (``wbuf``), grouped by decoder layer so a whole
+    layer's shard is one contiguous range per owner."""
 
-    def __init__(self, N, K, packed_buf: SymmBuffer, scale_buf: SymmBuffer, p_off: int, s_off: int, world: int,
-                 rank: int, group: int = 64):
+    def __init__(self, N, K, wbuf: SymmBuffer, p_off: int, s_off: int, world: int, rank: int, group: int = 64):
         self.N, self.K, self.group = N, K, group
         self.world, self.rank = world, rank
         self.rows = N // world
-        self._pbuf, self._sbuf, self._poff, self._soff = packed_buf, scale_buf, p_off, s_off
-        self.packed = packed_buf.local  # for .device
-        self.shards = [(packed_buf.ptrs[r] + p_off, scale_buf.ptrs[r] + s_off * 4, 0) for r in range(world)]
+        self._wbuf, self._poff, self._soff = wbuf, p_off, s_off          # byte offsets into wbuf
+        self.packed = wbuf.local  # for .device
+        self.shards = [(wbuf.ptrs[r] + p_off, wbuf.ptrs[r] + s_off, 0) for r in range(world)]
         self.prefetcher: Optional["ShardPrefetcher"] = None
         self.layer = -1
         self._stage_shards: List[list] = []
@@ -90,7 +91,7 @@ class ShardedNF4:
         if self.prefetcher is not None:
             # the layer's shards were pulled into a local staging buffer while the previous layer computed
             shards = self._stage_shards[self.prefetcher.acquire(self.layer)]
-        return w4_dequant(self._pbuf.local, self._sbuf.local, None, self.N, self.K, self.group, None, dtype, out,
+        return w4_dequant(self._wbuf.local, self._wbuf.local, None, self.N, self.K, self.group, None, dtype, out,
                           shards=shards, rows_per_shard=self.rows, transpose=transpose)
 
     def can_transpose(self) -> bool:
@@ -99,25 +100,28 @@ class ShardedNF4:
     def local_shard(self) -> Tuple[torch.Tensor, torch.Tensor]:
         nb = self.rows * self.K // 2
         ns = self.rows * self.K // self.group
-        return self._pbuf.local[self._poff:self._poff + nb], self._sbuf.local[self._soff:self._soff + ns]
+        return (self._wbuf.local[self._poff:self._poff + nb],
+                self._wbuf.local[self._soff:self._soff + 4 * ns].view(torch.float32))
 
 
 class ShardPrefetcher:
-    """ZeRO-3 parameter prefetch for the 4-bit base (the ``stage3_prefetch_bucket_size`` idea of
-    Fine-Tuning/ds_zero3_config.json, done per decoder layer): while layer L computes, one pull kernel on a side stream
-    copies layer L+1's (backward: L-1's) packed codes and scales out of the 8 owners' memory into one of two local
-    staging buffers, so the dequant kernels read HBM instead of stalling on NVLink latency. Measured at 8 GPUs the
-    in-kernel peer reads cost ~65 ms per step; a layer's shards are 21 MB per owner and take ~0.25 ms to pull, hidden
-    behind ~1.2 ms of GEMMs."""
+    """ZeRO-3 parameter prefetch for the 4-bit base (the ``stage3_prefetch_bucket_size`` / ``stage3_max_live_parameters``
+    idea of Fine-Tuning/ds_zero3_config.json, done per decoder layer: one layer ahead, two layers live). While layer L
+    computes, layer L+1's (backward: L-1's) shards — packed codes and scales, one contiguous range per owner — are
+    copied out of the owners' memory into one of two local staging buffers by the COPY ENGINES (one ``cudaMemcpyAsync``
+    per owner on a side stream), so the pull takes no SM away from the persistent GEMMs and the dequant kernels read
+    local HBM instead of stalling on NVLink latency. ``B200_PREFETCH_SM=1`` restores the SM pull kernel (the round-1
+    path: measured 29 ms of exposed time per step at 8 GPUs because it shares SMs and shared memory with the GEMMs).
 
-    def __init__(self, pbuf: SymmBuffer, sbuf: SymmBuffer, regions: Dict[int, Tuple[int, int, int, int]], world: int, device):
-        from .symm import peer_gather
-        self._gather = peer_gather
-        self.pbuf, self.sbuf, self.regions, self.world, self.rank = pbuf, sbuf, regions, world, pbuf.rank
-        pmax = max(r[1] - r[0] for r in regions.values())
-        smax = max(r[3] - r[2] for r in regions.values())
-        self.pstage = [torch.empty(world * pmax, dtype=torch.uint8, device=device) for _ in range(2)]
-        self.sstage = [torch.empty(world * smax, dtype=torch.float32, device=device) for _ in range(2)]
+    ``exposed_ms()``: time the consuming stream sat in the wait for a prefetch (CUDA event pairs around every wait)."""
+
+    def __init__(self, wbuf: SymmBuffer, regions: Dict[int, Tuple[int, int]], world: int, device):
+        from .symm import peer_gather, peer_gather_ce
+        self._gather = peer_gather if os.environ.get("B200_PREFETCH_SM", "0") == "1" else peer_gather_ce
+        self.wbuf, self.regions, self.world, self.rank = wbuf, regions, world, wbuf.rank
+        rmax = max(hi - lo for lo, hi in regions.values())
+        self.rmax = rmax
+        self.stage = [torch.empty(world * rmax, dtype=torch.uint8, device=device) for _ in range(2)]
         self.resident: List[Optional[int]] = [None, None]
         self.ready = [torch.cuda.Event(), torch.cuda.Event()]
         self.free = [torch.cuda.Event(), torch.cuda.Event()]
@@ -125,15 +129,16 @@ class ShardPrefetcher:
         self.last: Optional[int] = None
         self.direction = 1
         self.issued = 0
+        self.measure = True
+        self._waits: List[tuple] = []
 
     def _issue(self, layer: int, b: int) -> None:
-        p_lo, p_hi, s_lo, s_hi = self.regions[layer]
+        lo, hi = self.regions[layer]
         cur = torch.cuda.current_stream()
         self.free[b].record(cur)               # every dequant that read this buffer is already queued on `cur`
         self.stream.wait_event(self.free[b])
         with torch.cuda.stream(self.stream):
-            self._gather(self.pbuf, self.pstage[b][: self.world * (p_hi - p_lo)], p_lo, p_hi - p_lo, self.rank)
-            self._gather(self.sbuf, self.sstage[b][: self.world * (s_hi - s_lo)], s_lo * 4, (s_hi - s_lo) * 4, self.rank)
+            self._gather(self.wbuf, self.stage[b][: self.world * (hi - lo)], lo, hi - lo, self.rank)
             self.ready[b].record(self.stream)
         self.resident[b] = layer
         self.issued += 1
@@ -144,7 +149,17 @@ class ShardPrefetcher:
         else:
             b = 1 - self.resident.index(self.last) if self.last in self.resident else 0
             self._issue(layer, b)
-        torch.cuda.current_stream().wait_event(self.ready[b])
+        cur = torch.cuda.current_stream()
+        if self.measure and layer != self.last:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(cur)
+            cur.wait_event(self.ready[b])
+            e1.record(cur)
+            self._waits.append((e0, e1))
+            if len(self._waits) > 4096:
+                del self._waits[:2048]
+        else:
+            cur.wait_event(self.ready[b])
         if self.last is not None and layer != self.last:
             self.direction = 1 if layer > self.last else -1
         nxt = layer + self.direction
@@ -153,53 +168,73 @@ class ShardPrefetcher:
         self.last = layer
         return b
 
+    def reset_exposed(self) -> None:
+        self._waits.clear()
+
+    def exposed_ms(self) -> float:
+        """Sum over the recorded waits (since ``reset_exposed``) of the time between reaching the wait and passing it."""
+        tot = 0.0
+        for e0, e1 in self._waits:
+            if e1.query():
+                tot += e0.elapsed_time(e1)
+        return tot
+
 
 def shard_nf4_base(model: nn.Module, world: int, rank: int, device) -> Dict[str, int]:
     """Replace every ``NF4Weight`` of ``model`` by a ``ShardedNF4`` holding 1/world of the rows locally."""
     lins = [(n, m) for n, m in model.named_modules() if isinstance(m, FusedLinear) and isinstance(m.nf4, NF4Weight)]
-    p_total = s_total = 0
-    plan = []
-    for name, lin in lins:
+    if not lins:
+        return {"packed_bytes": 0, "scale_floats": 0}
+    al = lambda x: (x + 255) // 256 * 256
+    # group by decoder layer (layer_uid = 4 * layer + slot); linears without a layer id get a group of their own
+    groups: Dict[int, list] = {}
+    for i, (name, lin) in enumerate(lins):
         q = lin.nf4
         if q.N % world:
             raise ValueError(f"{name}: {q.N} rows do not divide over {world} ranks")
-        rows = q.N // world
-        pb, sb = rows * q.K // 2, rows * q.K // q.group
-        plan.append((lin, p_total, s_total, pb, sb, rows))
-        p_total += (pb + 255) // 256 * 256
-        s_total += (sb + 63) // 64 * 64
-    if not plan:
-        return {"packed_bytes": 0, "scale_floats": 0}
-    pbuf = SymmBuffer(p_total, torch.uint8, device, zero=False)
-    sbuf = SymmBuffer(s_total, torch.float32, device, zero=False)
+        L = lin.layer_uid // 4 if hasattr(lin, "layer_uid") and len(lins) > 1 else -(i + 1)
+        groups.setdefault(L, []).append(lin)
+    total = 0
+    plan = []                                   # (lin, p_off, s_off, packed bytes, scale bytes, rows)
+    regions: Dict[int, Tuple[int, int]] = {}
+    p_bytes = s_floats = 0
+    for L, members in groups.items():
+        lo = total
+        offs = []
+        for lin in members:                     # codes of every linear of the layer, then their scales
+            q = lin.nf4
+            rows = q.N // world
+            offs.append([lin, total, 0, rows * q.K // 2, rows * q.K // q.group * 4, rows])
+            total += al(offs[-1][3])
+        for o in offs:
+            o[2] = total
+            total += al(o[4])
+            p_bytes += o[3]
+            s_floats += o[4] // 4
+        plan += [tuple(o) for o in offs]
+        regions[L] = (lo, total)
+    wbuf = SymmBuffer(total, torch.uint8, device, zero=False)
     for lin, po, so, pb, sb, rows in plan:
         q = lin.nf4
-        pbuf.local[po:po + pb].copy_(q.packed.view(q.N, q.K // 2)[rank * rows:(rank + 1) * rows].reshape(-1))
-        sbuf.local[so:so + sb].copy_(q.scales().view(q.N, q.K // q.group)[rank * rows:(rank + 1) * rows].reshape(-1))
-        lin.nf4 = ShardedNF4(q.N, q.K, pbuf, sbuf, po, so, world, rank, q.group)
-    # ---- one-layer-ahead prefetch: group the linears by decoder layer (layer_uid = 4 * layer + slot) ----
+        wbuf.local[po:po + pb].copy_(q.packed.view(q.N, q.K // 2)[rank * rows:(rank + 1) * rows].reshape(-1))
+        wbuf.local[so:so + sb].view(torch.float32).copy_(
+            q.scales().view(q.N, q.K // q.group)[rank * rows:(rank + 1) * rows].reshape(-1))
+        lin.nf4 = ShardedNF4(q.N, q.K, wbuf, po, so, world, rank, q.group)
+    # ---- one-layer-ahead prefetch on the copy engines (default: on for every world size > 1) ----
     info_pf = 0
-    # default: on from 4 ranks (at 2 ranks half of every read is local and the in-kernel peer reads measured faster)
-    pf_env = os.environ.get("B200_ZERO_PREFETCH", "auto")
-    pf_on = pf_env == "1" or (pf_env == "auto" and world >= 4)
-    if pf_on and all(hasattr(pl[0], "layer_uid") for pl in plan):
-        regions: Dict[int, List[int]] = {}
+    pf_on = os.environ.get("B200_ZERO_PREFETCH", "1") != "0"
+    if pf_on and len(regions) > 1:
+        pf = ShardPrefetcher(wbuf, regions, world, device)
+        layer_of = {id(lin): L for L, members in groups.items() for lin in members}
         for lin, po, so, pb, sb, rows in plan:
-            L = lin.layer_uid // 4
-            r = regions.setdefault(L, [po, po, so, so])
-            r[0], r[2] = min(r[0], po), min(r[2], so)
-            r[1] = max(r[1], (po + pb + 255) // 256 * 256)
-            r[3] = max(r[3], (so + sb + 63) // 64 * 64)
-        pf = ShardPrefetcher(pbuf, sbuf, {k: tuple(v) for k, v in regions.items()}, world, device)
-        for lin, po, so, pb, sb, rows in plan:
-            L = lin.layer_uid // 4
-            p_lo, p_hi, s_lo, s_hi = pf.regions[L]
+            L = layer_of[id(lin)]
+            lo, hi = regions[L]
             q = lin.nf4
             q.prefetcher, q.layer = pf, L
             # remote shards come from the staging buffer, the local one is read where it lives
             q._stage_shards = [[q.shards[r] if r == rank else
-                                (pf.pstage[b].data_ptr() + r * (p_hi - p_lo) + (po - p_lo),
-                                 pf.sstage[b].data_ptr() + (r * (s_hi - s_lo) + (so - s_lo)) * 4, 0) for r in range(world)]
+                                (pf.stage[b].data_ptr() + r * (hi - lo) + (po - lo),
+                                 pf.stage[b].data_ptr() + r * (hi - lo) + (so - lo), 0) for r in range(world)]
                                for b in range(2)]
         model._shard_prefetcher = pf
         info_pf = 1
@@ -207,7 +242,7 @@ def shard_nf4_base(model: nn.Module, world: int, rank: int, device) -> Dict[str,
     if dist.is_initialized():
         dist.barrier()
     torch.cuda.empty_cache()
-    return {"packed_bytes": p_total, "scale_floats": s_total, "prefetch": info_pf}
+    return {"packed_bytes": p_bytes, "scale_floats": s_floats, "prefetch": info_pf, "buffer_bytes": total}
 
 
 # --------------------------------------------------------------------------------------------------
@@ -447,6 +482,48 @@ class ZeroEngine(nn.Module):
         self.backward(loss)
         return loss.detach()
 
+    def supports_fused_accumulation(self) -> bool:
+        import inspect
+        try:
+            return "micro_batches" in inspect.signature(self.module.forward).parameters
+        except (TypeError, ValueError):
+            return False
+
+    def train_batch(self, input_ids, labels=None, **kw) -> torch.Tensor:
+        """All ``gradient_accumulation_steps`` micro-batches of one optimizer step in ONE layer-major pass (the name is
+        DeepSpeed's ``PipelineEngine.train_batch``, which also consumes a whole step's micro-batches).
+
+        ``input_ids`` / ``labels``: a list of G micro-batches [B, S] (or already stacked [G * B, S]). Every layer
+        processes the G * B sequences together, so each frozen 4-bit weight is gathered from its owners and expanded
+        ONCE per direction per optimizer step instead of G times — the ZeRO-3 parameter traffic and the dequantisation
+        work both drop by G — and the GEMMs see G times more rows. The loss is the mean over micro-batches of each
+        one's mean token loss and the gradients equal those of G separate ``backward(loss / G)`` calls (attention is
+        per sequence, the normalisation per micro-batch; LoRA dropout draws one mask per element either way).
+        Falls back to G sequential micro-steps for modules without ``micro_batches`` support. Call ``step()`` after."""
+        G = self.ga
+        ids_l = list(input_ids) if isinstance(input_ids, (list, tuple)) else list(input_ids.chunk(G, 0))
+        lab_l = ids_l if labels is None else (list(labels) if isinstance(labels, (list, tuple)) else list(labels.chunk(G, 0)))
+        if len(ids_l) != G:
+            raise ValueError(f"train_batch needs {G} micro-batches (gradient_accumulation_steps), got {len(ids_l)}")
+        if G == 1 or not self.supports_fused_accumulation() or len({tuple(t.shape) for t in ids_l}) != 1:
+            loss = None
+            for a, b in zip(ids_l, lab_l):
+                l = self.train_micro_batch(a, b, **kw)
+                loss = l if loss is None else loss + l
+            return loss / G
+        ids = torch.cat(ids_l, 0)
+        lab = ids if labels is None else torch.cat(lab_l, 0)
+        ew.set_step(self.global_steps, 0)
+        from ..ops.loss import grad_scale_context
+        s = self.scaler.scale if self.scaler is not None else 1.0        # 1 / G is inside the per-row normalisation
+        with self._phase("forward"), grad_scale_context(s):
+            out = self.module(ids, labels=lab, micro_batches=G, **kw)
+        loss = out["loss"] if isinstance(out, dict) else out
+        with self._phase("backward"):
+            (loss * s if s != 1.0 else loss).backward()
+        self.micro_steps += G
+        return loss.detach()
+
     def is_gradient_accumulation_boundary(self) -> bool:
         return self.micro_steps % self.ga == 0 and self.micro_steps > 0
 
@@ -522,6 +599,18 @@ class ZeroEngine(nn.Module):
         a.grid = grid
         a.grid_ctr = F.grid_ctr.data_ptr()
         a.grid_target_base = F.take_grid_target(grid, 2)
+        if getattr(self, "time_skew", False):
+            # measurement mode: a device-side barrier across ranks first, so the K-C2 timer below holds kernel time
+            # only and the time spent waiting for the slowest rank shows up separately ("step_skew")
+            from .symm import peer_barrier
+            b0, b1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            b0.record()
+            peer_barrier(self.flags, channel=6)
+            b1.record()
+            sk = self._timers.setdefault("step_skew", [])
+            sk.append((b0, b1))
+            if len(sk) > 256:
+                del sk[:128]
         ev0 = torch.cuda.Event(enable_timing=True)
         ev1 = torch.cuda.Event(enable_timing=True)
         ev0.record()
@@ -597,7 +686,36 @@ class ZeroEngine(nn.Module):
                 out[k + "_ms"] = round(sum(ms) / len(ms), 4)
         if self.base_shard_info:
             out["nf4_shard_bytes_per_rank"] = self.base_shard_info["packed_bytes"] + 4 * self.base_shard_info["scale_floats"]
+        pf = getattr(self.module, "_shard_prefetcher", None)
+        if pf is not None:
+            out["prefetch"] = "copy-engine" if pf._gather.__name__.endswith("_ce") else "sm-kernel"
+            out["prefetch_issued"] = pf.issued
         return out
+
+    def reset_comm_timers(self) -> None:
+        """Start a fresh measurement window for ``exposed_comm_ms`` / ``zero_step_ms``."""
+        self._timers.pop("zero_step", None)
+        self._timers.pop("step_skew", None)
+        pf = getattr(self.module, "_shard_prefetcher", None)
+        if pf is not None:
+            pf.reset_exposed()
+        self._window_steps = self.global_steps
+
+    def exposed_comm_ms(self) -> Optional[float]:
+        """Exposed communication per optimizer step since ``reset_comm_timers`` (ms, this rank): the time the stream that
+        consumes the prefetched parameter shards sat waiting for them, plus the fused reduce-scatter / AdamW / all-gather
+        launch (K-C2), whose whole duration is serial with compute. ``None`` on one GPU."""
+        if self.world == 1:
+            return None
+        torch.cuda.synchronize()
+        steps = max(1, self.global_steps - getattr(self, "_window_steps", 0))
+        tot = 0.0
+        pf = getattr(self.module, "_shard_prefetcher", None)
+        if pf is not None:
+            tot += pf.exposed_ms()
+        for a, b in self._timers.get("zero_step", []):
+            tot += a.elapsed_time(b)
+        return tot / steps
 
     # ------------------------------------------------------------------ checkpoints
     def consolidated_state_dict(self) -> Dict[str, torch.Tensor]:

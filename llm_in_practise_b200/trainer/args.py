@@ -16,6 +16,7 @@ class TrainingArguments:
     per_device_train_batch_size: int = 8
     per_device_eval_batch_size: int = 8
     gradient_accumulation_steps: int = 1
+    fused_accumulation: bool = True      # run the micro-batches of a step as one layer-major pass (ZeroEngine.train_batch)
     num_train_epochs: float = 3.0
     max_steps: int = -1
     learning_rate: float = 5e-5

@@ -269,14 +269,36 @@ class Trainer:
         for epoch in range(start_step // steps_per_epoch, epochs):
             if hasattr(loader.sampler, "set_epoch"):
                 loader.sampler.set_epoch(epoch)
+            pending: List[Dict[str, Any]] = []
+            fuse = (self.engine is not None and ga > 1 and getattr(a, "fused_accumulation", True)
+                    and self.engine.supports_fused_accumulation())
             for i, batch in enumerate(loader):
                 if i // ga >= steps_per_epoch:
                     break
-                run_loss += self.training_step(batch)
-                run_n += 1
                 samples += a.per_device_train_batch_size * self.info.world_size
-                if (i + 1) % ga:
-                    continue
+                if fuse:
+                    # the micro-batches of one optimizer step go through the model as ONE layer-major pass
+                    # (ZeroEngine.train_batch): same gradients, frozen 4-bit weights gathered and expanded once
+                    pending.append(self._filter(self._to_device(batch)))
+                    if (i + 1) % ga:
+                        continue
+                    shapes = {tuple(b["input_ids"].shape) for b in pending}
+                    if len(shapes) == 1 and all(set(b) <= {"input_ids", "labels", "attention_mask"} for b in pending):
+                        run_loss += self.engine.train_batch([b["input_ids"] for b in pending],
+                                                            [b.get("labels", b["input_ids"]) for b in pending]) * ga
+                    else:
+                        for b in pending:
+                            out = self.engine(**b)
+                            loss = _get_loss(out)
+                            self.engine.backward(loss)
+                            run_loss += loss.detach()
+                    run_n += ga
+                    pending = []
+                else:
+                    run_loss += self.training_step(batch)
+                    run_n += 1
+                    if (i + 1) % ga:
+                        continue
                 self._optimizer_step()
                 self.state.global_step += 1
                 self.state.epoch = self.state.global_step / steps_per_epoch

@@ -24,6 +24,14 @@ shapes = [("qkv fwd", 1024, 7168, 5120, False), ("o fwd", 1024, 5120, 5120, Fals
           ("gate_up dgrad", 1024, 5120, 34816, True), ("down dgrad", 1024, 17408, 5120, True),
           ("lm_head dgrad", 1024, 5120, 151936, True), ("qkv dgrad", 1024, 5120, 7168, True),
           ("8k x 8k x 8k", 8192, 8192, 8192, False), ("4k tok gate_up 8B", 8192, 24576, 4096, False)]
+# the layer-major schedule runs both micro-batches of a step through a layer together: M = 2048; with an NF4 base the
+# dgrad reads W^T K-major (expanded transposed), so those rows are b_mn = False
+shapes += [("qkv fwd M2048", 2048, 7168, 5120, False), ("o fwd M2048", 2048, 5120, 5120, False),
+           ("gate_up fwd M2048", 2048, 34816, 5120, False), ("down fwd M2048", 2048, 5120, 17408, False),
+           ("gate_up dgrad(K-major) M2048", 2048, 5120, 34816, False), ("down dgrad(K-major) M2048", 2048, 17408, 5120, False),
+           ("lm_head fwd M2048", 2048, 151936, 5120, False), ("lm_head dgrad M2048", 2048, 5120, 151936, True)]
+if len(sys.argv) > 1:
+    shapes = [s_ for s_ in shapes if any(k in s_[0] for k in sys.argv[1:])]
 rows = []
 for name, M, N, K, bmn in shapes:
     a = torch.randn(M, K, device=dev, dtype=torch.bfloat16)

@@ -141,6 +141,51 @@ def test_linear_cross_entropy():
     assert rel(x.grad, x32.grad) < 3e-2 and rel(w.grad, w32.grad) < 3e-2
 
 
+def test_linear_cross_entropy_main_grad_scaling_and_eval():
+    """A head weight with a flat-arena ``main_grad``: evaluation under no_grad leaves it untouched, a declared upstream
+    scale (engines: 1 / grad_accum) is folded into what forward accumulates, and an undeclared ``(loss * c).backward()``
+    still lands ``c * dW`` there (gradient accumulation with ga = 2, an eval pass in between, vs the torch reference)."""
+    M, K, V = 256, 128, 1000
+    w = (torch.randn(V, K, device=DEV) / 8).bfloat16().requires_grad_()
+    w.main_grad = torch.zeros(V, K, device=DEV, dtype=torch.float32)
+    xs = [torch.randn(M, K, device=DEV, dtype=torch.bfloat16) for _ in range(2)]
+    ts = [torch.randint(0, V, (M,), device=DEV) for _ in range(2)]
+
+    def ref_grads(c):
+        w32 = w.detach().float().requires_grad_()
+        gx = []
+        for x, t in zip(xs, ts):
+            x32 = x.float().requires_grad_()
+            (F.cross_entropy(x32 @ w32.t(), t) * c).backward()
+            gx.append(x32.grad)
+        return w32.grad, gx
+
+    # (a) declared scale, as the ZeRO engine / pretrain loop do, with an evaluation pass between the micro-steps
+    want_w, want_x = ref_grads(0.5)
+    got_x = []
+    for i, (x, t) in enumerate(zip(xs, ts)):
+        xi = x.clone().requires_grad_()
+        with L.grad_scale_context(0.5):
+            loss = L.linear_cross_entropy(xi, w, t)
+        (loss * 0.5).backward()
+        got_x.append(xi.grad)
+        if i == 0:
+            before = w.main_grad.clone()
+            with torch.no_grad():
+                L.linear_cross_entropy(xs[1], w, ts[1])
+            assert torch.equal(w.main_grad, before), "an eval pass must not touch the gradient arena"
+    assert w.grad is None
+    assert rel(w.main_grad, want_w) < 2e-2
+    for g, r in zip(got_x, want_x):
+        assert rel(g, r) < 2e-2
+    # (b) nothing declared: the factor autograd delivers is applied in backward
+    w.main_grad.zero_()
+    want_w, _ = ref_grads(0.25)
+    for x, t in zip(xs, ts):
+        (L.linear_cross_entropy(x.clone().requires_grad_(), w, t) * 0.25).backward()
+    assert rel(w.main_grad, want_w) < 2e-2
+
+
 def test_nf4_roundtrip_and_double_quant():
     w = torch.randn(512, 1024, device=DEV, dtype=torch.bfloat16)
     packed, absmax = W4.nf4_quantize(w)

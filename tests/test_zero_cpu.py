@@ -70,3 +70,38 @@ def test_zero_stages_match_single_process(stage, tmp_path):
     assert (tmp_path / "ckpt" / "t" / "mp_rank_00_model_states.pt").exists()
     assert (tmp_path / "ckpt" / "t" / "zero_pp_rank_1_mp_rank_00_optim_states.pt").exists()
     assert (tmp_path / "ckpt" / "latest").read_text() == "t"
+
+
+def test_train_batch_equals_sequential_micro_batches():
+    """One layer-major pass over the G micro-batches of a step gives the gradients of G ``backward(loss / G)`` calls,
+    also when the micro-batches have different numbers of non-ignored targets."""
+    import copy
+    from llm_in_practise_b200.models.qwen3 import QWEN3_PRESETS, Qwen3ForCausalLM
+    from llm_in_practise_b200.parallel.zero import initialize
+    from llm_in_practise_b200.peft import LoraConfig
+
+    def engine():
+        torch.manual_seed(0)
+        m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32)
+        return initialize(model=m, lora_config=LoraConfig(r=4, lora_alpha=8, lora_dropout=0.0, target_modules=["q_proj", "v_proj"]),
+                          config={"zero_optimization": {"stage": 3}, "gradient_accumulation_steps": 2, "gradient_clipping": 0.0,
+                                  "train_micro_batch_size_per_gpu": 2, "optimizer": {"type": "AdamW", "params": {"lr": 1e-2}}})
+    g = torch.Generator().manual_seed(1)
+    ids = [torch.randint(0, 1024, (2, 24), generator=g) for _ in range(2)]
+    labels = [t.clone() for t in ids]
+    labels[1][:, :10] = -100                      # the second micro-batch has fewer valid targets
+    a, b = engine(), engine()
+    # B needs a non-zero adapter B matrix or every gradient of A is zero
+    for e in (a, b):
+        with torch.no_grad():
+            e.arena.data.copy_(torch.randn(e.arena.numel, generator=torch.Generator().manual_seed(5)) * 0.05)
+        for mod in e.module.modules():
+            if hasattr(mod, "invalidate_adapter_buffers"):
+                mod.invalidate_adapter_buffers()
+    la = [a.train_micro_batch(x, y) for x, y in zip(ids, labels)]
+    lb = b.train_batch(ids, labels)
+    assert b.supports_fused_accumulation() and b.micro_steps == 2 and b.is_gradient_accumulation_boundary()
+    assert abs(float(lb) - float(sum(la) / 2)) < 1e-5
+    assert torch.allclose(a.arena.grad, b.arena.grad, rtol=1e-4, atol=1e-6), float((a.arena.grad - b.arena.grad).abs().max())
+    a.step(); b.step()
+    assert torch.allclose(a.arena.data, b.arena.data, rtol=1e-4, atol=1e-6)
