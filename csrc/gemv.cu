@@ -46,6 +46,13 @@ __device__ __forceinline__ uint32_t fma2(uint32_t a, uint32_t b, uint32_t c) {
   return d;
 }
 
+// weights are read exactly once: bypass L1 allocation
+__device__ __forceinline__ uint4 ld_nc_v4(const void* ptr) {
+  uint4 r;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(ptr));
+  return r;
+}
+
 struct GemvParams {
   const uint16_t* x;      // [M, K] 16-bit activations
   const void* w;          // dense: uint16 [N, w_rs]; 4-bit: packed uint8 [N, K / 2]
@@ -97,15 +104,47 @@ gemv_mma_kernel(const GemvParams p) {
     for (int tg = 0; tg < TG; ++tg)
 #pragma unroll
       for (int i = 0; i < 4; ++i) c[tg][i] = 0.f;
-    for (int ch = warp; ch < nchunks; ch += 8) {
+    // The warp's chunks are taken U at a time: all packed weights (and scales) of a batch are requested before any of
+    // them is used, so a batch costs ONE trip to DRAM instead of U dependent ones. With K = 4096 a warp has 4 chunks —
+    // one batch — and a tile is a single round trip; the loop-per-chunk version of this kernel ran at 14 % of the HBM
+    // bandwidth because every chunk waited for the previous one's data (profiles/gemv_linear_ncu.md).
+    constexpr int U = 4;
+    for (int ch0 = warp; ch0 < nchunks; ch0 += 8 * U) {
+      uint4 wqa[U], wqb[U];        // W4: 16 packed bytes of rows g / g+8 per chunk; dense: unused
+      float sca[U], scb[U], zza[U], zzb[U];
+      if (W4) {
+        const uint8_t* pk = reinterpret_cast<const uint8_t*>(p.w);
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int ch = ch0 + 8 * u;
+          if (ch < nchunks) {
+            const int k = ch * 128 + t * 32;
+            wqa[u] = ld_nc_v4(pk + rA * (K / 2) + k / 2);
+            wqb[u] = ld_nc_v4(pk + rB * (K / 2) + k / 2);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int ch = ch0 + 8 * u;
+          if (ch < nchunks) {
+            const int k = ch * 128 + t * 32;
+            sca[u] = __ldg(p.scale + rA * gpr + k / p.group);
+            scb[u] = __ldg(p.scale + rB * gpr + k / p.group);
+            zza[u] = p.zs ? __ldg(p.zs + rA * gpr + k / p.group) : 0.f;
+            zzb[u] = p.zs ? __ldg(p.zs + rB * gpr + k / p.group) : 0.f;
+          }
+        }
+      }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int ch = ch0 + 8 * u;
+      if (ch >= nchunks) break;
       const int k = ch * 128 + t * 32;
       uint32_t aA[16], aB[16];   // rows g / g+8: 32 weights each as 16-bit pairs
       if (W4) {
-        const uint8_t* pk = reinterpret_cast<const uint8_t*>(p.w);
-        const uint4 wa = __ldg(reinterpret_cast<const uint4*>(pk + rA * (K / 2) + k / 2));
-        const uint4 wb = __ldg(reinterpret_cast<const uint4*>(pk + rB * (K / 2) + k / 2));
-        const float sa = __ldg(p.scale + rA * gpr + k / p.group), sb = __ldg(p.scale + rB * gpr + k / p.group);
-        const float za = p.zs ? __ldg(p.zs + rA * gpr + k / p.group) : 0.f, zb = p.zs ? __ldg(p.zs + rB * gpr + k / p.group) : 0.f;
+        const uint4 wa = wqa[u], wb = wqb[u];
+        const float sa = sca[u], sb = scb[u];
+        const float za = zza[u], zb = zzb[u];
         const uint32_t sa2 = pack2<BF16>(sa, sa), sb2 = pack2<BF16>(sb, sb), za2 = pack2<BF16>(-za, -za), zb2 = pack2<BF16>(-zb, -zb);
         const uint32_t wA[4] = {wa.x, wa.y, wa.z, wa.w}, wB[4] = {wb.x, wb.y, wb.z, wb.w};
         if (LIN) {
@@ -142,7 +181,7 @@ gemv_mma_kernel(const GemvParams p) {
         const uint4* pb = reinterpret_cast<const uint4*>(wd + rB * p.w_rs + k);
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const uint4 va = __ldg(pa + i), vb = __ldg(pb + i);
+          const uint4 va = ld_nc_v4(pa + i), vb = ld_nc_v4(pb + i);
           aA[4 * i] = va.x; aA[4 * i + 1] = va.y; aA[4 * i + 2] = va.z; aA[4 * i + 3] = va.w;
           aB[4 * i] = vb.x; aB[4 * i + 1] = vb.y; aB[4 * i + 2] = vb.z; aB[4 * i + 3] = vb.w;
         }
@@ -176,6 +215,7 @@ gemv_mma_kernel(const GemvParams p) {
         for (int j = 0; j < 8; ++j)
           mma16816<BF16>(c[tg], aA[2 * j], aB[2 * j], aA[2 * j + 1], aB[2 * j + 1], xw[2 * j], xw[2 * j + 1]);
       }
+    }
     }
     // c0: (row g, token 2t), c1: (row g, token 2t+1), c2: (row g+8, token 2t), c3: (row g+8, token 2t+1) of the group
 #pragma unroll

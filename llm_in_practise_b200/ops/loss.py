@@ -37,7 +37,7 @@ def _ce_native(logits2, targets, grad_scale, write_grad, ignore_index, row_scale
 
 class _CrossEntropyFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, logits, targets, ignore_index, n_valid):
+    def forward(ctx, logits, targets, ignore_index, row_scale):
         vocab = logits.shape[-1]
         l2 = logits.reshape(-1, vocab)
         t = targets.reshape(-1).contiguous()
@@ -45,12 +45,11 @@ class _CrossEntropyFn(torch.autograd.Function):
         work = l2.clone() if need_grad else l2  # the kernel overwrites its input with the gradient
         if not work.is_contiguous():
             work = work.contiguous()
-        inv = 1.0 / max(n_valid, 1)
-        loss_rows = _ce_native(work, t, inv, need_grad, ignore_index)
+        loss_rows = _ce_native(work, t, 1.0, need_grad, ignore_index, row_scale)
         if need_grad:
             ctx.save_for_backward(work)
         ctx.shape = logits.shape
-        return loss_rows.sum() * inv
+        return torch.dot(loss_rows, row_scale)
 
     @staticmethod
     def backward(ctx, g):
@@ -58,16 +57,23 @@ class _CrossEntropyFn(torch.autograd.Function):
         return (dlogits * g.to(dlogits.dtype)).view(ctx.shape), None, None, None
 
 
+def _row_scale(targets: torch.Tensor, ignore_index: int, n_valid: Optional[int]) -> torch.Tensor:
+    """Per-row weights of the mean over non-ignored rows, formed on the device: without ``n_valid`` the count never
+    travels to the host, so the loss does not stall the launch queue (small models are launch-bound)."""
+    valid = (targets.reshape(-1) != ignore_index).to(torch.float32)
+    if n_valid is not None:
+        return valid * (1.0 / max(n_valid, 1))
+    return valid / valid.sum().clamp_min_(1.0)
+
+
 def cross_entropy(logits: torch.Tensor, targets: torch.Tensor, ignore_index: int = -100,
                   n_valid: Optional[int] = None) -> torch.Tensor:
-    """Mean cross-entropy over rows whose target != ignore_index. ``n_valid`` (the number of such
-    rows) can be passed to avoid a device->host sync; it is computed otherwise."""
+    """Mean cross-entropy over rows whose target != ignore_index (nn.CrossEntropyLoss semantics). The normalisation is
+    computed on the device; ``n_valid`` (the number of such rows) may be passed when the caller knows it."""
     vocab = logits.shape[-1]
     es = 4 if logits.dtype == torch.float32 else 2
     if nv.use_native(logits) and (vocab * es) % 16 == 0:
-        if n_valid is None:
-            n_valid = int((targets != ignore_index).sum().item())
-        return _CrossEntropyFn.apply(logits, targets, ignore_index, n_valid)
+        return _CrossEntropyFn.apply(logits, targets, ignore_index, _row_scale(targets, ignore_index, n_valid))
     return F.cross_entropy(logits.reshape(-1, vocab).float(), targets.reshape(-1), ignore_index=ignore_index)
 
 
@@ -173,8 +179,8 @@ def linear_cross_entropy(x: torch.Tensor, w: torch.Tensor, targets: torch.Tensor
     held in a temporary and added in backward times the gradient autograd delivers — correct for any
     ``(loss * c).backward()``."""
     if nv.use_native(x) and x.dtype in (torch.bfloat16, torch.float16):
-        if n_valid is None and row_scale is None:
-            n_valid = int((targets != ignore_index).sum().item())
+        if row_scale is None:
+            row_scale = _row_scale(targets, ignore_index, n_valid)      # no host read-back of the valid count
         ge = torch.is_grad_enabled()
         return _LinearCEFn.apply(x.contiguous(), w, targets, ignore_index, n_valid or 1, chunk_tokens,
                                  getattr(w, "main_grad", None), ge and x.requires_grad, ge and w.requires_grad,
