@@ -410,6 +410,99 @@ peer_gather_kernel(PeerPtrs src, long long src_off_bytes, uint4* __restrict__ ou
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// K-C2 (FSDP / ZeRO-2 flavour): gradient reduce-scatter of one flat unit over peer memory, with the cast to the wire
+// dtype (MixedPrecision.reduce_dtype: bf16 halves the NVLink bytes) and the 1/world scale fused in.
+//   step 0  peers have finished reading the half of the staging buffer this call is about to overwrite (the call two
+//           epochs ago used it): wait on the "read done" channel
+//   step 1  stage: wire[half][i] = cast(grad[i] * scale)                                    (local HBM)
+//   step 2  everyone's staging is visible: signal / wait on the "staged" channel
+//   step 3  out[j] (+)= sum_r wire_r[half][rank * shard_len + j]                             (NVLink reads)
+//   step 4  publish "read done" for this epoch (nobody waits for it here)
+// The two halves make consecutive calls independent: a fast rank may stage unit k+1 while a slow one still reads
+// unit k. Replaces FSDP's reduce_scatter_tensor (fsdp_gpt_wikitext2.py:304-312 runs it inside the wrapper) and the
+// reduce-scatter of DeepSpeed ZeRO-2/3 (reduce_scatter: true, overlap_comm: true; DeepSpeed-GPTLike-ZeRO-2/ds_config.json:4-12).
+// ---------------------------------------------------------------------------------------------
+template <bool WIRE_BF16>
+__global__ void __launch_bounds__(kCommThreads)
+reduce_scatter_kernel(const float* __restrict__ grad, PeerPtrs wire, PeerPtrs flags, float* __restrict__ out, long long n,
+                      long long half_elems, int world, int rank, uint32_t epoch, float scale, int accumulate,
+                      unsigned int* grid_ctr, unsigned int grid_target0) {
+  const int W = world, R = rank;
+  const int half = (int)(epoch & 1u);
+  if (epoch > 2) wait_all(flags, 1, W, R, epoch - 2);
+  const long long tid = (long long)blockIdx.x * blockDim.x + threadIdx.x, nthreads = (long long)gridDim.x * blockDim.x;
+  const long long n4 = n / 4;
+  if (WIRE_BF16) {
+    uint2* dst = reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(wire.p[R]) + half * half_elems);
+    for (long long i = tid; i < n4; i += nthreads) {
+      const float4 g = reinterpret_cast<const float4*>(grad)[i];
+      dst[i] = make_uint2(pack_bf16x2(g.x * scale, g.y * scale), pack_bf16x2(g.z * scale, g.w * scale));
+    }
+  } else {
+    float4* dst = reinterpret_cast<float4*>(reinterpret_cast<float*>(wire.p[R]) + half * half_elems);
+    for (long long i = tid; i < n4; i += nthreads) {
+      float4 g = reinterpret_cast<const float4*>(grad)[i];
+      g.x *= scale; g.y *= scale; g.z *= scale; g.w *= scale;
+      dst[i] = g;
+    }
+  }
+  __threadfence_system();
+  grid_barrier(grid_ctr, grid_target0);
+  if (blockIdx.x == 0) signal_all(flags, 0, W, R, epoch);
+  wait_all(flags, 0, W, R, epoch);
+  const long long shard = n / W, s4 = shard / 4, base = shard * R;
+  constexpr int U = 2;
+  for (long long i0 = tid; i0 < s4; i0 += nthreads * U) {
+    float4 acc[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (WIRE_BF16) {
+      uint2 v[U][kMaxRanks];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < W && i0 + u * nthreads < s4)
+            v[u][r] = reinterpret_cast<const uint2*>(reinterpret_cast<const __nv_bfloat16*>(wire.p[r]) + half * half_elems + base)[i0 + u * nthreads];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < W && i0 + u * nthreads < s4) {
+            acc[u].x += __uint_as_float(v[u][r].x << 16); acc[u].y += __uint_as_float(v[u][r].x & 0xFFFF0000u);
+            acc[u].z += __uint_as_float(v[u][r].y << 16); acc[u].w += __uint_as_float(v[u][r].y & 0xFFFF0000u);
+          }
+    } else {
+      float4 v[U][kMaxRanks];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < W && i0 + u * nthreads < s4)
+            v[u][r] = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(wire.p[r]) + half * half_elems + base)[i0 + u * nthreads];
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < W && i0 + u * nthreads < s4) { acc[u].x += v[u][r].x; acc[u].y += v[u][r].y; acc[u].z += v[u][r].z; acc[u].w += v[u][r].w; }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * nthreads;
+      if (i >= s4) break;
+      float4 o = acc[u];
+      if (accumulate) {
+        const float4 old = reinterpret_cast<const float4*>(out)[i];
+        o.x += old.x; o.y += old.y; o.z += old.z; o.w += old.w;
+      }
+      reinterpret_cast<float4*>(out)[i] = o;
+    }
+  }
+  grid_barrier(grid_ctr, grid_target0 + gridDim.x);
+  if (blockIdx.x == 0) signal_all(flags, 1, W, R, epoch);
+}
+
 // cross-GPU barrier only (used around parameter updates of the NCCL-free paths and in tests)
 __global__ void peer_barrier_kernel(PeerPtrs flags, int channel, int world, int rank, uint32_t epoch) {
   signal_all(flags, channel, world, rank, epoch);
@@ -458,6 +551,29 @@ B200_API int b200_zero_step(const b200_zero_step_args* a, void* stream) {
   int grid = a->grid < 1 ? 1 : a->grid;
   p.grid_target0 = a->grid_target_base + (unsigned int)grid;
   zero_step_kernel<<<grid, kCommThreads, 0, (cudaStream_t)stream>>>(p);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// n: elements of the unit (multiple of 4 * world); half_elems: elements of one half of every rank's staging buffer
+// (>= n); wire_dtype: B200_DT_FP32 or B200_DT_BF16; epoch: 1, 2, 3, ... per flag set, the same on every rank.
+B200_API int b200_reduce_scatter(const float* grad, const void* const* wire_ptrs, const void* const* flag_ptrs, float* out,
+                                 long long n, long long half_elems, int world, int rank, unsigned int epoch, float scale,
+                                 int accumulate, int wire_dtype, unsigned int* grid_ctr, unsigned int grid_target_base,
+                                 int grid, void* stream) {
+  if (world < 1 || world > kMaxRanks || n <= 0 || n % (4ll * world) || half_elems < n || half_elems % 4 || epoch == 0)
+    return B200_ERR_BAD_SHAPE;
+  if (grid < 1) grid = 1;
+  const unsigned int t0 = grid_target_base + (unsigned int)grid;
+  if (wire_dtype == B200_DT_BF16)
+    reduce_scatter_kernel<true><<<grid, kCommThreads, 0, (cudaStream_t)stream>>>(
+        grad, to_peers(wire_ptrs, world), to_peers(flag_ptrs, world), out, n, half_elems, world, rank, epoch, scale,
+        accumulate, grid_ctr, t0);
+  else if (wire_dtype == B200_DT_FP32)
+    reduce_scatter_kernel<false><<<grid, kCommThreads, 0, (cudaStream_t)stream>>>(
+        grad, to_peers(wire_ptrs, world), to_peers(flag_ptrs, world), out, n, half_elems, world, rank, epoch, scale,
+        accumulate, grid_ctr, t0);
+  else return B200_ERR_UNSUPPORTED;
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -259,8 +259,10 @@ static cudaError_t launch_gemv_one(const GemvParams& p, cudaStream_t st) {
 template <bool BF16>
 static int launch_gemv_lin(const GemvParams& p, cudaStream_t st) {
   cudaError_t e;
-  if (p.M <= 8) e = launch_gemv_one<BF16, true, 1, 4, true>(p, st);
-  else if (p.M <= 16) e = launch_gemv_one<BF16, true, 2, 3, true>(p, st);
+  // 2 CTAs per SM (128 registers, no spills): with 4 chunks x 2 rows x 16 B requested up front per lane that is 64 KB in
+  // flight per SM, above the ~44 KB that 6.5 TB/s x ~1 us of DRAM latency asks of each of the 148 SMs
+  if (p.M <= 8) e = launch_gemv_one<BF16, true, 1, 2, true>(p, st);
+  else if (p.M <= 16) e = launch_gemv_one<BF16, true, 2, 2, true>(p, st);
   else if (p.M <= 32) e = launch_gemv_one<BF16, true, 4, 2, true>(p, st);
   else e = launch_gemv_one<BF16, true, 8, 1, true>(p, st);
   return (int)e;

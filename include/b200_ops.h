@@ -275,6 +275,14 @@ int b200_peer_gather_skip(const void* const* src_ptrs, long long src_off_bytes, 
 /* the same gather issued as one cudaMemcpyAsync per owner (copy engines instead of SMs): the ZeRO-3 shard prefetch */
 int b200_peer_gather_ce(const void* const* src_ptrs, long long src_off_bytes, void* out, long long shard_bytes,
                         int world, int skip, void* stream);
+/* K-C2 for FSDP / ZeRO-2: reduce-scatter of one flat gradient unit over peer memory; the cast to the wire dtype
+ * (fp32 or bf16 = MixedPrecision.reduce_dtype) and the scale are fused, the staging buffer (symmetric, 2 halves of
+ * half_elems elements) is written by the kernel itself. out = this rank's n / world slice (+= when accumulate).
+ * Replaces reduce_scatter_tensor inside FSDP (fsdp_gpt_wikitext2.py:304-312) and DeepSpeed's ZeRO-2 reduce-scatter. */
+int b200_reduce_scatter(const float* grad, const void* const* wire_ptrs, const void* const* flag_ptrs, float* out,
+                        long long n, long long half_elems, int world, int rank, unsigned int epoch, float scale,
+                        int accumulate, int wire_dtype, unsigned int* grid_ctr, unsigned int grid_target_base, int grid,
+                        void* stream);
 int b200_peer_barrier(const void* const* flag_ptrs, int channel, int world, int rank, unsigned int epoch,
                       void* stream);
 

@@ -12,11 +12,14 @@ Mechanics (one process per GPU):
 * every wrapped unit owns a flat parameter: an fp32 *master shard* (1/world of it, exposed as the unit's single
   ``nn.Parameter`` so any optimizer works on ``model.parameters()``) and a transient *full* buffer in the compute
   dtype whose storage is released between uses (``untyped_storage().resize_``), exactly when FULL_SHARD says so;
-* unshard = cast the master shard to the compute dtype into a symmetric buffer, then ONE pull-based gather kernel
-  that reads the other ranks' shards over NVLink (``b200_peer_gather``, K-C3) — or ``all_gather_into_tensor`` on
-  CPU/gloo and without symmetric memory;
+* the compute-dtype copy of every master shard is staged in symmetric memory ONCE per optimizer step (two device-side
+  barriers per step, none per unit); unshard = a pull-based gather of the peers' staged shards over NVLink on the COPY
+  ENGINES (``b200_peer_gather_ce``, K-C3), issued on a side stream one unit AHEAD of the compute (forward: the next
+  unit in execution order, backward: the previous one), so the gather of unit i+1 overlaps the compute of unit i —
+  or ``all_gather_into_tensor`` on CPU/gloo and without symmetric memory;
 * gradients accumulate in a transient fp32 full buffer (``p.main_grad`` for the wgrad GEMMs, autograd grads are
-  folded in), then a reduce-scatter leaves each rank its 1/world slice in the master shard's ``.grad``;
+  folded in), then ``b200_reduce_scatter`` (peer-memory reads, cast to ``MixedPrecision.reduce_dtype`` and 1/world
+  fused, double-buffered staging, on a side stream) leaves each rank its 1/world slice in the master shard's ``.grad``;
 * SHARD_GRAD_OP keeps the full buffer between forward and backward; NO_SHARD never frees it.
 """
 from __future__ import annotations
@@ -136,9 +139,20 @@ class _Unit:
             flat[off:off + p.numel()].copy_(p.data.reshape(-1).float())
         if W > 1 and owner.sync_states:
             dist.broadcast(flat, src=0)
-        # fp32 master shard = the Parameter the optimizer sees
-        self.master = nn.Parameter(flat[R * self.shard_len:(R + 1) * self.shard_len].clone())
+        # fp32 master shard = the Parameter the optimizer sees. CPUOffload(offload_params=True) / CPUOffloadPolicy /
+        # DeepSpeed ``offload_param: {device: cpu}``: the master shard and its gradient live in (pinned) host memory,
+        # the optimizer steps there, and the GPU only ever holds the compute-dtype copies.
+        self.offload = bool(owner.cpu_offload is not None and getattr(owner.cpu_offload, "offload_params", False))
+        shard = flat[R * self.shard_len:(R + 1) * self.shard_len].clone()
+        if self.offload:
+            shard = shard.cpu()
+            if dev.type == "cuda":
+                shard = shard.pin_memory()
+        self.master = nn.Parameter(shard)
         self.master.grad = torch.zeros_like(self.master.data)
+        if self.offload and dev.type == "cuda":
+            self.master.grad = self.master.grad.pin_memory()
+        self.gshard = torch.zeros(self.shard_len, dtype=torch.float32, device=dev) if self.offload else None
         self.master._fsdp_unit = self
         # compute-dtype shard staged for the gather (symmetric memory when peers can read it)
         self.symm = SymmBuffer(self.shard_len, self.pdtype, dev) if owner.use_symm else None
@@ -150,6 +164,7 @@ class _Unit:
         self._point_params()
         self.gfull: Optional[torch.Tensor] = None
         self.sharded = False
+        self.gather_ev = None
         self.pending: Set[int] = set()
         self.reduced = True
         self.master_version = -1
@@ -161,35 +176,69 @@ class _Unit:
             p._fsdp_unit = self
 
     # ---- parameters ----
-    def unshard(self) -> None:
-        if not self.sharded and self.master_version == self.master._version:
-            return
+    def stage(self) -> None:
+        """fp32 master shard -> compute dtype, into the buffer the peers read."""
+        self.shard_lowp.copy_(self.master.data)
+        self.master_version = self.master._version
+
+    def _alloc_full(self) -> None:
         es = self.full.element_size()
         if self.full.untyped_storage().size() == 0:
             self.full.untyped_storage().resize_(self.n * es)
-        W = self.o.world
-        self.shard_lowp.copy_(self.master.data)                 # fp32 master -> compute dtype
+
+    def issue_gather(self) -> None:
+        """Start the gather of this unit's peers' shards on the gather stream (copy engines); ``gather_ev`` marks its end."""
+        o = self.o
+        self._alloc_full()
+        cur = torch.cuda.current_stream()
+        o.gather_stream.wait_stream(cur)            # the buffer exists (and its last reader is done) in stream order
+        with torch.cuda.stream(o.gather_stream):
+            from .symm import peer_gather_ce
+            peer_gather_ce(self.symm, self.full, 0, self.shard_len * self.full.element_size())
+            self.gather_ev = torch.cuda.Event()
+            self.gather_ev.record(o.gather_stream)
+
+    def unshard(self, direction: int = 1) -> None:
+        o = self.o
+        W = o.world
+        if W > 1 and self.symm is not None:
+            o.ensure_staged()
+            if self.sharded:
+                if self.gather_ev is None:
+                    self.issue_gather()
+                o.wait_gather(self)
+                self.sharded = False
+            o.prefetch_after(self, direction)
+            return
+        if not self.sharded and self.master_version == self.master._version:
+            return
+        self._alloc_full()
+        self.stage()
         if W == 1:
             self.full.copy_(self.shard_lowp)
-        elif self.symm is not None:
-            from .symm import peer_barrier
-            peer_barrier(self.o.flags)                           # every rank's staged shard is current
-            peer_gather(self.symm, self.full, 0, self.shard_len * es)
-            peer_barrier(self.o.flags)                           # nobody restages while a peer still reads
         else:
             dist.all_gather_into_tensor(self.full, self.shard_lowp)
         self.sharded = False
-        self.master_version = self.master._version
 
     def reshard(self) -> None:
         if self.o.strategy == ShardingStrategy.NO_SHARD or self.o.world == 1:
             return
         self.full.untyped_storage().resize_(0)
         self.sharded = True
+        self.gather_ev = None
 
     # ---- gradients ----
+    def grad_target(self) -> torch.Tensor:
+        """Where the reduced gradient shard is accumulated on the device (the host copy follows in ``flush_offload``)."""
+        return self.gshard if self.offload else self.master.grad
+
+    def flush_offload(self) -> None:
+        if self.offload:
+            self.master.grad.add_(self.gshard.to(self.master.grad.device))
+            self.gshard.zero_()
+
     def prepare_backward(self) -> None:
-        self.unshard()
+        self.unshard(direction=-1)
         if self.gfull is None:
             self.gfull = torch.zeros(self.n, dtype=torch.float32, device=self.full.device)
             for p, off in zip(self.params, self.offs):
@@ -207,7 +256,9 @@ class _Unit:
                 p.grad = None
         W = self.o.world
         if W == 1:
-            self.master.grad += self.gfull
+            self.grad_target().add_(self.gfull)
+        elif self.o.use_symm:
+            self.o.peer_reduce_scatter(self)
         else:
             out = torch.empty(self.shard_len, dtype=torch.float32, device=self.gfull.device)
             if self.gfull.is_cuda:
@@ -215,7 +266,7 @@ class _Unit:
             else:
                 dist.all_reduce(self.gfull, op=dist.ReduceOp.SUM)
                 out.copy_(self.gfull[self.o.rank * self.shard_len:(self.o.rank + 1) * self.shard_len])
-            self.master.grad += out / W
+            self.grad_target().add_(out / W)
         if self.o.require_sync:
             for p in self.params:
                 if hasattr(p, "main_grad"):
@@ -237,6 +288,9 @@ class FullyShardedDataParallel(nn.Module):
         self.rank = info.rank if self.world > 1 else 0
         self.strategy = sharding_strategy or ShardingStrategy.FULL_SHARD
         self.param_dtype = mixed_precision.param_dtype if mixed_precision else None
+        self.reduce_dtype = (mixed_precision.reduce_dtype if mixed_precision else None) or torch.float32
+        if self.reduce_dtype not in (torch.float32, torch.bfloat16):
+            raise ValueError("reduce_dtype must be float32 or bfloat16")
         self.sync_states = sync_module_states
         self.cpu_offload = cpu_offload
         self.require_sync = True
@@ -274,6 +328,15 @@ class FullyShardedDataParallel(nn.Module):
         if rest:
             self.units.append(_Unit(self, module, rest, "root"))
         self._flat_params = nn.ParameterList([u.master for u in self.units])
+        self._order: List[_Unit] = []           # forward execution order (recorded on the first forward)
+        self._exposed: List[tuple] = []
+        self._rs_epoch = 0
+        if self.use_symm:
+            self.gather_stream = torch.cuda.Stream(dev)
+            self.rs_stream = torch.cuda.Stream(dev)
+            nmax = max(u.n for u in self.units)
+            self._wire_half = (nmax + 63) // 64 * 64
+            self._wire = SymmBuffer(2 * self._wire_half, self.reduce_dtype, dev, zero=False)
         # ---- hooks ----
         for u in self.units:
             u.module.register_forward_pre_hook(lambda m, a, uu=u: uu.unshard())
@@ -284,6 +347,73 @@ class FullyShardedDataParallel(nn.Module):
                 p._grad_ready = (lambda pp=p: self._on_grad(pp))
                 p.register_post_accumulate_grad_hook(lambda pp: self._on_grad(pp))
         self._cb_queued = False
+
+    # ------------------------------------------------------------------ peer-memory collectives
+    def ensure_staged(self) -> None:
+        """After an optimizer step the compute-dtype shards the peers read are stale. Restage ALL units at once between
+        two device-side barriers (peers are done reading the old ones / every new one is visible) — two barriers per
+        optimizer step instead of two per unit per pass."""
+        if all(u.master_version == u.master._version for u in self.units):
+            return
+        from .symm import peer_barrier
+        peer_barrier(self.flags, channel=7)
+        for u in self.units:
+            u.stage()
+            u.sharded = True                # whatever is gathered is stale now
+            u.gather_ev = None
+        peer_barrier(self.flags, channel=7)
+
+    def wait_gather(self, u: "_Unit") -> None:
+        cur = torch.cuda.current_stream()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(cur)
+        cur.wait_event(u.gather_ev)
+        e1.record(cur)
+        self._note_exposed(e0, e1)
+
+    def _note_exposed(self, e0, e1) -> None:
+        self._exposed.append((e0, e1))
+        if len(self._exposed) > 4096:
+            del self._exposed[:2048]
+
+    def prefetch_after(self, u: "_Unit", direction: int) -> None:
+        """Issue the gather of the unit that runs after ``u`` (forward order, or reverse order in backward)."""
+        if u not in self._order:
+            if direction > 0:
+                self._order.append(u)
+            return
+        i = self._order.index(u) + direction
+        if 0 <= i < len(self._order):
+            nxt = self._order[i]
+            if nxt.sharded and nxt.gather_ev is None and self.strategy != ShardingStrategy.NO_SHARD:
+                nxt.issue_gather()
+
+    def peer_reduce_scatter(self, u: "_Unit") -> None:
+        """``master.grad += sum over ranks of gfull / world`` for this rank's slice: one kernel on the reduce stream."""
+        import ctypes
+        from ..ops import _native as nv
+        vp, i32, i64, u32, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint, ctypes.c_float
+        cur = torch.cuda.current_stream()
+        self.rs_stream.wait_stream(cur)                          # the unit's gradients are complete in stream order
+        u.gfull.record_stream(self.rs_stream)
+        self._rs_epoch += 1
+        grid = max(1, min(64, u.n // 4 // 256))
+        base = self.flags.take_grid_target(grid, 2)
+        fn = nv.proto("b200_reduce_scatter", [vp, vp, vp, vp, i64, i64, i32, i32, u32, f32, i32, i32, vp, u32, i32, vp])
+        with torch.cuda.stream(self.rs_stream):
+            nv.check(fn(nv.ptr(u.gfull), ctypes.cast(self._wire.c_ptrs(), vp), ctypes.cast(self.flags.flags.c_ptrs(), vp),
+                        nv.ptr(u.grad_target()), u.n, self._wire_half, self.world, self.rank, self._rs_epoch, 1.0 / self.world, 1,
+                        nv.dtype_code(self.reduce_dtype), nv.ptr(self.flags.grid_ctr), base, grid, nv.stream()),
+                     "reduce_scatter")
+            nv.count_launch()
+
+    def exposed_ms(self, reset: bool = True) -> float:
+        """Time (ms, this rank) the compute stream spent waiting for gathers and for the last reduce-scatters."""
+        torch.cuda.synchronize()
+        t = sum(a.elapsed_time(b) for a, b in self._exposed)
+        if reset:
+            self._exposed.clear()
+        return t
 
     # ------------------------------------------------------------------ scheduling
     def _post_forward(self, u: _Unit) -> None:
@@ -313,6 +443,15 @@ class FullyShardedDataParallel(nn.Module):
         for u in self.units:
             if not u.reduced:
                 u.reduce_grads()
+        if self.use_symm:
+            cur = torch.cuda.current_stream()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(cur)
+            cur.wait_stream(self.rs_stream)                      # the optimizer may read master.grad after this
+            e1.record(cur)
+            self._note_exposed(e0, e1)
+        for u in self.units:
+            u.flush_offload()
 
     def forward(self, *args, **kwargs):
         root = self.units[-1] if self.units and self.units[-1].module is self.module else None
@@ -335,15 +474,16 @@ class FullyShardedDataParallel(nn.Module):
             u.master.grad.zero_()
 
     def clip_grad_norm_(self, max_norm: float) -> torch.Tensor:
-        ss = torch.zeros(1, device=self.units[0].master.device)
+        dev = self.units[0].full.device
+        ss = torch.zeros(1, device=dev)
         for u in self.units:
-            ss += u.master.grad.float().pow(2).sum()
+            ss += u.master.grad.float().pow(2).sum().to(dev)
         if self.world > 1:
             dist.all_reduce(ss)
         norm = ss.sqrt()
         coef = (max_norm / (norm + 1e-6)).clamp(max=1.0)
         for u in self.units:
-            u.master.grad.mul_(coef)
+            u.master.grad.mul_(coef.to(u.master.grad.device))
         return norm[0]
 
     class _NoSync:
@@ -398,7 +538,11 @@ def fully_shard(module: nn.Module, *, mesh: Optional[DeviceMesh] = None, reshard
     root, to get per-block groups — nested calls are honoured because already-sharded parameters are skipped."""
     mp = MixedPrecision(param_dtype=mp_policy.param_dtype, reduce_dtype=mp_policy.reduce_dtype) if mp_policy else None
     strat = ShardingStrategy.FULL_SHARD if reshard_after_forward else ShardingStrategy.SHARD_GRAD_OP
-    return FullyShardedDataParallel(module, sharding_strategy=strat, mixed_precision=mp, sync_module_states=True)
+    # the base ``OffloadPolicy()`` the reference passes means "no offload"; ``CPUOffloadPolicy`` keeps the fp32 shards,
+    # their gradients and the optimizer state in (pinned) host memory
+    off = CPUOffload(offload_params=True) if isinstance(offload_policy, CPUOffloadPolicy) else None
+    return FullyShardedDataParallel(module, sharding_strategy=strat, mixed_precision=mp, cpu_offload=off,
+                                    sync_module_states=True)
 
 
 def get_state_dict(model: nn.Module, optimizers: Iterable = (), options: Optional[StateDictOptions] = None):

@@ -328,6 +328,20 @@ class ZeroEngine(nn.Module):
                          and os.environ.get("B200_COMM", "symm") == "symm")
         self.unit = 256 * W  # arena length granularity: every rank's shard is a whole number of 8-bit blocks
 
+        # ---- ZeRO-2 / ZeRO-3 of DENSE trainable parameters: really partition gradients (2) and parameters (3) ----
+        self._fsdp = None
+        self.base_shard_info = None
+        dense = (lora_config is None and arena is None and getattr(model, "_lora_arena", None) is None
+                 and not any(isinstance(m, FusedLinear) and m.nf4 is not None for m in model.modules()))
+        want_param_offload = self.config.zero.offload_param_device == "cpu"
+        if dense and W > 1 and (self.stage >= 2 or want_param_offload) and os.environ.get("B200_ZERO_DENSE_SHARD", "1") != "0":
+            self._init_dense_sharded(model, optimizer, lr_scheduler, want_param_offload)
+            return
+        if want_param_offload and not (dense and W > 1):
+            log.warning("offload_param: cpu is honoured for dense models on > 1 rank (parameter shards in pinned host "
+                        "memory); this run keeps parameters on the GPU%s",
+                        "" if dense else " (LoRA / 4-bit base: the trainable set is a few MB)")
+
         # ---- trainable parameters -> flat arena (symmetric when fused collectives are on) ----
         alloc = None
         if self.use_symm:
@@ -357,7 +371,6 @@ class ZeroEngine(nn.Module):
         self.shard = slice(R * self.shard_len, (R + 1) * self.shard_len) if (self.stage >= 1 and W > 1) else slice(0, arena.numel)
 
         # ---- stage 3: partition the frozen 4-bit base ----
-        self.base_shard_info = None
         if self.stage >= 3 and W > 1 and self.use_symm:
             self.base_shard_info = shard_nf4_base(model, W, R, dev)
 
@@ -379,8 +392,72 @@ class ZeroEngine(nn.Module):
         self._breakdown = bool(self.config.wall_clock_breakdown) and self.device.type == "cuda"
         self._last_norm = None
 
+    # ------------------------------------------------------------------ dense ZeRO-2 / ZeRO-3 backend
+    def _init_dense_sharded(self, model, optimizer, lr_scheduler, offload_param: bool) -> None:
+        """Stage 2 (``SHARD_GRAD_OP``: gradients and optimizer state partitioned, parameters kept gathered between
+        forward and backward) and stage 3 (``FULL_SHARD``: parameters partitioned too, gathered per block one block
+        ahead on the copy engines and freed after use) of the reference's hand-written GPTLike loops
+        (LLM_Distributed_Trainning/DeepSpeed/DeepSpeed-GPTLike-ZeRO-{2,3,Offload}/ds_config.json). Every
+        ``nn.ModuleList`` member is one unit, the rest of the model another. ``overlap_comm``: the reduce-scatter of
+        a unit starts on a side stream as soon as backward has produced its last gradient; ``contiguous_gradients``:
+        a unit's gradients are one flat buffer that exists only between its backward and its reduce-scatter;
+        ``offload_param`` / ``offload_optimizer`` = cpu: fp32 shards, their gradients and the AdamW state live in
+        pinned host memory. Peak memory per rank falls as 1 / world for parameters (3), gradients and state (2, 3)."""
+        from .fsdp import CPUOffload, FullyShardedDataParallel, MixedPrecision, ShardingStrategy
+        dev = self.device
+        kinds = {type(m) for ml in model.modules() if isinstance(ml, nn.ModuleList) for m in ml
+                 if any(p.requires_grad for p in m.parameters())}
+        policy = (lambda m, recurse=False, n=0: type(m) in kinds) if kinds else None
+        first = next(p for p in model.parameters() if p.requires_grad)
+        rd = torch.bfloat16 if (self.config.bf16 and first.dtype == torch.bfloat16) else torch.float32
+        offload = offload_param or self.config.zero.offload_optimizer_device == "cpu"
+        strat = ShardingStrategy.FULL_SHARD if self.stage >= 3 else ShardingStrategy.SHARD_GRAD_OP
+        self._fsdp = FullyShardedDataParallel(model, auto_wrap_policy=policy, sharding_strategy=strat,
+                                              mixed_precision=MixedPrecision(param_dtype=None, reduce_dtype=rd),
+                                              cpu_offload=CPUOffload(offload_params=True) if offload else None,
+                                              sync_module_states=True)
+        self.use_symm = self._fsdp.use_symm
+        self.arena = None
+        self.offload = offload
+        kind, hp = self._optimizer_hparams(optimizer)
+        self.opt_kind = kind
+        if offload:
+            self.optimizer = torch.optim.AdamW(list(self._fsdp.parameters()), **hp)       # host tensors: torch's CPU AdamW
+        else:
+            self.optimizer = (PagedAdamW8bit if kind == "adamw8bit" else FusedAdamW)(list(self._fsdp.parameters()), **hp)
+        self.lr_scheduler = lr_scheduler or self._build_scheduler()
+        self.scaler = LossScaler(self.config.fp16) if self.config.fp16.enabled else None
+        self.micro_steps = self.global_steps = self.skipped_steps = 0
+        self._timers = {}
+        self._breakdown = bool(self.config.wall_clock_breakdown) and dev.type == "cuda"
+        self._last_norm = None
+        self.shard = None
+        log.info("ZeRO stage %d (dense): %d units, strategy %s, reduce dtype %s, offload %s", self.stage,
+                 len(self._fsdp.units), strat.name, rd, offload)
+
+    def _step_dense(self, inv_scale: float) -> None:
+        f = self._fsdp
+        if inv_scale != 1.0:
+            for u in f.units:
+                u.master.grad.mul_(inv_scale)
+        overflow = False
+        if self.max_norm > 0 or self.scaler is not None:
+            norm = f.clip_grad_norm_(self.max_norm if self.max_norm > 0 else float("inf"))
+            self._last_norm = norm
+            if self.scaler is not None:
+                overflow = not bool(torch.isfinite(norm).item())
+        if not overflow:
+            self.optimizer.step()
+            for u in f.units:        # the flat kernels write through .data: tell the units their shards changed
+                torch.autograd.graph.increment_version(u.master)
+        if self.scaler is not None:
+            self.skipped_steps += int(overflow)
+            self.scaler.update(overflow)
+        f.zero_grad()
+
     # ------------------------------------------------------------------ construction helpers
-    def _build_optimizer(self, client):
+    def _optimizer_hparams(self, client):
+        """(kind, hyper-parameters) from a client optimizer or the DeepSpeed JSON ``optimizer`` block."""
         if client is not None and not isinstance(client, FusedAdamW):
             # a client torch optimizer (e.g. optim.AdamW built by the script, DeepSpeed-GPTLike-ZeRO-1.py:272):
             # adopt its hyper-parameters, run our flat implementation
@@ -399,6 +476,10 @@ class ZeroEngine(nn.Module):
             p = dict(oc.get("params", {}))
             hp = dict(lr=p.get("lr", 1e-3), betas=tuple(p.get("betas", (0.9, 0.999))), eps=p.get("eps", 1e-8),
                       weight_decay=p.get("weight_decay", 0.0 if "adamw" not in t else 0.01) if "weight_decay" not in p else p["weight_decay"])
+        return kind, hp
+
+    def _build_optimizer(self, client):
+        kind, hp = self._optimizer_hparams(client)
         self.opt_kind = kind
         cls = PagedAdamW8bit if kind == "adamw8bit" else FusedAdamW
         if self.offload:
@@ -467,13 +548,19 @@ class ZeroEngine(nn.Module):
         # the factor ``backward`` will apply is declared up front so a fused lm_head + loss can scale the gradients
         # it forms during the forward launches (tied / trainable heads write their weight gradient there)
         with self._phase("forward"), grad_scale_context(self._loss_factor() if torch.is_grad_enabled() else None):
+            if self._fsdp is not None:
+                return self._fsdp(*args, **kwargs)
             return self.module(*args, **kwargs)
 
     def backward(self, loss: torch.Tensor) -> None:
         """Scales by 1/accumulation (and the fp16 loss scale) like DeepSpeed, then backpropagates into the arena."""
         s = self._loss_factor()
         with self._phase("backward"):
-            (loss * s).backward()
+            if self._fsdp is not None and (self.micro_steps + 1) % self.ga:
+                with self._fsdp.no_sync():           # non-boundary micro-step: accumulate locally, no collective
+                    (loss * s).backward()
+            else:
+                (loss * s).backward()
         self.micro_steps += 1
 
     def train_micro_batch(self, input_ids, labels=None, **kw) -> torch.Tensor:
@@ -484,6 +571,8 @@ class ZeroEngine(nn.Module):
 
     def supports_fused_accumulation(self) -> bool:
         import inspect
+        if self._fsdp is not None:
+            return False
         try:
             return "micro_batches" in inspect.signature(self.module.forward).parameters
         except (TypeError, ValueError):
@@ -532,13 +621,16 @@ class ZeroEngine(nn.Module):
             return  # non-boundary micro-steps issue no collective at all
         inv_scale = 1.0 / self.scaler.scale if self.scaler is not None else 1.0
         with self._phase("step"):
-            if self.world == 1:
+            if self._fsdp is not None:
+                self._step_dense(inv_scale)
+            elif self.world == 1:
                 self._step_single(inv_scale)
             elif self.use_symm and not self.offload:
                 self._step_fused(inv_scale)
             else:
                 self._step_collectives(inv_scale)
-        self.arena.zero_grad()
+        if self.arena is not None:
+            self.arena.zero_grad()
         if self.lr_scheduler is not None:
             self.lr_scheduler.step()
         self.global_steps += 1
@@ -680,6 +772,9 @@ class ZeroEngine(nn.Module):
     def comm_stats(self) -> Dict[str, Any]:
         out: Dict[str, Any] = {"backend": "nvlink-peer-fused" if self.use_symm else ("single" if self.world == 1 else "torch.distributed"),
                                "zero_stage": self.stage}
+        if self._fsdp is not None:
+            out["dense_sharding"] = self._fsdp.strategy.name
+            out["units"] = len(self._fsdp.units)
         for k, evs in self._timers.items():
             ms = [a.elapsed_time(b) for a, b in evs[-20:]]
             if ms:
@@ -721,6 +816,8 @@ class ZeroEngine(nn.Module):
     def consolidated_state_dict(self) -> Dict[str, torch.Tensor]:
         """Full trainable state dict on every rank (replicas are always current after ``step``) —
         what ``stage3_gather_16bit_weights_on_model_save`` / FSDP full_state_dict produce."""
+        if self._fsdp is not None:
+            return self._fsdp.full_state_dict(cpu=False)         # gathers every unit (C8), re-shards afterwards
         return {k: v.detach().clone() for k, v in self.module.state_dict().items()}
 
     def save_checkpoint(self, save_dir: str, tag: Optional[str] = None, client_state: Optional[dict] = None) -> None:
@@ -729,16 +826,18 @@ class ZeroEngine(nn.Module):
         tag = tag or f"global_step{self.global_steps}"
         d = os.path.join(save_dir, tag)
         os.makedirs(d, exist_ok=True)
+        full = self.consolidated_state_dict() if (self._fsdp is not None or self.rank == 0) else None   # a collective when sharded
         if self.rank == 0:
-            torch.save({"module": self.consolidated_state_dict(), "global_steps": self.global_steps,
+            torch.save({"module": full, "global_steps": self.global_steps,
                         "micro_steps": self.micro_steps, "skipped_steps": self.skipped_steps,
                         "lr_scheduler": None if self.lr_scheduler is None else self.lr_scheduler.state_dict(),
                         "ds_config": self.config.extra, "client_state": client_state or {}},
                        os.path.join(d, "mp_rank_00_model_states.pt"))
             with open(os.path.join(save_dir, "latest"), "w") as f:
                 f.write(tag)
-        torch.save({"optimizer_state_dict": self.optimizer.state_dict(), "shard": (self.shard.start, self.shard.stop),
-                    "master_shard": self.arena.data[self.shard].detach().cpu(), "zero_stage": self.stage,
+        torch.save({"optimizer_state_dict": self.optimizer.state_dict(), "shard": (self.shard.start, self.shard.stop) if self.shard is not None else None,
+                    "master_shard": (self.arena.data[self.shard].detach().cpu() if self.arena is not None else
+                                     [u.master.detach().cpu() for u in self._fsdp.units]), "zero_stage": self.stage,
                     "world_size": self.world, "loss_scale": None if self.scaler is None else self.scaler.scale},
                    os.path.join(d, f"zero_pp_rank_{self.rank}_mp_rank_00_optim_states.pt"))
         if self.world > 1:
@@ -750,7 +849,7 @@ class ZeroEngine(nn.Module):
                 tag = f.read().strip()
         d = os.path.join(load_dir, tag)
         ms = torch.load(os.path.join(d, "mp_rank_00_model_states.pt"), map_location="cpu", weights_only=False)
-        self.module.load_state_dict(ms["module"], strict=False)
+        (self._fsdp if self._fsdp is not None else self.module).load_state_dict(ms["module"], strict=False)
         self.global_steps, self.micro_steps = ms["global_steps"], ms["micro_steps"]
         if self.lr_scheduler is not None and ms.get("lr_scheduler"):
             self.lr_scheduler.load_state_dict(ms["lr_scheduler"])
@@ -764,7 +863,8 @@ class ZeroEngine(nn.Module):
             else:
                 log.warning("checkpoint %s was written by %d ranks, this job has %d: optimizer state NOT restored "
                             "(parameters are); the moments restart from zero", d, st["world_size"], self.world)
-        torch.autograd.graph.increment_version(self.arena.data)
+        if self.arena is not None:
+            torch.autograd.graph.increment_version(self.arena.data)
         return d, ms.get("client_state", {})
 
 

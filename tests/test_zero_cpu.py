@@ -105,3 +105,69 @@ def test_train_batch_equals_sequential_micro_batches():
     assert torch.allclose(a.arena.grad, b.arena.grad, rtol=1e-4, atol=1e-6), float((a.arena.grad - b.arena.grad).abs().max())
     a.step(); b.step()
     assert torch.allclose(a.arena.data, b.arena.data, rtol=1e-4, atol=1e-6)
+
+
+def _dense_worker(rank, world, stage, offload, tmp):
+    """Dense (no LoRA) GPTLike under ZeRO-2 / ZeRO-3 / ZeRO-Offload: gradients (2) and parameters (3) are partitioned."""
+    from llm_in_practise_b200.models.gpt import GPTLike
+    from llm_in_practise_b200.parallel.dist import setup_distributed
+    from llm_in_practise_b200.parallel.zero import initialize
+    setup_distributed()
+    torch.manual_seed(0)
+    model = GPTLike(64, 16, 2, 2, 32, dropout=0.0)
+    n_full = sum(p.numel() for p in model.parameters())
+    cfg = {"zero_optimization": {"stage": stage, "overlap_comm": True, "contiguous_gradients": True},
+           "gradient_accumulation_steps": 2, "gradient_clipping": 1.0, "train_micro_batch_size_per_gpu": 2,
+           "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}}}
+    if offload:
+        cfg["zero_optimization"]["offload_param"] = {"device": "cpu", "pin_memory": True}
+        cfg["zero_optimization"]["offload_optimizer"] = {"device": "cpu", "pin_memory": True}
+    eng = initialize(model=model, config=cfg)
+    assert eng._fsdp is not None and eng.arena is None
+    owned = sum(p.numel() for p in eng._fsdp.parameters())
+    assert owned <= n_full // world + 64 * world * len(eng._fsdp.units)        # each rank owns ~1/world of the fp32 masters
+    g = torch.Generator().manual_seed(7)
+    data = torch.randint(0, 64, (8, 2, 16), generator=g)
+    k = 0
+    for step in range(2):
+        for m in range(2):
+            x = data[(k * world + rank) % 8]
+            k += 1
+            out = eng(x, x)
+            eng.backward(out[1] if isinstance(out, tuple) else out)
+        eng.step()
+    if stage >= 3:       # parameters are released between uses
+        assert all(u.full.untyped_storage().size() == 0 for u in eng._fsdp.units if u.module is not eng.module)
+    sd = eng.consolidated_state_dict()
+    if rank == 0:
+        torch.save({k_: v.float().cpu() for k_, v in sd.items()}, f"{tmp}/dense.pt")
+    eng.save_checkpoint(f"{tmp}/ck", tag="t")
+
+
+@pytest.mark.parametrize("stage,offload", [(2, False), (3, False), (3, True)])
+def test_dense_zero2_zero3_partition_and_match_single_process(stage, offload, tmp_path):
+    run_distributed(_dense_worker, 2, (stage, offload, str(tmp_path)))
+    got = torch.load(tmp_path / "dense.pt")
+    from llm_in_practise_b200.models.gpt import GPTLike
+    from llm_in_practise_b200.parallel.zero import initialize
+    torch.manual_seed(0)
+    model = GPTLike(64, 16, 2, 2, 32, dropout=0.0)
+    eng = initialize(model=model, config={"zero_optimization": {"stage": 0}, "gradient_accumulation_steps": 4,
+                                          "gradient_clipping": 1.0, "train_micro_batch_size_per_gpu": 2,
+                                          "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.0}}})
+    g = torch.Generator().manual_seed(7)
+    data = torch.randint(0, 64, (8, 2, 16), generator=g)
+    k = 0
+    for step in range(2):
+        for m in range(2):
+            for r in range(2):
+                x = data[(k * 2 + r) % 8]
+                out = eng(x, x)
+                eng.backward(out[1] if isinstance(out, tuple) else out)
+            k += 1
+        eng.step()
+    want = {k_: v.float() for k_, v in model.state_dict().items()}
+    for k_ in want:
+        # the key bias of attention has a zero true gradient (softmax is shift-invariant): Adam turns its rounding noise
+        # into +-lr-sized moves, so the bound is 1e-3 — a wrong partition / missed update shows up as 2e-2 (2 steps x lr)
+        assert torch.allclose(got[k_], want[k_], atol=1e-3), (k_, (got[k_] - want[k_]).abs().max())
