@@ -1,5 +1,5 @@
 """Multi-GPU ZeRO-3 QLoRA check (run under torchrun, >= 2 GPUs): a few optimizer steps on a small Qwen3; prints one JSON
-line per rank-0 run with the per-step losses and a checksum of the LoRA parameters. tests/test_multigpu.py runs it
+line per rank-0 run with the per-step losses and a checksum of the LoRA parameters. tests/test_yy_multigpu.py runs it
 with the layer prefetcher on and off (and on 1 GPU) and compares."""
 import json, os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))

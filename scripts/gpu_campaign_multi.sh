@@ -14,5 +14,5 @@ echo "ddp2 rc=$?"; grep "^{" gpurun_out/minigpt2_n${N}.json; tail -2 gpurun_out/
 if [ "$N" = "2" ]; then
   timeout 200 $TR --master-port 29514 scripts/bench_infer_tp.py --batch 1 > gpurun_out/tp${N}_b1.json 2> gpurun_out/tp${N}_b1.err
   echo "tp b1 rc=$?"; cat gpurun_out/tp${N}_b1.json
-  timeout 300 python -m pytest tests/test_multigpu.py -x -q 2>&1 | tail -5
+  timeout 300 python -m pytest tests/test_yy_multigpu.py -x -q 2>&1 | tail -5
 fi

@@ -7,4 +7,4 @@ for b in 1 8; do
 done
 timeout 200 $TR --master-port 29543 scripts/bench_configs.py --config gptlike-ddp > gpurun_out/gptlike_n2.json 2> gpurun_out/gptlike_n2.err; echo "ddp rc=$?"; cat gpurun_out/gptlike_n2.json; tail -2 gpurun_out/gptlike_n2.err | cut -c1-300
 timeout 200 python scripts/bench_configs.py --config gptlike-ddp 2>/dev/null | tail -1
-timeout 400 python -m pytest tests/test_multigpu.py -x -q 2>&1 | tail -4
+timeout 400 python -m pytest tests/test_yy_multigpu.py -x -q 2>&1 | tail -4
