@@ -242,6 +242,9 @@ class _EmbeddingFn(torch.autograd.Function):
         nv.check(fn(nv.ptr(flat), nv.ptr(table), nv.ptr(pos_table), nv.ptr(out), flat.numel(), table.shape[1], period,
                     scale, nv.dtype_code(table.dtype), nv.stream()), "embedding_fwd")
         nv.count_launch()
+        if table.requires_grad:
+            from ..utils.arena import note_use
+            note_use(table, False)              # its gradient arrives through autograd (possibly after a tied head's)
         ctx.save_for_backward(flat)
         ctx.meta = (table.shape, table.dtype, pos_table is not None, period, scale,
                     None if pos_table is None else pos_table.shape)

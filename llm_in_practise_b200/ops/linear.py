@@ -30,6 +30,7 @@ from . import elementwise as ew
 from .gemm import gemm, gemm_w4, gemv16
 from .lora import lora_down, lora_dx, lora_wgrad
 from .w4 import NF4Weight
+from ..utils.arena import note_use
 
 _workspaces: Dict[Tuple[int, torch.dtype, int], torch.Tensor] = {}
 
@@ -56,6 +57,10 @@ class _LinearFn(torch.autograd.Function):
     def forward(ctx, x, w, bias, compute_dtype):
         wc = w if w.dtype == compute_dtype else w.to(compute_dtype)
         y = gemm(x, wc, bias=bias)
+        if w.requires_grad:
+            note_use(w, hasattr(w, "main_grad"))
+        if bias is not None and bias.requires_grad:
+            note_use(bias, hasattr(bias, "main_grad"))
         ctx.save_for_backward(x, w, bias)
         ctx.compute_dtype = compute_dtype
         return y

@@ -138,6 +138,11 @@ class _LinearCEFn(torch.autograd.Function):
         ctx.save_for_backward(dx, None if (in_place or not need_dw) else dw)
         ctx.pre = pre
         ctx.main_grad = w_main_grad if (need_dw and not in_place) else None
+        ctx.hook = None
+        if ctx.main_grad is not None:           # this op's backward adds into main_grad: one outstanding contribution
+            from ..utils.arena import note_use
+            note_use(w, True)
+            ctx.hook = getattr(w, "_grad_ready", None)
         ctx.w_dtype = w.dtype
         return loss_sum * inv
 
@@ -152,8 +157,10 @@ class _LinearCEFn(torch.autograd.Function):
                 ctx.main_grad.add_(dw * f)
             else:
                 gdw = (dw * f).to(ctx.w_dtype)
-        # no ``_grad_ready`` call here: a tied head still receives the embedding's contribution at the very end of
-        # backward, and DDP reduces buckets whose hooks never fired when backward finishes
+        # the in-place path put its contribution into main_grad during forward (nothing outstanding); the other one
+        # has just landed: tell the data-parallel wrapper (it waits for the remaining uses of a tied weight)
+        if ctx.hook is not None:
+            ctx.hook()
         return (gdx, gdw) + (None,) * 9
 
 

@@ -24,7 +24,7 @@ import torch
 import torch.distributed as dist
 from torch import nn
 
-from ..utils.arena import ParamArena, flatten_module
+from ..utils.arena import ParamArena, flatten_module, grad_landed, reset_uses
 from .dist import get_info
 from .symm import PeerFlags, SymmBuffer, allreduce_, symm_available
 
@@ -121,14 +121,14 @@ class DistributedDataParallel(nn.Module):
         for bi, bk in enumerate(self.buckets):
             for p in bk.params:
                 p._ddp_bucket = bi
-                p._grad_ready = (lambda pp=p: self._on_grad_ready(pp))
-                p.register_post_accumulate_grad_hook(lambda pp: self._on_grad_ready(pp))
+                p._grad_ready = (lambda pp=p: self._on_grad_ready(pp, True))
+                p.register_post_accumulate_grad_hook(lambda pp: self._on_grad_ready(pp, False))
 
     def _reset_buckets(self) -> None:
         for b in self.buckets:
             b.pending = set(id(p) for p in b.params)
             b.launched = False
-            b.ready = False
+            b.ready = not b.pending          # a bucket without parameters (padding) never blocks its successors
             b.work = None
         self._next_bucket = 0
 
@@ -146,7 +146,12 @@ class DistributedDataParallel(nn.Module):
         if self.mixed is not None:
             self.arena.fold()
 
-    def _on_grad_ready(self, p: nn.Parameter) -> None:
+    def _on_grad_ready(self, p: nn.Parameter, direct: bool = False) -> None:
+        """One contribution to ``p``'s gradient has landed (``direct``: written into ``main_grad`` by an op's backward;
+        otherwise accumulated by autograd). A parameter used several times in the forward — a tied embedding / lm_head —
+        is complete only after its last contribution (``utils.arena.note_use`` counts the uses during forward)."""
+        if not grad_landed(p, direct):
+            return
         if self.world == 1 or not self.require_sync:
             return
         if not self._callback_queued:
@@ -189,6 +194,7 @@ class DistributedDataParallel(nn.Module):
 
     def _finalize_backward(self) -> None:
         self._callback_queued = False
+        reset_uses(p for b in self.buckets for p in b.params)
         # buckets whose parameters never produced a gradient this step (unused / frozen paths) still need
         # their (zero) contribution reduced so every rank launches the same sequence of collectives
         for b in self.buckets:
@@ -224,6 +230,7 @@ class DistributedDataParallel(nn.Module):
 
     # ------------------------------------------------------------------ module surface
     def forward(self, *args, **kwargs):
+        reset_uses(p for b in self.buckets for p in b.params)      # use counts of a pass without backward (eval) are stale
         return self.module(*args, **kwargs)
 
     @contextlib.contextmanager

@@ -344,8 +344,8 @@ class FullyShardedDataParallel(nn.Module):
                 u.module.register_forward_hook(lambda m, a, o, uu=u: self._post_forward(uu))
                 u.module.register_full_backward_pre_hook(lambda m, g, uu=u: uu.prepare_backward())
             for p in u.params:
-                p._grad_ready = (lambda pp=p: self._on_grad(pp))
-                p.register_post_accumulate_grad_hook(lambda pp: self._on_grad(pp))
+                p._grad_ready = (lambda pp=p: self._on_grad(pp, True))
+                p.register_post_accumulate_grad_hook(lambda pp: self._on_grad(pp, False))
         self._cb_queued = False
 
     # ------------------------------------------------------------------ peer-memory collectives
@@ -420,7 +420,10 @@ class FullyShardedDataParallel(nn.Module):
         if self.strategy == ShardingStrategy.FULL_SHARD:
             u.reshard()
 
-    def _on_grad(self, p: nn.Parameter) -> None:
+    def _on_grad(self, p: nn.Parameter, direct: bool = False) -> None:
+        from ..utils.arena import grad_landed
+        if not grad_landed(p, direct):          # a tied weight: wait for its last contribution
+            return
         u: _Unit = p._fsdp_unit
         if not self._cb_queued:
             self._cb_queued = True
@@ -433,6 +436,8 @@ class FullyShardedDataParallel(nn.Module):
 
     def _finalize(self) -> None:
         self._cb_queued = False
+        from ..utils.arena import reset_uses
+        reset_uses(p for u in self.units for p in u.params)
         if not self.require_sync:
             for u in self.units:                 # no_sync: keep accumulating in the full fp32 buffers
                 for p in u.params:
@@ -454,6 +459,8 @@ class FullyShardedDataParallel(nn.Module):
             u.flush_offload()
 
     def forward(self, *args, **kwargs):
+        from ..utils.arena import reset_uses
+        reset_uses(p for u in self.units for p in u.params)        # use counts of a pass without backward (eval) are stale
         root = self.units[-1] if self.units and self.units[-1].module is self.module else None
         if root is not None:
             root.unshard()

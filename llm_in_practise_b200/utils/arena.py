@@ -99,6 +99,36 @@ class ParamArena:
         return iter(self._specs)
 
 
+def note_use(p, direct: bool) -> None:
+    """Called in the FORWARD of an op that will contribute to ``p``'s gradient (only while gradients are recorded).
+    A data-parallel wrapper must not reduce a parameter before its LAST contribution has landed, and a parameter can be
+    used more than once in a forward (tied embedding / lm_head): ``direct`` contributions are written into ``p.main_grad``
+    by the op's backward, which then calls ``p._grad_ready()``; the others arrive through autograd, whose accumulate hook
+    fires once after all of them. The wrappers (DDP / FSDP) count both kinds down in ``grad_landed``."""
+    if getattr(p, "_grad_ready", None) is None:
+        return
+    if direct:
+        p._uses_direct = getattr(p, "_uses_direct", 0) + 1
+    else:
+        p._uses_auto = 1
+
+
+def grad_landed(p, direct: bool) -> bool:
+    """One contribution to ``p``'s gradient has landed; True when none is outstanding."""
+    if direct:
+        if getattr(p, "_uses_direct", 0) > 0:
+            p._uses_direct -= 1
+    else:
+        p._uses_auto = 0
+    return getattr(p, "_uses_direct", 0) == 0 and getattr(p, "_uses_auto", 0) == 0
+
+
+def reset_uses(params) -> None:
+    for p in params:
+        p._uses_direct = 0
+        p._uses_auto = 0
+
+
 def flatten_module(module: nn.Module, dtype: Optional[torch.dtype] = None, device=None,
                    pad_to: int = 1, only_trainable: bool = True, alloc=None) -> ParamArena:
     """Re-home the (trainable) parameters of an arbitrary ``nn.Module`` into one arena, in

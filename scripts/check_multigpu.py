@@ -210,4 +210,6 @@ if cli.suite:
             print(json.dumps({"variant": name, **r}), flush=True)
 else:
     run_case(cli, cli.dump)
+sys.stdout.flush()
 cleanup_distributed()
+os._exit(0)      # the work is done and printed: skip interpreter teardown (symmetric-memory handles outliving the process group abort there)

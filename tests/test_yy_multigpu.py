@@ -66,6 +66,9 @@ def _suite(nproc, which, dump, port, env_extra=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), os.path.join(ROOT, "scripts", "check_multigpu.py"), "--suite", which, "--dump", dump]
     out = subprocess.run(cmd, capture_output=True, text=True, env=env, timeout=1500)
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    with open(os.path.join(ROOT, "gpurun_out", f"multigpu_suite_{which}_n{nproc}.log"), "w") as f:
+        f.write(out.stdout[-200000:] + "\n==== stderr ====\n" + out.stderr[-200000:])
     res = {}
     for ln in out.stdout.splitlines():
         if ln.startswith('{"variant"'):
