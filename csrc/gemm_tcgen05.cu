@@ -44,6 +44,7 @@ struct GemmKernelParams {
   int batch, nb0, b_div, nb0_b;
   long long d_rs, d_bs0, d_bs1;
   float alpha, beta;
+  const float* beta_rows;   // optional per-row beta (overrides `beta`)
   int out_dtype, bias_dtype;
   uint32_t idesc_main, idesc_lora;
   int num_m, num_n, num_k;  // num_m counts unit tiles (128 * CTAS rows); num_k = k-blocks of the main operands
@@ -148,7 +149,7 @@ __device__ __forceinline__ void umma_issue(uint32_t d, uint64_t a, uint64_t b, u
 
 template <typename OutT>
 __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* __restrict__ drow, int col0,
-                                               int col_limit, const uint32_t (&r)[32], bool row_ok) {
+                                               int col_limit, const uint32_t (&r)[32], bool row_ok, float beta) {
   // drow points at D[row, 0]; this thread owns columns col0 .. col0+31 (< col_limit) of its row.
   float v[32];
 #pragma unroll
@@ -172,13 +173,13 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
     constexpr int kPerVec = 16 / sizeof(OutT);
     constexpr int kVecs = 32 / kPerVec;
     uint4* dst = reinterpret_cast<uint4*>(drow + col0);
-    if (p.beta != 0.f) {
+    if (beta != 0.f) {
 #pragma unroll
       for (int i = 0; i < kVecs; ++i) {
         uint4 old = dst[i];
         const OutT* o = reinterpret_cast<const OutT*>(&old);
 #pragma unroll
-        for (int j = 0; j < kPerVec; ++j) v[i * kPerVec + j] += p.beta * to_f32<OutT>(o[j]);
+        for (int j = 0; j < kPerVec; ++j) v[i * kPerVec + j] += beta * to_f32<OutT>(o[j]);
       }
     }
 #pragma unroll
@@ -195,7 +196,7 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
       int c = col0 + j;
       if (c < col_limit) {
         float x = v[j];
-        if (p.beta != 0.f) x += p.beta * to_f32<OutT>(drow[c]);
+        if (beta != 0.f) x += beta * to_f32<OutT>(drow[c]);
         drow[c] = from_f32<OutT>(x);
       }
     }
@@ -594,6 +595,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       const uint32_t t0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * kAccStride;
       const int col_limit = min(p.N, n0 + p.bn);
       const int nchunks = (p.bn + 31) / 32;
+      const float beta = (p.beta_rows != nullptr && row_ok) ? p.beta_rows[row] : p.beta;
       if (sg.kb0 > 0) {
         // ---- stream-K contributor: publish this CTA's fp32 partial, the tile's owner finishes it ----
         float* slot = p.sk_ws + ((long long)blockIdx.x * kBM + (q * 32 + lane)) * kAccStride;
@@ -645,11 +647,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           }
         }
         if (p.out_dtype == B200_DT_BF16)
-          epilogue_store<__nv_bfloat16>(p, reinterpret_cast<__nv_bfloat16*>(p.D) + doff, col0, col_limit, r, row_ok);
+          epilogue_store<__nv_bfloat16>(p, reinterpret_cast<__nv_bfloat16*>(p.D) + doff, col0, col_limit, r, row_ok, beta);
         else if (p.out_dtype == B200_DT_FP32)
-          epilogue_store<float>(p, reinterpret_cast<float*>(p.D) + doff, col0, col_limit, r, row_ok);
+          epilogue_store<float>(p, reinterpret_cast<float*>(p.D) + doff, col0, col_limit, r, row_ok, beta);
         else
-          epilogue_store<__half>(p, reinterpret_cast<__half*>(p.D) + doff, col0, col_limit, r, row_ok);
+          epilogue_store<__half>(p, reinterpret_cast<__half*>(p.D) + doff, col0, col_limit, r, row_ok, beta);
       }
       }
       tc_fence_before();
@@ -825,6 +827,7 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   p.nb0_b = nb0 / b_div > 0 ? nb0 / b_div : 1;
   p.d_rs = a->d_rs; p.d_bs0 = a->d_bs0; p.d_bs1 = a->d_bs1;
   p.alpha = a->alpha; p.beta = a->beta;
+  p.beta_rows = (a->batch == 1) ? a->beta_rows : nullptr;
   p.out_dtype = a->out_dtype; p.bias_dtype = a->bias_dtype;
   p.a_mn = a->a_mn ? 1 : 0; p.b_mn = a->b_mn ? 1 : 0;
   p.num_k = ceil_div(a->K, EPR);
@@ -950,6 +953,7 @@ B200_API int b200_gemm_w4(const b200_gemm_args* a, const b200_w4_desc* w, void* 
   p.batch = 1; p.nb0 = 1; p.b_div = 1; p.nb0_b = 1;
   p.d_rs = a->d_rs; p.d_bs0 = 0; p.d_bs1 = 0;
   p.alpha = a->alpha; p.beta = a->beta;
+  p.beta_rows = (a->batch == 1) ? a->beta_rows : nullptr;
   p.out_dtype = a->out_dtype; p.bias_dtype = a->bias_dtype;
   p.a_mn = 0; p.b_mn = a->b_mn ? 1 : 0;
   p.num_k = a->K / EPR;

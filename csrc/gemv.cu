@@ -9,6 +9,7 @@
 // the model per step. That is the regime of the reference's serving table (concurrency 8..64,
 // LLM_on_Kubernetes/Inference_Platfrom/README.md:1504-1509), where a 128-row tensor-core tile would be >87 % padding.
 #include "common.cuh"
+#include "peer.cuh"
 #include "../include/b200_ops.h"
 
 #include <stdlib.h>
@@ -53,6 +54,16 @@ __device__ __forceinline__ uint4 ld_nc_v4(const void* ptr) {
   return r;
 }
 
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async4(void* smem, const void* gmem) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N_>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
+
 struct GemvParams {
   const uint16_t* x;      // [M, K] 16-bit activations
   const void* w;          // dense: uint16 [N, w_rs]; 4-bit: packed uint8 [N, K / 2]
@@ -64,6 +75,22 @@ struct GemvParams {
   int M, K, group, out_f32;
   float lin_a, lin_off;   // LIN: lut[code] = lin_a * (code - lin_off), lin_off an integer
   long long N, x_rs, w_rs, y_rs;
+  // ---- fused tail (fuse != 0): the product never goes to a y tensor of its own. Every CTA writes its 16-column tiles into
+  // a staging buffer (fuse 1: local; fuse 2: this rank's half of a symmetric buffer, tensor-parallel row-parallel layer),
+  // a ticket barrier closes the GEMV, (fuse 2) the epoch is published to the peers and theirs awaited, and CTA m then
+  // finishes token m: sum of the W ranks' partials (all-reduce, K-C5) + residual -> new residual, RMSNorm with the NEXT
+  // layer's weight -> its input. One launch instead of GEMV + all-reduce + residual/norm. Epoch and tickets live on the
+  // device (state[0..2]), so the launch replays from a CUDA graph.
+  int fuse, world, rank, channel;
+  PeerPtrs stage;             // 16-bit [2][half_elems] per rank (fuse 2) / stage.p[0] = local buffer (fuse 1)
+  PeerPtrs flags;
+  long long half_elems;
+  unsigned int* state;
+  const void* res_in;         // [M, N] 16-bit, may be null (first layer)
+  void* res_out;              // [M, N] 16-bit
+  const void* norm_w;         // [N] 16-bit, null: no norm, x_out receives the sum
+  void* x_out;                // [M, N] 16-bit
+  float eps;
 };
 
 // LIN (4-bit codes that are a linear function of the code, i.e. RTN / GPTQ / AWQ integers): no lookup table. A nibble is
@@ -72,7 +99,13 @@ struct GemvParams {
 // bound by the LSU pipe (profiles/decode_kernels_ncu.md). Nibbles are taken four pairs at a time from each 32-bit word
 // ((w >> 4 i) & 0x000F000F), which pairs elements (e, e + 4); the activations get the same pairing with two PRMTs per
 // word, so the k order inside an MMA is permuted consistently on both operands.
-template <bool BF16, bool W4, int TG, int MINB, bool LIN = false>
+// POST (LIN only, group a multiple of 128 so that a 128-wide chunk lies inside one scale group): the codes enter the MMA
+// as the exact 16-bit values (bias + code) — one logic op per pair of weights, no floating-point conversion at all — and
+// the affine map is applied to the chunk's fp32 partial sum instead:  sum_k w_k x_k = A_row * (sum_k (bias + c_k) x_k -
+// B_row * sum_k x_k), with sum_k x_k produced by one more MMA per k-step whose weight operand is the constant 1.0. That
+// replaces 32 packed FMAs per lane and chunk by 8 MMAs and 8 scalar FMAs: the kernel is bound by instruction issue,
+// not by HBM (3.5 instructions per weight before; profiles/r2/gemv.md).
+template <bool BF16, bool W4, int TG, int MINB, bool LIN = false, bool POST = false>
 __global__ void __launch_bounds__(256, MINB)
 gemv_mma_kernel(const GemvParams p) {
   extern __shared__ uint32_t table[];   // 4-bit table variant only: byte -> two 16-bit values, one column per lane (conflict-free)
@@ -92,46 +125,87 @@ gemv_mma_kernel(const GemvParams p) {
   const int g = lane >> 2, t = lane & 3;
   const int K = p.K, M = p.M;
   const long long N = p.N;
+  uint32_t epoch = 0;
+  void* ybase = p.y;
+  long long y_rs = p.y_rs;
+  if (p.fuse) {
+    epoch = *((volatile unsigned int*)p.state) + 1u;
+    const int me = p.fuse == 2 ? p.rank : 0;
+    ybase = reinterpret_cast<uint16_t*>(p.stage.p[me]) + (p.fuse == 2 ? (long long)(epoch & 1u) * p.half_elems : 0ll);
+    y_rs = N;
+  }
   const int gpr = W4 ? K / p.group : 0;
   const uint32_t* tl = table + lane;
   const int nchunks = K / 128;
   const long long ntiles = (N + 15) / 16;
-  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  // Work item = (16-row tile, batch of U chunks per warp). A CTA walks its items in order; for 4-bit weights the NEXT
+  // item's packed codes and scales are already on their way into shared memory (cp.async, one private 16-byte slot per
+  // thread and chunk-row: no barrier needed, a thread only ever reads what it requested itself) while the current item is
+  // expanded and multiplied. The previous structure (request a batch, wait, compute, next tile) left HBM idle during
+  // the compute phase and the tensor pipe idle during the load phase: 1.3-1.9 TB/s (profiles/r2/gemv.md).
+  constexpr int U = 4;
+  const int nb = (nchunks + 8 * U - 1) / (8 * U);
+  const long long my_tiles = blockIdx.x < ntiles ? (ntiles - 1 - blockIdx.x) / gridDim.x + 1 : 0;
+  const long long nitems = my_tiles * nb;
+  uint4* ring_w = reinterpret_cast<uint4*>(table + ((W4 && !LIN) ? 256 * 32 : 0));        // [2][2U][256] uint4
+  float* ring_s = reinterpret_cast<float*>(ring_w + 2 * 2 * U * 256);                      // [2][4U][256] float
+  auto issue = [&](long long it) {
+    if (W4) {
+      const long long tile_n = blockIdx.x + (it / nb) * gridDim.x;
+      const int ch0n = warp + (int)(it % nb) * 8 * U;
+      const long long rAn = min(tile_n * 16 + g, N - 1), rBn = min(tile_n * 16 + g + 8, N - 1);
+      const uint8_t* pk = reinterpret_cast<const uint8_t*>(p.w);
+      uint4* wb = ring_w + (it & 1) * (2 * U * 256) + threadIdx.x;
+      float* sb = ring_s + (it & 1) * (4 * U * 256) + threadIdx.x;
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int ch = ch0n + 8 * u;
+        if (ch < nchunks) {
+          const int k = ch * 128 + t * 32;
+          cp_async16(wb + (2 * u) * 256, pk + rAn * (K / 2) + k / 2);
+          cp_async16(wb + (2 * u + 1) * 256, pk + rBn * (K / 2) + k / 2);
+          cp_async4(sb + (4 * u) * 256, p.scale + rAn * gpr + k / p.group);
+          cp_async4(sb + (4 * u + 1) * 256, p.scale + rBn * gpr + k / p.group);
+          if (p.zs) {
+            cp_async4(sb + (4 * u + 2) * 256, p.zs + rAn * gpr + k / p.group);
+            cp_async4(sb + (4 * u + 3) * 256, p.zs + rBn * gpr + k / p.group);
+          }
+        }
+      }
+    }
+    cp_async_commit();
+  };
+  if (W4 && nitems > 0) issue(0);
+  float c[TG][4];
+  for (long long it = 0; it < nitems; ++it) {
+    const long long tile = blockIdx.x + (it / nb) * gridDim.x;
+    const int bidx = (int)(it % nb);
+    const int ch0 = warp + bidx * 8 * U;
     const long long row0 = tile * 16;
     const long long rA = min(row0 + g, N - 1), rB = min(row0 + g + 8, N - 1);
-    float c[TG][4];
+    if (bidx == 0) {
 #pragma unroll
-    for (int tg = 0; tg < TG; ++tg)
+      for (int tg = 0; tg < TG; ++tg)
 #pragma unroll
-      for (int i = 0; i < 4; ++i) c[tg][i] = 0.f;
-    // The warp's chunks are taken U at a time: all packed weights (and scales) of a batch are requested before any of
-    // them is used, so a batch costs ONE trip to DRAM instead of U dependent ones. With K = 4096 a warp has 4 chunks —
-    // one batch — and a tile is a single round trip; the loop-per-chunk version of this kernel ran at 14 % of the HBM
-    // bandwidth because every chunk waited for the previous one's data (profiles/gemv_linear_ncu.md).
-    constexpr int U = 4;
-    for (int ch0 = warp; ch0 < nchunks; ch0 += 8 * U) {
+        for (int i = 0; i < 4; ++i) c[tg][i] = 0.f;
+    }
+    {
       uint4 wqa[U], wqb[U];        // W4: 16 packed bytes of rows g / g+8 per chunk; dense: unused
       float sca[U], scb[U], zza[U], zzb[U];
       if (W4) {
-        const uint8_t* pk = reinterpret_cast<const uint8_t*>(p.w);
+        if (it + 1 < nitems) issue(it + 1); else cp_async_commit();     // (an empty group keeps the count uniform)
+        cp_async_wait<1>();
+        const uint4* wb = ring_w + (it & 1) * (2 * U * 256) + threadIdx.x;
+        const float* sb = ring_s + (it & 1) * (4 * U * 256) + threadIdx.x;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          const int ch = ch0 + 8 * u;
-          if (ch < nchunks) {
-            const int k = ch * 128 + t * 32;
-            wqa[u] = ld_nc_v4(pk + rA * (K / 2) + k / 2);
-            wqb[u] = ld_nc_v4(pk + rB * (K / 2) + k / 2);
-          }
-        }
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-          const int ch = ch0 + 8 * u;
-          if (ch < nchunks) {
-            const int k = ch * 128 + t * 32;
-            sca[u] = __ldg(p.scale + rA * gpr + k / p.group);
-            scb[u] = __ldg(p.scale + rB * gpr + k / p.group);
-            zza[u] = p.zs ? __ldg(p.zs + rA * gpr + k / p.group) : 0.f;
-            zzb[u] = p.zs ? __ldg(p.zs + rB * gpr + k / p.group) : 0.f;
+          if (ch0 + 8 * u < nchunks) {
+            wqa[u] = wb[(2 * u) * 256];
+            wqb[u] = wb[(2 * u + 1) * 256];
+            sca[u] = sb[(4 * u) * 256];
+            scb[u] = sb[(4 * u + 1) * 256];
+            zza[u] = p.zs ? sb[(4 * u + 2) * 256] : 0.f;
+            zzb[u] = p.zs ? sb[(4 * u + 3) * 256] : 0.f;
           }
         }
       }
@@ -147,7 +221,20 @@ gemv_mma_kernel(const GemvParams p) {
         const float za = zza[u], zb = zzb[u];
         const uint32_t sa2 = pack2<BF16>(sa, sa), sb2 = pack2<BF16>(sb, sb), za2 = pack2<BF16>(-za, -za), zb2 = pack2<BF16>(-zb, -zb);
         const uint32_t wA[4] = {wa.x, wa.y, wa.z, wa.w}, wB[4] = {wb.x, wb.y, wb.z, wb.w};
-        if (LIN) {
+        if (LIN && POST) {
+          constexpr uint32_t kMagic = BF16 ? 0x43004300u : 0x64006400u, kMask = 0x000F000Fu;
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {   // same (e0,e4) (e1,e5) (e2,e6) (e3,e7) register order as below, values left biased
+            aA[4 * q + 0] = ((wA[q] >> 4) & kMask) | kMagic;
+            aA[4 * q + 1] = (wA[q] & kMask) | kMagic;
+            aA[4 * q + 2] = ((wA[q] >> 12) & kMask) | kMagic;
+            aA[4 * q + 3] = ((wA[q] >> 8) & kMask) | kMagic;
+            aB[4 * q + 0] = ((wB[q] >> 4) & kMask) | kMagic;
+            aB[4 * q + 1] = (wB[q] & kMask) | kMagic;
+            aB[4 * q + 2] = ((wB[q] >> 12) & kMask) | kMagic;
+            aB[4 * q + 3] = ((wB[q] >> 8) & kMask) | kMagic;
+          }
+        } else if (LIN) {
           constexpr uint32_t kMagic = BF16 ? 0x43004300u : 0x64006400u, kMask = 0x000F000Fu;
           const float bias0 = (BF16 ? 128.f : 1024.f) + p.lin_off;
           const uint32_t one2 = pack2<BF16>(1.f, 1.f), neg2 = pack2<BF16>(-bias0, -bias0);
@@ -211,12 +298,31 @@ gemv_mma_kernel(const GemvParams p) {
             xw[4 * q + 3] = __byte_perm(x1, x3, 0x7632);
           }
         }
+        if (LIN && POST) {
+          constexpr uint32_t kOne2 = BF16 ? 0x3F803F80u : 0x3C003C00u;
+          float craw[4] = {0.f, 0.f, 0.f, 0.f}, csx[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          mma16816<BF16>(c[tg], aA[2 * j], aB[2 * j], aA[2 * j + 1], aB[2 * j + 1], xw[2 * j], xw[2 * j + 1]);
+          for (int j = 0; j < 8; ++j) {
+            mma16816<BF16>(craw, aA[2 * j], aB[2 * j], aA[2 * j + 1], aB[2 * j + 1], xw[2 * j], xw[2 * j + 1]);
+            mma16816<BF16>(csx, kOne2, kOne2, kOne2, kOne2, xw[2 * j], xw[2 * j + 1]);
+          }
+          // w = lin_a * (code - lin_off) * scale - zs = A * ((bias + code) - B),  A = lin_a * scale,  B = bias + lin_off + zs / A
+          const float bias0 = BF16 ? 128.f : 1024.f;
+          const float Aa = sca[u] * p.lin_a, Ab = scb[u] * p.lin_a;
+          const float Ba = bias0 + p.lin_off + (zza[u] != 0.f ? zza[u] / Aa : 0.f), Bb = bias0 + p.lin_off + (zzb[u] != 0.f ? zzb[u] / Ab : 0.f);
+          c[tg][0] += Aa * (craw[0] - Ba * csx[0]);
+          c[tg][1] += Aa * (craw[1] - Ba * csx[1]);
+          c[tg][2] += Ab * (craw[2] - Bb * csx[2]);
+          c[tg][3] += Ab * (craw[3] - Bb * csx[3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            mma16816<BF16>(c[tg], aA[2 * j], aB[2 * j], aA[2 * j + 1], aB[2 * j + 1], xw[2 * j], xw[2 * j + 1]);
+        }
       }
     }
     }
+    if (bidx != nb - 1) continue;
     // c0: (row g, token 2t), c1: (row g, token 2t+1), c2: (row g+8, token 2t), c3: (row g+8, token 2t+1) of the group
 #pragma unroll
     for (int tg = 0; tg < TG; ++tg) {
@@ -233,27 +339,136 @@ gemv_mma_kernel(const GemvParams p) {
         if (row < N && tok < M) {
           if (p.bias) s += BF16 ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[row])
                                 : __half2float(reinterpret_cast<const __half*>(p.bias)[row]);
-          if (p.out_f32) reinterpret_cast<float*>(p.y)[(long long)tok * p.y_rs + row] = s;
-          else if (BF16) reinterpret_cast<__nv_bfloat16*>(p.y)[(long long)tok * p.y_rs + row] = __float2bfloat16_rn(s);
-          else reinterpret_cast<__half*>(p.y)[(long long)tok * p.y_rs + row] = __float2half_rn(s);
+          if (p.out_f32 && !p.fuse) reinterpret_cast<float*>(ybase)[(long long)tok * y_rs + row] = s;
+          else if (BF16) reinterpret_cast<__nv_bfloat16*>(ybase)[(long long)tok * y_rs + row] = __float2bfloat16_rn(s);
+          else reinterpret_cast<__half*>(ybase)[(long long)tok * y_rs + row] = __float2half_rn(s);
         }
       }
       __syncthreads();   // `red` is reused by the next token group / tile
     }
   }
+  if (!p.fuse) return;
+  // ================= fused tail: (all-reduce +) residual + RMSNorm per token =================
+  __syncthreads();               // all of this CTA's tiles are written ...
+  if (threadIdx.x == 0) {
+    if (p.fuse == 2) __threadfence_system(); else __threadfence();   // ... and made visible (to the peers too) by ONE fence
+    const unsigned int old = atomicAdd(p.state + 1, 1u);
+    const unsigned int target = (old / gridDim.x + 1u) * gridDim.x;
+    const long long t0 = clock64();
+    while ((int)(*((volatile unsigned int*)(p.state + 1)) - target) < 0) {
+      if (clock64() - t0 > 20000000000ll) { printf("b200 gemv: fused-tail grid barrier timed out (block %d)\n", blockIdx.x); __trap(); }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+  const int W = p.fuse == 2 ? p.world : 1;
+  if (p.fuse == 2) {
+    if (blockIdx.x == 0) signal_all(p.flags, p.channel, W, p.rank, epoch);
+    if ((int)blockIdx.x < M) wait_all(p.flags, p.channel, W, p.rank, epoch);
+  }
+  {
+    float* redf = &red[0][0];
+    const int nvec = (int)(N / 8);
+    const long long hoff = p.fuse == 2 ? (long long)(epoch & 1u) * p.half_elems : 0ll;
+    for (int m = blockIdx.x; m < M; m += gridDim.x) {
+      // up to 4 vectors of 8 per thread (N <= 8192): the sums stay in registers between the two passes
+      float v[4][8];
+      float ss = 0.f;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int i = threadIdx.x + k * 256;
+        if (i < nvec) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[k][j] = 0.f;
+          for (int r = 0; r < W; ++r) {
+            const uint4 q = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.stage.p[p.fuse == 2 ? r : 0]) + hoff + (long long)m * N)[i];
+            const uint32_t w4[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float2 f;
+              if (BF16) f = unpack_bf16x2(w4[j]);
+              else f = __half22float2(*reinterpret_cast<const __half2*>(&w4[j]));
+              v[k][2 * j] += f.x; v[k][2 * j + 1] += f.y;
+            }
+          }
+          if (p.res_in) {
+            const uint4 q = reinterpret_cast<const uint4*>(reinterpret_cast<const uint16_t*>(p.res_in) + (long long)m * N)[i];
+            const uint32_t w4[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float2 f;
+              if (BF16) f = unpack_bf16x2(w4[j]);
+              else f = __half22float2(*reinterpret_cast<const __half2*>(&w4[j]));
+              v[k][2 * j] += f.x; v[k][2 * j + 1] += f.y;
+            }
+          }
+          // the hidden state is rounded to 16 bits first (what the stand-alone norm kernel does), then normalised
+          uint32_t o[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            o[j] = pack2<BF16>(v[k][2 * j], v[k][2 * j + 1]);
+            float2 f;
+            if (BF16) f = unpack_bf16x2(o[j]);
+            else f = __half22float2(*reinterpret_cast<const __half2*>(&o[j]));
+            v[k][2 * j] = f.x; v[k][2 * j + 1] = f.y;
+            ss += f.x * f.x + f.y * f.y;
+          }
+          if (p.res_out) reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.res_out) + (long long)m * N)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+          if (!p.norm_w) reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.x_out) + (long long)m * N)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+      }
+      if (p.norm_w) {
+        ss = block_sum(ss, redf);
+        const float rstd = rsqrtf(ss / (float)N + p.eps);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int i = threadIdx.x + k * 256;
+          if (i < nvec) {
+            const uint4 q = reinterpret_cast<const uint4*>(p.norm_w)[i];
+            const uint32_t w4[4] = {q.x, q.y, q.z, q.w};
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float2 f;
+              if (BF16) f = unpack_bf16x2(w4[j]);
+              else f = __half22float2(*reinterpret_cast<const __half2*>(&w4[j]));
+              o[j] = pack2<BF16>(v[k][2 * j] * rstd * f.x, v[k][2 * j + 1] * rstd * f.y);
+            }
+            reinterpret_cast<uint4*>(reinterpret_cast<uint16_t*>(p.x_out) + (long long)m * N)[i] = make_uint4(o[0], o[1], o[2], o[3]);
+          }
+        }
+        __syncthreads();
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    const unsigned int tkt = atomicAdd(p.state + 2, 1u);
+    if (tkt == gridDim.x - 1) {
+      p.state[2] = 0u;
+      __threadfence();
+      *((volatile unsigned int*)p.state) = epoch;   // the next fused launch (stream order) sees the new epoch
+    }
+  }
 }
 
-template <bool BF16, bool W4, int TG, int MINB, bool LIN = false>
+template <bool BF16, bool W4, int TG, int MINB, bool LIN = false, bool POST = false>
 static cudaError_t launch_gemv_one(const GemvParams& p, cudaStream_t st) {
   // persistent over 16-row tiles: one resident wave (occupancy x SMs), never more CTAs than tiles
   static int occ = 0;
-  const int smem = (W4 && !LIN) ? 256 * 32 * 4 : 0;
+  // 4-bit: [table 32 KB (non-linear code book only)] + prefetch ring: 2 x (8 x 256 x 16 B codes + 16 x 256 x 4 B scales) = 96 KB
+  const int smem = W4 ? ((LIN ? 0 : 256 * 32 * 4) + 2 * (2 * 4 * 256 * 16 + 4 * 4 * 256 * 4)) : 0;
+  static bool attr_done = false;
+  if (!attr_done && smem > 48 * 1024) {
+    cudaFuncSetAttribute(gemv_mma_kernel<BF16, W4, TG, MINB, LIN, POST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+    attr_done = true;
+  }
   if (!occ) {
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gemv_mma_kernel<BF16, W4, TG, MINB, LIN>, 256, smem) != cudaSuccess || occ < 1) occ = 1;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gemv_mma_kernel<BF16, W4, TG, MINB, LIN, POST>, 256, smem) != cudaSuccess || occ < 1) occ = 1;
   }
   const long long tiles = (p.N + 15) / 16;
   const unsigned grid = (unsigned)(tiles < (long long)kNumSMs * occ ? tiles : (long long)kNumSMs * occ);
-  return launch_pdl(gemv_mma_kernel<BF16, W4, TG, MINB, LIN>, grid, 256, smem, st, p);
+  return launch_pdl(gemv_mma_kernel<BF16, W4, TG, MINB, LIN, POST>, grid, 256, smem, st, p);
 }
 
 template <bool BF16>
@@ -261,6 +476,14 @@ static int launch_gemv_lin(const GemvParams& p, cudaStream_t st) {
   cudaError_t e;
   // 2 CTAs per SM (128 registers, no spills): with 4 chunks x 2 rows x 16 B requested up front per lane that is 64 KB in
   // flight per SM, above the ~44 KB that 6.5 TB/s x ~1 us of DRAM latency asks of each of the 148 SMs
+  static const bool post_off = [] { const char* e = getenv("B200_GEMV_POST"); return e && atoi(e) == 0; }();
+  if (p.group % 128 == 0 && !post_off) {   // scale applied to the chunk sums (see POST above)
+    if (p.M <= 8) e = launch_gemv_one<BF16, true, 1, 2, true, true>(p, st);
+    else if (p.M <= 16) e = launch_gemv_one<BF16, true, 2, 2, true, true>(p, st);
+    else if (p.M <= 32) e = launch_gemv_one<BF16, true, 4, 2, true, true>(p, st);
+    else e = launch_gemv_one<BF16, true, 8, 1, true, true>(p, st);
+    return (int)e;
+  }
   if (p.M <= 8) e = launch_gemv_one<BF16, true, 1, 2, true>(p, st);
   else if (p.M <= 16) e = launch_gemv_one<BF16, true, 2, 2, true>(p, st);
   else if (p.M <= 32) e = launch_gemv_one<BF16, true, 4, 2, true>(p, st);
@@ -324,5 +547,37 @@ B200_API int b200_w4_gemv_linear(const void* x, const uint8_t* packed, const flo
   p.lin_a = lin_a; p.lin_off = lin_off;
   if (dtype == B200_DT_BF16) return launch_gemv_lin<true>(p, (cudaStream_t)stream);
   if (dtype == B200_DT_FP16) return launch_gemv_lin<false>(p, (cudaStream_t)stream);
+  return B200_ERR_UNSUPPORTED;
+}
+
+// Row-parallel / plain projection with the fused tail (see GemvParams::fuse): kind 0 dense 16-bit weights, 1 4-bit codes
+// through the 16-entry table (NF4), 2 4-bit integer codes (GPTQ / AWQ / RTN). world == 1: residual + norm only.
+B200_API int b200_gemv_fused(const b200_gemv_fused_args* a, void* stream) {
+  if (!a || a->M < 1 || a->M > 64 || a->K % 128 || a->x_rs % 8 || a->N % 8 || a->N > 8192) return B200_ERR_BAD_SHAPE;
+  if (a->world < 1 || a->world > kMaxRanks || !a->state || !a->stage_ptrs || !a->x_out) return B200_ERR_BAD_SHAPE;
+  if (a->world > 1 && (!a->flag_ptrs || a->half_elems < (long long)a->M * a->N || a->half_elems % 8)) return B200_ERR_BAD_SHAPE;
+  if (a->kind != 0 && (a->group % 32 || a->K % a->group)) return B200_ERR_BAD_SHAPE;
+  GemvParams p = {};
+  p.x = (const uint16_t*)a->x; p.w = a->w; p.scale = a->scale; p.zs = a->zs; p.lut = a->lut; p.bias = a->bias; p.y = nullptr;
+  p.M = a->M; p.K = a->K; p.N = a->N; p.x_rs = a->x_rs; p.w_rs = a->w_rs; p.y_rs = a->N; p.out_f32 = 0;
+  p.group = a->kind == 0 ? 128 : a->group;
+  p.lin_a = a->lin_a; p.lin_off = a->lin_off;
+  p.fuse = a->world > 1 ? 2 : 1;
+  p.world = a->world; p.rank = a->rank; p.channel = a->channel;
+  for (int i = 0; i < kMaxRanks; ++i) {
+    p.stage.p[i] = i < a->world ? const_cast<void*>(a->stage_ptrs[i]) : nullptr;
+    p.flags.p[i] = (a->flag_ptrs && i < a->world) ? const_cast<void*>(a->flag_ptrs[i]) : nullptr;
+  }
+  p.half_elems = a->half_elems; p.state = a->state;
+  p.res_in = a->res_in; p.res_out = a->res_out; p.norm_w = a->norm_w; p.x_out = a->x_out; p.eps = a->eps;
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool bf = a->dtype == B200_DT_BF16;
+  if (!bf && a->dtype != B200_DT_FP16) return B200_ERR_UNSUPPORTED;
+  if (a->kind == 0) return bf ? launch_gemv<true, false>(p, st) : launch_gemv<false, false>(p, st);
+  if (a->kind == 1) return bf ? launch_gemv<true, true>(p, st) : launch_gemv<false, true>(p, st);
+  if (a->kind == 2) {
+    if (a->lin_off != (float)(int)a->lin_off || a->lin_off < -64.f || a->lin_off > 64.f) return B200_ERR_UNSUPPORTED;
+    return bf ? launch_gemv_lin<true>(p, st) : launch_gemv_lin<false>(p, st);
+  }
   return B200_ERR_UNSUPPORTED;
 }

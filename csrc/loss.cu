@@ -136,6 +136,115 @@ softmax_bwd_kernel(const TP* __restrict__ P, const TG* __restrict__ dP, TO* __re
     o[c] = from_f32<TO>(to_f32<TP>(p[c]) * (to_f32<TG>(g[c]) - dot) * scale);
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// K8 as a vocabulary-chunked, flash-attention-style reduction: the lm_head GEMM produces one [rows, C] chunk of logits at
+// a time (C = 8192 columns: 32 MB for 2048 rows, it stays in the 126 MB L2 between its GEMM and these kernels), so no
+// [tokens, vocab] tensor ever exists.
+//   ce_chunk_online  per row: m' = max(m, max_c l); alpha = exp(m - m'); l <- p = exp(l - m') in place; s = s * alpha + sum p;
+//                    the target's logit is captured when it falls in this chunk. With write_p = 0 only the statistics are
+//                    updated (first pass of the two-pass variant for a trainable head).
+//                    The caller then accumulates acc = alpha[row] * acc + p @ W_chunk (GEMM with per-row beta): after the
+//                    last chunk acc / s = softmax(l) @ W, i.e. dL/dx up to the one-hot term — ONE pass over the vocabulary.
+//   ce_chunk_grad    second pass of the two-pass variant: l <- (exp(l - lse) - [col == target]) * scale[row] in place.
+//   ce_online_finish loss[row] = m + log s - l_target;  dx[row] = (acc[row] / s - W[target]) * scale[row].
+// ---------------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(kCEThreads)
+ce_chunk_online_kernel(T* __restrict__ lg, long long row_stride, int C, int c0, const long long* __restrict__ targets,
+                       long long ignore_index, float* __restrict__ m_run, float* __restrict__ s_run,
+                       float* __restrict__ tgt_logit, float* __restrict__ alpha_out, int write_p) {
+  constexpr int V = 16 / sizeof(T);
+  __shared__ float red[32];
+  const long long row = blockIdx.x;
+  T* lr = lg + row * row_stride;
+  const int nvec = C / V;                       // C % V == 0 (the host pads the chunk width)
+  float cm = -INFINITY;
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(lr + (long long)i * V);
+    const T* e = reinterpret_cast<const T*>(&raw);
+#pragma unroll
+    for (int j = 0; j < V; ++j) cm = fmaxf(cm, to_f32<T>(e[j]));
+  }
+  cm = block_max(cm, red);
+  const float m_old = m_run[row];
+  const float m_new = fmaxf(m_old, cm);
+  const long long tgt = targets[row];
+  if (threadIdx.x == 0 && tgt != ignore_index && tgt >= c0 && tgt < c0 + C) tgt_logit[row] = to_f32<T>(lr[tgt - c0]);
+  __syncthreads();                               // the target logit is read before the row is overwritten
+  float sum = 0.f;
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(lr + (long long)i * V);
+    const T* e = reinterpret_cast<const T*>(&raw);
+    uint4 out;
+    T* o = reinterpret_cast<T*>(&out);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const float pj = __expf(to_f32<T>(e[j]) - m_new);
+      o[j] = from_f32<T>(pj);
+      sum += write_p ? to_f32<T>(o[j]) : pj;     // the sum uses the rounded p that the GEMM will see
+    }
+    if (write_p) *reinterpret_cast<uint4*>(lr + (long long)i * V) = out;
+  }
+  sum = block_sum(sum, red);
+  if (threadIdx.x == 0) {
+    const float a = (m_old == -INFINITY) ? 0.f : __expf(m_old - m_new);
+    s_run[row] = s_run[row] * a + sum;
+    m_run[row] = m_new;
+    if (alpha_out) alpha_out[row] = a;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kCEThreads)
+ce_chunk_grad_kernel(T* __restrict__ lg, long long row_stride, int C, int c0, const long long* __restrict__ targets,
+                     long long ignore_index, const float* __restrict__ m_run, const float* __restrict__ s_run,
+                     const float* __restrict__ row_scale, float grad_scale) {
+  constexpr int V = 16 / sizeof(T);
+  const long long row = blockIdx.x;
+  T* lr = lg + row * row_stride;
+  const long long tgt = targets[row];
+  const bool ignored = tgt == ignore_index;
+  const float lse = m_run[row] + __logf(s_run[row]);
+  const float gsc = ignored ? 0.f : grad_scale * (row_scale ? row_scale[row] : 1.f);
+  const int nvec = C / V;
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 raw = *reinterpret_cast<const uint4*>(lr + (long long)i * V);
+    const T* e = reinterpret_cast<const T*>(&raw);
+    uint4 out;
+    T* o = reinterpret_cast<T*>(&out);
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      float pj = __expf(to_f32<T>(e[j]) - lse);
+      if ((long long)(c0 + i * V + j) == tgt) pj -= 1.f;
+      o[j] = from_f32<T>(pj * gsc);
+    }
+    *reinterpret_cast<uint4*>(lr + (long long)i * V) = out;
+  }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+ce_online_finish_kernel(const float* __restrict__ acc, long long acc_rs, const T* __restrict__ W, long long w_rs, int K,
+                        const long long* __restrict__ targets, long long ignore_index, const float* __restrict__ m_run,
+                        const float* __restrict__ s_run, const float* __restrict__ tgt_logit,
+                        const float* __restrict__ row_scale, float grad_scale, T* __restrict__ dx, long long dx_rs,
+                        float* __restrict__ loss_rows) {
+  const long long row = blockIdx.x;
+  const long long tgt = targets[row];
+  const bool ignored = tgt == ignore_index;
+  const float s = s_run[row];
+  if (threadIdx.x == 0) loss_rows[row] = ignored ? 0.f : (m_run[row] + __logf(s) - tgt_logit[row]);
+  if (dx == nullptr) return;
+  const float gsc = ignored ? 0.f : grad_scale * (row_scale ? row_scale[row] : 1.f);
+  const float inv = 1.f / s;
+  const float* ar = acc + row * acc_rs;
+  const T* wr = W + (ignored ? 0 : tgt) * w_rs;
+  T* dr = dx + row * dx_rs;
+  for (int k = threadIdx.x; k < K; k += blockDim.x)
+    dr[k] = from_f32<T>((ar[k] * inv - to_f32<T>(wr[k])) * gsc);
+}
+
 }  // namespace b200
 using namespace b200;
 
@@ -201,6 +310,59 @@ B200_API int b200_softmax_bwd(const void* P, const void* dP, void* dS, long long
     softmax_bwd_kernel<__nv_bfloat16, __nv_bfloat16, __nv_bfloat16><<<grid, 256, 0, st>>>((const __nv_bfloat16*)P, (const __nv_bfloat16*)dP, (__nv_bfloat16*)dS, cols, scale);
   else
     return B200_ERR_UNSUPPORTED;
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+// dtype: 16-bit logits chunk [rows, C] with row stride row_stride (elements); C % 8 == 0 (pad the chunk; padded columns must
+// hold -inf / a large negative so that they contribute exp() = 0). m_run must start at -inf, s_run at 0.
+B200_API int b200_ce_chunk_online(void* lg, long long rows, long long row_stride, int C, int c0, const long long* targets,
+                                  long long ignore_index, float* m_run, float* s_run, float* tgt_logit, float* alpha_out,
+                                  int write_p, int dtype, void* stream) {
+  if (rows <= 0 || C <= 0 || C % 8 || (row_stride * 2) % 16 || (reinterpret_cast<uintptr_t>(lg) & 15)) return B200_ERR_BAD_SHAPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_DT_BF16)
+    ce_chunk_online_kernel<__nv_bfloat16><<<(unsigned)rows, kCEThreads, 0, st>>>((__nv_bfloat16*)lg, row_stride, C, c0, targets,
+                                                                                 ignore_index, m_run, s_run, tgt_logit, alpha_out, write_p);
+  else if (dtype == B200_DT_FP16)
+    ce_chunk_online_kernel<__half><<<(unsigned)rows, kCEThreads, 0, st>>>((__half*)lg, row_stride, C, c0, targets, ignore_index,
+                                                                          m_run, s_run, tgt_logit, alpha_out, write_p);
+  else return B200_ERR_UNSUPPORTED;
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_ce_chunk_grad(void* lg, long long rows, long long row_stride, int C, int c0, const long long* targets,
+                                long long ignore_index, const float* m_run, const float* s_run, const float* row_scale,
+                                float grad_scale, int dtype, void* stream) {
+  if (rows <= 0 || C <= 0 || C % 8 || (row_stride * 2) % 16) return B200_ERR_BAD_SHAPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_DT_BF16)
+    ce_chunk_grad_kernel<__nv_bfloat16><<<(unsigned)rows, kCEThreads, 0, st>>>((__nv_bfloat16*)lg, row_stride, C, c0, targets,
+                                                                               ignore_index, m_run, s_run, row_scale, grad_scale);
+  else if (dtype == B200_DT_FP16)
+    ce_chunk_grad_kernel<__half><<<(unsigned)rows, kCEThreads, 0, st>>>((__half*)lg, row_stride, C, c0, targets, ignore_index,
+                                                                        m_run, s_run, row_scale, grad_scale);
+  else return B200_ERR_UNSUPPORTED;
+  B200_LAUNCH_CHECK();
+  return 0;
+}
+
+B200_API int b200_ce_online_finish(const float* acc, long long acc_rs, const void* W, long long w_rs, int K,
+                                   const long long* targets, long long ignore_index, const float* m_run, const float* s_run,
+                                   const float* tgt_logit, const float* row_scale, float grad_scale, void* dx, long long dx_rs,
+                                   float* loss_rows, long long rows, int dtype, void* stream) {
+  if (rows <= 0) return B200_ERR_BAD_SHAPE;
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dtype == B200_DT_BF16)
+    ce_online_finish_kernel<__nv_bfloat16><<<(unsigned)rows, 256, 0, st>>>(acc, acc_rs, (const __nv_bfloat16*)W, w_rs, K, targets,
+                                                                           ignore_index, m_run, s_run, tgt_logit, row_scale,
+                                                                           grad_scale, (__nv_bfloat16*)dx, dx_rs, loss_rows);
+  else if (dtype == B200_DT_FP16)
+    ce_online_finish_kernel<__half><<<(unsigned)rows, 256, 0, st>>>(acc, acc_rs, (const __half*)W, w_rs, K, targets, ignore_index,
+                                                                    m_run, s_run, tgt_logit, row_scale, grad_scale, (__half*)dx,
+                                                                    dx_rs, loss_rows);
+  else return B200_ERR_UNSUPPORTED;
   B200_LAUNCH_CHECK();
   return 0;
 }

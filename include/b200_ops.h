@@ -72,6 +72,9 @@ typedef struct {
    * computed by one CTA / CTA pair. */
   void* workspace;
   int64_t workspace_bytes;
+  /* Optional per-row beta (float[M], batch 1 only): D[m, :] = alpha * acc + beta_rows[m] * D[m, :]. The running
+   * rescale of the online-softmax lm_head + cross-entropy (flash-attention style accumulation over vocabulary chunks). */
+  const float* beta_rows;
 } b200_gemm_args;
 
 long long b200_gemm_workspace_bytes(void);
@@ -169,6 +172,19 @@ int b200_cross_entropy(void* logits, const long long* targets, float* loss_rows,
 int b200_cross_entropy_rows(void* logits, const long long* targets, float* loss_rows, float* lse_rows, long long rows,
                             int vocab, long long row_stride, long long ignore_index, float grad_scale, int write_grad,
                             const float* row_scale, int dtype, void* stream);
+/* K8, vocabulary-chunked (no [tokens, vocab] tensor): online-softmax statistics / probabilities of one chunk of logits,
+ * the gradient of one chunk once the row log-sum-exp is known, and the closing kernel of the single-pass variant
+ * (dx = (acc / s - W[target]) * scale). See csrc/loss.cu and ops/loss.py (linear_cross_entropy). */
+int b200_ce_chunk_online(void* lg, long long rows, long long row_stride, int C, int c0, const long long* targets,
+                         long long ignore_index, float* m_run, float* s_run, float* tgt_logit, float* alpha_out,
+                         int write_p, int dtype, void* stream);
+int b200_ce_chunk_grad(void* lg, long long rows, long long row_stride, int C, int c0, const long long* targets,
+                       long long ignore_index, const float* m_run, const float* s_run, const float* row_scale,
+                       float grad_scale, int dtype, void* stream);
+int b200_ce_online_finish(const float* acc, long long acc_rs, const void* W, long long w_rs, int K,
+                          const long long* targets, long long ignore_index, const float* m_run, const float* s_run,
+                          const float* tgt_logit, const float* row_scale, float grad_scale, void* dx, long long dx_rs,
+                          float* loss_rows, long long rows, int dtype, void* stream);
 int b200_softmax_fwd(const void* S, void* P, long long batch, int rows, int cols, int causal, int window, float scale,
                      int in_dtype, int out_dtype, void* stream);
 int b200_softmax_bwd(const void* P, const void* dP, void* dS, long long total_rows, int cols, float scale,
@@ -338,6 +354,22 @@ int b200_w4_gemv_batched(const void* x, const uint8_t* packed, const float* scal
 int b200_w4_gemv_linear(const void* x, const uint8_t* packed, const float* scale, const float* zs, const void* bias, void* y,
                         int M, long long N, int K, int group, long long x_rs, long long y_rs, float lin_a, float lin_off,
                         int dtype, void* stream);
+
+/* K-C5 (decode flavour): a small-M projection whose launch also does what follows it in a decoder layer — the
+ * tensor-parallel all-reduce of the row-parallel partial products (each rank writes its tiles into its half of a
+ * symmetric 16-bit staging buffer, publishes an epoch to the peers over NVLink and sums everyone's partials), the
+ * residual add and the RMSNorm that feeds the next projection. world == 1: residual + norm only (stage_ptrs[0] is a
+ * local [M, N] buffer). kind: 0 dense 16-bit weights, 1 4-bit codes via table (NF4), 2 4-bit integer codes (lin_a,
+ * lin_off). state: 4 zero-initialised uint32 on the device (epoch + tickets; graph-replayable). N % 8 == 0, N <= 8192,
+ * M <= 64. Replaces vLLM's row-parallel linear + custom all-reduce + fused_add_rms_norm sequence that the reference
+ * reaches with --tensor-parallel-size (Quantization/README.md:175). */
+typedef struct {
+  const void* x; const void* w; const float* scale; const float* zs; const float* lut; const void* bias;
+  int kind, M; long long N; int K, group; long long x_rs, w_rs; float lin_a, lin_off; int dtype;
+  int world, rank, channel; const void* const* stage_ptrs; const void* const* flag_ptrs; long long half_elems;
+  unsigned int* state; const void* res_in; void* res_out; const void* norm_w; void* x_out; float eps;
+} b200_gemv_fused_args;
+int b200_gemv_fused(const b200_gemv_fused_args* a, void* stream);
 
 /* ---- gradient fold (csrc/elementwise.cu) -------------------------------------------------------
  * y (fp32) += scale * x (bf16/fp16), optionally clearing x: folds the low-precision .grad autograd produced for

@@ -24,6 +24,7 @@ import torch
 
 from ..ops import _native as nv
 from ..ops import elementwise as ew
+from ..ops import fused_decode
 from ..ops.attention import attention
 from ..ops.gemm import ensure_graph_workspace, gemm, gemv16
 from ..ops.norm import rms_norm
@@ -224,6 +225,29 @@ class Generator:
         graph.replay()
         return st["logits"][:n]
 
+    def _fused_tail(self, x: torch.Tensor):
+        """The fused-tail context (staging buffer + device state) when every o_proj / down_proj of the model can take the
+        fused launch for this batch, else None. ``B200_FUSED_DECODE=0`` turns it off (A/B timing)."""
+        if os.environ.get("B200_FUSED_DECODE", "1") == "0" or not x.is_cuda:
+            return None
+        m = self.model
+        hid = self.cfg.hidden_size
+        ok = getattr(self, "_fused_ok", None)
+        if ok is None:
+            l0 = m.layers[0]
+            ok = (m.norm.dtype == x.dtype and l0.input_layernorm.dtype == x.dtype and
+                  all(fused_decode.supported(getattr(l, n), x[:1], hid) for l in m.layers for n in ("o_proj", "down_proj")))
+            self._fused_ok = ok
+        if not ok or x.shape[0] > fused_decode.MAX_TOKENS:
+            return None
+        if getattr(self, "_tail", None) is None:
+            tp = getattr(m, "tp", None)
+            if tp is not None and tp.world > 1 and not getattr(tp, "fused", False):
+                self._fused_ok = False
+                return None
+            self._tail = fused_decode.FusedTail(hid, x.device, tp if (tp is not None and tp.world > 1) else None, x.dtype)
+        return self._tail
+
     @torch.no_grad()
     def _decode(self, tok: torch.Tensor, cache: KVCache, pos: Optional[torch.Tensor] = None,
                 slots: Optional[torch.Tensor] = None) -> torch.Tensor:
@@ -237,13 +261,27 @@ class Generator:
         if pos is None:
             pos = torch.full((B,), cache.len, device=dev, dtype=torch.int32)
         delta, res = ew.embedding(tok.reshape(-1), m.embed_tokens), None
-        for li, layer in enumerate(m.layers):
-            x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
-            qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
-            ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5, slots)
-            x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
-            delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
-        h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)
+        tail = self._fused_tail(delta)
+        if tail is not None:
+            # o_proj / down_proj run as ONE launch each with the tensor-parallel all-reduce, the residual add and the next
+            # RMSNorm in their tail (ops/fused_decode.py): 7 launches per layer instead of 10 (12 under TP)
+            layers = m.layers
+            x, res = rms_norm(delta, layers[0].input_layernorm, c.rms_norm_eps, None)
+            for li, layer in enumerate(layers):
+                qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
+                ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5, slots)
+                x, res = fused_decode.gemv_fused(layer.o_proj, ctx, res, layer.post_attention_layernorm, c.rms_norm_eps, tail)
+                nw = layers[li + 1].input_layernorm if li + 1 < len(layers) else m.norm
+                x, res = fused_decode.gemv_fused(layer.down_proj, ew.swiglu(layer.gate_up_proj(x)), res, nw, c.rms_norm_eps, tail)
+            h = x
+        else:
+            for li, layer in enumerate(m.layers):
+                x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
+                qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
+                ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5, slots)
+                x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
+                delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
+            h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)
         cache.len += 1
         logits = gemv16(h, m.head_weight(), out_dtype=torch.float32)
         return logits if logits is not None else gemm(h, m.head_weight(), out_dtype=torch.float32)

@@ -121,6 +121,7 @@ class GemmArgs(ctypes.Structure):
         ("a_mn", ctypes.c_int32), ("b_mn", ctypes.c_int32), ("in_dtype", ctypes.c_int32), ("out_dtype", ctypes.c_int32),
         ("alpha", ctypes.c_float), ("beta", ctypes.c_float),
         ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_int64),
+        ("beta_rows", ctypes.c_void_p),
     ]
 
 

@@ -42,8 +42,24 @@ def ensure_graph_workspace(device: torch.device) -> None:
         _sk_workspaces[key] = torch.zeros(int(fn()), dtype=torch.uint8, device=device)
 
 
+_overlapped_collectives = 0
+
+
+def overlapped_collectives(active: bool) -> None:
+    """Called by the wrappers that run a peer-memory collective kernel on a side stream WHILE compute continues (DDP
+    bucket all-reduce, FSDP reduce-scatter). Such a kernel spins on flags and has a grid barrier, i.e. it needs all of
+    its CTAs resident; a stream-K GEMM needs all of ITS CTAs resident too (tile owners wait for the partial sums of
+    other CTAs). Two kernels of that kind pending on one GPU can each get only part of their CTAs placed and then wait
+    for each other forever (seen as "stream-K wait timed out" in the 2-GPU DDP suite). While any such wrapper is alive,
+    GEMMs therefore run one CTA pair per tile (no cross-CTA dependency: their CTAs always drain)."""
+    global _overlapped_collectives
+    _overlapped_collectives = max(0, _overlapped_collectives + (1 if active else -1))
+
+
 def _stream_k_workspace(device: torch.device) -> Optional[torch.Tensor]:
     """Per (device, stream) scratch for stream-K GEMMs: zeroed once, then owned by that stream."""
+    if _overlapped_collectives:
+        return None
     if torch.cuda.is_current_stream_capturing():
         return _sk_workspaces.get((device.index, "graph"))       # None: captured without stream-K
     key = (device.index, torch.cuda.current_stream(device).cuda_stream)
@@ -88,8 +104,10 @@ def _ref_gemm(a, b, a_mn, b_mn, out, out_dtype, alpha, beta, bias, lora):
 def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
          out: Optional[torch.Tensor] = None, out_dtype: Optional[torch.dtype] = None,
          alpha: float = 1.0, beta: float = 0.0, bias: Optional[torch.Tensor] = None,
-         lora: Optional[Tuple[torch.Tensor, torch.Tensor]] = None) -> torch.Tensor:
-    """See module docstring. ``a``/``b`` are the *stored* tensors (last dim contiguous); leading dims
+         lora: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
+         beta_rows: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``beta_rows`` (float32 [M], 2-D problems): per-row beta, ``out[m] = alpha * acc[m] + beta_rows[m] * out[m]``.
+    See module docstring. ``a``/``b`` are the *stored* tensors (last dim contiguous); leading dims
     (up to two) are batch dims with arbitrary strides; ``b`` may have fewer batch entries in its
     inner batch dim (an integer divisor: grouped-query attention)."""
     if a.dtype != b.dtype:
@@ -99,6 +117,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     if beta != 0.0 and out is None:
         raise ValueError("beta != 0 needs `out`")
     if not nv.use_native(a):
+        if beta_rows is not None:
+            prev = out.float() * beta_rows.float().unsqueeze(-1)
+            res = _ref_gemm(a, b, a_mn, b_mn, None, torch.float32, alpha, 0.0, bias, lora) + prev
+            out.copy_(res.to(out.dtype))
+            return out
         return _ref_gemm(a, b, a_mn, b_mn, out, out_dtype, alpha, beta, bias, lora)
 
     if a.dtype == torch.float32 and (a_mn or b_mn):
@@ -154,6 +177,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     args.a_mn, args.b_mn = int(a_mn), int(b_mn)
     args.in_dtype, args.out_dtype = nv.dtype_code(a.dtype), nv.dtype_code(out.dtype)
     args.alpha, args.beta = alpha, beta
+    args.beta_rows = 0 if beta_rows is None else beta_rows.data_ptr()
     keep = None
     if lora is not None:
         a2, b2 = lora
@@ -296,7 +320,7 @@ def gemm_w4(a: torch.Tensor, q, *, b_mn: bool = False, out: Optional[torch.Tenso
         args.A2, args.B2, args.K2 = a2.data_ptr(), b2.data_ptr(), a2.shape[-1]
         args.a2_rs, args.b2_rs = a2.stride(0), b2.stride(0)
     ws = _stream_k_workspace(a.device)
-    args.workspace, args.workspace_bytes = ws.data_ptr(), ws.numel()
+    args.workspace, args.workspace_bytes = (ws.data_ptr(), ws.numel()) if ws is not None else (0, 0)
     fn = nv.proto("b200_gemm_w4", [ctypes.POINTER(nv.GemmArgs), ctypes.POINTER(W4Desc), ctypes.c_void_p])
     rc = fn(ctypes.byref(args), ctypes.byref(d), nv.stream())
     if rc == 10006:      # B200_ERR_UNSUPPORTED_: shape outside the fused kernel's domain

@@ -103,6 +103,80 @@ class grad_scale_context:
         return False
 
 
+_VOCAB_CHUNK = int(__import__("os").environ.get("B200_CE_VOCAB_CHUNK", "8192"))
+_VOCAB_CHUNK_MIN_BYTES = int(__import__("os").environ.get("B200_CE_VOCAB_MIN_MB", "64")) << 20
+
+
+def _vocab_chunked(x, w, t, ignore_index, row_scale, gscale, need_dx, dw):
+    """lm_head + CE over vocabulary chunks of ``_VOCAB_CHUNK`` columns (csrc/loss.cu, K8). The [M, C] chunk of logits
+    (32 MB for 2048 tokens x 8192 columns) lives in L2 between its GEMM and the kernels that consume it.
+
+    Frozen head (``dw is None``): ONE pass, flash-attention style — per chunk the kernel turns the logits into
+    p = exp(l - running max) and returns the row rescale alpha; ``acc = alpha * acc + p @ W_chunk`` runs as a GEMM with
+    a per-row beta; at the end ``dx = (acc / sum - W[target]) * scale``. Same two GEMMs as the materialising version.
+    Trainable / tied head: pass 1 collects the row statistics only, pass 2 recomputes each chunk, turns it into
+    d loss / d logits and feeds ``dx += dl @ W_chunk`` and ``dW_chunk += dl^T @ x`` (one extra lm_head GEMM)."""
+    M, K = x.shape
+    V = w.shape[0]
+    C = min(_VOCAB_CHUNK, (V + 7) // 8 * 8)
+    dev = x.device
+    dt = nv.dtype_code(x.dtype)
+    buf = torch.empty(M, C, dtype=x.dtype, device=dev)
+    m_run = torch.full((M,), float("-inf"), dtype=torch.float32, device=dev)
+    s_run = torch.zeros(M, dtype=torch.float32, device=dev)
+    tgt = torch.zeros(M, dtype=torch.float32, device=dev)
+    loss_rows = torch.empty(M, dtype=torch.float32, device=dev)
+    f_on = nv.proto("b200_ce_chunk_online", [vp, i64, i64, i32, i32, vp, i64, vp, vp, vp, vp, i32, i32, vp])
+    f_gr = nv.proto("b200_ce_chunk_grad", [vp, i64, i64, i32, i32, vp, i64, vp, vp, vp, f32, i32, vp])
+    f_fin = nv.proto("b200_ce_online_finish", [vp, i64, vp, i64, i32, vp, i64, vp, vp, vp, vp, f32, vp, i64, vp, i64, i32, vp])
+    chunks = [(c0, min(V, c0 + C)) for c0 in range(0, V, C)]
+
+    def logits(c0, c1):
+        cw = c1 - c0
+        if cw < C:
+            buf[:, cw:].fill_(float("-inf"))             # padded columns contribute exp() = 0
+        gemm(x, w[c0:c1], out=buf[:, :cw])
+        return cw
+
+    def online(c0, alpha, write_p):
+        nv.check(f_on(nv.ptr(buf), M, buf.stride(0), C, c0, nv.ptr(t), ignore_index, nv.ptr(m_run), nv.ptr(s_run), nv.ptr(tgt),
+                      None if alpha is None else nv.ptr(alpha), int(write_p), dt, nv.stream()), "ce_chunk_online")
+        nv.count_launch()
+
+    dx = None
+    if dw is None:
+        acc = torch.zeros(M, K, dtype=torch.float32, device=dev) if need_dx else None
+        alpha = torch.empty(M, dtype=torch.float32, device=dev)
+        for c0, c1 in chunks:
+            cw = logits(c0, c1)
+            online(c0, alpha, need_dx)
+            if need_dx:
+                gemm(buf[:, :cw], w[c0:c1], b_mn=True, out=acc, beta_rows=alpha)
+        if need_dx:
+            dx = torch.empty_like(x)
+        nv.check(f_fin(None if acc is None else nv.ptr(acc), K, nv.ptr(w), w.stride(0), K, nv.ptr(t), ignore_index, nv.ptr(m_run),
+                       nv.ptr(s_run), nv.ptr(tgt), nv.ptr(row_scale), gscale, None if dx is None else nv.ptr(dx), K,
+                       nv.ptr(loss_rows), M, dt, nv.stream()), "ce_online_finish")
+        nv.count_launch()
+    else:
+        for c0, c1 in chunks:
+            logits(c0, c1)
+            online(c0, None, False)
+        loss_rows = torch.where(t != ignore_index, m_run + torch.log(s_run) - tgt, torch.zeros_like(tgt))
+        acc = torch.zeros(M, K, dtype=torch.float32, device=dev) if need_dx else None
+        for c0, c1 in chunks:
+            cw = logits(c0, c1)
+            nv.check(f_gr(nv.ptr(buf), M, buf.stride(0), C, c0, nv.ptr(t), ignore_index, nv.ptr(m_run), nv.ptr(s_run),
+                          nv.ptr(row_scale), gscale, dt, nv.stream()), "ce_chunk_grad")
+            nv.count_launch()
+            if need_dx:
+                gemm(buf[:, :cw], w[c0:c1], b_mn=True, out=acc, beta=1.0)
+            gemm(buf[:, :cw], x, a_mn=True, b_mn=True, out=dw[c0:c1], beta=1.0)
+        if need_dx:
+            dx = acc.to(x.dtype)
+    return torch.dot(loss_rows, row_scale), dx
+
+
 class _LinearCEFn(torch.autograd.Function):
     """loss = mean CE(x @ w^T). Gradients are formed in forward (scaled by 1/n_valid, and by the declared upstream
     scale when there is one) and multiplied by the (remaining) upstream factor in backward."""
@@ -115,13 +189,26 @@ class _LinearCEFn(torch.autograd.Function):
         ld = (V + 7) // 8 * 8  # padded leading dimension keeps every logits row 16-byte aligned
         pre = 1.0 if declared is None else float(declared)     # folded into the gradients formed here
         inv = 1.0 if row_scale is not None else 1.0 / max(n_valid, 1)   # row_scale already holds the normalisation
-        dx = torch.empty_like(x) if need_dx else None
         dw = None
         in_place = need_dw and w_main_grad is not None and declared is not None
         if need_dw:
             dw = w_main_grad if in_place else torch.zeros(V, K, dtype=torch.float32, device=x.device)
-        loss_sum = torch.zeros((), dtype=torch.float32, device=x.device)
         t = targets.reshape(-1).contiguous()
+        if row_scale is not None and M * V * x.element_size() > _VOCAB_CHUNK_MIN_BYTES:
+            # vocabulary-chunked: no [tokens, vocab] tensor; one pass for a frozen head, two for a trainable one
+            loss, dx = _vocab_chunked(x, w, t, ignore_index, row_scale, inv * pre, need_dx, dw)
+            ctx.save_for_backward(dx, None if (in_place or not need_dw) else dw)
+            ctx.pre = pre
+            ctx.main_grad = w_main_grad if (need_dw and not in_place) else None
+            ctx.hook = None
+            if ctx.main_grad is not None:
+                from ..utils.arena import note_use
+                note_use(w, True)
+                ctx.hook = getattr(w, "_grad_ready", None)
+            ctx.w_dtype = w.dtype
+            return loss
+        dx = torch.empty_like(x) if need_dx else None
+        loss_sum = torch.zeros((), dtype=torch.float32, device=x.device)
         chunk = min(chunk_tokens, M)
         buf = torch.empty(chunk, ld, dtype=x.dtype, device=x.device)
         for s in range(0, M, chunk):

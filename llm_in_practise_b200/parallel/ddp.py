@@ -74,6 +74,8 @@ class DistributedDataParallel(nn.Module):
             self.grad_buf = self._bufs[1]
             self.flags = PeerFlags(dev)
             self.comm_stream = torch.cuda.Stream(device=dev)
+            from ..ops.gemm import overlapped_collectives
+            overlapped_collectives(True)        # collective kernels will overlap GEMMs: no stream-K (see ops/gemm.py)
         elif dev.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=dev)
         else:

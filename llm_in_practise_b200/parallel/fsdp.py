@@ -300,6 +300,8 @@ class FullyShardedDataParallel(nn.Module):
         if self.use_symm:
             from .symm import PeerFlags
             self.flags = PeerFlags(dev)
+            from ..ops.gemm import overlapped_collectives
+            overlapped_collectives(True)        # collective kernels will overlap GEMMs: no stream-K (see ops/gemm.py)
         if mixed_precision and mixed_precision.buffer_dtype:
             for b in module.buffers():
                 if b.is_floating_point():

@@ -40,13 +40,27 @@ torch.manual_seed(3)
 ref = Qwen3ForCausalLM(small, dtype=torch.bfloat16, device=dev, init_std=0.05)
 quantize_all(ref)
 ids = torch.randint(0, 1024, (2, 40), device=dev, generator=torch.Generator(device=dev).manual_seed(5))
+def decode_logits(model):
+    """prefill 40 tokens, then 3 decode steps through the (fused-tail) decode path: logits of the last step"""
+    g = Generator(model, max_len=64)
+    cache = KVCache(small.num_hidden_layers, 2, model.config.num_key_value_heads, 64, small.head_dim, torch.bfloat16, dev)
+    lg = g._prefill(ids, cache)
+    for _ in range(3):
+        lg = g._decode(lg.argmax(-1).reshape(-1), cache)
+    return lg.float()
+
+
 with torch.no_grad():
     want = ref(ids)["logits"].float()
+    want_dec = decode_logits(ref)
 tp = shard_qwen3(ref, max_tokens=a.batch * a.prompt)
 with torch.no_grad():
     got = ref(ids)["logits"].float()
+    got_dec = decode_logits(ref)
 err = float((got - want).abs().max() / want.abs().max())
 assert err < 3e-2, f"TP logits differ: {err}"
+err_dec = float((got_dec - want_dec).abs().max() / want_dec.abs().max())
+assert err_dec < 5e-2, f"TP decode logits differ: {err_dec}"
 del ref
 torch.cuda.empty_cache()
 
@@ -104,7 +118,7 @@ with torch.no_grad():
     t_decode = timed(decode_run, 2) / a.gen
 if rank == 0:
     print(json.dumps({"model": a.model + (f" ({a.layers} layers)" if a.layers else ""), "quant": "W4A16 RTN g128 sym (random-init)", "tp": world,
-                      "batch": B, "prompt_len": S, "gen_len": a.gen, "tp_logits_rel_err_small_model": err,
+                      "batch": B, "prompt_len": S, "gen_len": a.gen, "tp_logits_rel_err_small_model": err, "tp_decode_logits_rel_err_small_model": err_dec,
                       "prefill_ms": round(t_prefill, 3), "prefill_tokens_per_s": round(B * S / t_prefill * 1e3, 1),
                       "tpot_ms": round(t_decode, 3), "decode_tokens_per_s": round(B / t_decode * 1e3, 1),
                       "allreduce": "nvlink-peer-fused" if (tp.world > 1 and tp.fused) else ("none" if tp.world == 1 else "nccl")}))

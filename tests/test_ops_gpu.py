@@ -141,6 +141,35 @@ def test_linear_cross_entropy():
     assert rel(x.grad, x32.grad) < 3e-2 and rel(w.grad, w32.grad) < 3e-2
 
 
+@pytest.mark.parametrize("trainable_head", [False, True])
+def test_linear_cross_entropy_vocab_chunked(trainable_head, monkeypatch):
+    """K8 without a [tokens, vocab] tensor: one online-softmax pass for a frozen head (per-row-beta GEMM accumulation),
+    two passes for a trainable one; vocabulary 20011 (not a multiple of the chunk nor of 8), per-row weights, ignored rows."""
+    monkeypatch.setattr(L, "_VOCAB_CHUNK", 4096)
+    monkeypatch.setattr(L, "_VOCAB_CHUNK_MIN_BYTES", 0)
+    M, K, V = 300, 256, 20011
+    x = torch.randn(M, K, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    w = (torch.randn(V, K, device=DEV) / 16).bfloat16().requires_grad_(trainable_head)
+    t = torch.randint(0, V, (M,), device=DEV)
+    t[:10] = -100
+    t[10] = V - 1                                   # a target in the last, partial chunk
+    rs = L.micro_batch_row_scale(t, 2)
+    torch.cuda.reset_peak_memory_stats()
+    base = torch.cuda.memory_allocated()
+    loss = L.linear_cross_entropy(x, w, t, row_scale=rs)
+    loss.backward()
+    peak = torch.cuda.max_memory_allocated() - base
+    assert peak < M * V * 2, "a [tokens, vocab] tensor was allocated"
+    x32, w32 = x.detach().float().requires_grad_(), w.detach().float().requires_grad_(trainable_head)
+    rows = F.cross_entropy(x32 @ w32.t(), t, ignore_index=-100, reduction="none")
+    ref = torch.dot(rows, rs)
+    ref.backward()
+    assert abs(loss.item() - ref.item()) < 5e-3 * abs(ref.item())
+    assert rel(x.grad, x32.grad) < 3e-2
+    if trainable_head:
+        assert rel(w.grad, w32.grad) < 3e-2
+
+
 def test_linear_cross_entropy_main_grad_scaling_and_eval():
     """A head weight with a flat-arena ``main_grad``: evaluation under no_grad leaves it untouched, a declared upstream
     scale (engines: 1 / grad_accum) is folded into what forward accumulates, and an undeclared ``(loss * c).backward()``
@@ -404,3 +433,34 @@ def test_small_m_gemv_kernels(M, dtype):
         wd2 = W4.w4_dequant(packed, scale, zs, N_, K, 128, tbl, dtype)
         assert rel(y2, x.float() @ wd2.float().t()) < 1e-2
     assert W4.linear_lut(lut - 8) == (1.0, 8.0) and W4.linear_lut(lut.flip(0).contiguous() * 0.5) == (-0.5, 15.0)
+
+
+@pytest.mark.parametrize("kind", ["dense", "nf4", "int4"])
+@pytest.mark.parametrize("M", [1, 8, 33])
+def test_gemv_fused_tail_matches_separate_ops(kind, M):
+    """b200_gemv_fused at TP 1: projection + residual add + RMSNorm in one launch vs the fp32 torch expression."""
+    from llm_in_practise_b200.ops import fused_decode as FD
+    from llm_in_practise_b200.ops.linear import FusedLinear
+    torch.manual_seed(5)
+    K, N = 1024, 2048
+    lin = FusedLinear(K, [("o_proj", N)], dtype=torch.bfloat16, device=DEV, init_std=0.05)
+    wref = lin.weight.data.float().clone()
+    if kind == "nf4":
+        lin.quantize_nf4(True)
+        wref = lin.nf4.dequantize(torch.float32).float()
+    elif kind == "int4":
+        from llm_in_practise_b200.quant.formats import quantize_rtn
+        q = quantize_rtn(lin.weight.data, 128, True)
+        lin.set_nf4(q)
+        wref = W4._w4_dequant_ref(q.packed, q.scale, q.zs, N, K, 128, q._lut(), torch.float32)
+    x = torch.randn(M, K, device=DEV).bfloat16()
+    res = torch.randn(M, N, device=DEV).bfloat16()
+    nw = (1 + 0.1 * torch.randn(N, device=DEV)).bfloat16()
+    assert FD.supported(lin, x, N)
+    tail = FD.FusedTail(N, torch.device(DEV))
+    for rep in range(2):            # the second call starts from the first one's epoch / tickets
+        out, res_out = FD.gemv_fused(lin, x, res, nw, 1e-6, tail)
+    h = (x.float() @ wref.t()).bfloat16().float() + res.float()
+    hb = h.bfloat16().float()
+    want = hb * torch.rsqrt(hb.pow(2).mean(-1, keepdim=True) + 1e-6) * nw.float()
+    assert rel(res_out, hb) < 2e-2 and rel(out, want) < 2e-2
