@@ -64,6 +64,14 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N_>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
 
+// (a & b) | c in ONE instruction: with b and c as immediates the compiler splits it into two LOP3s (the expansion of the
+// codes is 22 % of all issued instructions of this kernel, profiles/r2/gemv.md)
+__device__ __forceinline__ uint32_t and_or(uint32_t a, uint32_t b, uint32_t c) {
+  uint32_t d;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+  return d;
+}
+
 struct GemvParams {
   const uint16_t* x;      // [M, K] 16-bit activations
   const void* w;          // dense: uint16 [N, w_rs]; 4-bit: packed uint8 [N, K / 2]
@@ -73,6 +81,7 @@ struct GemvParams {
   const void* bias;       // 16-bit, may be null
   void* y;                // [M, y_rs] 16-bit or fp32
   int M, K, group, out_f32;
+  int gshift;             // log2(group) when it is a power of two, else -1
   float lin_a, lin_off;   // LIN: lut[code] = lin_a * (code - lin_off), lin_off an integer
   long long N, x_rs, w_rs, y_rs;
   // ---- fused tail (fuse != 0): the product never goes to a y tensor of its own. Every CTA writes its 16-column tiles into
@@ -125,6 +134,17 @@ gemv_mma_kernel(const GemvParams p) {
   const int g = lane >> 2, t = lane & 3;
   const int K = p.K, M = p.M;
   const long long N = p.N;
+  // activations -> shared memory once per CTA (the host sized the allocation; 16-byte padded rows)
+  const bool xsm = (long long)M * (K + 8) * 2 <= 73728;
+  uint16_t* xs = reinterpret_cast<uint16_t*>(table + ((W4 && !LIN) ? 256 * 32 : 0));
+  if (xsm) {
+    const int vpr = K / 8;
+    for (int i = threadIdx.x; i < M * vpr; i += 256) {
+      const int r = i / vpr, cvec = i - r * vpr;
+      *reinterpret_cast<uint4*>(xs + (long long)r * (K + 8) + cvec * 8) = __ldg(reinterpret_cast<const uint4*>(p.x + (long long)r * p.x_rs) + cvec);
+    }
+    __syncthreads();
+  }
   uint32_t epoch = 0;
   void* ybase = p.y;
   long long y_rs = p.y_rs;
@@ -138,44 +158,14 @@ gemv_mma_kernel(const GemvParams p) {
   const uint32_t* tl = table + lane;
   const int nchunks = K / 128;
   const long long ntiles = (N + 15) / 16;
-  // Work item = (16-row tile, batch of U chunks per warp). A CTA walks its items in order; for 4-bit weights the NEXT
-  // item's packed codes and scales are already on their way into shared memory (cp.async, one private 16-byte slot per
-  // thread and chunk-row: no barrier needed, a thread only ever reads what it requested itself) while the current item is
-  // expanded and multiplied. The previous structure (request a batch, wait, compute, next tile) left HBM idle during
-  // the compute phase and the tensor pipe idle during the load phase: 1.3-1.9 TB/s (profiles/r2/gemv.md).
-  constexpr int U = 4;
+  // Work item = (16-row tile, batch of U chunks per warp). All packed weights (and scales) of an item are requested
+  // before any of them is used, so an item costs ONE trip to DRAM instead of U dependent ones; the activations come from
+  // shared memory (staged once per CTA when they fit), so the only long-latency operation left inside an item is that
+  // one trip. (A cp.async prefetch ring in shared memory was measured 1.5x SLOWER than this: profiles/r2/gemv.md.)
+  constexpr int U = MINB >= 3 ? 1 : 4;     // 3-4 CTAs per SM (<= 80 registers): one chunk at a time, occupancy hides the latency
   const int nb = (nchunks + 8 * U - 1) / (8 * U);
   const long long my_tiles = blockIdx.x < ntiles ? (ntiles - 1 - blockIdx.x) / gridDim.x + 1 : 0;
   const long long nitems = my_tiles * nb;
-  uint4* ring_w = reinterpret_cast<uint4*>(table + ((W4 && !LIN) ? 256 * 32 : 0));        // [2][2U][256] uint4
-  float* ring_s = reinterpret_cast<float*>(ring_w + 2 * 2 * U * 256);                      // [2][4U][256] float
-  auto issue = [&](long long it) {
-    if (W4) {
-      const long long tile_n = blockIdx.x + (it / nb) * gridDim.x;
-      const int ch0n = warp + (int)(it % nb) * 8 * U;
-      const long long rAn = min(tile_n * 16 + g, N - 1), rBn = min(tile_n * 16 + g + 8, N - 1);
-      const uint8_t* pk = reinterpret_cast<const uint8_t*>(p.w);
-      uint4* wb = ring_w + (it & 1) * (2 * U * 256) + threadIdx.x;
-      float* sb = ring_s + (it & 1) * (4 * U * 256) + threadIdx.x;
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int ch = ch0n + 8 * u;
-        if (ch < nchunks) {
-          const int k = ch * 128 + t * 32;
-          cp_async16(wb + (2 * u) * 256, pk + rAn * (K / 2) + k / 2);
-          cp_async16(wb + (2 * u + 1) * 256, pk + rBn * (K / 2) + k / 2);
-          cp_async4(sb + (4 * u) * 256, p.scale + rAn * gpr + k / p.group);
-          cp_async4(sb + (4 * u + 1) * 256, p.scale + rBn * gpr + k / p.group);
-          if (p.zs) {
-            cp_async4(sb + (4 * u + 2) * 256, p.zs + rAn * gpr + k / p.group);
-            cp_async4(sb + (4 * u + 3) * 256, p.zs + rBn * gpr + k / p.group);
-          }
-        }
-      }
-    }
-    cp_async_commit();
-  };
-  if (W4 && nitems > 0) issue(0);
   float c[TG][4];
   for (long long it = 0; it < nitems; ++it) {
     const long long tile = blockIdx.x + (it / nb) * gridDim.x;
@@ -193,19 +183,28 @@ gemv_mma_kernel(const GemvParams p) {
       uint4 wqa[U], wqb[U];        // W4: 16 packed bytes of rows g / g+8 per chunk; dense: unused
       float sca[U], scb[U], zza[U], zzb[U];
       if (W4) {
-        if (it + 1 < nitems) issue(it + 1); else cp_async_commit();     // (an empty group keeps the count uniform)
-        cp_async_wait<1>();
-        const uint4* wb = ring_w + (it & 1) * (2 * U * 256) + threadIdx.x;
-        const float* sb = ring_s + (it & 1) * (4 * U * 256) + threadIdx.x;
+        const uint8_t* pa0 = reinterpret_cast<const uint8_t*>(p.w) + rA * (K / 2) + t * 16;
+        const uint8_t* pb0 = reinterpret_cast<const uint8_t*>(p.w) + rB * (K / 2) + t * 16;
+        const float* sa0 = p.scale + rA * gpr;
+        const float* sb0 = p.scale + rB * gpr;
 #pragma unroll
         for (int u = 0; u < U; ++u) {
-          if (ch0 + 8 * u < nchunks) {
-            wqa[u] = wb[(2 * u) * 256];
-            wqb[u] = wb[(2 * u + 1) * 256];
-            sca[u] = sb[(4 * u) * 256];
-            scb[u] = sb[(4 * u + 1) * 256];
-            zza[u] = p.zs ? sb[(4 * u + 2) * 256] : 0.f;
-            zzb[u] = p.zs ? sb[(4 * u + 3) * 256] : 0.f;
+          const int ch = ch0 + 8 * u;
+          if (ch < nchunks) {
+            wqa[u] = ld_nc_v4(pa0 + ch * 64);
+            wqb[u] = ld_nc_v4(pb0 + ch * 64);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int ch = ch0 + 8 * u;
+          if (ch < nchunks) {
+            const int k = ch * 128 + t * 32;
+            const int gi = p.gshift >= 0 ? (k >> p.gshift) : (k / p.group);
+            sca[u] = __ldg(sa0 + gi);
+            scb[u] = __ldg(sb0 + gi);
+            zza[u] = p.zs ? __ldg(p.zs + rA * gpr + gi) : 0.f;
+            zzb[u] = p.zs ? __ldg(p.zs + rB * gpr + gi) : 0.f;
           }
         }
       }
@@ -222,17 +221,18 @@ gemv_mma_kernel(const GemvParams p) {
         const uint32_t sa2 = pack2<BF16>(sa, sa), sb2 = pack2<BF16>(sb, sb), za2 = pack2<BF16>(-za, -za), zb2 = pack2<BF16>(-zb, -zb);
         const uint32_t wA[4] = {wa.x, wa.y, wa.z, wa.w}, wB[4] = {wb.x, wb.y, wb.z, wb.w};
         if (LIN && POST) {
-          constexpr uint32_t kMagic = BF16 ? 0x43004300u : 0x64006400u, kMask = 0x000F000Fu;
+          uint32_t kMagic = BF16 ? 0x43004300u : 0x64006400u, kMask = 0x000F000Fu;
+          asm volatile("" : "+r"(kMagic), "+r"(kMask));      // keep both in registers (one LOP3 per pair of codes)
 #pragma unroll
           for (int q = 0; q < 4; ++q) {   // same (e0,e4) (e1,e5) (e2,e6) (e3,e7) register order as below, values left biased
-            aA[4 * q + 0] = ((wA[q] >> 4) & kMask) | kMagic;
-            aA[4 * q + 1] = (wA[q] & kMask) | kMagic;
-            aA[4 * q + 2] = ((wA[q] >> 12) & kMask) | kMagic;
-            aA[4 * q + 3] = ((wA[q] >> 8) & kMask) | kMagic;
-            aB[4 * q + 0] = ((wB[q] >> 4) & kMask) | kMagic;
-            aB[4 * q + 1] = (wB[q] & kMask) | kMagic;
-            aB[4 * q + 2] = ((wB[q] >> 12) & kMask) | kMagic;
-            aB[4 * q + 3] = ((wB[q] >> 8) & kMask) | kMagic;
+            aA[4 * q + 0] = and_or(wA[q] >> 4, kMask, kMagic);
+            aA[4 * q + 1] = and_or(wA[q], kMask, kMagic);
+            aA[4 * q + 2] = and_or(wA[q] >> 12, kMask, kMagic);
+            aA[4 * q + 3] = and_or(wA[q] >> 8, kMask, kMagic);
+            aB[4 * q + 0] = and_or(wB[q] >> 4, kMask, kMagic);
+            aB[4 * q + 1] = and_or(wB[q], kMask, kMagic);
+            aB[4 * q + 2] = and_or(wB[q] >> 12, kMask, kMagic);
+            aB[4 * q + 3] = and_or(wB[q] >> 8, kMask, kMagic);
           }
         } else if (LIN) {
           constexpr uint32_t kMagic = BF16 ? 0x43004300u : 0x64006400u, kMask = 0x000F000Fu;
@@ -278,10 +278,11 @@ gemv_mma_kernel(const GemvParams p) {
         const int tok = tg * 8 + g;
         uint32_t xw[16];
         if (tok < M) {
-          const uint4* xp = reinterpret_cast<const uint4*>(p.x + (long long)tok * p.x_rs + k);
+          const uint4* xp = xsm ? reinterpret_cast<const uint4*>(xs + (long long)tok * (K + 8) + k)
+                                : reinterpret_cast<const uint4*>(p.x + (long long)tok * p.x_rs + k);
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            const uint4 v = __ldg(xp + i);
+            const uint4 v = xsm ? xp[i] : __ldg(xp + i);
             xw[4 * i] = v.x; xw[4 * i + 1] = v.y; xw[4 * i + 2] = v.z; xw[4 * i + 3] = v.w;
           }
         } else {
@@ -300,24 +301,35 @@ gemv_mma_kernel(const GemvParams p) {
         }
         if (LIN && POST) {
           constexpr uint32_t kOne2 = BF16 ? 0x3F803F80u : 0x3C003C00u;
+          // two independent accumulator chains per sum (a chain of 8 dependent MMAs costs ~8 x 33 cycles of latency)
           float craw[4] = {0.f, 0.f, 0.f, 0.f}, csx[4] = {0.f, 0.f, 0.f, 0.f};
+          float craw2[4] = {0.f, 0.f, 0.f, 0.f}, csx2[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
+          for (int j = 0; j < 8; j += 2) {
             mma16816<BF16>(craw, aA[2 * j], aB[2 * j], aA[2 * j + 1], aB[2 * j + 1], xw[2 * j], xw[2 * j + 1]);
+            mma16816<BF16>(craw2, aA[2 * j + 2], aB[2 * j + 2], aA[2 * j + 3], aB[2 * j + 3], xw[2 * j + 2], xw[2 * j + 3]);
             mma16816<BF16>(csx, kOne2, kOne2, kOne2, kOne2, xw[2 * j], xw[2 * j + 1]);
+            mma16816<BF16>(csx2, kOne2, kOne2, kOne2, kOne2, xw[2 * j + 2], xw[2 * j + 3]);
           }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) { craw[i] += craw2[i]; csx[i] += csx2[i]; }
           // w = lin_a * (code - lin_off) * scale - zs = A * ((bias + code) - B),  A = lin_a * scale,  B = bias + lin_off + zs / A
           const float bias0 = BF16 ? 128.f : 1024.f;
           const float Aa = sca[u] * p.lin_a, Ab = scb[u] * p.lin_a;
-          const float Ba = bias0 + p.lin_off + (zza[u] != 0.f ? zza[u] / Aa : 0.f), Bb = bias0 + p.lin_off + (zzb[u] != 0.f ? zzb[u] / Ab : 0.f);
+          const float Ba = bias0 + p.lin_off + __fdividef(zza[u], Aa), Bb = bias0 + p.lin_off + __fdividef(zzb[u], Ab);
           c[tg][0] += Aa * (craw[0] - Ba * csx[0]);
           c[tg][1] += Aa * (craw[1] - Ba * csx[1]);
           c[tg][2] += Ab * (craw[2] - Bb * csx[2]);
           c[tg][3] += Ab * (craw[3] - Bb * csx[3]);
         } else {
+          float c2[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-          for (int j = 0; j < 8; ++j)
+          for (int j = 0; j < 8; j += 2) {
             mma16816<BF16>(c[tg], aA[2 * j], aB[2 * j], aA[2 * j + 1], aB[2 * j + 1], xw[2 * j], xw[2 * j + 1]);
+            mma16816<BF16>(c2, aA[2 * j + 2], aB[2 * j + 2], aA[2 * j + 3], aB[2 * j + 3], xw[2 * j + 2], xw[2 * j + 3]);
+          }
+#pragma unroll
+          for (int i = 0; i < 4; ++i) c[tg][i] += c2[i];
         }
       }
     }
@@ -453,16 +465,20 @@ gemv_mma_kernel(const GemvParams p) {
 }
 
 template <bool BF16, bool W4, int TG, int MINB, bool LIN = false, bool POST = false>
-static cudaError_t launch_gemv_one(const GemvParams& p, cudaStream_t st) {
+static cudaError_t launch_gemv_one(const GemvParams& p_in, cudaStream_t st) {
+  GemvParams p = p_in;
+  p.gshift = (p.group > 0 && (p.group & (p.group - 1)) == 0) ? __builtin_ctz(p.group) : -1;
   // persistent over 16-row tiles: one resident wave (occupancy x SMs), never more CTAs than tiles
-  static int occ = 0;
-  // 4-bit: [table 32 KB (non-linear code book only)] + prefetch ring: 2 x (8 x 256 x 16 B codes + 16 x 256 x 4 B scales) = 96 KB
-  const int smem = W4 ? ((LIN ? 0 : 256 * 32 * 4) + 2 * (2 * 4 * 256 * 16 + 4 * 4 * 256 * 4)) : 0;
+  // [table 32 KB (4-bit, non-linear code book only)] + the activations [M, K] 16-bit when they fit in 64 KB
+  const long long xbytes = (long long)p.M * (p.K + 8) * 2;      // rows padded by 16 bytes (bank spread)
+  const int smem = ((W4 && !LIN) ? 256 * 32 * 4 : 0) + (xbytes <= 73728 ? (int)xbytes : 0);
   static bool attr_done = false;
-  if (!attr_done && smem > 48 * 1024) {
-    cudaFuncSetAttribute(gemv_mma_kernel<BF16, W4, TG, MINB, LIN, POST>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  static int occ_by_kb[129] = {0};
+  if (!attr_done) {
+    cudaFuncSetAttribute(gemv_mma_kernel<BF16, W4, TG, MINB, LIN, POST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024);
     attr_done = true;
   }
+  int& occ = occ_by_kb[(smem + 1023) >> 10];
   if (!occ) {
     if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, gemv_mma_kernel<BF16, W4, TG, MINB, LIN, POST>, 256, smem) != cudaSuccess || occ < 1) occ = 1;
   }
@@ -477,14 +493,15 @@ static int launch_gemv_lin(const GemvParams& p, cudaStream_t st) {
   // 2 CTAs per SM (128 registers, no spills): with 4 chunks x 2 rows x 16 B requested up front per lane that is 64 KB in
   // flight per SM, above the ~44 KB that 6.5 TB/s x ~1 us of DRAM latency asks of each of the 148 SMs
   static const bool post_off = [] { const char* e = getenv("B200_GEMV_POST"); return e && atoi(e) == 0; }();
+  static const int minb8 = [] { const char* e = getenv("B200_GEMV_MINB8"); return e ? atoi(e) : 4; }();
   if (p.group % 128 == 0 && !post_off) {   // scale applied to the chunk sums (see POST above)
-    if (p.M <= 8) e = launch_gemv_one<BF16, true, 1, 2, true, true>(p, st);
+    if (p.M <= 8) e = minb8 >= 4 ? launch_gemv_one<BF16, true, 1, 3, true, true>(p, st) : launch_gemv_one<BF16, true, 1, 2, true, true>(p, st);
     else if (p.M <= 16) e = launch_gemv_one<BF16, true, 2, 2, true, true>(p, st);
     else if (p.M <= 32) e = launch_gemv_one<BF16, true, 4, 2, true, true>(p, st);
     else e = launch_gemv_one<BF16, true, 8, 1, true, true>(p, st);
     return (int)e;
   }
-  if (p.M <= 8) e = launch_gemv_one<BF16, true, 1, 2, true>(p, st);
+  if (p.M <= 8) e = minb8 >= 4 ? launch_gemv_one<BF16, true, 1, 3, true>(p, st) : launch_gemv_one<BF16, true, 1, 2, true>(p, st);
   else if (p.M <= 16) e = launch_gemv_one<BF16, true, 2, 2, true>(p, st);
   else if (p.M <= 32) e = launch_gemv_one<BF16, true, 4, 2, true>(p, st);
   else e = launch_gemv_one<BF16, true, 8, 1, true>(p, st);

@@ -103,7 +103,7 @@ class grad_scale_context:
         return False
 
 
-_VOCAB_CHUNK = int(__import__("os").environ.get("B200_CE_VOCAB_CHUNK", "8192"))
+_VOCAB_CHUNK = int(__import__("os").environ.get("B200_CE_VOCAB_CHUNK", "16384"))
 _VOCAB_CHUNK_MIN_BYTES = int(__import__("os").environ.get("B200_CE_VOCAB_MIN_MB", "64")) << 20
 
 

@@ -26,6 +26,7 @@ ap.add_argument("--opt", default="adamw")
 ap.add_argument("--impl", default="ours")
 ap.add_argument("--comm", default="", help="symm | nccl (sets B200_COMM for this variant)")
 ap.add_argument("--skew", action="store_true")
+ap.add_argument("--synthetic", action="store_true", help="zero case: seeded random gradients instead of training (collective in isolation)")
 ap.add_argument("--steps", type=int, default=3)
 ap.add_argument("--dump", default="", help="file (single case) or directory (suite) for the parameter dumps")
 cli = ap.parse_args()
@@ -68,7 +69,16 @@ def run_case(a, dump=""):
                                  "optimizer": {"type": "paged_adamw_8bit" if a.opt == "adamw8bit" else "AdamW",
                                                "params": {"lr": 1e-3, "weight_decay": 0.0}}})
         data = torch.randint(0, cfg.vocab_size, (a.steps, 2, TOTAL, 2, 256), generator=gen)   # [step, micro, vrank, B, S]
-        for step in range(a.steps):
+        if getattr(a, "synthetic", False):
+            # the collective in isolation: every rank's gradient arena is a seeded random tensor (identical in the runs
+            # that are compared), so the only difference between the fused kernel and NCCL is the order of the fp32 adds
+            for step in range(a.steps):
+                g = torch.Generator(device=dev).manual_seed(1000 * step + rank)
+                eng.arena.grad.copy_(torch.randn(eng.arena.numel, device=dev, generator=g) * 1e-2)
+                eng.micro_steps = eng.ga * (step + 1)
+                eng.step()
+                losses.append(0.0)
+        for step in range(0 if getattr(a, "synthetic", False) else a.steps):
             for m in range(2):
                 for v in [v for v in range(TOTAL) if v % world == rank]:
                     ids = data[step, m, v].to(dev)
@@ -133,9 +143,10 @@ def run_case(a, dump=""):
         gc.collect()
         torch.cuda.empty_cache()
         base_mem = torch.cuda.memory_allocated()        # whatever earlier variants of a suite left behind
-        model = gptlike(torch.bfloat16, layers=8)
+        # 1 rank: the replicated baseline (fp32 arena: parameters + gradients + AdamW moments = 16 B / parameter)
+        model = gptlike(torch.bfloat16 if world > 1 else torch.float32, layers=8)
         n_params = sum(p.numel() for p in model.parameters())
-        eng = initialize(model=model, config={"bf16": {"enabled": True}, "zero_optimization": {"stage": a.stage},
+        eng = initialize(model=model, config={"bf16": {"enabled": world > 1}, "zero_optimization": {"stage": a.stage},
                                               "gradient_accumulation_steps": 1, "gradient_clipping": 1.0,
                                               "train_micro_batch_size_per_gpu": 4,
                                               "optimizer": {"type": "AdamW", "params": {"lr": 1e-3, "weight_decay": 0.0}}})
@@ -176,16 +187,18 @@ def run_case(a, dump=""):
 
 
 def V(**kw):
-    d = dict(case="zero", stage=2, opt="adamw", impl="ours", comm="symm", skew=False, steps=3)
+    d = dict(case="zero", stage=2, opt="adamw", impl="ours", comm="symm", skew=False, steps=3, synthetic=False)
     d.update(kw)
     return argparse.Namespace(**d)
 
 
 SUITES = {
     "multi": {
-        "zero0_symm": V(stage=0), "zero0_nccl": V(stage=0, comm="nccl"),
+        "grad0_symm": V(stage=0, synthetic=True), "grad0_nccl": V(stage=0, comm="nccl", synthetic=True),
+        "grad2_symm": V(stage=2, synthetic=True), "grad2_nccl": V(stage=2, comm="nccl", synthetic=True),
+        "grad3_8bit_symm": V(stage=3, opt="adamw8bit", synthetic=True),
+        "grad3_8bit_nccl": V(stage=3, opt="adamw8bit", comm="nccl", synthetic=True),
         "zero2_symm": V(stage=2), "zero2_nccl": V(stage=2, comm="nccl"), "zero2_skew": V(stage=2, skew=True),
-        "zero3_8bit_symm": V(stage=3, opt="adamw8bit"), "zero3_8bit_nccl": V(stage=3, opt="adamw8bit", comm="nccl"),
         "zero3_symm": V(stage=3),
         "ddp_ours": V(case="ddp", steps=4), "ddp_torch": V(case="ddp", impl="torch", steps=4),
         "ddp_skew": V(case="ddp", steps=4, skew=True),

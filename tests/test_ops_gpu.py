@@ -159,7 +159,9 @@ def test_linear_cross_entropy_vocab_chunked(trainable_head, monkeypatch):
     loss = L.linear_cross_entropy(x, w, t, row_scale=rs)
     loss.backward()
     peak = torch.cuda.max_memory_allocated() - base
-    assert peak < M * V * 2, "a [tokens, vocab] tensor was allocated"
+    # frozen head: everything allocated stays below ONE bf16 [tokens, vocab] tensor; a trainable head also owns its
+    # fp32 gradient (and the temporary it is formed in): allow those
+    assert peak < M * V * 2 + (3 * V * K * 4 if trainable_head else 0), "a [tokens, vocab] tensor was allocated"
     x32, w32 = x.detach().float().requires_grad_(), w.detach().float().requires_grad_(trainable_head)
     rows = F.cross_entropy(x32 @ w32.t(), t, ignore_index=-100, reduction="none")
     ref = torch.dot(rows, rs)
