@@ -147,6 +147,46 @@ class Generator:
         return gemm(last.contiguous(), m.head_weight(), out_dtype=torch.float32)
 
     @torch.no_grad()
+    def copy_prefix(self, cache: KVCache, src: int, dst: int, n: int) -> None:
+        """K/V of the first ``n`` positions of cache row ``src`` -> row ``dst`` (a prefix-cache hit on a row that is still
+        in use). A method of the generator so that tensor-parallel followers repeat it on their slice of the cache."""
+        for li in range(len(cache.k)):
+            cache.k[li][dst, :, :n] = cache.k[li][src, :, :n]
+            cache.v[li][dst, :, :n] = cache.v[li][src, :, :n]
+
+    @torch.no_grad()
+    def _prefill_chunk(self, ids: torch.Tensor, cache: KVCache, slot: int, pos0: int) -> torch.Tensor:
+        """Prefill ``ids`` [T] of ONE sequence at positions pos0 .. pos0 + T - 1 of cache row ``slot``, attending to what
+        the row already holds below ``pos0``: the unit of chunked prefill and of a prefix-cache hit (the shared prefix is
+        in the row, only the suffix is computed). Returns the logits of the last token [1, V]."""
+        m, c = self.model, self.cfg
+        n_real = ids.shape[0]
+        dev = ids.device
+        # the score / probability rows of the tensor-core path need 16-byte strides: the chunk is padded with dummy tokens
+        # until pos0 + T is a multiple of 8. Their K/V land beyond the sequence's valid length (rewritten before they can
+        # ever be attended to) and their outputs are dropped.
+        padn = (-(pos0 + n_real)) % 8
+        if padn and pos0 + n_real + padn <= cache.max_len and ids.is_cuda:
+            ids = torch.cat([ids, ids.new_zeros(padn)])
+        T = ids.shape[0]
+        H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
+        cos, sin = m.rope(dev, self.max_len)
+        pos = torch.arange(pos0, pos0 + T, device=dev, dtype=torch.int32)
+        from ..ops.attention import attention_with_past
+        delta, res = ew.embedding(ids, m.embed_tokens), None
+        for li, layer in enumerate(m.layers):
+            x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
+            qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
+            t = qkv.view(T, H + 2 * Hkv, D)
+            cache.k[li][slot, :, pos0:pos0 + T] = t[:, H:H + Hkv].permute(1, 0, 2)
+            cache.v[li][slot, :, pos0:pos0 + T] = t[:, H + Hkv:].permute(1, 0, 2)
+            ctx = attention_with_past(qkv, cache.k[li][slot], cache.v[li][slot], pos0, H, Hkv, D)
+            x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
+            delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
+        h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)
+        return gemm(h[n_real - 1:n_real].contiguous(), m.head_weight(), out_dtype=torch.float32)
+
+    @torch.no_grad()
     def _prefill_packed_core(self, ids, pos, row, cu, last, max_seqlen: int, cache: KVCache) -> torch.Tensor:
         """Tensor-level body of the packed prefill (everything it reads is a device tensor, so it can be captured):
         ids / pos / row [T] (token, position and cache row of every packed token), cu [n + 1] int32, last [n] (row index

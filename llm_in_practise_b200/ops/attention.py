@@ -225,3 +225,41 @@ def attention(qkv: torch.Tensor, B: int, S: int, n_heads: int, n_kv_heads: int, 
     if causal and window == 0 and dropout_p == 0.0 and S > _BLOCK_Q and S % 8 == 0:
         return _BlockedCausalAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, scale, _BLOCK_Q)
     return _TiledAttentionFn.apply(qkv, B, S, n_heads, n_kv_heads, head_dim, causal, window, scale, dropout_p)
+
+
+def attention_with_past(qkv: torch.Tensor, k_cache: torch.Tensor, v_cache: torch.Tensor, pos0: int, n_heads: int,
+                        n_kv_heads: int, head_dim: int, scale: Optional[float] = None) -> torch.Tensor:
+    """Attention of T new tokens of ONE sequence over its KV-cache row: chunked prefill and prefix-cache hits
+    (vLLM's ``enable_chunked_prefill`` / ``enable_prefix_caching``, Deployment/Ray/serve_run_examples/deepseek.py:29-34).
+
+    ``qkv`` [T, (H + 2 Hkv) * D] holds the new tokens (positions pos0 .. pos0 + T - 1, already rotated); ``k_cache`` /
+    ``v_cache`` [Hkv, L, D] already contain their keys / values at those positions and the past before them. Query row r
+    sees cache columns 0 .. pos0 + r (the causal offset of the row-softmax kernel). Query blocks of ``_BLOCK_Q`` rows keep
+    the score transient small. Returns the context [T, H * D]."""
+    T = qkv.shape[0]
+    H, Hkv, D = n_heads, n_kv_heads, head_dim
+    if scale is None:
+        scale = 1.0 / math.sqrt(D)
+    q = qkv.view(1, T, H + 2 * Hkv, D)[:, :, :H].permute(0, 2, 1, 3)           # [1, H, T, D] strided view
+    out = torch.empty(1, T, H, D, dtype=qkv.dtype, device=qkv.device)
+    o4 = out.permute(0, 2, 1, 3)
+    native = nv.use_native(qkv)
+    for q0 in range(0, T, _BLOCK_Q):
+        q1 = min(T, q0 + _BLOCK_Q)
+        kv_len = pos0 + q1
+        k = k_cache[:, :kv_len].unsqueeze(0)                                   # [1, Hkv, kv_len, D]
+        v = v_cache[:, :kv_len].unsqueeze(0)
+        if native and kv_len % 8 == 0:
+            sc = gemm(q[:, :, q0:q1], k, alpha=scale, out_dtype=torch.float32)                 # [1, H, rows, kv_len]
+            P = _softmax_fwd(sc, True, 0, qkv.dtype)
+            gemm(P, v, b_mn=True, out=o4[:, :, q0:q1])
+        else:
+            g = H // Hkv
+            kf = k.float().repeat_interleave(g, 1)
+            vf = v.float().repeat_interleave(g, 1)
+            sc = torch.matmul(q[:, :, q0:q1].float(), kf.transpose(-1, -2)) * scale
+            rows = torch.arange(q0, q1, device=qkv.device).view(-1, 1) + pos0
+            cols = torch.arange(kv_len, device=qkv.device).view(1, -1)
+            sc = sc.masked_fill(cols > rows, float("-inf"))
+            o4[:, :, q0:q1] = torch.matmul(sc.softmax(-1), vf).to(qkv.dtype)
+    return out.view(T, H * D)

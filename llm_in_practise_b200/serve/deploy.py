@@ -49,10 +49,20 @@ class LLMConfig:
         a.setdefault("target_ongoing_requests", 5)
         return a
 
-    def validate(self) -> None:
+    def parallel_size(self) -> int:
+        """GPUs one replica spans. ``pipeline_parallel_size`` (the reference's two-Ray-worker recipe,
+        serve_deploy_examples/qwen3_app_pipeline_parallel.yaml:21-31, splits layers across HOSTS over TCP) is folded into
+        the tensor-parallel degree: inside one NVLink / NVSwitch node the same GPUs are better used as TP ranks."""
         ek = self.engine_kwargs
-        if int(ek.get("tensor_parallel_size", 1)) != 1 or int(ek.get("pipeline_parallel_size", 1)) != 1:
-            raise NotImplementedError("one engine per GPU: scale with replicas (ReplicaRouter); TP/PP > 1 is not available in serve.deploy")
+        return int(ek.get("tensor_parallel_size", 1)) * int(ek.get("pipeline_parallel_size", 1))
+
+    def validate(self) -> None:
+        import torch.distributed as dist
+        want = self.parallel_size()
+        have = dist.get_world_size() if (dist.is_available() and dist.is_initialized()) else 1
+        if want != have:
+            raise RuntimeError(f"engine_kwargs ask for {want} GPUs per replica (tensor_parallel_size x pipeline_parallel_size) but "
+                               f"this process group has {have} rank(s): launch with `torchrun --nproc-per-node {want}`")
 
 
 class ReplicaRouter:
@@ -85,8 +95,14 @@ def build_engine(cfg: LLMConfig, device=None):
     ek = cfg.engine_kwargs
     dt = {"auto": torch.bfloat16, "bfloat16": torch.bfloat16, "half": torch.float16, "float16": torch.float16}[str(ek.get("dtype", "auto"))]
     model, tok = _load(cfg.model_source, None, dt)
-    return LLMEngine(model, tok, EngineArgs(max_num_seqs=int(ek.get("max_num_seqs", 16)), max_model_len=int(ek.get("max_model_len", 4096))),
-                     model_name=cfg.model_id)
+    args = EngineArgs(max_num_seqs=int(ek.get("max_num_seqs", 16)), max_model_len=int(ek.get("max_model_len", 4096)),
+                      enable_prefix_caching=bool(ek.get("enable_prefix_caching", True)),
+                      enable_chunked_prefill=bool(ek.get("enable_chunked_prefill", True)),
+                      gpu_memory_utilization=float(ek.get("gpu_memory_utilization", 0.0)) if "max_num_seqs" not in ek else 0.0)
+    if cfg.parallel_size() > 1:
+        from .tp_engine import build_tp_engine
+        return build_tp_engine(model, tok, args, model_name=cfg.model_id)     # ranks > 0: call engine.serve_forever()
+    return LLMEngine(model, tok, args, model_name=cfg.model_id)
 
 
 def build_openai_app(args: Dict[str, Any], engines: Optional[Dict[str, Any]] = None):

@@ -20,7 +20,7 @@ import itertools
 import queue
 import threading
 import time
-from collections import deque
+from collections import OrderedDict, deque
 from dataclasses import dataclass, field
 from typing import Deque, Dict, Iterator, List, Optional, Sequence
 
@@ -37,6 +37,11 @@ class EngineArgs:
     max_prefill_tokens: int = 2048       # ... and on their total prompt tokens (one packed prefill pass per iteration)
     seed: Optional[int] = None
     warmup: bool = True                  # capture the prefill / decode CUDA graphs in start() instead of in the first requests
+    # the three engine_kwargs the reference's serving recipes set (Deployment/Ray/serve_run_examples/deepseek.py:29-34)
+    enable_prefix_caching: bool = True   # finished sequences keep their KV row; a new prompt reuses the longest cached prefix
+    enable_chunked_prefill: bool = True  # prompts longer than max_prefill_tokens are prefilled in pieces between decode steps
+    prefix_block: int = 16               # prefix matches are counted in blocks of this many tokens (vLLM's block_size)
+    gpu_memory_utilization: float = 0.0  # > 0: derive max_num_seqs from the free HBM (rows of max_model_len tokens)
 
 
 @dataclass
@@ -54,6 +59,8 @@ class Request:
     stream: "queue.Queue" = field(default_factory=queue.Queue)
     error: Optional[str] = None
     token_times: List[float] = field(default_factory=list)   # perf_counter at every emitted token (TTFT / ITL statistics)
+    prefilled: int = 0                                       # prompt tokens whose K/V are already in the cache row
+    cached_tokens: int = 0                                   # ... of which came from the prefix cache
     aborted: bool = False                                    # set by LLMEngine.abort(): dropped at the next scheduler iteration
 
     @property
@@ -81,6 +88,8 @@ class EngineMetrics:
         self.ttft_sum = 0.0
         self.e2e_sum = 0.0
         self.steps = 0
+        self.prefix_queries = 0          # prompt tokens looked up in the prefix cache (vllm:gpu_prefix_cache_queries)
+        self.prefix_hits = 0             # ... and found there                        (vllm:gpu_prefix_cache_hits)
 
     def observe_ttft(self, v: float) -> None:
         with self.lock:
@@ -99,12 +108,24 @@ class LLMEngine:
         self.model, self.tokenizer, self.model_name = self.gen.model, tokenizer, model_name
         c = self.model.config
         self.device = self.model.embed_tokens.device
+        if self.args.gpu_memory_utilization > 0 and self.device.type == "cuda":
+            # vLLM's knob: the KV pool takes what is left of `utilization x total HBM` after the weights
+            free, total = torch.cuda.mem_get_info(self.device)
+            budget = free - (1.0 - self.args.gpu_memory_utilization) * total
+            row = 2 * c.num_hidden_layers * c.num_key_value_heads * self.args.max_model_len * c.head_dim * self.model.embed_tokens.element_size()
+            self.args.max_num_seqs = int(max(1, min(4096, budget // row - 1)))
         # one extra row: the scratch slot that padded rows of a bucketed (CUDA-graph) decode batch write into
         self.cache = KVCache(c.num_hidden_layers, self.args.max_num_seqs + 1, c.num_key_value_heads, self.args.max_model_len,
                              c.head_dim, self.model.embed_tokens.dtype, self.device)
         self.free: List[int] = list(range(self.args.max_num_seqs))[::-1]
         self.waiting: Deque[Request] = deque()
         self.running: List[Request] = []
+        self.prefilling: List[Request] = []                 # admitted, prompt only partly in the cache (chunked prefill)
+        # prefix cache: rows of finished sequences stay valid until their slot is needed (LRU), indexed by the hash of
+        # every whole block-prefix of their tokens
+        self._cached: "OrderedDict[int, bool]" = OrderedDict()            # slots of finished sequences, least recently used first
+        self._prefix_index: Dict[int, int] = {}                           # hash(tokens[:k * block]) -> slot
+        self._row_tokens: Dict[int, List[int]] = {}                       # slot -> tokens with valid K/V (cached or running rows)
         self.metrics = EngineMetrics()
         self._ids = itertools.count()
         self._cv = threading.Condition()
@@ -203,25 +224,93 @@ class LLMEngine:
         used = sum(len(r.prompt_ids) + len(r.output_ids) for r in self.running)
         return used / float(self.args.max_num_seqs * self.args.max_model_len)
 
+    # ------------------------------------------------------------------ prefix cache (enable_prefix_caching)
+    def _block_hashes(self, toks: Sequence[int], upto: int):
+        """(n, hash of toks[:n]) for every whole block-prefix n = block, 2 * block, ... <= upto (chained hashes)."""
+        B = self.args.prefix_block
+        h = 0
+        for k in range(1, upto // B + 1):
+            h = hash((h, tuple(toks[(k - 1) * B:k * B])))
+            yield k * B, h
+
+    def _index_row(self, slot: int, toks: List[int]) -> None:
+        """Row ``slot`` holds valid K/V for ``toks`` (a running sequence's prompt, or a finished sequence)."""
+        self._unindex_row(slot)
+        self._row_tokens[slot] = toks
+        for _, h in self._block_hashes(toks, len(toks)):
+            self._prefix_index[h] = slot
+
+    def _unindex_row(self, slot: int) -> None:
+        toks = self._row_tokens.pop(slot, None)
+        if toks is not None:
+            for _, h in self._block_hashes(toks, len(toks)):
+                if self._prefix_index.get(h) == slot:
+                    del self._prefix_index[h]
+
+    def _lookup_prefix(self, prompt: List[int]):
+        """Longest cached block-prefix of ``prompt`` that leaves at least one token to compute: (slot, n) or (-1, 0)."""
+        best = (-1, 0)
+        for n, h in self._block_hashes(prompt, len(prompt) - 1):
+            slot = self._prefix_index.get(h)
+            if slot is None:
+                break
+            if self._row_tokens.get(slot, [])[:n] == prompt[:n]:        # guards against hash collisions / stale entries
+                best = (slot, n)
+            else:
+                break
+        return best
+
+    def _take_slot(self, keep: int = -1) -> int:
+        """A free KV row, else the least recently used cached one (never ``keep``, the row a prefix is copied from)."""
+        if self.free:
+            return self.free.pop()
+        for slot in self._cached:
+            if slot != keep:
+                del self._cached[slot]
+                self._unindex_row(slot)
+                return slot
+        return -1
+
+    def _slots_available(self) -> int:
+        return len(self.free) + len(self._cached)
+
+    def _release_slot(self, r: Request) -> None:
+        """The request is done with its row: keep it as a cached prefix (LRU) or hand it back."""
+        slot, r.slot = r.slot, -1
+        if slot < 0:
+            return
+        valid = r.prompt_ids[:r.prefilled] if r.prefilled < len(r.prompt_ids) else r.prompt_ids + r.output_ids[:-1]
+        if self.args.enable_prefix_caching and len(valid) >= self.args.prefix_block and r.finish_reason != "error":
+            self._index_row(slot, list(valid))
+            self._cached[slot] = True
+            self._cached.move_to_end(slot)
+        else:
+            self._unindex_row(slot)
+            self.free.append(slot)
+
     # ------------------------------------------------------------------ scheduler
     def _loop(self) -> None:
         if self.device.type == "cuda":
             torch.cuda.set_device(self.device)
         while True:
             with self._cv:
-                while not self._stop and not self.waiting and not self.running:
+                while not self._stop and not self.waiting and not self.running and not self.prefilling:
                     self._cv.wait(timeout=0.5)
                 if self._stop:
                     break
             try:
                 self.step()
             except Exception as e:  # fail the in-flight requests, keep serving
-                for r in self.running + list(self.waiting):
+                for r in self.running + self.prefilling + list(self.waiting):
                     r.error = f"{type(e).__name__}: {e}"
                     self._finish(r, "error")
                 self.running.clear()
+                self.prefilling.clear()
                 self.waiting.clear()
                 self.free = list(range(self.args.max_num_seqs))[::-1]
+                self._cached.clear()
+                self._prefix_index.clear()
+                self._row_tokens.clear()
 
     def _eos(self, cfg: GenerationConfig) -> List[int]:
         e = cfg.eos_token_id
@@ -233,9 +322,7 @@ class LLMEngine:
     def _finish(self, r: Request, reason: str) -> None:
         r.finish_reason = reason
         r.finish_time = time.perf_counter()
-        if r.slot >= 0:
-            self.free.append(r.slot)
-            r.slot = -1
+        self._release_slot(r)
         with self.metrics.lock:
             self.metrics.requests_finished[reason] = self.metrics.requests_finished.get(reason, 0) + 1
             self.metrics.e2e_sum += r.finish_time - r.arrival
@@ -280,19 +367,76 @@ class LLMEngine:
                 out[i] = t
         return out
 
+    def _start_running(self, r: Request) -> None:
+        self.running.append(r)
+        if self.args.enable_prefix_caching:
+            self._index_row(r.slot, r.prompt_ids)          # later prompts may copy this (still running) row's prefix
+
+    def _prefill_piece(self, r: Request, budget: int) -> int:
+        """Prefill the next piece (at most ``budget`` tokens when chunking is on) of a partly cached prompt; on the last
+        piece sample the first token and move the request to the decode batch. Returns the tokens processed."""
+        L = len(r.prompt_ids)
+        n = L - r.prefilled
+        if self.args.enable_chunked_prefill:
+            n = min(n, max(budget, 8))
+            if r.prefilled + n < L:
+                n = max(8, n // 8 * 8)                       # pieces end on 8-token boundaries (aligned score rows)
+        ids = torch.tensor(r.prompt_ids[r.prefilled:r.prefilled + n], device=self.device)
+        logits = self.gen._prefill_chunk(ids, self.cache, r.slot, r.prefilled)
+        r.prefilled += n
+        with self.metrics.lock:
+            self.metrics.prompt_tokens += n
+        if r.prefilled >= L:
+            self.prefilling.remove(r)
+            tok = self._sample(logits, [r])[0]
+            if not self._emit(r, tok):
+                self._start_running(r)
+        return n
+
     @torch.no_grad()
     def step(self) -> None:
         """One scheduler iteration: admit + prefill, then one batched decode step."""
         batch: List[Request] = []
         budget = self.args.max_prefill_tokens
-        while self.waiting and self.free and len(batch) < self.args.max_prefill_per_step:
+        # (1) sequences whose prompt is only partly in the cache (chunked prefill / prefix hits): one more piece each
+        for r in list(self.prefilling):
+            if r.aborted:
+                self.prefilling.remove(r)
+                self._finish(r, "abort")
+            elif budget > 0:
+                budget -= self._prefill_piece(r, budget)
+        # (2) admissions
+        while (self.waiting and self._slots_available() and budget > 0
+               and len(batch) + len(self.prefilling) < self.args.max_prefill_per_step):
             with self._cv:
-                if batch and len(self.waiting[0].prompt_ids) > budget:
+                r = self.waiting[0]
+                L = len(r.prompt_ids)
+                src, P = self._lookup_prefix(r.prompt_ids) if self.args.enable_prefix_caching else (-1, 0)
+                piecewise = P > 0 or (L > budget and self.args.enable_chunked_prefill and not batch)
+                if not piecewise and batch and L > budget:
                     break
-                r = self.waiting.popleft()
-            r.slot = self.free.pop()
-            budget -= len(r.prompt_ids)
-            batch.append(r)
+                self.waiting.popleft()
+            with self.metrics.lock:
+                self.metrics.prefix_queries += L
+                self.metrics.prefix_hits += P
+            if not piecewise:
+                r.slot = self._take_slot()
+                r.prefilled = L
+                budget -= L
+                batch.append(r)
+                continue
+            if P > 0 and src in self._cached:
+                # the prefix lives in the row of a finished sequence: continue in that very row, nothing is copied
+                del self._cached[src]
+                self._unindex_row(src)
+                r.slot = src
+            else:
+                r.slot = self._take_slot(keep=src)
+                if P > 0:
+                    self.gen.copy_prefix(self.cache, src, r.slot, P)     # the prefix belongs to a running sequence: copy its K/V
+            r.prefilled = r.cached_tokens = P
+            self.prefilling.append(r)
+            budget -= self._prefill_piece(r, budget)
         if batch:
             # the admitted prompts run as ONE packed pass (token-level batching): GEMMs see the sum of the prompt lengths
             if self.device.type == "cuda":
@@ -309,7 +453,7 @@ class LLMEngine:
                 self.metrics.prompt_tokens += sum(len(r.prompt_ids) for r in batch)
             for r, tok in zip(batch, self._sample(logits, batch)):
                 if not self._emit(r, tok):
-                    self.running.append(r)
+                    self._start_running(r)
         if any(r.aborted for r in self.running):
             for r in [r for r in self.running if r.aborted]:
                 self._finish(r, "abort")

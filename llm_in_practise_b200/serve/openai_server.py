@@ -103,6 +103,8 @@ def render_metrics(engine: LLMEngine) -> str:
     with m.lock:
         counter("vllm:prompt_tokens_total", m.prompt_tokens, "Number of prefill tokens processed.")
         counter("vllm:generation_tokens_total", m.generation_tokens, "Number of generation tokens processed.")
+        counter("vllm:gpu_prefix_cache_queries_total", m.prefix_queries, "Prompt tokens looked up in the prefix cache.")
+        counter("vllm:gpu_prefix_cache_hits_total", m.prefix_hits, "Prompt tokens served from the prefix cache.")
         out.extend(["# HELP vllm:request_success_total Count of successfully processed requests.",
                     "# TYPE vllm:request_success_total counter"])
         for reason, n in sorted(m.requests_finished.items()):

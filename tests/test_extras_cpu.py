@@ -63,11 +63,12 @@ def test_deploy_layer(tmp_path):
     apps = load_serve_yaml(str(y))
     cfg = apps[0]["llm_configs"][0]
     assert cfg.model_id == "qwen3" and cfg.autoscaling()["max_replicas"] == 4
+    assert cfg.parallel_size() == 2                         # TP 1 x PP 2 -> two tensor-parallel ranks on one node
     try:
         cfg.validate()
-        raise AssertionError("pipeline_parallel_size 2 must be rejected")
-    except NotImplementedError:
-        pass
+        raise AssertionError("a 2-GPU replica must not start in a single process")
+    except RuntimeError as e:
+        assert "torchrun --nproc-per-node 2" in str(e)
     torch.manual_seed(0)
     m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32, device="cpu")
     e1, e2 = (LLMEngine(m, ByteTokenizer(), EngineArgs(max_num_seqs=2, max_model_len=64), model_name=n) for n in ("a", "b"))

@@ -29,7 +29,8 @@ def test_continuous_batching_matches_sequential(model):
     prompts = [torch.randint(0, 300, (n,)).tolist() for n in (5, 9, 3, 12, 7)]
     g = Generator(model, max_len=64)
     want = [g.generate(torch.tensor([p]), max_new_tokens=6 + i, do_sample=False)[0, len(p):].tolist() for i, p in enumerate(prompts)]
-    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=2, max_model_len=64, max_prefill_per_step=1))   # forces queueing + slot reuse
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=2, max_model_len=64, max_prefill_per_step=1,
+                                              enable_prefix_caching=False))   # forces queueing + slot reuse
     reqs = [eng.submit(p, GenerationConfig(max_new_tokens=6 + i, do_sample=False)) for i, p in enumerate(prompts)]
     assert eng.num_waiting == 5
     while not all(r.done.is_set() for r in reqs):
@@ -40,6 +41,38 @@ def test_continuous_batching_matches_sequential(model):
     assert sorted(eng.free) == [0, 1] and eng.metrics.generation_tokens == sum(len(w) for w in want)
 
 
+def test_chunked_prefill_and_prefix_cache_match_plain_generation(model):
+    """enable_chunked_prefill: a prompt longer than the token budget is prefilled in pieces between decode steps of the
+    running sequences; enable_prefix_caching: a prompt that starts like an earlier one reuses that row's K/V (in place
+    when the earlier sequence has finished, by copy while it is still running). Outputs equal one-by-one generation."""
+    torch.manual_seed(3)
+    system = torch.randint(0, 300, (40,)).tolist()                    # a shared "system prompt" of 2.5 blocks
+    prompts = [system + torch.randint(0, 300, (n,)).tolist() for n in (7, 11, 3)] + [torch.randint(0, 300, (50,)).tolist()]
+    g = Generator(model, max_len=96)
+    want = [g.generate(torch.tensor([p]), max_new_tokens=5, do_sample=False)[0, len(p):].tolist() for p in prompts]
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=3, max_model_len=96, max_prefill_per_step=4, max_prefill_tokens=24,
+                                            prefix_block=16))
+    r0 = eng.submit(prompts[0], GenerationConfig(max_new_tokens=5, do_sample=False))
+    eng.step()                                                          # 47 tokens > 24: first piece only
+    assert r0 in eng.prefilling and 0 < r0.prefilled < len(prompts[0]) and eng.num_running == 0
+    eng.step()
+    assert eng.num_running == 1 and r0.first_token_time is not None
+    r1 = eng.submit(prompts[1], GenerationConfig(max_new_tokens=5, do_sample=False))   # r0 still running: prefix by copy
+    eng.step()
+    assert r1.cached_tokens == 32 and r1.slot != r0.slot
+    while not (r0.done.is_set() and r1.done.is_set()):
+        eng.step()
+    r2 = eng.submit(prompts[2], GenerationConfig(max_new_tokens=5, do_sample=False))   # both finished: continues in a cached row
+    r3 = eng.submit(prompts[3], GenerationConfig(max_new_tokens=5, do_sample=False))   # no shared prefix, chunked
+    while not (r2.done.is_set() and r3.done.is_set()):
+        eng.step()
+    assert r2.cached_tokens == 32 and r3.cached_tokens == 0
+    assert [r.output_ids for r in (r0, r1, r2, r3)] == want
+    m = eng.metrics
+    assert m.prefix_hits == 64 and m.prefix_queries == sum(len(p) for p in prompts)
+    assert len(eng.free) + len(eng._cached) == 3                        # every row is free or a cached prefix
+
+
 def test_packed_admission_respects_token_budget(model):
     """Several prompts admitted in one iteration run as one packed prefill; the token budget splits a burst over
     iterations (a single over-long prompt is still admitted alone); results equal one-by-one generation."""
@@ -47,7 +80,8 @@ def test_packed_admission_respects_token_budget(model):
     prompts = [torch.randint(0, 300, (n,)).tolist() for n in (6, 6, 6, 20, 4)]
     g = Generator(model, max_len=64)
     want = [g.generate(torch.tensor([p]), max_new_tokens=5, do_sample=False)[0, len(p):].tolist() for p in prompts]
-    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=8, max_model_len=64, max_prefill_per_step=8, max_prefill_tokens=13))
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=8, max_model_len=64, max_prefill_per_step=8, max_prefill_tokens=13,
+                                              enable_chunked_prefill=False, enable_prefix_caching=False))
     reqs = [eng.submit(p, GenerationConfig(max_new_tokens=5, do_sample=False)) for p in prompts]
     eng.step()
     assert eng.num_running == 2 and eng.num_waiting == 3          # 6 + 6 fit the budget of 13, the third prompt does not

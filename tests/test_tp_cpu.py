@@ -48,3 +48,32 @@ def test_tp2_matches_single(quant, tmp_path):
     assert torch.allclose(got["logits"], ref, atol=2e-4, rtol=1e-3), (got["logits"] - ref).abs().max()
     assert torch.equal(got["out"], Generator(m, max_len=64).generate(ids, max_new_tokens=5, do_sample=False))
     assert got["calls"] > 0
+
+
+def _serve_worker(rank, world, tmp):
+    """Tensor-parallel serving: rank 0 schedules (continuous batching, chunked prefill, prefix cache), rank 1 follows."""
+    from llm_in_practise_b200.inference import GenerationConfig
+    from llm_in_practise_b200.parallel.dist import setup_distributed
+    from llm_in_practise_b200.serve import EngineArgs
+    from llm_in_practise_b200.serve.tp_engine import build_tp_engine
+    setup_distributed()
+    eng = build_tp_engine(_model("w4"), None, EngineArgs(max_num_seqs=3, max_model_len=96, max_prefill_tokens=24, warmup=False))
+    if rank != 0:
+        eng.serve_forever()
+        return
+    torch.manual_seed(4)
+    shared = torch.randint(0, 256, (32,)).tolist()
+    prompts = [shared + [5, 6, 7], torch.randint(0, 256, (40,)).tolist(), shared + [9]]
+    reqs = eng.generate(prompts, GenerationConfig(max_new_tokens=4, do_sample=False))
+    torch.save({"out": [r.output_ids for r in reqs], "cached": [r.cached_tokens for r in reqs], "prompts": prompts}, f"{tmp}/serve.pt")
+    eng.shutdown()
+
+
+def test_tp2_serving_engine_matches_single_process(tmp_path):
+    from llm_in_practise_b200.inference import Generator
+    run_distributed(_serve_worker, 2, (str(tmp_path),))
+    got = torch.load(tmp_path / "serve.pt")
+    g = Generator(_model("w4"), max_len=96)
+    want = [g.generate(torch.tensor([p]), max_new_tokens=4, do_sample=False)[0, len(p):].tolist() for p in got["prompts"]]
+    assert got["out"] == want
+    assert max(got["cached"]) == 32            # the third prompt reused the first one's prefix
