@@ -493,7 +493,7 @@ static int launch_gemv_lin(const GemvParams& p, cudaStream_t st) {
   // 2 CTAs per SM (128 registers, no spills): with 4 chunks x 2 rows x 16 B requested up front per lane that is 64 KB in
   // flight per SM, above the ~44 KB that 6.5 TB/s x ~1 us of DRAM latency asks of each of the 148 SMs
   static const bool post_off = [] { const char* e = getenv("B200_GEMV_POST"); return e && atoi(e) == 0; }();
-  static const int minb8 = [] { const char* e = getenv("B200_GEMV_MINB8"); return e ? atoi(e) : 4; }();
+  static const int minb8 = [] { const char* e = getenv("B200_GEMV_MINB8"); return e ? atoi(e) : 2; }();
   if (p.group % 128 == 0 && !post_off) {   // scale applied to the chunk sums (see POST above)
     if (p.M <= 8) e = minb8 >= 4 ? launch_gemv_one<BF16, true, 1, 3, true, true>(p, st) : launch_gemv_one<BF16, true, 1, 2, true, true>(p, st);
     else if (p.M <= 16) e = launch_gemv_one<BF16, true, 2, 2, true, true>(p, st);

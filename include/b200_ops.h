@@ -335,6 +335,12 @@ int b200_flash_attn_varlen_fwd(const void* qkv, void* out, const int* cu_seqlens
 int b200_flash_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, float* delta,
                         float* dqkv32, void* dqkv, int B, int S, int H, int Hkv, int D, int causal, float scale,
                         float dropout_p, unsigned long long seed, int dtype, void* stream);
+/* The same forward on the 5th-generation tensor cores (csrc/flash_tc.cu): tcgen05.mma for Q K^T and P V with both
+ * accumulators in TMEM, Q / K / V tiles by TMA straight from qkv, one softmax thread per query row. head_dim 128, 16-bit
+ * dtypes, no dropout; returns B200_ERR_UNSUPPORTED for anything else (callers then use b200_flash_attn_fwd). B * S rows
+ * of qkv must be addressable as one 2-D tensor map (row stride (H + 2 Hkv) * 128 elements, 16-byte aligned base). */
+int b200_flash_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int S, int H, int Hkv, int D, int causal,
+                           float scale, int dtype, void* stream);
 
 /* ---- small-M products for decode / serving steps (csrc/gemv.cu) ---------------------------------
  * y[m, n] = sum_k x[m, k] w[n, k] (+ bias[n]) for 1 <= M <= 64 tokens with the weights read exactly once (mma.sync with

@@ -18,9 +18,22 @@ def flash_supported(qkv: torch.Tensor, head_dim: int) -> bool:
     return qkv.dtype in (torch.bfloat16, torch.float16) and head_dim in (32, 64, 96, 128)
 
 
+_TC = __import__("os").environ.get("B200_FLASH_TC", "1") != "0"
+
+
 def _fwd(qkv, B, S, H, Hkv, D, causal, scale, want_lse=True, dropout_p=0.0, seed=0):
     out = torch.empty(B * S, H * D, dtype=qkv.dtype, device=qkv.device)
     lse = torch.empty(B, H, S, dtype=torch.float32, device=qkv.device) if want_lse else None
+    if _TC and D == 128 and dropout_p == 0.0:
+        # tcgen05 / TMEM / TMA forward (csrc/flash_tc.cu); the mma.sync kernel below keeps the other head sizes and dropout
+        ft = nv.proto("b200_flash_attn_fwd_tc", [vp, vp, vp, i32, i32, i32, i32, i32, i32, f32, i32, vp])
+        rc = ft(nv.ptr(qkv), nv.ptr(out), nv.ptr(lse), B, S, H, Hkv, D, int(causal), float(scale), nv.dtype_code(qkv.dtype),
+                nv.stream())
+        if rc == 0:
+            nv.count_launch()
+            return out, lse
+        if rc != 10006:
+            nv.check(rc, "flash_attn_fwd_tc")
     fn = nv.proto("b200_flash_attn_fwd", [vp, vp, vp, i32, i32, i32, i32, i32, i32, f32, f32, u64, i32, vp])
     nv.check(fn(nv.ptr(qkv), nv.ptr(out), nv.ptr(lse), B, S, H, Hkv, D, int(causal), float(scale), float(dropout_p), int(seed),
                 nv.dtype_code(qkv.dtype), nv.stream()), "flash_attn_fwd")

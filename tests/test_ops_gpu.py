@@ -388,6 +388,26 @@ def test_flash_attention(H, Hkv, D, S, dtype, causal):
     assert torch.equal(out2, out)
 
 
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("H,Hkv,S,dtype", [(8, 2, 512, torch.bfloat16), (4, 4, 77, torch.float16), (5, 1, 200, torch.bfloat16),
+                                           (2, 2, 1000, torch.bfloat16), (2, 1, 128, torch.float16), (3, 3, 64, torch.bfloat16)])
+def test_flash_attention_tcgen05_forward(H, Hkv, S, dtype, causal, monkeypatch):
+    """csrc/flash_tc.cu (tcgen05 / TMEM / TMA forward, head_dim 128): context vs the fp32 reference, log-sum-exp vs the
+    mma.sync kernel (the backward kernel consumes it), sequence lengths that do not fill the 128 x 64 tiles, GQA."""
+    from llm_in_practise_b200.ops import flash as FL
+    B, D = 2, 128
+    torch.manual_seed(S * 3 + H)
+    qkv = torch.randn(B * S, (H + 2 * Hkv) * D, device=DEV, dtype=dtype)
+    monkeypatch.setattr(FL, "_TC", True)
+    out, lse = FL._fwd(qkv, B, S, H, Hkv, D, causal, D ** -0.5, True)
+    monkeypatch.setattr(FL, "_TC", False)
+    out_old, lse_old = FL._fwd(qkv, B, S, H, Hkv, D, causal, D ** -0.5, True)
+    ref = _ref_attention(qkv.float(), B, S, H, Hkv, D, causal, 0, D ** -0.5)
+    assert rel(out, ref) < 2e-2, rel(out, ref)
+    assert rel(out_old, ref) < 2e-2
+    assert (lse - lse_old).abs().max().item() < 2e-2
+
+
 def test_adamw_and_8bit():
     from llm_in_practise_b200.optim import FusedAdamW, PagedAdamW8bit
     from llm_in_practise_b200.utils.arena import ParamArena
