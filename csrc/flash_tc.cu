@@ -1,18 +1,18 @@
-// K4 on the 5th-generation tensor cores: causal flash-attention forward with tcgen05.mma, S and PV accumulators in
-// TMEM, Q / K / V tiles brought in by TMA straight out of the fused qkv projection (no head transposes, GQA by
-// column offset), online softmax by four warps whose threads each own ONE query row (TMEM lane = row, so row max and
-// row sum need no shuffles).
+// K4 on the 5th-generation tensor cores: causal flash-attention forward with tcgen05.mma, S, P and O in TMEM, Q / K / V
+// tiles brought in by TMA straight out of the fused qkv projection (no head transposes, GQA by column offset), online
+// softmax by four warps whose threads each own ONE query row (TMEM lane = row, so row max and row sum need no shuffles).
 //
-//   CTA = (128-query tile, head, batch); 256 threads: warps 0-3 softmax (one warpgroup), warp 4 TMA producer, warp 5
-//   tcgen05 issuer (setmaxnreg is a per-warpgroup instruction: the roles that give registers away and the ones that
-//   take them sit in different, 4-warp-aligned groups).
-//   per 64-key block j:   S = Q K_j^T           (M 128 x N 64 x K 128, 8 UMMAs)        -> TMEM columns [0, 64)
-//                         softmax warps: tcgen05.ld S, m / l update, P = exp2(S c - m c) -> 16-bit, 128B-swizzled smem tile
-//                         PV = P V_j             (M 128 x N 128 x K 64, 4 UMMAs, V read MN-major in place) -> TMEM [64, 192)
-//                         softmax warps: O = O * alpha + tcgen05.ld(PV)                  (O lives in registers, fp32)
-//   S(j+1) is issued as soon as the softmax warps have pulled S(j) into registers, so the tensor pipe works on the next
-//   scores while exp2 runs; two CTAs fit on an SM (115 KB of shared memory, 256 TMEM columns each) and overlap further.
-//   The register file is split with setmaxnreg: 40 per thread for the producer warpgroup, 216 for the softmax rows.
+//   CTA = (128-query tile, head, batch); 256 threads: warps 0-3 softmax, warp 4 TMA producer, warp 5 tcgen05 issuer.
+//   TMEM (256 columns, two CTAs per SM): S(even j) [0, 64), S(odd j) [64, 128), O [128, 256).
+//   per 64-key block j:   S_j = Q K_j^T          (M 128 x N 64 x K 128, 8 UMMAs), issued one block AHEAD of the softmax
+//                         softmax warps: tcgen05.ld S_j (64 registers), running max, P = exp2(S c - m c) -> 16 bit,
+//                                        written over S_j in TMEM (tcgen05.st, two values per column)
+//                         O += P V_j             (M 128 x N 128 x K 64, 4 UMMAs, A operand from TMEM, V MN-major in place)
+//   O never leaves TMEM during the loop: the running max is only raised when a row's new max exceeds it by more than
+//   2^8 (exponents stay representable either way), and only then is O read, scaled and written back — a rare event
+//   after the first blocks of a row. The tensor pipe therefore sees QK(j+1), PV(j), QK(j+2), ... back to back while the
+//   softmax warps work on block j, and the second resident CTA fills the remaining bubbles.
+//   B200_FLASH_TC_PSMEM=1 selects the variant that hands P over through a 128B-swizzled shared-memory tile instead.
 //
 // Replaces the mma.sync kernel of flash_attn.cu for head_dim 128 forward passes (training forward, prefill); that
 // kernel stays for other head sizes, dropout and the backward pass. Reference call sites: SDPA behind
@@ -23,6 +23,7 @@
 #include "../include/b200_ops.h"
 
 #include <stdio.h>
+#include <stdlib.h>
 
 namespace b200 {
 
@@ -31,7 +32,7 @@ constexpr int kTcThreads = 256;
 constexpr uint32_t kTcQBytes = 32768, kTcKVStage = 16384, kTcPBytes = 16384;
 constexpr uint32_t kTcSmemQ = 0, kTcSmemK = 32768, kTcSmemV = 65536, kTcSmemP = 98304, kTcSmemBar = 114688;
 constexpr uint32_t kTcSmemBytes = kTcSmemBar + 256;
-constexpr uint32_t kTcTmemCols = 256, kTcTmemO = 64;
+constexpr uint32_t kTcTmemCols = 256, kTcTmemO = 128;
 
 struct FlashTcParams {
   void* out;
@@ -48,7 +49,25 @@ __device__ __forceinline__ float ex2f(float x) {
   return y;
 }
 
+// D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (P, 16-bit, row = lane, two k values per column) comes from TMEM.
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 template <bool BF16>
+__device__ __forceinline__ uint32_t pack16(float a, float b) {
+  if (BF16) return pack_bf16x2(a, b);
+  const __half2 hh = __floats2half2_rn(a, b);
+  return *reinterpret_cast<const uint32_t*>(&hh);
+}
+
+// PT: P goes to the PV product through TMEM (over S); otherwise through the shared-memory tile at kTcSmemP.
+template <bool BF16, bool PT>
 __global__ void __launch_bounds__(kTcThreads, 2)
 flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm, const FlashTcParams p) {
   extern __shared__ __align__(1024) uint8_t smem_tc[];
@@ -66,18 +85,18 @@ flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm, const FlashTcParams 
   const int nblk = (kv_end + kTcBN - 1) / kTcBN;
 
   const uint32_t bar = sbase + kTcSmemBar;
-  const uint32_t q_full = bar, kv_full0 = bar + 8, kv_empty0 = bar + 24, s_full = bar + 40, s_free = bar + 48,
-                 p_full = bar + 56, o_full = bar + 64, o_free = bar + 72, tmem_slot = bar + 80;
+  const uint32_t q_full = bar, kv_full0 = bar + 8, kv_empty0 = bar + 24, s_full0 = bar + 40, s_free0 = bar + 56,
+                 p_full = bar + 72, o_done = bar + 80, tmem_slot = bar + 96;
   if (threadIdx.x == 0) {
     if (sbase & 1023u) { printf("flash_tc: shared memory base is not 1024-byte aligned\n"); __trap(); }
     tma_prefetch_desc(&tm);
     mbar_init(q_full, 1);
-    for (int s = 0; s < 2; ++s) { mbar_init(kv_full0 + 8 * s, 1); mbar_init(kv_empty0 + 8 * s, 1); }
-    mbar_init(s_full, 1);
-    mbar_init(s_free, 4);
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(kv_full0 + 8 * s, 1); mbar_init(kv_empty0 + 8 * s, 1);
+      mbar_init(s_full0 + 8 * s, 1); mbar_init(s_free0 + 8 * s, 4);
+    }
     mbar_init(p_full, 4);
-    mbar_init(o_full, 1);
-    mbar_init(o_free, 4);
+    mbar_init(o_done, 1);
     fence_mbar_init();
   }
   if (warp == 5) { tmem_alloc(tmem_slot, kTcTmemCols); tmem_relinquish(); }
@@ -87,9 +106,8 @@ flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm, const FlashTcParams 
   uint32_t tmem_base;
   asm volatile("ld.shared.u32 %0, [%1];" : "=r"(tmem_base) : "r"(tmem_slot));
 
-  if (warp >= 4) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
-    if (warp == 4 && lane == 0) {
+  if (warp == 4) {
+    if (lane == 0) {
       // ---- Q: two 64-column halves, each 128 rows (two 64-row boxes stacked = one K-major 128B-swizzled tile) ----
       mbar_arrive_expect_tx(q_full, kTcQBytes);
       for (int half = 0; half < 2; ++half)
@@ -105,7 +123,9 @@ flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm, const FlashTcParams 
           tma_load_2d(sbase + kTcSmemV + s * kTcKVStage + half * 8192, &tm, kv_full0 + 8 * s, vcol + half * 64, r);
         }
       }
-    } else if (warp == 5 && lane == 0) {
+    }
+  } else if (warp == 5) {
+    if (lane == 0) {
       // descriptors: hi word = SBO 1024 | version 1 | 128B swizzle; lo word = address >> 4 (| LBO << 16 for MN-major)
       constexpr uint32_t kHi = (1024u >> 4) | (1u << 14) | (kSwizzle128B << 29);
       constexpr uint32_t kLoK = (16u >> 4) << 16, kLoMN = (8192u >> 4) << 16;
@@ -121,9 +141,9 @@ flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm, const FlashTcParams 
         for (int half = 0; half < 2; ++half)
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks)
-            umma_f16(tS, desc(qlo + half * (16384u >> 4) + ks * 2u), desc(klo + half * (8192u >> 4) + ks * 2u), idesc_qk,
-                     (half | ks) ? 1u : 0u);
-        umma_commit(s_full);
+            umma_f16(tS + s * kTcBN, desc(qlo + half * (16384u >> 4) + ks * 2u), desc(klo + half * (8192u >> 4) + ks * 2u),
+                     idesc_qk, (half | ks) ? 1u : 0u);
+        umma_commit(s_full0 + 8 * s);
       };
       mbar_wait(q_full, 0);
       mbar_wait(kv_full0, 0);
@@ -133,129 +153,148 @@ flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm, const FlashTcParams 
         const int s = j & 1;
         if (j + 1 < nblk) {
           mbar_wait(kv_full0 + 8 * ((j + 1) & 1), ((uint32_t)(j + 1) >> 1) & 1u);
-          mbar_wait(s_free, (uint32_t)j & 1u);            // the softmax warps hold S(j) in registers
+          // S buffer (j+1)&1 last held block j-1. PT: P(j-1) sat in it and PV(j-1) was issued before this UMMA, the pipe
+          // runs in order. Otherwise: the softmax warps have pulled S(j-1) into registers.
+          if (!PT && j >= 1) mbar_wait(s_free0 + 8 * ((j + 1) & 1), ((uint32_t)(j - 1) >> 1) & 1u);
           tc_fence_after();
           issue_qk(j + 1);
         }
-        mbar_wait(p_full, (uint32_t)j & 1u);               // P(j) is in shared memory
-        mbar_wait(o_free, ((uint32_t)j & 1u) ^ 1u);        // PV(j-1) has been read out of TMEM
+        mbar_wait(p_full, (uint32_t)j & 1u);               // P(j) is written (and O rescaled where a row needed it)
         tc_fence_after();
         const uint32_t vlo = ((sbase + kTcSmemV + s * kTcKVStage) >> 4) | kLoMN;
 #pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-          umma_f16(tO, desc(plo + ks * 2u), desc(vlo + ks * (2048u >> 4)), idesc_pv, ks ? 1u : 0u);
-        umma_commit(o_full);
+        for (int ks = 0; ks < 4; ++ks) {
+          if (PT) umma_f16_ts(tO, tS + s * kTcBN + ks * 8, desc(vlo + ks * (2048u >> 4)), idesc_pv, (j | ks) ? 1u : 0u);
+          else umma_f16(tO, desc(plo + ks * 2u), desc(vlo + ks * (2048u >> 4)), idesc_pv, (j | ks) ? 1u : 0u);
+        }
+        umma_commit(o_done);
         umma_commit(kv_empty0 + 8 * s);
       }
     }
-  } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;");
-    // ================= softmax / accumulation: thread = query row =================
+  } else if (warp < 4) {
+    // ================= softmax: thread = query row =================
     const int q = warp;                             // TMEM lane quarter this warp may touch (warp index mod 4)
     const int r = q * 32 + lane;                    // row inside the tile
     const int grow = q0 + r;                        // position in the sequence
     const uint32_t lane_addr = (uint32_t)(q * 32) << 16;
     const uint32_t tS = tmem_base + lane_addr, tO = tmem_base + lane_addr + kTcTmemO;
     const float sl = p.scale_log2;
-    float O[kTcD];
-#pragma unroll
-    for (int i = 0; i < kTcD; ++i) O[i] = 0.f;
-    float m = -INFINITY, l = 0.f;
+    const int lim = p.causal ? min(grow, S - 1) : S - 1;      // last visible key of this row
+    float m_ref = -INFINITY, l = 0.f;
+    uint32_t v[64];
     for (int j = 0; j < nblk; ++j) {
-      const int kv0 = j * kTcBN;
+      const int kv0 = j * kTcBN, sb = j & 1;
       const bool need_mask = (p.causal && kv0 + kTcBN - 1 > q0) || (kv0 + kTcBN > S);
-      const int lim = p.causal ? min(grow, S - 1) : S - 1;      // last visible key of this row
-      mbar_wait(s_full, (uint32_t)j & 1u);
+      mbar_wait_warp(s_full0 + 8 * sb, ((uint32_t)j >> 1) & 1u);
       tc_fence_after();
-      // pass 1: row maximum (S is read twice out of TMEM instead of held in 64 registers next to the 128 of O)
+      tmem_ld_32x32(tS + sb * kTcBN, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+      tmem_ld_32x32(tS + sb * kTcBN + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+      tmem_ld_wait();
+      if (!PT) {
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_free0 + 8 * sb);
+      }
       float mx = -INFINITY;
-      uint32_t v[32];
+      if (need_mask) {
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_32x32(tS + c * 32, v);
-        tmem_ld_wait();
+        for (int i = 0; i < 64; ++i)
+          if (kv0 + i > lim) v[i] = 0xff800000u;    // -inf
+      }
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          float x = __uint_as_float(v[i]);
-          if (need_mask && kv0 + c * 32 + i > lim) x = -INFINITY;
-          mx = fmaxf(mx, x);
+      for (int i = 0; i < 64; ++i) mx = fmaxf(mx, __uint_as_float(v[i]));
+      const float m_new = fmaxf(m_ref, mx * sl);
+      // raise the reference max only when it is off by more than 2^8: exp2 of at most 8 stays exact enough in 16 bits
+      const bool raise = m_new > m_ref + 8.f;
+      float alpha = 1.f;
+      if (raise) { alpha = ex2f(m_ref - m_new); m_ref = m_new; }
+      const float m_use = (m_ref == -INFINITY) ? 0.f : m_ref;
+      const bool any_raise = j > 0 && __any_sync(0xffffffffu, raise);
+      if (j > 0 && (!PT || any_raise)) {            // PV(j-1) complete: O is stable (and the shared P tile is free)
+        mbar_wait_warp(o_done, (uint32_t)(j - 1) & 1u);
+        tc_fence_after();
+      }
+      if (any_raise) {
+        uint32_t o[32];
+#pragma unroll 1
+        for (int c = 0; c < 4; ++c) {
+          tmem_ld_32x32(tO + c * 32, o);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st_32x32(tO + c * 32, o);
         }
       }
-      const float m_new = fmaxf(m, mx * sl);
-      const float m_use = (m_new == -INFINITY) ? 0.f : m_new;    // a row that sees no key yet (only possible beyond S)
-      const float alpha = ex2f(m - m_use);
-      float rs = 0.f;
-      const uint32_t prow = sbase + kTcSmemP + (uint32_t)r * 128u;
-      // pass 2: probabilities -> 16-bit, straight into the swizzled A tile of the PV product
+      l *= alpha;
+      float rs0 = 0.f, rs1 = 0.f;
+      const float nm = -m_use;
+      if (PT) {
+        uint32_t w[32];
 #pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        tmem_ld_32x32(tS + c * 32, v);
-        tmem_ld_wait();
-        if (c == 1) {                                   // S(j) is not needed in TMEM any more: the next QK may overwrite it
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(s_free);
+        for (int i = 0; i < 32; ++i) {
+          const float p0 = ex2f(fmaf(__uint_as_float(v[2 * i]), sl, nm)), p1 = ex2f(fmaf(__uint_as_float(v[2 * i + 1]), sl, nm));
+          rs0 += p0; rs1 += p1;
+          w[i] = pack16<BF16>(p0, p1);
         }
+        tmem_st_32x32(tS + sb * kTcBN, w);
+        tmem_st_wait();
+        tc_fence_before();
+      } else {
+        const uint32_t prow = sbase + kTcSmemP + (uint32_t)r * 128u;
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
+        for (int g = 0; g < 8; ++g) {
           uint32_t o[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) {
             const int i0 = g * 8 + e * 2;
-            float x0 = __uint_as_float(v[i0]) * sl - m_use, x1 = __uint_as_float(v[i0 + 1]) * sl - m_use;
-            if (need_mask) {
-              if (kv0 + c * 32 + i0 > lim) x0 = -INFINITY;
-              if (kv0 + c * 32 + i0 + 1 > lim) x1 = -INFINITY;
-            }
-            const float p0 = ex2f(x0), p1 = ex2f(x1);
-            if (BF16) o[e] = pack_bf16x2(p0, p1);
-            else { const __half2 hh = __floats2half2_rn(p0, p1); o[e] = *reinterpret_cast<const uint32_t*>(&hh); }
-            // the row sum uses the rounded probabilities, i.e. exactly what the tensor core multiplies
-            float2 f;
-            if (BF16) f = unpack_bf16x2(o[e]);
-            else f = __half22float2(*reinterpret_cast<const __half2*>(&o[e]));
-            rs += f.x + f.y;
+            const float p0 = ex2f(fmaf(__uint_as_float(v[i0]), sl, nm)), p1 = ex2f(fmaf(__uint_as_float(v[i0 + 1]), sl, nm));
+            rs0 += p0; rs1 += p1;
+            o[e] = pack16<BF16>(p0, p1);
           }
-          const uint32_t chunk = (uint32_t)(c * 4 + g);
-          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(prow + ((chunk ^ ((uint32_t)r & 7u)) << 4)), "r"(o[0]),
-                       "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
+          asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(prow + (((uint32_t)g ^ ((uint32_t)r & 7u)) << 4)),
+                       "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
         }
+        if (any_raise) tmem_st_wait();
+        tc_fence_before();
+        fence_proxy_async_smem();                        // generic-proxy stores -> visible to tcgen05.mma
       }
-      fence_proxy_async_smem();                          // generic-proxy stores -> visible to tcgen05.mma
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
-      l = l * alpha + rs;
-      m = m_use;
-      // O = O * alpha + PV(j)
-      mbar_wait(o_full, (uint32_t)j & 1u);
-      tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 4; ++c) {
-        tmem_ld_32x32(tO + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) O[c * 32 + i] = O[c * 32 + i] * alpha + __uint_as_float(v[i]);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(o_free);
+      l += rs0 + rs1;
     }
-    // ---- finish: O / l -> 16 bit, lse ----
-    if (grow < S) {
-      const float inv = l > 0.f ? 1.f / l : 0.f;
-      uint16_t* orow = reinterpret_cast<uint16_t*>(p.out) + (long long)(row_base + grow) * p.out_rs + (long long)h * kTcD;
+    // ---- finish: O / l -> 16 bit through shared memory (the Q tile is dead: every QK product has completed) ----
+    mbar_wait_warp(o_done, (uint32_t)(nblk - 1) & 1u);
+    tc_fence_after();
+    const float inv = l > 0.f ? 1.f / l : 0.f;
+    const uint32_t orow = sbase + kTcSmemQ + (uint32_t)r * 256u;
+#pragma unroll 1
+    for (int c = 0; c < 4; ++c) {
+      uint32_t o[32];
+      tmem_ld_32x32(tO + c * 32, o);
+      tmem_ld_wait();
 #pragma unroll
-      for (int c = 0; c < kTcD / 8; ++c) {
-        uint32_t o[4];
+      for (int g = 0; g < 4; ++g) {
+        uint32_t w[4];
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float a0 = O[c * 8 + e * 2] * inv, a1 = O[c * 8 + e * 2 + 1] * inv;
-          if (BF16) o[e] = pack_bf16x2(a0, a1);
-          else { const __half2 hh = __floats2half2_rn(a0, a1); o[e] = *reinterpret_cast<const uint32_t*>(&hh); }
-        }
-        reinterpret_cast<uint4*>(orow)[c] = make_uint4(o[0], o[1], o[2], o[3]);
+        for (int e = 0; e < 4; ++e)
+          w[e] = pack16<BF16>(__uint_as_float(o[g * 8 + e * 2]) * inv, __uint_as_float(o[g * 8 + e * 2 + 1]) * inv);
+        const uint32_t chunk = (uint32_t)(c * 4 + g);
+        asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(orow + ((chunk ^ ((uint32_t)r & 15u)) << 4)), "r"(w[0]),
+                     "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
       }
-      if (p.lse) p.lse[((long long)b * p.H + h) * S + grow] = m * 0.6931471805599453f + __logf(l);
+    }
+    if (p.lse && grow < S) p.lse[((long long)b * p.H + h) * S + grow] = m_ref * 0.6931471805599453f + __logf(l);
+    __syncwarp();
+    // each warp copies ITS 32 rows out (written by its own lanes): 16 lanes cover the 256 bytes of a row
+    uint16_t* obase = reinterpret_cast<uint16_t*>(p.out) + (long long)h * kTcD;
+#pragma unroll 4
+    for (int it = 0; it < 16; ++it) {
+      const int rr = q * 32 + it * 2 + (lane >> 4), chunk = lane & 15;
+      uint32_t w0, w1, w2, w3;
+      asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3)
+                   : "r"(sbase + kTcSmemQ + (uint32_t)rr * 256u + (((uint32_t)chunk ^ ((uint32_t)rr & 15u)) << 4)));
+      if (q0 + rr < S)
+        *reinterpret_cast<uint4*>(obase + (long long)(row_base + q0 + rr) * p.out_rs + chunk * 8) = make_uint4(w0, w1, w2, w3);
     }
   }
   tc_fence_before();
@@ -287,16 +326,24 @@ B200_API int b200_flash_attn_fwd_tc(const void* qkv, void* out, float* lse, int 
   FlashTcParams p = {};
   p.out = out; p.lse = lse; p.B = B; p.S = S; p.H = H; p.Hkv = Hkv; p.out_rs = (long long)H * kTcD;
   p.scale_log2 = scale * 1.4426950408889634f; p.causal = causal; p.is_bf16 = dtype == B200_DT_BF16;
+  static const bool psmem = [] { const char* e = getenv("B200_FLASH_TC_PSMEM"); return e && atoi(e) != 0; }();
   static bool attr = false;
   if (!attr) {
-    B200_CHECK(cudaFuncSetAttribute(flash_fwd_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
-    B200_CHECK(cudaFuncSetAttribute(flash_fwd_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
+    B200_CHECK(cudaFuncSetAttribute(flash_fwd_tc_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
+    B200_CHECK(cudaFuncSetAttribute(flash_fwd_tc_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
+    B200_CHECK(cudaFuncSetAttribute(flash_fwd_tc_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
+    B200_CHECK(cudaFuncSetAttribute(flash_fwd_tc_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
     attr = true;
   }
   dim3 grid((S + kTcBM - 1) / kTcBM, H, B);
   cudaStream_t st = (cudaStream_t)stream;
-  if (p.is_bf16) flash_fwd_tc_kernel<true><<<grid, kTcThreads, kTcSmemBytes, st>>>(tm, p);
-  else flash_fwd_tc_kernel<false><<<grid, kTcThreads, kTcSmemBytes, st>>>(tm, p);
+  if (psmem) {
+    if (p.is_bf16) flash_fwd_tc_kernel<true, false><<<grid, kTcThreads, kTcSmemBytes, st>>>(tm, p);
+    else flash_fwd_tc_kernel<false, false><<<grid, kTcThreads, kTcSmemBytes, st>>>(tm, p);
+  } else {
+    if (p.is_bf16) flash_fwd_tc_kernel<true, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(tm, p);
+    else flash_fwd_tc_kernel<false, true><<<grid, kTcThreads, kTcSmemBytes, st>>>(tm, p);
+  }
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -389,15 +389,18 @@ def test_flash_attention(H, Hkv, D, S, dtype, causal):
 
 
 @pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("gain", [1.0, 3.0])
 @pytest.mark.parametrize("H,Hkv,S,dtype", [(8, 2, 512, torch.bfloat16), (4, 4, 77, torch.float16), (5, 1, 200, torch.bfloat16),
                                            (2, 2, 1000, torch.bfloat16), (2, 1, 128, torch.float16), (3, 3, 64, torch.bfloat16)])
-def test_flash_attention_tcgen05_forward(H, Hkv, S, dtype, causal, monkeypatch):
+def test_flash_attention_tcgen05_forward(H, Hkv, S, dtype, causal, gain, monkeypatch):
     """csrc/flash_tc.cu (tcgen05 / TMEM / TMA forward, head_dim 128): context vs the fp32 reference, log-sum-exp vs the
-    mma.sync kernel (the backward kernel consumes it), sequence lengths that do not fill the 128 x 64 tiles, GQA."""
+    mma.sync kernel (the backward kernel consumes it), sequence lengths that do not fill the 128 x 64 tiles, GQA.
+    gain 3 spreads the scores over ~±40 (log2 units), so the running maximum is raised in late key blocks too and the
+    O accumulator in TMEM is rescaled there."""
     from llm_in_practise_b200.ops import flash as FL
     B, D = 2, 128
     torch.manual_seed(S * 3 + H)
-    qkv = torch.randn(B * S, (H + 2 * Hkv) * D, device=DEV, dtype=dtype)
+    qkv = (torch.randn(B * S, (H + 2 * Hkv) * D, device=DEV) * gain).to(dtype)
     monkeypatch.setattr(FL, "_TC", True)
     out, lse = FL._fwd(qkv, B, S, H, Hkv, D, causal, D ** -0.5, True)
     monkeypatch.setattr(FL, "_TC", False)
