@@ -100,6 +100,77 @@ allreduce_kernel(PeerPtrs data, PeerPtrs flags, PeerPtrs lowp, long long n, int 
 }
 
 // ---------------------------------------------------------------------------------------------
+// K-C1 through the switch (NVLS): the same two-shot shape, but the reduction happens INSIDE NVSwitch. `mc` is the
+// multicast address of the symmetric buffer: multimem.ld_reduce returns the sum of all ranks' copies of a 16-byte
+// vector in one NVLink read, multimem.st writes the result to every rank in one NVLink write. A rank moves 2 n / W
+// bytes over its links instead of the 2 n (W - 1) / W of the peer-pointer kernel above. fp32 (gradient buckets; an
+// optional 16-bit copy of the result is multicast too) or bf16 with fp32 accumulation in the switch (activations of
+// tensor-parallel prefill).
+// ---------------------------------------------------------------------------------------------
+template <bool BF16>
+__device__ __forceinline__ uint4 multimem_ld_reduce(const void* mc_addr) {
+  uint4 v;
+  if (BF16)
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc_addr) : "memory");
+  else
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(mc_addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st16(void* mc_addr, uint4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void multimem_st8(void* mc_addr, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.f32 [%0], {%1, %2};" ::"l"(mc_addr), "r"(v.x), "r"(v.y) : "memory");
+}
+
+template <bool BF16>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_nvls_kernel(uint4* __restrict__ mc, PeerPtrs flags, uint2* __restrict__ lowp_mc, long long nvec, int world, int rank,
+                      uint32_t epoch, float scale, unsigned int* grid_ctr, unsigned int grid_target) {
+  if (blockIdx.x == 0) signal_all(flags, 0, world, rank, epoch);
+  wait_all(flags, 0, world, rank, epoch);
+  const long long per = (nvec + world - 1) / world;
+  const long long lo = per * rank, hi = min(nvec, lo + per);
+  constexpr int U = 4;
+  const long long step = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < hi; i0 += step * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * step;
+      if (i < hi) v[u] = multimem_ld_reduce<BF16>(mc + i);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = i0 + u * step;
+      if (i >= hi) break;
+      if (BF16) {
+        if (scale != 1.f) {
+          uint32_t* w = reinterpret_cast<uint32_t*>(&v[u]);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) { const float2 f = unpack_bf16x2(w[e]); w[e] = pack_bf16x2(f.x * scale, f.y * scale); }
+        }
+        multimem_st16(mc + i, v[u]);
+      } else {
+        float4 a = *reinterpret_cast<float4*>(&v[u]);
+        a.x *= scale; a.y *= scale; a.z *= scale; a.w *= scale;
+        multimem_st16(mc + i, *reinterpret_cast<uint4*>(&a));
+        if (lowp_mc) multimem_st8(lowp_mc + i, make_uint2(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w)));
+      }
+    }
+  }
+  __threadfence_system();
+  grid_barrier(grid_ctr, grid_target);
+  if (blockIdx.x == 0) {
+    signal_all(flags, 1, world, rank, epoch);
+    wait_all(flags, 1, world, rank, epoch);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
 // K-C5 (decode): one-shot all-reduce (sum) of a small 16-bit activation [tokens, hidden] for tensor-parallel decode.
 // Everything the kernel needs between launches lives on the device (state[0] = epoch, state[1] = grid-barrier ticket,
 // state[2] = exit ticket), so the same launch can be replayed from a CUDA graph on every rank — the two-shot kernel
@@ -493,6 +564,30 @@ B200_API int b200_allreduce(const void* const* data_ptrs, const void* const* fla
   return 0;
 }
 
+
+// NVLS flavour of b200_allreduce. mc_ptr: multicast address of the symmetric buffer at the reduced offset (fp32, or bf16
+// with dtype = B200_DT_BF16); lowp_mc_ptr: multicast address of a bf16 copy of the result (fp32 only, may be NULL).
+// n elements, a multiple of 4 (fp32) / 8 (bf16); both addresses 16-byte aligned.
+B200_API int b200_allreduce_nvls(void* mc_ptr, const void* const* flag_ptrs, void* lowp_mc_ptr, long long n, int world,
+                                 int rank, unsigned int epoch, float scale, int dtype, unsigned int* grid_ctr,
+                                 unsigned int grid_target_base, int grid, void* stream) {
+  const bool bf16 = dtype == B200_DT_BF16;
+  if (!bf16 && dtype != B200_DT_FP32) return B200_ERR_UNSUPPORTED;
+  if (world < 1 || world > kMaxRanks || n % (bf16 ? 8 : 4) || !mc_ptr) return B200_ERR_BAD_SHAPE;
+  if ((reinterpret_cast<uintptr_t>(mc_ptr) | reinterpret_cast<uintptr_t>(lowp_mc_ptr)) & 15) return B200_ERR_BAD_ALIGN;
+  if (grid < 1) grid = 1;
+  const long long nvec = n / (bf16 ? 8 : 4);
+  if (bf16)
+    allreduce_nvls_kernel<true><<<grid, kCommThreads, 0, (cudaStream_t)stream>>>(
+        (uint4*)mc_ptr, to_peers(flag_ptrs, world), nullptr, nvec, world, rank, epoch, scale, grid_ctr,
+        grid_target_base + (unsigned int)grid);
+  else
+    allreduce_nvls_kernel<false><<<grid, kCommThreads, 0, (cudaStream_t)stream>>>(
+        (uint4*)mc_ptr, to_peers(flag_ptrs, world), (uint2*)lowp_mc_ptr, nvec, world, rank, epoch, scale, grid_ctr,
+        grid_target_base + (unsigned int)grid);
+  B200_LAUNCH_CHECK();
+  return 0;
+}
 
 B200_API int b200_zero_step(const b200_zero_step_args* a, void* stream) {
   if (a->world < 1 || a->world > kMaxRanks) return B200_ERR_BAD_SHAPE;

@@ -58,6 +58,18 @@ struct GemmKernelParams {
   unsigned int* sk_flags;
   unsigned int sk_epoch;      // host-provided epoch (used when sk_state is null)
   unsigned int* sk_state;     // device epoch: [0] = epoch of the last stream-K launch, [1] = ticket counter (graph-replayable)
+  // K-C5: all-reduce of D over the tensor-parallel ranks inside this launch (row-parallel projection). D is every rank's
+  // copy of one symmetric bf16 buffer and ar_mc its multicast address. A finished tile is announced to its owner rank
+  // (tile % world) with an epoch flag per (tile, CTA of the pair, source rank); once a CTA has no GEMM tile left, its
+  // epilogue warps take the owned tiles whose partials have arrived from every rank and sum them IN PLACE inside NVSwitch
+  // (multimem.ld_reduce of the W copies, multimem.st of the sum back to all of them). The last CTA of a rank then tells
+  // the peers that this rank's share is reduced and waits for theirs, so the launch ends with D complete everywhere.
+  int ar_world, ar_rank, ar_channel;
+  unsigned int ar_epoch;
+  char* ar_mc;
+  unsigned int* ar_tile_flags[8];   // per rank: uint32 [tile][2][8]
+  unsigned int* ar_sync[8];         // per rank: uint32 [channel][8] epoch flags
+  unsigned int* ar_ticket;          // local ticket counter (returns to 0)
 };
 
 // Fused 4-bit B operand (W4 = true instantiation): the weight matrix W [rows, kw] is stored packed (two codes per
@@ -662,6 +674,88 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;
+      if (p.ar_world > 1) {
+        // this CTA's rows of the tile are in D: one system-scope fence + release by one thread covers the stores the
+        // other epilogue threads made before the barrier
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (threadIdx.x == 64) {
+          __threadfence_system();
+          unsigned int* f = p.ar_tile_flags[tile % p.ar_world] + ((long long)(tile * 2 + (int)rank) * 8 + p.ar_rank);
+          asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(p.ar_epoch) : "memory");
+        }
+      }
+    }
+    if (p.ar_world > 1) {
+      // ---- reduce the tiles this rank owns (in place, inside the switch), then the cross-rank completion barrier ----
+      const int et = (int)threadIdx.x - 64;     // 0..127
+      const int W = p.ar_world;
+      const int n_owned = (total_tiles - p.ar_rank + W - 1) / W;
+      for (int k = blockIdx.x; k < n_owned; k += gridDim.x) {
+        const int tile = k * W + p.ar_rank;
+        if (et < CTAS * W) {
+          const unsigned int* f = p.ar_tile_flags[p.ar_rank] + ((long long)(tile * 2 + et / W) * 8 + et % W);
+          unsigned int seen;
+          const long long tw = clock64();
+          do {
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+            if (clock64() - tw > 20000000000ll) {
+              printf("b200 gemm+allreduce: rank %d timed out waiting for tile %d of rank %d\n", p.ar_rank, tile, et % W);
+              __trap();
+            }
+          } while ((int)(seen - p.ar_epoch) < 0);
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int n_blk = tile / p.num_m, m_blk = tile - n_blk * p.num_m;
+        const int m0 = m_blk * (kBM * CTAS), n0 = n_blk * p.bn;
+        const int rows = min(kBM * CTAS, p.M - m0);
+        const int vpr = (min(p.N, n0 + p.bn) - n0) / 8;            // 16-byte vectors per row (bf16)
+        const int nvec = rows * vpr;
+        char* base = p.ar_mc + ((long long)m0 * p.d_rs + n0) * 2;
+        constexpr int U = 8;
+        for (int v0 = et; v0 < nvec; v0 += 128 * U) {
+          uint4 x[U];
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int v = v0 + u * 128;
+            if (v < nvec) {
+              const char* a = base + (long long)(v / vpr) * p.d_rs * 2 + (v % vpr) * 16;
+              asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                           : "=r"(x[u].x), "=r"(x[u].y), "=r"(x[u].z), "=r"(x[u].w) : "l"(a) : "memory");
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < U; ++u) {
+            const int v = v0 + u * 128;
+            if (v < nvec) {
+              char* a = base + (long long)(v / vpr) * p.d_rs * 2 + (v % vpr) * 16;
+              asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a), "r"(x[u].x), "r"(x[u].y),
+                           "r"(x[u].z), "r"(x[u].w) : "memory");
+            }
+          }
+        }
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (et == 0) {
+        __threadfence_system();
+        if (atomicAdd(p.ar_ticket, 1u) == gridDim.x - 1) {
+          *((volatile unsigned int*)p.ar_ticket) = 0u;
+          __threadfence_system();
+          for (int r = 0; r < W; ++r)
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.ar_sync[r] + p.ar_channel * 8 + p.ar_rank), "r"(p.ar_epoch) : "memory");
+          for (int r = 0; r < W; ++r) {
+            const unsigned int* f = p.ar_sync[p.ar_rank] + p.ar_channel * 8 + r;
+            unsigned int seen;
+            const long long tw = clock64();
+            do {
+              asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+              if (clock64() - tw > 20000000000ll) {
+                printf("b200 gemm+allreduce: rank %d timed out waiting for rank %d to finish its share\n", p.ar_rank, r);
+                __trap();
+              }
+            } while ((int)(seen - p.ar_epoch) < 0);
+          }
+        }
+      }
     }
   }
 
@@ -833,7 +927,13 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   p.num_k = ceil_div(a->K, EPR);
   const int nkt = p.num_k + (lora ? 1 : 0);
   const long long sk_need = (long long)g_num_sms * kBM * kAccStride * 4 + (long long)g_num_sms * 4;
-  const bool allow_sk = a->workspace != nullptr && a->workspace_bytes >= sk_need;
+  const b200_gemm_allreduce* ar = a->ar;
+  if (ar) {
+    if (ar->world < 2 || ar->world > 8 || ar->rank < 0 || ar->rank >= ar->world || !ar->d_mc || !ar->ticket) return B200_ERR_BAD_SHAPE;
+    if (a->batch != 1 || a->out_dtype != B200_DT_BF16 || a->beta != 0.f || a->beta_rows) return B200_ERR_UNSUPPORTED;
+    if ((reinterpret_cast<uintptr_t>(a->D) | reinterpret_cast<uintptr_t>(ar->d_mc)) & 15 || a->d_rs % 8 || a->N % 8) return B200_ERR_BAD_ALIGN;
+  }
+  const bool allow_sk = !ar && a->workspace != nullptr && a->workspace_bytes >= sk_need;
   const GemmConfig cfg = pick_config(a->M, a->N, a->batch, nkt, p.b_mn, EPR, g_num_sms, allow_sk);
   const int ctas = cfg.ctas;
   p.bn = cfg.bn;
@@ -914,6 +1014,17 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   }
 
   const long long total_tiles = (long long)p.num_m * p.num_n * p.batch;
+  p.ar_world = 0; p.ar_rank = 0; p.ar_channel = 0; p.ar_epoch = 0; p.ar_mc = nullptr; p.ar_ticket = nullptr;
+  for (int r = 0; r < 8; ++r) { p.ar_tile_flags[r] = nullptr; p.ar_sync[r] = nullptr; }
+  if (ar) {
+    if (total_tiles > ar->max_tiles) return B200_ERR_TOO_LARGE;
+    p.ar_world = ar->world; p.ar_rank = ar->rank; p.ar_channel = ar->channel; p.ar_epoch = ar->epoch;
+    p.ar_mc = reinterpret_cast<char*>(ar->d_mc); p.ar_ticket = ar->ticket;
+    for (int r = 0; r < ar->world; ++r) {
+      p.ar_tile_flags[r] = reinterpret_cast<unsigned int*>(const_cast<void*>(ar->tile_flag_ptrs[r]));
+      p.ar_sync[r] = reinterpret_cast<unsigned int*>(const_cast<void*>(ar->sync_flag_ptrs[r]));
+    }
+  }
   const int units = g_num_sms / ctas;
   const int grid = (cfg.stream_k ? units : (int)(total_tiles < units ? total_tiles : units)) * ctas;
   const int smem = stages * stage_bytes + 8 * (2 * stages + 5) + 1024;

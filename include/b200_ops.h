@@ -75,7 +75,27 @@ typedef struct {
   /* Optional per-row beta (float[M], batch 1 only): D[m, :] = alpha * acc + beta_rows[m] * D[m, :]. The running
    * rescale of the online-softmax lm_head + cross-entropy (flash-attention style accumulation over vocabulary chunks). */
   const float* beta_rows;
+  /* Optional: all-reduce D over tensor-parallel ranks inside the same launch (see b200_gemm_allreduce below); b200_gemm only. */
+  const struct b200_gemm_allreduce* ar;
 } b200_gemm_args;
+
+/* K-C5: row-parallel projection + all-reduce in ONE launch (y = sum over ranks of x_r W_r^T — o_proj / down_proj under
+ * vLLM's --tensor-parallel-size, Quantization/README.md:175; Deployment/Ray/serve_deploy_examples/*.yaml). Every rank calls
+ * b200_gemm with D = its copy of one symmetric bf16 buffer (same offset everywhere, batch 1, 16-byte aligned rows) and
+ * this descriptor. Tiles are announced to their owner rank as they finish; CTAs that have run out of GEMM tiles sum the
+ * owned tiles in place inside NVSwitch (multimem.ld_reduce / multimem.st on d_mc, fp32 accumulation) while other CTAs
+ * are still multiplying; the launch returns with the full sum in every rank's D. All ranks must launch it (bounded
+ * waits trap otherwise). tile_flag_ptrs[r]: uint32 [max_tiles * 16] on rank r (zero-initialised once); sync_flag_ptrs[r]:
+ * uint32 [channels][8] epoch flags on rank r; ticket: one local zero-initialised uint32; epoch: grows by >= 1 per call. */
+typedef struct b200_gemm_allreduce {
+  void* d_mc;                          /* multicast address of D */
+  const void* const* tile_flag_ptrs;   /* [world] */
+  const void* const* sync_flag_ptrs;   /* [world] */
+  unsigned int* ticket;
+  int32_t world, rank, channel;
+  uint32_t epoch;
+  int64_t max_tiles;
+} b200_gemm_allreduce;
 
 long long b200_gemm_workspace_bytes(void);
 
@@ -253,6 +273,13 @@ int b200_lora_dx(const void* dT, const void* A, void* dX, int M, int K, int r, l
 int b200_allreduce(const void* const* data_ptrs, const void* const* flag_ptrs, const void* const* lowp_ptrs,
                    long long n, int world, int rank, unsigned int epoch, float scale, unsigned int* grid_ctr,
                    unsigned int grid_target_base, int grid, void* stream);
+/* The same all-reduce with the reduction done by NVSwitch (NVLS): mc_ptr is the MULTICAST address of the symmetric buffer
+ * (torch symmetric memory: handle.multicast_ptr + byte offset). multimem.ld_reduce / multimem.st: 2 n / W bytes per rank
+ * over NVLink instead of 2 n (W - 1) / W. dtype B200_DT_FP32 (n % 4 == 0; lowp_mc_ptr = multicast address of an optional
+ * bf16 copy of the result) or B200_DT_BF16 (n % 8 == 0, fp32 accumulation in the switch, lowp_mc_ptr ignored). */
+int b200_allreduce_nvls(void* mc_ptr, const void* const* flag_ptrs, void* lowp_mc_ptr, long long n, int world, int rank,
+                        unsigned int epoch, float scale, int dtype, unsigned int* grid_ctr, unsigned int grid_target_base,
+                        int grid, void* stream);
 
 typedef struct {
   const void* const* grad_ptrs;

@@ -14,6 +14,7 @@ of its communication is implicit inside DDP / FSDP / DeepSpeed
 from __future__ import annotations
 
 import ctypes
+import os
 from typing import List, Optional
 
 import torch
@@ -136,14 +137,44 @@ def peer_gather_ce(src: SymmBuffer, out: torch.Tensor, src_off_bytes: int, shard
     return out
 
 
+def nvls_enabled(*bufs: Optional[SymmBuffer]) -> bool:
+    """True when every given buffer has a multicast (NVLS) address and B200_NVLS is not 0."""
+    if os.environ.get("B200_NVLS", "1") == "0":
+        return False
+    return all(b is None or getattr(b, "multicast_ptr", 0) for b in bufs)
+
+
 def allreduce_(buf: SymmBuffer, flags: PeerFlags, offset: int, n: int, scale: float,
                lowp: Optional[SymmBuffer] = None, grid: int = 64) -> None:
-    """In-place average (``scale`` = 1/world) of fp32 ``buf[offset : offset+n]`` across ranks — K-C1."""
+    """In-place average (``scale`` = 1/world) of fp32 ``buf[offset : offset+n]`` across ranks — K-C1. With a multicast
+    address (NVLS) the reduction runs inside NVSwitch (``b200_allreduce_nvls``), otherwise over peer pointers."""
     vp, i32, i64, u32, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint, ctypes.c_float
-    fn = nv.proto("b200_allreduce", [vp, vp, vp, i64, i32, i32, u32, f32, vp, u32, i32, vp])
     grid = max(1, min(grid, (n // 4 + 255) // 256))
     base = flags.take_grid_target(grid, 1)
+    if nvls_enabled(buf, lowp) and (offset * 4) % 16 == 0:
+        fn = nv.proto("b200_allreduce_nvls", [vp, vp, vp, i64, i32, i32, u32, f32, i32, vp, u32, i32, vp])
+        lp = (lowp.multicast_ptr + offset * 2) if lowp is not None else None
+        nv.check(fn(buf.multicast_ptr + offset * 4, ctypes.cast(flags.flags.c_ptrs(), vp), lp, n, buf.world, buf.rank,
+                    flags.next_epoch(), scale, nv.dtype_code(torch.float32), nv.ptr(flags.grid_ctr), base, grid, nv.stream()),
+                 "allreduce_nvls")
+        nv.count_launch()
+        return
+    fn = nv.proto("b200_allreduce", [vp, vp, vp, i64, i32, i32, u32, f32, vp, u32, i32, vp])
     lp = ctypes.cast(lowp.c_ptrs(offset * 2), vp) if lowp is not None else None
     nv.check(fn(ctypes.cast(buf.c_ptrs(offset * 4), vp), ctypes.cast(flags.flags.c_ptrs(), vp), lp, n, buf.world, buf.rank,
                 flags.next_epoch(), scale, nv.ptr(flags.grid_ctr), base, grid, nv.stream()), "allreduce")
+    nv.count_launch()
+
+
+def allreduce_bf16_nvls_(buf: SymmBuffer, flags: PeerFlags, offset: int, n: int, scale: float = 1.0, grid: int = 64) -> None:
+    """In-place sum (times ``scale``) of bf16 ``buf[offset : offset+n]`` across ranks, reduced by the switch with fp32
+    accumulation. ``buf`` needs a multicast address; n % 8 == 0, offset % 8 == 0."""
+    vp, i32, i64, u32, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_uint, ctypes.c_float
+    assert buf.dtype == torch.bfloat16 and buf.multicast_ptr and n % 8 == 0 and offset % 8 == 0
+    grid = max(1, min(grid, (n // 8 + 255) // 256))
+    base = flags.take_grid_target(grid, 1)
+    fn = nv.proto("b200_allreduce_nvls", [vp, vp, vp, i64, i32, i32, u32, f32, i32, vp, u32, i32, vp])
+    nv.check(fn(buf.multicast_ptr + offset * 2, ctypes.cast(flags.flags.c_ptrs(), vp), None, n, buf.world, buf.rank,
+                flags.next_epoch(), scale, nv.dtype_code(torch.bfloat16), nv.ptr(flags.grid_ctr), base, grid, nv.stream()),
+             "allreduce_nvls")
     nv.count_launch()

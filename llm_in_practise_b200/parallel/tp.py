@@ -29,7 +29,7 @@ from ..ops import _native as nv
 from ..ops.linear import FusedLinear
 from ..ops.w4 import NF4Weight
 from .dist import get_info
-from .symm import PeerFlags, SymmBuffer, allreduce_, symm_available
+from .symm import PeerFlags, SymmBuffer, allreduce_, allreduce_bf16_nvls_, nvls_enabled, symm_available
 
 
 class TensorParallel:
@@ -72,6 +72,12 @@ class TensorParallel:
                      "allreduce_oneshot")
             nv.count_launch()
             return out
+        if y.dtype == torch.bfloat16 and n % 8 == 0 and nvls_enabled(self.lowp):
+            # prefill-sized bf16 activations: summed inside NVSwitch (multimem.ld_reduce, fp32 accumulation), 2 n / W
+            # bytes per rank on the wire
+            self.lowp.local[:n].view(y.shape).copy_(y)
+            allreduce_bf16_nvls_(self.lowp, self.flags, 0, n)
+            return self.lowp.local[:n].view(y.shape).clone()
         self.buf.local[:n].view(y.shape).copy_(y)                       # fp32 partial into the symmetric buffer
         allreduce_(self.buf, self.flags, 0, n, 1.0, lowp=self.lowp if y.dtype == torch.bfloat16 else None)
         src = self.lowp.local if y.dtype == torch.bfloat16 else self.buf.local

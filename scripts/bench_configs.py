@@ -25,6 +25,7 @@ ap.add_argument("--warmup", type=int, default=3)
 ap.add_argument("--batch", type=int, default=0)
 ap.add_argument("--stage", type=int, default=0)
 ap.add_argument("--layers", type=int, default=0)
+ap.add_argument("--wrapper", default="ddp", choices=["ddp", "fsdp"], help="gptlike / minigpt2: DDP (reference ddp_basics) or FSDP FULL_SHARD (fsdp_basics)")
 a = ap.parse_args()
 info = setup_distributed()
 rank, world, dev = info.rank, info.world_size, info.device
@@ -65,8 +66,18 @@ if a.config in ("gptlike-ddp", "minigpt2-ddp"):
         cfg = Config(vocab_size=4096)
         B, S, V = a.batch or 32, cfg.seq_len, 4096
         model = MiniGPT2(cfg, causal=True, dtype=torch.bfloat16, device=dev)
-    ddp = DDP(model, mixed_precision=torch.bfloat16)
-    opt = ddp.make_optimizer(lr=3e-4, weight_decay=0.01)
+    if a.wrapper == "fsdp":
+        # LLM_Distributed_Trainning/PyTorch/fsdp_basics/fsdp_gpt_wikitext2.py:278-312: FULL_SHARD, one unit per block, bf16
+        from llm_in_practise_b200.models.gpt import TransformerBlock
+        from llm_in_practise_b200.parallel.fsdp import (FullyShardedDataParallel as FSDP, MixedPrecision, ShardingStrategy,
+                                                        transformer_auto_wrap_policy)
+        ddp = FSDP(model, auto_wrap_policy=transformer_auto_wrap_policy(transformer_layer_cls={TransformerBlock}),
+                   sharding_strategy=ShardingStrategy.FULL_SHARD,
+                   mixed_precision=MixedPrecision(param_dtype=torch.bfloat16, reduce_dtype=torch.bfloat16, buffer_dtype=torch.bfloat16))
+        opt = torch.optim.AdamW(ddp.parameters(), lr=3e-4, weight_decay=0.01, fused=True)
+    else:
+        ddp = DDP(model, mixed_precision=torch.bfloat16)
+        opt = ddp.make_optimizer(lr=3e-4, weight_decay=0.01)
     gen = torch.Generator(device=dev).manual_seed(7 + rank)
     xs = [torch.randint(0, V, (B, S), device=dev, generator=gen) for _ in range(4)]
     k = [0]
@@ -82,8 +93,13 @@ if a.config in ("gptlike-ddp", "minigpt2-ddp"):
     ms = timed(step)
     n_params = sum(p.numel() for p in model.parameters())
     torch.cuda.synchronize()
-    exposed = ddp.exposed_ms[-a.steps:]
-    out["exposed_events"] = len(ddp._exposed_events)
+    if a.wrapper == "fsdp":
+        exposed = [ddp.exposed_ms() / (a.steps + a.warmup)] if ddp.use_symm else []
+        out["wrapper"], out["units"] = "fsdp-full-shard", len(ddp.units)
+        out["peak_mem_gb"] = round(torch.cuda.max_memory_allocated() / 2 ** 30, 2)
+    else:
+        exposed = ddp.exposed_ms[-a.steps:]
+        out["exposed_events"] = len(ddp._exposed_events)
     out.update({"metric": f"{a.config} train tok/s", "ms_per_step": round(ms, 3), "value": round(B * S * world / ms * 1e3, 1), "unit": "tokens/s",
                 "params_m": round(n_params / 1e6, 2), "grad_bytes_per_step": n_params * 4, "batch_per_gpu": B, "seq_len": S,
                 "exposed_allreduce_ms": round(sum(exposed) / max(len(exposed), 1), 3) if exposed else None,

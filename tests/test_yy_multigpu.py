@@ -51,6 +51,23 @@ def test_tp_oneshot_allreduce_eager_and_graph():
     assert r["eager_rel_err"] < 2e-2 and r["graph_rel_err"] < 3e-2 and r["ranks_identical"], r
 
 
+@pytest.mark.gpu
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_allreduce_peer_and_nvls_match_nccl():
+    """K-C1 both ways — peer-pointer two-shot kernel and the NVLS kernel (multimem.ld_reduce / multimem.st, reduction in
+    NVSwitch; fp32 with a bf16 copy, and bf16 with fp32 accumulation) — against ncclAllReduce of the same data. Skips the
+    NVLS half when symmetric memory reports no multicast address."""
+    import os, subprocess, sys, json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    n = _ngpu()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr",
+                          "127.0.0.1", "--master-port", "29633", os.path.join(root, "scripts", "bench_allreduce.py"),
+                          "--sizes-mib", "0.25,3", "--check-only"], capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    r = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1])
+    assert r["ok"], r
+
+
 # ------------------------------------------------------------------------------------------------------------------
 # fused collectives vs torch.distributed (NCCL), N-GPU vs 1-GPU, wrappers vs torch's own, injected rank skew.
 # scripts/check_multigpu.py runs every variant in ONE torchrun job per world size (module-scoped fixture below): a job per
@@ -119,6 +136,11 @@ def test_fused_collectives_match_nccl_path(runs, name, tol):
     a, b = runs["multi"][name + "_symm"], runs["multi"][name + "_nccl"]
     assert a["fused"] and not b["fused"] and a["ranks_identical"] and b["ranks_identical"]
     r = _rel(_params(runs, "multi", name + "_symm"), _params(runs, "multi", name + "_nccl"))
+    # fp32 sums over more than two ranks depend on the order (rank order here, in-switch order under NVLS, NCCL's tree);
+    # Adam turns a last-bit gradient difference into a parameter difference of a few 1e-5 of the largest weight after three
+    # steps (measured 3e-5 .. 6e-5 at 8 ranks). A lost or doubled contribution shows up as > 1e-2.
+    if runs["n"] > 2:
+        tol = max(tol, 2e-4)
     assert r < tol, r
 
 
