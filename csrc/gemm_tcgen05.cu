@@ -70,6 +70,7 @@ struct GemmKernelParams {
   unsigned int* ar_tile_flags[8];   // per rank: uint32 [tile][2][8]
   unsigned int* ar_sync[8];         // per rank: uint32 [channel][8] epoch flags
   unsigned int* ar_ticket;          // local ticket counter (returns to 0)
+  char* ar_d[2];                    // two ranks: both copies of D by peer pointer (ar_mc null)
 };
 
 // Fused 4-bit B operand (W4 = true instantiation): the weight matrix W [rows, kw] is stored packed (two codes per
@@ -213,6 +214,116 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
       }
     }
   }
+}
+
+// ---- K-C5: the all-reduce half of the fused row-parallel GEMM (called by the four epilogue warps, 128 threads) ----
+// A reduction item is a slab of kArSlabRows rows of a tile this rank owns (tile % world == rank); item i of the rank goes
+// to CTA i % gridDim.x. An item can be summed once every rank has announced the tile (both CTAs of a pair). With
+// `block` false the call returns at the first item that is not ready yet (it is made between two GEMM tiles, while the
+// tensor pipe works on the next one). The sum of the W copies of a 16-byte vector is taken inside NVSwitch
+// (multimem.ld_reduce, fp32 accumulation) and written back to every copy (multimem.st) when ar_mc is set and W > 2; with
+// two ranks plain peer loads / stores move the same bytes faster.
+constexpr int kArSlabRows = 32;
+
+template <int CTAS>
+__device__ __noinline__ int ar_reduce(const GemmKernelParams& p, int next, int n_items, int budget, bool block,
+                                         int total_tiles, uint32_t poll_slot) {
+  const int et = (int)threadIdx.x - 64;     // 0..127
+  const int W = p.ar_world;
+  constexpr int kSlabs = (kBM * CTAS) / kArSlabRows;
+  while (next < n_items && budget > 0) {
+    const int tile = (next / kSlabs) * W + p.ar_rank, slab = next % kSlabs;
+    // ---- have all ranks (and both CTAs of their pairs) stored this tile? ----
+    if (et < 32) {
+      bool ok = true;
+      if (et < CTAS * W) {
+        const unsigned int* f = p.ar_tile_flags[p.ar_rank] + ((long long)(tile * 2 + et / W) * 8 + et % W);
+        unsigned int seen;
+        const long long tw = clock64();
+        do {
+          asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
+          ok = (int)(seen - p.ar_epoch) >= 0;
+          if (block && !ok && clock64() - tw > 20000000000ll) {
+            printf("b200 gemm+allreduce: rank %d timed out waiting for tile %d (CTA %d of the pair) of rank %d: flag %u, epoch %u\n",
+                   p.ar_rank, tile, et / W, et % W, seen, p.ar_epoch);
+            __trap();
+          }
+        } while (block && !ok);
+      }
+      ok = __all_sync(0xffffffffu, ok);
+      if (et == 0) asm volatile("st.shared.u32 [%0], %1;" ::"r"(poll_slot), "r"(ok ? 1u : 0u) : "memory");
+    }
+    asm volatile("bar.sync 1, 128;" ::: "memory");
+    uint32_t ready;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(ready) : "r"(poll_slot) : "memory");
+    asm volatile("bar.sync 1, 128;" ::: "memory");      // everyone has read the verdict before the slot is rewritten
+    if (!ready) break;
+    const int n_blk = tile / p.num_m, m_blk = tile - n_blk * p.num_m;
+    const int m0 = m_blk * (kBM * CTAS) + slab * kArSlabRows, n0 = n_blk * p.bn;
+    const int rows = min(kArSlabRows, p.M - m0);
+    const int vpr = (min(p.N, n0 + p.bn) - n0) / 8;            // 16-byte vectors per row (bf16)
+    const int nvec = rows > 0 ? rows * vpr : 0;
+    const long long off0 = ((long long)m0 * p.d_rs + n0) * 2;
+    constexpr int U = 8;
+    if (p.ar_mc != nullptr) {
+      char* base = p.ar_mc + off0;
+      for (int v0 = et; v0 < nvec; v0 += 128 * U) {
+        uint4 x[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int v = v0 + u * 128;
+          if (v < nvec) {
+            const char* a = base + (long long)(v / vpr) * p.d_rs * 2 + (v % vpr) * 16;
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                         : "=r"(x[u].x), "=r"(x[u].y), "=r"(x[u].z), "=r"(x[u].w) : "l"(a) : "memory");
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int v = v0 + u * 128;
+          if (v < nvec) {
+            char* a = base + (long long)(v / vpr) * p.d_rs * 2 + (v % vpr) * 16;
+            asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a), "r"(x[u].x), "r"(x[u].y),
+                         "r"(x[u].z), "r"(x[u].w) : "memory");
+          }
+        }
+      }
+    } else {
+      for (int v0 = et; v0 < nvec; v0 += 128 * U) {
+        uint4 x[U][2];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int v = v0 + u * 128;
+          if (v < nvec) {
+            const long long o = off0 + (long long)(v / vpr) * p.d_rs * 2 + (v % vpr) * 16;
+            x[u][0] = *reinterpret_cast<const uint4*>(p.ar_d[0] + o);
+            x[u][1] = *reinterpret_cast<const uint4*>(p.ar_d[1] + o);
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+          const int v = v0 + u * 128;
+          if (v < nvec) {
+            const long long o = off0 + (long long)(v / vpr) * p.d_rs * 2 + (v % vpr) * 16;
+            uint4 y;
+            const uint32_t* a = reinterpret_cast<const uint32_t*>(&x[u][0]);
+            const uint32_t* b = reinterpret_cast<const uint32_t*>(&x[u][1]);
+            uint32_t* c = reinterpret_cast<uint32_t*>(&y);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 fa = unpack_bf16x2(a[e]), fb = unpack_bf16x2(b[e]);
+              c[e] = pack_bf16x2(fa.x + fb.x, fa.y + fb.y);
+            }
+            *reinterpret_cast<uint4*>(p.ar_d[0] + o) = y;
+            *reinterpret_cast<uint4*>(p.ar_d[1] + o) = y;
+          }
+        }
+      }
+    }
+    next += gridDim.x;
+    --budget;
+  }
+  return next;
 }
 
 template <int ES, int CTAS, bool W4>
@@ -591,6 +702,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     if (p.stream_k) asm volatile("ld.shared.u32 %0, [%1];" : "=r"(sk_epoch_v) : "r"(sk_epoch_slot) : "memory");
     const int sk_groups = nunits / sk_g, sk_grp = unit / sk_g;
     const long long sk_total = (long long)(total_tiles / sk_g) * num_k_total;
+    // fused all-reduce: this CTA's reduction items are ar_next, ar_next + gridDim.x, ... < ar_items (see ar_reduce)
+    const int ar_slabs = (kBM * CTAS) / kArSlabRows;
+    const int ar_items = p.ar_world > 1 ? ((total_tiles - p.ar_rank + p.ar_world - 1) / p.ar_world) * ar_slabs : 0;
+    int ar_next = blockIdx.x;
+    const uint32_t ar_poll_slot = sk_epoch_slot;     // stream-K is off in this mode: the slot is free
     while (it.next(sg)) {
       const int tile = sg.tile;
       const int bt = tile / tiles_per_batch;
@@ -674,7 +790,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       }
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1u;
-      if (p.ar_world > 1) {
+      if (!W4 && p.ar_world > 1) {
         // this CTA's rows of the tile are in D: one system-scope fence + release by one thread covers the stores the
         // other epilogue threads made before the barrier
         asm volatile("bar.sync 1, 128;" ::: "memory");
@@ -683,59 +799,16 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           unsigned int* f = p.ar_tile_flags[tile % p.ar_world] + ((long long)(tile * 2 + (int)rank) * 8 + p.ar_rank);
           asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(f), "r"(p.ar_epoch) : "memory");
         }
+        // while the tensor pipe works on this CTA's next tile: sum up to two owned row slabs whose partials have arrived
+        ar_next = ar_reduce<CTAS>(p, ar_next, ar_items, 2, false, total_tiles, ar_poll_slot);
       }
     }
-    if (p.ar_world > 1) {
-      // ---- reduce the tiles this rank owns (in place, inside the switch), then the cross-rank completion barrier ----
-      const int et = (int)threadIdx.x - 64;     // 0..127
-      const int W = p.ar_world;
-      const int n_owned = (total_tiles - p.ar_rank + W - 1) / W;
-      for (int k = blockIdx.x; k < n_owned; k += gridDim.x) {
-        const int tile = k * W + p.ar_rank;
-        if (et < CTAS * W) {
-          const unsigned int* f = p.ar_tile_flags[p.ar_rank] + ((long long)(tile * 2 + et / W) * 8 + et % W);
-          unsigned int seen;
-          const long long tw = clock64();
-          do {
-            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
-            if (clock64() - tw > 20000000000ll) {
-              printf("b200 gemm+allreduce: rank %d timed out waiting for tile %d of rank %d\n", p.ar_rank, tile, et % W);
-              __trap();
-            }
-          } while ((int)(seen - p.ar_epoch) < 0);
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        const int n_blk = tile / p.num_m, m_blk = tile - n_blk * p.num_m;
-        const int m0 = m_blk * (kBM * CTAS), n0 = n_blk * p.bn;
-        const int rows = min(kBM * CTAS, p.M - m0);
-        const int vpr = (min(p.N, n0 + p.bn) - n0) / 8;            // 16-byte vectors per row (bf16)
-        const int nvec = rows * vpr;
-        char* base = p.ar_mc + ((long long)m0 * p.d_rs + n0) * 2;
-        constexpr int U = 8;
-        for (int v0 = et; v0 < nvec; v0 += 128 * U) {
-          uint4 x[U];
-#pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int v = v0 + u * 128;
-            if (v < nvec) {
-              const char* a = base + (long long)(v / vpr) * p.d_rs * 2 + (v % vpr) * 16;
-              asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
-                           : "=r"(x[u].x), "=r"(x[u].y), "=r"(x[u].z), "=r"(x[u].w) : "l"(a) : "memory");
-            }
-          }
-#pragma unroll
-          for (int u = 0; u < U; ++u) {
-            const int v = v0 + u * 128;
-            if (v < nvec) {
-              char* a = base + (long long)(v / vpr) * p.d_rs * 2 + (v % vpr) * 16;
-              asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(a), "r"(x[u].x), "r"(x[u].y),
-                           "r"(x[u].z), "r"(x[u].w) : "memory");
-            }
-          }
-        }
-      }
+    if (!W4 && p.ar_world > 1) {
+      // ---- the rest of this CTA's share of the reduction, then the cross-rank completion barrier ----
+      ar_reduce<CTAS>(p, ar_next, ar_items, 1 << 30, true, total_tiles, ar_poll_slot);
       asm volatile("bar.sync 1, 128;" ::: "memory");
-      if (et == 0) {
+      if (threadIdx.x == 64) {
+        const int W = p.ar_world;
         __threadfence_system();
         if (atomicAdd(p.ar_ticket, 1u) == gridDim.x - 1) {
           *((volatile unsigned int*)p.ar_ticket) = 0u;
@@ -749,7 +822,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
             do {
               asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(seen) : "l"(f) : "memory");
               if (clock64() - tw > 20000000000ll) {
-                printf("b200 gemm+allreduce: rank %d timed out waiting for rank %d to finish its share\n", p.ar_rank, r);
+                printf("b200 gemm+allreduce: rank %d timed out waiting for rank %d to finish its share (flag %u, epoch %u)\n",
+                       p.ar_rank, r, seen, p.ar_epoch);
                 __trap();
               }
             } while ((int)(seen - p.ar_epoch) < 0);
@@ -773,7 +847,7 @@ template <int ES, int CTAS>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const __grid_constant__ CUtensorMap tmA2, const __grid_constant__ CUtensorMap tmB2,
-                    const GemmKernelParams p) {
+                    const __grid_constant__ GemmKernelParams p) {
   gemm_body<ES, CTAS, false>(tmA, tmB, tmA2, tmB2, p, nullptr);
 }
 
@@ -782,7 +856,7 @@ gemm_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 __global__ void __launch_bounds__(kW4Threads, 1)
 gemm_w4_tcgen05_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmA2,
                        const __grid_constant__ CUtensorMap tmB2, const __grid_constant__ W4Params w4,
-                       const GemmKernelParams p) {
+                       const __grid_constant__ GemmKernelParams p) {
   gemm_body<2, 2, true>(tmA, tmA, tmA2, tmB2, p, &w4);
 }
 
@@ -1015,11 +1089,19 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
 
   const long long total_tiles = (long long)p.num_m * p.num_n * p.batch;
   p.ar_world = 0; p.ar_rank = 0; p.ar_channel = 0; p.ar_epoch = 0; p.ar_mc = nullptr; p.ar_ticket = nullptr;
+  p.ar_d[0] = p.ar_d[1] = nullptr;
   for (int r = 0; r < 8; ++r) { p.ar_tile_flags[r] = nullptr; p.ar_sync[r] = nullptr; }
   if (ar) {
     if (total_tiles > ar->max_tiles) return B200_ERR_TOO_LARGE;
     p.ar_world = ar->world; p.ar_rank = ar->rank; p.ar_channel = ar->channel; p.ar_epoch = ar->epoch;
     p.ar_mc = reinterpret_cast<char*>(ar->d_mc); p.ar_ticket = ar->ticket;
+    // two ranks: the switch has nothing to save (each byte crosses one link either way) and plain peer loads are faster
+    static const int force_peer = [] { const char* e = getenv("B200_GEMM_AR_PEER"); return e ? atoi(e) : -1; }();
+    if (ar->d_ptrs && ar->world == 2 && force_peer != 0) {
+      p.ar_mc = nullptr;
+      p.ar_d[0] = reinterpret_cast<char*>(const_cast<void*>(ar->d_ptrs[0]));
+      p.ar_d[1] = reinterpret_cast<char*>(const_cast<void*>(ar->d_ptrs[1]));
+    }
     for (int r = 0; r < ar->world; ++r) {
       p.ar_tile_flags[r] = reinterpret_cast<unsigned int*>(const_cast<void*>(ar->tile_flag_ptrs[r]));
       p.ar_sync[r] = reinterpret_cast<unsigned int*>(const_cast<void*>(ar->sync_flag_ptrs[r]));

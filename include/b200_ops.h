@@ -84,11 +84,12 @@ typedef struct {
  * b200_gemm with D = its copy of one symmetric bf16 buffer (same offset everywhere, batch 1, 16-byte aligned rows) and
  * this descriptor. Tiles are announced to their owner rank as they finish; CTAs that have run out of GEMM tiles sum the
  * owned tiles in place inside NVSwitch (multimem.ld_reduce / multimem.st on d_mc, fp32 accumulation) while other CTAs
- * are still multiplying; the launch returns with the full sum in every rank's D. All ranks must launch it (bounded
+ * are still multiplying (between two of their own tiles, too); the launch returns with the full sum in every rank's D. All ranks must launch it (bounded
  * waits trap otherwise). tile_flag_ptrs[r]: uint32 [max_tiles * 16] on rank r (zero-initialised once); sync_flag_ptrs[r]:
  * uint32 [channels][8] epoch flags on rank r; ticket: one local zero-initialised uint32; epoch: grows by >= 1 per call. */
 typedef struct b200_gemm_allreduce {
   void* d_mc;                          /* multicast address of D */
+  const void* const* d_ptrs;           /* [world] peer addresses of D (optional; used instead of d_mc when world == 2) */
   const void* const* tile_flag_ptrs;   /* [world] */
   const void* const* sync_flag_ptrs;   /* [world] */
   unsigned int* ticket;

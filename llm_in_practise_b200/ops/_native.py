@@ -122,6 +122,17 @@ class GemmArgs(ctypes.Structure):
         ("alpha", ctypes.c_float), ("beta", ctypes.c_float),
         ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_int64),
         ("beta_rows", ctypes.c_void_p),
+        ("ar", ctypes.c_void_p),
+    ]
+
+
+class GemmAllReduce(ctypes.Structure):
+    """``b200_gemm_allreduce`` (include/b200_ops.h): all-reduce of D over tensor-parallel ranks inside the GEMM launch."""
+    _fields_ = [
+        ("d_mc", ctypes.c_void_p), ("d_ptrs", ctypes.c_void_p), ("tile_flag_ptrs", ctypes.c_void_p), ("sync_flag_ptrs", ctypes.c_void_p),
+        ("ticket", ctypes.c_void_p),
+        ("world", ctypes.c_int32), ("rank", ctypes.c_int32), ("channel", ctypes.c_int32), ("epoch", ctypes.c_uint32),
+        ("max_tiles", ctypes.c_int64),
     ]
 
 

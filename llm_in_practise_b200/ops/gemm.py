@@ -105,8 +105,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
          out: Optional[torch.Tensor] = None, out_dtype: Optional[torch.dtype] = None,
          alpha: float = 1.0, beta: float = 0.0, bias: Optional[torch.Tensor] = None,
          lora: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
-         beta_rows: Optional[torch.Tensor] = None) -> torch.Tensor:
+         beta_rows: Optional[torch.Tensor] = None, ar=None) -> torch.Tensor:
     """``beta_rows`` (float32 [M], 2-D problems): per-row beta, ``out[m] = alpha * acc[m] + beta_rows[m] * out[m]``.
+    ``ar`` (``nv.GemmAllReduce``): ``out`` is this rank's copy of a symmetric bf16 buffer and is summed over the
+    tensor-parallel ranks inside the launch (K-C5, see ``parallel/tp.TensorParallel.gemm_allreduce``).
     See module docstring. ``a``/``b`` are the *stored* tensors (last dim contiguous); leading dims
     (up to two) are batch dims with arbitrary strides; ``b`` may have fewer batch entries in its
     inner batch dim (an integer divisor: grouped-query attention)."""
@@ -178,6 +180,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, *, a_mn: bool = False, b_mn: bool = F
     args.in_dtype, args.out_dtype = nv.dtype_code(a.dtype), nv.dtype_code(out.dtype)
     args.alpha, args.beta = alpha, beta
     args.beta_rows = 0 if beta_rows is None else beta_rows.data_ptr()
+    args.ar = ctypes.addressof(ar) if ar is not None else 0
     keep = None
     if lora is not None:
         a2, b2 = lora

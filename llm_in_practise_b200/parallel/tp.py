@@ -50,7 +50,39 @@ class TensorParallel:
             self.stage16 = SymmBuffer(2 * self.half16, torch.bfloat16, self.device, group)
             self.state16 = torch.zeros(4, dtype=torch.int32, device=self.device)
             self.oneshot = os.environ.get("B200_TP_ONESHOT", "1") != "0"
+            # K-C5: all-reduce inside the row-parallel GEMM (prefill-sized products). Tile flags: [max_tiles][2][8] uint32.
+            self.max_tiles = 16384
+            self.tile_flags = SymmBuffer(self.max_tiles * 16, torch.int32, self.device, group)
+            self.ticket = torch.zeros(1, dtype=torch.int32, device=self.device)
+            self.fuse_gemm = os.environ.get("B200_TP_GEMM_AR", "1") != "0"
         self.calls = 0
+        self.fused_gemm_calls = 0
+
+    def can_fuse_gemm(self, x: torch.Tensor, n_out: int) -> bool:
+        """Row-parallel product of ``x`` [tokens, k] with an [n_out, k] weight as ONE launch that also all-reduces."""
+        return (self.world > 1 and self.fused and self.fuse_gemm and x.is_cuda and x.dtype == torch.bfloat16 and x.dim() == 2
+                and x.shape[0] > 64 and n_out % 8 == 0 and x.shape[0] * n_out <= self.n_max and nvls_enabled(self.lowp)
+                and nv.use_native(x) and not torch.cuda.is_current_stream_capturing())
+
+    def gemm_allreduce(self, x: torch.Tensor, w: torch.Tensor) -> torch.Tensor:
+        """sum over ranks of ``x_r @ w_r^T``: the tcgen05 GEMM writes its partial tile into the symmetric bf16 buffer and the
+        same launch sums the tiles in place inside NVSwitch as they complete on every rank (``b200_gemm_allreduce``)."""
+        from ..ops.gemm import gemm
+        M, N = x.shape[0], w.shape[0]
+        out = self.lowp.local[:M * N].view(M, N)
+        ar = nv.GemmAllReduce()
+        ar.d_mc = self.lowp.multicast_ptr
+        self._ar_keep = (self.tile_flags.c_ptrs(), self.flags.flags.c_ptrs(), self.lowp.c_ptrs())
+        ar.d_ptrs = ctypes.cast(self._ar_keep[2], ctypes.c_void_p)
+        ar.tile_flag_ptrs = ctypes.cast(self._ar_keep[0], ctypes.c_void_p)
+        ar.sync_flag_ptrs = ctypes.cast(self._ar_keep[1], ctypes.c_void_p)
+        ar.ticket = self.ticket.data_ptr()
+        ar.world, ar.rank, ar.channel, ar.epoch = self.world, self.rank, 7, self.flags.next_epoch()
+        ar.max_tiles = self.max_tiles
+        gemm(x, w, out=out, ar=ar)
+        self.calls += 1
+        self.fused_gemm_calls += 1
+        return out.clone()
 
     def all_reduce(self, y: torch.Tensor) -> torch.Tensor:
         """Sum of the ranks' partial activations ``y`` [tokens, hidden]; returns a tensor of y's dtype."""
@@ -168,7 +200,10 @@ class RowParallelLinear(nn.Module):
         self.in_features, self.out_features = k, lin.out_features
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        y = self.tp.all_reduce(self.inner(x))
+        if x.dim() == 2 and not getattr(self.inner, "has_lora", False) and self.tp.can_fuse_gemm(x, self.out_features):
+            y = self.tp.gemm_allreduce(x.contiguous(), self.inner._materialize_weight(x.dtype))
+        else:
+            y = self.tp.all_reduce(self.inner(x))
         return y if self.bias is None else y + self.bias
 
 

@@ -53,6 +53,24 @@ def test_tp_oneshot_allreduce_eager_and_graph():
 
 @pytest.mark.gpu
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
+def test_gemm_with_fused_allreduce_matches_nccl():
+    """K-C5: the row-parallel tcgen05 GEMM that all-reduces its tiles inside the launch (NVLS, in place in symmetric
+    memory) against fp32 GEMM + ncclAllReduce; a second launch on the same buffer gives the same bits; all ranks agree."""
+    import os, subprocess, sys, json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    n = _ngpu()
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr",
+                          "127.0.0.1", "--master-port", "29634", os.path.join(root, "scripts", "check_gemm_allreduce.py")],
+                         capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0, out.stderr[-2000:]
+    r = json.loads([ln for ln in out.stdout.splitlines() if ln.startswith("{")][-1])
+    if not r["nvls"]:
+        pytest.skip("symmetric memory reports no multicast address on this box")
+    assert r["ok"] and r["fused_calls"] > 0, r
+
+
+@pytest.mark.gpu
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs >= 2 GPUs")
 def test_allreduce_peer_and_nvls_match_nccl():
     """K-C1 both ways — peer-pointer two-shot kernel and the NVLS kernel (multimem.ld_reduce / multimem.st, reduction in
     NVSwitch; fp32 with a bf16 copy, and bf16 with fp32 accumulation) — against ncclAllReduce of the same data. Skips the
