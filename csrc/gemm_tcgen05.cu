@@ -58,6 +58,10 @@ struct GemmKernelParams {
   unsigned int* sk_flags;
   unsigned int sk_epoch;      // host-provided epoch (used when sk_state is null)
   unsigned int* sk_state;     // device epoch: [0] = epoch of the last stream-K launch, [1] = ticket counter (graph-replayable)
+  // K16 (grouped GEMM): b_map[batch] = which B matrix (and bias row) batch entry `batch` multiplies with, -1 = skip the
+  // entry. Read on the device, so the grouping (tokens sorted by expert) never visits the host.
+  const int* b_map;
+  long long bias_bs;          // elements between the bias rows of consecutive B matrices (0 = one shared bias)
   // K-C5: all-reduce of D over the tensor-parallel ranks inside this launch (row-parallel projection). D is every rank's
   // copy of one symmetric bf16 buffer and ar_mc its multicast address. A finished tile is announced to its owner rank
   // (tile % world) with an epoch flag per (tile, CTA of the pair, source rank); once a CTA has no GEMM tile left, its
@@ -162,7 +166,8 @@ __device__ __forceinline__ void umma_issue(uint32_t d, uint64_t a, uint64_t b, u
 
 template <typename OutT>
 __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* __restrict__ drow, int col0,
-                                               int col_limit, const uint32_t (&r)[32], bool row_ok, float beta) {
+                                               int col_limit, const uint32_t (&r)[32], bool row_ok, float beta,
+                                               long long bias_off) {
   // drow points at D[row, 0]; this thread owns columns col0 .. col0+31 (< col_limit) of its row.
   float v[32];
 #pragma unroll
@@ -170,8 +175,8 @@ __device__ __forceinline__ void epilogue_store(const GemmKernelParams& p, OutT* 
   if (p.bias != nullptr) {
 #pragma unroll
     for (int j = 0; j < 32; ++j) {
-      int c = col0 + j;
-      if (c < col_limit) {
+      const long long c = bias_off + col0 + j;
+      if (col0 + j < col_limit) {
         float b = p.bias_dtype == B200_DT_FP32 ? reinterpret_cast<const float*>(p.bias)[c]
                   : p.bias_dtype == B200_DT_BF16
                       ? __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p.bias)[c])
@@ -443,7 +448,8 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         const int m0 = m_blk * (kBM * CTAS) + (int)rank * kBM;
         const int n0 = n_blk * p.bn + (int)rank * bn_cta;
         const int ab0 = bt % p.nb0, ab1 = bt / p.nb0;
-        const int btb = bt / p.b_div;
+        const int btb = p.b_map ? p.b_map[bt] : bt / p.b_div;
+        if (btb < 0) continue;                       // grouped GEMM: unused row tile
         const int bb0 = btb % p.nb0_b, bb1 = btb / p.nb0_b;
         for (int kb = sg.kb0; kb < sg.kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1u);
@@ -509,6 +515,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       SegmentIter it(p, unit, nunits, total_tiles, num_k_total);
       Segment sg;
       while (it.next(sg)) {
+        if (p.b_map && p.b_map[sg.tile / tiles_per_batch] < 0) continue;   // grouped GEMM: unused row tile
         mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + (uint32_t)acc * kAccStride;
@@ -715,6 +722,9 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
       const int m_blk = rem - n_blk * p.num_m;
       const int m0 = m_blk * (kBM * CTAS) + (int)rank * kBM, n0 = n_blk * p.bn;
       const int ab0 = bt % p.nb0, ab1 = bt / p.nb0;
+      const int bsel = p.b_map ? p.b_map[bt] : 0;
+      if (bsel < 0) continue;                        // grouped GEMM: unused row tile
+      const long long bias_off = (long long)bsel * p.bias_bs;
       mbar_wait_sleep(tfull_bar(acc), acc_phase, 128);
       tc_fence_after();
       const int row = m0 + q * 32 + lane;
@@ -775,11 +785,11 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           }
         }
         if (p.out_dtype == B200_DT_BF16)
-          epilogue_store<__nv_bfloat16>(p, reinterpret_cast<__nv_bfloat16*>(p.D) + doff, col0, col_limit, r, row_ok, beta);
+          epilogue_store<__nv_bfloat16>(p, reinterpret_cast<__nv_bfloat16*>(p.D) + doff, col0, col_limit, r, row_ok, beta, bias_off);
         else if (p.out_dtype == B200_DT_FP32)
-          epilogue_store<float>(p, reinterpret_cast<float*>(p.D) + doff, col0, col_limit, r, row_ok, beta);
+          epilogue_store<float>(p, reinterpret_cast<float*>(p.D) + doff, col0, col_limit, r, row_ok, beta, bias_off);
         else
-          epilogue_store<__half>(p, reinterpret_cast<__half*>(p.D) + doff, col0, col_limit, r, row_ok, beta);
+          epilogue_store<__half>(p, reinterpret_cast<__half*>(p.D) + doff, col0, col_limit, r, row_ok, beta, bias_off);
       }
       }
       tc_fence_before();
@@ -987,12 +997,17 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   int rc = device_props();
   if (rc) return rc;
 
-  GemmKernelParams p;
+  GemmKernelParams p = {};
   p.D = a->D;
   p.bias = a->bias;
   p.M = a->M; p.N = a->N; p.K = a->K; p.K2 = lora ? a->K2 : 0;
   p.batch = a->batch; p.nb0 = nb0; p.b_div = b_div;
   p.nb0_b = nb0 / b_div > 0 ? nb0 / b_div : 1;
+  p.b_map = a->b_map; p.bias_bs = a->b_map ? a->bias_bs : 0;
+  if (a->b_map) {
+    if (a->b_count < 1 || a->ar) return B200_ERR_BAD_SHAPE;
+    p.nb0_b = a->b_count;
+  }
   p.d_rs = a->d_rs; p.d_bs0 = a->d_bs0; p.d_bs1 = a->d_bs1;
   p.alpha = a->alpha; p.beta = a->beta;
   p.beta_rows = (a->batch == 1) ? a->beta_rows : nullptr;
@@ -1007,7 +1022,7 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
     if (a->batch != 1 || a->out_dtype != B200_DT_BF16 || a->beta != 0.f || a->beta_rows) return B200_ERR_UNSUPPORTED;
     if ((reinterpret_cast<uintptr_t>(a->D) | reinterpret_cast<uintptr_t>(ar->d_mc)) & 15 || a->d_rs % 8 || a->N % 8) return B200_ERR_BAD_ALIGN;
   }
-  const bool allow_sk = !ar && a->workspace != nullptr && a->workspace_bytes >= sk_need;
+  const bool allow_sk = !ar && !a->b_map && a->workspace != nullptr && a->workspace_bytes >= sk_need;
   const GemmConfig cfg = pick_config(a->M, a->N, a->batch, nkt, p.b_mn, EPR, g_num_sms, allow_sk);
   const int ctas = cfg.ctas;
   p.bn = cfg.bn;
@@ -1068,7 +1083,7 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
     uint32_t box[4];
     if (!p.b_mn) { dims[0] = a->K; dims[1] = a->N; box[0] = EPR; box[1] = bn_cta; }
     else         { dims[0] = a->N; dims[1] = a->K; box[0] = EPR; box[1] = EPR; }
-    dims[2] = p.nb0_b; dims[3] = nb1_b; box[2] = 1; box[3] = 1;
+    dims[2] = p.nb0_b; dims[3] = a->b_map ? 1 : nb1_b; box[2] = 1; box[3] = 1;
     str[0] = (uint64_t)a->b_rs * ES; str[1] = (uint64_t)a->b_bs0 * ES; str[2] = (uint64_t)a->b_bs1 * ES;
     rc = make_tensor_map(&tmB, a->B, ES, 4, dims, str, box, CU_TENSOR_MAP_SWIZZLE_128B);
     if (rc) return rc;
@@ -1139,7 +1154,7 @@ B200_API int b200_gemm_w4(const b200_gemm_args* a, const b200_w4_desc* w, void* 
   int rc = device_props();
   if (rc) return rc;
 
-  GemmKernelParams p;
+  GemmKernelParams p = {};
   p.D = a->D;
   p.bias = a->bias;
   p.M = a->M; p.N = a->N; p.K = a->K; p.K2 = lora ? a->K2 : 0;

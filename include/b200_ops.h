@@ -77,6 +77,13 @@ typedef struct {
   const float* beta_rows;
   /* Optional: all-reduce D over tensor-parallel ranks inside the same launch (see b200_gemm_allreduce below); b200_gemm only. */
   const struct b200_gemm_allreduce* ar;
+  /* Optional grouped GEMM (K16, mixture-of-experts FFN — DeepSeekLike_spare_MoE_wikitext2.py:300-329): b_map is a DEVICE
+   * array of `batch` ints; batch entry b multiplies with B matrix b_map[b] (B + b_map[b] * b_bs0, bias + b_map[b] *
+   * bias_bs) and is skipped when b_map[b] < 0. b_count = number of B matrices. The caller sorts tokens by expert into
+   * row tiles (one batch entry = one tile of M rows) on the device; nothing about the grouping is read by the host. */
+  const int32_t* b_map;
+  int32_t b_count;
+  int64_t bias_bs;
 } b200_gemm_args;
 
 /* K-C5: row-parallel projection + all-reduce in ONE launch (y = sum over ranks of x_r W_r^T — o_proj / down_proj under

@@ -93,6 +93,13 @@ class MoEFeedForward(nn.Module):
         self.shared_experts = nn.ModuleList([Expert(d_model, hidden, dropout, dtype, device) for _ in range(self.ns)])
         self.last_load = None  # tokens routed to each expert in the last forward (observability)
 
+    def _grouped_ok(self, xf) -> bool:
+        from ..ops import _native as nv
+        ex = self.experts[0]
+        return (nv.use_native(xf) and xf.dtype in (torch.bfloat16, torch.float16) and ex.fc1.weight is not None
+                and ex.fc1.weight.dtype == xf.dtype and xf.shape[1] % 8 == 0 and ex.fc1.weight.shape[0] % 8 == 0
+                and not getattr(ex.fc1, "has_lora", False) and ex.fc1.nf4 is None)
+
     def forward(self, x):
         B, L, D = x.shape
         xf = x.reshape(B * L, D)
@@ -106,6 +113,18 @@ class MoEFeedForward(nn.Module):
             for e, ex in enumerate(self.experts):
                 w = (top_p * (top_i == e).to(top_p.dtype)).sum(-1, keepdim=True)   # gate weight or 0
                 moe = moe + ex(xf) * w
+        elif self.impl == "sparse" and self._grouped_ok(xf):
+            # K16: tokens counting-sorted by expert on the device, every expert's rows padded to whole 128-row tiles, ONE
+            # grouped tcgen05 GEMM per projection (ops/moe.py); no host read of the per-expert counts on the forward path
+            from ..ops.moe import moe_ffn
+            w1 = torch.stack([ex.fc1.weight for ex in self.experts])
+            b1 = torch.stack([ex.fc1.bias for ex in self.experts])
+            w2 = torch.stack([ex.fc2.weight for ex in self.experts])
+            b2 = torch.stack([ex.fc2.bias for ex in self.experts])
+            ex_p = self.experts[0].p                            # the reference's Expert ends in its own dropout
+            moe, d = moe_ffn(xf, top_i, top_p, w1, b1, w2, b2, ew.gelu,
+                             post=(lambda y: ew.dropout(y, ex_p, True)) if (ex_p and self.training) else None)
+            self.last_load = d.counts
         else:
             # sort the (token, slot) assignments by expert: each expert sees one contiguous row segment
             flat_e = top_i.reshape(-1)

@@ -123,6 +123,7 @@ class GemmArgs(ctypes.Structure):
         ("workspace", ctypes.c_void_p), ("workspace_bytes", ctypes.c_int64),
         ("beta_rows", ctypes.c_void_p),
         ("ar", ctypes.c_void_p),
+        ("b_map", ctypes.c_void_p), ("b_count", ctypes.c_int32), ("bias_bs", ctypes.c_int64),
     ]
 
 

@@ -489,3 +489,42 @@ def test_gemv_fused_tail_matches_separate_ops(kind, M):
     hb = h.bfloat16().float()
     want = hb * torch.rsqrt(hb.pow(2).mean(-1, keepdim=True) + 1e-6) * nw.float()
     assert rel(res_out, hb) < 2e-2 and rel(out, want) < 2e-2
+
+
+@pytest.mark.parametrize("T,E,k", [(1000, 8, 2), (77, 4, 1), (4096, 8, 2)])
+def test_moe_grouped_gemm_matches_expert_loop(T, E, k):
+    """K16 (ops/moe.py): device-side counting sort + ONE grouped tcgen05 GEMM per projection (b_map picks the expert's weight
+    per 128-row tile, unused tiles skipped) against the per-expert loop in fp32, forward and all gradients."""
+    from llm_in_practise_b200.ops.moe import moe_ffn
+    from llm_in_practise_b200.ops import elementwise as ew
+    torch.manual_seed(T + E)
+    D, H = 256, 512
+    dt = torch.bfloat16
+    x = (torch.randn(T, D, device=DEV) * 0.5).to(dt).requires_grad_()
+    w1 = (torch.randn(E, H, D, device=DEV) * D ** -0.5).to(dt).requires_grad_()
+    b1 = (torch.randn(E, H, device=DEV) * 0.1).to(dt).requires_grad_()
+    w2 = (torch.randn(E, D, H, device=DEV) * H ** -0.5).to(dt).requires_grad_()
+    b2 = (torch.randn(E, D, device=DEV) * 0.1).to(dt).requires_grad_()
+    logits = torch.randn(T, E, device=DEV)
+    if E > 4:
+        logits[:, 5] = -1e9                                # an expert without tokens
+    top_v, top_i = torch.topk(logits, k, dim=-1)
+    top_p = torch.softmax(top_v, -1)
+    from llm_in_practise_b200.ops import _native as nvm
+    n0 = nvm.launch_count
+    out, d = moe_ffn(x, top_i, top_p.to(dt), w1, b1, w2, b2, ew.gelu)
+    assert nvm.launch_count - n0 >= 2                         # the two grouped launches went through the native library
+    xf, w1f, b1f, w2f, b2f = (t.detach().float().requires_grad_() for t in (x, w1, b1, w2, b2))
+    ref = torch.zeros(T, D, device=DEV)
+    for e in range(E):
+        for s in range(k):
+            m = top_i[:, s] == e
+            if m.any():
+                y = torch.nn.functional.gelu(xf[m] @ w1f[e].T + b1f[e]) @ w2f[e].T + b2f[e]
+                ref = ref.index_add(0, m.nonzero().squeeze(1), y * top_p[m, s:s + 1])
+    assert rel(out, ref) < 2e-2, rel(out, ref)
+    g = torch.randn(T, D, device=DEV)
+    grads = torch.autograd.grad(out, [x, w1, b1, w2, b2], g.to(dt))
+    grads_ref = torch.autograd.grad(ref, [xf, w1f, b1f, w2f, b2f], g)
+    for name, a, b in zip(("dx", "dw1", "db1", "dw2", "db2"), grads, grads_ref):
+        assert rel(a, b) < 3e-2, (name, rel(a, b))
