@@ -10,9 +10,9 @@ Semantics kept from the reference:
 * router ``Linear(d, E)``; **top-k on the raw logits, softmax over the k selected values**; ``num_shared`` always-on
   experts averaged; every expert is Linear(d,4d) -> GELU -> Linear(4d,d) (…:255-329).
 
-B200 mapping (K16/K17): q|k|v is one fused tcgen05 GEMM; RoPE is one kernel over the fused projection; the latent
-products are batched tcgen05 GEMMs over head-major strided views with the masked-softmax kernel in between (no
-L x L mask tensor); tokens are sorted by expert on the device so each expert runs two dense GEMMs over a
+B200 mapping (K16/K17): q|k|v is one fused tcgen05 GEMM; RoPE is one kernel over the fused projection; latent attention
+runs on the flash kernels with the latent vectors zero-padded to 32 columns (no L x L score or mask tensor; fp32 /
+non-native runs keep the batched-GEMM + masked-softmax path); tokens are sorted by expert on the device so each expert runs two dense GEMMs over a
 contiguous row segment (``moe_impl="sparse"``), or every expert runs on all tokens and is masked
 (``moe_impl="dense"``, the first script's behaviour — same function, E/k times the FLOPs).
 """
@@ -22,10 +22,12 @@ import math
 from typing import Optional
 
 import torch
+import torch.nn.functional as F
 from torch import nn
 
 from ..ops import elementwise as ew
 from ..ops import functional as Fn
+from ..ops.flash import flash_attention
 from ..ops.gemm import gemm
 from ..ops.linear import FusedLinear
 from ..ops.loss import cross_entropy, linear_cross_entropy
@@ -48,12 +50,31 @@ class CausalMLA(nn.Module):
         self.out_proj = FusedLinear(d_model, [("o_proj", d_model)], bias=True, **kw)
         self.p = resid_dropout
 
+    FLASH_LATENT = 32      # smallest head size of the flash kernels (csrc/flash_attn.cu)
+
+    def _flash_ok(self, x, lat) -> bool:
+        from ..ops import _native as nv
+        return (nv.use_native(x) and x.dtype in (torch.bfloat16, torch.float16) and lat <= self.FLASH_LATENT
+                and self.q_compress.weight is not None and self.q_compress.weight.dtype == x.dtype)
+
     def forward(self, x, cos, sin, pos):
         B, L, D = x.shape
         H, hd, lat = self.h, self.hd, self.latent
         qkv = self.qkv(x.reshape(B * L, D))
         qkv = ew.qknorm_rope(qkv, None, None, cos, sin, pos, H, H, hd, interleaved=True)
         q, k, v = (qkv[:, i * D:(i + 1) * D].contiguous().view(B * L * H, hd) for i in range(3))
+        if self._flash_ok(x, lat):
+            # K17: latent attention on the flash kernels. The three per-head compressions write latent vectors zero-padded
+            # to the kernel's smallest head size (32): zero q / k columns leave the scores unchanged, the extra v columns
+            # come out zero and are dropped before `decompress`. No L x L score or mask tensor in either direction.
+            pad = self.FLASH_LATENT - lat
+            def comp(lin, t):
+                return Fn.linear(t, F.pad(lin.weight, (0, 0, 0, pad)), F.pad(lin.bias, (0, pad))).view(B * L, H * self.FLASH_LATENT)
+            lat_qkv = torch.cat([comp(self.q_compress, q), comp(self.k_compress, k), comp(self.v_compress, v)], dim=1)
+            o = flash_attention(lat_qkv, B, L, H, H, self.FLASH_LATENT, True, 1.0 / math.sqrt(lat))
+            o = o.view(B * L * H, self.FLASH_LATENT)[:, :lat]
+            o = self.decompress(o.contiguous()).view(B * L, D)
+            return ew.dropout(self.out_proj(o), self.p, self.training).view(B, L, D)
         # per-head compression into the latent space; pad the latent dim to a multiple of 8 for 16-byte rows
         qc = self.q_compress(q).view(B, L, H, lat).permute(0, 2, 1, 3)
         kc = self.k_compress(k).view(B, L, H, lat).permute(0, 2, 1, 3)

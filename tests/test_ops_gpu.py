@@ -528,3 +528,23 @@ def test_moe_grouped_gemm_matches_expert_loop(T, E, k):
     grads_ref = torch.autograd.grad(ref, [xf, w1f, b1f, w2f, b2f], g)
     for name, a, b in zip(("dx", "dw1", "db1", "dw2", "db2"), grads, grads_ref):
         assert rel(a, b) < 3e-2, (name, rel(a, b))
+
+
+def test_deepseeklike_flash_mla_and_grouped_moe_match_fp32_model():
+    """K16 + K17 in the model: bf16 DeepSeekLike on the native paths (latent attention on the flash kernels with the latent
+    dim zero-padded to 32, grouped-GEMM MoE) against the SAME weights in fp32 on the batched-matmul / expert-loop paths."""
+    from llm_in_practise_b200.models.deepseeklike import DeepSeekLike
+    torch.manual_seed(1)
+    kw = dict(vocab_size=512, block_size=128, n_layer=2, n_head=4, d_model=256, dropout=0.0, num_experts=4, top_k=2, num_shared=1)
+    ref = DeepSeekLike(dtype=torch.float32, device=DEV, **kw)
+    m = DeepSeekLike(dtype=torch.bfloat16, device=DEV, **kw)
+    m.load_state_dict({k: v.to(torch.bfloat16) for k, v in ref.state_dict().items()})
+    ref.load_state_dict({k: v.float() for k, v in m.state_dict().items()})      # identical (bf16-representable) weights
+    ids = torch.randint(0, 512, (4, 128), device=DEV)
+    la, lb = m(ids, ids), ref(ids, ids)
+    assert abs(float(la) - float(lb)) < 3e-2 * abs(float(lb)), (float(la), float(lb))
+    la.backward()
+    lb.backward()
+    ga = torch.cat([p.grad.float().reshape(-1) for p in m.parameters()])
+    gb = torch.cat([p.grad.float().reshape(-1) for p in ref.parameters()])
+    assert float((ga - gb).norm() / gb.norm()) < 8e-2
