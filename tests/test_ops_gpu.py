@@ -535,7 +535,7 @@ def test_deepseeklike_flash_mla_and_grouped_moe_match_fp32_model():
     dim zero-padded to 32, grouped-GEMM MoE) against the SAME weights in fp32 on the batched-matmul / expert-loop paths."""
     from llm_in_practise_b200.models.deepseeklike import DeepSeekLike
     torch.manual_seed(1)
-    kw = dict(vocab_size=512, block_size=128, n_layer=2, n_head=4, d_model=256, dropout=0.0, num_experts=4, top_k=2, num_shared=1)
+    kw = dict(vocab_size=512, block_size=128, n_layer=2, n_head=4, d_model=256, dropout=0.0, num_experts=8, top_k=2, num_shared=1)
     ref = DeepSeekLike(dtype=torch.float32, device=DEV, **kw)
     m = DeepSeekLike(dtype=torch.bfloat16, device=DEV, **kw)
     m.load_state_dict({k: v.to(torch.bfloat16) for k, v in ref.state_dict().items()})
