@@ -316,6 +316,9 @@ B200_API int b200_flash_attn_fwd_tc(const void* qkv, void* out, float* lse, int 
   if (D != kTcD || (dtype != B200_DT_BF16 && dtype != B200_DT_FP16)) return B200_ERR_UNSUPPORTED;
   if (B < 1 || S < 1 || H < 1 || Hkv < 1 || H % Hkv) return B200_ERR_BAD_SHAPE;
   if ((reinterpret_cast<uintptr_t>(qkv) | reinterpret_cast<uintptr_t>(out)) & 15) return B200_ERR_BAD_ALIGN;
+  // autograd's backward threads have no current driver context until a runtime call binds the primary one; the tensor-map
+  // encode below is a driver entry point
+  { int dev = 0; B200_CHECK(cudaGetDevice(&dev)); B200_CHECK(cudaSetDevice(dev)); }
   const long long W = (long long)(H + 2 * Hkv) * kTcD;
   CUtensorMap tm;
   {

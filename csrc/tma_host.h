@@ -2,6 +2,7 @@
 // is resolved through the runtime (cudaGetDriverEntryPoint) the first time it is needed, so the
 // library loads on a CPU-only box (where only the build and the CPU tests run).
 #pragma once
+#include <stdio.h>
 
 #include <cuda.h>
 #include <cuda_runtime.h>
@@ -55,7 +56,13 @@ inline int make_tensor_map(CUtensorMap* map, const void* base, int elem_bytes, i
   CUresult r = enc(map, dt, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  return r == CUDA_SUCCESS ? 0 : 10004;  // B200_ERR_TENSORMAP
+  if (r != CUDA_SUCCESS) {
+    fprintf(stderr, "b200: cuTensorMapEncodeTiled failed (CUresult %d): base %p elem %d rank %d dims [%llu, %llu] stride0 %llu box [%u, %u]\n",
+            (int)r, base, elem_bytes, rank, (unsigned long long)gdim[0], (unsigned long long)(rank > 1 ? gdim[1] : 0),
+            (unsigned long long)(rank > 1 ? gstr[0] : 0), bx[0], rank > 1 ? bx[1] : 0u);
+    return 10004;  // B200_ERR_TENSORMAP
+  }
+  return 0;
 }
 
 }  // namespace b200

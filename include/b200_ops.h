@@ -377,6 +377,13 @@ int b200_flash_attn_bwd(const void* qkv, const void* out, const void* dout, cons
 int b200_flash_attn_fwd_tc(const void* qkv, void* out, float* lse, int B, int S, int H, int Hkv, int D, int causal,
                            float scale, int dtype, void* stream);
 
+/* Backward on the same tensor cores (csrc/flash_bwd_tc.cu): a dK/dV pass (K, V resident per 64-key block, query tiles
+ * stream) and a dQ pass (Q, dO resident per 128-row tile, key blocks stream), every product a tcgen05.mma with TMEM
+ * accumulators; no atomics and no fp32 staging buffer (delta [B, H, S] is the only work buffer). head_dim 128, 16-bit,
+ * no dropout; B200_ERR_UNSUPPORTED otherwise. */
+int b200_flash_attn_bwd_tc(const void* qkv, const void* out, const void* dout, const float* lse, float* delta, void* dqkv,
+                           int B, int S, int H, int Hkv, int D, int causal, float scale, int dtype, void* stream);
+
 /* ---- small-M products for decode / serving steps (csrc/gemv.cu) ---------------------------------
  * y[m, n] = sum_k x[m, k] w[n, k] (+ bias[n]) for 1 <= M <= 64 tokens with the weights read exactly once (mma.sync with
  * the weight rows as the A operand, token groups of 8 as B). K % 128 == 0; x / w 16-byte aligned, row strides

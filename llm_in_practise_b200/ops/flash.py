@@ -19,6 +19,7 @@ def flash_supported(qkv: torch.Tensor, head_dim: int) -> bool:
 
 
 _TC = __import__("os").environ.get("B200_FLASH_TC", "1") != "0"
+_TC_BWD = __import__("os").environ.get("B200_FLASH_TC_BWD", "1") != "0"
 
 
 def _fwd(qkv, B, S, H, Hkv, D, causal, scale, want_lse=True, dropout_p=0.0, seed=0):
@@ -55,8 +56,17 @@ class _FlashAttentionFn(torch.autograd.Function):
         B, S, H, Hkv, D, causal, scale, dropout_p, seed = ctx.cfg
         dout = dout.contiguous()
         dqkv = torch.empty_like(qkv)
-        dqkv32 = torch.empty(qkv.shape, dtype=torch.float32, device=qkv.device)
         delta = torch.empty(B, H, S, dtype=torch.float32, device=qkv.device)
+        if _TC_BWD and D == 128 and dropout_p == 0.0:
+            # tcgen05 backward (csrc/flash_bwd_tc.cu): dK/dV pass + dQ pass, no atomics, no fp32 staging buffer
+            ft = nv.proto("b200_flash_attn_bwd_tc", [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, f32, i32, vp])
+            rc = ft(nv.ptr(qkv), nv.ptr(out), nv.ptr(dout), nv.ptr(lse), nv.ptr(delta), nv.ptr(dqkv), B, S, H, Hkv, D, int(causal),
+                    float(scale), nv.dtype_code(qkv.dtype), nv.stream())
+            if rc != 10006:
+                nv.check(rc, "flash_attn_bwd_tc")
+                nv.count_launch(3)   # delta, dK/dV pass, dQ pass
+                return dqkv, None, None, None, None, None, None, None, None, None
+        dqkv32 = torch.empty(qkv.shape, dtype=torch.float32, device=qkv.device)
         fn = nv.proto("b200_flash_attn_bwd", [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, i32, f32, f32, u64, i32, vp])
         nv.check(fn(nv.ptr(qkv), nv.ptr(out), nv.ptr(dout), nv.ptr(lse), nv.ptr(delta), nv.ptr(dqkv32), nv.ptr(dqkv),
                     B, S, H, Hkv, D, int(causal), float(scale), float(dropout_p), int(seed), nv.dtype_code(qkv.dtype),

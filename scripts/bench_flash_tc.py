@@ -35,6 +35,19 @@ for name, B, S, H, Hkv in (("qwen3-14b 4x512", 4, 512, 40, 8), ("qwen3-8b 1x4096
         t = timed(lambda: FL._fwd(qkv, B, S, H, Hkv, D, True, D ** -0.5, True))
         row["tcgen05_ms" if tc else "mma_sync_ms"] = round(t, 4)
         row["tcgen05_tflops" if tc else "mma_sync_tflops"] = round(fl / t / 1e9, 1)
+    # forward + backward through the autograd function (delta + dK/dV pass + dQ pass, or the mma.sync kernel)
+    qg = qkv.clone().requires_grad_()
+    go = torch.randn(B * S, H * D, device=dev, dtype=torch.bfloat16)
+    def fb():
+        o = FL.flash_attention(qg, B, S, H, Hkv, D, True, D ** -0.5)
+        torch.autograd.grad(o, qg, go)
+    for tc in ((True, False) if BASE else (True,)):
+        FL._TC = tc
+        FL._TC_BWD = tc
+        t = timed(fb, 6)
+        row["tcgen05_fwd_bwd_ms" if tc else "mma_sync_fwd_bwd_ms"] = round(t, 4)
+        row["tcgen05_fwd_bwd_tflops" if tc else "mma_sync_fwd_bwd_tflops"] = round(3.5 * fl / t / 1e9, 1)
+    FL._TC = FL._TC_BWD = True
     if not BASE:
         print(json.dumps(row), flush=True)
         continue

@@ -411,6 +411,28 @@ def test_flash_attention_tcgen05_forward(H, Hkv, S, dtype, causal, gain, monkeyp
     assert (lse - lse_old).abs().max().item() < 2e-2
 
 
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("H,Hkv,S,dtype", [(8, 2, 512, torch.bfloat16), (4, 4, 77, torch.float16), (5, 1, 200, torch.bfloat16),
+                                           (2, 2, 1000, torch.bfloat16), (2, 1, 128, torch.float16), (3, 3, 64, torch.bfloat16)])
+def test_flash_attention_tcgen05_backward(H, Hkv, S, dtype, causal, monkeypatch):
+    """csrc/flash_bwd_tc.cu (dK/dV pass + dQ pass on tcgen05, no atomics): gradient of the fused projection against autograd
+    through the fp32 reference attention, ragged sequence lengths, GQA groups accumulated inside one CTA."""
+    from llm_in_practise_b200.ops import flash as FL
+    B, D = 2, 128
+    torch.manual_seed(S * 7 + H)
+    qkv = torch.randn(B * S, (H + 2 * Hkv) * D, device=DEV).to(dtype).requires_grad_()
+    g = torch.randn(B * S, H * D, device=DEV).to(dtype)
+    monkeypatch.setattr(FL, "_TC", True)
+    monkeypatch.setattr(FL, "_TC_BWD", True)
+    out = FL.flash_attention(qkv, B, S, H, Hkv, D, causal, D ** -0.5)
+    (dq,) = torch.autograd.grad(out, qkv, g)
+    q32 = qkv.detach().float().requires_grad_()
+    ref = _ref_attention(q32, B, S, H, Hkv, D, causal, 0, D ** -0.5)
+    (dref,) = torch.autograd.grad(ref, q32, g.float())
+    for name, lo, hi in (("dq", 0, H * D), ("dk", H * D, (H + Hkv) * D), ("dv", (H + Hkv) * D, (H + 2 * Hkv) * D)):
+        assert rel(dq[:, lo:hi], dref[:, lo:hi]) < 3e-2, (name, rel(dq[:, lo:hi], dref[:, lo:hi]))
+
+
 def test_adamw_and_8bit():
     from llm_in_practise_b200.optim import FusedAdamW, PagedAdamW8bit
     from llm_in_practise_b200.utils.arena import ParamArena
@@ -536,15 +558,15 @@ def test_deepseeklike_flash_mla_and_grouped_moe_match_fp32_model():
     from llm_in_practise_b200.models.deepseeklike import DeepSeekLike
     torch.manual_seed(1)
     kw = dict(vocab_size=512, block_size=128, n_layer=2, n_head=4, d_model=256, dropout=0.0, num_experts=8, top_k=2, num_shared=1)
-    ref = DeepSeekLike(dtype=torch.float32, device=DEV, **kw)
+    ref = DeepSeekLike(dtype=torch.float32, device="cpu", **kw)                 # plain torch paths (matmul attention, expert loop)
     m = DeepSeekLike(dtype=torch.bfloat16, device=DEV, **kw)
     m.load_state_dict({k: v.to(torch.bfloat16) for k, v in ref.state_dict().items()})
-    ref.load_state_dict({k: v.float() for k, v in m.state_dict().items()})      # identical (bf16-representable) weights
+    ref.load_state_dict({k: v.float().cpu() for k, v in m.state_dict().items()})      # identical (bf16-representable) weights
     ids = torch.randint(0, 512, (4, 128), device=DEV)
-    la, lb = m(ids, ids), ref(ids, ids)
+    la, lb = m(ids, ids), ref(ids.cpu(), ids.cpu())
     assert abs(float(la) - float(lb)) < 3e-2 * abs(float(lb)), (float(la), float(lb))
     la.backward()
     lb.backward()
-    ga = torch.cat([p.grad.float().reshape(-1) for p in m.parameters()])
+    ga = torch.cat([p.grad.float().reshape(-1).cpu() for p in m.parameters()])
     gb = torch.cat([p.grad.float().reshape(-1) for p in ref.parameters()])
     assert float((ga - gb).norm() / gb.norm()) < 8e-2
