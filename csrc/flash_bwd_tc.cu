@@ -18,7 +18,8 @@
 // one-pass kernel are ~64 KB per pair — 2 GB at 4k tokens x 32 heads), no zero-filled fp32 [tokens, 3 x heads x 128]
 // buffer, bit-reproducible gradients.
 //
-// 256 threads: warps 0-3 element-wise, warp 4 TMA producer, warp 5 tcgen05 issuer; 1 CTA per SM (384 TMEM columns, up to
+// 320 threads: warps 0-7 element-wise (warp w and w + 4 share a TMEM lane quarter and split the 64 key columns), warp 8
+// TMA producer, warp 9 tcgen05 issuer; 1 CTA per SM (384 TMEM columns, up to
 // 193 KB of shared memory). head_dim 128, 16-bit, no dropout — anything else goes to the mma.sync kernel of
 // flash_attn.cu. Reference call sites: the SDPA backward behind nn.MultiheadAttention
 // (LLM_Distributed_Trainning/PyTorch/ddp_basics/ddp_gpt_wikitext2.py:89-96) and HF Qwen3 attention under the Trainer
@@ -33,7 +34,7 @@
 namespace b200 {
 
 constexpr int kBwBM = 128, kBwBN = 64, kBwD = 128;
-constexpr int kBwThreads = 256;
+constexpr int kBwThreads = 320;       // warps 0-7 element-wise (two per TMEM lane quarter), warp 8 TMA, warp 9 tcgen05 issuer
 constexpr uint32_t kBwQTile = 32768;     // 128 rows x 128 columns x 2 B (two 64-column halves of 16 KB)
 constexpr uint32_t kBwKTile = 16384;     // 64 rows x 128 columns x 2 B (two halves of 8 KB)
 constexpr uint32_t kBwPTile = 16384;     // 128 rows x 64 keys x 2 B
@@ -80,6 +81,32 @@ __device__ __forceinline__ float bw_ex2(float x) {
   return y;
 }
 
+// Whole-warp wait, one lane spinning on the non-blocking test_wait (try_wait may park the thread for a while: these
+// hand-offs are on the critical path of every pair)
+__device__ __forceinline__ void bw_wait_warp(uint32_t bar, uint32_t parity) {
+  if ((threadIdx.x & 31) == 0) mbar_wait_spin(bar, parity);
+  __syncwarp();
+}
+
+// tcgen05.mma / commit issued from CONVERGED warp code (every lane runs the loop, elect.sync picks the issuing lane): the
+// descriptors stay in uniform registers. Issued from inside `if (lane == 0)` each UTCHMMA costs two R2UR moves and a
+// divergence loop, ~100 cycles per instruction — more than these 128 x 64 x 16 products take on the tensor pipe.
+__device__ __forceinline__ void umma_f16_w(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_w(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar) : "memory");
+}
+
 template <bool BF16>
 __device__ __forceinline__ uint32_t bw_pack16(float a, float b) {
   if (BF16) return pack_bf16x2(a, b);
@@ -115,26 +142,25 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
   // shared memory map (bytes): resident tile(s) | 2 streaming stages | P | dS | barriers
   constexpr uint32_t kRes = MODE_Q ? 2 * kBwQTile : 2 * kBwKTile;
   constexpr uint32_t kStage = MODE_Q ? 2 * kBwKTile : 2 * kBwQTile;
+  constexpr int NST = MODE_Q ? 3 : 2;      // streaming stages: 3 x 32 KB next to the resident Q / dO, 2 x 64 KB next to K / V
   constexpr uint32_t kOffP = 163840, kOffDS = 180224, kOffBar = 196608;
   const uint32_t sRes = sbase, sStage0 = sbase + kRes, sP = sbase + kOffP, sDS = sbase + kOffDS;
   const uint32_t bar = sbase + kOffBar;
-  const uint32_t res_full = bar, st_full0 = bar + 8, st_empty0 = bar + 24, s_full0 = bar + 40, s_free0 = bar + 56,
-                 pds_full = bar + 72, pds_free = bar + 80, acc_done = bar + 88, tmem_slot = bar + 96;
+  const uint32_t res_full = bar, st_full0 = bar + 8, st_empty0 = bar + 40, s_full0 = bar + 72, s_free0 = bar + 88,
+                 pds_full = bar + 104, pds_free = bar + 112, acc_done = bar + 120, tmem_slot = bar + 128;
   if (threadIdx.x == 0) {
     if (sbase & 1023u) { printf("flash_bwd_tc: shared memory base is not 1024-byte aligned\n"); __trap(); }
     tma_prefetch_desc(&tmq);
     tma_prefetch_desc(&tmd);
     mbar_init(res_full, 1);
-    for (int s = 0; s < 2; ++s) {
-      mbar_init(st_full0 + 8 * s, 1); mbar_init(st_empty0 + 8 * s, 1);
-      mbar_init(s_full0 + 8 * s, 1); mbar_init(s_free0 + 8 * s, 4);
-    }
-    mbar_init(pds_full, 4);
+    for (int s = 0; s < NST; ++s) { mbar_init(st_full0 + 8 * s, 1); mbar_init(st_empty0 + 8 * s, 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(s_full0 + 8 * s, 1); mbar_init(s_free0 + 8 * s, 8); }
+    mbar_init(pds_full, 8);
     mbar_init(pds_free, 1);
     mbar_init(acc_done, 1);
     fence_mbar_init();
   }
-  if (warp == 5) { tmem_alloc(tmem_slot, kBwTmemCols); tmem_relinquish(); }
+  if (warp == 9) { tmem_alloc(tmem_slot, kBwTmemCols); tmem_relinquish(); }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -147,7 +173,7 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
     else { qh = hq; qrow0 = q0; kvrow0 = n * kBwBN; }
   };
 
-  if (warp == 4) {
+  if (warp == 8) {
     if (lane == 0) {
       // 128-row x 128-column tile (Q or dO): two 64-column halves, each two 64-row boxes; 64-row tile (K or V): two boxes
       auto load_q = [&](uint32_t dst, const CUtensorMap* tm, uint32_t fb, int col, int row) {
@@ -166,10 +192,10 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
         load_q(sRes + kBwQTile, &tmd, res_full, hq * kBwD, row_base + q0);
       }
       for (int n = 0; n < n_iter; ++n) {
-        const int s = n & 1;
+        const int s = n % NST;
         int qh, qr, kr;
         pair_of(n, qh, qr, kr);
-        mbar_wait(st_empty0 + 8 * s, (((uint32_t)n >> 1) & 1u) ^ 1u);
+        mbar_wait(st_empty0 + 8 * s, (((uint32_t)(n / NST)) & 1u) ^ 1u);
         mbar_arrive_expect_tx(st_full0 + 8 * s, kStage);
         const uint32_t dst = sStage0 + s * kStage;
         if (!MODE_Q) {
@@ -181,8 +207,8 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
         }
       }
     }
-  } else if (warp == 5) {
-    if (lane == 0) {
+  } else if (warp == 9) {
+    {   // the whole warp runs this block (see umma_f16_w)
       constexpr uint32_t kHi = (1024u >> 4) | (1u << 14) | (kSwizzle128B << 29);
       constexpr uint32_t kLoK = (16u >> 4) << 16;
       constexpr uint32_t kLoMNq = (16384u >> 4) << 16;   // MN-major 128-row tile: 64-column chunks 16 KB apart
@@ -193,9 +219,9 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
       const uint32_t idesc_kv = make_idesc_f16(kBwD, kBwBN, BF16, true, true);      // dV^T / dK^T: both MN-major
       const uint32_t idesc_q = make_idesc_f16(kBwBM, kBwD, BF16, false, true);      // dQ: dS K-major, K MN-major
       // operand addresses of iteration n
-      auto q_of = [&](int n) { return MODE_Q ? sRes : sStage0 + (uint32_t)(n & 1) * kStage; };
+      auto q_of = [&](int n) { return MODE_Q ? sRes : sStage0 + (uint32_t)(n % NST) * kStage; };
       auto do_of = [&](int n) { return q_of(n) + kBwQTile; };
-      auto k_of = [&](int n) { return MODE_Q ? sStage0 + (uint32_t)(n & 1) * kStage : sRes; };
+      auto k_of = [&](int n) { return MODE_Q ? sStage0 + (uint32_t)(n % NST) * kStage : sRes; };
       auto v_of = [&](int n) { return k_of(n) + kBwKTile; };
       auto issue_sdp = [&](int n) {
         const uint32_t buf = (uint32_t)(n & 1) * kBwTBuf;
@@ -204,81 +230,88 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
         for (int half = 0; half < 2; ++half)
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks)
-            umma_f16(tmem_base + kBwTS + buf, desc(ql + half * (16384u >> 4) + ks * 2u), desc(kl + half * (8192u >> 4) + ks * 2u),
+            umma_f16_w(tmem_base + kBwTS + buf, desc(ql + half * (16384u >> 4) + ks * 2u), desc(kl + half * (8192u >> 4) + ks * 2u),
                      idesc_s, (half | ks) ? 1u : 0u);
 #pragma unroll
         for (int half = 0; half < 2; ++half)
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks)
-            umma_f16(tmem_base + kBwTdP + buf, desc(dl + half * (16384u >> 4) + ks * 2u), desc(vl + half * (8192u >> 4) + ks * 2u),
+            umma_f16_w(tmem_base + kBwTdP + buf, desc(dl + half * (16384u >> 4) + ks * 2u), desc(vl + half * (8192u >> 4) + ks * 2u),
                      idesc_s, (half | ks) ? 1u : 0u);
-        umma_commit(s_full0 + 8 * (n & 1));
+        umma_commit_w(s_full0 + 8 * (n & 1));
       };
-      mbar_wait(res_full, 0);
-      mbar_wait(st_full0, 0);
+      mbar_wait_spin(res_full, 0);
+      mbar_wait_spin(st_full0, 0);
       tc_fence_after();
       issue_sdp(0);
       for (int n = 0; n < n_iter; ++n) {
         if (n + 1 < n_iter) {
-          mbar_wait(st_full0 + 8 * ((n + 1) & 1), ((uint32_t)(n + 1) >> 1) & 1u);
-          if (n >= 1) mbar_wait(s_free0 + 8 * ((n + 1) & 1), ((uint32_t)(n - 1) >> 1) & 1u);   // S / dP of pair n-1 are in registers
+          mbar_wait_spin(st_full0 + 8 * ((n + 1) % NST), ((uint32_t)((n + 1) / NST)) & 1u);
+          if (n >= 1) mbar_wait_spin(s_free0 + 8 * ((n + 1) & 1), ((uint32_t)(n - 1) >> 1) & 1u);   // S / dP of pair n-1 are in registers
           tc_fence_after();
           issue_sdp(n + 1);
         }
-        mbar_wait(pds_full, (uint32_t)n & 1u);           // P and dS of pair n are in shared memory
+        mbar_wait_spin(pds_full, (uint32_t)n & 1u);           // P and dS of pair n are in shared memory
         tc_fence_after();
         const uint32_t pl = sP >> 4, dsl = sDS >> 4;
         if (!MODE_Q) {
           const uint32_t dol = (do_of(n) >> 4) | kLoMNq, ql = (q_of(n) >> 4) | kLoMNq;
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
-            umma_f16(tmem_base + kBwTAcc + 64, desc(dol + ks * kStepMN), desc((pl | kLoMNq) + ks * kStepMN), idesc_kv, (n | ks) ? 1u : 0u);
+            umma_f16_w(tmem_base + kBwTAcc + 64, desc(dol + ks * kStepMN), desc((pl | kLoMNq) + ks * kStepMN), idesc_kv, (n | ks) ? 1u : 0u);
 #pragma unroll
           for (int ks = 0; ks < 8; ++ks)
-            umma_f16(tmem_base + kBwTAcc, desc(ql + ks * kStepMN), desc((dsl | kLoMNq) + ks * kStepMN), idesc_kv, (n | ks) ? 1u : 0u);
+            umma_f16_w(tmem_base + kBwTAcc, desc(ql + ks * kStepMN), desc((dsl | kLoMNq) + ks * kStepMN), idesc_kv, (n | ks) ? 1u : 0u);
         } else {
           const uint32_t kl = (k_of(n) >> 4) | kLoMNk;
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks)
-            umma_f16(tmem_base + kBwTAcc, desc((dsl | kLoK) + ks * 2u), desc(kl + ks * kStepMN), idesc_q, (n | ks) ? 1u : 0u);
+            umma_f16_w(tmem_base + kBwTAcc, desc((dsl | kLoK) + ks * 2u), desc(kl + ks * kStepMN), idesc_q, (n | ks) ? 1u : 0u);
         }
-        umma_commit(pds_free);
-        umma_commit(st_empty0 + 8 * (n & 1));
+        umma_commit_w(pds_free);
+        umma_commit_w(st_empty0 + 8 * (n % NST));
       }
-      umma_commit(acc_done);
+      umma_commit_w(acc_done);
     }
-  } else if (warp < 4) {
-    // ================= element-wise: thread = query row =================
-    const int r = warp * 32 + lane;
-    const uint32_t lane_addr = (uint32_t)(warp * 32) << 16;
+  } else if (warp < 8) {
+    // ================= element-wise: thread = (query row, half of the key columns) =================
+    const int wq = warp & 3, c = warp >> 2;        // TMEM lane quarter, 32-column half of S / dP
+    const int r = wq * 32 + lane;
+    const uint32_t lane_addr = (uint32_t)(wq * 32) << 16;
     const float sl = p.scale_log2, sc = p.scale;
+    // per-row softmax statistics of the pair: loaded one pair ahead (in mode Q they never change)
+    auto row_stats = [&](int n, float& lse2, float& dl) {
+      int qh, qr, kr;
+      pair_of(n, qh, qr, kr);
+      lse2 = INFINITY; dl = 0.f;
+      if (qr + r < S) {
+        const long long o = ((long long)b * H + qh) * S + qr + r;
+        lse2 = p.lse[o] * 1.4426950408889634f;
+        dl = p.delta[o];
+      }
+    };
+    float lse2_next, dl_next;
+    row_stats(0, lse2_next, dl_next);
     for (int n = 0; n < n_iter; ++n) {
       int qh, qr, kr;
       pair_of(n, qh, qr, kr);
       const int grow = qr + r;
-      float lse2 = INFINITY, dl = 0.f;
-      if (grow < S) {
-        const long long o = ((long long)b * H + qh) * S + grow;
-        lse2 = p.lse[o] * 1.4426950408889634f;
-        dl = p.delta[o];
-      }
+      const float lse2 = lse2_next, dl = dl_next;
+      if (!MODE_Q && n + 1 < n_iter) row_stats(n + 1, lse2_next, dl_next);
       const bool need_mask = (p.causal && kr + kBwBN - 1 > qr) || (kr + kBwBN > S);
       const int lim = p.causal ? min(grow, S - 1) : S - 1;
       const uint32_t buf = (uint32_t)(n & 1) * kBwTBuf;
-      mbar_wait_warp(s_full0 + 8 * (n & 1), ((uint32_t)n >> 1) & 1u);
+      bw_wait_warp(s_full0 + 8 * (n & 1), ((uint32_t)n >> 1) & 1u);
       tc_fence_after();
       const uint32_t prow = sP + (uint32_t)r * 128u, dsrow = sDS + (uint32_t)r * 128u;
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      {
         uint32_t sv[32], dv[32];
         tmem_ld_32x32(tmem_base + lane_addr + kBwTS + buf + c * 32, sv);
         tmem_ld_32x32(tmem_base + lane_addr + kBwTdP + buf + c * 32, dv);
         tmem_ld_wait();
-        if (c == 1) {
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(s_free0 + 8 * (n & 1));
-        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(s_free0 + 8 * (n & 1));
         uint32_t pw[16], dw[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
@@ -290,7 +323,7 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
           pw[i] = bw_pack16<BF16>(p0, p1);
           dw[i] = bw_pack16<BF16>(p0 * (__uint_as_float(dv[2 * i]) - dl) * sc, p1 * (__uint_as_float(dv[2 * i + 1]) - dl) * sc);
         }
-        if (c == 0 && n > 0) mbar_wait_warp(pds_free, (uint32_t)(n - 1) & 1u);    // the products of pair n-1 have read P / dS
+        if (n > 0) bw_wait_warp(pds_free, (uint32_t)(n - 1) & 1u);    // the products of pair n-1 have read P / dS
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           const uint32_t off = (((uint32_t)(c * 4 + g)) ^ ((uint32_t)r & 7u)) << 4;
@@ -305,22 +338,22 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
       if (lane == 0) mbar_arrive(pds_full);
     }
     // ---- write the accumulators out ----
-    mbar_wait_warp(acc_done, 0);
+    bw_wait_warp(acc_done, 0);
     tc_fence_after();
     uint16_t* dq = reinterpret_cast<uint16_t*>(p.dqkv);
     if (!MODE_Q) {
       // TMEM lane = head-dim index d (this thread), column = key: dK^T at kBwTAcc, dV^T at kBwTAcc + 64
-#pragma unroll 1
-      for (int which = 0; which < 2; ++which) {
+      {
+        const int which = c;                       // warps 0-3 write dK, warps 4-7 dV
         const long long col = (long long)(which == 0 ? (H + hk) : (H + Hkv + hk)) * kBwD + r;
 #pragma unroll 1
-        for (int c = 0; c < 2; ++c) {
+        for (int cc = 0; cc < 2; ++cc) {
           uint32_t v[32];
-          tmem_ld_32x32(tmem_base + lane_addr + kBwTAcc + which * 64 + c * 32, v);
+          tmem_ld_32x32(tmem_base + lane_addr + kBwTAcc + which * 64 + cc * 32, v);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 32; ++i) {
-            const int key = kv0 + c * 32 + i;
+            const int key = kv0 + cc * 32 + i;
             if (key < S) {
               const float x = __uint_as_float(v[i]);
               uint16_t o;
@@ -335,24 +368,24 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
       // dQ rows through shared memory (the resident Q tile is dead) for 16-byte coalesced stores
       const uint32_t orow = sRes + (uint32_t)r * 256u;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int cc = 2 * c; cc < 2 * c + 2; ++cc) {
         uint32_t v[32];
-        tmem_ld_32x32(tmem_base + lane_addr + kBwTAcc + c * 32, v);
+        tmem_ld_32x32(tmem_base + lane_addr + kBwTAcc + cc * 32, v);
         tmem_ld_wait();
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint32_t w[4];
 #pragma unroll
           for (int e = 0; e < 4; ++e) w[e] = bw_pack16<BF16>(__uint_as_float(v[g * 8 + e * 2]), __uint_as_float(v[g * 8 + e * 2 + 1]));
-          const uint32_t chunk = (uint32_t)(c * 4 + g);
+          const uint32_t chunk = (uint32_t)(cc * 4 + g);
           asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(orow + ((chunk ^ ((uint32_t)r & 15u)) << 4)), "r"(w[0]),
                        "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
         }
       }
-      __syncwarp();
+      asm volatile("bar.sync 1, 256;" ::: "memory");      // both column halves of every row are in shared memory
 #pragma unroll 4
-      for (int it = 0; it < 16; ++it) {
-        const int rr = warp * 32 + it * 2 + (lane >> 4), chunk = lane & 15;
+      for (int it = 0; it < 8; ++it) {
+        const int rr = warp * 16 + it * 2 + (lane >> 4), chunk = lane & 15;
         uint32_t w0, w1, w2, w3;
         asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(w0), "=r"(w1), "=r"(w2), "=r"(w3)
                      : "r"(sRes + (uint32_t)rr * 256u + (((uint32_t)chunk ^ ((uint32_t)rr & 15u)) << 4)));
@@ -363,7 +396,7 @@ flash_bwd_tc_kernel(const __grid_constant__ CUtensorMap tmq, const __grid_consta
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == 9) {
     tc_fence_after();
     tmem_dealloc(tmem_base, kBwTmemCols);
   }

@@ -59,6 +59,34 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, ui
       : "memory");
 }
 
+// The same instructions issued from CONVERGED warp code (every lane of the issuing warp runs the loop, elect.sync picks the
+// lane): descriptors stay in uniform registers. From inside `if (lane == 0)` each UTCHMMA costs two R2UR moves and a
+// divergence loop — more cycles than a 128 x 64 x 16 product spends on the tensor pipe.
+__device__ __forceinline__ void umma_f16_w(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_f16_ts_w(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_w(uint32_t bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar) : "memory");
+}
+
 template <bool BF16>
 __device__ __forceinline__ uint32_t pack16(float a, float b) {
   if (BF16) return pack_bf16x2(a, b);
@@ -125,7 +153,7 @@ flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm, const FlashTcParams 
       }
     }
   } else if (warp == 5) {
-    if (lane == 0) {
+    {   // the whole warp runs this block (see umma_f16_w)
       // descriptors: hi word = SBO 1024 | version 1 | 128B swizzle; lo word = address >> 4 (| LBO << 16 for MN-major)
       constexpr uint32_t kHi = (1024u >> 4) | (1u << 14) | (kSwizzle128B << 29);
       constexpr uint32_t kLoK = (16u >> 4) << 16, kLoMN = (8192u >> 4) << 16;
@@ -141,34 +169,34 @@ flash_fwd_tc_kernel(const __grid_constant__ CUtensorMap tm, const FlashTcParams 
         for (int half = 0; half < 2; ++half)
 #pragma unroll
           for (int ks = 0; ks < 4; ++ks)
-            umma_f16(tS + s * kTcBN, desc(qlo + half * (16384u >> 4) + ks * 2u), desc(klo + half * (8192u >> 4) + ks * 2u),
+            umma_f16_w(tS + s * kTcBN, desc(qlo + half * (16384u >> 4) + ks * 2u), desc(klo + half * (8192u >> 4) + ks * 2u),
                      idesc_qk, (half | ks) ? 1u : 0u);
-        umma_commit(s_full0 + 8 * s);
+        umma_commit_w(s_full0 + 8 * s);
       };
-      mbar_wait(q_full, 0);
-      mbar_wait(kv_full0, 0);
+      mbar_wait_spin(q_full, 0);
+      mbar_wait_spin(kv_full0, 0);
       tc_fence_after();
       issue_qk(0);
       for (int j = 0; j < nblk; ++j) {
         const int s = j & 1;
         if (j + 1 < nblk) {
-          mbar_wait(kv_full0 + 8 * ((j + 1) & 1), ((uint32_t)(j + 1) >> 1) & 1u);
+          mbar_wait_spin(kv_full0 + 8 * ((j + 1) & 1), ((uint32_t)(j + 1) >> 1) & 1u);
           // S buffer (j+1)&1 last held block j-1. PT: P(j-1) sat in it and PV(j-1) was issued before this UMMA, the pipe
           // runs in order. Otherwise: the softmax warps have pulled S(j-1) into registers.
-          if (!PT && j >= 1) mbar_wait(s_free0 + 8 * ((j + 1) & 1), ((uint32_t)(j - 1) >> 1) & 1u);
+          if (!PT && j >= 1) mbar_wait_spin(s_free0 + 8 * ((j + 1) & 1), ((uint32_t)(j - 1) >> 1) & 1u);
           tc_fence_after();
           issue_qk(j + 1);
         }
-        mbar_wait(p_full, (uint32_t)j & 1u);               // P(j) is written (and O rescaled where a row needed it)
+        mbar_wait_spin(p_full, (uint32_t)j & 1u);               // P(j) is written (and O rescaled where a row needed it)
         tc_fence_after();
         const uint32_t vlo = ((sbase + kTcSmemV + s * kTcKVStage) >> 4) | kLoMN;
 #pragma unroll
         for (int ks = 0; ks < 4; ++ks) {
-          if (PT) umma_f16_ts(tO, tS + s * kTcBN + ks * 8, desc(vlo + ks * (2048u >> 4)), idesc_pv, (j | ks) ? 1u : 0u);
-          else umma_f16(tO, desc(plo + ks * 2u), desc(vlo + ks * (2048u >> 4)), idesc_pv, (j | ks) ? 1u : 0u);
+          if (PT) umma_f16_ts_w(tO, tS + s * kTcBN + ks * 8, desc(vlo + ks * (2048u >> 4)), idesc_pv, (j | ks) ? 1u : 0u);
+          else umma_f16_w(tO, desc(plo + ks * 2u), desc(vlo + ks * (2048u >> 4)), idesc_pv, (j | ks) ? 1u : 0u);
         }
-        umma_commit(o_done);
-        umma_commit(kv_empty0 + 8 * s);
+        umma_commit_w(o_done);
+        umma_commit_w(kv_empty0 + 8 * s);
       }
     }
   } else if (warp < 4) {
