@@ -82,6 +82,14 @@ struct GemmKernelParams {
 // elements, possibly split by rows over up to 8 buffers (ZeRO-3 shards in peer memory, read through NVLink by TMA).
 // w = lut[code] * scale - zs. b_mn = 0: B = W (forward, GEMM N = rows, K = kw); b_mn = 1: B = W^T read in place
 // (dgrad, GEMM N = kw, K = rows).
+// Timing experiments on the fused 4-bit path (skip table look-ups, fences, barrier legs, ...) are compiled out of the
+// shipped kernel: W4DBG(mask) is the constant 0 unless the library is built with -DB200_W4_EXPERIMENT.
+#ifdef B200_W4_EXPERIMENT
+#define W4DBG(mask) (w4->debug & (mask))
+#else
+#define W4DBG(mask) 0
+#endif
+
 struct W4Params {
   CUtensorMap tmW[8];
   const float* scale[8];
@@ -90,7 +98,7 @@ struct W4Params {
   int nshards, rows_per_shard, group, kw;
   int raw_stages, is_bf16;
   int lut_bytes;
-  int debug;  // B200_W4_DEBUG bit mask (timing experiments only): 1 no table look-ups, 2 no proxy fence, 4 release.cluster arrive
+  int debug;  // B200_W4_DEBUG bit mask; only read when the library is built with -DB200_W4_EXPERIMENT (timing experiments)
 };
 
 constexpr int kW4Threads = 480;      // + 8 dequant warps + 1 packed-tile TMA warp
@@ -388,12 +396,12 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
     }
     for (int s = 0; s < p.stages; ++s) {
       // one arrival per CTA's producer (+ the TMA transaction bytes) (+ W4: the dequant warps of every CTA)
-      mbar_init(full_bar(s), (W4 && !(w4->debug & 128)) ? CTAS * 2 : CTAS);   // W4: + one arrival per CTA from its dequant warps
+      mbar_init(full_bar(s), (W4 && !W4DBG(128)) ? CTAS * 2 : CTAS);   // W4: + one arrival per CTA from its dequant warps
       mbar_init(empty_bar(s), 1);     // tcgen05.commit (multicast to both CTAs of a pair)
     }
     for (int s = 0; s < raw_stages; ++s) {
       mbar_init(rfull_bar(s), 1);
-      mbar_init(rempty_bar(s), (w4->debug & 256) ? 1 : kW4DqWarps);
+      mbar_init(rempty_bar(s), W4DBG(256) ? 1 : kW4DqWarps);
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
@@ -455,7 +463,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
           mbar_wait(empty_bar(stage), phase ^ 1u);
           const uint32_t fb_local = full_bar(stage);
           const uint32_t fb = leader ? fb_local : mapa_shared(fb_local, 0);  // the leader's barrier
-          const bool dbg_b = W4 && (w4->debug & 64);   // timing experiment: also stream a (dummy) B tile through TMA
+          const bool dbg_b = W4 && W4DBG(64);   // timing experiment: also stream a (dummy) B tile through TMA
           if (leader) mbar_arrive_expect_tx(fb_local, (W4 && kb < p.num_k && !dbg_b) ? tx_a_only : tx_full);
           else mbar_arrive_cluster(fb);
           const uint32_t sa = sA0 + (uint32_t)stage * kStageABytes;
@@ -549,7 +557,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         if (acc == 0) acc_phase ^= 1u;
       }
     }
-  } else if (W4 && warp >= 6 && ((w4->debug & 128) || ((w4->debug & 256) && warp > 6 && warp < 6 + kW4DqWarps))) {
+  } else if (W4 && warp >= 6 && (W4DBG(128) || (W4DBG(256) && warp > 6 && warp < 6 + kW4DqWarps))) {
     // timing experiment: the extra warps stay out of the way
   } else if (W4 && warp == 6 + kW4DqWarps) {
     // ================= packed-weight TMA producer: runs `raw_stages` k-blocks ahead of the dequant warps ========
@@ -564,7 +572,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
         const int n0 = n_blk * p.bn + (int)rank * bn_cta;
         for (int kb = sg.kb0; kb < sg.kb1 && kb < p.num_k; ++kb) {
           mbar_wait(rempty_bar(rs), rphase ^ 1u);
-          if (w4->debug & 32) {   // timing experiment: no packed-tile traffic
+          if (W4DBG(32)) {   // timing experiment: no packed-tile traffic
             mbar_arrive(rfull_bar(rs));
             if (++rs == raw_stages) { rs = 0; rphase ^= 1u; }
             continue;
@@ -637,7 +645,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
               const __half2 a = __floats2half2_rn(sc, sc), b = __floats2half2_rn(-zs, -zs);
               sc2 = *reinterpret_cast<const uint32_t*>(&a); nz2 = *reinterpret_cast<const uint32_t*>(&b);
             }
-            if (w4->debug & 8) {   // timing experiment: no expansion at all, only the barrier traffic
+            if (W4DBG(8)) {   // timing experiment: no expansion at all, only the barrier traffic
               mbar_wait(rfull_bar(rs), rphase);
               __syncwarp();
               if (lane == 0) mbar_arrive(rempty_bar(rs));
@@ -656,7 +664,7 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 #pragma unroll
               for (int b = 0; b < 4; ++b) {
                 const uint32_t off = b == 0 ? (w[c] << 7) & 0x7F80u : (w[c] >> (8 * b - 7)) & 0x7F80u;
-                if (w4->debug & 1) v[c * 4 + b] = off;
+                if (W4DBG(1)) v[c * 4 + b] = off;
                 else asm("ld.shared.u32 %0, [%1];" : "=r"(v[c * 4 + b]) : "r"(lut_lane + off));
               }
             }
@@ -675,17 +683,17 @@ __device__ __forceinline__ void gemm_body(const CUtensorMap& tmA, const CUtensor
 #pragma unroll
                 for (int b = 0; b < 4; ++b) asm("fma.rn.f16x2 %0, %1, %2, %3;" : "=r"(o[b]) : "r"(v[c * 4 + b]), "r"(sc2), "r"(nz2));
               }
-              if (!(w4->debug & 16))
+              if (!W4DBG(16))
               asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (((uint32_t)(sub * 4 + c) ^ key) << 4)), "r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]) : "memory");
               else asm volatile("" ::"r"(o[0]), "r"(o[1]), "r"(o[2]), "r"(o[3]));
             }
-            if (!(w4->debug & 2)) fence_proxy_async_smem();   // generic-proxy stores to this CTA's smem -> visible to tcgen05.mma
+            if (!W4DBG(2)) fence_proxy_async_smem();   // generic-proxy stores to this CTA's smem -> visible to tcgen05.mma
           } else {
             mbar_wait(empty_bar(stage), phase ^ 1u);             // LoRA k-block: B2 comes from TMA, nothing to expand
           }
         signal:
-          if (!(w4->debug & 256)) asm volatile("bar.sync 2, 256;" ::: "memory");   // all dequant warps of this CTA wrote (and fenced) their part
-          if (t == 0 && !(w4->debug & 4)) {
+          if (!W4DBG(256)) asm volatile("bar.sync 2, 256;" ::: "memory");   // all dequant warps of this CTA wrote (and fenced) their part
+          if (t == 0 && !W4DBG(4)) {
             // same signalling as a TMA-less CUTLASS producer: proxy fence by every writer, then a plain arrive
             if (leader) mbar_arrive(fb_local);
             else mbar_arrive_cluster(mapa_shared(fb_local, 0));
@@ -1243,7 +1251,11 @@ B200_API int b200_gemm_w4(const b200_gemm_args* a, const b200_w4_desc* w, void* 
   wp.raw_stages = raw_stages;
   wp.lut_bytes = lut_bytes;
   wp.is_bf16 = a->in_dtype == B200_DT_BF16;
+#ifdef B200_W4_EXPERIMENT
   { const char* d = getenv("B200_W4_DEBUG"); wp.debug = d ? atoi(d) : 0; }
+#else
+  wp.debug = 0;
+#endif
 
   const int grid = (p.stream_k ? units : (int)(tiles < units ? tiles : units)) * ctas;
   const int smem = stages * stage_bytes + raw_stages * kRawStageBytes + lut_bytes + 8 * (2 * stages + 5 + 2 * raw_stages) + 1024;
