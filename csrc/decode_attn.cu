@@ -30,6 +30,32 @@ __device__ __forceinline__ void load_row(const T* __restrict__ p, float (&out)[P
   }
 }
 
+// Where position t of a sequence lives. Slot pool (tbl == nullptr): the sequence owns row `slot` of a [slots, Hkv, max_len, D]
+// cache. Paged (tbl = the sequence's row of the block table): the cache is [blocks, Hkv, block, D] and logical block
+// t / block maps to physical block tbl[t / block] (block = 1 << bshift) - vLLM's PagedAttention layout
+// (LLM_on_Kubernetes/Inference_Platfrom/README.md:1504-1509 serves through it).
+struct KvAddr {
+  const int* tbl;
+  long long slot_base;   // slot pool: (slot * Hkv + kvh) * max_len * D
+  long long head_off;    // paged: kvh * block * D
+  long long blk_stride;  // paged: Hkv * block * D
+  int bshift, bmask, D;
+  __device__ __forceinline__ long long row(int t) const {
+    if (tbl == nullptr) return slot_base + (long long)t * D;
+    return (long long)tbl[t >> bshift] * blk_stride + head_off + (long long)(t & bmask) * D;
+  }
+};
+__device__ __forceinline__ KvAddr make_kv_addr(const int* block_table, int table_stride, int bshift, long long slot, int Hkv,
+                                               int kvh, int max_len, int D) {
+  KvAddr a;
+  a.tbl = block_table ? block_table + slot * table_stride : nullptr;
+  a.slot_base = (slot * Hkv + kvh) * (long long)max_len * D;
+  a.bshift = bshift; a.bmask = (1 << bshift) - 1; a.D = D;
+  a.head_off = (long long)kvh * (1 << bshift) * D;
+  a.blk_stride = (long long)Hkv * (1 << bshift) * D;
+  return a;
+}
+
 // qkv: [B, (H + 2 Hkv) * D] (post-RoPE) for the new token; cache_k / cache_v: [B, Hkv, max_len, D];
 // pos[b] = index the new token is written at (= number of tokens already cached); slots[b] (optional) = cache row
 // of batch row b; out: [B, H * D]
@@ -37,7 +63,7 @@ template <typename T, int D>
 __global__ void __launch_bounds__(128)
 decode_attn_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __restrict__ cache_v,
                    const int* __restrict__ pos, const int* __restrict__ slots, T* __restrict__ out, int H, int Hkv, int max_len,
-                   float scale, int window) {
+                   float scale, int window, const int* __restrict__ block_table, int table_stride, int bshift) {
   constexpr int PER = D / 32;  // elements per lane
   pdl_launch_dependents();
   pdl_wait();
@@ -47,13 +73,15 @@ decode_attn_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __rest
   const int t_new = pos[b];
   const long long row = (long long)b * (H + 2 * Hkv) * D;
   const long long slot = slots ? slots[b] : b;  // continuous batching: batch row -> cache slot
-  T* kc = cache_k + (slot * Hkv + kvh) * max_len * D;
-  T* vc = cache_v + (slot * Hkv + kvh) * max_len * D;
+  const KvAddr ka = make_kv_addr(block_table, table_stride, bshift, slot, Hkv, kvh, max_len, D);
+  T* kc = cache_k;
+  T* vc = cache_v;
   // append the new K / V row once per kv head (the first query head of the group does it)
   if (h % (H / Hkv) == 0 && warp == 0) {
+    const long long rn = ka.row(t_new);
     for (int i = lane; i < D; i += 32) {
-      kc[(long long)t_new * D + i] = qkv[row + (long long)(H + kvh) * D + i];
-      vc[(long long)t_new * D + i] = qkv[row + (long long)(H + Hkv + kvh) * D + i];
+      kc[rn + i] = qkv[row + (long long)(H + kvh) * D + i];
+      vc[rn + i] = qkv[row + (long long)(H + Hkv + kvh) * D + i];
     }
   }
   float q[PER];
@@ -78,8 +106,9 @@ decode_attn_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __rest
     for (int u = 0; u < UN; ++u) {
       const int t = tb + u;
       if (t <= t_new) {
-        load_row<T, PER>(t == t_new ? knew : kc + (long long)t * D + lane * PER, kx[u]);
-        load_row<T, PER>(t == t_new ? vnew : vc + (long long)t * D + lane * PER, vx[u]);
+        const long long rt = t == t_new ? 0 : ka.row(t);
+        load_row<T, PER>(t == t_new ? knew : kc + rt + lane * PER, kx[u]);
+        load_row<T, PER>(t == t_new ? vnew : vc + rt + lane * PER, vx[u]);
       } else {
 #pragma unroll
         for (int i = 0; i < PER; ++i) { kx[u][i] = 0.f; vx[u][i] = 0.f; }
@@ -143,7 +172,7 @@ template <typename T, int D, int G>
 __global__ void __launch_bounds__(128)
 decode_attn_split_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* __restrict__ cache_v,
                          const int* __restrict__ pos, const int* __restrict__ slots, float* __restrict__ part, int H, int Hkv,
-                         int max_len, float scale, int nsplit) {
+                         int max_len, float scale, int nsplit, const int* __restrict__ block_table, int table_stride, int bshift) {
   constexpr int PER = D / 32, CH = D / 8;   // output channels per lane; 16-byte chunks per row
   pdl_launch_dependents();
   pdl_wait();
@@ -156,14 +185,16 @@ decode_attn_split_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* 
   const int t_new = pos[b];
   const long long row = (long long)b * (H + 2 * Hkv) * D;
   const long long slot = slots ? slots[b] : b;
-  T* kc = cache_k + (slot * Hkv + kvh) * max_len * D;
-  T* vc = cache_v + (slot * Hkv + kvh) * max_len * D;
+  const KvAddr ka = make_kv_addr(block_table, table_stride, bshift, slot, Hkv, kvh, max_len, D);
+  T* kc = cache_k;
+  T* vc = cache_v;
   const T* knew = qkv + row + (long long)(H + kvh) * D;
   const T* vnew = qkv + row + (long long)(H + Hkv + kvh) * D;
   if (sp == 0 && warp == 0) {   // append the new token's K / V (read back from qkv below, never from the cache)
+    const long long rn = ka.row(t_new);
     for (int i = lane; i < D; i += 32) {
-      kc[(long long)t_new * D + i] = knew[i];
-      vc[(long long)t_new * D + i] = vnew[i];
+      kc[rn + i] = knew[i];
+      vc[rn + i] = vnew[i];
     }
   }
   for (int i = threadIdx.x; i < G * D; i += 128)
@@ -180,7 +211,7 @@ decode_attn_split_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* 
     // ---- scores: lane = position ----
     const int t = base + lane;
     const bool valid = t <= t_new;
-    const T* kr = !valid ? knew : (t == t_new ? knew : kc + (long long)t * D);
+    const T* kr = !valid ? knew : (t == t_new ? knew : kc + ka.row(t));
     float s[G];
 #pragma unroll
     for (int h = 0; h < G; ++h) s[h] = 0.f;
@@ -217,7 +248,7 @@ decode_attn_split_kernel(const T* __restrict__ qkv, T* __restrict__ cache_k, T* 
     for (int tt = 0; tt < nv_; ++tt) {
       const int tv = base + tt;
       float vf[PER];
-      load_row<T, PER>((tv == t_new ? vnew : vc + (long long)tv * D) + lane * PER, vf);
+      load_row<T, PER>((tv == t_new ? vnew : vc + ka.row(tv)) + lane * PER, vf);
 #pragma unroll
       for (int h = 0; h < G; ++h) {
         const float p = ps[warp][h][tt];
@@ -276,9 +307,15 @@ using namespace b200;
 
 // scratch: B * H * nsplit * (D + 2) floats. Returns B200_ERR_UNSUPPORTED for shapes the split kernel does not cover
 // (callers use b200_decode_attn then).
-B200_API int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out,
-                                    float* scratch, int B, int H, int Hkv, int D, int max_len, float scale, int nsplit,
-                                    int dtype, void* stream) {
+static int log2_exact(int v) {
+  int s = 0;
+  while ((1 << s) < v) ++s;
+  return (1 << s) == v ? s : -1;
+}
+
+static int decode_attn_split_impl(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out,
+                                  float* scratch, int B, int H, int Hkv, int D, int max_len, float scale, int nsplit,
+                                  int dtype, void* stream, const int* block_table, int table_stride, int bshift) {
   if (B <= 0 || H % Hkv || nsplit < 1 || nsplit > 64) return B200_ERR_BAD_SHAPE;
   if (dtype != B200_DT_BF16 && dtype != B200_DT_FP16) return B200_ERR_UNSUPPORTED;
   const int G = H / Hkv;
@@ -287,7 +324,7 @@ B200_API int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_
 #define B200_DS(T, DD, GG)                                                                                              \
   do {                                                                                                                  \
     launch_pdl(decode_attn_split_kernel<T, DD, GG>, grid, 128, 0, st, (const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, \
-               scratch, H, Hkv, max_len, scale, nsplit);                                                               \
+               scratch, H, Hkv, max_len, scale, nsplit, block_table, table_stride, bshift);                            \
     launch_pdl(decode_attn_combine_kernel<T, DD>, grid2, DD, 0, st, (const float*)scratch, (T*)out, nsplit);            \
   } while (0)
 #define B200_DS_G(T, DD)                                                         \
@@ -305,12 +342,31 @@ B200_API int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_
   return 0;
 }
 
-B200_API int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B, int H,
-                              int Hkv, int D, int max_len, float scale, int window, int dtype, void* stream) {
+B200_API int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out,
+                                    float* scratch, int B, int H, int Hkv, int D, int max_len, float scale, int nsplit,
+                                    int dtype, void* stream) {
+  return decode_attn_split_impl(qkv, cache_k, cache_v, pos, slots, out, scratch, B, H, Hkv, D, max_len, scale, nsplit, dtype, stream,
+                                nullptr, 0, 0);
+}
+
+// Paged KV cache: cache_k / cache_v [blocks, Hkv, block_size, D]; block_table [rows, table_stride] int32 (device), row
+// slots[b] (or b) lists the physical blocks of sequence b in logical order; block_size a power of two.
+B200_API int b200_decode_attn_split_paged(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots,
+                                          void* out, float* scratch, int B, int H, int Hkv, int D, const int* block_table,
+                                          int table_stride, int block_size, float scale, int nsplit, int dtype, void* stream) {
+  const int sh = log2_exact(block_size);
+  if (!block_table || sh < 0 || table_stride < 1) return B200_ERR_BAD_SHAPE;
+  return decode_attn_split_impl(qkv, cache_k, cache_v, pos, slots, out, scratch, B, H, Hkv, D, block_size, scale, nsplit, dtype,
+                                stream, block_table, table_stride, sh);
+}
+
+static int decode_attn_impl(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B, int H,
+                            int Hkv, int D, int max_len, float scale, int window, int dtype, void* stream,
+                            const int* block_table, int table_stride, int bshift) {
   if (B <= 0 || H % Hkv) return B200_ERR_BAD_SHAPE;
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned grid = (unsigned)(B * H);
-#define B200_DA(T, DD) launch_pdl(decode_attn_kernel<T, DD>, grid, 128, 0, st, (const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, (T*)out, H, Hkv, max_len, scale, window)
+#define B200_DA(T, DD) launch_pdl(decode_attn_kernel<T, DD>, grid, 128, 0, st, (const T*)qkv, (T*)cache_k, (T*)cache_v, pos, slots, (T*)out, H, Hkv, max_len, scale, window, block_table, table_stride, bshift)
   if (dtype == B200_DT_BF16) {
     if (D == 128) B200_DA(__nv_bfloat16, 128); else if (D == 64) B200_DA(__nv_bfloat16, 64);
     else if (D == 32) B200_DA(__nv_bfloat16, 32); else if (D == 96) B200_DA(__nv_bfloat16, 96); else return B200_ERR_UNSUPPORTED;
@@ -324,4 +380,18 @@ B200_API int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, con
 #undef B200_DA
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+B200_API int b200_decode_attn(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B, int H,
+                              int Hkv, int D, int max_len, float scale, int window, int dtype, void* stream) {
+  return decode_attn_impl(qkv, cache_k, cache_v, pos, slots, out, B, H, Hkv, D, max_len, scale, window, dtype, stream, nullptr, 0, 0);
+}
+
+B200_API int b200_decode_attn_paged(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B,
+                                    int H, int Hkv, int D, const int* block_table, int table_stride, int block_size, float scale,
+                                    int window, int dtype, void* stream) {
+  const int sh = log2_exact(block_size);
+  if (!block_table || sh < 0 || table_stride < 1) return B200_ERR_BAD_SHAPE;
+  return decode_attn_impl(qkv, cache_k, cache_v, pos, slots, out, B, H, Hkv, D, block_size, scale, window, dtype, stream, block_table,
+                          table_stride, sh);
 }

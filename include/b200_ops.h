@@ -353,6 +353,18 @@ int b200_decode_attn_split(const void* qkv, void* cache_k, void* cache_v, const 
                            float* scratch, int B, int H, int Hkv, int D, int max_len, float scale, int nsplit,
                            int dtype, void* stream);
 
+/* The same two kernels over a PAGED cache (vLLM's PagedAttention layout, the engine behind every `vllm serve` deployment
+ * of the reference, LLM_on_Kubernetes/Inference_Platfrom/README.md:1504-1509): cache_k / cache_v are
+ * [blocks, Hkv, block_size, D]; block_table [rows, table_stride] int32 on the device, row slots[b] (or b) lists the
+ * physical blocks of sequence b in logical order; block_size a power of two. Position t of a sequence lives in block
+ * block_table[row][t / block_size] at offset t % block_size. */
+int b200_decode_attn_paged(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out, int B,
+                           int H, int Hkv, int D, const int* block_table, int table_stride, int block_size, float scale,
+                           int window, int dtype, void* stream);
+int b200_decode_attn_split_paged(const void* qkv, void* cache_k, void* cache_v, const int* pos, const int* slots, void* out,
+                                 float* scratch, int B, int H, int Hkv, int D, const int* block_table, int table_stride,
+                                 int block_size, float scale, int nsplit, int dtype, void* stream);
+
 /* ---- flash attention for training / prefill (csrc/flash_attn.cu) ----------------------------------
  * softmax(Q K^T * scale [+ causal mask]) V read in place from the fused projection qkv [B*S, (H + 2 Hkv) * D]; context to
  * out [B*S, H*D], row log-sum-exp (natural log) to lse [B, H, S]. No S x S tensor, no mask tensor (the reference builds

@@ -70,14 +70,70 @@ def sample_next(logits: torch.Tensor, cfg: GenerationConfig, prev: Optional[torc
 
 
 class KVCache:
+    """Slot pool: sequence ``slot`` owns row ``slot`` of ``k[layer]`` / ``v[layer]`` [slots, Hkv, max_len, D]."""
+    paged = False
+
     def __init__(self, n_layers, B, Hkv, max_len, D, dtype, device):
         self.k = [torch.zeros(B, Hkv, max_len, D, dtype=dtype, device=device) for _ in range(n_layers)]
         self.v = [torch.zeros(B, Hkv, max_len, D, dtype=dtype, device=device) for _ in range(n_layers)]
         self.max_len = max_len
         self.len = 0
 
+    def store(self, li: int, rows: torch.Tensor, pos: torch.Tensor, k: torch.Tensor, v: torch.Tensor) -> None:
+        """k / v [T, Hkv, D] of token t -> position pos[t] of sequence rows[t] (both long [T])."""
+        self.k[li][rows, :, pos] = k
+        self.v[li][rows, :, pos] = v
 
-def _decode_attn(qkv, ck, cv, pos, H, Hkv, D, scale, slots=None):
+    def seq_view(self, li: int, slot: int, n: int):
+        """(K, V) of sequence ``slot`` as [Hkv, >= n, D] tensors (positions 0 .. n-1 valid)."""
+        return self.k[li][slot], self.v[li][slot]
+
+
+class PagedKVCache(KVCache):
+    """vLLM's PagedAttention layout (the engine behind every `vllm serve` deployment of the reference,
+    LLM_on_Kubernetes/Inference_Platfrom/README.md:1504-1509): ``k[layer]`` / ``v[layer]`` are
+    [num_blocks, Hkv, block_size, D]; ``table`` [max_seqs, max_blocks] int32 maps the logical blocks of every sequence to
+    physical ones. Memory is committed per ``block_size`` tokens a sequence actually holds, not per ``max_len``; two
+    sequences may list the same physical block (a shared prompt prefix). The block allocator lives with the scheduler
+    (serve/engine.py); this class only holds the storage and the table."""
+    paged = True
+
+    def __init__(self, n_layers, num_blocks, Hkv, block_size, D, dtype, device, max_seqs, max_len):
+        if block_size & (block_size - 1):
+            raise ValueError("block_size must be a power of two")
+        self.k = [torch.zeros(num_blocks, Hkv, block_size, D, dtype=dtype, device=device) for _ in range(n_layers)]
+        self.v = [torch.zeros(num_blocks, Hkv, block_size, D, dtype=dtype, device=device) for _ in range(n_layers)]
+        self.block_size, self.num_blocks = block_size, num_blocks
+        self.max_len = max_len
+        self.max_blocks = -(-max_len // block_size)
+        self.table = torch.zeros(max_seqs, self.max_blocks, dtype=torch.int32, device=device)
+        self.len = 0
+
+    def set_row(self, slot: int, blocks) -> None:
+        """Logical block j of sequence ``slot`` -> physical block blocks[j]."""
+        if len(blocks):
+            self.table[slot, :len(blocks)] = torch.as_tensor(list(blocks), dtype=torch.int32).to(self.table.device, non_blocking=True)
+
+    def _where(self, rows, pos):
+        blk = self.table[rows, pos // self.block_size].long()
+        return blk, pos % self.block_size
+
+    def store(self, li, rows, pos, k, v):
+        blk, off = self._where(rows, pos)
+        self.k[li][blk, :, off] = k
+        self.v[li][blk, :, off] = v
+
+    def seq_view(self, li, slot, n):
+        nb = -(-n // self.block_size)
+        blks = self.table[slot, :nb].long()
+        Hkv, D = self.k[li].shape[1], self.k[li].shape[3]
+        k = self.k[li].index_select(0, blks).permute(1, 0, 2, 3).reshape(Hkv, nb * self.block_size, D)
+        v = self.v[li].index_select(0, blks).permute(1, 0, 2, 3).reshape(Hkv, nb * self.block_size, D)
+        return k, v
+
+
+def _decode_attn(qkv, ck, cv, pos, H, Hkv, D, scale, slots=None, table=None):
+    """``table`` (int32 [rows, max_blocks]): ck / cv are a paged cache [blocks, Hkv, block_size, D]."""
     B = qkv.shape[0]
     if nv.use_native(qkv):
         out = torch.empty(B, H * D, dtype=qkv.dtype, device=qkv.device)
@@ -85,25 +141,46 @@ def _decode_attn(qkv, ck, cv, pos, H, Hkv, D, scale, slots=None):
             # K/V read once per GQA group; enough (sequence, kv head, split) CTAs to fill the 148 SMs about twice
             nsplit = max(1, min(16, -(-296 // (B * Hkv))))
             scratch = torch.empty(B * H * nsplit * (D + 2), dtype=torch.float32, device=qkv.device)
-            fs = nv.proto("b200_decode_attn_split", [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
-            nv.check(fs(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), nv.ptr(scratch), B, H, Hkv, D,
-                        ck.shape[2], scale, nsplit, nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn_split")
+            if table is not None:
+                fp = nv.proto("b200_decode_attn_split_paged", [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, f32, i32, i32, vp])
+                nv.check(fp(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), nv.ptr(scratch), B, H, Hkv, D,
+                            nv.ptr(table), table.shape[1], ck.shape[2], scale, nsplit, nv.dtype_code(qkv.dtype), nv.stream()),
+                         "decode_attn_split_paged")
+            else:
+                fs = nv.proto("b200_decode_attn_split", [vp, vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
+                nv.check(fs(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), nv.ptr(scratch), B, H, Hkv, D,
+                            ck.shape[2], scale, nsplit, nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn_split")
             nv.count_launch(2)
             return out
-        fn = nv.proto("b200_decode_attn", [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
-        nv.check(fn(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), B, H, Hkv, D, ck.shape[2], scale, 0,
-                    nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn")
+        if table is not None:
+            fp = nv.proto("b200_decode_attn_paged", [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, vp, i32, i32, f32, i32, i32, vp])
+            nv.check(fp(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), B, H, Hkv, D, nv.ptr(table),
+                        table.shape[1], ck.shape[2], scale, 0, nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn_paged")
+        else:
+            fn = nv.proto("b200_decode_attn", [vp, vp, vp, vp, vp, vp, i32, i32, i32, i32, i32, f32, i32, i32, vp])
+            nv.check(fn(nv.ptr(qkv), nv.ptr(ck), nv.ptr(cv), nv.ptr(pos), nv.ptr(slots), nv.ptr(out), B, H, Hkv, D, ck.shape[2], scale, 0,
+                        nv.dtype_code(qkv.dtype), nv.stream()), "decode_attn")
         nv.count_launch()
         return out
     x = qkv.view(B, H + 2 * Hkv, D)
     g = H // Hkv
     rows = (slots if slots is not None else torch.arange(B, device=qkv.device)).long()
     p = pos.long()
-    ck[rows, :, p] = x[:, H:H + Hkv]
-    cv[rows, :, p] = x[:, H + Hkv:]
     tmax = int(p.max()) + 1
-    k = ck[rows, :, :tmax].float().repeat_interleave(g, 1)
-    v = cv[rows, :, :tmax].float().repeat_interleave(g, 1)
+    if table is not None:
+        BS = ck.shape[2]
+        blk = table[rows, p // BS].long()
+        ck[blk, :, p % BS] = x[:, H:H + Hkv]
+        cv[blk, :, p % BS] = x[:, H + Hkv:]
+        nb = -(-tmax // BS)
+        tb = table[rows, :nb].long()                                             # [B, nb]
+        k = ck[tb].permute(0, 2, 1, 3, 4).reshape(B, Hkv, nb * BS, D)[:, :, :tmax].float().repeat_interleave(g, 1)
+        v = cv[tb].permute(0, 2, 1, 3, 4).reshape(B, Hkv, nb * BS, D)[:, :, :tmax].float().repeat_interleave(g, 1)
+    else:
+        ck[rows, :, p] = x[:, H:H + Hkv]
+        cv[rows, :, p] = x[:, H + Hkv:]
+        k = ck[rows, :, :tmax].float().repeat_interleave(g, 1)
+        v = cv[rows, :, :tmax].float().repeat_interleave(g, 1)
     s = torch.einsum("bhd,bhtd->bht", x[:, :H].float(), k) * scale
     s = s.masked_fill(torch.arange(tmax, device=qkv.device)[None, None, :] > p[:, None, None], float("-inf"))
     return torch.einsum("bht,bhtd->bhd", s.softmax(-1), v).reshape(B, H * D).to(qkv.dtype)
@@ -127,17 +204,16 @@ class Generator:
         m, c = self.model, self.cfg
         B, S = ids.shape
         dev = ids.device
-        rows = slots.long() if slots is not None else slice(None)
         H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
         cos, sin = m.rope(dev, self.max_len)
         pos = torch.arange(S, device=dev, dtype=torch.int32).repeat(B)
+        srow = (slots.long() if slots is not None else torch.arange(B, device=dev)).repeat_interleave(S)   # cache row of every token
         delta, res = ew.embedding(ids.reshape(-1), m.embed_tokens), None
         for li, layer in enumerate(m.layers):
             x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
             qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
-            t = qkv.view(B, S, H + 2 * Hkv, D)
-            cache.k[li][rows, :, :S] = t[:, :, H:H + Hkv].permute(0, 2, 1, 3)
-            cache.v[li][rows, :, :S] = t[:, :, H + Hkv:].permute(0, 2, 1, 3)
+            t = qkv.view(B * S, H + 2 * Hkv, D)
+            cache.store(li, srow, pos.long(), t[:, H:H + Hkv], t[:, H + Hkv:])
             ctx = attention(qkv, B, S, H, Hkv, D, causal=True)
             x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
             delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
@@ -150,9 +226,17 @@ class Generator:
     def copy_prefix(self, cache: KVCache, src: int, dst: int, n: int) -> None:
         """K/V of the first ``n`` positions of cache row ``src`` -> row ``dst`` (a prefix-cache hit on a row that is still
         in use). A method of the generator so that tensor-parallel followers repeat it on their slice of the cache."""
+        if cache.paged:
+            return            # paged cache: the scheduler lists the prefix's physical blocks in both table rows, nothing to copy
         for li in range(len(cache.k)):
             cache.k[li][dst, :, :n] = cache.k[li][src, :, :n]
             cache.v[li][dst, :, :n] = cache.v[li][src, :, :n]
+
+    @torch.no_grad()
+    def set_block_row(self, cache: KVCache, slot: int, blocks) -> None:
+        """Paged cache: logical -> physical block list of sequence ``slot``. A generator method so that tensor-parallel
+        followers apply the same table update to their slice of the cache."""
+        cache.set_row(slot, blocks)
 
     @torch.no_grad()
     def _prefill_chunk(self, ids: torch.Tensor, cache: KVCache, slot: int, pos0: int) -> torch.Tensor:
@@ -172,15 +256,16 @@ class Generator:
         H, Hkv, D = c.num_attention_heads, c.num_key_value_heads, c.head_dim
         cos, sin = m.rope(dev, self.max_len)
         pos = torch.arange(pos0, pos0 + T, device=dev, dtype=torch.int32)
+        srow = torch.full((T,), slot, device=dev, dtype=torch.long)
         from ..ops.attention import attention_with_past
         delta, res = ew.embedding(ids, m.embed_tokens), None
         for li, layer in enumerate(m.layers):
             x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
             qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
             t = qkv.view(T, H + 2 * Hkv, D)
-            cache.k[li][slot, :, pos0:pos0 + T] = t[:, H:H + Hkv].permute(1, 0, 2)
-            cache.v[li][slot, :, pos0:pos0 + T] = t[:, H + Hkv:].permute(1, 0, 2)
-            ctx = attention_with_past(qkv, cache.k[li][slot], cache.v[li][slot], pos0, H, Hkv, D)
+            cache.store(li, srow, pos.long(), t[:, H:H + Hkv], t[:, H + Hkv:])
+            kq, vq = cache.seq_view(li, slot, pos0 + T)
+            ctx = attention_with_past(qkv, kq, vq, pos0, H, Hkv, D)
             x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
             delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
         h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)
@@ -201,8 +286,7 @@ class Generator:
             x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
             qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
             t = qkv.view(-1, H + 2 * Hkv, D)
-            cache.k[li][row, :, pl] = t[:, H:H + Hkv]
-            cache.v[li][row, :, pl] = t[:, H + Hkv:]
+            cache.store(li, row, pl, t[:, H:H + Hkv], t[:, H + Hkv:])
             ctx = flash_attention_varlen(qkv, cu, max_seqlen, H, Hkv, D, D ** -0.5)
             x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
             delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
@@ -309,7 +393,7 @@ class Generator:
             x, res = rms_norm(delta, layers[0].input_layernorm, c.rms_norm_eps, None)
             for li, layer in enumerate(layers):
                 qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
-                ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5, slots)
+                ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5, slots, getattr(cache, "table", None))
                 x, res = fused_decode.gemv_fused(layer.o_proj, ctx, res, layer.post_attention_layernorm, c.rms_norm_eps, tail)
                 nw = layers[li + 1].input_layernorm if li + 1 < len(layers) else m.norm
                 x, res = fused_decode.gemv_fused(layer.down_proj, ew.swiglu(layer.gate_up_proj(x)), res, nw, c.rms_norm_eps, tail)
@@ -318,7 +402,7 @@ class Generator:
             for li, layer in enumerate(m.layers):
                 x, res = rms_norm(delta, layer.input_layernorm, c.rms_norm_eps, res)
                 qkv = ew.qknorm_rope(layer.qkv_proj(x), layer.q_norm, layer.k_norm, cos, sin, pos, H, Hkv, D, False, c.rms_norm_eps)
-                ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5, slots)
+                ctx = _decode_attn(qkv, cache.k[li], cache.v[li], pos, H, Hkv, D, D ** -0.5, slots, getattr(cache, "table", None))
                 x, res = rms_norm(layer.o_proj(ctx), layer.post_attention_layernorm, c.rms_norm_eps, res)
                 delta = layer.down_proj(ew.swiglu(layer.gate_up_proj(x)))
             h, _ = rms_norm(delta, m.norm, c.rms_norm_eps, res)

@@ -26,7 +26,7 @@ from typing import Deque, Dict, Iterator, List, Optional, Sequence
 
 import torch
 
-from ..inference.generate import GenerationConfig, Generator, KVCache, sample_next
+from ..inference.generate import GenerationConfig, Generator, KVCache, PagedKVCache, sample_next
 
 
 @dataclass
@@ -42,6 +42,11 @@ class EngineArgs:
     enable_chunked_prefill: bool = True  # prompts longer than max_prefill_tokens are prefilled in pieces between decode steps
     prefix_block: int = 16               # prefix matches are counted in blocks of this many tokens (vLLM's block_size)
     gpu_memory_utilization: float = 0.0  # > 0: derive max_num_seqs from the free HBM (rows of max_model_len tokens)
+    # paged KV cache (vLLM's PagedAttention): block_size > 0 (a power of two, e.g. 16) replaces the per-sequence rows of
+    # max_model_len tokens by a pool of num_kv_blocks blocks of block_size tokens, handed out as sequences grow and shared
+    # between sequences with a common prompt prefix. num_kv_blocks 0 = the capacity the slot pool would have had.
+    block_size: int = 0
+    num_kv_blocks: int = 0
 
 
 @dataclass
@@ -62,6 +67,7 @@ class Request:
     prefilled: int = 0                                       # prompt tokens whose K/V are already in the cache row
     cached_tokens: int = 0                                   # ... of which came from the prefix cache
     aborted: bool = False                                    # set by LLMEngine.abort(): dropped at the next scheduler iteration
+    reserved_blocks: int = 0                                 # paged cache: blocks promised to this request but not handed out yet
 
     @property
     def ttft(self) -> Optional[float]:
@@ -115,8 +121,24 @@ class LLMEngine:
             row = 2 * c.num_hidden_layers * c.num_key_value_heads * self.args.max_model_len * c.head_dim * self.model.embed_tokens.element_size()
             self.args.max_num_seqs = int(max(1, min(4096, budget // row - 1)))
         # one extra row: the scratch slot that padded rows of a bucketed (CUDA-graph) decode batch write into
-        self.cache = KVCache(c.num_hidden_layers, self.args.max_num_seqs + 1, c.num_key_value_heads, self.args.max_model_len,
-                             c.head_dim, self.model.embed_tokens.dtype, self.device)
+        self.paged = self.args.block_size > 0
+        if self.paged:
+            BS = self.args.block_size
+            per_seq = -(-self.args.max_model_len // BS)
+            nb = self.args.num_kv_blocks or (self.args.max_num_seqs * per_seq)
+            # physical block 0 is never handed out: table entries that were never set (the scratch row, positions a padded
+            # prefill piece writes past a sequence's end) point at it
+            self.cache = PagedKVCache(c.num_hidden_layers, nb + 1, c.num_key_value_heads, BS, c.head_dim,
+                                      self.model.embed_tokens.dtype, self.device, self.args.max_num_seqs + 1, self.args.max_model_len)
+            self._free_blocks: List[int] = list(range(nb, 0, -1))
+            self._block_ref: List[int] = [0] * (nb + 1)
+            self._slot_blocks: Dict[int, List[int]] = {}
+            self._reserved = 0
+            if self.args.prefix_block % BS:
+                self.args.prefix_block = -(-self.args.prefix_block // BS) * BS      # prefixes are shared in whole blocks
+        else:
+            self.cache = KVCache(c.num_hidden_layers, self.args.max_num_seqs + 1, c.num_key_value_heads, self.args.max_model_len,
+                                 c.head_dim, self.model.embed_tokens.dtype, self.device)
         self.free: List[int] = list(range(self.args.max_num_seqs))[::-1]
         self.waiting: Deque[Request] = deque()
         self.running: List[Request] = []
@@ -221,8 +243,92 @@ class LLMEngine:
         return len(self.running)
 
     def kv_cache_usage(self) -> float:
+        if self.paged:
+            total = len(self._block_ref) - 1
+            return (total - len(self._free_blocks)) / float(max(1, total))
         used = sum(len(r.prompt_ids) + len(r.output_ids) for r in self.running)
         return used / float(self.args.max_num_seqs * self.args.max_model_len)
+
+    # ------------------------------------------------------------------ paged KV cache: block allocator
+    def _nblocks(self, n_tokens: int) -> int:
+        """Blocks that hold ``n_tokens`` plus the <= 7 dummy positions a padded prefill piece may write past them."""
+        return -(-(min(n_tokens + 8, self.args.max_model_len)) // self.args.block_size)
+
+    def _blocks_free(self) -> int:
+        return len(self._free_blocks) - self._reserved
+
+    def _drop_blocks(self, slot: int) -> None:
+        for b in self._slot_blocks.pop(slot, []):
+            self._block_ref[b] -= 1
+            if self._block_ref[b] == 0:
+                self._free_blocks.append(b)
+
+    def _truncate_blocks(self, slot: int, n_blocks: int) -> None:
+        blocks = self._slot_blocks.get(slot, [])
+        for b in blocks[n_blocks:]:
+            self._block_ref[b] -= 1
+            if self._block_ref[b] == 0:
+                self._free_blocks.append(b)
+        del blocks[n_blocks:]
+
+    def _evict_cached_rows(self, need: int, keep: int = -1) -> None:
+        """Give finished sequences' rows back (least recently used first) until ``need`` blocks are free."""
+        for slot in list(self._cached):
+            if self._blocks_free() >= need:
+                return
+            if slot != keep:
+                del self._cached[slot]
+                self._unindex_row(slot)
+                self._drop_blocks(slot)
+                self.free.append(slot)
+
+    def _admit_blocks(self, r: Request, shared_from: int = -1, shared_tokens: int = 0) -> bool:
+        """Reserve every block ``r`` can need (prompt + max_new_tokens, less the prefix blocks it shares) so that decode
+        never runs out; returns False when the pool cannot promise that yet."""
+        total = self._nblocks(min(len(r.prompt_ids) + r.cfg.max_new_tokens, self.args.max_model_len))
+        have = len(self._slot_blocks.get(r.slot, [])) if r.slot >= 0 else 0
+        shared = shared_tokens // self.args.block_size if shared_from >= 0 else 0
+        need = max(0, total - max(have, shared))
+        if self._blocks_free() < need:
+            self._evict_cached_rows(need, keep=shared_from if shared_from >= 0 else r.slot)
+        if self._blocks_free() < need:
+            return False
+        r.reserved_blocks = need
+        self._reserved += need
+        return True
+
+    def _share_prefix(self, src: int, dst: int, n_tokens: int) -> None:
+        blocks = self._slot_blocks[src][:n_tokens // self.args.block_size]
+        self._drop_blocks(dst)
+        for b in blocks:
+            self._block_ref[b] += 1
+        self._slot_blocks[dst] = list(blocks)
+        self.gen.set_block_row(self.cache, dst, blocks)
+
+    def _grow(self, r: Request, n_tokens: int) -> None:
+        """Make sure ``r``'s row has blocks for ``n_tokens`` positions (taken out of its reservation)."""
+        blocks = self._slot_blocks.setdefault(r.slot, [])
+        want = self._nblocks(n_tokens)
+        if len(blocks) >= want:
+            return
+        first_new = len(blocks)
+        while len(blocks) < want:
+            if not self._free_blocks:
+                raise RuntimeError("KV block pool exhausted (reservation accounting is broken)")
+            b = self._free_blocks.pop()
+            self._block_ref[b] = 1
+            blocks.append(b)
+            if r.reserved_blocks > 0:
+                r.reserved_blocks -= 1
+                self._reserved -= 1
+        self.gen.set_block_row(self.cache, r.slot, blocks) if first_new == 0 else self._set_row_tail(r.slot, blocks, first_new)
+
+    def _set_row_tail(self, slot: int, blocks: List[int], first_new: int) -> None:
+        self.gen.set_block_row(self.cache, slot, blocks)          # rows are short (max_model_len / block_size ints)
+
+    def _unreserve(self, r: Request) -> None:
+        self._reserved -= r.reserved_blocks
+        r.reserved_blocks = 0
 
     # ------------------------------------------------------------------ prefix cache (enable_prefix_caching)
     def _block_hashes(self, toks: Sequence[int], upto: int):
@@ -268,6 +374,8 @@ class LLMEngine:
             if slot != keep:
                 del self._cached[slot]
                 self._unindex_row(slot)
+                if self.paged:
+                    self._drop_blocks(slot)
                 return slot
         return -1
 
@@ -279,6 +387,8 @@ class LLMEngine:
         slot, r.slot = r.slot, -1
         if slot < 0:
             return
+        if self.paged:
+            self._unreserve(r)
         valid = r.prompt_ids[:r.prefilled] if r.prefilled < len(r.prompt_ids) else r.prompt_ids + r.output_ids[:-1]
         if self.args.enable_prefix_caching and len(valid) >= self.args.prefix_block and r.finish_reason != "error":
             self._index_row(slot, list(valid))
@@ -286,6 +396,8 @@ class LLMEngine:
             self._cached.move_to_end(slot)
         else:
             self._unindex_row(slot)
+            if self.paged:
+                self._drop_blocks(slot)
             self.free.append(slot)
 
     # ------------------------------------------------------------------ scheduler
@@ -382,6 +494,8 @@ class LLMEngine:
             if r.prefilled + n < L:
                 n = max(8, n // 8 * 8)                       # pieces end on 8-token boundaries (aligned score rows)
         ids = torch.tensor(r.prompt_ids[r.prefilled:r.prefilled + n], device=self.device)
+        if self.paged:
+            self._grow(r, r.prefilled + n)
         logits = self.gen._prefill_chunk(ids, self.cache, r.slot, r.prefilled)
         r.prefilled += n
         with self.metrics.lock:
@@ -421,6 +535,14 @@ class LLMEngine:
                 self.metrics.prefix_hits += P
             if not piecewise:
                 r.slot = self._take_slot()
+                if self.paged:
+                    if not self._admit_blocks(r):
+                        self.free.append(r.slot)
+                        r.slot = -1
+                        with self._cv:
+                            self.waiting.appendleft(r)        # the pool cannot promise its blocks yet: retry next iteration
+                        break
+                    self._grow(r, L)
                 r.prefilled = L
                 budget -= L
                 batch.append(r)
@@ -430,9 +552,29 @@ class LLMEngine:
                 del self._cached[src]
                 self._unindex_row(src)
                 r.slot = src
+                if self.paged:
+                    # positions >= P of the row are rewritten: blocks past the prefix go back to the pool (some may be listed
+                    # by other sequences that share a longer prefix of the old row - those keep them)
+                    self._truncate_blocks(src, P // self.args.block_size)
+                    if not self._admit_blocks(r):
+                        self._drop_blocks(src)
+                        self.free.append(src)
+                        r.slot = -1
+                        with self._cv:
+                            self.waiting.appendleft(r)
+                        break
             else:
                 r.slot = self._take_slot(keep=src)
-                if P > 0:
+                if self.paged:
+                    if not self._admit_blocks(r, src if P > 0 else -1, P):
+                        self.free.append(r.slot)
+                        r.slot = -1
+                        with self._cv:
+                            self.waiting.appendleft(r)
+                        break
+                    if P > 0:
+                        self._share_prefix(src, r.slot, P)               # both table rows list the prefix's physical blocks
+                elif P > 0:
                     self.gen.copy_prefix(self.cache, src, r.slot, P)     # the prefix belongs to a running sequence: copy its K/V
             r.prefilled = r.cached_tokens = P
             self.prefilling.append(r)
@@ -462,6 +604,9 @@ class LLMEngine:
             return
         reqs = self.running
         n = len(reqs)
+        if self.paged:
+            for r in reqs:
+                self._grow(r, len(r.prompt_ids) + len(r.output_ids))
         nb = n
         if self.device.type == "cuda":          # pad to a power-of-two bucket: one captured graph per bucket, not per batch size
             nb = 1

@@ -20,7 +20,7 @@ import torch.distributed as dist
 
 from .engine import EngineArgs, LLMEngine
 
-_CALLS = ("_prefill_packed", "_prefill", "_prefill_chunk", "decode_graphed", "copy_prefix")
+_CALLS = ("_prefill_packed", "_prefill", "_prefill_chunk", "decode_graphed", "copy_prefix", "set_block_row")
 
 
 def _to_wire(x: Any) -> Any:

@@ -483,13 +483,14 @@ def test_small_m_gemv_kernels(M, dtype):
 
 
 @pytest.mark.parametrize("kind", ["dense", "nf4", "int4"])
-@pytest.mark.parametrize("M", [1, 8, 33])
-def test_gemv_fused_tail_matches_separate_ops(kind, M):
-    """b200_gemv_fused at TP 1: projection + residual add + RMSNorm in one launch vs the fp32 torch expression."""
+@pytest.mark.parametrize("M,K", [(1, 1024), (8, 1024), (33, 1024), (2, 128), (2, 256), (8, 384)])
+def test_gemv_fused_tail_matches_separate_ops(kind, M, K):
+    """b200_gemv_fused at TP 1: projection + residual add + RMSNorm in one launch vs the fp32 torch expression. The short
+    contractions are what a row-parallel layer is left with at TP 8 on small models (K = 128: one quantisation group)."""
     from llm_in_practise_b200.ops import fused_decode as FD
     from llm_in_practise_b200.ops.linear import FusedLinear
     torch.manual_seed(5)
-    K, N = 1024, 2048
+    N = 2048
     lin = FusedLinear(K, [("o_proj", N)], dtype=torch.bfloat16, device=DEV, init_std=0.05)
     wref = lin.weight.data.float().clone()
     if kind == "nf4":
