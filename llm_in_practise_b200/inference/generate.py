@@ -369,7 +369,17 @@ class Generator:
             if tp is not None and tp.world > 1 and not getattr(tp, "fused", False):
                 self._fused_ok = False
                 return None
-            self._tail = fused_decode.FusedTail(hid, x.device, tp if (tp is not None and tp.world > 1) else None, x.dtype)
+            if tp is not None and tp.world > 1:
+                # ONE tail per tensor-parallel group and width: its epoch lives on the device and the flags it is compared
+                # with live in the group's symmetric memory — a second tail on the same flag channel would start again at
+                # epoch 1, find the previous tail's (larger) epochs in the flags and stop waiting for its peers
+                tails = tp.__dict__.setdefault("_fused_tails", {})
+                key = (hid, x.dtype)
+                if key not in tails:
+                    tails[key] = fused_decode.FusedTail(hid, x.device, tp, x.dtype)
+                self._tail = tails[key]
+            else:
+                self._tail = fused_decode.FusedTail(hid, x.device, None, x.dtype)
         return self._tail
 
     @torch.no_grad()

@@ -40,13 +40,20 @@ torch.manual_seed(3)
 ref = Qwen3ForCausalLM(small, dtype=torch.bfloat16, device=dev, init_std=0.05)
 quantize_all(ref)
 ids = torch.randint(0, 1024, (2, 40), device=dev, generator=torch.Generator(device=dev).manual_seed(5))
+_forced = []   # the unsharded run's greedy tokens, replayed in the sharded run: a near-tie in the argmax would otherwise
+               # send the two runs down different continuations and compare unrelated logits
+
+
 def decode_logits(model):
     """prefill 40 tokens, then 3 decode steps through the (fused-tail) decode path: logits of the last step"""
     g = Generator(model, max_len=64)
     cache = KVCache(small.num_hidden_layers, 2, model.config.num_key_value_heads, 64, small.head_dim, torch.bfloat16, dev)
     lg = g._prefill(ids, cache)
-    for _ in range(3):
-        lg = g._decode(lg.argmax(-1).reshape(-1), cache)
+    record = not _forced
+    for i in range(3):
+        if record:
+            _forced.append(lg.argmax(-1).reshape(-1).clone())
+        lg = g._decode(_forced[i], cache)
     return lg.float()
 
 

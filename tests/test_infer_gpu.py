@@ -124,3 +124,63 @@ def test_packed_prefill_matches_per_prompt_prefill_gpu():
     e2 = g._prefill_packed(other, cb, [0, 1])
     assert (g2 - e2).abs().max() < 0.02 * e2.abs().max()
     assert torch.equal(cc.k[1][1, :, :200], cb.k[1][1, :, :200])
+
+
+@pytest.mark.parametrize("D,dtype,G", [(128, torch.bfloat16, 4), (64, torch.float16, 2), (32, torch.float32, 4)])
+def test_paged_decode_attention_matches_slot_pool(D, dtype, G):
+    """b200_decode_attn{,_split}_paged: the same K/V scattered over a shuffled pool of 16-token blocks (block table per
+    sequence) gives the same output as the contiguous [slot, head, position] cache, and the new token's K/V lands in the
+    right physical block; sequences of different lengths, slots out of order."""
+    from llm_in_practise_b200.inference.generate import _decode_attn
+    torch.manual_seed(1)
+    B, Hkv, L, BS = 3, 2, 96, 16
+    H = Hkv * G
+    qkv = torch.randn(B, (H + 2 * Hkv) * D, device="cuda", dtype=dtype)
+    ck = torch.randn(4, Hkv, L, D, device="cuda", dtype=dtype)
+    cv = torch.randn(4, Hkv, L, D, device="cuda", dtype=dtype)
+    slots = torch.tensor([2, 0, 3], device="cuda", dtype=torch.int32)
+    pos = torch.tensor([70, 5, 47], device="cuda", dtype=torch.int32)
+    nbs = L // BS
+    perm = torch.randperm(4 * nbs, device="cuda") + 1                            # physical block 0 stays unused
+    table = perm.view(4, nbs).to(torch.int32).contiguous()
+    pk = torch.zeros(4 * nbs + 1, Hkv, BS, D, device="cuda", dtype=dtype)
+    pv = torch.zeros_like(pk)
+    for s in range(4):
+        for j in range(nbs):
+            pk[table[s, j]] = ck[s, :, j * BS:(j + 1) * BS]
+            pv[table[s, j]] = cv[s, :, j * BS:(j + 1) * BS]
+    want = _decode_attn(qkv, ck, cv, pos, H, Hkv, D, D ** -0.5, slots)
+    got = _decode_attn(qkv, pk, pv, pos, H, Hkv, D, D ** -0.5, slots, table)
+    torch.testing.assert_close(got.float(), want.float(), rtol=1e-3, atol=1e-3)
+    for b in range(B):
+        s, t = int(slots[b]), int(pos[b])
+        blk = int(table[s, t // BS])
+        assert torch.equal(pk[blk, :, t % BS], ck[s, :, t]) and torch.equal(pv[blk, :, t % BS], cv[s, :, t])
+
+
+def test_paged_engine_matches_slot_pool_engine_gpu():
+    """LLMEngine with block_size 16 (paged cache, CUDA-graph decode buckets, packed prefill, shared prefix blocks) emits
+    the same greedy tokens as the slot-pool engine."""
+    from llm_in_practise_b200.inference import GenerationConfig
+    from llm_in_practise_b200.serve import EngineArgs, LLMEngine
+    model = _tiny()
+    torch.manual_seed(2)
+    system = torch.randint(0, 512, (48,)).tolist()
+    prompts = [system + torch.randint(0, 512, (n,)).tolist() for n in (9, 21, 4)] + [torch.randint(0, 512, (70,)).tolist()]
+    outs = []
+    for bs in (0, 16):
+        eng = LLMEngine(model, None, EngineArgs(max_num_seqs=4, max_model_len=256, max_prefill_tokens=64, warmup=False,
+                                                block_size=bs))
+        reqs = [eng.submit(p, GenerationConfig(max_new_tokens=12, do_sample=False)) for p in prompts[:2]]
+        for _ in range(3):
+            eng.step()
+        reqs += [eng.submit(p, GenerationConfig(max_new_tokens=12, do_sample=False)) for p in prompts[2:]]
+        n = 0
+        while not all(r.done.is_set() for r in reqs):
+            eng.step()
+            n += 1
+            assert n < 500
+        outs.append([r.output_ids for r in reqs])
+        if bs:
+            assert eng._reserved == 0 and sum(r.cached_tokens for r in reqs) >= 48
+    assert outs[0] == outs[1]

@@ -261,3 +261,74 @@ def test_stop_strings_and_abort(model):
     while not w.done.is_set():
         eng2.step()
     assert len(w.output_ids) == 2
+
+
+def _drain(eng, reqs):
+    n = 0
+    while not all(r.done.is_set() for r in reqs):
+        eng.step()
+        n += 1
+        assert n < 2000
+    return n
+
+
+def test_paged_kv_cache_matches_slot_pool(model):
+    """block_size > 0: the KV cache is a pool of 16-token blocks with a block table (vLLM's PagedAttention layout). Same
+    tokens as one-by-one generation through chunked prefill, a prefix shared with a RUNNING sequence (both table rows list
+    the same physical blocks — nothing is copied), a prefix continued in a finished sequence's row, and queueing when the
+    pool cannot promise a request its blocks; every block returns to the pool."""
+    torch.manual_seed(3)
+    system = torch.randint(0, 300, (40,)).tolist()
+    prompts = [system + torch.randint(0, 300, (n,)).tolist() for n in (7, 11, 3)] + [torch.randint(0, 300, (50,)).tolist()]
+    g = Generator(model, max_len=96)
+    want = [g.generate(torch.tensor([p]), max_new_tokens=5, do_sample=False)[0, len(p):].tolist() for p in prompts]
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=3, max_model_len=96, max_prefill_per_step=4, max_prefill_tokens=24,
+                                            prefix_block=16, block_size=16))
+    assert eng.paged and eng.cache.k[0].shape == (3 * 6 + 1, 2, 16, 16)
+    total = len(eng._block_ref) - 1
+    r0 = eng.submit(prompts[0], GenerationConfig(max_new_tokens=5, do_sample=False))
+    eng.step()
+    assert r0 in eng.prefilling and 0 < r0.prefilled < len(prompts[0])
+    eng.step()
+    r1 = eng.submit(prompts[1], GenerationConfig(max_new_tokens=5, do_sample=False))   # r0 still running: shared blocks
+    eng.step()
+    assert r1.cached_tokens == 32 and r1.slot != r0.slot
+    assert eng._slot_blocks[r1.slot][:2] == eng._slot_blocks[r0.slot][:2]
+    assert all(eng._block_ref[b] == 2 for b in eng._slot_blocks[r0.slot][:2])
+    _drain(eng, [r0, r1])
+    r2 = eng.submit(prompts[2], GenerationConfig(max_new_tokens=5, do_sample=False))
+    r3 = eng.submit(prompts[3], GenerationConfig(max_new_tokens=5, do_sample=False))
+    _drain(eng, [r2, r3])
+    assert r2.cached_tokens == 32 and r3.cached_tokens == 0
+    assert [r.output_ids for r in (r0, r1, r2, r3)] == want
+    # accounting: nothing reserved, every block is free or held by a cached row, reference counts match the table rows
+    assert eng._reserved == 0
+    held = {}
+    for slot, blocks in eng._slot_blocks.items():
+        for b in blocks:
+            held[b] = held.get(b, 0) + 1
+    assert all(eng._block_ref[b] == n for b, n in held.items())
+    assert len(eng._free_blocks) + len(held) == total and 0 not in held
+
+
+def test_paged_kv_cache_small_pool_queues_and_recovers(model):
+    """A pool smaller than max_num_seqs x max_model_len: admissions wait until finished sequences give their blocks back
+    (cached prefix rows are evicted first); outputs still equal sequential generation."""
+    torch.manual_seed(5)
+    prompts = [torch.randint(0, 300, (n,)).tolist() for n in (20, 33, 18, 40, 25, 9)]
+    g = Generator(model, max_len=96)
+    want = [g.generate(torch.tensor([p]), max_new_tokens=8, do_sample=False)[0, len(p):].tolist() for p in prompts]
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=4, max_model_len=96, max_prefill_per_step=4, max_prefill_tokens=64,
+                                            block_size=16, num_kv_blocks=9))        # 144 tokens of KV for 4 rows x 96
+    reqs = [eng.submit(p, GenerationConfig(max_new_tokens=8, do_sample=False)) for p in prompts]
+    peak = 0
+    n = 0
+    while not all(r.done.is_set() for r in reqs):
+        eng.step()
+        peak = max(peak, eng.num_running + len(eng.prefilling))
+        assert len(eng._free_blocks) - eng._reserved >= 0
+        n += 1
+        assert n < 2000
+    assert [r.output_ids for r in reqs] == want
+    assert peak < 4                                                     # the block pool, not the row count, was the limit
+    assert 0.0 <= eng.kv_cache_usage() <= 1.0
