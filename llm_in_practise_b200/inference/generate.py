@@ -376,6 +376,9 @@ class Generator:
                 tails = tp.__dict__.setdefault("_fused_tails", {})
                 key = (hid, x.dtype)
                 if key not in tails:
+                    if tails:                     # the flag channel is taken by a tail of another width / dtype
+                        self._fused_ok = False
+                        return None
                     tails[key] = fused_decode.FusedTail(hid, x.device, tp, x.dtype)
                 self._tail = tails[key]
             else:
