@@ -1,7 +1,10 @@
 """Llama-Guard moderation service: OpenAI ``/v1/moderations`` on top of a completions endpoint.
 
 Behavioural match for the reference wrapper (Deployment/litellm-proxy/llama-guard-wrapper/app.py:22-72,
-model_client.py:35-128, openai_moderation_map.py:5-64, schemas.py:4-5):
+model_client.py:35-128, openai_moderation_map.py:5-64, schemas.py:4-5). The Llama-Guard system prompt, the category list
+and the S1-S14 -> OpenAI category table below are TAKEN VERBATIM from the reference (a guard prompt has to match the
+format the model was trained on, and the mapping is a constant table); the function names and signatures follow the
+reference's so that its callers port one to one. The engine-backed backend (`engine_backend`) is this repository's own.
 
 * ``POST /v1/moderations`` and ``/moderations`` with ``{"input": text}`` (400 on empty input), ``GET /healthz``,
   ``POST /v1/generate`` -> 501, optional ``X-API-KEY`` check (401) when ``WRAPPER_API_KEY`` is set;
