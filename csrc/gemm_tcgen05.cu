@@ -916,7 +916,7 @@ struct GemmConfig {
 
 static GemmConfig pick_config(int M, int N, int batch, int nkt, int b_mn, int EPR, int num_sms, bool allow_sk) {
   GemmConfig best = {1, 256, 0, 1e30};
-  const char* no_sk = getenv("B200_GEMM_NO_STREAMK");
+  static const bool no_sk = getenv("B200_GEMM_NO_STREAMK") != nullptr;     // tuning switches are read once per process
   for (int ctas = 2; ctas >= 1; --ctas) {
     if (g_force_ctas && ctas != g_force_ctas) continue;
     if (ctas == 2 && (M <= kBM || num_sms < 2)) continue;
@@ -1041,9 +1041,10 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   p.sk_group = 1;
   p.sk_ws = nullptr; p.sk_flags = nullptr; p.sk_epoch = 0; p.sk_state = nullptr;
   if (cfg.stream_k) {
+    static const bool sk_flat = getenv("B200_GEMM_SK_FLAT") != nullptr;
     // lock-step groups when the M-tiles of a panel fit a group and at most ~5 % of the units are left without one
     const int units_sk = g_num_sms / ctas;
-    if (p.num_m > 1 && p.num_m <= units_sk && (units_sk % p.num_m) * 20 <= units_sk && !getenv("B200_GEMM_SK_FLAT"))
+    if (p.num_m > 1 && p.num_m <= units_sk && (units_sk % p.num_m) * 20 <= units_sk && !sk_flat)
       p.sk_group = p.num_m;
     static unsigned int epoch = 0;
     p.sk_ws = reinterpret_cast<float*>(a->workspace);
@@ -1057,7 +1058,8 @@ B200_API int b200_gemm(const b200_gemm_args* a, void* stream_) {
   // 6 stages sustain the pipe (5..7 measure the same); the 32 KB left free let bandwidth-bound kernels of other streams
   // (the next weight's dequant, the ZeRO-3 shard pull) co-reside with the persistent GEMM CTAs
   if (stages > 6) stages = 6;
-  { const char* e = getenv("B200_GEMM_STAGES"); if (e && atoi(e) >= 2 && atoi(e) < stages) stages = atoi(e); }
+  static const int env_stages = [] { const char* e = getenv("B200_GEMM_STAGES"); return e ? atoi(e) : 0; }();
+  if (env_stages >= 2 && env_stages < stages) stages = env_stages;
   if (stages < 2) return B200_ERR_UNSUPPORTED;
   p.stages = stages;
   const int umma_m = kBM * ctas;
@@ -1180,7 +1182,8 @@ B200_API int b200_gemm_w4(const b200_gemm_args* a, const b200_w4_desc* w, void* 
   const int units = g_num_sms / ctas;
   const long long tiles = (long long)p.num_m * p.num_n;
   const long long sk_need = (long long)g_num_sms * kBM * kAccStride * 4 + (long long)g_num_sms * 4;
-  const bool allow_sk = a->workspace != nullptr && a->workspace_bytes >= sk_need && !getenv("B200_GEMM_NO_STREAMK");
+  static const bool no_sk_w4 = getenv("B200_GEMM_NO_STREAMK") != nullptr;
+  const bool allow_sk = a->workspace != nullptr && a->workspace_bytes >= sk_need && !no_sk_w4;
   const long long waves = (tiles + units - 1) / units;
   const double classic = (double)waves * nkt, sk = (double)tiles * nkt / units + 10.0;
   p.stream_k = (allow_sk && tiles % units != 0 && tiles * nkt >= 4ll * units && waves <= 4 && sk < classic * 0.85) ? 1 : 0;
@@ -1196,8 +1199,10 @@ B200_API int b200_gemm_w4(const b200_gemm_args* a, const b200_w4_desc* w, void* 
   }
   const int stage_bytes = kStageABytes + bn_cta * 128;
   int raw_stages = 8, lut_bytes = kLutBytes;
-  { const char* e = getenv("B200_W4_RAW"); if (e) raw_stages = atoi(e); }
-  { const char* e = getenv("B200_W4_NOLUT"); if (e) lut_bytes = 0; }
+  static const int env_raw = [] { const char* e = getenv("B200_W4_RAW"); return e ? atoi(e) : -1; }();
+  static const bool env_nolut = getenv("B200_W4_NOLUT") != nullptr;
+  if (env_raw >= 0) raw_stages = env_raw;
+  if (env_nolut) lut_bytes = 0;
   int stages = (g_max_smem - 1024 - lut_bytes - raw_stages * kRawStageBytes - 8 * (2 * 8 + 5 + 2 * raw_stages)) / stage_bytes;
   if (stages > 8) stages = 8;
   if (stages < 3) return B200_ERR_UNSUPPORTED;
