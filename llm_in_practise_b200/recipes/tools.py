@@ -73,6 +73,10 @@ def main(argv=None):
     l.add_argument("rest", nargs=argparse.REMAINDER)
     mod = sub.add_parser("moderation")
     mod.add_argument("--port", type=int, default=int(os.getenv("WRAPPER_PORT", "8099")))
+    ro = sub.add_parser("router", help="LiteLLM-style model router / load balancer (serve/router.py)")
+    ro.add_argument("--config", required=True, help="YAML in the reference's litellm-config-router-lb.yaml shape")
+    ro.add_argument("--port", type=int, default=4000)
+    ro.add_argument("--master-key", default=os.getenv("LITELLM_MASTER_KEY"))
     a = ap.parse_args(argv)
 
     if a.cmd == "env":
@@ -91,6 +95,14 @@ def main(argv=None):
         import uvicorn
         from ..serve.moderation import build_moderation_app
         return uvicorn.run(build_moderation_app(), host="0.0.0.0", port=a.port, log_level="info")
+    if a.cmd == "router":
+        import uvicorn
+        import yaml
+        from ..serve.router import Router, build_router_app
+        with open(a.config, encoding="utf-8") as f:
+            cfg = yaml.safe_load(f)
+        interval = float((cfg.get("router_settings") or {}).get("health_check_interval", 0))
+        return uvicorn.run(build_router_app(Router.from_config(cfg), interval, a.master_key), host="0.0.0.0", port=a.port, log_level="info")
     if a.cmd == "convert-self-cognition":
         from ..data.chat import convert_self_cognition_to_alpaca, load_self_cognition
         rows = load_self_cognition(a.input, "{{NAME}}", "{{AUTHOR}}")

@@ -1,2 +1,2 @@
-"""Serving: continuous-batching engine, OpenAI-compatible server, moderation wrapper, load generator."""
+"""Serving: continuous-batching engine, OpenAI-compatible server, model router, cache gateway, moderation wrapper, load generator."""
 from .engine import EngineArgs, LLMEngine, Request
