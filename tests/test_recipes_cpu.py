@@ -83,3 +83,55 @@ def test_finetune_from_llamafactory_yaml(tmp_path):
     assert os.path.exists(d + "/out/adapter_model.safetensors")
     cfg = json.load(open(d + "/out/adapter_config.json"))
     assert cfg["r"] == 4 and cfg["lora_alpha"] == 8 and sorted(cfg["target_modules"]) == ["q_proj", "v_proj"]
+
+
+def test_webui_path_with_a_stand_in_gradio(tmp_path, monkeypatch):
+    """`recipes.infer webui` (Scripts/inference/05/06-…webui-infr.py: Blocks + Chatbot + Textbox + three sliders + clear
+    button on 0.0.0.0:7860). gradio is not in this image, so a minimal stand-in module records what the recipe builds and
+    drives the registered streaming callback once."""
+    import sys
+    import types
+    from llm_in_practise_b200.io.hf import from_pretrained, save_pretrained
+    from llm_in_practise_b200.recipes import infer
+    d = str(tmp_path)
+    save_pretrained(from_pretrained("qwen3-tiny", dtype=torch.float32, device="cpu"), d + "/base")
+    rec = {"components": [], "launch": None, "submit": None, "clear": None}
+
+    class _Comp:
+        def __init__(self, kind, *a, **k):
+            self.kind, self.args, self.kw = kind, a, k
+            rec["components"].append(self)
+
+        def submit(self, fn, inputs, outputs):
+            rec["submit"] = (fn, inputs, outputs)
+
+        def click(self, fn, inputs, outputs):
+            rec["clear"] = (fn, inputs, outputs)
+
+    class _Blocks:
+        def __init__(self, **k):
+            self.kw = k
+
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *a):
+            return False
+
+        def launch(self, **k):
+            rec["launch"] = k
+
+    gr = types.ModuleType("gradio")
+    gr.Blocks = _Blocks
+    for kind in ("Chatbot", "Textbox", "Slider", "Button"):
+        setattr(gr, kind, (lambda kind: (lambda *a, **k: _Comp(kind, *a, **k)))(kind))
+    monkeypatch.setitem(sys.modules, "gradio", gr)
+    infer.main(["webui", "--model", d + "/base", "--max_new_tokens", "16"])
+    assert rec["launch"] == {"server_name": "0.0.0.0", "server_port": 7860}
+    kinds = [c.kind for c in rec["components"]]
+    assert kinds.count("Slider") == 3 and "Chatbot" in kinds and "Textbox" in kinds and "Button" in kinds
+    respond, inputs, outputs = rec["submit"]
+    assert len(inputs) == 5 and outputs.kind == "Chatbot"
+    frames = list(respond("hello", [("hi", "there")], 0.7, 0.9, 4))
+    assert frames and frames[-1][0] == ("hi", "there") and frames[-1][-1][0] == "hello" and isinstance(frames[-1][-1][1], str)
+    assert rec["clear"][0]() == []
