@@ -50,14 +50,15 @@ def test_tp2_matches_single(quant, tmp_path):
     assert got["calls"] > 0
 
 
-def _serve_worker(rank, world, tmp):
+def _serve_worker(rank, world, tmp, block_size=0):
     """Tensor-parallel serving: rank 0 schedules (continuous batching, chunked prefill, prefix cache), rank 1 follows."""
     from llm_in_practise_b200.inference import GenerationConfig
     from llm_in_practise_b200.parallel.dist import setup_distributed
     from llm_in_practise_b200.serve import EngineArgs
     from llm_in_practise_b200.serve.tp_engine import build_tp_engine
     setup_distributed()
-    eng = build_tp_engine(_model("w4"), None, EngineArgs(max_num_seqs=3, max_model_len=96, max_prefill_tokens=24, warmup=False))
+    eng = build_tp_engine(_model("w4"), None, EngineArgs(max_num_seqs=3, max_model_len=96, max_prefill_tokens=24, warmup=False,
+                                                          block_size=block_size))
     if rank != 0:
         eng.serve_forever()
         return
@@ -69,9 +70,12 @@ def _serve_worker(rank, world, tmp):
     eng.shutdown()
 
 
-def test_tp2_serving_engine_matches_single_process(tmp_path):
+@pytest.mark.parametrize("block_size", [0, 16])
+def test_tp2_serving_engine_matches_single_process(tmp_path, block_size):
+    """block_size 16: the paged KV cache under tensor parallelism — rank 0's block-table updates are announced and applied
+    to the follower's slice of the cache."""
     from llm_in_practise_b200.inference import Generator
-    run_distributed(_serve_worker, 2, (str(tmp_path),))
+    run_distributed(_serve_worker, 2, (str(tmp_path), block_size))
     got = torch.load(tmp_path / "serve.pt")
     g = Generator(_model("w4"), max_len=96)
     want = [g.generate(torch.tensor([p]), max_new_tokens=4, do_sample=False)[0, len(p):].tolist() for p in got["prompts"]]
