@@ -217,7 +217,9 @@ def main():
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     sync_all()
     ev0.record()
+    t_host0 = time.perf_counter()
     run_steps(args.steps, e2e=False)
+    host_enqueue_ms = (time.perf_counter() - t_host0) * 1e3 / args.steps   # how long Python needs to ISSUE a step's launches
     ev1.record()
     sync_all()
     ms = ev0.elapsed_time(ev1)
@@ -273,6 +275,9 @@ def main():
                        "tokens_per_step": tokens_per_step},
             "clocks": clocks,
             "gpu_launches": launches,
+            # wall time the host needs to issue one step's launches (no synchronisation inside): close to ms_per_step means
+            # the step is bound by the Python / ctypes launch path rather than by the GPU
+            "host_enqueue_ms_per_step": round(host_enqueue_ms, 3),
             "model_tflops_per_gpu": round(flops_per_token(cfg, S) * tokens_per_step / world / (ms_per_step / 1e3) / 1e12, 1),
             "build_s": round(build_s, 1),
         }
