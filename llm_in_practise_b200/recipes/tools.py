@@ -73,6 +73,8 @@ def main(argv=None):
     l.add_argument("rest", nargs=argparse.REMAINDER)
     mod = sub.add_parser("moderation")
     mod.add_argument("--port", type=int, default=int(os.getenv("WRAPPER_PORT", "8099")))
+    hc = sub.add_parser("healthcheck", help="node / cluster health check (single process, or every rank of a torchrun job)")
+    hc.add_argument("--object-mib", type=int, default=16)
     ro = sub.add_parser("router", help="LiteLLM-style model router / load balancer (serve/router.py)")
     ro.add_argument("--config", required=True, help="YAML in the reference's litellm-config-router-lb.yaml shape")
     ro.add_argument("--port", type=int, default=4000)
@@ -95,6 +97,15 @@ def main(argv=None):
         import uvicorn
         from ..serve.moderation import build_moderation_app
         return uvicorn.run(build_moderation_app(), host="0.0.0.0", port=a.port, log_level="info")
+    if a.cmd == "healthcheck":
+        from ..serve.deploy import cluster_healthcheck, cluster_healthcheck_distributed
+        if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+            rep = cluster_healthcheck_distributed(a.object_mib)
+        else:
+            rep = cluster_healthcheck(object_mib=a.object_mib)
+        if rep is not None:
+            print(json.dumps(rep, indent=1, default=str))
+        return rep
     if a.cmd == "router":
         import uvicorn
         import yaml

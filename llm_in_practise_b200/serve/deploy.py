@@ -180,3 +180,59 @@ def cluster_healthcheck(cpu_tasks: int = 8, object_mib: int = 16) -> Dict[str, A
     rep["gpus"] = gpus
     rep["healthy"] = rep["cpu_probe"] == cpu_tasks and all(g["roundtrip_ok"] for g in gpus)
     return rep
+
+
+def cluster_healthcheck_distributed(object_mib: int = 16) -> Optional[Dict[str, Any]]:
+    """The reference's Ray cluster check (Deployment/Ray/scripts/ray_cluster_healthcheck.py: driver reaches the cluster,
+    worker processes start on every node, CPU tasks are scheduled, GPUs are visible and usable, the object store moves
+    data between nodes) for a ``torchrun`` job: every rank is a worker process. Each rank reports host / pid / its GPU,
+    runs a CPU probe and a small GPU kernel, then the data path is exercised the way the reference does it — an
+    ``object_mib`` MiB object made on rank 0 is sent to every rank (broadcast), checksummed there, and the checksums
+    travel back (all-gather). Rank 0 returns the aggregated report (other ranks return None). Launch under
+    ``torchrun --nnodes N --nproc-per-node G -m llm_in_practise_b200.recipes.tools healthcheck``."""
+    import socket
+    import torch.distributed as dist
+    from ..parallel.dist import get_info, setup_distributed
+    if not (dist.is_available() and dist.is_initialized()):
+        setup_distributed()
+    info = get_info()
+    rank, world, dev = info.rank, info.world_size, info.device
+    me: Dict[str, Any] = {"rank": rank, "hostname": socket.gethostname(), "pid": os.getpid(), "device": str(dev)}
+    t0 = time.perf_counter()
+    me["cpu_probe_ok"] = sum(j * j for j in range(200000)) > 0
+    me["cpu_probe_s"] = time.perf_counter() - t0
+    if dev.type == "cuda":
+        p = torch.cuda.get_device_properties(dev)
+        free, total = torch.cuda.mem_get_info(dev)
+        x = torch.ones(1 << 20, device=dev)
+        me.update(gpu_name=p.name, gpu_sm=f"{p.major}.{p.minor}", gpu_memory_free_gib=free / 2 ** 30, gpu_memory_total_gib=total / 2 ** 30,
+                  gpu_kernel_ok=bool(float((x * 2).sum()) == float(2 << 20)))
+    # object path: rank 0 -> everyone, checksums back
+    n = object_mib << 20
+    obj = torch.arange(n, dtype=torch.int64, device=dev).to(torch.uint8) if rank == 0 else torch.empty(n, dtype=torch.uint8, device=dev)
+    if dev.type == "cuda":
+        torch.cuda.synchronize(dev)
+    dist.barrier()
+    t0 = time.perf_counter()
+    dist.broadcast(obj, src=0)
+    if dev.type == "cuda":
+        torch.cuda.synchronize(dev)
+    me["object_recv_s"] = time.perf_counter() - t0
+    me["object_checksum"] = int(obj.to(torch.int64).sum())
+    reports: list = [None] * world
+    dist.all_gather_object(reports, me)
+    if rank != 0:
+        return None
+    hosts: Dict[str, list] = {}
+    for r in reports:
+        hosts.setdefault(r["hostname"], []).append(r["rank"])
+    want = reports[0]["object_checksum"]
+    rep = {"world_size": world, "nodes": len(hosts), "ranks_per_host": hosts, "workers": reports,
+           "distinct_pids": len({(r["hostname"], r["pid"]) for r in reports}) == world,
+           "cpu_ok": all(r["cpu_probe_ok"] for r in reports),
+           "gpu_ok": all(r.get("gpu_kernel_ok", True) for r in reports),
+           "gpus_visible": sum(1 for r in reports if "gpu_name" in r),
+           "object_path_ok": all(r["object_checksum"] == want for r in reports),
+           "object_gbs_slowest": (n / max(r["object_recv_s"] for r in reports) / 1e9) if world > 1 else None}
+    rep["healthy"] = rep["distinct_pids"] and rep["cpu_ok"] and rep["gpu_ok"] and rep["object_path_ok"]
+    return rep

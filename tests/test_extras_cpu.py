@@ -92,3 +92,26 @@ def test_deploy_layer(tmp_path):
         e2.shutdown()
     h = cluster_healthcheck(4, 1)
     assert h["healthy"] and h["cpu_probe"] == 4
+
+
+def _hc_worker(rank, world, tmp):
+    import json
+    from llm_in_practise_b200.parallel.dist import setup_distributed
+    from llm_in_practise_b200.serve.deploy import cluster_healthcheck_distributed
+    setup_distributed()
+    rep = cluster_healthcheck_distributed(object_mib=1)
+    assert (rep is None) == (rank != 0)
+    if rank == 0:
+        json.dump(rep, open(f"{tmp}/hc.json", "w"), default=str)
+
+
+def test_distributed_cluster_healthcheck(tmp_path):
+    """The torchrun counterpart of the reference's Ray cluster health check: every rank is a worker process; rank 0 gets the
+    aggregated report (nodes, workers, CPU / GPU probes, the rank-0 -> everyone object path verified by checksum)."""
+    import json
+    from dist_utils import run_distributed
+    run_distributed(_hc_worker, 2, (str(tmp_path),))
+    rep = json.load(open(tmp_path / "hc.json"))
+    assert rep["healthy"] and rep["world_size"] == 2 and rep["nodes"] == 1 and rep["distinct_pids"]
+    assert rep["object_path_ok"] and len(rep["workers"]) == 2 and rep["workers"][1]["rank"] == 1
+    assert rep["object_gbs_slowest"] > 0
