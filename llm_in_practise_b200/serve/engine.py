@@ -199,6 +199,15 @@ class LLMEngine:
             raise ValueError("empty prompt")
         if len(ids) >= self.args.max_model_len:
             raise ValueError(f"prompt of {len(ids)} tokens does not fit max_model_len={self.args.max_model_len}")
+        if self.paged:
+            pool = len(self._block_ref) - 1
+            if self._nblocks(len(ids) + 1) > pool:
+                raise ValueError(f"prompt of {len(ids)} tokens does not fit the KV block pool ({pool} blocks of {self.args.block_size})")
+            if self._nblocks(min(len(ids) + cfg.max_new_tokens, self.args.max_model_len)) > pool:
+                # the pool could never promise this request its worst case: cap the generation at what the pool holds
+                import dataclasses
+                room = pool * self.args.block_size - 8 - len(ids)
+                cfg = dataclasses.replace(cfg, max_new_tokens=max(1, room))
         r = Request(next(self._ids), ids, cfg)
         with self._cv:
             self.waiting.append(r)

@@ -332,3 +332,14 @@ def test_paged_kv_cache_small_pool_queues_and_recovers(model):
     assert [r.output_ids for r in reqs] == want
     assert peak < 4                                                     # the block pool, not the row count, was the limit
     assert 0.0 <= eng.kv_cache_usage() <= 1.0
+
+
+def test_paged_pool_rejects_or_caps_requests_it_can_never_hold(model):
+    import pytest as _pt
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=2, max_model_len=96, block_size=16, num_kv_blocks=3))   # 48 tokens of KV
+    with _pt.raises(ValueError):
+        eng.submit(list(range(60)), GenerationConfig(max_new_tokens=4, do_sample=False))
+    r = eng.submit(list(range(20)), GenerationConfig(max_new_tokens=64, do_sample=False))                       # worst case 84 tokens
+    assert r.cfg.max_new_tokens == 48 - 8 - 20
+    _drain(eng, [r])
+    assert len(r.output_ids) == 20 and r.finish_reason == "length" and eng._reserved == 0
