@@ -10,7 +10,8 @@
 // Per (query tile, key block) pair, in both modes:
 //     S  = Q K^T      (M 128 x N 64 x K 128)   -> TMEM, double-buffered            \  issued one pair AHEAD of the
 //     dP = dO V^T     (M 128 x N 64 x K 128)   -> TMEM, double-buffered            /  element-wise warps
-//     warps 0-3, thread = query row:  P = exp2(S c - lse),  dS = P (dP - delta) * scale  -> two 16-bit 128B-swizzled tiles
+//     warps 0-7, thread = (query row, half of the keys):  P = exp2(S c - lse),  dS = P (dP - delta) * scale  -> two 16-bit
+//                                                          128B-swizzled tiles in shared memory
 //     mode KV:  dV^T += dO^T P   (M 128 (d) x N 64 x K 128 (rows), both operands MN-major, read in place)
 //               dK^T += Q^T dS
 //     mode Q :  dQ   += dS K     (M 128 x N 128 x K 64)

@@ -2,7 +2,8 @@
 // tiles brought in by TMA straight out of the fused qkv projection (no head transposes, GQA by column offset), online
 // softmax by four warps whose threads each own ONE query row (TMEM lane = row, so row max and row sum need no shuffles).
 //
-//   CTA = (128-query tile, head, batch); 256 threads: warps 0-3 softmax, warp 4 TMA producer, warp 5 tcgen05 issuer.
+//   CTA = (128-query tile, head, batch); 256 threads: warps 0-3 softmax, warp 4 TMA producer, warp 5 tcgen05 issuer (the
+//   whole warp runs the issue loop, elect.sync picks the lane: descriptors stay in uniform registers).
 //   TMEM (256 columns, two CTAs per SM): S(even j) [0, 64), S(odd j) [64, 128), O [128, 256).
 //   per 64-key block j:   S_j = Q K_j^T          (M 128 x N 64 x K 128, 8 UMMAs), issued one block AHEAD of the softmax
 //                         softmax warps: tcgen05.ld S_j (64 registers), running max, P = exp2(S c - m c) -> 16 bit,
