@@ -88,6 +88,66 @@ class ReplicaRouter:
         return max(self.auto["min_replicas"], min(self.auto["max_replicas"], max(want, 1)))
 
 
+class AutoscalingReplicaSet(ReplicaRouter):
+    """A replica set that ACTS on the autoscaling block of the Ray Serve YAMLs
+    (Deployment/Ray/serve_deploy_examples/qwen3_app_autoscaling.yaml: ``min_replicas`` / ``max_replicas`` /
+    ``initial_replicas`` / ``target_ongoing_requests`` / ``upscale_delay_s`` / ``downscale_delay_s``): ``tick()`` compares the
+    desired count (``ceil(ongoing / target)``) with the live one; a wish to grow that has lasted ``upscale_delay_s`` starts
+    replicas through ``factory()`` (one engine per call, e.g. one per GPU), a wish to shrink that has lasted
+    ``downscale_delay_s`` takes the least-loaded replica out of rotation, lets it drain and shuts it down. ``submit`` routes
+    to the least-loaded live replica (and ticks)."""
+
+    def __init__(self, factory, autoscaling: Optional[Dict[str, Any]] = None, clock=time.monotonic):
+        a = dict(autoscaling or {})
+        a.setdefault("min_replicas", 1)
+        a.setdefault("max_replicas", max(1, a["min_replicas"]))
+        a.setdefault("target_ongoing_requests", 5)
+        a.setdefault("upscale_delay_s", 30.0)
+        a.setdefault("downscale_delay_s", 600.0)
+        self.factory, self._clock = factory, clock
+        n0 = int(a.get("initial_replicas", a["min_replicas"]))
+        n0 = max(a["min_replicas"], min(a["max_replicas"], n0))
+        super().__init__([factory() for _ in range(n0)], a)
+        self.draining: List[Any] = []
+        self._up_since: Optional[float] = None
+        self._down_since: Optional[float] = None
+        self.events: List[tuple] = []          # (time, "up" | "down" | "stopped", live replicas afterwards)
+
+    def tick(self) -> int:
+        now = self._clock()
+        for e in list(self.draining):                       # replicas taken out of rotation: stop them once they are idle
+            if e.num_running + e.num_waiting == 0:
+                self.draining.remove(e)
+                if hasattr(e, "shutdown"):
+                    e.shutdown()
+                self.events.append((now, "stopped", len(self.engines)))
+        want, have = self.desired_replicas(), len(self.engines)
+        if want > have:
+            self._down_since = None
+            self._up_since = now if self._up_since is None else self._up_since
+            if now - self._up_since >= float(self.auto["upscale_delay_s"]):
+                while len(self.engines) < want:
+                    self.engines.append(self.factory())
+                self._up_since = None
+                self.events.append((now, "up", len(self.engines)))
+        elif want < have:
+            self._up_since = None
+            self._down_since = now if self._down_since is None else self._down_since
+            if now - self._down_since >= float(self.auto["downscale_delay_s"]):
+                loads = self.ongoing()
+                victim = self.engines.pop(loads.index(min(loads)))        # one replica per decision, like Ray Serve's smoothing
+                self.draining.append(victim)
+                self._down_since = None
+                self.events.append((now, "down", len(self.engines)))
+        else:
+            self._up_since = self._down_since = None
+        return len(self.engines)
+
+    def submit(self, prompt_ids, cfg=None):
+        self.tick()
+        return super().submit(prompt_ids, cfg)
+
+
 def build_engine(cfg: LLMConfig, device=None):
     from ..recipes.infer import _load
     from .engine import EngineArgs, LLMEngine

@@ -115,3 +115,54 @@ def test_distributed_cluster_healthcheck(tmp_path):
     assert rep["healthy"] and rep["world_size"] == 2 and rep["nodes"] == 1 and rep["distinct_pids"]
     assert rep["object_path_ok"] and len(rep["workers"]) == 2 and rep["workers"][1]["rank"] == 1
     assert rep["object_gbs_slowest"] > 0
+
+
+def test_autoscaling_replica_set_follows_the_ray_serve_rule():
+    """deploy.AutoscalingReplicaSet acts on min / max / initial replicas, target_ongoing_requests and the up / down delays of
+    the reference's Ray Serve autoscaling YAML: grows after upscale_delay_s of sustained load, drains and stops one
+    replica per downscale decision, never leaves [min, max]."""
+    from llm_in_practise_b200.serve.deploy import AutoscalingReplicaSet
+
+    class FakeEngine:
+        def __init__(self):
+            self.num_running, self.num_waiting, self.stopped = 0, 0, False
+
+        def submit(self, ids, cfg=None):
+            self.num_running += 1
+            return self
+
+        def shutdown(self):
+            self.stopped = True
+
+    made = []
+    t = [0.0]
+
+    def factory():
+        made.append(FakeEngine())
+        return made[-1]
+
+    rs = AutoscalingReplicaSet(factory, {"min_replicas": 1, "max_replicas": 3, "initial_replicas": 1, "target_ongoing_requests": 2,
+                                         "upscale_delay_s": 10, "downscale_delay_s": 60}, clock=lambda: t[0])
+    assert len(rs.engines) == 1
+    for _ in range(7):
+        rs.submit([1, 2, 3])
+    assert rs.desired_replicas() == 3 and len(rs.engines) == 1          # the wish is younger than upscale_delay_s
+    t[0] = 11
+    assert rs.tick() == 3 and len(made) == 3
+    for _ in range(4):                                                   # new work goes to the empty replicas
+        rs.submit([1])
+    assert sorted(rs.ongoing()) == [2, 2, 7]
+    for e in made:                                                       # all work finishes
+        e.num_running = 0
+    t[0] = 20
+    assert rs.tick() == 3                                                # wish to shrink, but downscale_delay_s has not passed
+    t[0] = 85
+    assert rs.tick() == 2 and len(rs.draining) == 1
+    t[0] = 86
+    rs.tick()
+    assert not rs.draining and sum(e.stopped for e in made) == 1
+    t[0] = 150
+    assert rs.tick() == 1
+    t[0] = 300
+    assert rs.tick() == 1                                                # min_replicas holds
+    assert [e[1] for e in rs.events].count("up") == 1 and [e[1] for e in rs.events].count("down") == 2
