@@ -97,8 +97,13 @@ class AutoscalingReplicaSet(ReplicaRouter):
     ``downscale_delay_s`` takes the least-loaded replica out of rotation, lets it drain and shuts it down. ``submit`` routes
     to the least-loaded live replica (and ticks)."""
 
-    def __init__(self, factory, autoscaling: Optional[Dict[str, Any]] = None, clock=time.monotonic):
+    def __init__(self, factory, autoscaling: Optional[Dict[str, Any]] = None, clock=time.monotonic,
+                 max_ongoing_requests: Optional[int] = None):
         a = dict(autoscaling or {})
+        for short in ("upscale_delay", "downscale_delay"):          # the reference's YAML spells them without the _s suffix
+            if short in a and short + "_s" not in a:
+                a[short + "_s"] = a[short]
+        self.max_ongoing = max_ongoing_requests                     # deployment_config.max_ongoing_requests: per-replica cap
         a.setdefault("min_replicas", 1)
         a.setdefault("max_replicas", max(1, a["min_replicas"]))
         a.setdefault("target_ongoing_requests", 5)
@@ -145,6 +150,8 @@ class AutoscalingReplicaSet(ReplicaRouter):
 
     def submit(self, prompt_ids, cfg=None):
         self.tick()
+        if self.max_ongoing is not None and min(self.ongoing()) >= self.max_ongoing:
+            raise RuntimeError(f"every replica holds max_ongoing_requests={self.max_ongoing} requests (back-pressure)")
         return super().submit(prompt_ids, cfg)
 
 

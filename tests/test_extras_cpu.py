@@ -166,3 +166,17 @@ def test_autoscaling_replica_set_follows_the_ray_serve_rule():
     t[0] = 300
     assert rs.tick() == 1                                                # min_replicas holds
     assert [e[1] for e in rs.events].count("up") == 1 and [e[1] for e in rs.events].count("down") == 2
+    # the reference's own YAML: keys without the _s suffix, per-replica max_ongoing_requests as back-pressure
+    import os
+    import yaml
+    ref = "/root/reference/Deployment/Ray/serve_deploy_examples/qwen3_app_autoscaling.yaml"
+    if os.path.exists(ref):
+        dc = yaml.safe_load(open(ref))["applications"][0]["args"]["llm_configs"][0]["deployment_config"]
+        rs2 = AutoscalingReplicaSet(factory, dc["autoscaling_config"], clock=lambda: t[0], max_ongoing_requests=2)
+        assert rs2.auto["upscale_delay_s"] == 5.0 and rs2.auto["downscale_delay_s"] == 30.0 and rs2.auto["max_replicas"] == 2
+        rs2.submit([1]); rs2.submit([1])
+        try:
+            rs2.submit([1])
+            raise AssertionError("expected back-pressure")
+        except RuntimeError as e:
+            assert "back-pressure" in str(e)
