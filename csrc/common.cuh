@@ -241,6 +241,14 @@ __device__ __forceinline__ void mbar_wait_warp(uint32_t bar, uint32_t parity) {
 }
 
 // --------------------------------------------------------------------------------------------
+// State a CUDA-graph replay has to see change: kernel ARGUMENTS are frozen at capture, device MEMORY is not.
+//   b200_graph_seed_offset(): device pointer (or null) to one uint64 that every Philox-drawing kernel adds to its seed
+//   argument. A captured training step copies it from pinned host memory at its start, so each replay drops different
+//   elements while the forward and the backward of one replay still agree (b200_set_graph_state, elementwise.cu).
+// --------------------------------------------------------------------------------------------
+const unsigned long long* b200_graph_seed_offset();
+
+// --------------------------------------------------------------------------------------------
 // proxy fences
 // --------------------------------------------------------------------------------------------
 // generic-proxy smem writes -> visible to the async proxy (TMA store / tcgen05.mma reads)

@@ -40,10 +40,11 @@ __device__ __forceinline__ bool dropout_keep(unsigned long long seed, unsigned l
 // y = keep ? x / (1-p) : 0 ; the backward is the same kernel applied to dy (same seed).
 template <typename T>
 __global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, unsigned long long seed,
-                               uint32_t thresh, float inv_keep) {
+                               uint32_t thresh, float inv_keep, const unsigned long long* __restrict__ seed_off) {
   const long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long i0 = q * 4;
   if (i0 >= n) return;
+  if (seed_off) seed += *seed_off;          // CUDA-graph replay: the per-step part of the seed lives in device memory
   const uint4 b = dropout_bits(seed, (unsigned long long)q);
   const uint32_t r[4] = {b.x, b.y, b.z, b.w};
 #pragma unroll
@@ -360,6 +361,16 @@ using namespace b200;
   else if (dtype == B200_DT_FP32) { using T = float; __VA_ARGS__; }    \
   else return B200_ERR_UNSUPPORTED;
 
+static const unsigned long long* g_graph_seed_offset = nullptr;
+const unsigned long long* b200::b200_graph_seed_offset() { return g_graph_seed_offset; }
+
+// seed_offset_dev: device pointer to one uint64 added to the seed argument of every dropout-drawing kernel launched from
+// now on (b200_dropout, the flash-attention kernels with dropout), or NULL to switch it off. See common.cuh.
+B200_API int b200_set_graph_state(const void* seed_offset_dev) {
+  g_graph_seed_offset = reinterpret_cast<const unsigned long long*>(seed_offset_dev);
+  return 0;
+}
+
 B200_API int b200_dropout(const void* x, void* y, long long n, unsigned long long seed, float p, int dtype,
                           void* stream) {
   if (n <= 0) return 0;
@@ -368,7 +379,8 @@ B200_API int b200_dropout(const void* x, void* y, long long n, unsigned long lon
   const long long q = (n + 3) / 4;
   const int tb = 256;
   const unsigned grid = (unsigned)((q + tb - 1) / tb);
-  B200_DISPATCH_T(dtype, dropout_kernel<T><<<grid, tb, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, n, seed, thresh, inv_keep));
+  B200_DISPATCH_T(dtype, dropout_kernel<T><<<grid, tb, 0, (cudaStream_t)stream>>>((const T*)x, (T*)y, n, seed, thresh, inv_keep,
+                                                                                   b200_graph_seed_offset()));
   B200_LAUNCH_CHECK();
   return 0;
 }

@@ -38,6 +38,7 @@ struct FlashParams {
   unsigned long long seed;   // attention-probability dropout (nn.MultiheadAttention(dropout=p)): Philox, regenerated in backward
   uint32_t drop_thresh;      // 0 = no dropout; P(drop) = thresh / 2^32
   float inv_keep;
+  const unsigned long long* seed_off;   // optional per-replay seed offset in device memory (CUDA-graph captured steps)
 };
 
 constexpr float kLog2e = 1.4426950408889634f;
@@ -63,7 +64,7 @@ __device__ __forceinline__ uint4 flash_philox(unsigned long long seed, unsigned 
 __device__ __forceinline__ void flash_drop4(const FlashParams& p, long long bh, int row_lo, int key0, float (&m)[4]) {
   const unsigned long long q = ((unsigned long long)bh * (unsigned long long)p.S + (unsigned long long)row_lo) *
                                (unsigned long long)((p.S + 1) / 2) + (unsigned long long)(key0 >> 1);
-  const uint4 r = flash_philox(p.seed, q);
+  const uint4 r = flash_philox(p.seed + (p.seed_off ? __ldg(p.seed_off) : 0ull), q);
   m[0] = r.x >= p.drop_thresh ? p.inv_keep : 0.f;
   m[1] = r.y >= p.drop_thresh ? p.inv_keep : 0.f;
   m[2] = r.z >= p.drop_thresh ? p.inv_keep : 0.f;
@@ -811,6 +812,7 @@ using namespace b200;
 
 static void set_dropout(FlashParams& p, float dropout_p, unsigned long long seed) {
   p.seed = seed;
+  p.seed_off = b200_graph_seed_offset();
   if (dropout_p <= 0.f) { p.drop_thresh = 0; p.inv_keep = 1.f; return; }
   p.drop_thresh = dropout_p >= 1.f ? 0xFFFFFFFFu : (uint32_t)((double)dropout_p * 4294967296.0);
   p.inv_keep = dropout_p >= 1.f ? 0.f : 1.f / (1.f - dropout_p);

@@ -26,8 +26,9 @@ template <typename PT, typename GT, typename LT>
 __global__ void __launch_bounds__(256)
 adamw_kernel(PT* __restrict__ p, const GT* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
              LT* __restrict__ p_lowp, long long n, AdamHyper h, const float* __restrict__ dyn_scale,
-             const float* __restrict__ found_inf) {
+             const float* __restrict__ found_inf, const AdamHyper* __restrict__ h_dev) {
   if (found_inf && *found_inf != 0.f) return;  // overflowed step: skip (fp16 dynamic loss scaling)
+  if (h_dev) h = *h_dev;                       // CUDA-graph replay: lr / bias corrections come from device memory
   const float gs = h.grad_scale * (dyn_scale ? *dyn_scale : 1.f);
   const float step = h.lr / h.bias_c1;
   const float rs2 = rsqrtf(h.bias_c2);
@@ -150,15 +151,17 @@ static inline unsigned flat_grid(long long n, int tb) {
 using namespace b200;
 
 // p: params (p_dtype fp32 or bf16); g: grads (g_dtype); m, v: fp32; p_lowp: optional bf16 copy.
-B200_API int b200_adamw(void* p, const void* g, float* m, float* v, void* p_lowp, long long n,
-                        const b200_adam_hyper* hy, const float* dyn_scale, const float* found_inf, int p_dtype,
-                        int g_dtype, void* stream) {
+static int adamw_impl(void* p, const void* g, float* m, float* v, void* p_lowp, long long n,
+                      const b200_adam_hyper* hy, const void* hyper_dev, const float* dyn_scale, const float* found_inf, int p_dtype,
+                      int g_dtype, void* stream) {
   if (n <= 0) return 0;
-  AdamHyper h = {hy->lr, hy->beta1, hy->beta2, hy->eps, hy->weight_decay, hy->bias_c1, hy->bias_c2, hy->grad_scale};
+  AdamHyper h = {};
+  if (hy) h = {hy->lr, hy->beta1, hy->beta2, hy->eps, hy->weight_decay, hy->bias_c1, hy->bias_c2, hy->grad_scale};
+  const AdamHyper* h_dev = reinterpret_cast<const AdamHyper*>(hyper_dev);
   cudaStream_t st = (cudaStream_t)stream;
   const unsigned grid = flat_grid(n, 256);
   __nv_bfloat16* lp = (__nv_bfloat16*)p_lowp;
-#define B200_ADAM(PT, GT) adamw_kernel<PT, GT, __nv_bfloat16><<<grid, 256, 0, st>>>((PT*)p, (const GT*)g, m, v, lp, n, h, dyn_scale, found_inf)
+#define B200_ADAM(PT, GT) adamw_kernel<PT, GT, __nv_bfloat16><<<grid, 256, 0, st>>>((PT*)p, (const GT*)g, m, v, lp, n, h, dyn_scale, found_inf, h_dev)
   if (p_dtype == B200_DT_FP32 && g_dtype == B200_DT_FP32) B200_ADAM(float, float);
   else if (p_dtype == B200_DT_FP32 && g_dtype == B200_DT_BF16) B200_ADAM(float, __nv_bfloat16);
   else if (p_dtype == B200_DT_BF16 && g_dtype == B200_DT_BF16) B200_ADAM(__nv_bfloat16, __nv_bfloat16);
@@ -168,6 +171,23 @@ B200_API int b200_adamw(void* p, const void* g, float* m, float* v, void* p_lowp
 #undef B200_ADAM
   B200_LAUNCH_CHECK();
   return 0;
+}
+
+B200_API int b200_adamw(void* p, const void* g, float* m, float* v, void* p_lowp, long long n,
+                        const b200_adam_hyper* hy, const float* dyn_scale, const float* found_inf, int p_dtype,
+                        int g_dtype, void* stream) {
+  if (!hy) return B200_ERR_BAD_SHAPE;
+  return adamw_impl(p, g, m, v, p_lowp, n, hy, nullptr, dyn_scale, found_inf, p_dtype, g_dtype, stream);
+}
+
+// The same update with the hyper-parameters (8 floats in b200_adam_hyper's order: lr, beta1, beta2, eps, weight_decay,
+// 1 - beta1^t, 1 - beta2^t, grad_scale) read from DEVICE memory inside the kernel: a launch captured in a CUDA graph
+// follows the learning-rate schedule and the bias corrections of later steps (the caller refreshes hyper_dev, e.g. with a
+// captured copy from pinned host memory, before each replay).
+B200_API int b200_adamw_graph(void* p, const void* g, float* m, float* v, void* p_lowp, long long n, const void* hyper_dev,
+                              const float* dyn_scale, const float* found_inf, int p_dtype, int g_dtype, void* stream) {
+  if (!hyper_dev) return B200_ERR_BAD_SHAPE;
+  return adamw_impl(p, g, m, v, p_lowp, n, nullptr, hyper_dev, dyn_scale, found_inf, p_dtype, g_dtype, stream);
 }
 
 B200_API int b200_adamw8bit(void* p, const void* g, uint8_t* s1, uint8_t* s2, float* absmax1, float* absmax2,

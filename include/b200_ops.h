@@ -230,6 +230,13 @@ typedef struct {
 
 int b200_adamw(void* p, const void* g, float* m, float* v, void* p_lowp, long long n, const b200_adam_hyper* hy,
                const float* dyn_scale, const float* found_inf, int p_dtype, int g_dtype, void* stream);
+/* b200_adamw with the hyper-parameters read from device memory (8 floats, b200_adam_hyper's order) inside the kernel, so
+ * that a launch captured in a CUDA graph follows the schedule of later steps; b200_set_graph_state registers the device
+ * uint64 that every dropout-drawing kernel (b200_dropout, flash attention with dropout) adds to its seed argument, for the
+ * same reason. Both are refreshed by the caller (a captured copy from pinned host memory) before each replay. */
+int b200_adamw_graph(void* p, const void* g, float* m, float* v, void* p_lowp, long long n, const void* hyper_dev,
+                     const float* dyn_scale, const float* found_inf, int p_dtype, int g_dtype, void* stream);
+int b200_set_graph_state(const void* seed_offset_dev);
 int b200_adamw8bit(void* p, const void* g, uint8_t* s1, uint8_t* s2, float* absmax1, float* absmax2,
                    const float* qmap1, const float* qmap2, void* p_lowp, long long n, const b200_adam_hyper* hy,
                    const float* dyn_scale, const float* found_inf, int p_dtype, int g_dtype, void* stream);

@@ -69,6 +69,32 @@ class FusedAdamW(torch.optim.Optimizer):
         self.dyn_scale: Optional[torch.Tensor] = None   # device scalar multiplied into every gradient
         self.found_inf: Optional[torch.Tensor] = None   # device flag: skip the step when non-zero
         self.grad_scale = 1.0
+        self._graph_mode = False
+
+    # ------------------------------------------------------------------ CUDA-graph capturable mode
+    def enable_graph_mode(self) -> None:
+        """Hyper-parameters (lr, bias corrections, ...) travel through device memory instead of kernel arguments, so a
+        ``step()`` captured in a CUDA graph keeps following the schedule: ``step()`` writes them to pinned host memory and
+        issues the host->device copy (a memcpy node under capture); before each replay ``advance_graph_step()`` moves the
+        step counter on and rewrites the pinned values. fp32 / bf16 AdamW only (``utils/graph_step.GraphedTrainStep``)."""
+        if self.eight_bit:
+            raise NotImplementedError("the 8-bit AdamW keeps its hyper-parameters in kernel arguments")
+        if self._ranges is None:
+            self._ranges = self._build_ranges()
+        dev = self._ranges[0].p.device
+        self._hyper_host = torch.zeros(len(self._ranges), 8, dtype=torch.float32).pin_memory()
+        self._hyper_dev = torch.zeros(len(self._ranges), 8, dtype=torch.float32, device=dev)
+        self._graph_mode = True
+
+    def _write_hyper(self) -> None:
+        for i, r in enumerate(self._ranges):
+            h = _hyper(getattr(r, "group", self.param_groups[0]), self._step, self.grad_scale)
+            self._hyper_host[i] = torch.tensor([h.lr, h.beta1, h.beta2, h.eps, h.weight_decay, h.bias_c1, h.bias_c2, h.grad_scale])
+
+    def advance_graph_step(self) -> None:
+        """Call before replaying a graph that contains ``step()``."""
+        self._step += 1
+        self._write_hyper()
 
     # ------------------------------------------------------------------
     def _build_ranges(self) -> List[_Range]:
@@ -113,7 +139,10 @@ class FusedAdamW(torch.optim.Optimizer):
         if self._ranges is None:
             self._ranges = self._build_ranges()
         self._step += 1
-        for r in self._ranges:
+        if self._graph_mode:
+            self._write_hyper()
+            self._hyper_dev.copy_(self._hyper_host, non_blocking=True)      # under capture: a memcpy node, re-read every replay
+        for ri, r in enumerate(self._ranges):
             group = getattr(r, "group", self.param_groups[0])
             g = r.g
             if g is None:
@@ -124,7 +153,15 @@ class FusedAdamW(torch.optim.Optimizer):
             if not r.state:
                 self._init_state(r)
             h = _hyper(group, self._step, self.grad_scale)
-            if nv.use_native(r.p):
+            if self._graph_mode and nv.use_native(r.p):
+                fn = nv.proto("b200_adamw_graph", [vp] * 5 + [i64, vp, vp, vp, i32, i32, vp])
+                st = r.state
+                nv.check(fn(nv.ptr(r.p), nv.ptr(g), nv.ptr(st["exp_avg"]), nv.ptr(st["exp_avg_sq"]), nv.ptr(r.lowp), r.p.numel(),
+                            self._hyper_dev[ri].data_ptr(), nv.ptr(self.dyn_scale), nv.ptr(self.found_inf),
+                            nv.dtype_code(r.p.dtype), nv.dtype_code(g.dtype), nv.stream()), "adamw_graph")
+                nv.count_launch()
+                torch.autograd.graph.increment_version(r.p)
+            elif nv.use_native(r.p):
                 self._native(r, g, h)
             else:
                 self._reference(r, g, h)

@@ -25,6 +25,7 @@ ap.add_argument("--warmup", type=int, default=3)
 ap.add_argument("--batch", type=int, default=0)
 ap.add_argument("--stage", type=int, default=0)
 ap.add_argument("--layers", type=int, default=0)
+ap.add_argument("--graph", action="store_true", help="gptlike / minigpt2 on one GPU: the whole step replayed from a CUDA graph (utils/graph_step.py)")
 ap.add_argument("--wrapper", default="ddp", choices=["ddp", "fsdp"], help="gptlike / minigpt2: DDP (reference ddp_basics) or FSDP FULL_SHARD (fsdp_basics)")
 a = ap.parse_args()
 info = setup_distributed()
@@ -90,6 +91,21 @@ if a.config in ("gptlike-ddp", "minigpt2-ddp"):
         loss.backward()
         opt.step()
         ddp.zero_grad()
+    if a.graph:
+        if world != 1 or a.wrapper != "ddp":
+            raise SystemExit("--graph: single process, DDP wrapper only")
+        from llm_in_practise_b200.utils.graph_step import GraphedTrainStep
+
+        def loss_fn(x):
+            o = ddp(x, x)
+            return o[1] if isinstance(o, tuple) else o
+        gstep = GraphedTrainStep(loss_fn, opt, [xs[0]], zero_grad=ddp.zero_grad)
+
+        def step():                                          # noqa: F811 - the graph-replayed step replaces the eager one
+            x = xs[k[0] % 4]
+            k[0] += 1
+            gstep(x)
+        out["cuda_graph"] = True
     ms = timed(step)
     n_params = sum(p.numel() for p in model.parameters())
     torch.cuda.synchronize()

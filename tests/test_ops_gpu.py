@@ -571,3 +571,89 @@ def test_deepseeklike_flash_mla_and_grouped_moe_match_fp32_model():
     ga = torch.cat([p.grad.float().reshape(-1).cpu() for p in m.parameters()])
     gb = torch.cat([p.grad.float().reshape(-1) for p in ref.parameters()])
     assert float((ga - gb).norm() / gb.norm()) < 8e-2
+
+
+def test_dropout_seed_offset_from_device_memory():
+    """b200_set_graph_state: a dropout launch captured in a CUDA graph drops different elements at every replay (the per-step
+    part of the Philox seed is read from device memory), forward and backward of one replay use the same mask."""
+    import ctypes
+    from llm_in_practise_b200.ops import _native as nvm
+    x = torch.ones(1 << 16, device=DEV, dtype=torch.bfloat16, requires_grad=True)
+    off = torch.zeros(1, dtype=torch.int64, device=DEV)
+    fn = nvm.proto("b200_set_graph_state", [ctypes.c_void_p])
+    nvm.check(fn(off.data_ptr()), "set_graph_state")
+    try:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            y = ew.dropout(x, 0.25, True, seed=1234)
+            y.sum().backward()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        x.grad = None
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            y = ew.dropout(x, 0.25, True, seed=1234)
+            (gx,) = torch.autograd.grad(y.sum(), x)
+        masks = []
+        for step in range(3):
+            off.fill_(step * 7919)
+            g.replay()
+            torch.cuda.synchronize()
+            keep = y.detach() != 0
+            assert torch.equal(keep, gx != 0)                      # backward regenerated the forward's mask
+            assert abs(float(keep.float().mean()) - 0.75) < 0.02
+            masks.append(keep.clone())
+        assert not torch.equal(masks[0], masks[1]) and not torch.equal(masks[1], masks[2])
+        off.fill_(0)
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(y.detach() != 0, masks[0])             # same offset, same mask
+    finally:
+        nvm.check(fn(None), "set_graph_state")
+
+
+def test_graphed_train_step_matches_eager_and_trains_with_dropout():
+    """utils/graph_step.GraphedTrainStep: forward + backward + AdamW + zero_grad of a small GPTLike replayed from ONE CUDA
+    graph. Without dropout the parameters follow the eager run step for step (learning rate and bias corrections reach the
+    captured optimizer kernel through device memory); with dropout the loss still falls and differs from replay to replay."""
+    import ctypes
+    from llm_in_practise_b200.models.gpt import GPTLike
+    from llm_in_practise_b200.ops import _native as nvm
+    from llm_in_practise_b200.parallel.ddp import DistributedDataParallel as DDP
+    from llm_in_practise_b200.utils.graph_step import GraphedTrainStep
+
+    def build(dropout):
+        torch.manual_seed(3)
+        ew.manual_seed(11)
+        m = GPTLike(512, 64, 2, 4, 128, dropout=dropout, dtype=torch.bfloat16, device=DEV)
+        d = DDP(m, mixed_precision=torch.bfloat16)
+        return m, d, d.make_optimizer(lr=3e-3, weight_decay=0.01)
+
+    def loss_of(d, x):
+        o = d(x, x)
+        return o[1] if isinstance(o, tuple) else o
+
+    x = torch.randint(0, 512, (4, 64), device=DEV, generator=torch.Generator(device=DEV).manual_seed(1))
+    try:
+        # ---- parity without dropout: 3 warm-up steps inside GraphedTrainStep + 5 replays == 8 eager steps ----
+        m1, d1, o1 = build(0.0)
+        for _ in range(8):
+            loss_of(d1, x).backward()
+            o1.step()
+            d1.zero_grad()
+        m2, d2, o2 = build(0.0)
+        gs = GraphedTrainStep(lambda t: loss_of(d2, t), o2, [x], zero_grad=d2.zero_grad, warmup=3)
+        for _ in range(5):
+            lg = gs(x)
+        torch.cuda.synchronize()
+        p1 = torch.cat([p.detach().float().reshape(-1) for p in m1.parameters()])
+        p2 = torch.cat([p.detach().float().reshape(-1) for p in m2.parameters()])
+        assert o2._step == 8 and float((p1 - p2).norm() / p1.norm()) < 2e-2      # bf16 + atomics in the embedding backward: not bit-reproducible
+        # ---- with dropout: trains, and no two replays see the same loss (different masks) ----
+        m3, d3, o3 = build(0.1)
+        gs3 = GraphedTrainStep(lambda t: loss_of(d3, t), o3, [x], zero_grad=d3.zero_grad, warmup=3)
+        losses = [float(gs3(x)) for _ in range(30)]
+        assert losses[-1] < 0.7 * losses[0] and len(set(round(v, 5) for v in losses)) > 25
+    finally:
+        nvm.check(nvm.proto("b200_set_graph_state", [ctypes.c_void_p])(None), "set_graph_state")
