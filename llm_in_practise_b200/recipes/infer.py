@@ -72,8 +72,19 @@ def main(argv=None):
     ap.add_argument("--max_num_seqs", type=int, default=16)
     ap.add_argument("--prompt_style", default="chatml", choices=["chatml", "deepseek"])
     ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float16"])
+    ap.add_argument("--tensor-parallel-size", "--tensor_parallel_size", dest="tp", type=int, default=1,
+                    help="serve: ranks that share every layer (vllm serve --tensor-parallel-size; launch under torchrun)")
+    ap.add_argument("--pipeline-parallel-size", "--pipeline_parallel_size", dest="pp", type=int, default=1,
+                    help="serve: pipeline stages (engine_kwargs.pipeline_parallel_size of the Ray Serve recipe)")
+    ap.add_argument("--block-size", "--block_size", dest="block_size", type=int, default=0, help="serve: paged KV cache block (0 = one row per sequence)")
     a = ap.parse_args(argv)
     dtype = getattr(torch, a.dtype)
+    if a.tp * a.pp > 1:
+        from ..parallel.dist import setup_distributed
+        info = setup_distributed()                      # one process per GPU; sets the device the checkpoint is loaded onto
+        if a.cmd != "serve" or info.world_size != a.tp * a.pp:
+            ap.error(f"--tensor-parallel-size x --pipeline-parallel-size = {a.tp * a.pp} needs `serve` under "
+                     f"`torchrun --nproc-per-node {a.tp * a.pp}` (this run has {info.world_size} rank(s))")
     model, tok = _load(a.model, a.adapter, dtype)
     dev = getattr(model, "base_model", model).embed_tokens.device
     eos = [t for t in (getattr(tok, "eos_token_id", None),) if t is not None]
@@ -140,7 +151,18 @@ def main(argv=None):
     elif a.cmd == "serve":
         from ..serve import EngineArgs, LLMEngine
         from ..serve.openai_server import serve
-        eng = LLMEngine(model, tok, EngineArgs(max_num_seqs=a.max_num_seqs, max_model_len=a.max_model_len), model_name=os.path.basename(a.model.rstrip("/")))
+        eargs = EngineArgs(max_num_seqs=a.max_num_seqs, max_model_len=a.max_model_len, block_size=a.block_size)
+        name = os.path.basename(a.model.rstrip("/"))
+        if a.tp * a.pp > 1:
+            # SPMD: rank 0 schedules and answers HTTP, the others repeat its model calls on their shard / stage
+            from ..serve.tp_engine import build_pp_engine, build_tp_engine
+            base = getattr(model, "base_model", model)
+            eng = (build_pp_engine(base, tok, eargs, name, a.pp, a.tp) if a.pp > 1 else build_tp_engine(base, tok, eargs, name))
+            if eng.rank != 0:
+                eng.serve_forever()
+                return
+        else:
+            eng = LLMEngine(model, tok, eargs, model_name=name)
         serve(eng, a.host, a.port, prompt_style=a.prompt_style)
 
 

@@ -6,8 +6,9 @@ Deployment/Ray/serve_deploy_examples/*.yaml) and map them onto ``LLMEngine`` + t
 
 * ``model_loading_config``: ``model_id`` (served name) and ``model_source`` (checkpoint directory, GPTQ / AWQ
   checkpoints are auto-detected — the "minimal AWQ" example);
-* ``engine_kwargs``: ``max_num_seqs``, ``max_model_len``, ``dtype``; ``tensor_parallel_size`` and ``pipeline_parallel_size``
-  must be 1 here (one engine per GPU; more GPUs = more replicas behind ``ReplicaRouter``), ``gpu_memory_utilization`` /
+* ``engine_kwargs``: ``max_num_seqs``, ``max_model_len``, ``dtype``; ``tensor_parallel_size`` x ``pipeline_parallel_size``
+  ranks under torchrun form one replica (``serve/tp_engine.py``: Megatron sharding inside a stage, ``parallel/pp.py`` stages
+  across; more GPUs otherwise = more replicas behind ``ReplicaRouter``), ``gpu_memory_utilization`` /
   ``enable_prefix_caching`` / ``enable_chunked_prefill`` / ``enforce_eager`` are accepted and recorded;
 * ``deployment_config.autoscaling_config``: ``min_replicas`` / ``max_replicas`` / ``target_ongoing_requests`` drive
   ``ReplicaRouter.desired_replicas`` (the decision rule; starting processes is the launcher's job);
@@ -50,9 +51,9 @@ class LLMConfig:
         return a
 
     def parallel_size(self) -> int:
-        """GPUs one replica spans. ``pipeline_parallel_size`` (the reference's two-Ray-worker recipe,
-        serve_deploy_examples/qwen3_app_pipeline_parallel.yaml:21-31, splits layers across HOSTS over TCP) is folded into
-        the tensor-parallel degree: inside one NVLink / NVSwitch node the same GPUs are better used as TP ranks."""
+        """GPUs one replica spans: ``tensor_parallel_size x pipeline_parallel_size`` ranks under torchrun. With
+        ``pipeline_parallel_size`` > 1 (serve_deploy_examples/qwen3_app_pipeline_parallel.yaml:21-31) the decoder layers are
+        split into that many stages (``parallel/pp.py``), each stage tensor-parallel over ``tensor_parallel_size`` ranks."""
         ek = self.engine_kwargs
         return int(ek.get("tensor_parallel_size", 1)) * int(ek.get("pipeline_parallel_size", 1))
 
@@ -166,7 +167,11 @@ def build_engine(cfg: LLMConfig, device=None):
                       enable_prefix_caching=bool(ek.get("enable_prefix_caching", True)),
                       enable_chunked_prefill=bool(ek.get("enable_chunked_prefill", True)),
                       gpu_memory_utilization=float(ek.get("gpu_memory_utilization", 0.0)) if "max_num_seqs" not in ek else 0.0)
-    if cfg.parallel_size() > 1:
+    pp, tp = int(ek.get("pipeline_parallel_size", 1)), int(ek.get("tensor_parallel_size", 1))
+    if pp > 1:
+        from .tp_engine import build_pp_engine
+        return build_pp_engine(model, tok, args, cfg.model_id, pp, tp)         # ranks > 0: call engine.serve_forever()
+    if tp > 1:
         from .tp_engine import build_tp_engine
         return build_tp_engine(model, tok, args, model_name=cfg.model_id)     # ranks > 0: call engine.serve_forever()
     return LLMEngine(model, tok, args, model_name=cfg.model_id)

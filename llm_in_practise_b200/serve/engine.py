@@ -108,9 +108,11 @@ class EngineMetrics:
 
 
 class LLMEngine:
+    generator_cls = Generator            # serve/tp_engine.PipelineParallelEngine runs a pipeline stage instead
+
     def __init__(self, model, tokenizer=None, args: Optional[EngineArgs] = None, model_name: str = "b200-model"):
         self.args = args or EngineArgs()
-        self.gen = Generator(model, tokenizer, self.args.max_model_len)
+        self.gen = self.generator_cls(model, tokenizer, self.args.max_model_len)
         self.model, self.tokenizer, self.model_name = self.gen.model, tokenizer, model_name
         c = self.model.config
         self.device = self.model.embed_tokens.device

@@ -238,4 +238,7 @@ def build_app(engine: Optional[LLMEngine], prompt_style: str = "chatml", allow_s
 def serve(engine: LLMEngine, host: str = "0.0.0.0", port: int = 8000, **kw) -> None:
     import uvicorn
     engine.start()
-    uvicorn.run(build_app(engine, **kw), host=host, port=port)
+    try:
+        uvicorn.run(build_app(engine, **kw), host=host, port=port)
+    finally:
+        engine.shutdown()            # tensor- / pipeline-parallel engines: also releases the follower ranks

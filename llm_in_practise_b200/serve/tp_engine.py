@@ -18,6 +18,7 @@ from typing import Any, List, Optional
 import torch
 import torch.distributed as dist
 
+from ..parallel.pp import PipelineGenerator
 from .engine import EngineArgs, LLMEngine
 
 _CALLS = ("_prefill_packed", "_prefill", "_prefill_chunk", "decode_graphed", "copy_prefix", "set_block_row")
@@ -103,3 +104,20 @@ def build_tp_engine(model, tokenizer=None, args: Optional[EngineArgs] = None, mo
     from ..parallel.tp import shard_qwen3
     shard_qwen3(model, None, max_tokens=max_tokens)
     return TensorParallelEngine(model, tokenizer, args, model_name)
+
+
+class PipelineParallelEngine(TensorParallelEngine):
+    """The same SPMD engine over a ``stages x tp`` grid (``parallel/pp.py``): every rank runs its pipeline stage of each
+    announced call, the last stage's logits reach rank 0, which schedules and samples. This is what
+    ``engine_kwargs.pipeline_parallel_size`` of Deployment/Ray/serve_deploy_examples/qwen3_app_pipeline_parallel.yaml:21-31
+    builds."""
+    generator_cls = PipelineGenerator
+
+
+def build_pp_engine(model, tokenizer=None, args: Optional[EngineArgs] = None, model_name: str = "b200-model",
+                    pipeline_parallel_size: Optional[int] = None, tensor_parallel_size: int = 1,
+                    max_tokens: int = 8192) -> PipelineParallelEngine:
+    """Split ``model`` into pipeline stages (each optionally tensor-parallel) over the default process group."""
+    from ..parallel.pp import shard_qwen3_pipeline
+    shard_qwen3_pipeline(model, pipeline_parallel_size, tensor_parallel_size, max_tokens=max_tokens)
+    return PipelineParallelEngine(model, tokenizer, args, model_name)

@@ -63,7 +63,7 @@ def test_deploy_layer(tmp_path):
     apps = load_serve_yaml(str(y))
     cfg = apps[0]["llm_configs"][0]
     assert cfg.model_id == "qwen3" and cfg.autoscaling()["max_replicas"] == 4
-    assert cfg.parallel_size() == 2                         # TP 1 x PP 2 -> two tensor-parallel ranks on one node
+    assert cfg.parallel_size() == 2                         # TP 1 x PP 2 -> two ranks, one pipeline stage each
     try:
         cfg.validate()
         raise AssertionError("a 2-GPU replica must not start in a single process")
