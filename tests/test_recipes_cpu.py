@@ -135,3 +135,11 @@ def test_webui_path_with_a_stand_in_gradio(tmp_path, monkeypatch):
     frames = list(respond("hello", [("hi", "there")], 0.7, 0.9, 4))
     assert frames and frames[-1][0] == ("hi", "there") and frames[-1][-1][0] == "hello" and isinstance(frames[-1][-1][1], str)
     assert rec["clear"][0]() == []
+
+
+def test_serve_parallel_flags_need_matching_torchrun(capsys):
+    """``serve --tensor-parallel-size 2 --pipeline-parallel-size 2`` outside a 4-rank torchrun is refused with the launch line."""
+    from llm_in_practise_b200.recipes import infer
+    with pytest.raises(SystemExit):
+        infer.main(["serve", "--model", "qwen3-tiny", "--tensor-parallel-size", "2", "--pipeline-parallel-size", "2"])
+    assert "torchrun --nproc-per-node 4" in capsys.readouterr().err
