@@ -15,6 +15,12 @@
 * ``env``        device name, compute capability, CUDA / torch versions (HF_Basics/env_test.py)
 * ``loadtest``   the Locust profiles against an OpenAI-compatible endpoint (Deployment/Ray/scripts/locustfile*.py)
 * ``moderation`` the Llama-Guard moderation wrapper service (Deployment/litellm-proxy/llama-guard-wrapper/app.py)
+* ``preload``    mirror a model directory into the node-local cache behind a ``.ready`` marker
+                 (LLM_on_Kubernetes/Inference_Platfrom/02-Preloader/model-preloader-daemonset.yaml:44-78)
+* ``autoscale``  poll replicas' ``/metrics`` and print the replica count the KEDA ScaledObject would set
+                 (…/05-KEDA-AutoScale/keda-scaledobject.yaml:12-53)
+* ``canary``     run the canary steps and the Prometheus smoke analysis against a canary replica's ``/metrics``
+                 (…/09-Canary-Deployment/vllm-rollout.yaml:22-33, analysis-template.yaml:8-53)
 """
 from __future__ import annotations
 
@@ -79,8 +85,50 @@ def main(argv=None):
     ro.add_argument("--config", required=True, help="YAML in the reference's litellm-config-router-lb.yaml shape")
     ro.add_argument("--port", type=int, default=4000)
     ro.add_argument("--master-key", default=os.getenv("LITELLM_MASTER_KEY"))
+    pl = sub.add_parser("preload", help="model preloader (serve/platform.preload_model)")
+    pl.add_argument("--source", required=True)
+    pl.add_argument("--target", required=True)
+    pl.add_argument("--require", nargs="*", default=["config.json", "tokenizer.json"])
+    au = sub.add_parser("autoscale", help="KEDA scaling rule over /metrics endpoints (serve/platform.KedaScaler)")
+    au.add_argument("--config", default=None, help="ScaledObject YAML (default: configs/keda_scaledobject.yaml)")
+    au.add_argument("--metrics-url", nargs="+", required=True)
+    au.add_argument("--replicas", type=int, default=1, help="current replica count")
+    au.add_argument("--polls", type=int, default=0, help="stop after this many polls (0 = run until interrupted)")
+    ca = sub.add_parser("canary", help="canary steps + smoke analysis (serve/platform.CanaryRollout)")
+    ca.add_argument("--metrics-url", nargs="+", required=True, help="/metrics of the canary replicas (and of a GPU exporter)")
+    ca.add_argument("--interval", type=float, default=60.0)
     a = ap.parse_args(argv)
 
+    if a.cmd in ("autoscale", "canary"):
+        import time
+        import urllib.request
+        from ..serve import platform as P
+        scrape = lambda: [urllib.request.urlopen(u, timeout=5).read().decode() for u in a.metrics_url]
+        if a.cmd == "autoscale":
+            import yaml
+            path = a.config or os.path.join(os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "configs", "keda_scaledobject.yaml")
+            with open(path, encoding="utf-8") as f:
+                k = P.KedaScaler.from_scaled_object(yaml.safe_load(f))
+            n, i = a.replicas, 0
+            while True:
+                n = k.tick(n, scrape)
+                print(json.dumps({"replicas": n, "fallback": k.in_fallback, **k.last_values}), flush=True)
+                i += 1
+                if a.polls and i >= a.polls:
+                    return n
+                time.sleep(k.polling_interval_s)
+        ro_ = P.CanaryRollout()
+        while True:
+            ph = ro_.advance(lambda: scrape() + [P.gpu_memory_metrics_text()])
+            print(json.dumps({"step": ro_.index, "weight": ro_.weight, "phase": ph}), flush=True)
+            if ph != "Progressing":
+                return ph
+            time.sleep(a.interval)
+    if a.cmd == "preload":
+        from ..serve.platform import preload_model
+        rep = preload_model(a.source, a.target, a.require)
+        print(json.dumps(rep))
+        return rep
     if a.cmd == "env":
         print("torch", torch.__version__, "cuda", torch.version.cuda, "available", torch.cuda.is_available())
         if torch.cuda.is_available():

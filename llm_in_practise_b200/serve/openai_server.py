@@ -108,7 +108,10 @@ def render_metrics(engine: LLMEngine) -> str:
         out.extend(["# HELP vllm:request_success_total Count of successfully processed requests.",
                     "# TYPE vllm:request_success_total counter"])
         for reason, n in sorted(m.requests_finished.items()):
-            out.append(f'vllm:request_success_total{{model_name="{name}",finished_reason="{reason}"}} {n}')
+            if reason != "error":
+                out.append(f'vllm:request_success_total{{model_name="{name}",finished_reason="{reason}"}} {n}')
+        # the canary gate of the reference divides this by request_success_total (09-Canary-Deployment/analysis-template.yaml:24-37)
+        counter("vllm:request_failure_total", m.requests_finished.get("error", 0), "Count of requests that failed inside the engine.")
         out.extend(["# HELP vllm:time_to_first_token_seconds Histogram of time to first token in seconds.",
                     "# TYPE vllm:time_to_first_token_seconds histogram"])
         cum = 0

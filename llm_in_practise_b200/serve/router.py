@@ -32,7 +32,11 @@ from fastapi.responses import JSONResponse, PlainTextResponse
 
 Transport = Callable[[str, Dict[str, Any]], Awaitable[Tuple[int, Dict[str, Any]]]]
 
-STRATEGIES = ("simple-shuffle", "least-busy", "cost-based-routing", "latency-based-routing", "usage-based-routing")
+STRATEGIES = ("simple-shuffle", "least-busy", "cost-based-routing", "latency-based-routing", "usage-based-routing",
+              "prefix-aware", "load-aware-prefix")
+
+# llm-d's load score (LLM_on_Kubernetes/Inference_Platfrom/08-LLM-Router/llm-d/llm-d-config.yaml:19-23)
+LOAD_WEIGHTS = {"pending_requests": 0.4, "gpu_cache_usage": 0.3, "ttft_ms": 0.2, "queue_time_ms": 0.1}
 
 
 def http_transport(api_base: str, api_key: Optional[str] = None, timeout: float = 90.0) -> Transport:
@@ -47,6 +51,18 @@ def http_transport(api_base: str, api_key: Optional[str] = None, timeout: float 
         except Exception:
             return r.status_code, {"error": {"message": r.text[:500]}}
     return call
+
+
+def http_metrics(api_base: str, timeout: float = 3.0) -> Callable[[], Awaitable[str]]:
+    """``GET <server root>/metrics`` of an OpenAI-compatible endpoint whose ``api_base`` ends in ``/v1``."""
+    root = api_base.rstrip("/")
+    root = root[:-3] if root.endswith("/v1") else root
+
+    async def fetch() -> str:
+        import urllib.request
+        loop = asyncio.get_running_loop()
+        return await loop.run_in_executor(None, lambda: urllib.request.urlopen(root + "/metrics", timeout=timeout).read().decode())
+    return fetch
 
 
 @dataclass
@@ -71,6 +87,8 @@ class Deployment:
     _latencies: Deque[float] = field(default_factory=lambda: deque(maxlen=32))
     requests: int = 0
     failures: int = 0
+    metrics_fn: Optional[Callable[[], Awaitable[str]]] = None      # GET of the replica's /metrics (load-aware routing)
+    load: Dict[str, float] = field(default_factory=dict)           # last scraped load figures, keys of LOAD_WEIGHTS
 
     def _trim(self, now: float) -> None:
         while self._req_times and now - self._req_times[0] > 60.0:
@@ -118,6 +136,7 @@ class Router:
                  fallbacks: Optional[Sequence[Dict[str, List[str]]]] = None, default_fallbacks: Optional[List[str]] = None,
                  context_window_fallbacks: Optional[Sequence[Dict[str, Any]]] = None, enable_pre_call_checks: bool = False,
                  fallback_retries: bool = True, rate_limit_cooldown: float = 5.0, seed: Optional[int] = None,
+                 load_weights: Optional[Dict[str, float]] = None, prefix_weight: float = 0.5, prefix_chunk: int = 128,
                  clock: Callable[[], float] = time.monotonic, sleep: Callable[[float], Awaitable[None]] = asyncio.sleep):
         if routing_strategy not in STRATEGIES:
             raise ValueError(f"routing_strategy must be one of {STRATEGIES}")
@@ -141,6 +160,13 @@ class Router:
         self._rng = random.Random(seed)
         self._clock, self._sleep = clock, sleep
         self.fallback_events = 0
+        # the two cache-aware strategies of the reference's Kubernetes routers (vLLM production-stack ``prefixaware``,
+        # llm-d ``load_aware_prefix``): remember which deployment saw which prompt prefix
+        from .platform import PrefixIndex
+        self.prefix_index = PrefixIndex(prefix_chunk)
+        self.load_weights = dict(load_weights or LOAD_WEIGHTS)
+        self.prefix_weight = prefix_weight
+        self.prefix_routed = 0
 
     # ------------------------------------------------------------------ construction from the reference's YAML shape
     @classmethod
@@ -157,7 +183,8 @@ class Router:
                                    input_cost=float(lp.get("input_cost_per_token", 0.0)),
                                    output_cost=float(lp.get("output_cost_per_token", 0.0)),
                                    weight=float(entry.get("weight", lp.get("weight", 1.0))),
-                                   max_input_tokens=(entry.get("model_info") or {}).get("max_input_tokens")))
+                                   max_input_tokens=(entry.get("model_info") or {}).get("max_input_tokens"),
+                                   metrics_fn=(http_metrics(lp["api_base"]) if (transport_factory is None and lp.get("api_base")) else None)))
         rs = dict(cfg.get("router_settings", {}))
         ls = rs.pop("litellm_settings", None) or cfg.get("litellm_settings", {}) or {}
         kw = dict(routing_strategy=rs.get("routing_strategy", "simple-shuffle"), num_retries=int(rs.get("num_retries", 2)),
@@ -166,7 +193,7 @@ class Router:
                   default_fallbacks=rs.get("default_fallbacks"),
                   context_window_fallbacks=rs.get("context_window_fallbacks") or ls.get("context_window_fallbacks"),
                   enable_pre_call_checks=bool(rs.get("enable_pre_call_checks", False)),
-                  fallback_retries=bool(rs.get("fallback_retries", True)))
+                  fallback_retries=bool(rs.get("fallback_retries", True)), load_weights=cfg.get("load_weights"))
         kw.update(overrides)
         return cls(deps, **kw)
 
@@ -197,12 +224,42 @@ class Router:
             out.append(d)
         return out
 
-    def pick(self, name: str, tokens: int = 0, exclude: Sequence[Deployment] = ()) -> Optional[Deployment]:
+    def _load_score(self, d: Deployment, cands: Sequence[Deployment]) -> float:
+        """Weighted sum of the load figures, each scaled by the largest value among the candidates (0 = idle, 1 = the
+        busiest on every axis). Without a scrape, the router's own counters stand in for queue depth and latency."""
+        def fig(x: Deployment, k: str) -> float:
+            if k in x.load:
+                return float(x.load[k])
+            return {"pending_requests": float(x.in_flight), "ttft_ms": x.avg_latency() * 1000.0}.get(k, 0.0)
+        score = 0.0
+        for k, w in self.load_weights.items():
+            top = max(fig(x, k) for x in cands)
+            score += w * (fig(d, k) / top if top > 0 else 0.0)
+        return score
+
+    def pick(self, name: str, tokens: int = 0, exclude: Sequence[Deployment] = (), prompt: Optional[str] = None) -> Optional[Deployment]:
         """One deployment of group ``name`` under the configured strategy, or None when none is available."""
         cands = self._available(name, tokens, exclude)
         if not cands:
             return None
         now = self._clock()
+        if self.strategy in ("prefix-aware", "load-aware-prefix"):
+            text = prompt or ""
+            hit = {id(d): self.prefix_index.match(d.api_base or id(d), text) for d in cands}
+            if self.strategy == "prefix-aware":
+                # the replica holding the longest cached prefix of this prompt; nobody has one -> the least busy replica
+                key = lambda d: (-hit[id(d)], d.in_flight)
+            else:
+                frac = {k: (v / len(text) if text else 0.0) for k, v in hit.items()}
+                key = lambda d: (round(self._load_score(d, cands) - self.prefix_weight * frac[id(d)], 9), d.in_flight)
+            best = min(key(d) for d in cands)
+            ties = [d for d in cands if key(d) == best]
+            d = ties[0] if len(ties) == 1 else self._rng.choice(ties)
+            if hit[id(d)] > 0:
+                self.prefix_routed += 1
+            if text:
+                self.prefix_index.insert(d.api_base or id(d), text)
+            return d
         if self.strategy == "simple-shuffle":
             return self._rng.choices(cands, weights=[max(d.weight, 1e-9) for d in cands], k=1)[0]
         if self.strategy == "least-busy":
@@ -245,10 +302,14 @@ class Router:
         """-> (status, json, context_window_error). Retries inside the group, moving to another deployment after a failure."""
         tried: List[Deployment] = []
         fixed = retries is not None
+        prompt = None
+        if self.strategy in ("prefix-aware", "load-aware-prefix"):
+            from .platform import prompt_text
+            prompt = prompt_text(body)
         attempt, budget = 0, (retries if fixed else self.num_retries)
         last: Tuple[int, Dict[str, Any]] = (503, {"error": {"message": f"no healthy deployment for model '{name}'"}})
         while attempt <= budget:
-            d = self.pick(name, tokens, exclude=tried) or self.pick(name, tokens)
+            d = self.pick(name, tokens, exclude=tried, prompt=prompt) or self.pick(name, tokens, prompt=prompt)
             if d is None:
                 return last[0], last[1], False
             payload = dict(body, model=d.upstream_model)
@@ -330,6 +391,23 @@ class Router:
         return {"healthy_endpoints": healthy, "unhealthy_endpoints": unhealthy, "healthy_count": len(healthy),
                 "unhealthy_count": len(unhealthy)}
 
+    async def refresh_load(self) -> None:
+        """Scrape every deployment that has a ``metrics_fn`` and keep the four figures llm-d weighs: queue depth, KV-cache
+        usage, mean time to first token and (its stand-in here) mean queueing share of the end-to-end latency."""
+        from .platform import metric_sum, parse_prometheus_text
+        for d in self.deployments:
+            if d.metrics_fn is None:
+                continue
+            try:
+                s = parse_prometheus_text(await d.metrics_fn())
+            except Exception:
+                continue
+            n = metric_sum(s, "vllm:time_to_first_token_seconds_count")
+            ttft = metric_sum(s, "vllm:time_to_first_token_seconds_sum") / n * 1000.0 if n else 0.0
+            d.load = {"pending_requests": metric_sum(s, "vllm:num_requests_waiting"),
+                      "gpu_cache_usage": metric_sum(s, "vllm:gpu_cache_usage_perc"), "ttft_ms": ttft,
+                      "queue_time_ms": metric_sum(s, "vllm:request_queue_time_seconds_sum") / n * 1000.0 if n else 0.0}
+
     def metrics_text(self) -> str:
         lines = ["# TYPE router_deployment_requests_total counter", "# TYPE router_deployment_failures_total counter",
                  "# TYPE router_deployment_in_flight gauge", "# TYPE router_deployment_cooldown gauge"]
@@ -339,7 +417,8 @@ class Router:
             lines += [f"router_deployment_requests_total{lab} {d.requests}", f"router_deployment_failures_total{lab} {d.failures}",
                       f"router_deployment_in_flight{lab} {d.in_flight}",
                       f"router_deployment_cooldown{lab} {1 if now < d.cooldown_until or not d.healthy else 0}"]
-        lines += ["# TYPE router_fallbacks_total counter", f"router_fallbacks_total {self.fallback_events}"]
+        lines += ["# TYPE router_fallbacks_total counter", f"router_fallbacks_total {self.fallback_events}",
+                  "# TYPE router_prefix_routed_total counter", f"router_prefix_routed_total {self.prefix_routed}"]
         return "\n".join(lines) + "\n"
 
 
@@ -354,6 +433,7 @@ def build_router_app(router: Router, health_check_interval: float = 0.0, master_
             async def loop():
                 while True:
                     await router.health_check()
+                    await router.refresh_load()
                     await asyncio.sleep(health_check_interval)
             task = asyncio.create_task(loop())
         yield
