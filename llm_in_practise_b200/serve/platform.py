@@ -568,3 +568,41 @@ def prompt_text(body: Dict[str, Any]) -> str:
         return "\n".join(f"{m.get('role', '')}:{m.get('content', '')}" for m in body.get("messages") or [] if isinstance(m, dict))
     p = body.get("prompt", "")
     return p if isinstance(p, str) else "\n".join(str(x) for x in p)
+
+
+# ------------------------------------------------------------------------------------------- KEDA acting on replicas
+def keda_replica_set(factory: Callable[[], Any], scaler: KedaScaler, clock: Callable[[], float] = time.monotonic):
+    """A replica set of in-process engines whose size follows ``scaler`` (the ScaledObject's rule) instead of the Ray Serve
+    rule: every ``polling_interval_s`` the live engines' own ``/metrics`` text is scraped, ``KedaScaler.tick`` decides, new
+    replicas come from ``factory()``, surplus ones leave the rotation, drain and shut down
+    (``serve/deploy.AutoscalingReplicaSet`` does the starting / draining)."""
+    from .deploy import AutoscalingReplicaSet
+    from .openai_server import render_metrics
+
+    class KedaReplicaSet(AutoscalingReplicaSet):
+        def __init__(self):
+            super().__init__(factory, {"min_replicas": scaler.min_replicas, "max_replicas": scaler.max_replicas}, clock)
+            self.scaler, self._next_poll = scaler, clock()
+
+        def tick(self) -> int:
+            now = self._clock()
+            for e in list(self.draining):
+                if e.num_running + e.num_waiting == 0:
+                    self.draining.remove(e)
+                    if hasattr(e, "shutdown"):
+                        e.shutdown()
+                    self.events.append((now, "stopped", len(self.engines)))
+            if now < self._next_poll:
+                return len(self.engines)
+            self._next_poll = now + self.scaler.polling_interval_s
+            want = self.scaler.tick(len(self.engines), lambda: [render_metrics(e) for e in self.engines])
+            while len(self.engines) < want:
+                self.engines.append(self.factory())
+                self.events.append((now, "up", len(self.engines)))
+            while len(self.engines) > max(want, 1):
+                loads = self.ongoing()
+                self.draining.append(self.engines.pop(loads.index(min(loads))))
+                self.events.append((now, "down", len(self.engines)))
+            return len(self.engines)
+
+    return KedaReplicaSet()

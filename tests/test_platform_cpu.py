@@ -323,3 +323,36 @@ def test_rules_read_the_engines_own_metrics():
     assert 0 < p99 <= 10.0
     run = P.CanaryAnalysis([mt for mt in P.smoke_template() if mt.name != "gpu-memory-saturation"])
     assert run.measure(hist) == "Running" and run.results["error-rate"][0][1] == "Successful"
+
+
+def test_keda_replica_set_starts_and_drains_engines():
+    import torch
+    from llm_in_practise_b200.data.tokenizers import ByteTokenizer
+    from llm_in_practise_b200.inference import GenerationConfig
+    from llm_in_practise_b200.models.qwen3 import QWEN3_PRESETS, Qwen3ForCausalLM
+    from llm_in_practise_b200.serve import EngineArgs, LLMEngine
+    torch.manual_seed(0)
+    m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32, device="cpu")
+    made = []
+
+    def factory():
+        made.append(LLMEngine(m, ByteTokenizer(), EngineArgs(max_num_seqs=2, max_model_len=64, warmup=False), model_name=f"r{len(made)}"))
+        return made[-1]
+    clk = Clock()
+    scaler = P.KedaScaler([P.queue_depth_trigger(2.0)], 1, 3, P.ScalePolicy(0.0, 4, 15.0), P.ScalePolicy(30.0, 1, 15.0), clock=clk)
+    rs = P.keda_replica_set(factory, scaler, clk)
+    assert len(rs.engines) == 1
+    cfg = GenerationConfig(max_new_tokens=2, do_sample=False)
+    reqs = [rs.engines[0].submit([1, 2, 3], cfg) for _ in range(6)]          # six waiting -> ceil(6 / 2) = 3 replicas
+    assert rs.tick() == 3 and len(made) == 3
+    assert rs.tick() == 3                                                    # inside the polling interval: no new decision
+    reqs.append(rs.submit([4, 5, 6], cfg))                                   # routed to one of the new, idle replicas
+    assert made[0].num_waiting == 6 and made[1].num_waiting + made[2].num_waiting == 1
+    for e in made:
+        while e.num_waiting or e.num_running:
+            e.step()
+    assert all(r.done.is_set() for r in reqs)
+    for _ in range(6):                                                       # the lull outlasts the 30 s scale-down window
+        clk.t += 15
+        rs.tick()
+    assert len(rs.engines) == 1 and [ev[1] for ev in rs.events].count("stopped") == 2
