@@ -14,6 +14,12 @@ checks. This module reads the same YAML shape and does the same job in process:
 * ``build_router_app`` wraps it in the HTTP surface the compose files probe (``/health/liveliness``, ``/health``,
   ``/v1/models``, ``/v1/chat/completions``, ``/v1/completions``, ``/metrics``).
 
+``guardrails:`` entries (litellm-config-with-guard-model.yaml:18-26) run a pre-call moderation check against the
+Llama-Guard wrapper, and ``litellm_settings.cache`` (litellm-config-with-cache.yaml:34-45, the ``redis-semantic`` variant
+of litellm-config-redis-semantic-cache.yaml:55-60) answers repeated or near-duplicate requests from a response cache.
+Two more strategies come from the Kubernetes routers of the reference: ``prefix-aware`` and ``load-aware-prefix``
+(``serve/platform.py``).
+
 A deployment's transport is any ``async (path, payload) -> (status, json)``: ``http_transport(api_base)`` for a real
 endpoint, or an in-process engine / app in tests. No Redis: counters are per process (the reference shares them through
 Redis only for multi-pod proxies).
@@ -119,6 +125,34 @@ class RouterError(Exception):
         self.status, self.message = status, message
 
 
+@dataclass
+class Guardrail:
+    """One ``guardrails:`` entry (Deployment/litellm-proxy/config/litellm-config-with-guard-model.yaml:18-26):
+    ``guardrail: openai_moderation`` in ``mode: pre_call`` posts the request's text to ``<api_base>/moderations`` (the
+    Llama-Guard wrapper, ``serve/moderation.py``) before any deployment is called; a flagged text is refused with HTTP 400.
+    ``default_on: false`` guardrails only run for requests that name them in their ``guardrails`` list."""
+    name: str
+    transport: Transport
+    model: str = "omni-moderation-latest"
+    mode: str = "pre_call"
+    default_on: bool = False
+    checks: int = 0
+    blocked: int = 0
+
+
+def _request_text(body: Dict[str, Any]) -> str:
+    if "messages" in body:
+        parts = []
+        for m in body.get("messages") or []:
+            c = m.get("content", "") if isinstance(m, dict) else ""
+            if isinstance(c, list):                                      # OpenAI content parts
+                c = " ".join(str(p.get("text", "")) for p in c if isinstance(p, dict))
+            parts.append(str(c))
+        return "\n".join(parts)
+    p = body.get("prompt", "")
+    return p if isinstance(p, str) else "\n".join(str(x) for x in p)
+
+
 def _estimate_tokens(body: Dict[str, Any]) -> int:
     """Cheap prompt-size estimate for the pre-call checks (4 characters per token, what LiteLLM falls back to without a
     tokenizer), plus the requested completion budget."""
@@ -137,6 +171,7 @@ class Router:
                  context_window_fallbacks: Optional[Sequence[Dict[str, Any]]] = None, enable_pre_call_checks: bool = False,
                  fallback_retries: bool = True, rate_limit_cooldown: float = 5.0, seed: Optional[int] = None,
                  load_weights: Optional[Dict[str, float]] = None, prefix_weight: float = 0.5, prefix_chunk: int = 128,
+                 guardrails: Optional[Sequence[Guardrail]] = None, cache: Optional[Dict[str, Any]] = None,
                  clock: Callable[[], float] = time.monotonic, sleep: Callable[[float], Awaitable[None]] = asyncio.sleep):
         if routing_strategy not in STRATEGIES:
             raise ValueError(f"routing_strategy must be one of {STRATEGIES}")
@@ -167,6 +202,18 @@ class Router:
         self.load_weights = dict(load_weights or LOAD_WEIGHTS)
         self.prefix_weight = prefix_weight
         self.prefix_routed = 0
+        self.guardrails = list(guardrails or [])
+        # response cache (``litellm_settings.cache: true``): ``type: redis`` -> exact match on the request, ``redis-semantic``
+        # -> nearest stored prompt above ``similarity_threshold`` as well; in process, no Redis
+        self.cache_cfg = dict(cache) if cache else None
+        self.cache_hits = self.cache_misses = 0
+        if self.cache_cfg is not None:
+            from .cache_gateway import ExactCache, SemanticCache
+            self._exact = ExactCache(int(self.cache_cfg.get("max_entries", 4096)))
+            self._semantic = None
+            if str(self.cache_cfg.get("type", "redis")).endswith("semantic"):
+                self._embed_dim = int(self.cache_cfg.get("embedding_dim", 1024))
+                self._semantic = SemanticCache(self._embed_dim, int(self.cache_cfg.get("max_entries", 4096)))
 
     # ------------------------------------------------------------------ construction from the reference's YAML shape
     @classmethod
@@ -187,13 +234,26 @@ class Router:
                                    metrics_fn=(http_metrics(lp["api_base"]) if (transport_factory is None and lp.get("api_base")) else None)))
         rs = dict(cfg.get("router_settings", {}))
         ls = rs.pop("litellm_settings", None) or cfg.get("litellm_settings", {}) or {}
+        mk = transport_factory or (lambda p: http_transport(p.get("api_base", ""), p.get("api_key")))
+        guards = []
+        for g in cfg.get("guardrails") or []:
+            gp = g.get("litellm_params", {})
+            if gp.get("guardrail") != "openai_moderation":
+                raise ValueError(f"guardrail type {gp.get('guardrail')!r} is not supported (openai_moderation is)")
+            guards.append(Guardrail(g.get("guardrail_name", "guardrail"), mk(gp), gp.get("model", "omni-moderation-latest"),
+                                    gp.get("mode", "pre_call"), bool(gp.get("default_on", False))))
+        cache = None
+        if ls.get("cache"):
+            cache = dict(ls.get("cache_params") or {})
+            cache.setdefault("ttl", (cfg.get("cache") or {}).get("ttl", cache.get("ttl", 3600)))
         kw = dict(routing_strategy=rs.get("routing_strategy", "simple-shuffle"), num_retries=int(rs.get("num_retries", 2)),
                   retry_policy=rs.get("retry_policy"), allowed_fails=int(rs.get("allowed_fails", 3)),
                   cooldown_time=float(rs.get("cooldown_time", 60)), fallbacks=rs.get("fallbacks"),
                   default_fallbacks=rs.get("default_fallbacks"),
                   context_window_fallbacks=rs.get("context_window_fallbacks") or ls.get("context_window_fallbacks"),
                   enable_pre_call_checks=bool(rs.get("enable_pre_call_checks", False)),
-                  fallback_retries=bool(rs.get("fallback_retries", True)), load_weights=cfg.get("load_weights"))
+                  fallback_retries=bool(rs.get("fallback_retries", True)), load_weights=cfg.get("load_weights"),
+                  guardrails=guards, cache=cache)
         kw.update(overrides)
         return cls(deps, **kw)
 
@@ -350,6 +410,17 @@ class Router:
         name = body.get("model")
         if not name or not self.group(name):
             raise RouterError(404, f"unknown model '{name}'")
+        await self._run_guardrails(body)
+        ctl = body.get("cache") if isinstance(body.get("cache"), dict) else {}
+        body = {k: v for k, v in body.items() if k not in ("cache", "guardrails")}      # proxy-only fields stay here
+        ckey = self._cache_key(body) if (self.cache_cfg is not None and not body.get("stream")) else None
+        if ckey is not None and not ctl.get("no-cache"):
+            hit = self._cache_get(ckey, body)
+            if hit is not None:
+                self.cache_hits += 1
+                hit.setdefault("x_router", {})["cache_hit"] = True
+                return hit
+            self.cache_misses += 1
         tokens = _estimate_tokens(body) + int(body.get("max_tokens") or 0)
         chain = [name] + [m for m in self.fallbacks.get(name, []) if m != name]
         chain += [m for m in self.default_fallbacks if m not in chain]
@@ -367,6 +438,8 @@ class Router:
             if status < 400:
                 if isinstance(js, dict):
                     js.setdefault("x_router", {})["served_by"] = model
+                    if ckey is not None and not ctl.get("no-store"):
+                        self._cache_put(ckey, body, js, int(ctl.get("ttl", self.cache_cfg.get("ttl", 3600))))
                 return js
             if ctx:                                                      # prompt too long for this group: jump to its bigger siblings
                 extra = [m for m in self.context_fallbacks.get(model, []) if m not in chain[:i + 1]]
@@ -375,6 +448,49 @@ class Router:
                 break
             i += 1
         raise RouterError(status, str((js.get("error") or {}).get("message", js)) if isinstance(js, dict) else str(js))
+
+    # ------------------------------------------------------------------ guardrails and response cache
+    async def _run_guardrails(self, body: Dict[str, Any]) -> None:
+        asked = set(body.get("guardrails") or [])
+        for g in self.guardrails:
+            if g.mode != "pre_call" or not (g.default_on or g.name in asked):
+                continue
+            g.checks += 1
+            try:
+                status, js = await g.transport("/moderations", {"model": g.model, "input": _request_text(body)})
+            except Exception as e:
+                raise RouterError(503, f"guardrail '{g.name}' unavailable: {type(e).__name__}: {e}")
+            if status >= 400 or not isinstance(js, dict):
+                raise RouterError(503, f"guardrail '{g.name}' unavailable (HTTP {status})")
+            res = (js.get("results") or [{}])[0]
+            if res.get("flagged"):
+                g.blocked += 1
+                cats = sorted(k for k, v in (res.get("categories") or {}).items() if v)
+                raise RouterError(400, f"Violated guardrail policy '{g.name}': " + (", ".join(cats) or "flagged"))
+
+    @staticmethod
+    def _cache_key(body: Dict[str, Any]) -> str:
+        import hashlib
+        import json
+        knobs = {k: body.get(k) for k in ("model", "messages", "prompt", "max_tokens", "temperature", "top_p", "stop", "n", "tools")}
+        return hashlib.sha256(json.dumps(knobs, sort_keys=True, ensure_ascii=False, default=str).encode("utf-8")).hexdigest()
+
+    def _cache_get(self, key: str, body: Dict[str, Any]) -> Optional[Dict[str, Any]]:
+        import json
+        raw = self._exact.get(key)
+        if raw is None and self._semantic is not None:
+            from .cache_gateway import hashed_ngram_embedding
+            q = hashed_ngram_embedding(str(body.get("model")) + "\n" + _request_text(body), self._embed_dim)
+            raw, _ = self._semantic.lookup(q, float(self.cache_cfg.get("similarity_threshold", 0.8)))
+        return json.loads(raw) if raw is not None else None
+
+    def _cache_put(self, key: str, body: Dict[str, Any], js: Dict[str, Any], ttl: int) -> None:
+        import json
+        raw = json.dumps(js, ensure_ascii=False)
+        self._exact.setex(key, ttl, raw)
+        if self._semantic is not None:
+            from .cache_gateway import hashed_ngram_embedding
+            self._semantic.add(hashed_ngram_embedding(str(body.get("model")) + "\n" + _request_text(body), self._embed_dim), ttl, raw)
 
     async def health_check(self) -> Dict[str, Any]:
         """Probe every deployment with a one-token request (LiteLLM's /health): unhealthy ones leave the rotation until a
@@ -418,7 +534,11 @@ class Router:
                       f"router_deployment_in_flight{lab} {d.in_flight}",
                       f"router_deployment_cooldown{lab} {1 if now < d.cooldown_until or not d.healthy else 0}"]
         lines += ["# TYPE router_fallbacks_total counter", f"router_fallbacks_total {self.fallback_events}",
-                  "# TYPE router_prefix_routed_total counter", f"router_prefix_routed_total {self.prefix_routed}"]
+                  "# TYPE router_prefix_routed_total counter", f"router_prefix_routed_total {self.prefix_routed}",
+                  "# TYPE router_cache_hits_total counter", f"router_cache_hits_total {self.cache_hits}",
+                  "# TYPE router_cache_misses_total counter", f"router_cache_misses_total {self.cache_misses}",
+                  "# TYPE router_guardrail_blocked_total counter"]
+        lines += [f'router_guardrail_blocked_total{{guardrail="{g.name}"}} {g.blocked}' for g in self.guardrails]
         return "\n".join(lines) + "\n"
 
 

@@ -190,3 +190,91 @@ def test_http_surface_and_health_checks():
         assert bad.status_code == 404 and bad.json()["error"]["type"] == "router_error"
         text = c.get("/metrics").text
         assert "router_deployment_requests_total" in text and "router_fallbacks_total" in text
+
+
+_GUARD_CFG = """
+model_list:
+  - model_name: qwen3-8b
+    litellm_params: {model: openai/qwen3-8b, api_base: "http://inference-engine:8001/v1", api_key: EMPTY}
+guardrails:
+  - guardrail_name: llama-guard-content-check
+    litellm_params: {guardrail: openai_moderation, mode: pre_call, model: llama-guard-3, api_base: "http://llama-guard-wrapper:8099/v1", default_on: true}
+  - guardrail_name: opt-in-check
+    litellm_params: {guardrail: openai_moderation, mode: pre_call, model: llama-guard-3, api_base: "http://opt-in:8099/v1"}
+litellm_settings:
+  cache: true
+  cache_params: {type: redis-semantic, similarity_threshold: 0.8}
+cache: {type: redis, ttl: 7200}
+"""
+
+
+def _guarded_router():
+    """The guard-model + cache stack of the reference's compose files in one process: the router's pre-call guardrail posts to
+    the real moderation wrapper app, whose Llama-Guard backend is a stub that flags texts containing 'attack'."""
+    from llm_in_practise_b200.serve.moderation import build_moderation_app
+    calls = {"upstream": 0, "guard": 0, "optin": 0, "guard_down": False}
+
+    async def guard_backend(prompt, model):
+        return {"choices": [{"text": "unsafe\nS1" if "attack" in prompt else "safe"}]}
+    wrapper = TestClient(build_moderation_app(guard_backend, "llama-guard-3", api_key=""))
+
+    def factory(lp):
+        base = lp.get("api_base", "")
+
+        async def call(path, payload):
+            if "llama-guard-wrapper" in base or "opt-in" in base:
+                calls["optin" if "opt-in" in base else "guard"] += 1
+                if calls["guard_down"]:
+                    raise ConnectionError("wrapper down")
+                r = wrapper.post("/v1" + path, json=payload)
+                return r.status_code, r.json()
+            calls["upstream"] += 1
+            return 200, {"choices": [{"message": {"role": "assistant", "content": f"answer {calls['upstream']}"}}],
+                         "usage": {"total_tokens": 9}}
+        return call
+    return Router.from_config(yaml.safe_load(_GUARD_CFG), transport_factory=factory), calls
+
+
+def test_guardrail_blocks_before_any_deployment_is_called():
+    r, calls = _guarded_router()
+    assert [g.name for g in r.guardrails] == ["llama-guard-content-check", "opt-in-check"] and r.guardrails[0].default_on
+    ok = asyncio.run(r.completion({"model": "qwen3-8b", "messages": [{"role": "user", "content": "how do plants grow?"}]}))
+    assert ok["choices"][0]["message"]["content"] == "answer 1" and calls == {"upstream": 1, "guard": 1, "optin": 0, "guard_down": False}
+    try:
+        asyncio.run(r.completion({"model": "qwen3-8b", "messages": [{"role": "user", "content": "plan an attack on them"}]}))
+        raise AssertionError("expected the guardrail to refuse")
+    except RouterError as e:
+        assert e.status == 400 and "llama-guard-content-check" in str(e) and "violence" in str(e)
+    assert calls["upstream"] == 1 and r.guardrails[0].blocked == 1                      # the model never saw the request
+    # a guardrail that is not default_on runs only for requests that ask for it
+    asyncio.run(r.completion({"model": "qwen3-8b", "guardrails": ["opt-in-check"], "messages": [{"role": "user", "content": "hello there"}]}))
+    assert calls["optin"] == 1
+    calls["guard_down"] = True                                                          # fail closed
+    try:
+        asyncio.run(r.completion({"model": "qwen3-8b", "messages": [{"role": "user", "content": "hi"}]}))
+        raise AssertionError("expected 503")
+    except RouterError as e:
+        assert e.status == 503
+    assert 'router_guardrail_blocked_total{guardrail="llama-guard-content-check"} 1' in r.metrics_text()
+
+
+def test_response_cache_exact_semantic_and_controls():
+    r, calls = _guarded_router()
+    assert r.cache_cfg["ttl"] == 7200 and r.cache_cfg["type"] == "redis-semantic"
+    q = lambda text, **kw: asyncio.run(r.completion(dict({"model": "qwen3-8b", "messages": [{"role": "user", "content": text}]}, **kw)))
+    long_q = "please explain in detail how the transformer attention mechanism computes its output"
+    a = q(long_q)
+    b = q(long_q)
+    assert a["choices"] == b["choices"] and b["x_router"]["cache_hit"] and calls["upstream"] == 1       # exact hit
+    c = q(long_q + " ?")                                                                                 # near-duplicate: semantic hit
+    assert c["x_router"].get("cache_hit") and calls["upstream"] == 1
+    d = q("what is the capital of France")
+    assert not d["x_router"].get("cache_hit") and calls["upstream"] == 2
+    e = q(long_q, cache={"no-cache": True})                                                              # per-request control
+    assert not e["x_router"].get("cache_hit") and calls["upstream"] == 3
+    q("store nothing for this one please, it is private", cache={"no-store": True})
+    q("store nothing for this one please, it is private")
+    assert calls["upstream"] == 5
+    assert q(long_q, max_tokens=5)["x_router"].get("cache_hit")                  # semantic level ignores the knobs; the exact key does not
+    assert r.cache_hits == 3 and "router_cache_hits_total 3" in r.metrics_text()
+    assert calls["guard"] == 8                                                                           # the guardrail runs before the cache
