@@ -68,8 +68,19 @@ def main(argv=None):
     ap.add_argument("--top_p", type=float, default=0.95)
     ap.add_argument("--host", default="0.0.0.0")
     ap.add_argument("--port", type=int, default=8000)
-    ap.add_argument("--max_model_len", type=int, default=4096)
-    ap.add_argument("--max_num_seqs", type=int, default=16)
+    ap.add_argument("--max_model_len", "--max-model-len", dest="max_model_len", type=int, default=4096)
+    ap.add_argument("--max_num_seqs", "--max-num-seqs", dest="max_num_seqs", type=int, default=None)
+    # the vLLM server flags the reference's compose files and manifests pass (Deployment/Basics-02/docker-compose.yml:56-65,
+    # LLM_on_Kubernetes/Inference_Platfrom/06-GPU-Timeslicing/vllm-statefulset.yaml:65-82)
+    ap.add_argument("--gpu-memory-utilization", "--gpu_memory_utilization", dest="gpu_mem", type=float, default=0.0,
+                    help="serve: size the KV pool from this share of HBM when --max-num-seqs is not given")
+    ap.add_argument("--enable-prefix-caching", dest="prefix_caching", action=argparse.BooleanOptionalAction, default=True)
+    ap.add_argument("--enable-chunked-prefill", dest="chunked_prefill", action=argparse.BooleanOptionalAction, default=True)
+    ap.add_argument("--served-model-name", dest="served_name", default=None)
+    ap.add_argument("--quantization", default=None, choices=["awq", "gptq", "compressed-tensors", "bitsandbytes"],
+                    help="serve: awq / gptq / compressed-tensors checkpoints are detected from their config; bitsandbytes "
+                         "quantises a 16-bit checkpoint to NF4 while loading")
+    ap.add_argument("--enforce-eager", dest="enforce_eager", action="store_true", help="serve: no CUDA-graph warm-up at start")
     ap.add_argument("--prompt_style", default="chatml", choices=["chatml", "deepseek"])
     ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float16"])
     ap.add_argument("--tensor-parallel-size", "--tensor_parallel_size", dest="tp", type=int, default=1,
@@ -86,6 +97,12 @@ def main(argv=None):
             ap.error(f"--tensor-parallel-size x --pipeline-parallel-size = {a.tp * a.pp} needs `serve` under "
                      f"`torchrun --nproc-per-node {a.tp * a.pp}` (this run has {info.world_size} rank(s))")
     model, tok = _load(a.model, a.adapter, dtype)
+    if a.quantization == "bitsandbytes":
+        getattr(model, "base_model", model).quantize_nf4(True)
+    elif a.quantization is not None:
+        from ..quant import detect_quant_format
+        if not (os.path.isdir(a.model) and detect_quant_format(a.model)):
+            ap.error(f"--quantization {a.quantization}: {a.model} is not a quantised checkpoint (no quantization_config found)")
     dev = getattr(model, "base_model", model).embed_tokens.device
     eos = [t for t in (getattr(tok, "eos_token_id", None),) if t is not None]
     gen = Generator(model, tok, a.max_model_len)
@@ -151,8 +168,10 @@ def main(argv=None):
     elif a.cmd == "serve":
         from ..serve import EngineArgs, LLMEngine
         from ..serve.openai_server import serve
-        eargs = EngineArgs(max_num_seqs=a.max_num_seqs, max_model_len=a.max_model_len, block_size=a.block_size)
-        name = os.path.basename(a.model.rstrip("/"))
+        eargs = EngineArgs(max_num_seqs=a.max_num_seqs or 16, max_model_len=a.max_model_len, block_size=a.block_size,
+                           enable_prefix_caching=a.prefix_caching, enable_chunked_prefill=a.chunked_prefill,
+                           gpu_memory_utilization=(a.gpu_mem if a.max_num_seqs is None else 0.0), warmup=not a.enforce_eager)
+        name = a.served_name or os.path.basename(a.model.rstrip("/"))
         if a.tp * a.pp > 1:
             # SPMD: rank 0 schedules and answers HTTP, the others repeat its model calls on their shard / stage
             from ..serve.tp_engine import build_pp_engine, build_tp_engine

@@ -143,3 +143,23 @@ def test_serve_parallel_flags_need_matching_torchrun(capsys):
     with pytest.raises(SystemExit):
         infer.main(["serve", "--model", "qwen3-tiny", "--tensor-parallel-size", "2", "--pipeline-parallel-size", "2"])
     assert "torchrun --nproc-per-node 4" in capsys.readouterr().err
+
+
+def test_serve_accepts_the_vllm_flags_of_the_compose_files(monkeypatch):
+    """``vllm serve``'s flags as the reference passes them map onto EngineArgs; ``--quantization bitsandbytes`` quantises at load."""
+    from llm_in_practise_b200.recipes import infer
+    from llm_in_practise_b200.serve import openai_server
+    got = {}
+    monkeypatch.setattr(openai_server, "serve", lambda eng, host, port, **kw: got.update(eng=eng, host=host, port=port, kw=kw))
+    infer.main(["serve", "--model", "qwen3-tiny", "--quantization", "bitsandbytes", "--no-enable-prefix-caching", "--max-num-seqs", "3",
+                "--max-model-len", "128", "--served-model-name", "tiny-nf4", "--block-size", "16", "--enforce-eager",
+                "--gpu-memory-utilization", "0.9", "--port", "8123"])
+    eng = got["eng"]
+    a = eng.args
+    assert (a.max_num_seqs, a.max_model_len, a.block_size, a.enable_prefix_caching, a.enable_chunked_prefill, a.warmup) == \
+        (3, 128, 16, False, True, False)
+    assert a.gpu_memory_utilization == 0.0                # an explicit --max-num-seqs wins over the memory share
+    assert eng.model_name == "tiny-nf4" and eng.paged and got["port"] == 8123
+    assert eng.model.layers[0].qkv_proj.nf4 is not None   # the decoder projections were quantised to NF4
+    with pytest.raises(SystemExit):
+        infer.main(["serve", "--model", "qwen3-tiny", "--quantization", "awq"])          # not an AWQ checkpoint
