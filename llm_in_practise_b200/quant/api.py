@@ -27,7 +27,7 @@ from ..models.qwen3 import Qwen3ForCausalLM
 from ..ops import elementwise as ew
 from ..ops.linear import FusedLinear
 from .algorithms import ActivationStats, awq_search_scale, gptq_quantize
-from .formats import (W4Weight, from_compressed_tensors, from_gptq, pack_codes, quantize_rtn, to_compressed_tensors,
+from .formats import (W4Weight, from_awq, from_compressed_tensors, from_gptq, pack_codes, quantize_rtn, to_compressed_tensors,
                       to_gptq)
 
 

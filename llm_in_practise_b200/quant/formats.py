@@ -13,6 +13,11 @@ Readers / writers (bit layouts reconstructed from the formats' public descriptio
   ``weight_packed`` int32 [N, K/8] (nibbles along K, LSB first, values offset by 8 when symmetric),
   ``weight_scale`` [N, K/g], ``weight_zero_point`` int32 [N/8, K/g] (asymmetric only, nibbles along N),
   ``weight_shape`` [2]; ``quantization_config`` inside ``config.json``.
+* AutoAWQ ``gemm`` (the published ``Qwen3-*-AWQ`` checkpoints the serving recipes load with ``quantization: awq``,
+  Deployment/Ray/serve_deploy_examples/qwen3_app_minimal.yaml:9-13): ``qweight`` int32 [K, N/8] and ``qzeros`` int32
+  [K/g, N/8] — eight OUTPUT columns per word, nibble i holding column ``8*b + (0,2,4,6,1,3,5,7)[i]`` — ``scales`` fp16
+  [K/g, N]; ``w = (q - zero) * scale`` with no zero offset; ``quantization_config`` {quant_method awq, bits 4,
+  group_size 128, zero_point true, version gemm}.
 """
 from __future__ import annotations
 
@@ -134,6 +139,41 @@ def from_gptq(t: Dict[str, torch.Tensor], group: int = 128, zero_offset: int = 1
     q = _unpack_int32(qw, 0).t().contiguous()                # [N, K]
     z = ((_unpack_int32(qz, 1).to(torch.int32) + zero_offset) & 15).t().contiguous().float()   # [N, K/g]
     s = sc.t().contiguous().float()
+    return W4Weight(pack_codes(q), s.reshape(-1), (z * s).reshape(-1), N, K, group, INT4_LUT.to(qw.device))
+
+
+# ------------------------------------------------------------------------------------------------
+# AutoAWQ (gemm)
+# ------------------------------------------------------------------------------------------------
+_AWQ_ORDER = (0, 2, 4, 6, 1, 3, 5, 7)        # nibble i of a word holds column 8 * block + _AWQ_ORDER[i]
+
+
+def _awq_unpack(v: torch.Tensor) -> torch.Tensor:
+    """int32 [R, N/8] -> uint8 [R, N] in natural column order."""
+    x = _unpack_int32(v, 1)                                  # column 8 * b + i = nibble i of word b
+    R = x.shape[0]
+    out = torch.empty_like(x).view(R, -1, 8)
+    out[:, :, list(_AWQ_ORDER)] = x.view(R, -1, 8)
+    return out.view(R, -1)
+
+
+def _awq_pack(x: torch.Tensor) -> torch.Tensor:
+    R = x.shape[0]
+    return _pack_int32(x.view(R, -1, 8)[:, :, list(_AWQ_ORDER)].reshape(R, -1), 1)
+
+
+def to_awq(w: W4Weight) -> Dict[str, torch.Tensor]:
+    return {"qweight": _awq_pack(w.codes().t().contiguous()),                    # [K, N/8]
+            "qzeros": _awq_pack(w.zero_points().t().contiguous()),               # [K/g, N/8]
+            "scales": w.scale.view(w.N, -1).t().contiguous().to(torch.float16)}  # [K/g, N]
+
+
+def from_awq(t: Dict[str, torch.Tensor], group: int = 128) -> W4Weight:
+    qw, sc = t["qweight"], t["scales"]
+    K, N = qw.shape[0], qw.shape[1] * 8
+    q = _awq_unpack(qw).t().contiguous()                     # [N, K]
+    s = sc.t().contiguous().float()                          # [N, K/g]
+    z = _awq_unpack(t["qzeros"]).t().contiguous().float() if "qzeros" in t else torch.full_like(s, 8.0)
     return W4Weight(pack_codes(q), s.reshape(-1), (z * s).reshape(-1), N, K, group, INT4_LUT.to(qw.device))
 
 

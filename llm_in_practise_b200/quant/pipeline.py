@@ -17,8 +17,8 @@ from ..models.qwen3 import Qwen3ForCausalLM
 from ..ops import elementwise as ew
 from .algorithms import ActivationStats, gptq_quantize
 from .api import AWQModifier, GPTQModifier, QuantizeConfig, _awq_fold_layer, _Modifier, tokenize_calibration
-from .formats import (W4Weight, from_compressed_tensors, from_gptq, pack_codes, quantize_rtn, to_compressed_tensors,
-                      to_gptq)
+from .formats import (W4Weight, from_awq, from_compressed_tensors, from_gptq, pack_codes, quantize_rtn, to_awq,
+                      to_compressed_tensors, to_gptq)
 
 _PARTS = (("qkv_proj", ("q", "k", "v")), ("o_proj", ("o",)), ("gate_up_proj", ("gate", "up")), ("down_proj", ("down",)))
 
@@ -87,8 +87,11 @@ def _cat_rows(parts: List[W4Weight]) -> W4Weight:
 
 
 def save_quantized(model: Qwen3ForCausalLM, out_dir: str, fmt: str = "gptq", tokenizer=None) -> None:
-    """fmt: ``gptq`` (qweight/qzeros/scales/g_idx + quantize_config.json) or ``compressed-tensors``
-    (weight_packed/weight_scale/weight_zero_point/weight_shape + quantization_config in config.json)."""
+    """fmt: ``gptq`` (qweight/qzeros/scales/g_idx + quantize_config.json), ``compressed-tensors``
+    (weight_packed/weight_scale/weight_zero_point/weight_shape + quantization_config in config.json) or ``awq`` (AutoAWQ
+    gemm layout: qweight/qzeros/scales, the form of the published ``*-AWQ`` checkpoints)."""
+    if fmt not in ("gptq", "compressed-tensors", "awq"):
+        raise ValueError(f"unknown checkpoint format {fmt!r}")
     qc: QuantizeConfig = getattr(model, "quant_config", QuantizeConfig())
     os.makedirs(out_dir, exist_ok=True)
     dt = model.embed_tokens.dtype
@@ -107,7 +110,7 @@ def save_quantized(model: Qwen3ForCausalLM, out_dir: str, fmt: str = "gptq", tok
             for p, size in zip(parts, lin.part_sizes):
                 if isinstance(lin.nf4, W4Weight):
                     sub = _split_rows(lin.nf4, off, off + size)
-                    tensors = to_gptq(sub) if fmt == "gptq" else to_compressed_tensors(sub, qc.sym)
+                    tensors = to_gptq(sub) if fmt == "gptq" else to_awq(sub) if fmt == "awq" else to_compressed_tensors(sub, qc.sym)
                     for tn, tv in tensors.items():
                         sd[f"{n[p]}.{tn}"] = tv
                 else:
@@ -123,6 +126,9 @@ def save_quantized(model: Qwen3ForCausalLM, out_dir: str, fmt: str = "gptq", tok
         cfg["quantization_config"] = qd
         with open(os.path.join(out_dir, "quantize_config.json"), "w") as f:
             json.dump(qd, f, indent=2)
+    elif fmt == "awq":
+        cfg["quantization_config"] = {"quant_method": "awq", "bits": 4, "group_size": qc.group_size, "zero_point": True,
+                                      "version": "gemm", "modules_to_not_convert": None}
     else:
         cfg["quantization_config"] = {
             "quant_method": "compressed-tensors", "format": "pack-quantized", "ignore": ["lm_head"],
@@ -139,12 +145,12 @@ def detect_quant_format(path: str) -> Optional[str]:
         q = json.load(f).get("quantization_config")
     if q is None:
         return "gptq" if os.path.exists(os.path.join(path, "quantize_config.json")) else None
-    return {"gptq": "gptq", "compressed-tensors": "compressed-tensors"}.get(q.get("quant_method"))
+    return {"gptq": "gptq", "compressed-tensors": "compressed-tensors", "awq": "awq"}.get(q.get("quant_method"))
 
 
 @torch.no_grad()
 def load_quantized(path: str, dtype=torch.bfloat16, device=None) -> Qwen3ForCausalLM:
-    """Read a GPTQ or compressed-tensors W4A16 checkpoint; the sub-projections of each fused linear are re-joined
+    """Read a GPTQ, AutoAWQ or compressed-tensors W4A16 checkpoint; the sub-projections of each fused linear are re-joined
     into one kernel-layout ``W4Weight`` (row concatenation — scales are per output row, so nothing is requantised)."""
     fmt = detect_quant_format(path)
     if fmt is None:
@@ -158,6 +164,10 @@ def load_quantized(path: str, dtype=torch.bfloat16, device=None) -> Qwen3ForCaus
         group, sym = qd.get("group_size", 128), qd.get("sym", True)
         if qd.get("desc_act"):
             raise NotImplementedError("desc_act=True checkpoints are not supported")
+    elif fmt == "awq":
+        group, sym = qd.get("group_size", qd.get("q_group_size", 128)), not qd.get("zero_point", True)
+        if int(qd.get("bits", qd.get("w_bit", 4))) != 4 or str(qd.get("version", "gemm")).lower() != "gemm":
+            raise NotImplementedError("AutoAWQ checkpoints are read in the 4-bit 'gemm' layout only")
     else:
         wq = next(iter(qd["config_groups"].values()))["weights"]
         group, sym = wq.get("group_size", 128), wq.get("symmetric", True)
@@ -168,8 +178,9 @@ def load_quantized(path: str, dtype=torch.bfloat16, device=None) -> Qwen3ForCaus
     put(model.norm, "model.norm.weight")
     if model.lm_head is not None:
         put(model.lm_head, "lm_head.weight" if sh.has("lm_head.weight") else "model.embed_tokens.weight")
-    keys = ("qweight", "qzeros", "scales", "g_idx") if fmt == "gptq" else \
-        ("weight_packed", "weight_scale", "weight_zero_point", "weight_shape")
+    keys = {"gptq": ("qweight", "qzeros", "scales", "g_idx"), "awq": ("qweight", "qzeros", "scales")}.get(
+        fmt, ("weight_packed", "weight_scale", "weight_zero_point", "weight_shape"))
+    read = {"gptq": from_gptq, "awq": from_awq}.get(fmt, from_compressed_tensors)
     for i, layer in enumerate(model.layers):
         n = hf_names(i)
         put(layer.input_layernorm, n["ln1"])
@@ -184,7 +195,7 @@ def load_quantized(path: str, dtype=torch.bfloat16, device=None) -> Qwen3ForCaus
             for p in parts:
                 if sh.has(f"{n[p]}.{keys[0]}"):
                     t = {k: sh.get(f"{n[p]}.{k}").to(device) for k in keys if sh.has(f"{n[p]}.{k}")}
-                    subs.append(from_gptq(t, group) if fmt == "gptq" else from_compressed_tensors(t, group))
+                    subs.append(read(t, group))
                 else:                                     # an ignored (dense) projection inside a fused group
                     subs.append(sh.get(n[p] + ".weight").to(device, dtype))
             if all(isinstance(s, W4Weight) for s in subs):
