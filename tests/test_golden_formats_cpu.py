@@ -177,3 +177,22 @@ def test_peft_adapter_is_what_vllm_and_transformers_expect(tmp_path):
         seen.add((module.rsplit(".", 1)[-1], is_a))
     assert seen == {(p, a) for p in ("q_proj", "v_proj", "down_proj") for a in (True, False)}
     assert len(sd) == cfg.num_hidden_layers * 3 * 2
+
+
+def test_nf4_codebook_equals_its_definition():
+    """The 16 NF4 levels are not free parameters: QLoRA defines them as normal quantiles (8 on the positive side, 7 on the
+    negative, plus an exact zero) scaled to [-1, 1]. Recomputing them with scipy gives the table the kernels use."""
+    stats = pytest.importorskip("scipy.stats")
+    import numpy as np
+    from llm_in_practise_b200.ops.w4 import NF4_CODE, create_dynamic_map
+    offset = 0.9677083                                                    # the probability mass cut-off of the construction
+    pos = stats.norm.ppf(np.linspace(offset, 0.5, 9)[:-1])
+    neg = -stats.norm.ppf(np.linspace(offset, 0.5, 8)[:-1])
+    levels = np.sort(np.concatenate([pos, [0.0], neg]))
+    levels /= levels.max()
+    assert levels.shape == (16,) and np.abs(levels - NF4_CODE.numpy()).max() < 5e-7
+    # the 8-bit dynamic code of the nested absmax / 8-bit Adam state: 256 sorted levels in [-1, 1] with exact 0 and 1
+    for signed in (True, False):
+        code = create_dynamic_map(signed=signed)
+        assert code.numel() == 256 and bool((code[1:] >= code[:-1]).all()) and float(code.max()) == 1.0
+        assert 0.0 in code.tolist() and (float(code.min()) < 0) == signed
