@@ -232,6 +232,37 @@ class Generator:
             cache.k[li][dst, :, :n] = cache.k[li][src, :, :n]
             cache.v[li][dst, :, :n] = cache.v[li][src, :, :n]
 
+    # -- host tier of the prefix cache (serve/engine.py, ``kv_offload_gb``): generator methods so that tensor- / pipeline-parallel
+    #    followers keep their own slice of every off-loaded row under the same key
+    @torch.no_grad()
+    def offload_row(self, cache: KVCache, slot: int, n: int, key: int) -> None:
+        """K/V of the first ``n`` positions of sequence ``slot`` (every local layer) -> pinned host memory under ``key``."""
+        store = self.__dict__.setdefault("_host_kv", {})
+        ks, vs = [], []
+        for li in range(len(cache.k)):
+            k, v = cache.seq_view(li, slot, n)
+            for src, dst in ((k, ks), (v, vs)):
+                h = torch.empty((src.shape[0], n, src.shape[2]), dtype=src.dtype, device="cpu", pin_memory=src.is_cuda)
+                h.copy_(src[:, :n], non_blocking=src.is_cuda)
+                dst.append(h)
+        if cache.k[0].is_cuda:
+            torch.cuda.current_stream().synchronize()          # the row is about to be overwritten by its next owner
+        store[key] = (ks, vs)
+
+    @torch.no_grad()
+    def restore_row(self, cache: KVCache, key: int, slot: int, n: int) -> None:
+        """The first ``n`` positions stored under ``key`` -> sequence ``slot`` (its blocks are already allocated)."""
+        ks, vs = self._host_kv[key]
+        dev = cache.k[0].device
+        rows = torch.full((n,), slot, dtype=torch.long, device=dev)
+        pos = torch.arange(n, dtype=torch.long, device=dev)
+        for li in range(len(cache.k)):
+            cache.store(li, rows, pos, ks[li][:, :n].to(dev, non_blocking=True).transpose(0, 1),
+                        vs[li][:, :n].to(dev, non_blocking=True).transpose(0, 1))
+
+    def drop_host_row(self, key: int) -> None:
+        self.__dict__.get("_host_kv", {}).pop(key, None)
+
     @torch.no_grad()
     def set_block_row(self, cache: KVCache, slot: int, blocks) -> None:
         """Paged cache: logical -> physical block list of sequence ``slot``. A generator method so that tensor-parallel

@@ -80,6 +80,8 @@ def main(argv=None):
     ap.add_argument("--quantization", default=None, choices=["awq", "gptq", "compressed-tensors", "bitsandbytes"],
                     help="serve: awq / gptq / compressed-tensors checkpoints are detected from their config; bitsandbytes "
                          "quantises a 16-bit checkpoint to NF4 while loading")
+    ap.add_argument("--kv-offloading-size", "--kv-offload-gb", dest="kv_offload_gb", type=float, default=0.0,
+                    help="serve: GiB of pinned host memory for cached prefixes that lose their HBM row (LMCache-style tier)")
     ap.add_argument("--enforce-eager", dest="enforce_eager", action="store_true", help="serve: no CUDA-graph warm-up at start")
     ap.add_argument("--prompt_style", default="chatml", choices=["chatml", "deepseek"])
     ap.add_argument("--dtype", default="bfloat16", choices=["bfloat16", "float16"])
@@ -170,7 +172,8 @@ def main(argv=None):
         from ..serve.openai_server import serve
         eargs = EngineArgs(max_num_seqs=a.max_num_seqs or 16, max_model_len=a.max_model_len, block_size=a.block_size,
                            enable_prefix_caching=a.prefix_caching, enable_chunked_prefill=a.chunked_prefill,
-                           gpu_memory_utilization=(a.gpu_mem if a.max_num_seqs is None else 0.0), warmup=not a.enforce_eager)
+                           gpu_memory_utilization=(a.gpu_mem if a.max_num_seqs is None else 0.0), warmup=not a.enforce_eager,
+                           kv_offload_gb=a.kv_offload_gb)
         name = a.served_name or os.path.basename(a.model.rstrip("/"))
         if a.tp * a.pp > 1:
             # SPMD: rank 0 schedules and answers HTTP, the others repeat its model calls on their shard / stage

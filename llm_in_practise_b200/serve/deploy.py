@@ -166,7 +166,8 @@ def build_engine(cfg: LLMConfig, device=None):
     args = EngineArgs(max_num_seqs=int(ek.get("max_num_seqs", 16)), max_model_len=int(ek.get("max_model_len", 4096)),
                       enable_prefix_caching=bool(ek.get("enable_prefix_caching", True)),
                       enable_chunked_prefill=bool(ek.get("enable_chunked_prefill", True)),
-                      gpu_memory_utilization=float(ek.get("gpu_memory_utilization", 0.0)) if "max_num_seqs" not in ek else 0.0)
+                      gpu_memory_utilization=float(ek.get("gpu_memory_utilization", 0.0)) if "max_num_seqs" not in ek else 0.0,
+                      block_size=int(ek.get("block_size", 0)), kv_offload_gb=float(ek.get("kv_offloading_size", 0.0)))
     pp, tp = int(ek.get("pipeline_parallel_size", 1)), int(ek.get("tensor_parallel_size", 1))
     if pp > 1:
         from .tp_engine import build_pp_engine

@@ -22,7 +22,7 @@ import threading
 import time
 from collections import OrderedDict, deque
 from dataclasses import dataclass, field
-from typing import Deque, Dict, Iterator, List, Optional, Sequence
+from typing import Deque, Dict, Iterator, List, Optional, Sequence, Tuple
 
 import torch
 
@@ -47,6 +47,10 @@ class EngineArgs:
     # between sequences with a common prompt prefix. num_kv_blocks 0 = the capacity the slot pool would have had.
     block_size: int = 0
     num_kv_blocks: int = 0
+    # host tier of the prefix cache (the LMCache stage of the reference's platform, LLM_on_Kubernetes/Inference_Platfrom/
+    # 07-L1-Cache/LMCache): > 0 keeps the K/V of cached prefixes that lose their HBM row in this many GB of pinned host
+    # memory (LRU) and copies them back on a later prefix hit instead of recomputing the prompt
+    kv_offload_gb: float = 0.0
 
 
 @dataclass
@@ -96,6 +100,8 @@ class EngineMetrics:
         self.steps = 0
         self.prefix_queries = 0          # prompt tokens looked up in the prefix cache (vllm:gpu_prefix_cache_queries)
         self.prefix_hits = 0             # ... and found there                        (vllm:gpu_prefix_cache_hits)
+        self.host_hits = 0               # prompt tokens restored from the host tier instead of being recomputed
+        self.host_offloads = 0           # rows copied to the host tier
 
     def observe_ttft(self, v: float) -> None:
         with self.lock:
@@ -151,6 +157,13 @@ class LLMEngine:
         self._prefix_index: Dict[int, int] = {}                           # hash(tokens[:k * block]) -> slot
         self._row_tokens: Dict[int, List[int]] = {}                       # slot -> tokens with valid K/V (cached or running rows)
         self.metrics = EngineMetrics()
+        # host tier: key -> (tokens whose K/V the entry holds, bytes); block-prefix hash -> key
+        self._host_rows: "OrderedDict[int, Tuple[List[int], int]]" = OrderedDict()
+        self._host_index: Dict[int, int] = {}
+        self._host_bytes, self._host_budget = 0, int(self.args.kv_offload_gb * 2 ** 30)
+        self._host_keys = itertools.count()
+        self._host_pin = -1
+        self._kv_token_bytes = 2 * c.num_hidden_layers * c.num_key_value_heads * c.head_dim * self.model.embed_tokens.element_size()
         self._ids = itertools.count()
         self._cv = threading.Condition()
         self._stop = False
@@ -289,6 +302,7 @@ class LLMEngine:
                 return
             if slot != keep:
                 del self._cached[slot]
+                self._offload(slot)
                 self._unindex_row(slot)
                 self._drop_blocks(slot)
                 self.free.append(slot)
@@ -384,11 +398,61 @@ class LLMEngine:
         for slot in self._cached:
             if slot != keep:
                 del self._cached[slot]
+                self._offload(slot)
                 self._unindex_row(slot)
                 if self.paged:
                     self._drop_blocks(slot)
                 return slot
         return -1
+
+    # ------------------------------------------------------------------ host tier of the prefix cache (kv_offload_gb)
+    def _drop_host(self, key: int) -> None:
+        toks, nbytes = self._host_rows.pop(key)
+        self._host_bytes -= nbytes
+        for _, h in self._block_hashes(toks, len(toks)):
+            if self._host_index.get(h) == key:
+                del self._host_index[h]
+        self.gen.drop_host_row(key)
+
+    def _offload(self, slot: int) -> None:
+        """A cached row is about to lose its HBM: keep its whole-block prefix in host memory (least recently used out)."""
+        if self._host_budget <= 0:
+            return
+        toks = self._row_tokens.get(slot)
+        B = self.args.prefix_block
+        n = (len(toks) // B * B) if toks else 0
+        nbytes = n * self._kv_token_bytes
+        if n < B or nbytes > self._host_budget:
+            return
+        hashes = list(self._block_hashes(toks, n))
+        if hashes[-1][1] in self._host_index:                 # the host tier already holds this prefix (or a longer one)
+            self._host_rows.move_to_end(self._host_index[hashes[-1][1]])
+            return
+        while self._host_bytes + nbytes > self._host_budget:
+            victim = next((k for k in self._host_rows if k != self._host_pin), None)
+            if victim is None:
+                return
+            self._drop_host(victim)
+        key = next(self._host_keys)
+        self.gen.offload_row(self.cache, slot, n, key)
+        self._host_rows[key] = (list(toks[:n]), nbytes)
+        self._host_bytes += nbytes
+        for _, h in hashes:
+            self._host_index[h] = key
+        with self.metrics.lock:
+            self.metrics.host_offloads += 1
+
+    def _lookup_host(self, prompt: List[int]):
+        """Longest block-prefix of ``prompt`` the host tier holds (leaving one token to compute): (key, n) or (-1, 0)."""
+        best = (-1, 0)
+        if not self._host_rows:
+            return best
+        for n, h in self._block_hashes(prompt, len(prompt) - 1):
+            key = self._host_index.get(h)
+            if key is None or self._host_rows[key][0][:n] != prompt[:n]:
+                break
+            best = (key, n)
+        return best
 
     def _slots_available(self) -> int:
         return len(self.free) + len(self._cached)
@@ -537,13 +601,34 @@ class LLMEngine:
                 r = self.waiting[0]
                 L = len(r.prompt_ids)
                 src, P = self._lookup_prefix(r.prompt_ids) if self.args.enable_prefix_caching else (-1, 0)
-                piecewise = P > 0 or (L > budget and self.args.enable_chunked_prefill and not batch)
+                hkey, Ph = self._lookup_host(r.prompt_ids) if self.args.enable_prefix_caching else (-1, 0)
+                from_host = Ph > P                            # the host tier knows a longer prefix than any HBM row
+                piecewise = P > 0 or from_host or (L > budget and self.args.enable_chunked_prefill and not batch)
                 if not piecewise and batch and L > budget:
                     break
                 self.waiting.popleft()
             with self.metrics.lock:
                 self.metrics.prefix_queries += L
-                self.metrics.prefix_hits += P
+                self.metrics.prefix_hits += max(P, Ph) if from_host else P
+                self.metrics.host_hits += Ph if from_host else 0
+            if from_host:
+                self._host_pin = hkey                         # taking a slot may off-load another row: not at this entry's cost
+                self._host_rows.move_to_end(hkey)
+                r.slot = self._take_slot()
+                self._host_pin = -1
+                if self.paged:
+                    if not self._admit_blocks(r):
+                        self.free.append(r.slot)
+                        r.slot = -1
+                        with self._cv:
+                            self.waiting.appendleft(r)
+                        break
+                    self._grow(r, Ph)
+                self.gen.restore_row(self.cache, hkey, r.slot, Ph)
+                r.prefilled = r.cached_tokens = Ph
+                self.prefilling.append(r)
+                budget -= self._prefill_piece(r, budget)
+                continue
             if not piecewise:
                 r.slot = self._take_slot()
                 if self.paged:

@@ -105,6 +105,8 @@ def render_metrics(engine: LLMEngine) -> str:
         counter("vllm:generation_tokens_total", m.generation_tokens, "Number of generation tokens processed.")
         counter("vllm:gpu_prefix_cache_queries_total", m.prefix_queries, "Prompt tokens looked up in the prefix cache.")
         counter("vllm:gpu_prefix_cache_hits_total", m.prefix_hits, "Prompt tokens served from the prefix cache.")
+        counter("b200:host_prefix_cache_hits_total", m.host_hits, "Prompt tokens restored from the host tier of the prefix cache.")
+        counter("b200:host_kv_offloads_total", m.host_offloads, "Cached rows copied to the host tier when they lost their HBM.")
         out.extend(["# HELP vllm:request_success_total Count of successfully processed requests.",
                     "# TYPE vllm:request_success_total counter"])
         for reason, n in sorted(m.requests_finished.items()):

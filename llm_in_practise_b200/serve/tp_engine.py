@@ -21,7 +21,8 @@ import torch.distributed as dist
 from ..parallel.pp import PipelineGenerator
 from .engine import EngineArgs, LLMEngine
 
-_CALLS = ("_prefill_packed", "_prefill", "_prefill_chunk", "decode_graphed", "copy_prefix", "set_block_row")
+_CALLS = ("_prefill_packed", "_prefill", "_prefill_chunk", "decode_graphed", "copy_prefix", "set_block_row",
+          "offload_row", "restore_row", "drop_host_row")
 
 
 def _to_wire(x: Any) -> Any:

@@ -343,3 +343,48 @@ def test_paged_pool_rejects_or_caps_requests_it_can_never_hold(model):
     assert r.cfg.max_new_tokens == 48 - 8 - 20
     _drain(eng, [r])
     assert len(r.output_ids) == 20 and r.finish_reason == "length" and eng._reserved == 0
+
+
+@pytest.mark.parametrize("block_size", [0, 16])
+def test_host_tier_restores_an_evicted_prefix(model, block_size):
+    """kv_offload_gb: a cached prefix that loses its HBM row goes to host memory; a later prompt with that prefix gets it copied
+    back (cached_tokens counts it, only the suffix is computed) and generates exactly what a cold engine generates."""
+    torch.manual_seed(11)
+    system = torch.randint(0, 300, (48,)).tolist()
+    others = [torch.randint(0, 300, (40,)).tolist() for _ in range(3)]
+    first, again = system + [7, 8, 9], system + [21, 22]
+    g = Generator(model, max_len=96)
+    cfg = GenerationConfig(max_new_tokens=4, do_sample=False)
+    want = {tuple(p): g.generate(torch.tensor([p]), max_new_tokens=4, do_sample=False)[0, len(p):].tolist() for p in [first, again] + others}
+    eng = LLMEngine(model, None, EngineArgs(max_num_seqs=2, max_model_len=96, block_size=block_size, kv_offload_gb=0.01, warmup=False))
+
+    def run(p):
+        r = eng.submit(p, cfg)
+        while not r.done.is_set():
+            eng.step()
+        assert r.output_ids == want[tuple(p)]
+        return r
+    run(first)
+    for p in others:                                            # two rows only: the system prompt's row is recycled
+        run(p)
+    assert eng.metrics.host_offloads >= 1 and eng._lookup_prefix(again) == (-1, 0)
+    key, n = eng._lookup_host(again)
+    assert key >= 0 and n == 48
+    r = run(again)
+    assert r.cached_tokens == 48 and eng.metrics.host_hits == 48
+    # budget: the tier holds at most kv_offload_gb of rows and forgets the least recently used ones
+    assert eng._host_bytes <= eng._host_budget and eng._host_bytes == sum(b for _, b in eng._host_rows.values())
+    tiny = LLMEngine(model, None, EngineArgs(max_num_seqs=1, max_model_len=96, block_size=block_size, warmup=False,
+                                             kv_offload_gb=(48 * eng._kv_token_bytes + 64) / 2 ** 30))       # room for one 48-token row
+    for p in [first] + others:
+        r = tiny.submit(p, cfg)
+        while not r.done.is_set():
+            tiny.step()
+    assert len(tiny._host_rows) == 1 and tiny._lookup_host(again) == (-1, 0)      # the system prompt was the oldest entry
+    assert set(tiny.gen._host_kv) == set(tiny._host_rows)                         # dropped entries free their host memory
+    off = LLMEngine(model, None, EngineArgs(max_num_seqs=1, max_model_len=96, warmup=False))
+    for p in (first, others[0]):
+        r = off.submit(p, cfg)
+        while not r.done.is_set():
+            off.step()
+    assert off.metrics.host_offloads == 0 and not off._host_rows                  # off by default

@@ -81,3 +81,37 @@ def test_tp2_serving_engine_matches_single_process(tmp_path, block_size):
     want = [g.generate(torch.tensor([p]), max_new_tokens=4, do_sample=False)[0, len(p):].tolist() for p in got["prompts"]]
     assert got["out"] == want
     assert max(got["cached"]) == 32            # the third prompt reused the first one's prefix
+
+
+def _offload_worker(rank, world, tmp):
+    """Host tier of the prefix cache under tensor parallelism: every rank keeps its own kv-head slice of an off-loaded row."""
+    from llm_in_practise_b200.inference import GenerationConfig
+    from llm_in_practise_b200.parallel.dist import setup_distributed
+    from llm_in_practise_b200.serve import EngineArgs
+    from llm_in_practise_b200.serve.tp_engine import build_tp_engine
+    setup_distributed()
+    eng = build_tp_engine(_model("dense"), None, EngineArgs(max_num_seqs=1, max_model_len=96, warmup=False, kv_offload_gb=0.01))
+    if rank != 0:
+        eng.serve_forever()
+        assert len(eng.gen._host_kv) >= 1 and next(iter(eng.gen._host_kv.values()))[0][0].shape[0] == 1     # one local kv head
+        return
+    torch.manual_seed(4)
+    shared = torch.randint(0, 256, (32,)).tolist()
+    prompts = [shared + [5, 6, 7], torch.randint(0, 256, (40,)).tolist(), shared + [9]]
+    outs, cached = [], []
+    for p in prompts:                                  # one row: each prompt evicts the previous one's
+        r = eng.generate([p], GenerationConfig(max_new_tokens=4, do_sample=False))[0]
+        outs.append(r.output_ids)
+        cached.append(r.cached_tokens)
+    torch.save({"out": outs, "cached": cached, "prompts": prompts, "host_hits": eng.metrics.host_hits}, f"{tmp}/offload.pt")
+    eng.shutdown()
+
+
+def test_tp2_host_tier_restores_prefix_on_every_rank(tmp_path):
+    from llm_in_practise_b200.inference import Generator
+    run_distributed(_offload_worker, 2, (str(tmp_path),))
+    got = torch.load(tmp_path / "offload.pt")
+    g = Generator(_model("dense"), max_len=96)
+    want = [g.generate(torch.tensor([p]), max_new_tokens=4, do_sample=False)[0, len(p):].tolist() for p in got["prompts"]]
+    assert got["out"] == want
+    assert got["cached"] == [0, 0, 32] and got["host_hits"] == 32
