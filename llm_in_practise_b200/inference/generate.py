@@ -43,6 +43,7 @@ class GenerationConfig:
     repetition_penalty: float = 1.0
     eos_token_id: Optional[Sequence[int]] = None
     pad_token_id: int = 0
+    ignore_eos: bool = False             # vLLM's sampling parameter: generate max_new_tokens whatever is sampled (benchmarks)
 
 
 def sample_next(logits: torch.Tensor, cfg: GenerationConfig, prev: Optional[torch.Tensor] = None,
@@ -495,7 +496,7 @@ class Generator:
                  seed: Optional[int] = None, return_logprobs: bool = False, **kw):
         cfg = config or GenerationConfig(**{k: v for k, v in kw.items() if k in GenerationConfig.__dataclass_fields__})
         eos = cfg.eos_token_id
-        eos = [eos] if isinstance(eos, int) else list(eos or [])
+        eos = [] if cfg.ignore_eos else ([eos] if isinstance(eos, int) else list(eos or []))
         was = self.model.training
         self.model.eval()
         B, S = input_ids.shape

@@ -15,6 +15,8 @@
 * ``env``        device name, compute capability, CUDA / torch versions (HF_Basics/env_test.py)
 * ``loadtest``   the Locust profiles against an OpenAI-compatible endpoint (Deployment/Ray/scripts/locustfile*.py)
 * ``moderation`` the Llama-Guard moderation wrapper service (Deployment/litellm-proxy/llama-guard-wrapper/app.py)
+* ``bench-serve`` the HTTP serving benchmark with ``vllm bench serve``'s flags and result keys (serve/bench_client.py;
+                 LLM_on_Kubernetes/Inference_Platfrom/README.md:1361-1375)
 * ``preload``    mirror a model directory into the node-local cache behind a ``.ready`` marker
                  (LLM_on_Kubernetes/Inference_Platfrom/02-Preloader/model-preloader-daemonset.yaml:44-78)
 * ``autoscale``  poll replicas' ``/metrics`` and print the replica count the KEDA ScaledObject would set
@@ -85,6 +87,8 @@ def main(argv=None):
     ro.add_argument("--config", required=True, help="YAML in the reference's litellm-config-router-lb.yaml shape")
     ro.add_argument("--port", type=int, default=4000)
     ro.add_argument("--master-key", default=os.getenv("LITELLM_MASTER_KEY"))
+    bs = sub.add_parser("bench-serve", help="HTTP serving benchmark (serve/bench_client.py)")
+    bs.add_argument("rest", nargs=argparse.REMAINDER)
     pl = sub.add_parser("preload", help="model preloader (serve/platform.preload_model)")
     pl.add_argument("--source", required=True)
     pl.add_argument("--target", required=True)
@@ -124,6 +128,9 @@ def main(argv=None):
             if ph != "Progressing":
                 return ph
             time.sleep(a.interval)
+    if a.cmd == "bench-serve":
+        from ..serve.bench_client import main as bench_main
+        return bench_main(a.rest)
     if a.cmd == "preload":
         from ..serve.platform import preload_model
         rep = preload_model(a.source, a.target, a.require)

@@ -500,6 +500,8 @@ class LLMEngine:
                 self._row_tokens.clear()
 
     def _eos(self, cfg: GenerationConfig) -> List[int]:
+        if cfg.ignore_eos:
+            return []
         e = cfg.eos_token_id
         if e is None:
             t = getattr(self.tokenizer, "eos_token_id", None)

@@ -44,6 +44,8 @@ class ChatCompletionRequest(BaseModel):
     top_k: Optional[int] = 0
     repetition_penalty: Optional[float] = 1.0
     stop: Optional[Union[str, List[str]]] = None    # vLLM / OpenAI stop strings (not in the reference's FastAPI schema)
+    ignore_eos: Optional[bool] = False              # vLLM extension (``vllm bench serve --ignore-eos``)
+    stream_options: Optional[Dict[str, Any]] = None  # {"include_usage": true}: one more chunk with the token counts
 
 
 class CompletionRequest(BaseModel):
@@ -54,6 +56,8 @@ class CompletionRequest(BaseModel):
     max_tokens: Optional[int] = 16
     stream: Optional[bool] = False
     stop: Optional[Union[str, List[str]]] = None
+    ignore_eos: Optional[bool] = False
+    stream_options: Optional[Dict[str, Any]] = None
 
 
 def deepseek_prompt_from_messages(messages: List[ChatMessage]) -> str:
@@ -144,11 +148,15 @@ def build_app(engine: Optional[LLMEngine], prompt_style: str = "chatml", allow_s
         except TypeError:
             return eng.tokenizer.decode(ids)
 
-    def gen_cfg(temperature, top_p, max_tokens, top_k=0, rep=1.0) -> GenerationConfig:
+    def gen_cfg(temperature, top_p, max_tokens, top_k=0, rep=1.0, ignore_eos=False) -> GenerationConfig:
         t = 0.0 if temperature is None else float(temperature)
         return GenerationConfig(max_new_tokens=int(max_tokens or 16), do_sample=t > 0.0, temperature=max(t, 1e-5),
                                 top_p=1.0 if top_p is None else float(top_p), top_k=int(top_k or 0),
-                                repetition_penalty=float(rep or 1.0))
+                                repetition_penalty=float(rep or 1.0), ignore_eos=bool(ignore_eos))
+
+    def usage_chunk(head, n_p, n_c) -> str:
+        return "data: " + json.dumps({**head, "choices": [], "usage": {"prompt_tokens": n_p, "completion_tokens": n_c,
+                                                                       "total_tokens": n_p + n_c}}) + "\n\n"
 
     @app.get("/health")
     @app.get("/healthz")
@@ -174,7 +182,7 @@ def build_app(engine: Optional[LLMEngine], prompt_style: str = "chatml", allow_s
         prompt = render(req.messages)
         ids = eng.tokenizer.encode(prompt)
         try:
-            r = eng.submit(ids, gen_cfg(req.temperature, req.top_p, req.max_tokens, req.top_k, req.repetition_penalty))
+            r = eng.submit(ids, gen_cfg(req.temperature, req.top_p, req.max_tokens, req.top_k, req.repetition_penalty, req.ignore_eos))
         except ValueError as e:
             raise HTTPException(status_code=400, detail=str(e))
         cid, created = f"chatcmpl-{uuid.uuid4().hex}", int(time.time())
@@ -202,6 +210,8 @@ def build_app(engine: Optional[LLMEngine], prompt_style: str = "chatml", allow_s
                     if tail:
                         yield "data: " + json.dumps({**head, "choices": [{"index": 0, "delta": {"content": tail}, "finish_reason": None}]}, ensure_ascii=False) + "\n\n"
                 yield "data: " + json.dumps({**head, "choices": [{"index": 0, "delta": {}, "finish_reason": "stop" if hit else r.finish_reason}]}) + "\n\n"
+                if (req.stream_options or {}).get("include_usage"):
+                    yield usage_chunk(head, len(ids), len(acc))
                 yield "data: [DONE]\n\n"
             return StreamingResponse(events(), media_type="text/event-stream")
         r.done.wait()
@@ -217,14 +227,46 @@ def build_app(engine: Optional[LLMEngine], prompt_style: str = "chatml", allow_s
     @app.post("/v1/completions")
     def completions(req: CompletionRequest):
         eng = ready()
-        if req.stream:
-            raise HTTPException(status_code=501, detail="Streaming is only implemented for /v1/chat/completions.")
+        if req.stream and not allow_stream:
+            raise HTTPException(status_code=501, detail="Streaming is not yet implemented.")
         prompts = [req.prompt] if isinstance(req.prompt, str) else list(req.prompt)
-        cfg = gen_cfg(req.temperature, req.top_p, req.max_tokens)
+        cfg = gen_cfg(req.temperature, req.top_p, req.max_tokens, ignore_eos=req.ignore_eos)
+        if req.stream and len(prompts) != 1:
+            raise HTTPException(status_code=400, detail="streaming takes one prompt per request")
         try:
             reqs = [eng.submit(eng.tokenizer.encode(p), cfg) for p in prompts]
         except ValueError as e:
             raise HTTPException(status_code=400, detail=str(e))
+        if req.stream:
+            # the form ``vllm bench serve --backend vllm`` reads: text deltas in choices[0].text, then the usage chunk
+            r = reqs[0]
+            head = {"id": f"cmpl-{uuid.uuid4().hex}", "object": "text_completion", "created": int(time.time()), "model": req.model}
+
+            def events():
+                sent, acc, stops, hit = "", [], _stops(req.stop), False
+                hold = max((len(x) for x in stops), default=1) - 1
+                for tok in r.tokens():
+                    acc.append(tok)
+                    text = decode(eng, acc)
+                    if text.endswith("\ufffd"):          # incomplete UTF-8 sequence: wait for the next token
+                        continue
+                    text, hit = cut_at_stop(text, stops)
+                    safe = text if hit else text[:max(len(text) - hold, len(sent))]
+                    delta, sent = safe[len(sent):], safe
+                    if delta:
+                        yield "data: " + json.dumps({**head, "choices": [{"index": 0, "text": delta, "finish_reason": None, "logprobs": None}]},
+                                                    ensure_ascii=False) + "\n\n"
+                    if hit:
+                        eng.abort(r)
+                        break
+                tail = "" if hit else cut_at_stop(decode(eng, acc), stops)[0][len(sent):]
+                yield "data: " + json.dumps({**head, "choices": [{"index": 0, "text": tail, "logprobs": None,
+                                                                  "finish_reason": "stop" if hit else r.finish_reason}]},
+                                            ensure_ascii=False) + "\n\n"
+                if (req.stream_options or {}).get("include_usage"):
+                    yield usage_chunk(head, len(r.prompt_ids), len(acc))
+                yield "data: [DONE]\n\n"
+            return StreamingResponse(events(), media_type="text/event-stream")
         choices, n_p, n_c = [], 0, 0
         for i, r in enumerate(reqs):
             r.done.wait()

@@ -388,3 +388,67 @@ def test_host_tier_restores_an_evicted_prefix(model, block_size):
         while not r.done.is_set():
             off.step()
     assert off.metrics.host_offloads == 0 and not off._host_rows                  # off by default
+
+
+def test_completions_stream_ignore_eos_and_usage_chunk(model):
+    """What ``vllm bench serve --backend vllm --ignore-eos`` sends: a streaming /v1/completions request with ignore_eos and
+    stream_options.include_usage; the answer is text deltas, a finish chunk and a usage chunk."""
+    tok = ByteTokenizer()
+    eng = LLMEngine(model, tok, EngineArgs(max_num_seqs=2, max_model_len=128, warmup=False), model_name="qwen3").start()
+    try:
+        c = TestClient(build_app(eng))
+        body = {"model": "qwen3", "prompt": "hello", "max_tokens": 6, "temperature": 0.0}
+        plain = c.post("/v1/completions", json=body).json()
+        first = plain["choices"][0]
+        # make the engine stop early: the second generated token becomes EOS
+        ids = eng.generate([tok.encode("hello")], GenerationConfig(max_new_tokens=6, do_sample=False))[0].output_ids
+        tok.eos_token_id = ids[1]
+        assert c.post("/v1/completions", json=body).json()["usage"]["completion_tokens"] == ids.index(ids[1]) < 6     # the EOS token itself is not output
+        r = c.post("/v1/completions", json=dict(body, stream=True, ignore_eos=True, stream_options={"include_usage": True}))
+        assert r.status_code == 200 and r.headers["content-type"].startswith("text/event-stream")
+        events = [json.loads(l[6:]) for l in r.text.splitlines() if l.startswith("data: ") and l != "data: [DONE]"]
+        assert r.text.rstrip().endswith("data: [DONE]")
+        usage = [e for e in events if e.get("usage")]
+        assert len(usage) == 1 and usage[0]["usage"]["completion_tokens"] == 6 and usage[0]["choices"] == []      # EOS ignored
+        assert usage[0]["usage"]["prompt_tokens"] == len(tok.encode("hello"))
+        text = "".join(e["choices"][0]["text"] for e in events if e["choices"])
+        assert text == first["text"] and [e["choices"][0]["finish_reason"] for e in events if e["choices"]][-1] == "length"
+        chat = c.post("/v1/chat/completions", json={"model": "qwen3", "messages": [{"role": "user", "content": "hi"}], "max_tokens": 4,
+                                                    "temperature": 0.0, "stream": True, "ignore_eos": True,
+                                                    "stream_options": {"include_usage": True}})
+        ev = [json.loads(l[6:]) for l in chat.text.splitlines() if l.startswith("data: ") and l != "data: [DONE]"]
+        assert ev[-1]["usage"]["completion_tokens"] == 4
+    finally:
+        del tok.eos_token_id
+        eng.shutdown()
+
+
+def test_bench_serve_client_reports_vllm_result_keys(model, tmp_path):
+    from llm_in_practise_b200.serve.bench_client import format_report, load_sharegpt, random_requests, run_benchmark
+    tok = ByteTokenizer()
+    eng = LLMEngine(model, tok, EngineArgs(max_num_seqs=4, max_model_len=256, warmup=False), model_name="qwen3").start()
+    data = [{"conversations": [{"from": "human", "value": f"question number {i}"}, {"from": "gpt", "value": "an answer of five words"}]}
+            for i in range(5)] + [{"conversations": [{"from": "human", "value": "only one turn"}]}]
+    path = tmp_path / "sharegpt.json"
+    path.write_text(json.dumps(data))
+    reqs = load_sharegpt(str(path), 8, 5, seed=1)
+    assert len(reqs) == 8 and all(r.output_len == 5 for r in reqs) and len({r.prompt for r in reqs}) == 5
+    assert load_sharegpt(str(path), 2, None)[0].output_len == 5                       # from the reference answer's length
+    try:
+        for backend in ("vllm", "openai-chat"):
+            out = asyncio.run(run_benchmark("http://test", "qwen3", reqs, backend=backend, max_concurrency=3, ignore_eos=True,
+                                            transport=httpx.ASGITransport(app=build_app(eng))))
+            assert out["completed"] == 8 and out["failed"] == 0 and out["total_output_tokens"] == 8 * 5, out
+            assert out["total_input_tokens"] > 0 and out["output_throughput"] > 0 and out["request_throughput"] > 0
+            for k in ("mean_ttft_ms", "median_ttft_ms", "p99_ttft_ms", "mean_tpot_ms", "p99_tpot_ms", "mean_itl_ms", "mean_e2el_ms", "p99_e2el_ms"):
+                assert k in out and out[k] >= 0
+            assert out["mean_e2el_ms"] >= out["mean_ttft_ms"] > 0
+            assert "Output token throughput" in format_report(out)
+        paced = asyncio.run(run_benchmark("http://test", "qwen3", random_requests(4, 6, 3), request_rate=200.0,
+                                          transport=httpx.ASGITransport(app=build_app(eng))))
+        assert paced["completed"] == 4 and paced["request_rate"] == 200.0
+        bad = asyncio.run(run_benchmark("http://test", "nope", random_requests(2, 300, 3), backend="vllm",
+                                        transport=httpx.ASGITransport(app=build_app(eng))))     # prompts longer than max_model_len
+        assert bad["completed"] == 0 and bad["failed"] == 2 and "HTTP 400" in bad["errors"][0]
+    finally:
+        eng.shutdown()
