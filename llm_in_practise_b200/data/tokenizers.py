@@ -227,10 +227,66 @@ class BPETokenizer:
             json.dump({"type": "b200-byte-bpe", "merges": self.merges.tolist(), "special_tokens": self.special_tokens}, f)
 
     @classmethod
-    def from_file(cls, path: str) -> "BPETokenizer":
+    def from_file(cls, path: str):
+        """``bpe_tokenizer.json`` written by ``save``; a ``tokenizer.json`` written by the reference's own scripts (HF
+        ``tokenizers``, ByteLevel BPE — …/GPTLike_wikitext2_fixed_pe.py:61-75) comes back as an ``HFTokenizerFile`` so that
+        the token ids a reference checkpoint was trained with stay valid."""
         with open(path) as f:
             d = json.load(f)
+        if d.get("type") != "b200-byte-bpe" and isinstance(d.get("model"), dict):
+            return HFTokenizerFile(path)
         return cls(d["merges"], d.get("special_tokens", ()))
+
+
+class HFTokenizerFile:
+    """A ``tokenizer.json`` of the HF ``tokenizers`` library behind this module's tokenizer interface (``encode`` ->
+    list of ids, ``encode_batch``, ``decode``, ``vocab_size``, ``token_to_id``, pad / eos ids, callable form)."""
+
+    def __init__(self, path: str):
+        from tokenizers import Tokenizer
+        self.tk = Tokenizer.from_file(path)
+        self.path = path
+
+    @property
+    def vocab_size(self) -> int:
+        return self.tk.get_vocab_size(with_added_tokens=True)
+
+    def token_to_id(self, tok: str) -> Optional[int]:
+        return self.tk.token_to_id(tok)
+
+    @property
+    def pad_token_id(self) -> int:
+        i = self.tk.token_to_id("[PAD]")
+        return 0 if i is None else i
+
+    @property
+    def eos_token_id(self) -> Optional[int]:
+        for name in ("[EOS]", "[SEP]", "</s>", "<|endoftext|>"):
+            i = self.tk.token_to_id(name)
+            if i is not None:
+                return i
+        return None
+
+    def encode(self, text: str) -> List[int]:
+        return self.tk.encode(text).ids
+
+    def encode_batch(self, texts: Sequence[str], chunk: int = 1024) -> List[List[int]]:
+        out: List[List[int]] = []
+        for i in range(0, len(texts), chunk):
+            out.extend(e.ids for e in self.tk.encode_batch(list(texts[i:i + chunk])))
+        return out
+
+    def decode(self, ids: Iterable[int], skip_special_tokens: bool = True) -> str:
+        return self.tk.decode([int(i) for i in ids], skip_special_tokens=skip_special_tokens)
+
+    def __call__(self, texts, truncation: bool = False, max_length: Optional[int] = None, **_):
+        ids = self.encode_batch([texts] if isinstance(texts, str) else list(texts))
+        if truncation and max_length:
+            ids = [x[:max_length] for x in ids]
+        return {"input_ids": ids}
+
+    def save(self, path: str) -> None:
+        self.tk.save(path)
 
 
 def load_or_train_bpe(path: str, texts_fn, vocab_size: int = 3000, rank: int = 0, barrier=None) -> BPETokenizer:

@@ -196,3 +196,34 @@ def test_nf4_codebook_equals_its_definition():
         code = create_dynamic_map(signed=signed)
         assert code.numel() == 256 and bool((code[1:] >= code[:-1]).all()) and float(code.max()) == 1.0
         assert 0.0 in code.tolist() and (float(code.min()) < 0) == signed
+
+
+def test_reference_tokenizer_json_keeps_its_ids(tmp_path):
+    """A ``tokenizer.json`` produced the way the reference's training scripts produce it (HF tokenizers, ByteLevel BPE, the
+    four special tokens) loads through ``BPETokenizer.from_file`` / ``load_or_train_bpe`` and encodes to the same ids."""
+    tokenizers = pytest.importorskip("tokenizers")
+    from tokenizers import Tokenizer, models, pre_tokenizers, trainers
+    from llm_in_practise_b200.data.tokenizers import BPETokenizer, HFTokenizerFile, load_or_train_bpe
+    texts = ["the quick brown fox jumps over the lazy dog", "pack my box with five dozen liquor jugs", "the fox and the dog"] * 20
+    tk = Tokenizer(models.BPE(unk_token="[UNK]"))
+    tk.pre_tokenizer = pre_tokenizers.ByteLevel()
+    tk.train_from_iterator(iter(texts), trainer=trainers.BpeTrainer(vocab_size=300, special_tokens=["[PAD]", "[UNK]", "[CLS]", "[SEP]"],
+                                                                      show_progress=False))
+    path = tmp_path / "tokenizer.json"
+    tk.save(str(path))
+    mine = BPETokenizer.from_file(str(path))
+    assert isinstance(mine, HFTokenizerFile) and mine.vocab_size == tk.get_vocab_size()
+    s = "the lazy fox packs five boxes"
+    assert mine.encode(s) == tk.encode(s).ids
+    assert mine.encode_batch(texts[:3]) == [e.ids for e in tk.encode_batch(texts[:3])]
+    assert mine(texts[:2], truncation=True, max_length=4)["input_ids"] == [e.ids[:4] for e in tk.encode_batch(texts[:2])]
+    assert mine.pad_token_id == 0 and mine.token_to_id("[SEP]") == 3 == mine.eos_token_id
+    assert mine.decode(mine.encode(s)) == tk.decode(tk.encode(s).ids)        # (the reference sets no decoder: pieces joined by spaces)
+    # the cache-or-train helper finds the file and does not retrain over it
+    again = load_or_train_bpe(str(path), lambda: (_ for _ in ()).throw(AssertionError("must not retrain")), vocab_size=300)
+    assert again.encode(s) == tk.encode(s).ids
+    # this framework's own file format still round-trips
+    own = BPETokenizer.train_from_iterator(texts, vocab_size=280)
+    own.save(str(tmp_path / "bpe_tokenizer.json"))
+    assert BPETokenizer.from_file(str(tmp_path / "bpe_tokenizer.json")).encode(s) == own.encode(s)
+    assert tokenizers.__version__
