@@ -83,6 +83,15 @@ class Config:
         for k, v in kw.items():
             setattr(self, k, v)
 
+    # the reference spells the width ``embed_dim`` (llm-demo/minigpt2/model.py:9); both names reach the same attribute
+    @property
+    def embed_dim(self) -> int:
+        return self.n_embd
+
+    @embed_dim.setter
+    def embed_dim(self, v: int) -> None:
+        self.n_embd = v
+
 
 class MiniGPT2(nn.Module):
     def __init__(self, config: Config, causal: bool = False, dtype=torch.float32, device=None):
@@ -110,6 +119,35 @@ class MiniGPT2(nn.Module):
             h, res = blk(h, res)
         x, _ = layer_norm(h, self.ln_f_w, self.ln_f_b, 1e-5, res)
         return x
+
+    # ---- the reference's own checkpoint layout (llm-demo/minigpt2/model.py:39-57: nn.Embedding ``embed``, ``pos_embed``,
+    #      ``transformer.layers.N`` = nn.TransformerEncoderLayer, ``ln``, ``head``) ---------------------------------------
+    def load_reference_state_dict(self, sd: dict) -> None:
+        with torch.no_grad():
+            self.token_embedding.copy_(sd["embed.weight"])
+            self.position_embedding.copy_(sd["pos_embed"])
+            self.ln_f_w.copy_(sd["ln.weight"]); self.ln_f_b.copy_(sd["ln.bias"])
+            self.head_w.copy_(sd["head.weight"]); self.head_b.copy_(sd["head.bias"])
+            for i, b in enumerate(self.blocks):
+                p = f"transformer.layers.{i}."
+                b.attn.load_torch_mha_state(sd, p + "self_attn.")
+                b.mlp.fc1.weight.copy_(sd[p + "linear1.weight"]); b.mlp.fc1.bias.copy_(sd[p + "linear1.bias"])
+                b.mlp.fc2.weight.copy_(sd[p + "linear2.weight"]); b.mlp.fc2.bias.copy_(sd[p + "linear2.bias"])
+                b.ln1_w.copy_(sd[p + "norm1.weight"]); b.ln1_b.copy_(sd[p + "norm1.bias"])
+                b.ln2_w.copy_(sd[p + "norm2.weight"]); b.ln2_b.copy_(sd[p + "norm2.bias"])
+
+    def reference_state_dict(self) -> dict:
+        c = lambda t: t.detach().clone()  # noqa: E731
+        sd = {"embed.weight": c(self.token_embedding), "pos_embed": c(self.position_embedding), "ln.weight": c(self.ln_f_w),
+              "ln.bias": c(self.ln_f_b), "head.weight": c(self.head_w), "head.bias": c(self.head_b)}
+        for i, b in enumerate(self.blocks):
+            p = f"transformer.layers.{i}."
+            sd.update(b.attn.export_torch_mha_state(p + "self_attn."))
+            sd[p + "linear1.weight"], sd[p + "linear1.bias"] = c(b.mlp.fc1.weight), c(b.mlp.fc1.bias)
+            sd[p + "linear2.weight"], sd[p + "linear2.bias"] = c(b.mlp.fc2.weight), c(b.mlp.fc2.bias)
+            sd[p + "norm1.weight"], sd[p + "norm1.bias"] = c(b.ln1_w), c(b.ln1_b)
+            sd[p + "norm2.weight"], sd[p + "norm2.bias"] = c(b.ln2_w), c(b.ln2_b)
+        return sd
 
     def forward(self, idx: torch.Tensor, targets: Optional[torch.Tensor] = None, n_valid: Optional[int] = None):
         x = self.hidden(idx)
@@ -232,7 +270,10 @@ class GPTTester:
             setattr(self.config, k, v)
         self.stoi, self.itos = ck["stoi"], ck["itos"]
         self.model = MiniGPT2(self.config, causal=causal).to(device)
-        self.model.load_state_dict(ck["model_state"])
+        if "embed.weight" in ck["model_state"]:                    # a checkpoint written by the reference's own script
+            self.model.load_reference_state_dict(ck["model_state"])
+        else:
+            self.model.load_state_dict(ck["model_state"])
         self.model.eval()
         self.device = device
 
