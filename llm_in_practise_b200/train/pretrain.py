@@ -99,6 +99,9 @@ class PretrainConfig:
     keep_last: int = 5
     final_model_path: Optional[str] = None
     resume: bool = False
+    init_from: Optional[str] = None         # start from a saved model: a state dict of this framework or one written by the
+                                            # reference's scripts (torch module names: ``models/final_model.pth``,
+                                            # ``checkpoints/model_epoch_N.pth``, or a ``{"model_state_dict": ...}`` checkpoint)
     early_stop_patience: int = 0
     log_every: int = 100
     device: Optional[str] = None
@@ -214,6 +217,27 @@ def _loss_of(out):
     return out
 
 
+def load_initial_weights(model: nn.Module, path: str, device="cpu") -> str:
+    """``model`` <- the state dict at ``path``; returns which layout was recognised. A reference ``.pth`` holds torch module
+    names (``tok_emb.weight``, ``blocks.0.attn.mha.in_proj_weight`` — ddp_gpt_wikitext2.py:320-331) and goes through the
+    model's ``load_reference_state_dict``; DDP's ``module.`` prefix is dropped."""
+    sd = torch.load(path, map_location=device, weights_only=False)
+    for key in ("model_state_dict", "model_state", "state_dict"):
+        if isinstance(sd, dict) and key in sd and isinstance(sd[key], dict):
+            sd = sd[key]
+            break
+    sd = {(k[7:] if k.startswith("module.") else k): v for k, v in sd.items()}
+    own = set(model.state_dict().keys())
+    if own and own <= set(sd.keys()):
+        model.load_state_dict(sd, strict=False)
+        return "native"
+    if hasattr(model, "load_reference_state_dict"):
+        model.load_reference_state_dict(sd)
+        return "reference"
+    raise ValueError(f"{path}: the state dict matches neither this model's parameter names nor a layout it can convert "
+                     f"(first keys: {sorted(sd)[:4]})")
+
+
 def _bare(model: nn.Module) -> nn.Module:
     return getattr(model, "module", model)
 
@@ -255,6 +279,8 @@ def run_pretraining(cfg: PretrainConfig) -> Dict[str, Any]:
     engine = None
     batch_size = cfg.batch_size
     model = build_model(cfg, vocab, device)
+    if cfg.init_from:
+        load_initial_weights(model, cfg.init_from, device)
     n_params = sum(p.numel() for p in model.parameters())
     if cfg.strategy == "zero":
         from ..parallel.zero import initialize

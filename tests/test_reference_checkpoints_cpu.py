@@ -86,3 +86,36 @@ def test_minigpt_reference_state_dict_loads_strictly():
     x = torch.randint(0, 40, (4, 16))
     with torch.no_grad():
         assert torch.allclose(mine(x), theirs(x), atol=1e-5)
+
+
+def test_init_from_accepts_reference_and_native_files(tmp_path):
+    """``PretrainConfig.init_from``: a ``.pth`` written by the reference's DDP script (module names of torch, DDP's ``module.``
+    prefix, or wrapped in a checkpoint dict) and one written here both initialise the model."""
+    ref = _ref_module("ddp_gpt_wikitext2.py")
+    from llm_in_practise_b200.models.gpt import GPTLike
+    from llm_in_practise_b200.train.pretrain import load_initial_weights
+    torch.manual_seed(1)
+    theirs = ref.GPTLike(vocab_size=120, block_size=16, n_layer=1, n_head=2, d_model=32, dropout=0.0).eval()
+    ids = torch.randint(0, 120, (2, 12))
+    with torch.no_grad():
+        want = theirs(ids)
+    p1, p2, p3 = (str(tmp_path / n) for n in ("final_model.pth", "ckpt.pt", "native.pth"))
+    torch.save({"module." + k: v for k, v in theirs.state_dict().items()}, p1)
+    torch.save({"epoch": 3, "model_state_dict": theirs.state_dict()}, p2)
+    for path in (p1, p2):
+        mine = GPTLike(vocab_size=120, block_size=16, n_layer=1, n_head=2, d_model=32, dropout=0.0).eval()
+        assert load_initial_weights(mine, path) == "reference"
+        with torch.no_grad():
+            got = mine(ids)
+        got = got["logits"] if isinstance(got, dict) else got
+        assert torch.allclose(got, want, atol=2e-4, rtol=1e-4)
+    torch.save(mine.state_dict(), p3)
+    again = GPTLike(vocab_size=120, block_size=16, n_layer=1, n_head=2, d_model=32, dropout=0.0).eval()
+    assert load_initial_weights(again, p3) == "native"
+    with torch.no_grad():
+        g2 = again(ids)
+    g2 = g2["logits"] if isinstance(g2, dict) else g2
+    assert torch.allclose(g2, want, atol=2e-4, rtol=1e-4)
+    torch.save({"foo": torch.zeros(1)}, p3)
+    with pytest.raises((ValueError, KeyError)):
+        load_initial_weights(GPTLike(vocab_size=120, block_size=16, n_layer=1, n_head=2, d_model=32), p3)
