@@ -88,7 +88,6 @@ def build_parser() -> argparse.ArgumentParser:
     ap.add_argument("--gradient_accumulation_steps", type=int, default=None, help="alias of --grad_accum")
     ap.add_argument("--eval_interval", type=int, default=None, help="accepted; validation runs once per epoch")
     ap.add_argument("--train_tokenizer", action="store_true", help="train a byte-level BPE on the corpus (tokenizer=bytelevel-bpe)")
-    ap.add_argument("--init_from", type=str, default=None, help="start from a saved state dict (this framework's or the reference's .pth)")
     ap.add_argument("--use_pretrained_tokenizer", type=str, default=None, help="name or path of a pretrained tokenizer (tokenizer=<value>)")
     ap.add_argument("--local_rank", type=int, default=None, help="accepted for launcher compatibility")
     return ap
@@ -115,8 +114,6 @@ def main(argv=None) -> dict:
         kw["grad_accum"] = a.gradient_accumulation_steps
     if a.train_tokenizer:
         kw["tokenizer"] = "bytelevel-bpe"
-    if a.init_from:
-        kw["init_from"] = a.init_from
     if a.use_pretrained_tokenizer:
         kw["tokenizer"] = a.use_pretrained_tokenizer
     try:
