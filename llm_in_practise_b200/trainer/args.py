@@ -5,7 +5,7 @@ from __future__ import annotations
 
 import json
 import os
-from dataclasses import asdict, dataclass, field
+from dataclasses import asdict, dataclass, field, fields
 from typing import Any, Dict, List, Optional, Union
 
 
@@ -108,15 +108,25 @@ class TrainerState:
     best_metric: Optional[float] = None
     best_model_checkpoint: Optional[str] = None
     total_flos: float = 0.0
+    # fields of a ``trainer_state.json`` written by HF transformers that this trainer does not use (``eval_steps``,
+    # ``stateful_callbacks``, ``train_batch_size`` ...): kept and written back, so a checkpoint can move both ways
+    extra: Dict[str, Any] = field(default_factory=dict)
 
     def save_to_json(self, path: str) -> None:
+        d = asdict(self)
+        d.update(d.pop("extra"))
         with open(path, "w") as f:
-            json.dump(asdict(self), f, indent=2)
+            json.dump(d, f, indent=2, sort_keys=True)
 
     @classmethod
     def load_from_json(cls, path: str) -> "TrainerState":
         with open(path) as f:
-            return cls(**json.load(f))
+            d = json.load(f)
+        known = {f.name for f in fields(cls)} - {"extra"}
+        st = cls(**{k: v for k, v in d.items() if k in known})
+        st.extra = {k: v for k, v in d.items() if k not in known}
+        st.epoch = float(st.epoch or 0.0)
+        return st
 
 
 @dataclass

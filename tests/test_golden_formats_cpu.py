@@ -227,3 +227,26 @@ def test_reference_tokenizer_json_keeps_its_ids(tmp_path):
     own.save(str(tmp_path / "bpe_tokenizer.json"))
     assert BPETokenizer.from_file(str(tmp_path / "bpe_tokenizer.json")).encode(s) == own.encode(s)
     assert tokenizers.__version__
+
+
+def test_trainer_state_json_moves_between_hf_and_this_trainer(tmp_path):
+    """``checkpoint-N/trainer_state.json``: a file written by the real ``transformers.TrainerState`` resumes here (its extra
+    fields survive a save), and a file written here loads with transformers."""
+    tc = pytest.importorskip("transformers.trainer_callback")
+    from llm_in_practise_b200.trainer.args import TrainerState
+    hf = tc.TrainerState(epoch=1.5, global_step=30, max_steps=100, logging_steps=10, eval_steps=20, save_steps=20, train_batch_size=2,
+                         num_train_epochs=3, total_flos=1.5e12, best_metric=0.42, best_model_checkpoint="out/checkpoint-20",
+                         log_history=[{"loss": 2.5, "learning_rate": 1e-4, "epoch": 0.5, "step": 10}, {"eval_loss": 2.1, "epoch": 1.0, "step": 20}])
+    theirs, ours = str(tmp_path / "hf.json"), str(tmp_path / "ours.json")
+    hf.save_to_json(theirs)
+    st = TrainerState.load_from_json(theirs)
+    assert (st.global_step, st.epoch, st.max_steps, st.best_metric, st.best_model_checkpoint) == (30, 1.5, 100, 0.42, "out/checkpoint-20")
+    assert st.log_history == hf.log_history and st.extra["train_batch_size"] == 2 and st.extra["eval_steps"] == 20
+    st.global_step, st.epoch = 40, 2.0
+    st.log_history.append({"loss": 1.9, "epoch": 2.0, "step": 40})
+    st.save_to_json(ours)
+    back = tc.TrainerState.load_from_json(ours)                              # transformers reads what this trainer wrote
+    assert back.global_step == 40 and back.epoch == 2.0 and back.train_batch_size == 2 and len(back.log_history) == 3
+    fresh = str(tmp_path / "fresh.json")
+    TrainerState(epoch=0.25, global_step=5, max_steps=20, log_history=[{"loss": 3.0, "step": 5}]).save_to_json(fresh)
+    assert tc.TrainerState.load_from_json(fresh).global_step == 5
