@@ -139,9 +139,11 @@ class DistributedSampler(Sampler):
 
 class DataCollatorForLanguageModeling:
     def __init__(self, tokenizer=None, mlm: bool = False, pad_token_id: Optional[int] = None,
-                 pad_to_multiple_of: Optional[int] = None, assistant_only_loss: bool = False):
+                 pad_to_multiple_of: Optional[int] = None, assistant_only_loss: bool = False, return_tensors: str = "pt"):
         if mlm:
             raise NotImplementedError("masked-LM collation is not used anywhere in the reference")
+        if return_tensors != "pt":                # Fine-Tuning/qwen3-8b-qlora.py passes return_tensors="pt"
+            raise ValueError("only return_tensors='pt' is produced")
         self.pad = pad_token_id if pad_token_id is not None else getattr(tokenizer, "pad_token_id", 0)
         self.multiple = pad_to_multiple_of
         self.assistant_only = assistant_only_loss

@@ -40,7 +40,15 @@ class BitsAndBytesConfig:
 def config_from_hf(d: dict) -> Qwen3Config:
     mt = d.get("model_type", "qwen3")
     hd = d.get("head_dim") or d["hidden_size"] // d["num_attention_heads"]
+    # rope scaling: ``rope_scaling`` (transformers 4) or ``rope_parameters`` (transformers 5, which also holds rope_theta)
+    rp = d.get("rope_parameters") or {}
+    rs = d.get("rope_scaling") or ({k: v for k, v in rp.items() if k != "rope_theta"} if rp else None)
+    if rs and rs.get("rope_type", rs.get("type", "default")) in ("default", None):
+        rs = None
+    if "rope_theta" not in d and "rope_theta" in rp:
+        d = dict(d, rope_theta=rp["rope_theta"])
     return Qwen3Config(
+        rope_scaling=rs,
         vocab_size=d["vocab_size"], hidden_size=d["hidden_size"], intermediate_size=d["intermediate_size"],
         num_hidden_layers=d["num_hidden_layers"], num_attention_heads=d["num_attention_heads"],
         num_key_value_heads=d.get("num_key_value_heads", d["num_attention_heads"]), head_dim=hd,
@@ -56,6 +64,7 @@ def config_to_hf(c: Qwen3Config, dtype=torch.bfloat16) -> dict:
             "intermediate_size": c.intermediate_size, "num_hidden_layers": c.num_hidden_layers,
             "num_attention_heads": c.num_attention_heads, "num_key_value_heads": c.num_key_value_heads,
             "head_dim": c.head_dim, "rms_norm_eps": c.rms_norm_eps, "rope_theta": c.rope_theta,
+            "rope_scaling": c.rope_scaling,
             "max_position_embeddings": c.max_position_embeddings, "tie_word_embeddings": c.tie_word_embeddings,
             "attention_bias": c.attention_bias, "hidden_act": "silu", "torch_dtype": str(dtype).replace("torch.", ""),
             "use_cache": True, "attention_dropout": 0.0}
@@ -126,9 +135,11 @@ def load_hf_weights(model: Qwen3ForCausalLM, path: str, quantization_config: Opt
 
 def from_pretrained(path: str, dtype: torch.dtype = torch.bfloat16, torch_dtype: Optional[torch.dtype] = None,
                     device_map=None, device=None, quantization_config: Optional[BitsAndBytesConfig] = None,
-                    low_cpu_mem_usage: bool = True, use_cache: bool = True, trust_remote_code: bool = False, **_) -> Qwen3ForCausalLM:
+                    low_cpu_mem_usage: bool = True, use_cache: bool = True, trust_remote_code: bool = False, **extra) -> Qwen3ForCausalLM:
     """``AutoModelForCausalLM.from_pretrained`` for Qwen3 / Qwen2-style checkpoints on local disk. ``path`` may also
-    be a preset name (``qwen3-14b`` ...) to get random-init weights of that architecture (no network here)."""
+    be a preset name (``qwen3-14b`` ...) to get random-init weights of that architecture (no network here).
+    ``rope_scaling=<dict or None>`` overrides the checkpoint's own setting, as the config kwarg does in transformers
+    (the reference passes ``rope_scaling=None`` to switch YaRN off for fine-tuning)."""
     dtype = torch_dtype or dtype
     if device is None:
         device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
@@ -139,6 +150,8 @@ def from_pretrained(path: str, dtype: torch.dtype = torch.bfloat16, torch_dtype:
         return model
     with open(os.path.join(path, "config.json")) as f:
         cfg = config_from_hf(json.load(f))
+    if "rope_scaling" in extra:
+        cfg.rope_scaling = extra["rope_scaling"]
     model = Qwen3ForCausalLM(cfg, dtype=dtype, device=device)
     load_hf_weights(model, path, quantization_config)
     model.name_or_path = path

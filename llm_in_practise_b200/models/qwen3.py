@@ -39,6 +39,7 @@ class Qwen3Config:
     head_dim: int = 128
     rms_norm_eps: float = 1e-6
     rope_theta: float = 1000000.0
+    rope_scaling: Optional[dict] = None      # HF ``rope_scaling`` / ``rope_parameters`` (linear, yarn, llama3); None = plain RoPE
     max_position_embeddings: int = 40960
     tie_word_embeddings: bool = False
     model_type: str = "qwen3"
@@ -140,7 +141,8 @@ class Qwen3ForCausalLM(nn.Module):
     def rope(self, device, need: int):
         if self._rope is None or self._rope[0].device != device or self._rope[0].shape[0] < need:
             n = max(need, min(self.config.max_position_embeddings, 8192))
-            self._rope = ew.rope_tables(n, self.config.head_dim, self.config.rope_theta, device)
+            self._rope = ew.rope_tables(n, self.config.head_dim, self.config.rope_theta, device, self.config.rope_scaling,
+                                        self.config.max_position_embeddings)
         return self._rope
 
     def quantize_nf4(self, double_quant: bool = True) -> "Qwen3ForCausalLM":

@@ -13,6 +13,7 @@ ddp_gpt_wikitext2.py:86-165, …/transformer_basics/DeepSeekLike_spare_MoE_wikit
 from __future__ import annotations
 
 import ctypes
+import math
 from typing import Optional
 
 import torch
@@ -26,10 +27,63 @@ vp, i32, i64, u64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctype
 # ------------------------------------------------------------------------------------------------
 # rotary tables
 # ------------------------------------------------------------------------------------------------
-def rope_tables(max_pos: int, head_dim: int, theta: float = 10000.0, device=None):
-    """cos/sin tables [max_pos, head_dim/2] in fp32 (angles = pos * theta^(-2i/d))."""
-    inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.float32, device=device) / head_dim))
+def _yarn_correction_dim(num_rotations: float, dim: int, base: float, max_pos: int) -> float:
+    return dim * math.log(max_pos / (num_rotations * 2 * math.pi)) / (2 * math.log(base))
+
+
+def rope_inv_freq(head_dim: int, theta: float, scaling: Optional[dict] = None, max_position_embeddings: Optional[int] = None,
+                  device=None):
+    """(inverse frequencies [head_dim / 2] fp32, attention factor) for plain RoPE or the ``rope_scaling`` of an HF config
+    (``rope_type`` / ``type``: ``linear``, ``yarn``, ``llama3``) — e.g. DeepSeek-R1-0528-Qwen3-8B ships YaRN with factor 4,
+    which the reference's fine-tune script switches off with ``rope_scaling=None``
+    (Fine-Tuning/deepseek-r1-0528-qwen3-8b-qlora.dist.py:98-112) and its vLLM servers leave on."""
+    idx = torch.arange(0, head_dim, 2, dtype=torch.float32, device=device)
+    inv = 1.0 / (theta ** (idx / head_dim))
+    kind = (scaling or {}).get("rope_type", (scaling or {}).get("type", "default"))
+    if not scaling or kind in ("default", None):
+        return inv, 1.0
+    factor = float(scaling.get("factor", 1.0))
+    if kind == "linear":
+        return inv / factor, 1.0
+    if kind == "yarn":
+        orig = int(scaling.get("original_max_position_embeddings") or max_position_embeddings or 0)
+        if orig <= 0:
+            raise ValueError("yarn rope scaling needs original_max_position_embeddings")
+        beta_fast, beta_slow = float(scaling.get("beta_fast") or 32), float(scaling.get("beta_slow") or 1)
+        att = scaling.get("attention_factor", scaling.get("attn_factor"))
+        msc = lambda s, m=1.0: 1.0 if s <= 1 else 0.1 * m * math.log(s) + 1.0  # noqa: E731
+        if att is None:
+            m, ma = scaling.get("mscale"), scaling.get("mscale_all_dim")
+            att = msc(factor, m) / msc(factor, ma) if (m and ma) else msc(factor)
+        low = _yarn_correction_dim(beta_fast, head_dim, theta, orig)
+        high = _yarn_correction_dim(beta_slow, head_dim, theta, orig)
+        if scaling.get("truncate", True):
+            low, high = math.floor(low), math.ceil(high)
+        low, high = max(low, 0), min(high, head_dim - 1)
+        if low == high:
+            high += 0.001
+        ramp = ((torch.arange(head_dim // 2, dtype=torch.float32, device=device) - low) / (high - low)).clamp(0, 1)
+        keep = 1.0 - ramp                                       # 1: high-frequency dims keep their frequency, 0: interpolated
+        return (inv / factor) * (1 - keep) + inv * keep, float(att)
+    if kind == "llama3":
+        orig = int(scaling["original_max_position_embeddings"])
+        lo_f, hi_f = float(scaling.get("low_freq_factor", 1.0)), float(scaling.get("high_freq_factor", 4.0))
+        wavelen = 2 * math.pi / inv
+        smooth = ((orig / wavelen - lo_f) / (hi_f - lo_f)).clamp(0, 1)
+        mixed = (1 - smooth) * inv / factor + smooth * inv
+        out = torch.where(wavelen > orig / lo_f, inv / factor, torch.where(wavelen < orig / hi_f, inv, mixed))
+        return out, 1.0
+    raise NotImplementedError(f"rope scaling type {kind!r} is not implemented (linear, yarn and llama3 are)")
+
+
+def rope_tables(max_pos: int, head_dim: int, theta: float = 10000.0, device=None, scaling: Optional[dict] = None,
+                max_position_embeddings: Optional[int] = None):
+    """cos/sin tables [max_pos, head_dim/2] in fp32 (angles = pos * theta^(-2i/d)); with ``scaling`` the frequencies follow the
+    HF ``rope_scaling`` rule and YaRN's attention factor is folded into the tables (as transformers does)."""
+    inv_freq, att = rope_inv_freq(head_dim, theta, scaling, max_position_embeddings, device)
     ang = torch.outer(torch.arange(max_pos, dtype=torch.float32, device=device), inv_freq)
+    if att != 1.0:
+        return (ang.cos() * att).contiguous(), (ang.sin() * att).contiguous()
     return ang.cos().contiguous(), ang.sin().contiguous()
 
 
