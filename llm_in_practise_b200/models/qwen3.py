@@ -138,6 +138,47 @@ class Qwen3ForCausalLM(nn.Module):
     def gradient_checkpointing_disable(self):
         self.gradient_checkpointing = False
 
+    # ---- the rest of the transformers call surface the reference's scripts use on a model -------------------------------
+    @property
+    def device(self) -> torch.device:
+        return self.embed_tokens.device
+
+    def enable_input_require_grads(self) -> None:
+        """transformers needs this so that checkpointed blocks of a frozen base still get a gradient path to the adapters
+        (Fine-Tuning/qwen3-8b-qlora.py calls it after ``prepare_model_for_kbit_training``); the fused LoRA linears here take
+        their gradients from their own autograd functions, so there is nothing to switch on."""
+        self.input_require_grads = True
+
+    def save_pretrained(self, save_directory: str, **kw) -> None:
+        from ..io.hf import save_pretrained
+        shard = kw.get("max_shard_size")
+        if isinstance(shard, str):                       # "5GB", "500MB" as transformers spells it
+            units = {"KB": 10 ** 3, "MB": 10 ** 6, "GB": 10 ** 9, "KIB": 2 ** 10, "MIB": 2 ** 20, "GIB": 2 ** 30}
+            u = next((s for s in sorted(units, key=len, reverse=True) if shard.upper().endswith(s)), None)
+            shard = int(float(shard[:-len(u)]) * units[u]) if u else int(shard)
+        save_pretrained(self, save_directory, **({"max_shard_size": shard} if shard else {}), tokenizer=kw.get("tokenizer"))
+
+    @torch.no_grad()
+    def generate(self, input_ids: Optional[torch.Tensor] = None, attention_mask: Optional[torch.Tensor] = None,
+                 max_length: Optional[int] = None, streamer=None, **kw) -> torch.Tensor:
+        """``model.generate(**tokenizer(text, return_tensors="pt"), max_new_tokens=…, do_sample=…, temperature=…, top_p=…)``
+        as the inference scripts call it (Scripts/inference/01-*.py:20-30, Fine-Tuning/inferences.py:60-75): runs
+        ``inference.Generator`` (KV cache, CUDA-graph decode) and returns prompt + continuation ids. Padded batches are not
+        taken (the scripts generate one prompt at a time)."""
+        from ..inference.generate import Generator
+        if input_ids is None:
+            input_ids = kw.pop("inputs")
+        if attention_mask is not None and not bool(attention_mask.bool().all()):
+            raise NotImplementedError("generate() takes unpadded prompts (attention_mask must be all ones)")
+        if max_length is not None and "max_new_tokens" not in kw:
+            kw["max_new_tokens"] = max(1, int(max_length) - input_ids.shape[1])
+        need = input_ids.shape[1] + int(kw.get("max_new_tokens", 256))
+        g = self.__dict__.get("_generator")
+        if g is None or g.max_len < need:
+            g = Generator(self, None, max(need, min(self.config.max_position_embeddings, 4096)))
+            self.__dict__["_generator"] = g
+        return g.generate(input_ids.to(self.device), streamer=streamer, **kw)
+
     def rope(self, device, need: int):
         if self._rope is None or self._rope[0].device != device or self._rope[0].shape[0] < need:
             n = max(need, min(self.config.max_position_embeddings, 8192))

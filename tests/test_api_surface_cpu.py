@@ -54,3 +54,33 @@ def test_reference_call_sites_are_accepted():
                 refused.append((os.path.relpath(f, REF), name, bad))
     assert calls > 30, calls
     assert not refused, refused
+
+
+def test_methods_the_scripts_call_exist():
+    """``model.<x>(...)`` / ``trainer.<x>(...)`` / ``peft_model.<x>(...)`` in the reference's scripts: each name exists on the
+    object that plays that role here (``model`` is a causal LM, a PEFT wrapper or a GPTQModel depending on the script)."""
+    if not os.path.isdir(REF):
+        pytest.skip("reference tree not present")
+    from llm_in_practise_b200.models.classifier import EncoderClassifier
+    from llm_in_practise_b200.models.qwen3 import Qwen3ForCausalLM
+    from llm_in_practise_b200.peft import PeftModel
+    from llm_in_practise_b200.quant import GPTQModel
+    from llm_in_practise_b200.trainer.trainer import Trainer
+    roles = {"model": (Qwen3ForCausalLM, PeftModel, GPTQModel, EncoderClassifier), "peft_model": (PeftModel, Qwen3ForCausalLM),
+             "trainer": (Trainer,)}
+    files = [f for pat in ("Fine-Tuning/*.py", "HF_Basics/*.py", "Scripts/**/*.py", "Quantization/**/*.py")
+             for f in glob.glob(os.path.join(REF, pat), recursive=True)]
+    used = {k: set() for k in roles}
+    for f in files:
+        try:
+            tree = ast.parse(open(f, encoding="utf-8").read())
+        except SyntaxError:
+            continue
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute) and isinstance(node.func.value, ast.Name) \
+                    and node.func.value.id in roles:
+                used[node.func.value.id].add(node.func.attr)
+    assert {"generate", "save_pretrained", "print_trainable_parameters"} <= used["model"] and "train" in used["trainer"]
+    missing = [(role, name) for role, names in used.items() for name in sorted(names)
+               if not any(hasattr(cls, name) for cls in roles[role])]
+    assert not missing, missing

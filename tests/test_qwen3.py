@@ -104,3 +104,31 @@ def test_qlora_step_8bit_optimizer_gpu():
         opt.step()
         losses.append(loss.item())
     assert losses[-1] < losses[0]
+
+
+def test_transformers_call_surface_on_the_model(tmp_path):
+    """What the reference's scripts call on a model object: ``.device``, ``.generate(**inputs, …)``, ``.save_pretrained``,
+    ``.enable_input_require_grads()`` — on the bare model and through a PEFT wrapper."""
+    import torch
+    from llm_in_practise_b200.inference import Generator
+    from llm_in_practise_b200.io.hf import from_pretrained
+    from llm_in_practise_b200.models.qwen3 import QWEN3_PRESETS, Qwen3ForCausalLM
+    from llm_in_practise_b200.peft import LoraConfig, get_peft_model
+    torch.manual_seed(0)
+    m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32, device="cpu").eval()
+    assert m.device == torch.device("cpu")
+    inputs = {"input_ids": torch.arange(1, 9).view(1, 8), "attention_mask": torch.ones(1, 8, dtype=torch.long)}
+    out = m.generate(**inputs, max_new_tokens=5, do_sample=False)
+    assert out.shape == (1, 13) and torch.equal(out, Generator(m, max_len=64).generate(inputs["input_ids"], max_new_tokens=5, do_sample=False))
+    assert m.generate(inputs["input_ids"], max_length=11, do_sample=False).shape == (1, 11)
+    sampled = m.generate(**inputs, max_new_tokens=4, do_sample=True, temperature=0.7, top_p=0.9, seed=1)
+    assert sampled.shape == (1, 12)
+    with pytest.raises(NotImplementedError):
+        m.generate(input_ids=inputs["input_ids"], attention_mask=torch.tensor([[0, 1, 1, 1, 1, 1, 1, 1]]), max_new_tokens=2)
+    m.save_pretrained(str(tmp_path / "m"), max_shard_size="5GB")
+    back = from_pretrained(str(tmp_path / "m"), dtype=torch.float32, device=torch.device("cpu")).eval()
+    with torch.no_grad():
+        assert torch.allclose(back(inputs["input_ids"])["logits"], m(inputs["input_ids"])["logits"], atol=1e-5)
+    pm = get_peft_model(m, LoraConfig(r=2, lora_alpha=4, target_modules=["q_proj", "v_proj"]))
+    pm.enable_input_require_grads()
+    assert pm.device == torch.device("cpu") and pm.generate(**inputs, max_new_tokens=3, do_sample=False).shape == (1, 11)
