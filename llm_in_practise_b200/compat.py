@@ -1,0 +1,93 @@
+"""Import namespace for moving a reference script over with its imports changed and little else.
+
+The fine-tuning / quantisation / inference scripts of the reference start with
+
+    from transformers import AutoModelForCausalLM, AutoTokenizer, BitsAndBytesConfig, TrainingArguments, Trainer, \\
+        DataCollatorForLanguageModeling, TextIteratorStreamer, set_seed
+    from peft import LoraConfig, get_peft_model, TaskType, prepare_model_for_kbit_training, PeftModel
+    from gptqmodel import GPTQModel, QuantizeConfig
+    from llmcompressor import oneshot; from llmcompressor.modifiers... import GPTQModifier, AWQModifier
+
+(Fine-Tuning/qwen3-14b-qlora-dist-deepspeed.py:1-14, Quantization/GPTQModel/quantize_qwen3_4b_gptq.py:1-8,
+Quantization/LLM-Compressor/*/quantize_*.py, Scripts/inference/06-*.py). Every one of those names is importable from
+here and resolves to this framework's implementation:
+
+    from llm_in_practise_b200.compat import AutoModelForCausalLM, AutoTokenizer, BitsAndBytesConfig, ...
+
+``AutoModelForCausalLM.from_pretrained`` reads a local HF checkpoint directory (dense, GPTQ, AutoAWQ or compressed-tensors —
+detected from its config) or a preset name; ``AutoTokenizer`` is the real ``transformers`` tokenizer (host-side, not a hot
+path). ``tests/test_api_surface_cpu.py`` checks that the keyword arguments and methods the reference's scripts use on
+these objects exist.
+"""
+from __future__ import annotations
+
+import enum
+import os
+from typing import Optional
+
+import torch
+
+from .data.datasets import DataCollatorForLanguageModeling, DataCollatorWithPadding, set_seed  # noqa: F401
+from .inference.generate import GenerationConfig, TextIteratorStreamer  # noqa: F401
+from .io.hf import BitsAndBytesConfig  # noqa: F401
+from .peft import LoraConfig, PeftModel, get_peft_model, prepare_model_for_kbit_training  # noqa: F401
+from .quant import AWQModifier, GPTQModel, GPTQModifier, QuantizationModifier, QuantizeConfig, oneshot  # noqa: F401
+from .trainer import EvalPrediction, Trainer, TrainingArguments  # noqa: F401
+
+
+class TaskType(str, enum.Enum):
+    """``peft.TaskType``: ``LoraConfig(task_type=TaskType.CAUSAL_LM)``."""
+    CAUSAL_LM = "CAUSAL_LM"
+    SEQ_CLS = "SEQ_CLS"
+    SEQ_2_SEQ_LM = "SEQ_2_SEQ_LM"
+    TOKEN_CLS = "TOKEN_CLS"
+    FEATURE_EXTRACTION = "FEATURE_EXTRACTION"
+
+
+class AutoModelForCausalLM:
+    @staticmethod
+    def from_pretrained(pretrained_model_name_or_path: str, *args, **kw):
+        """Local checkpoint directory or preset name -> ``Qwen3ForCausalLM``. ``torch_dtype`` / ``dtype``, ``device_map``
+        (``"auto"`` / ``None`` / ``{"": i}``: one device per process here), ``quantization_config``, ``rope_scaling``,
+        ``use_cache``, ``trust_remote_code``, ``low_cpu_mem_usage`` are taken as transformers takes them."""
+        from .io.hf import from_pretrained
+        from .quant import detect_quant_format, load_quantized
+        path = pretrained_model_name_or_path
+        dtype = kw.pop("torch_dtype", None) or kw.pop("dtype", None) or torch.bfloat16
+        if dtype == "auto":
+            dtype = torch.bfloat16
+        dm = kw.pop("device_map", None)
+        device = kw.pop("device", None)
+        if device is None and isinstance(dm, dict) and dm:
+            d = next(iter(dm.values()))
+            device = torch.device("cuda", d) if isinstance(d, int) else torch.device(d)
+        if os.path.isdir(path) and detect_quant_format(path) is not None:
+            return load_quantized(path, dtype=dtype, device=device)
+        return from_pretrained(path, dtype=dtype, device=device, **kw)
+
+
+class AutoModelForSequenceClassification:
+    @staticmethod
+    def from_pretrained(pretrained_model_name_or_path: str, num_labels: int = 2, **kw):
+        """The encoder + classification head of HF_Basics/trainer_demo.py:61-64. BERT weights are not converted: the model is
+        built with the vocabulary of the tokenizer found at the path (or 30522) and trained from scratch."""
+        from .models.classifier import EncoderClassifier
+        vocab = 30522
+        try:
+            vocab = len(AutoTokenizer.from_pretrained(pretrained_model_name_or_path))
+        except Exception:
+            pass
+        dev = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+        return EncoderClassifier(vocab_size=vocab, num_labels=num_labels, device=dev,
+                                 **{k: v for k, v in kw.items() if k in ("d_model", "n_layer", "n_head", "max_len", "dropout")})
+
+
+class AutoTokenizer:
+    @staticmethod
+    def from_pretrained(pretrained_model_name_or_path: str, use_fast: bool = True, trust_remote_code: bool = False,
+                        padding_side: Optional[str] = None, **_):
+        from .data.tokenizers import load_pretrained_tokenizer
+        tok = load_pretrained_tokenizer(pretrained_model_name_or_path, add_pad_token=False)
+        if padding_side:
+            tok.padding_side = padding_side
+        return tok
