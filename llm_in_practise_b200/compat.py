@@ -91,3 +91,54 @@ class AutoTokenizer:
         if padding_side:
             tok.padding_side = padding_side
         return tok
+
+
+# ---- torch.distributed / deepspeed names of the hand-written training loops (LLM_Distributed_Trainning/PyTorch/**) ----------
+from .data.datasets import DistributedSampler  # noqa: E402,F401
+from .parallel.ddp import DistributedDataParallel  # noqa: E402,F401
+from .parallel.fsdp import (CPUOffload, CPUOffloadPolicy, FSDP, MixedPrecision, MixedPrecisionPolicy, ShardingStrategy,  # noqa: E402,F401
+                            StateDictOptions, fully_shard, get_state_dict, init_device_mesh, transformer_auto_wrap_policy)
+
+DDP = DistributedDataParallel
+FullyShardedDataParallel = FSDP
+
+
+class DeepSpeedCPUAdam(torch.optim.AdamW):
+    """``deepspeed.ops.adam.DeepSpeedCPUAdam(model.parameters(), lr=…)`` (…/deepspeed_basics/GPTLike_wikitext2_ZeRO-Offload.py:
+    27,228). Handed to ``deepspeed.initialize`` it only carries the hyper-parameters: the engine keeps the fp32 masters and the
+    AdamW state in pinned host memory and steps them with the C++ host optimizer (``csrc/host/cpu_adam.cpp``) when the config
+    says ``offload_optimizer: cpu``. Used on its own it is torch's AdamW."""
+
+    def __init__(self, model_params, lr: float = 1e-3, bias_correction: bool = True, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, amsgrad: bool = False, adamw_mode: bool = True, fp32_optimizer_states: bool = True):
+        super().__init__(model_params, lr=lr, betas=betas, eps=eps, weight_decay=weight_decay if adamw_mode else 0.0, amsgrad=amsgrad)
+
+
+class _DeepSpeedOpsAdam:
+    DeepSpeedCPUAdam = DeepSpeedCPUAdam
+
+
+class _DeepSpeedOps:
+    adam = _DeepSpeedOpsAdam
+
+
+class deepspeed:  # noqa: N801 - spelled like the module it stands in for
+    """``import deepspeed`` for the ZeRO training loops: ``deepspeed.init_distributed()``, ``engine, optimizer, _, scheduler =
+    deepspeed.initialize(args=…, model=…, optimizer=…, model_parameters=…, config=…)`` (the engine has ``backward`` / ``step`` /
+    ``save_checkpoint`` / ``load_checkpoint``), ``deepspeed.ops.adam.DeepSpeedCPUAdam``."""
+    ops = _DeepSpeedOps
+
+    @staticmethod
+    def init_distributed(dist_backend: Optional[str] = None, **kw):
+        from .parallel.zero import init_distributed
+        return init_distributed(dist_backend, **kw)
+
+    @staticmethod
+    def initialize(*a, **kw):
+        from .parallel.zero import ds_initialize
+        return ds_initialize(*a, **kw)
+
+    @staticmethod
+    def shutdown() -> None:
+        from .parallel.dist import cleanup_distributed
+        cleanup_distributed()

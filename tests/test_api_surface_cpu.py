@@ -56,6 +56,38 @@ def test_reference_call_sites_are_accepted():
     assert not refused, refused
 
 
+def test_distributed_training_call_sites_are_accepted():
+    """Same scan over LLM_Distributed_Trainning/**: DDP / FSDP / fully_shard / MixedPrecision / DistributedSampler /
+    deepspeed.initialize keyword arguments."""
+    if not os.path.isdir(REF):
+        pytest.skip("reference tree not present")
+    from llm_in_practise_b200 import compat as C
+    mirrors = {"DDP": C.DDP, "DistributedDataParallel": C.DDP, "FSDP": C.FSDP, "FullyShardedDataParallel": C.FSDP,
+               "fully_shard": C.fully_shard, "MixedPrecision": C.MixedPrecision, "MixedPrecisionPolicy": C.MixedPrecisionPolicy,
+               "CPUOffload": C.CPUOffload, "CPUOffloadPolicy": C.CPUOffloadPolicy, "DistributedSampler": C.DistributedSampler,
+               "DeepSpeedCPUAdam": C.DeepSpeedCPUAdam, "init_device_mesh": C.init_device_mesh, "StateDictOptions": C.StateDictOptions,
+               "transformer_auto_wrap_policy": C.transformer_auto_wrap_policy, "get_state_dict": C.get_state_dict}
+    from llm_in_practise_b200.parallel.zero import initialize
+    mirrors["initialize"] = initialize
+    calls, refused = 0, []
+    for f in glob.glob(os.path.join(REF, "LLM_Distributed_Trainning/**/*.py"), recursive=True):
+        try:
+            tree = ast.parse(open(f, encoding="utf-8").read())
+        except SyntaxError:
+            continue
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Call):
+                name = getattr(node.func, "id", getattr(node.func, "attr", None))
+                if name in mirrors:
+                    calls += 1
+                    names, varkw = _accepted(mirrors[name])
+                    bad = [k.arg for k in node.keywords if k.arg and k.arg not in names]
+                    if bad and not varkw:
+                        refused.append((os.path.relpath(f, REF), name, bad))
+    assert calls > 30, calls
+    assert not refused, refused
+
+
 def test_methods_the_scripts_call_exist():
     """``model.<x>(...)`` / ``trainer.<x>(...)`` / ``peft_model.<x>(...)`` in the reference's scripts: each name exists on the
     object that plays that role here (``model`` is a causal LM, a PEFT wrapper or a GPTQModel depending on the script)."""

@@ -75,3 +75,40 @@ def test_qlora_script_with_only_its_imports_changed(tmp_path):
                          eos_token_id=tokenizer.eos_token_id, pad_token_id=tokenizer.pad_token_id)
     assert out.shape[0] == 1 and inputs["input_ids"].shape[1] < out.shape[1] <= inputs["input_ids"].shape[1] + 6
     assert isinstance(tokenizer.decode(out[0], skip_special_tokens=True), str)
+
+
+def test_deepspeed_style_loop_with_only_its_imports_changed(tmp_path):
+    """The ZeRO training loop of LLM_Distributed_Trainning/PyTorch/deepspeed_basics/*.py: ``deepspeed.init_distributed()``,
+    ``engine, optimizer, _, _ = deepspeed.initialize(args=args, model=model, optimizer=optimizer, config=args.ds_config)``,
+    ``logits = engine(x)`` -> criterion -> ``engine.backward(loss)`` -> ``engine.step()``, ``engine.save_checkpoint``; the
+    ZeRO-Offload variant builds ``DeepSpeedCPUAdam`` first."""
+    import argparse
+    from llm_in_practise_b200.compat import deepspeed
+    from llm_in_practise_b200.models.gpt import GPTLike
+    ds_config = {"train_micro_batch_size_per_gpu": 4, "gradient_accumulation_steps": 1, "gradient_clipping": 1.0,
+                 "zero_optimization": {"stage": 2, "offload_optimizer": {"device": "cpu", "pin_memory": True}},
+                 "optimizer": {"type": "AdamW", "params": {"lr": 1e-2, "weight_decay": 0.01}}}
+    path = tmp_path / "ds_config.json"
+    path.write_text(json.dumps(ds_config))
+    args = argparse.Namespace(ds_config=str(path), local_rank=0, lr=1e-2)
+    deepspeed.init_distributed()
+    torch.manual_seed(0)
+    model = GPTLike(vocab_size=64, block_size=16, n_layer=2, n_head=2, d_model=32, dropout=0.0)
+    optimizer = deepspeed.ops.adam.DeepSpeedCPUAdam(model.parameters(), lr=args.lr)
+    engine, optimizer, _, _ = deepspeed.initialize(args=args, model=model, optimizer=optimizer, config=args.ds_config)
+    criterion = torch.nn.CrossEntropyLoss()
+    g = torch.Generator().manual_seed(1)
+    x = torch.randint(0, 64, (4, 16), generator=g)
+    y = torch.roll(x, -1, 1)
+    losses = []
+    for _ in range(12):
+        logits = engine(x)
+        logits = logits["logits"] if isinstance(logits, dict) else logits
+        loss = criterion(logits.reshape(-1, 64).float(), y.reshape(-1))
+        engine.backward(loss)
+        engine.step()
+        losses.append(float(loss.detach()))
+    assert losses[-1] < 0.7 * losses[0], losses
+    engine.save_checkpoint(str(tmp_path / "ck"), tag="epoch_1")
+    assert os.path.exists(tmp_path / "ck" / "latest")
+    deepspeed.shutdown()
