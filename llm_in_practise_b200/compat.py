@@ -142,3 +142,16 @@ class deepspeed:  # noqa: N801 - spelled like the module it stands in for
     def shutdown() -> None:
         from .parallel.dist import cleanup_distributed
         cleanup_distributed()
+
+
+# ---- ``from ray import serve`` / ``from ray.serve.llm import LLMConfig, build_openai_app`` (Deployment/Ray/serve_run_examples) ----
+from .serve.deploy import LLMConfig, build_openai_app  # noqa: E402,F401
+
+
+class serve:  # noqa: N801
+    """``serve.run(llm_app, route_prefix="/")``; ``serve deploy file.yaml`` is ``recipes.tools serve-deploy file.yaml``."""
+
+    @staticmethod
+    def run(app, route_prefix: str = "/", blocking: bool = True, host: str = "0.0.0.0", port: int = 8000, **kw):
+        from .serve.deploy import run
+        return run(app, host=host, port=port, route_prefix=route_prefix, blocking=blocking, **kw)

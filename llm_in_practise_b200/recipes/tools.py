@@ -17,6 +17,8 @@
 * ``moderation`` the Llama-Guard moderation wrapper service (Deployment/litellm-proxy/llama-guard-wrapper/app.py)
 * ``bench-serve`` the HTTP serving benchmark with ``vllm bench serve``'s flags and result keys (serve/bench_client.py;
                  LLM_on_Kubernetes/Inference_Platfrom/README.md:1361-1375)
+* ``serve-deploy`` ``serve deploy <file>.yaml`` of the Ray Serve recipes: every application of the YAML at its route prefix
+                 (Deployment/Ray/serve_deploy_examples/*.yaml; serve/deploy.py::deploy_yaml)
 * ``preload``    mirror a model directory into the node-local cache behind a ``.ready`` marker
                  (LLM_on_Kubernetes/Inference_Platfrom/02-Preloader/model-preloader-daemonset.yaml:44-78)
 * ``autoscale``  poll replicas' ``/metrics`` and print the replica count the KEDA ScaledObject would set
@@ -87,6 +89,10 @@ def main(argv=None):
     ro.add_argument("--config", required=True, help="YAML in the reference's litellm-config-router-lb.yaml shape")
     ro.add_argument("--port", type=int, default=4000)
     ro.add_argument("--master-key", default=os.getenv("LITELLM_MASTER_KEY"))
+    sd = sub.add_parser("serve-deploy", help="serve a Ray Serve LLM YAML (serve/deploy.py)")
+    sd.add_argument("config")
+    sd.add_argument("--host", default="0.0.0.0")
+    sd.add_argument("--port", type=int, default=8000)
     bs = sub.add_parser("bench-serve", help="HTTP serving benchmark (serve/bench_client.py)")
     bs.add_argument("rest", nargs=argparse.REMAINDER)
     pl = sub.add_parser("preload", help="model preloader (serve/platform.preload_model)")
@@ -128,6 +134,10 @@ def main(argv=None):
             if ph != "Progressing":
                 return ph
             time.sleep(a.interval)
+    if a.cmd == "serve-deploy":
+        from ..serve import deploy
+        app = deploy.deploy_yaml(a.config)
+        return None if app is None else deploy.run(app, a.host, a.port)
     if a.cmd == "bench-serve":
         from ..serve.bench_client import main as bench_main
         return bench_main(a.rest)

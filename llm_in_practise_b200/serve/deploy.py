@@ -218,6 +218,54 @@ def build_openai_app(args: Dict[str, Any], engines: Optional[Dict[str, Any]] = N
     return root
 
 
+def run(app, host: str = "0.0.0.0", port: int = 8000, route_prefix: str = "/", blocking: bool = True, **uvicorn_kw):
+    """``serve.run(llm_app, route_prefix="/")`` (Deployment/Ray/serve_run_examples/deepseek.py:44-47): serve the app with
+    uvicorn, under ``route_prefix`` when it is not the root."""
+    import uvicorn
+    from fastapi import FastAPI
+    if route_prefix not in ("", "/"):
+        root = FastAPI(title="llm_in_practise_b200 serve")
+        root.mount(route_prefix.rstrip("/"), app)
+        app = root
+    if not blocking:
+        import threading
+        server = uvicorn.Server(uvicorn.Config(app, host=host, port=port, **uvicorn_kw))
+        threading.Thread(target=server.run, name="b200-serve", daemon=True).start()
+        return server
+    return uvicorn.run(app, host=host, port=port, **uvicorn_kw)
+
+
+def deploy_yaml(path: str, engines: Optional[Dict[str, Any]] = None):
+    """``serve deploy <file>.yaml``: one FastAPI app for the whole file — every application of the YAML is built with
+    ``build_openai_app`` and mounted at its ``route_prefix`` (the two-models-two-routes layout of
+    Deployment/Ray/serve_deploy_examples/serve_app_two_models.yaml). Under torchrun (tensor- / pipeline-parallel replicas)
+    the ranks other than 0 never return from here: they follow rank 0's engine until it shuts down."""
+    from fastapi import FastAPI
+    apps = load_serve_yaml(path)
+    if not apps:
+        raise ValueError(f"{path} lists no applications")
+    built = []
+    for a in apps:
+        cfgs = a["llm_configs"]
+        engs = dict(engines or {})
+        for c in cfgs:
+            if c.model_id not in engs:
+                engs[c.model_id] = build_engine(c)
+            if getattr(engs[c.model_id], "rank", 0) != 0:
+                engs[c.model_id].serve_forever()               # follower rank of a parallel replica
+                return None
+        built.append((a["route_prefix"] or "/", build_openai_app({"llm_configs": cfgs}, engines=engs)))
+    if len(built) == 1 and built[0][0] in ("", "/"):
+        return built[0][1]
+    root = FastAPI(title="llm_in_practise_b200 serve deploy")
+    for prefix, app in sorted(built, key=lambda x: -len(x[0])):          # longest prefix first; "/" last
+        if prefix in ("", "/"):
+            root.mount("", app)
+        else:
+            root.mount(prefix.rstrip("/"), app)
+    return root
+
+
 def load_serve_yaml(path: str) -> List[Dict[str, Any]]:
     """Parse a ``serve deploy`` YAML: returns [{name, route_prefix, llm_configs: [LLMConfig]}]."""
     import yaml

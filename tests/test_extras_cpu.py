@@ -180,3 +180,51 @@ def test_autoscaling_replica_set_follows_the_ray_serve_rule():
             raise AssertionError("expected back-pressure")
         except RuntimeError as e:
             assert "back-pressure" in str(e)
+
+
+def test_serve_deploy_yaml_mounts_every_application_at_its_route(tmp_path):
+    """``serve deploy`` of the two-models-two-routes YAML: each application answers under its own ``route_prefix``."""
+    import textwrap
+    import torch
+    from fastapi.testclient import TestClient
+    from llm_in_practise_b200 import compat
+    from llm_in_practise_b200.data.tokenizers import ByteTokenizer
+    from llm_in_practise_b200.models.qwen3 import QWEN3_PRESETS, Qwen3ForCausalLM
+    from llm_in_practise_b200.serve import EngineArgs, LLMEngine
+    from llm_in_practise_b200.serve.deploy import deploy_yaml
+    y = tmp_path / "two.yaml"
+    y.write_text(textwrap.dedent("""
+        applications:
+          - name: qwen3_8b_app
+            route_prefix: /qwen3-8b
+            import_path: ray.serve.llm:build_openai_app
+            args:
+              llm_configs:
+                - model_loading_config: {model_id: qwen3-8b, model_source: /models/a}
+                  engine_kwargs: {tensor_parallel_size: 1, max_model_len: 64}
+          - name: qwen3_4b_awq_app
+            route_prefix: /qwen3-4b-awq
+            import_path: ray.serve.llm:build_openai_app
+            args:
+              llm_configs:
+                - model_loading_config: {model_id: qwen3-4b-awq, model_source: /models/b}
+                  engine_kwargs: {quantization: awq, max_model_len: 64}
+    """))
+    torch.manual_seed(0)
+    m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32, device="cpu")
+    engines = {n: LLMEngine(m, ByteTokenizer(), EngineArgs(max_num_seqs=2, max_model_len=64, warmup=False), model_name=n)
+               for n in ("qwen3-8b", "qwen3-4b-awq")}
+    app = deploy_yaml(str(y), engines=engines)
+    try:
+        c = TestClient(app)
+        for name in engines:
+            body = {"model": name, "messages": [{"role": "user", "content": "hi"}], "max_tokens": 3, "temperature": 0}
+            r = c.post(f"/{name}/v1/chat/completions", json=body)
+            assert r.status_code == 200 and r.json()["model"] == name
+            assert c.get(f"/{name}/v1/models").json()["data"][0]["id"] == name
+        assert c.post("/v1/chat/completions", json={"model": "qwen3-8b", "messages": []}).status_code == 404      # no app at the root
+        # serve.run(app, blocking=False) returns a server object whose thread can be stopped
+        assert callable(compat.serve.run) and compat.build_openai_app is not None
+    finally:
+        for e in engines.values():
+            e.shutdown()
