@@ -155,3 +155,38 @@ class serve:  # noqa: N801
     def run(app, route_prefix: str = "/", blocking: bool = True, host: str = "0.0.0.0", port: int = 8000, **kw):
         from .serve.deploy import run
         return run(app, host=host, port=port, route_prefix=route_prefix, blocking=blocking, **kw)
+
+
+# ---- ``import evaluate`` (HF_Basics/trainer_demo.py:66-75, accelerate_demo.py:58-66): the classification metrics ----------------
+class _Metric:
+    def __init__(self, name: str):
+        if name not in ("accuracy", "f1", "precision", "recall"):
+            raise ValueError(f"metric {name!r} is not provided (accuracy, f1, precision, recall are)")
+        self.name = name
+
+    def compute(self, predictions=None, references=None, average: str = "binary", pos_label: int = 1, **_):
+        import numpy as np
+        p, r = np.asarray(predictions).reshape(-1), np.asarray(references).reshape(-1)
+        if self.name == "accuracy":
+            return {"accuracy": float((p == r).mean()) if len(r) else 0.0}
+        labels = [pos_label] if average == "binary" else sorted(set(r.tolist()) | set(p.tolist()))
+        per, weights = [], []
+        for c in labels:
+            tp, fp, fn = float(((p == c) & (r == c)).sum()), float(((p == c) & (r != c)).sum()), float(((p != c) & (r == c)).sum())
+            prec = tp / (tp + fp) if tp + fp else 0.0
+            rec = tp / (tp + fn) if tp + fn else 0.0
+            f1 = 2 * prec * rec / (prec + rec) if prec + rec else 0.0
+            per.append({"precision": prec, "recall": rec, "f1": f1}[self.name])
+            weights.append(float((r == c).sum()))
+        if average == "micro" and self.name in ("precision", "recall", "f1"):
+            return {self.name: float((p == r).mean())}          # single-label: micro P = R = F1 = accuracy
+        if average == "weighted":
+            tot = sum(weights) or 1.0
+            return {self.name: float(sum(v * w for v, w in zip(per, weights)) / tot)}
+        return {self.name: float(sum(per) / max(1, len(per)))}
+
+
+class evaluate:  # noqa: N801
+    @staticmethod
+    def load(name: str, *_, **__) -> _Metric:
+        return _Metric(name)

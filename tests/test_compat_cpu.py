@@ -112,3 +112,20 @@ def test_deepspeed_style_loop_with_only_its_imports_changed(tmp_path):
     engine.save_checkpoint(str(tmp_path / "ck"), tag="epoch_1")
     assert os.path.exists(tmp_path / "ck" / "latest")
     deepspeed.shutdown()
+
+
+def test_evaluate_shim_matches_sklearn():
+    sk = pytest.importorskip("sklearn.metrics")
+    import numpy as np
+    from llm_in_practise_b200.compat import evaluate
+    rng = np.random.default_rng(0)
+    y, p = rng.integers(0, 3, 200), rng.integers(0, 3, 200)
+    assert evaluate.load("accuracy").compute(predictions=p, references=y)["accuracy"] == pytest.approx(sk.accuracy_score(y, p))
+    for avg in ("macro", "weighted", "micro"):
+        for name, fn in (("f1", sk.f1_score), ("precision", sk.precision_score), ("recall", sk.recall_score)):
+            got = evaluate.load(name).compute(predictions=p, references=y, average=avg)[name]
+            assert got == pytest.approx(fn(y, p, average=avg, zero_division=0)), (name, avg)
+    yb, pb = (y > 0).astype(int), (p > 0).astype(int)
+    assert evaluate.load("f1").compute(predictions=pb, references=yb)["f1"] == pytest.approx(sk.f1_score(yb, pb))
+    with pytest.raises(ValueError):
+        evaluate.load("bleu")
