@@ -55,6 +55,13 @@ def _calibration_rows(path, n):
 
 
 def main(argv=None):
+    argv = list(sys.argv[1:] if argv is None else argv)
+    if argv and argv[0] in ("loadtest", "bench-serve"):       # pass-through commands: their own parsers see every flag
+        if argv[0] == "loadtest":
+            from ..serve.loadtest import main as lt
+            return lt(argv[1:])
+        from ..serve.bench_client import main as bench_main
+        return bench_main(argv[1:])
     ap = argparse.ArgumentParser(description=__doc__, formatter_class=argparse.RawDescriptionHelpFormatter)
     sub = ap.add_subparsers(dest="cmd", required=True)
     m = sub.add_parser("merge")

@@ -163,3 +163,16 @@ def test_serve_accepts_the_vllm_flags_of_the_compose_files(monkeypatch):
     assert eng.model.layers[0].qkv_proj.nf4 is not None   # the decoder projections were quantised to NF4
     with pytest.raises(SystemExit):
         infer.main(["serve", "--model", "qwen3-tiny", "--quantization", "awq"])          # not an AWQ checkpoint
+
+
+def test_tools_passthrough_commands_see_their_own_flags(capsys):
+    """``tools bench-serve --base-url …`` / ``tools loadtest --host …``: flags go to the sub-tool's parser (argparse's REMAINDER
+    would have refused a leading option)."""
+    from llm_in_practise_b200.recipes import tools
+    out = tools.main(["bench-serve", "--base-url", "http://127.0.0.1:9", "--model", "x", "--num-prompts", "2",
+                      "--random-input-len", "4", "--random-output-len", "2"])
+    assert out["completed"] == 0 and out["failed"] == 2 and out["num_prompts"] == 2       # nothing listens on port 9
+    assert "Serving Benchmark Result" in capsys.readouterr().out
+    with pytest.raises(SystemExit) as e:
+        tools.main(["loadtest", "--help"])
+    assert e.value.code == 0 and "--profile" in capsys.readouterr().out
