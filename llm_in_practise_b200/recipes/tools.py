@@ -160,7 +160,8 @@ def main(argv=None):
                 p = torch.cuda.get_device_properties(i)
                 print(f"GPU {i}: {p.name}, sm_{p.major}{p.minor}, {p.total_memory / 2 ** 30:.0f} GiB, {p.multi_processor_count} SMs")
         from ..ops import _native as nv
-        print("libb200ops:", nv.lib_path(), "present" if nv.available() else "NOT BUILT")
+        state = "NOT BUILT" if not nv.lib_path().exists() else ("loadable" if nv.available() else "built (no CUDA device here: CPU paths run)")
+        print("libb200ops:", nv.lib_path(), state)
         return
     if a.cmd == "loadtest":
         from ..serve.loadtest import main as lt
