@@ -37,7 +37,7 @@ class CharTokenizer:
     def encode(self, s: str, unk: int = 0) -> List[int]:
         return [self.stoi.get(c, unk) for c in s]
 
-    def decode(self, ids: Iterable[int]) -> str:
+    def decode(self, ids: Iterable[int], skip_special_tokens: bool = True, **_) -> str:
         return "".join(self.itos.get(int(i), "") for i in ids)
 
 
@@ -48,7 +48,7 @@ class ByteTokenizer:
     def encode(self, s: str) -> List[int]:
         return list(s.encode("utf-8"))
 
-    def decode(self, ids: Iterable[int]) -> str:
+    def decode(self, ids: Iterable[int], skip_special_tokens: bool = True, **_) -> str:
         return bytes(int(i) & 0xFF for i in ids).decode("utf-8", errors="replace")
 
     def __call__(self, texts, **_):

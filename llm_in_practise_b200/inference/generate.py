@@ -494,6 +494,14 @@ class Generator:
     @torch.no_grad()
     def generate(self, input_ids: torch.Tensor, config: Optional[GenerationConfig] = None, streamer=None,
                  seed: Optional[int] = None, return_logprobs: bool = False, **kw):
+        try:
+            return self._generate(input_ids, config, streamer, seed, return_logprobs, **kw)
+        finally:
+            if streamer is not None:
+                streamer.end()            # also when generation raised: the thread reading the streamer must not wait for ever
+
+    def _generate(self, input_ids: torch.Tensor, config: Optional[GenerationConfig], streamer, seed: Optional[int],
+                  return_logprobs: bool, **kw):
         cfg = config or GenerationConfig(**{k: v for k, v in kw.items() if k in GenerationConfig.__dataclass_fields__})
         eos = cfg.eos_token_id
         eos = [] if cfg.ignore_eos else ([eos] if isinstance(eos, int) else list(eos or []))
@@ -538,8 +546,6 @@ class Generator:
                 cache.len += 1
             else:
                 logits = self._decode(nxt, cache)
-        if streamer is not None:
-            streamer.end()
         self.model.train(was)
         return (out, torch.stack(logprobs, 1)) if return_logprobs else out
 
@@ -550,11 +556,34 @@ class TextIteratorStreamer:
     def __init__(self, tokenizer, skip_prompt: bool = True, timeout: Optional[float] = None, **decode_kw):
         self.tok, self.q, self.timeout, self.kw = tokenizer, queue.Queue(), timeout, decode_kw
         self._end = object()
+        self._ids: List[int] = []          # tokens of the current line, decoded together: a character may span tokens
+        self._sent = 0                     # characters of that decoding already handed out
+        self._ended = False
 
     def put(self, ids: torch.Tensor) -> None:
-        self.q.put(self.tok.decode(ids.reshape(-1).tolist(), **self.kw))
+        """New token(s) of ONE sequence. Byte-level vocabularies split multi-byte characters (most CJK text) over several
+        tokens, so the text is re-decoded from the start of the line and only complete characters are emitted."""
+        self._ids.extend(int(i) for i in ids.reshape(-1).tolist())
+        text = self.tok.decode(self._ids, **self.kw)
+        if text.endswith("\ufffd"):
+            return                         # an unfinished character: wait for its remaining bytes
+        piece, self._sent = text[self._sent:], len(text)
+        if piece:
+            self.q.put(piece)
+        if text.endswith("\n"):
+            self._ids, self._sent = [], 0  # a new line cannot change how the earlier text decodes
 
     def end(self) -> None:
+        if self._ended:
+            return
+        self._ended = True
+        if self._ids:
+            try:
+                tail = self.tok.decode(self._ids, **self.kw)[self._sent:]
+            except Exception:              # the failure that ended generation must not also block the reader
+                tail = ""
+            if tail:
+                self.q.put(tail)
         self.q.put(self._end)
 
     def __iter__(self) -> Iterator[str]:

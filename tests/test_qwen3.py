@@ -132,3 +132,51 @@ def test_transformers_call_surface_on_the_model(tmp_path):
     pm = get_peft_model(m, LoraConfig(r=2, lora_alpha=4, target_modules=["q_proj", "v_proj"]))
     pm.enable_input_require_grads()
     assert pm.device == torch.device("cpu") and pm.generate(**inputs, max_new_tokens=3, do_sample=False).shape == (1, 11)
+
+
+def test_streaming_thread_flow_of_the_webui_script():
+    """Scripts/inference/06-…streaming-infr.py:55-85: ``Thread(target=model.generate, kwargs=dict(**inputs, streamer=streamer, …))``
+    and ``for new_text in streamer``. The consumer also terminates when generation fails inside the thread."""
+    import threading
+    import torch
+    from llm_in_practise_b200.compat import TextIteratorStreamer
+    from llm_in_practise_b200.data.tokenizers import ByteTokenizer
+    from llm_in_practise_b200.models.qwen3 import QWEN3_PRESETS, Qwen3ForCausalLM
+    tok = ByteTokenizer()
+    torch.manual_seed(0)
+    m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32, device="cpu").eval()
+    ids = torch.tensor([tok.encode("hello")])
+    streamer = TextIteratorStreamer(tok, skip_prompt=True, skip_special_tokens=True, timeout=30)
+    kw = dict(input_ids=ids, attention_mask=torch.ones_like(ids), streamer=streamer, max_new_tokens=8, do_sample=False)
+    t = threading.Thread(target=m.generate, kwargs=kw)
+    t.start()
+    pieces = list(streamer)
+    t.join(30)
+    want = m.generate(ids, max_new_tokens=8, do_sample=False)[0, ids.shape[1]:].tolist()
+    assert not t.is_alive() and "".join(pieces) == tok.decode(want)
+
+    class Broken(ByteTokenizer):
+        def decode(self, ids, **kw):
+            raise RuntimeError("injected tokenizer failure")
+    s2 = TextIteratorStreamer(Broken(), skip_prompt=True, timeout=30)
+    t2 = threading.Thread(target=lambda: pytest.raises(RuntimeError, m.generate, ids, streamer=s2, max_new_tokens=4, do_sample=False))
+    t2.start()
+    assert list(s2) == []                                   # the iterator ends instead of waiting for ever
+    t2.join(30)
+    assert not t2.is_alive()
+
+
+def test_streamer_emits_whole_characters_only():
+    """Byte-level tokens cut multi-byte characters; the streamer holds back until a character is complete."""
+    import torch
+    from llm_in_practise_b200.data.tokenizers import ByteTokenizer
+    from llm_in_practise_b200.inference import TextIteratorStreamer
+    tok = ByteTokenizer()
+    text = "马哥教育\nok 云原生"
+    st = TextIteratorStreamer(tok, timeout=5)
+    for b in tok.encode(text):
+        st.put(torch.tensor([b]))
+    st.end()
+    pieces = list(st)
+    assert "".join(pieces) == text and all("�" not in p for p in pieces)
+    assert pieces[:4] == ["马", "哥", "教", "育"]                 # three bytes each, one piece per character
