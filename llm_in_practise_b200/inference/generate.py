@@ -592,6 +592,9 @@ class TextIteratorStreamer:
     def __next__(self) -> str:
         v = self.q.get(timeout=self.timeout)
         if v is self._end:
+            th = getattr(self, "thread", None)
+            if th is not None and th is not threading.current_thread():
+                th.join()                  # the producer is past its last token: let it finish before the caller moves on
             raise StopIteration
         return v
 
@@ -599,7 +602,8 @@ class TextIteratorStreamer:
 def stream_generate(gen: Generator, input_ids: torch.Tensor, tokenizer, **kw) -> Iterator[str]:
     st = TextIteratorStreamer(tokenizer)
     th = threading.Thread(target=lambda: gen.generate(input_ids, streamer=st, **kw), daemon=True)
-    th.start()
+    st.thread = th                         # joined by the iterator at the end of the stream (a daemon thread still inside
+    th.start()                             # native code at interpreter exit aborts the process)
     return st
 
 

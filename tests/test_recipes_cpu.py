@@ -176,3 +176,15 @@ def test_tools_passthrough_commands_see_their_own_flags(capsys):
     with pytest.raises(SystemExit) as e:
         tools.main(["loadtest", "--help"])
     assert e.value.code == 0 and "--profile" in capsys.readouterr().out
+
+
+def test_stream_command_exits_cleanly():
+    """``recipes.infer stream`` in its own process: the generation thread is joined before the interpreter shuts down (it used
+    to be killed inside native code: 'terminate called without an active exception', exit status 134)."""
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "llm_in_practise_b200.recipes.infer", "stream", "--model", "qwen3-tiny",
+                        "--max_new_tokens", "6", "--prompt", "hi"], cwd=root, capture_output=True, timeout=300)
+    assert r.returncode == 0, (r.returncode, r.stderr[-400:])
+    assert b"terminate called" not in r.stderr
