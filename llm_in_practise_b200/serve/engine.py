@@ -100,6 +100,8 @@ class EngineMetrics:
         self.steps = 0
         self.prefix_queries = 0          # prompt tokens looked up in the prefix cache (vllm:gpu_prefix_cache_queries)
         self.prefix_hits = 0             # ... and found there                        (vllm:gpu_prefix_cache_hits)
+        self.queue_sum = 0.0             # seconds requests spent waiting before admission (vllm:request_queue_time_seconds)
+        self.queue_count = 0
         self.host_hits = 0               # prompt tokens restored from the host tier instead of being recomputed
         self.host_offloads = 0           # rows copied to the host tier
 
@@ -610,6 +612,10 @@ class LLMEngine:
                     break
                 self.waiting.popleft()
             with self.metrics.lock:
+                if not getattr(r, "_queued_counted", False):      # a request put back for lack of blocks is counted once
+                    r._queued_counted = True
+                    self.metrics.queue_sum += time.perf_counter() - r.arrival
+                    self.metrics.queue_count += 1
                 self.metrics.prefix_queries += L
                 self.metrics.prefix_hits += max(P, Ph) if from_host else P
                 self.metrics.host_hits += Ph if from_host else 0

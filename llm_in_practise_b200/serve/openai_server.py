@@ -129,6 +129,8 @@ def render_metrics(engine: LLMEngine) -> str:
         out.append(f"vllm:time_to_first_token_seconds_count{lab} {cum}")
         out.append(f"vllm:time_to_first_token_seconds_sum{lab} {m.ttft_sum}")
         counter("vllm:e2e_request_latency_seconds_sum", m.e2e_sum, "Sum of end to end request latency in seconds.")
+        counter("vllm:request_queue_time_seconds_sum", m.queue_sum, "Sum of the time requests spent in the waiting queue.")
+        counter("vllm:request_queue_time_seconds_count", m.queue_count, "Requests that left the waiting queue.")
     return "\n".join(out) + "\n"
 
 

@@ -522,7 +522,8 @@ class Router:
             ttft = metric_sum(s, "vllm:time_to_first_token_seconds_sum") / n * 1000.0 if n else 0.0
             d.load = {"pending_requests": metric_sum(s, "vllm:num_requests_waiting"),
                       "gpu_cache_usage": metric_sum(s, "vllm:gpu_cache_usage_perc"), "ttft_ms": ttft,
-                      "queue_time_ms": metric_sum(s, "vllm:request_queue_time_seconds_sum") / n * 1000.0 if n else 0.0}
+                      "queue_time_ms": (metric_sum(s, "vllm:request_queue_time_seconds_sum") * 1000.0 /
+                                        (metric_sum(s, "vllm:request_queue_time_seconds_count") or n)) if n else 0.0}
 
     def metrics_text(self) -> str:
         lines = ["# TYPE router_deployment_requests_total counter", "# TYPE router_deployment_failures_total counter",

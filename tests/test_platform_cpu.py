@@ -356,3 +356,35 @@ def test_keda_replica_set_starts_and_drains_engines():
         clk.t += 15
         rs.tick()
     assert len(rs.engines) == 1 and [ev[1] for ev in rs.events].count("stopped") == 2
+
+
+def test_queue_time_metric_feeds_the_load_score():
+    """``vllm:request_queue_time_seconds`` (the fourth figure llm-d weighs): exported by the engine, read by ``refresh_load``."""
+    import time
+    import torch
+    from llm_in_practise_b200.data.tokenizers import ByteTokenizer
+    from llm_in_practise_b200.inference import GenerationConfig
+    from llm_in_practise_b200.models.qwen3 import QWEN3_PRESETS, Qwen3ForCausalLM
+    from llm_in_practise_b200.serve import EngineArgs, LLMEngine
+    from llm_in_practise_b200.serve.openai_server import render_metrics
+    from llm_in_practise_b200.serve.router import Deployment, Router
+    torch.manual_seed(0)
+    m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32, device="cpu")
+    eng = LLMEngine(m, ByteTokenizer(), EngineArgs(max_num_seqs=1, max_model_len=64, warmup=False), model_name="tiny")
+    reqs = [eng.submit([1, 2, 3], GenerationConfig(max_new_tokens=2, do_sample=False)) for _ in range(3)]
+    time.sleep(0.05)                                              # everybody waits at least this long
+    while not all(r.done.is_set() for r in reqs):
+        eng.step()
+    s = P.parse_prometheus_text(render_metrics(eng))
+    assert P.metric_sum(s, "vllm:request_queue_time_seconds_count") == 3
+    assert P.metric_sum(s, "vllm:request_queue_time_seconds_sum") >= 3 * 0.05
+
+    async def fetch():
+        return render_metrics(eng)
+
+    async def noop(path, payload):
+        return 200, {}
+    d = Deployment(model_name="tiny", upstream_model="tiny", transport=noop, metrics_fn=fetch)
+    r = Router([d], routing_strategy="load-aware-prefix")
+    asyncio.run(r.refresh_load())
+    assert d.load["queue_time_ms"] >= 50.0 and d.load["ttft_ms"] > 0
