@@ -148,6 +148,9 @@ def from_pretrained(path: str, dtype: torch.dtype = torch.bfloat16, torch_dtype:
         if quantization_config is not None and quantization_config.load_in_4bit:
             model.quantize_nf4(quantization_config.bnb_4bit_use_double_quant)
         return model
+    if not os.path.isfile(os.path.join(path, "config.json")):
+        raise FileNotFoundError(f"{path!r} is neither a local checkpoint directory (no config.json there) nor one of the presets "
+                                f"{sorted(QWEN3_PRESETS)}; hub ids cannot be downloaded here — pass the directory the weights are in")
     with open(os.path.join(path, "config.json")) as f:
         cfg = config_from_hf(json.load(f))
     if "rope_scaling" in extra:
