@@ -1,3 +1,4 @@
+"""MoE dispatch / grouped expert path against the per-expert loop, and DeepSeekLike (MLA + MoE) training on CPU."""
 
 
 def test_moe_dispatch_and_grouped_reference_path():
