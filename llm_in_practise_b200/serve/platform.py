@@ -606,3 +606,44 @@ def keda_replica_set(factory: Callable[[], Any], scaler: KedaScaler, clock: Call
             return len(self.engines)
 
     return KedaReplicaSet()
+
+
+# ------------------------------------------------------------------------------------------ canary acting on replicas
+class CanaryReplicaSet:
+    """Two sets of in-process engines behind one ``submit``: requests go to the canary set with the rollout's current
+    weight, ``tick()`` advances the rollout on the canary engines' own ``/metrics`` text (plus this process's GPU memory
+    gauges), and the outcome is applied — ``Healthy``: the canary engines become the stable set and the old ones drain and
+    shut down; ``Degraded``: the canary engines drain and shut down, all traffic is back on the stable set."""
+
+    def __init__(self, stable: Sequence[Any], canary: Sequence[Any], rollout: Optional[CanaryRollout] = None, seed: Optional[int] = None):
+        import random
+        self.stable, self.canary = list(stable), list(canary)
+        self.rollout = rollout or CanaryRollout()
+        self.draining: List[Any] = []
+        self._rng = random.Random(seed)
+        self.sent = {"stable": 0, "canary": 0}
+
+    def submit(self, prompt_ids, cfg=None):
+        eng = self.rollout.pick(self.stable, self.canary, self._rng)
+        self.sent["canary" if any(eng is c for c in self.canary) else "stable"] += 1
+        return eng.submit(prompt_ids, cfg)
+
+    def _scrape(self) -> List[str]:
+        from .openai_server import render_metrics
+        return [render_metrics(e) for e in self.canary] + [gpu_memory_metrics_text()]
+
+    def tick(self) -> str:
+        for e in list(self.draining):
+            if e.num_running + e.num_waiting == 0:
+                self.draining.remove(e)
+                if hasattr(e, "shutdown"):
+                    e.shutdown()
+        before = self.rollout.phase
+        phase = self.rollout.advance(self._scrape if self.canary else None)
+        if phase != before and phase == "Healthy" and self.canary:
+            self.draining += self.stable
+            self.stable, self.canary = self.canary, []
+        elif phase != before and phase == "Degraded":
+            self.draining += self.canary
+            self.canary = []
+        return phase

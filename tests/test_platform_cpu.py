@@ -388,3 +388,49 @@ def test_queue_time_metric_feeds_the_load_score():
     r = Router([d], routing_strategy="load-aware-prefix")
     asyncio.run(r.refresh_load())
     assert d.load["queue_time_ms"] >= 50.0 and d.load["ttft_ms"] > 0
+
+
+def test_canary_replica_set_promotes_and_rolls_back_real_engines():
+    import torch
+    from llm_in_practise_b200.data.tokenizers import ByteTokenizer
+    from llm_in_practise_b200.inference import GenerationConfig
+    from llm_in_practise_b200.models.qwen3 import QWEN3_PRESETS, Qwen3ForCausalLM
+    from llm_in_practise_b200.serve import EngineArgs, LLMEngine
+    torch.manual_seed(0)
+    m = Qwen3ForCausalLM(QWEN3_PRESETS["qwen3-tiny"], dtype=torch.float32, device="cpu")
+    mk = lambda n: LLMEngine(m, ByteTokenizer(), EngineArgs(max_num_seqs=2, max_model_len=64, warmup=False), model_name=n)
+    cfg = GenerationConfig(max_new_tokens=2, do_sample=False)
+    gate = [mt for mt in P.smoke_template() if mt.name != "gpu-memory-saturation"]          # no GPU exporter on this machine
+    for t in gate:
+        t.count = 2
+    steps = ({"setWeight": 50}, {"pause": {"duration": "1m"}}, {"analysis": {}}, {"setWeight": 100})
+
+    def run(fail: bool):
+        clk = Clock()
+        stable, canary = mk("v1"), mk("v2")
+        rs = P.CanaryReplicaSet([stable], [canary], P.CanaryRollout(steps, template=lambda: gate, clock=clk), seed=0)
+        phase = "Progressing"
+        for _ in range(12):
+            reqs = [rs.submit([1, 2, 3], cfg) for _ in range(8)]
+            for e in (stable, canary):
+                while e.num_waiting or e.num_running:
+                    e.step()
+            if fail:                                            # the new version errors on what it is given
+                with canary.metrics.lock:
+                    canary.metrics.requests_finished["error"] = canary.metrics.requests_finished.get("error", 0) + 4
+            phase = rs.tick()
+            if phase != "Progressing":
+                break
+            clk.t += 60
+        return rs, stable, canary, phase
+    rs, stable, canary, phase = run(fail=False)
+    assert phase == "Healthy" and rs.stable == [canary] and rs.canary == []
+    assert rs.sent["canary"] > 0 and rs.sent["stable"] > 0                    # traffic was split while the rollout ran
+    rs.tick()
+    assert rs.draining == []                                                  # the old version drained and was shut down
+    rs, stable, canary, phase = run(fail=True)
+    assert phase == "Degraded" and rs.stable == [stable] and rs.canary == []
+    n0 = rs.sent["stable"]
+    for _ in range(5):
+        rs.submit([1, 2, 3], cfg)
+    assert rs.sent["stable"] == n0 + 5                                         # everything is back on the stable version
