@@ -29,7 +29,7 @@ import re
 import shutil
 import time
 from collections import OrderedDict, deque
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Any, Callable, Deque, Dict, Iterable, List, Optional, Sequence, Tuple
 
 Labels = Tuple[Tuple[str, str], ...]
